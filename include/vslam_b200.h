@@ -1,0 +1,103 @@
+/*
+ * vslam_b200.h -- C ABI of libvslam_b200.so (sm_100a only).
+ *
+ * This is the drop-in boundary for the match -> RANSAC pose -> bundle adjustment
+ * hot path of juuso-oskari/visual_slam src/v2.  The reference has no FFI layer of
+ * its own (it is pure Python over the cv2 and g2o wheels), so every entry point
+ * below cites the reference call site whose third-party native call it replaces.
+ *
+ * Conventions
+ *   - every pointer marked "dev" is a DEVICE pointer (HBM); the caller owns all
+ *     buffers; the library allocates nothing on the data path except the opaque
+ *     BA problem object (vslam_ba_create / vslam_ba_destroy).
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).
+ *   - every function returns a vslam_status; 0 is success.  Nothing falls back
+ *     to the CPU: without a B200 the calls fail with VSLAM_ERR_CUDA.
+ */
+#ifndef VSLAM_B200_H
+#define VSLAM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  VSLAM_OK = 0,
+  VSLAM_ERR_BAD_ARG = 1,    /* null pointer, negative size, size over a documented limit */
+  VSLAM_ERR_ALIGNMENT = 2,  /* descriptor buffers must be 16-byte aligned */
+  VSLAM_ERR_CUDA = 3,       /* a CUDA runtime call failed; see vslam_last_cuda_error() */
+  VSLAM_ERR_NUMERIC = 4,    /* solver breakdown reported in-band (PCG indefinite, ...) */
+  VSLAM_ERR_NO_DEVICE = 5
+} vslam_status;
+
+const char* vslam_status_string(int status);
+const char* vslam_last_cuda_error(void);
+/* ABI version of this header; bumped on any signature change. */
+int vslam_abi_version(void);
+/* Number of SMs of the current device (148 on B200), or <0 on error. */
+int vslam_device_sm_count(void);
+
+/* ------------------------------------------------------------------------- */
+/* 1. Descriptor matching                                                     */
+/* ------------------------------------------------------------------------- */
+
+/* Limits of the packed (distance, index) keys used by the kNN kernels. */
+#define VSLAM_HAMMING_MAX_N (1 << 22)
+#define VSLAM_DESC_BYTES 32
+
+/*
+ * Brute-force 256-bit Hamming kNN, k = 2, for `batch` independent frame pairs.
+ * Replaces cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(desc1, desc2, k=2)
+ * (reference: src/v2/frame.py:23, ORB variant of frame.py:8/18).
+ *
+ *   q        dev  uint8 [batch][nq][32]   query descriptors (desc1)
+ *   t        dev  uint8 [batch][nt][32]   train descriptors (desc2)
+ *   idx      dev  int32 [batch][nq][2]    trainIdx of best / second best
+ *   dist     dev  int32 [batch][nq][2]    their Hamming distances
+ *   rev_key  dev  uint32[batch][nt] or NULL.  When non-NULL the same pass also
+ *            produces, for every train row, the packed key (distance << 22 | q)
+ *            of its nearest query with first-min tie-break (the cross-check
+ *            direction, reference semantics src/slam.py:40-47).  The kernel
+ *            initialises it; the caller need not.
+ *
+ * Order and ties are bit-exact with OpenCV: ascending (distance, trainIdx).
+ * If nt < 2 the missing entries are idx = -1, dist = -1.
+ * nq, nt <= VSLAM_HAMMING_MAX_N.
+ */
+int vslam_hamming_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt,
+                       int32_t* idx, int32_t* dist, uint32_t* rev_key,
+                       int batch, void* stream);
+
+/*
+ * Lowe ratio test (+ optional mutual-nearest cross-check) and order-preserving
+ * compaction.  Replaces the Python loop src/v2/frame.py:30-42.
+ *
+ *   idx, dist  dev  outputs of vslam_hamming_knn2
+ *   rev_key    dev  as produced by vslam_hamming_knn2 (required iff cross_check)
+ *   ratio      the reference compares float32 distances in float64:
+ *              keep iff (double)d0 < ratio * (double)d1     (frame.py:33)
+ *   keep_q     dev  int32 [batch][nq]  kept query indices, ascending, padded -1
+ *   keep_t     dev  int32 [batch][nq]  their trainIdx,               padded -1
+ *   n_keep     dev  int32 [batch]
+ */
+int vslam_match_filter(const int32_t* idx, const int32_t* dist,
+                       const uint32_t* rev_key, int nq, int nt, double ratio,
+                       int cross_check, int32_t* keep_q, int32_t* keep_t,
+                       int32_t* n_keep, int batch, void* stream);
+
+/*
+ * Integer-pipe microbenchmark used for the matching roofline:
+ * runs `iters` dependent-free popc.b32 per thread on a full grid and returns
+ * the achieved popc/s in *popc_per_s (host pointer).
+ */
+int vslam_microbench_popc(int iters, double* popc_per_s, void* stream);
+
+/* Tuning knob for bench sweeps: selects a tile/thread variant of the kNN kernel (0 = default). */
+int vslam_hamming_set_variant(int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VSLAM_B200_H */

@@ -1,0 +1,97 @@
+"""GPU parity: CUDA Hamming kNN-2 + ratio + cross-check vs the oracle, bit-exact."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import matching as om
+from visual_slam_b200 import FeatureMatcher, match_batch, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def run_gpu(q, t, ratio=0.8, cross=True):
+    out = match_batch(torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda(), ratio, cross)
+    torch.cuda.synchronize()
+    return {k: (v.cpu().numpy() if v is not None else None) for k, v in out.items()}
+
+
+def check_pair(q, t, ratio=0.8):
+    for cross in (False, True):
+        g = run_gpu(q[None], t[None], ratio, cross)
+        idx, dist = om.knn2_numpy(q, t)
+        assert np.array_equal(g["idx"][0], idx)
+        assert np.array_equal(g["dist"][0], dist)
+        rev_idx = None
+        if cross and q.shape[0] and t.shape[0]:
+            rev_idx, rev_d = om.rev_nearest_numpy(q, t)
+            key = g["rev_key"][0].view(np.uint32)
+            assert np.array_equal((key & ((1 << 22) - 1)).astype(np.int32), rev_idx)
+            assert np.array_equal((key >> 22).astype(np.int32), rev_d)
+        kq, kt = om.filter_numpy(idx, dist, ratio, rev_idx)
+        n = int(g["n_keep"][0])
+        assert n == len(kq)
+        assert np.array_equal(g["keep_q"][0, :n], kq) and np.array_equal(g["keep_t"][0, :n], kt)
+        assert (g["keep_q"][0, n:] == -1).all()
+
+
+@pytest.mark.parametrize("nq,nt", [(1, 2), (2, 2), (31, 33), (33, 31), (2000, 2049), (2049, 2000),
+                                   (513, 1025), (5, 1), (1, 1)])
+def test_ragged_sizes_random_and_ties(nq, nt):
+    q, t, _ = synth.descriptors_pair(nq, nt, seed=nq + nt)
+    check_pair(q, t)
+    q, t = synth.low_entropy_pair(nq, nt, seed=nq * 7 + nt)
+    check_pair(q, t, ratio=0.95)
+
+
+def test_golden_reference_vectors(golden_dir):
+    gold = np.load(os.path.join(golden_dir, "matching_icl_orb.npz"))
+    for case, ratio in (("icl", 0.8), ("tie", 0.95)):
+        q, t = gold[case + "_desc1"], gold[case + "_desc2"]
+        g = run_gpu(q[None], t[None], ratio, cross=False)
+        assert np.array_equal(g["idx"][0], gold[case + "_idx"])
+        assert np.array_equal(g["dist"][0], gold[case + "_dist"])
+        n = int(g["n_keep"][0])
+        assert np.array_equal(g["keep_q"][0, :n], gold[case + "_keep_q"])
+        assert np.array_equal(g["keep_t"][0, :n], gold[case + "_keep_t"])
+        g = run_gpu(q[None], t[None], 10.0, cross=True)  # ratio never rejects: pure mutual-NN
+        n = int(g["n_keep"][0])
+        pairs = np.stack([g["keep_q"][0, :n], g["keep_t"][0, :n]], axis=1)
+        keep_all = gold[case + "_dist"][:, 1] > 0  # ratio 10 still rejects d1 == 0 (0 < 0 false)
+        want = np.array([r for r in gold[case + "_mutual"] if keep_all[r[0]]]).reshape(-1, 2)
+        assert np.array_equal(pairs, want)
+
+
+def test_drop_in_feature_matcher_matches_reference_wrapper(golden_dir):
+    gold = np.load(os.path.join(golden_dir, "matching_icl_orb.npz"))
+    kp1, kp2, d1, d2 = (gold["icl_" + k] for k in ("kp1", "kp2", "desc1", "desc2"))
+    matches, p1, f1, p2, f2 = FeatureMatcher().match_features(kp1, d1, kp2, d2)
+    assert [m[0].queryIdx for m in matches] == gold["icl_keep_q"].tolist()
+    assert [m[0].trainIdx for m in matches] == gold["icl_keep_t"].tolist()
+    assert np.array_equal(p1, gold["icl_pts1"]) and np.array_equal(p2, gold["icl_pts2"])
+    assert np.array_equal(f1, d1[gold["icl_keep_q"]]) and np.array_equal(f2, d2[gold["icl_keep_t"]])
+    rm, rp1, rf1, rp2, rf2 = om.match_features_cv2(kp1, d1, kp2, d2)
+    assert [m[0].distance for m in matches] == [m[0].distance for m in rm]
+    with pytest.raises(ValueError):
+        FeatureMatcher().match_features(kp1, d1, kp2[:1], d2[:1])
+
+
+def test_c2_full_size_batch_properties():
+    """2048 x 2048 x 64 pairs: planted matches recovered, batch entries independent, cv2 parity
+    on one pair, and idempotence across two launches."""
+    B = 64
+    q, t = synth.descriptors_batch(B, seed=1)
+    g1 = run_gpu(q, t, 0.8, True)
+    g2 = run_gpu(q, t, 0.8, True)
+    for k in ("idx", "dist", "keep_q", "keep_t", "n_keep", "rev_key"):
+        assert np.array_equal(g1[k], g2[k])
+    for b in (0, B - 1):
+        idx, dist = om.knn2_cv2(q[b], t[b])
+        assert np.array_equal(g1["idx"][b], idx) and np.array_equal(g1["dist"][b], dist)
+    one = run_gpu(q[5:6], t[5:6], 0.8, True)
+    assert np.array_equal(one["idx"][0], g1["idx"][5])
+    assert np.array_equal(one["keep_q"][0], g1["keep_q"][5])
+    assert (g1["n_keep"] > 0.6 * 2048).all() and (g1["n_keep"] <= 0.7 * 2048 + 1).all()
+    d = g1["dist"]
+    assert (d[..., 0] <= d[..., 1]).all() and (d >= 0).all() and (d <= 256).all()

@@ -1,0 +1,64 @@
+"""ctypes binding of libvslam_b200.so (include/vslam_b200.h).
+
+There is no CPU fallback: if the library is missing or a call returns a non-zero
+status this module raises.
+"""
+import ctypes as C
+import os
+
+from . import build as _build
+
+_lib = None
+
+
+class VslamError(RuntimeError):
+    pass
+
+
+def _declare(lib):
+    vp, i32, f64 = C.c_void_p, C.c_int, C.c_double
+    lib.vslam_status_string.restype = C.c_char_p
+    lib.vslam_status_string.argtypes = [i32]
+    lib.vslam_last_cuda_error.restype = C.c_char_p
+    lib.vslam_last_cuda_error.argtypes = []
+    lib.vslam_abi_version.restype = i32
+    lib.vslam_device_sm_count.restype = i32
+    lib.vslam_hamming_knn2.argtypes = [vp, i32, vp, i32, vp, vp, vp, i32, vp]
+    lib.vslam_match_filter.argtypes = [vp, vp, vp, i32, i32, f64, i32, vp, vp, vp, i32, vp]
+    lib.vslam_microbench_popc.argtypes = [i32, C.POINTER(f64), vp]
+    lib.vslam_hamming_set_variant.argtypes = [i32]
+
+
+def lib():
+    """Loads (building first if the sources are newer and nvcc is present) the C-ABI library."""
+    global _lib
+    if _lib is None:
+        path = _build.LIB_PATH
+        if os.path.exists(_build.NVCC):
+            path = _build.build()
+        if not os.path.exists(path):
+            raise VslamError(
+                "libvslam_b200.so is missing and nvcc is not available; "
+                "run `python -m visual_slam_b200.build` (no CPU fallback exists)")
+        _lib = C.CDLL(path)
+        _declare(_lib)
+    return _lib
+
+
+def check(status):
+    if status != 0:
+        l = lib()
+        msg = l.vslam_status_string(status).decode()
+        if status == 3:
+            msg += ": " + l.vslam_last_cuda_error().decode()
+        raise VslamError("vslam_b200: " + msg)
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,101 @@
+"""Descriptor matching: drop-in for FeatureMatcher (reference src/v2/frame.py:16-49).
+
+`FeatureMatcher.match_features` keeps the reference signature and return objects
+(list of [cv2.DMatch], matched keypoints and descriptors in query order); the
+arithmetic runs in the sm_100a kernels of csrc/hamming.cu through the C ABI.
+`match_batch` is the tensor-native entry used by the batched tracking path.
+"""
+import numpy as np
+import torch
+
+from . import _cabi
+
+
+def _require_cuda():
+    if not torch.cuda.is_available():
+        raise _cabi.VslamError("visual_slam_b200 needs a CUDA device (no CPU fallback)")
+
+
+def knn2_batch(q, t, want_rev=True):
+    """q: uint8 cuda [B, nq, 32]; t: uint8 cuda [B, nt, 32].
+
+    Returns (idx int32 [B,nq,2], dist int32 [B,nq,2], rev_key uint32-as-int32 [B,nt] or None),
+    ordered exactly like cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) (frame.py:23)."""
+    _require_cuda()
+    if q.dtype != torch.uint8 or t.dtype != torch.uint8:
+        raise ValueError("descriptors must be uint8")
+    if q.dim() != 3 or t.dim() != 3 or q.shape[2] != 32 or t.shape[2] != 32:
+        raise ValueError("descriptors must be [batch, n, 32] (256-bit)")
+    if q.shape[0] != t.shape[0]:
+        raise ValueError("query/train batch mismatch")
+    q = q.contiguous()
+    t = t.contiguous()
+    B, nq, nt = q.shape[0], q.shape[1], t.shape[1]
+    idx = torch.empty((B, nq, 2), dtype=torch.int32, device=q.device)
+    dist = torch.empty((B, nq, 2), dtype=torch.int32, device=q.device)
+    rev = torch.empty((B, nt), dtype=torch.int32, device=q.device) if want_rev else None
+    with torch.cuda.device(q.device):
+        _cabi.check(_cabi.lib().vslam_hamming_knn2(
+            _cabi.ptr(q), nq, _cabi.ptr(t), nt, _cabi.ptr(idx), _cabi.ptr(dist), _cabi.ptr(rev),
+            B, _cabi.stream_ptr()))
+    return idx, dist, rev
+
+
+def filter_batch(idx, dist, rev, nt, ratio=0.8, cross_check=False):
+    """Ratio test (frame.py:33) + optional mutual-NN check (src/slam.py:40-47), compacted."""
+    B, nq = idx.shape[0], idx.shape[1]
+    keep_q = torch.empty((B, nq), dtype=torch.int32, device=idx.device)
+    keep_t = torch.empty((B, nq), dtype=torch.int32, device=idx.device)
+    n_keep = torch.empty((B,), dtype=torch.int32, device=idx.device)
+    if cross_check and rev is None:
+        raise ValueError("cross_check needs the reverse keys from knn2_batch(want_rev=True)")
+    with torch.cuda.device(idx.device):
+        _cabi.check(_cabi.lib().vslam_match_filter(
+            _cabi.ptr(idx), _cabi.ptr(dist), _cabi.ptr(rev), nq, nt, float(ratio),
+            1 if cross_check else 0, _cabi.ptr(keep_q), _cabi.ptr(keep_t), _cabi.ptr(n_keep),
+            B, _cabi.stream_ptr()))
+    return keep_q, keep_t, n_keep
+
+
+def match_batch(q, t, ratio=0.8, cross_check=False):
+    """Batched kNN-2 + ratio (+ cross-check).  Returns a dict of device tensors."""
+    idx, dist, rev = knn2_batch(q, t, want_rev=cross_check)
+    keep_q, keep_t, n_keep = filter_batch(idx, dist, rev, t.shape[1], ratio, cross_check)
+    return {"idx": idx, "dist": dist, "rev_key": rev, "keep_q": keep_q, "keep_t": keep_t,
+            "n_keep": n_keep}
+
+
+class FeatureMatcher:
+    """Same interface as the reference class (src/v2/frame.py:16-49), Hamming/ORB variant
+    (frame.py:8).  `cross_check=True` adds the mutual-nearest test of src/slam.py:40-47."""
+
+    def __init__(self, cross_check=False, device="cuda:0"):
+        self.cross_check = bool(cross_check)
+        self.device = torch.device(device)
+
+    def match_features(self, kp1, desc1, kp2, desc2, ratio=0.8):
+        import cv2  # only to build cv2.DMatch return objects, as callers expect (main.py:187,216)
+        desc1 = np.ascontiguousarray(desc1)
+        desc2 = np.ascontiguousarray(desc2)
+        if desc1.dtype != np.uint8 or desc2.dtype != np.uint8:
+            raise ValueError("match_features: ORB/Hamming path needs uint8 descriptors")
+        if desc1.ndim != 2 or desc2.ndim != 2 or desc1.shape[1] != 32 or desc2.shape[1] != 32:
+            raise ValueError("match_features: descriptors must be (N, 32) uint8")
+        if desc2.shape[0] < 2 and desc1.shape[0] > 0:
+            # the reference unpacks `for m, n in rawMatches` (frame.py:30) and raises here too
+            raise ValueError("not enough values to unpack (expected 2, got %d)" % desc2.shape[0])
+        _require_cuda()
+        q = torch.from_numpy(desc1).to(self.device, non_blocking=True)[None]
+        t = torch.from_numpy(desc2).to(self.device, non_blocking=True)[None]
+        out = match_batch(q, t, ratio, self.cross_check)
+        n = int(out["n_keep"][0].item())
+        kq = out["keep_q"][0, :n].cpu().numpy()
+        kt = out["keep_t"][0, :n].cpu().numpy()
+        d0 = out["dist"][0, :, 0].cpu().numpy()
+        matches = [[cv2.DMatch(int(a), int(b), 0, float(d0[a]))] for a, b in zip(kq, kt)]
+        kp1 = np.asarray(kp1)
+        kp2 = np.asarray(kp2)
+        if n == 0:
+            e = np.asarray([])
+            return matches, e, e.copy(), e.copy(), e.copy()
+        return matches, kp1[kq], desc1[kq], kp2[kt], desc2[kt]
