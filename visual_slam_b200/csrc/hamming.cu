@@ -229,22 +229,19 @@ __global__ void fill_u32_kernel(uint32_t* p, size_t n, uint32_t v) {
   for (; i < n; i += stride) p[i] = v;
 }
 
-// Dependent-free popc throughput probe (roofline denominator for matching).
+// popc throughput probe (roofline denominator for matching): 8 independent chains per thread,
+// each step = one POPC (its input depends on the running sum, so ptxas cannot CSE it) + one IADD3.
 __global__ void __launch_bounds__(256) popc_probe_kernel(int iters, uint32_t seed, uint32_t* out) {
-  uint32_t a[8], acc[8];
+  uint32_t acc[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) { a[i] = seed + threadIdx.x * 2654435761u + i * 40503u; acc[i] = 0; }
+  for (int i = 0; i < 8; ++i) acc[i] = seed + threadIdx.x * 2654435761u + i * 40503u;
   for (int it = 0; it < iters; ++it) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      uint32_t p;
-      asm volatile("popc.b32 %0, %1;" : "=r"(p) : "r"(a[i]));
-      acc[i] += p;      // one IADD (alu pipe) per popc; asm volatile is not hoisted
-    }
+    for (int i = 0; i < 8; ++i) acc[i] = acc[i] + __popc(acc[i]) + 0x9e3779b9u;
   }
   uint32_t s = 0;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) s += acc[i];
+  for (int i = 0; i < 8; ++i) s ^= acc[i];
   if (s == 0xdeadbeefu) out[0] = s;
 }
 
