@@ -94,6 +94,64 @@ int vslam_match_filter(const int32_t* idx, const int32_t* dist,
  */
 int vslam_microbench_popc(int iters, double* popc_per_s, void* stream);
 
+
+/* ------------------------------------------------------------------------- */
+/* 3. Bundle adjustment                                                       */
+/* ------------------------------------------------------------------------- */
+/*
+ * Opaque problem object = what reference src/v2/LocalBA.py builds as a g2o graph on every call
+ * (add_pose :56-65, add_point :68-77, add_edge :79-94, AddScalingEdge :115-131) plus the solver
+ * stack it selects (:22-25: BlockSolverSE3 + Levenberg).  Structure arrays are HOST pointers
+ * (graph construction is host work in the reference too); state arrays are DEVICE pointers.
+ *
+ *   cams   [n_cams][7] f64  camera->world pose, quaternion (x,y,z,w) + translation (SBACam)
+ *   pts    [n_pts][3]  f64
+ *   obs_uv [n_obs][2]  f64  pixel measurements, in the order of obs_cam / obs_pt
+ *   K      host f64[4]      fx, fy, cx, cy (LocalBA.py:59 set_cam, baseline 0)
+ * Fixed vertices (cam_fixed / pt_fixed, uint8 flags, may be NULL) get no column; all points fixed
+ * = motionOnlyBundleAdjustement (:195-229).  Scale edges are EdgeSBAScale with DCS (:115-131).
+ */
+typedef struct vslam_ba vslam_ba;
+
+int vslam_ba_create(vslam_ba** out, int n_cams, int n_pts, int n_obs, int n_scale,
+                    const int32_t* obs_cam, const int32_t* obs_pt,
+                    const uint8_t* cam_fixed, const uint8_t* pt_fixed,
+                    const int32_t* scale_a, const int32_t* scale_b);
+int vslam_ba_destroy(vslam_ba* ba);
+int vslam_ba_set_state(vslam_ba* ba, const double* cams, const double* pts, const double* obs_uv,
+                       const double* scale_meas, const double* K, void* stream);
+int vslam_ba_get_state(vslam_ba* ba, double* cams, double* pts, void* stream);
+/* PCG relative residual tolerance (default 1e-10) and iteration cap (<=0 keeps the default). */
+int vslam_ba_set_solver(vslam_ba* ba, double pcg_tol, int pcg_max_iter);
+
+/*
+ * SparseOptimizer::optimize(max_iterations) with OptimizationAlgorithmLevenberg
+ * (LocalBA.py:39-42 calls it with 10).  stats8 (host): initial cost, final cost, outer
+ * iterations, trials, final lambda, total PCG iterations, rejected trials, PCG breakdowns.
+ * Cost = sum of robustified chi2 (Huber sqrt(5.991) on projections, DCS on scale edges).
+ */
+int vslam_ba_optimize(vslam_ba* ba, int max_iterations, double* stats8, void* stream);
+
+/* The stages of one LM iteration, exposed for parity tests and profiling. */
+/* buildSystem(): out2 (host) = {robust cost, max |diag H|}.  Synchronises the stream. */
+int vslam_ba_linearize(vslam_ba* ba, double* out2, void* stream);
+/* One damped solve + trial update: out4 (host) = {trial cost, computeScale(), PCG status
+ * (0 converged, 1 breakdown, 2 iteration cap), PCG iterations}.  Synchronises the stream. */
+int vslam_ba_trial(vslam_ba* ba, double lambda, double* out4, void* stream);
+/* Make the last trial state current (g2o discardTop()). */
+int vslam_ba_accept(vslam_ba* ba);
+/* out8 (host): free cams, free pts, n = 6*free cams, Schur items, work units, S blocks, PCG CTAs, rows/CTA */
+int vslam_ba_dims(vslam_ba* ba, int32_t* out8);
+/* Copies an internal buffer to dst (device): 0 Hpp[Cf][36] 1 bp 2 Hll[Pf][6] 3 bl 4 S[n][n]
+ * 5 bhat 6 dp 7 dl 8 trial cams 9 trial pts. */
+int vslam_ba_read(vslam_ba* ba, int what, double* dst, int64_t capacity, void* stream);
+
+/* Block-Jacobi PCG on a caller-supplied dense symmetric system (n multiple of 6, device pointers);
+ * status_iters (host int32[2]) = {status, iterations}.  Status 1 = not positive definite, the case
+ * g2o reports as "Cholesky failure" (reference debug.txt). */
+int vslam_pcg_solve(const double* S, const double* b, double* x, int n, double tol, int max_iter,
+                    int32_t* status_iters, void* stream);
+
 /* Tuning knob for bench sweeps: selects a tile/thread variant of the kNN kernel (0 = default). */
 int vslam_hamming_set_variant(int variant);
 

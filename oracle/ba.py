@@ -194,24 +194,30 @@ def lambda_init(L, tau=1e-5):
     return tau * mx
 
 
-def solve(L, lam):
-    """BlockSolver::solve with lambda on every diagonal entry.  Returns (ok, dp [6Cf], dl [Pf,3])."""
+def schur_system(L, lam):
+    """(S, bhat, W, Hinv): S = Hpp + lam I - Hpl (Hll + lam I)^-1 Hpl^T, bhat = bp - Hpl Hll^-1 bl."""
     n = L.Hpp.shape[0]
     Pf = L.Hll.shape[0]
     Hpp = L.Hpp + lam * np.eye(n)
     if Pf == 0:
-        S, bh, W, Hinv = Hpp, L.bp, None, None
-    else:
-        Hinv = np.linalg.inv(L.Hll + lam * np.eye(3)[None])
-        nb = L.Hpl_blocks.shape[0]
-        rows = (6 * L.Hpl_cam[:, None, None] + np.arange(6)[None, :, None]) + np.zeros((1, 1, 3), dtype=np.int64)
-        cols = (3 * L.Hpl_pt[:, None, None] + np.arange(3)[None, None, :]) + np.zeros((1, 6, 1), dtype=np.int64)
-        W = sp.csr_matrix((L.Hpl_blocks.reshape(-1), (rows.reshape(-1), cols.reshape(-1))),
-                          shape=(n, 3 * Pf)) if nb else sp.csr_matrix((n, 3 * Pf))
-        Dinv = sp.block_diag([sp.csr_matrix(b) for b in Hinv], format="csr") if Pf < 2000 else _blockdiag(Hinv)
-        WD = W @ Dinv
-        S = Hpp - (WD @ W.T).toarray()
-        bh = L.bp - WD @ L.bl.reshape(-1)
+        return Hpp, L.bp, None, None
+    Hinv = np.linalg.inv(L.Hll + lam * np.eye(3)[None])
+    nb = L.Hpl_blocks.shape[0]
+    rows = (6 * L.Hpl_cam[:, None, None] + np.arange(6)[None, :, None]) + np.zeros((1, 1, 3), dtype=np.int64)
+    cols = (3 * L.Hpl_pt[:, None, None] + np.arange(3)[None, None, :]) + np.zeros((1, 6, 1), dtype=np.int64)
+    W = sp.csr_matrix((L.Hpl_blocks.reshape(-1), (rows.reshape(-1), cols.reshape(-1))),
+                      shape=(n, 3 * Pf)) if nb else sp.csr_matrix((n, 3 * Pf))
+    WD = W @ _blockdiag(Hinv)
+    S = Hpp - (WD @ W.T).toarray()
+    bh = L.bp - WD @ L.bl.reshape(-1)
+    return S, bh, W, Hinv
+
+
+def solve(L, lam):
+    """BlockSolver::solve with lambda on every diagonal entry.  Returns (ok, dp [6Cf], dl [Pf,3])."""
+    n = L.Hpp.shape[0]
+    Pf = L.Hll.shape[0]
+    S, bh, W, Hinv = schur_system(L, lam)
     ok = True
     if n == 0:
         dp = np.zeros(0)

@@ -1,0 +1,195 @@
+"""GPU parity: CUDA bundle adjustment vs the CPU restatement of the reference optimiser
+(oracle/ba.py; parity UNPINNED -- g2o itself cannot run anywhere in this project)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ba as oba
+from visual_slam_b200.ba import BAEngine, BundleAdjustment, pcg_solve, solve_problem
+from visual_slam_b200.ba_problem import BAProblem, synthetic_ba
+
+pytestmark = pytest.mark.gpu
+
+
+def sym6(h):  # (xx,xy,xz,yy,yz,zz) -> 3x3
+    m = np.zeros(h.shape[:-1] + (3, 3))
+    idx = [(0, 0), (0, 1), (0, 2), (1, 1), (1, 2), (2, 2)]
+    for k, (i, j) in enumerate(idx):
+        m[..., i, j] = h[..., k]
+        m[..., j, i] = h[..., k]
+    return m
+
+
+def close(a, b, rtol=1e-9):
+    a, b = np.asarray(a), np.asarray(b)
+    scale = max(np.abs(b).max(), 1e-300) if b.size else 1.0
+    return np.abs(a - b).max() <= rtol * scale if b.size else True
+
+
+@pytest.mark.parametrize("args", [dict(n_cams=4, n_pts=60, obs_per_pt=3.0, seed=1),
+                                  dict(n_cams=10, n_pts=5000, obs_per_pt=6.0, seed=0),
+                                  dict(n_cams=7, n_pts=300, obs_per_pt=4.0, seed=2, with_scale=False),
+                                  dict(n_cams=6, n_pts=500, obs_per_pt=4.0, seed=3, motion_only=True)])
+def test_linearize_and_one_trial_match_restatement(args):
+    p = synthetic_ba(**args)
+    eng = BAEngine(p)
+    lin = eng.linearize()
+    L = oba.linearize(p)
+    assert abs(lin["cost"] - L.cost) <= 1e-11 * L.cost
+    Cf = p.n_free_cams
+    Hpp_diag = np.stack([L.Hpp[6 * c:6 * c + 6, 6 * c:6 * c + 6] for c in range(Cf)])
+    # the engine keeps scale-edge blocks apart from Hpp: compare through S below, and Hpp without
+    if p.n_scale == 0:
+        assert close(eng.read("Hpp").cpu().numpy(), Hpp_diag)
+    assert close(eng.read("bp").cpu().numpy(), L.bp)
+    if p.n_free_pts:
+        assert close(sym6(eng.read("Hll").cpu().numpy()), L.Hll)
+        assert close(eng.read("bl").cpu().numpy(), L.bl)
+    assert abs(lin["max_diag"] - oba.lambda_init(L, 1.0)) <= 1e-10 * lin["max_diag"]
+    lam = 1e-5 * lin["max_diag"]
+    tr = eng.trial(lam)
+    S, bh, _, _ = oba.schur_system(L, lam)
+    assert close(eng.read("S").cpu().numpy(), S, 1e-9)
+    assert close(eng.read("bhat").cpu().numpy(), bh, 1e-9)
+    ok, dp, dl = oba.solve(L, lam)
+    assert ok and tr["pcg_status"] == 0
+    assert close(eng.read("dp").cpu().numpy(), dp, 1e-6)
+    if p.n_free_pts:
+        assert close(eng.read("dl").cpu().numpy(), dl, 1e-6)
+    cams, pts = oba.apply_update(p, dp, dl)
+    assert close(eng.read("trial_cams").cpu().numpy(), cams, 1e-7)
+    want = oba.cost(p, cams, pts)
+    assert abs(tr["cost"] - want) <= 1e-7 * want
+    x = np.concatenate([dp, dl.reshape(-1)]); b = np.concatenate([L.bp, L.bl.reshape(-1)])
+    want_scale = float(np.sum(x * (lam * x + b)))
+    assert abs(tr["scale"] - want_scale) <= 1e-6 * abs(want_scale)
+    eng.close()
+
+
+@pytest.mark.parametrize("args", [dict(n_cams=10, n_pts=5000, obs_per_pt=6.0, seed=0),
+                                  dict(n_cams=5, n_pts=200, obs_per_pt=3.5, seed=7),
+                                  dict(n_cams=8, n_pts=800, obs_per_pt=5.0, seed=5, motion_only=True)])
+def test_ten_lm_iterations_match_restatement(args):
+    """north_star tolerance: final cost within 1e-4 relative, RMS reprojection within 1e-3 px."""
+    p = synthetic_ba(**args)
+    ref = p.copy()
+    h = oba.optimize(ref, 10)
+    got = p.copy()
+    stats = solve_problem(got, 10)
+    assert abs(stats["final_cost"] - h["final_cost"]) <= 1e-4 * h["final_cost"]
+    assert int(stats["iterations"]) == h["iterations"] and int(stats["trials"]) == h["trials"]
+    e, _ = oba.residuals(got)
+    rms = float(np.sqrt(np.mean(np.sum(e * e, axis=1))))
+    assert abs(rms - h["rms_px"]) <= 1e-3
+    assert abs(oba.cost(got) - stats["final_cost"]) <= 1e-9 * stats["final_cost"]
+    assert np.abs(got.cams - ref.cams).max() < 1e-6 and np.abs(got.pts - ref.pts).max() < 1e-5
+
+
+def test_runs_are_bit_reproducible():
+    p = synthetic_ba(6, 1000, 5.0, seed=9)
+    a, b = p.copy(), p.copy()
+    sa, sb = solve_problem(a, 5), solve_problem(b, 5)
+    assert sa == sb and np.array_equal(a.cams, b.cams) and np.array_equal(a.pts, b.pts)
+
+
+def test_pcg_reports_indefinite_fixture_f1(golden_dir):
+    S = np.load(os.path.join(golden_dir, "ba_debug_reduced_system.npz"))["S"]
+    x, status, iters = pcg_solve(torch.from_numpy(S).cuda(), torch.ones(90, dtype=torch.float64).cuda())
+    assert status == 1 and float(x.abs().max()) == 0.0
+
+
+def test_pcg_solves_spd_systems():
+    rng = np.random.default_rng(0)
+    for n in (6, 54, 96, 300):
+        A = rng.normal(size=(n, n)); S = A @ A.T + n * np.eye(n); b = rng.normal(size=n)
+        x, status, iters = pcg_solve(torch.from_numpy(S).cuda(), torch.from_numpy(b).cuda(), 1e-12, 5000)
+        assert status == 0 and iters <= 5000
+        assert np.abs(S @ x.cpu().numpy() - b).max() <= 1e-9 * np.abs(b).max()
+
+
+def test_rejected_step_leaves_state_untouched_and_lambda_grows():
+    p = synthetic_ba(4, 80, 3.0, seed=11)
+    eng = BAEngine(p)
+    lin = eng.linearize()
+    tr = eng.trial(1e-30 * lin["max_diag"])  # nearly undamped Gauss-Newton on a gauge-free system
+    cams, pts = eng.get_state()
+    assert np.array_equal(cams.cpu().numpy(), p.cams) and np.array_equal(pts.cpu().numpy(), p.pts)
+    assert tr["pcg_status"] in (0, 1, 2)
+    eng.close()
+
+
+class _Frame:
+    def __init__(self, fid, pose, kf=False):
+        self.ID, self.pose, self.kf, self.parents = fid, pose, kf, {}
+    def GetPose(self): return self.pose
+    def GetParentIDs(self): return self.parents.keys()
+    def GetTransitionWithParentID(self, pid): return self.parents[pid]
+    def IsKeyFrame(self): return self.kf
+    def GetID(self): return self.ID
+
+
+class _Point:
+    def __init__(self, pid, xyz):
+        self.ID, self.location_3d, self.frames = pid, xyz, {}
+    def GetFrame(self, fid): return self.frames.get(fid)
+    def Get3dPoint(self): return self.location_3d
+    def GetID(self): return self.ID
+
+
+class _Map:
+    def __init__(self): self.frames, self.points_3d = {}, {}
+    def GetFrame(self, fid): return self.frames[fid]
+    def GetPoint(self, pid): return self.points_3d[pid]
+    def UpdatePose(self, new_pose, frame_id): self.frames[frame_id].pose = new_pose
+    def UpdatePoint3D(self, new_point, point_id): self.points_3d[point_id].location_3d = new_point
+
+
+class _Cam:
+    fx, fy, cx, cy = 481.2, 480.0, 319.5, 239.5
+
+
+def _map_from_problem(p):
+    from visual_slam_b200.ba_problem import quat_to_R
+    m = _Map()
+    for c in range(p.n_cams):
+        T = np.eye(4); T[:3, :3] = quat_to_R(p.cams[c, :4]); T[:3, 3] = p.cams[c, 4:]
+        m.frames[c] = _Frame(c, T)
+    for k in range(p.n_scale):
+        a, b = int(p.scale_a[k]), int(p.scale_b[k])
+        rel = np.eye(4); rel[:3, 3] = [p.scale_meas[k], 0, 0]
+        m.frames[b].parents[a] = rel
+    for j in range(p.n_pts):
+        m.points_3d[j] = _Point(j, p.pts[j].copy())
+    for o in range(p.n_obs):
+        m.points_3d[int(p.obs_pt[o])].frames[int(p.obs_cam[o])] = (m.frames[int(p.obs_cam[o])], p.obs_uv[o], None)
+    return m
+
+
+def test_drop_in_bundle_adjustment_class_local_and_motion_only():
+    p = synthetic_ba(5, 300, 4.0, seed=13)
+    m = _map_from_problem(p)
+    ba = BundleAdjustment(_Cam())
+    ba.localBundleAdjustement(m)
+    ref = p.copy()
+    h = oba.optimize(ref, 10)
+    assert abs(ba.stats["final_cost"] - h["final_cost"]) <= 1e-4 * h["final_cost"]
+    got = np.array([m.frames[c].pose[:3, 3] for c in range(p.n_cams)])
+    assert np.abs(got - ref.cams[:, 4:]).max() < 1e-6
+    assert np.abs(np.array([m.points_3d[j].location_3d for j in range(p.n_pts)]) - ref.pts).max() < 1e-5
+    # motion only: key frames fixed, all points fixed
+    p2 = synthetic_ba(5, 300, 4.0, seed=14, motion_only=True)
+    m2 = _map_from_problem(p2)
+    m2.frames[0].kf = True
+    ba2 = BundleAdjustment(_Cam())
+    ba2.motionOnlyBundleAdjustement(m2)
+    ref2 = p2.copy()
+    h2 = oba.optimize(ref2, 10)
+    assert abs(ba2.stats["final_cost"] - h2["final_cost"]) <= 1e-4 * h2["final_cost"]
+    # scale=True path rescales by the median point norm (LocalBA.py:178-190)
+    m3 = _map_from_problem(p)
+    ba3 = BundleAdjustment(_Cam())
+    ba3.localBundleAdjustement(m3, scale=True)
+    med = np.median(np.linalg.norm(ref.pts, axis=1))
+    assert np.allclose(np.array([m3.points_3d[j].location_3d for j in range(p.n_pts)]), ref.pts / med, atol=1e-5)

@@ -27,6 +27,19 @@ def _declare(lib):
     lib.vslam_match_filter.argtypes = [vp, vp, vp, i32, i32, f64, i32, vp, vp, vp, i32, vp]
     lib.vslam_microbench_popc.argtypes = [i32, C.POINTER(f64), vp]
     lib.vslam_hamming_set_variant.argtypes = [i32]
+    pp = C.POINTER(vp)
+    lib.vslam_ba_create.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
+    lib.vslam_ba_destroy.argtypes = [vp]
+    lib.vslam_ba_set_state.argtypes = [vp, vp, vp, vp, vp, C.POINTER(f64), vp]
+    lib.vslam_ba_get_state.argtypes = [vp, vp, vp, vp]
+    lib.vslam_ba_set_solver.argtypes = [vp, f64, i32]
+    lib.vslam_ba_optimize.argtypes = [vp, i32, C.POINTER(f64), vp]
+    lib.vslam_ba_linearize.argtypes = [vp, C.POINTER(f64), vp]
+    lib.vslam_ba_trial.argtypes = [vp, f64, C.POINTER(f64), vp]
+    lib.vslam_ba_accept.argtypes = [vp]
+    lib.vslam_ba_dims.argtypes = [vp, C.POINTER(C.c_int32)]
+    lib.vslam_ba_read.argtypes = [vp, i32, vp, C.c_int64, vp]
+    lib.vslam_pcg_solve.argtypes = [vp, vp, vp, i32, f64, i32, C.POINTER(C.c_int32), vp]
 
 
 def lib():

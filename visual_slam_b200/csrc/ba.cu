@@ -1,0 +1,628 @@
+// Bundle adjustment engine: problem structure (host, built once), LM loop (host scalar logic,
+// device reductions), C ABI.  Replaces the g2o SparseOptimizer / BlockSolverSE3 /
+// OptimizationAlgorithmLevenberg stack driven by reference src/v2/LocalBA.py:20-229.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+#include "ba_kernels.cuh"
+#include "ba_pcg.cuh"
+
+namespace vslam {
+
+// scale edges (EdgeSBAScale + DCS, LocalBA.py:115-131): sequential, E is tiny.
+// cost_only = evaluate sum(rho) on the given cameras; else also fill the extra blocks / bp_extra.
+__global__ void ba_scale_edges(int E, const int* __restrict__ sa, const int* __restrict__ sb,
+                               const double* __restrict__ meas, const double* __restrict__ cams,
+                               const int* __restrict__ cam_col, const int* __restrict__ ex_aa,
+                               const int* __restrict__ ex_ab, const int* __restrict__ ex_bb,
+                               int n_extra, int Cf, int cost_only, double* __restrict__ extra,
+                               double* __restrict__ bp_extra, double* __restrict__ scale_cost) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  if (!cost_only) {
+    for (int i = 0; i < n_extra * 36; ++i) extra[i] = 0.0;
+    for (int i = 0; i < Cf * 6; ++i) bp_extra[i] = 0.0;
+  }
+  double cost = 0.0;
+  for (int k = 0; k < E; ++k) {
+    const double* ta = cams + 7 * sa[k] + 4;
+    const double* tb = cams + 7 * sb[k] + 4;
+    const double d[3] = {tb[0] - ta[0], tb[1] - ta[1], tb[2] - ta[2]};
+    const double nrm = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    const double es = meas[k] - nrm;
+    double rho, w;
+    dcs(es * es, rho, w);
+    cost += rho;
+    if (cost_only) continue;
+    const double u[3] = {d[0] / nrm, d[1] / nrm, d[2] / nrm};  // d e / d ta = +u, d e / d tb = -u
+    const int ca = cam_col[sa[k]], cb = cam_col[sb[k]];
+    for (int i = 0; i < 3; ++i) {
+      if (ca >= 0) bp_extra[6 * ca + i] += -w * u[i] * es;
+      if (cb >= 0) bp_extra[6 * cb + i] += w * u[i] * es;
+      for (int j = 0; j < 3; ++j) {
+        const double h = w * u[i] * u[j];
+        if (ex_aa[k] >= 0) extra[36 * ex_aa[k] + 6 * i + j] += h;
+        if (ex_bb[k] >= 0) extra[36 * ex_bb[k] + 6 * i + j] += h;
+        if (ex_ab[k] >= 0) extra[36 * ex_ab[k] + 6 * i + j] -= h;
+      }
+    }
+  }
+  *scale_cost = cost;
+}
+
+// res[0] = sum cam_cost + scale cost; res[1] = computeScale: sum x (lambda x + b) over cams + points
+__global__ void ba_finish(int C, const double* __restrict__ cam_cost,
+                          const double* __restrict__ scale_cost, int n_sp,
+                          const double* __restrict__ scale_partial, int n, const double* __restrict__ dp,
+                          const double* __restrict__ bp, double lambda, const int* __restrict__ pcg_status,
+                          const int* __restrict__ pcg_iters, double* __restrict__ res) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  double c = 0.0;
+  for (int i = 0; i < C; ++i) c += cam_cost[i];
+  res[0] = c + *scale_cost;
+  if (dp) {
+    double s = 0.0;
+    for (int i = 0; i < n; ++i) s += dp[i] * (lambda * dp[i] + bp[i]);
+    for (int i = 0; i < n_sp; ++i) s += scale_partial[i];
+    res[1] = s;
+    res[3] = (double)*pcg_status;
+    res[4] = (double)*pcg_iters;
+  }
+}
+
+// computeLambdaInit: max |diag H| over free cameras (incl. scale-edge part) and free points.
+__global__ void ba_max_diag(int Cf, const double* __restrict__ Hpp, const int* __restrict__ diag_extra,
+                            const double* __restrict__ extra, int Pf, const double* __restrict__ Hll,
+                            double* __restrict__ res) {
+  __shared__ double red[8];
+  double m = 0.0;
+  for (int i = threadIdx.x; i < Cf * 6; i += blockDim.x) {
+    const int c = i / 6, k = i % 6;
+    double v = Hpp[36 * c + 7 * k];
+    if (diag_extra[c] >= 0) v += extra[36 * diag_extra[c] + 7 * k];
+    m = fmax(m, fabs(v));
+  }
+  for (int i = threadIdx.x; i < Pf; i += blockDim.x) {
+    m = fmax(m, fmax(fabs(Hll[6 * (size_t)i]), fmax(fabs(Hll[6 * (size_t)i + 3]), fabs(Hll[6 * (size_t)i + 5]))));
+  }
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 0; w < (int)blockDim.x / 32; ++w) m = fmax(m, red[w]);
+    res[2] = m;
+  }
+}
+
+__global__ void ba_gather_uv(int N, const int* __restrict__ src, const double2* __restrict__ uv,
+                             double2* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) out[i] = uv[src[i]];
+}
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  cudaError_t alloc(size_t count) {
+    n = count;
+    return cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+  }
+  cudaError_t upload(const std::vector<T>& h) {
+    cudaError_t e = alloc(h.size());
+    if (e != cudaSuccess || h.empty()) return e;
+    return cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+  }
+  ~DevBuf() { if (p) cudaFree(p); }
+};
+
+struct BA {
+  int C = 0, P = 0, N = 0, E = 0, Cf = 0, Pf = 0, n = 0, max_chunks = 1;
+  int n_items = 0, n_units = 0, n_seg = 0, n_extra = 0, n_sp = 0;
+  double4 K = make_double4(0, 0, 0, 0);
+  // structure
+  DevBuf<int> cam_col, pt_col, cm_start, cm_pt, cm_pm, cm_src, pt_start, pm_cam, pm_src;
+  DevBuf<int> item_a, item_b, unit_start, unit_len, seg_a, seg_b, seg_unit_start, seg_extra_idx;
+  DevBuf<int> sa, sb, ex_aa, ex_ab, ex_bb, diag_extra;
+  DevBuf<double2> cm_uv, pm_uv;
+  // state: [0] current, [1] trial
+  DevBuf<double> cams[2], pts[2], scale_meas;
+  DevBuf<CamRT> camrt[2];
+  int cur = 0;
+  // system
+  DevBuf<double> Hpl, Ebuf, Hpp, bp, bhat, Hll, bl, Hinv, camp, cam_cost, S, dp, dl, tmp3;
+  DevBuf<double> unit_partial, seg_extra_dense, extra, bp_extra, scale_cost, scale_partial, res, p_glob, part;
+  DevBuf<unsigned> bar;
+  DevBuf<int> pcg_flags;  // [0] fail flag, [1] status, [2] iters
+  double* res_host = nullptr;  // pinned [8]
+  // PCG launch configuration
+  int pcg_G = 1, pcg_rows = 6, pcg_slab = 1;
+  size_t pcg_smem = 0;
+  double pcg_tol = 1e-10;
+  int pcg_max_iter = 0;
+  bool linearized = false;
+
+  BAView view() const {
+    BAView V;
+    V.C = C; V.P = P; V.N = N; V.Cf = Cf; V.Pf = Pf; V.E = E; V.max_chunks = max_chunks; V.K = K;
+    V.cam_col = cam_col.p; V.pt_col = pt_col.p; V.cm_start = cm_start.p; V.cm_pt = cm_pt.p;
+    V.cm_pm = cm_pm.p; V.cm_uv = cm_uv.p; V.pt_start = pt_start.p; V.pm_cam = pm_cam.p;
+    V.pm_uv = pm_uv.p;
+    return V;
+  }
+  ~BA() { if (res_host) cudaFreeHost(res_host); }
+};
+
+static void counting_sort(const std::vector<int>& in, const int* key, int n_keys, std::vector<int>& out) {
+  std::vector<int> cnt(n_keys + 1, 0);
+  for (int i : in) cnt[key[i] + 1]++;
+  for (int k = 0; k < n_keys; ++k) cnt[k + 1] += cnt[k];
+  out.resize(in.size());
+  for (int i : in) out[cnt[key[i]]++] = i;
+}
+
+#define BA_TRY(expr)                                                   \
+  do {                                                                 \
+    cudaError_t _e = (expr);                                           \
+    if (_e != cudaSuccess) { set_cuda_error(_e, #expr); return VSLAM_ERR_CUDA; } \
+  } while (0)
+
+static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, const int32_t* obs_pt,
+                    const uint8_t* cam_fixed, const uint8_t* pt_fixed, const int32_t* sa,
+                    const int32_t* sb) {
+  B.C = C; B.P = P; B.N = N; B.E = E;
+  std::vector<int> cam_col(C), pt_col(P);
+  int Cf = 0, Pf = 0;
+  for (int c = 0; c < C; ++c) cam_col[c] = (cam_fixed && cam_fixed[c]) ? -1 : Cf++;
+  for (int p = 0; p < P; ++p) pt_col[p] = (pt_fixed && pt_fixed[p]) ? -1 : Pf++;
+  B.Cf = Cf; B.Pf = Pf; B.n = 6 * Cf;
+  for (int i = 0; i < N; ++i)
+    if (obs_cam[i] < 0 || obs_cam[i] >= C || obs_pt[i] < 0 || obs_pt[i] >= P) return VSLAM_ERR_BAD_ARG;
+  for (int k = 0; k < E; ++k)
+    if (sa[k] < 0 || sa[k] >= C || sb[k] < 0 || sb[k] >= C || sa[k] == sb[k]) return VSLAM_ERR_BAD_ARG;
+  // two stable counting sorts per ordering
+  std::vector<int> ident(N), by_pt, by_cam, cm_src, pm_src;
+  for (int i = 0; i < N; ++i) ident[i] = i;
+  counting_sort(ident, obs_pt, P, by_pt);
+  counting_sort(by_pt, obs_cam, C, cm_src);   // (cam, pt)
+  counting_sort(ident, obs_cam, C, by_cam);
+  counting_sort(by_cam, obs_pt, P, pm_src);   // (pt, cam)
+  std::vector<int> pm_pos(N);
+  for (int i = 0; i < N; ++i) pm_pos[pm_src[i]] = i;
+  std::vector<int> cm_pos(N);
+  for (int i = 0; i < N; ++i) cm_pos[cm_src[i]] = i;
+  std::vector<int> cm_start(C + 1, 0), pt_start(P + 1, 0), cm_pt(N), cm_pm(N), pm_cam(N);
+  for (int i = 0; i < N; ++i) { cm_start[obs_cam[i] + 1]++; pt_start[obs_pt[i] + 1]++; }
+  for (int c = 0; c < C; ++c) cm_start[c + 1] += cm_start[c];
+  for (int p = 0; p < P; ++p) pt_start[p + 1] += pt_start[p];
+  int max_obs = 0;
+  for (int c = 0; c < C; ++c) max_obs = std::max(max_obs, cm_start[c + 1] - cm_start[c]);
+  B.max_chunks = std::max(1, (max_obs + kCamChunk - 1) / kCamChunk);
+  for (int i = 0; i < N; ++i) {
+    cm_pt[i] = obs_pt[cm_src[i]];
+    cm_pm[i] = pm_pos[cm_src[i]];
+    pm_cam[i] = obs_cam[pm_src[i]];
+  }
+  // Schur items, counted then filled per (col_a <= col_b) key
+  if ((long long)Cf * Cf > (1ll << 26)) return VSLAM_ERR_BAD_ARG;  // dense reduced system limit
+  std::vector<long long> cnt((size_t)Cf * Cf + 1, 0);
+  auto for_items = [&](auto&& fn) {
+    for (int p = 0; p < P; ++p) {
+      if (pt_col[p] < 0) continue;
+      for (int i = pt_start[p]; i < pt_start[p + 1]; ++i) {
+        const int ci = cam_col[pm_cam[i]];
+        if (ci < 0) continue;
+        for (int j = i; j < pt_start[p + 1]; ++j) {
+          const int cj = cam_col[pm_cam[j]];
+          if (cj < 0) continue;
+          fn((size_t)ci * Cf + cj, cm_pos[pm_src[i]], cm_pos[pm_src[j]]);
+          if (i != j && ci == cj) fn((size_t)ci * Cf + cj, cm_pos[pm_src[j]], cm_pos[pm_src[i]]);
+        }
+      }
+    }
+  };
+  for_items([&](size_t key, int, int) { cnt[key + 1]++; });
+  std::vector<char> present((size_t)Cf * Cf, 0);
+  for (size_t k = 0; k < (size_t)Cf * Cf; ++k) present[k] = cnt[k + 1] > 0;
+  for (int c = 0; c < Cf; ++c) present[(size_t)c * Cf + c] = 1;
+  std::vector<int> ex_aa(E, -1), ex_ab(E, -1), ex_bb(E, -1);
+  for (int k = 0; k < E; ++k) {
+    const int ca = cam_col[sa[k]], cb = cam_col[sb[k]];
+    if (ca >= 0 && cb >= 0) present[(size_t)std::min(ca, cb) * Cf + std::max(ca, cb)] = 1;
+  }
+  for (size_t k = 0; k < (size_t)Cf * Cf; ++k) cnt[k + 1] += cnt[k];
+  const long long n_items = cnt[(size_t)Cf * Cf];
+  if (n_items > (1ll << 31) - 1) return VSLAM_ERR_BAD_ARG;
+  std::vector<int> item_a(n_items), item_b(n_items);
+  {
+    std::vector<long long> fill(cnt.begin(), cnt.end() - 1);
+    for_items([&](size_t key, int a, int b) { long long o = fill[key]++; item_a[o] = a; item_b[o] = b; });
+  }
+  std::vector<int> seg_a, seg_b, seg_unit_start, unit_start, unit_len, seg_of_key((size_t)Cf * Cf, -1);
+  for (int a = 0; a < Cf; ++a)
+    for (int b = a; b < Cf; ++b) {
+      const size_t key = (size_t)a * Cf + b;
+      if (!present[key]) continue;
+      seg_of_key[key] = (int)seg_a.size();
+      seg_a.push_back(a); seg_b.push_back(b);
+      seg_unit_start.push_back((int)unit_start.size());
+      for (long long s = cnt[key]; s < cnt[key + 1]; s += kUnitItems) {
+        unit_start.push_back((int)s);
+        unit_len.push_back((int)std::min<long long>(kUnitItems, cnt[key + 1] - s));
+      }
+    }
+  seg_unit_start.push_back((int)unit_start.size());
+  B.n_items = (int)n_items; B.n_units = (int)unit_start.size(); B.n_seg = (int)seg_a.size();
+  // extra (scale-edge) blocks: one per touched segment
+  std::vector<int> seg_extra_idx(B.n_seg, -1), diag_extra(Cf, -1);
+  int n_extra = 0;
+  auto touch = [&](int a, int b) {
+    int seg = seg_of_key[(size_t)std::min(a, b) * Cf + std::max(a, b)];
+    if (seg_extra_idx[seg] < 0) seg_extra_idx[seg] = n_extra++;
+    return seg_extra_idx[seg];
+  };
+  for (int k = 0; k < E; ++k) {
+    const int ca = cam_col[sa[k]], cb = cam_col[sb[k]];
+    if (ca >= 0) { ex_aa[k] = touch(ca, ca); diag_extra[ca] = ex_aa[k]; }
+    if (cb >= 0) { ex_bb[k] = touch(cb, cb); diag_extra[cb] = ex_bb[k]; }
+    if (ca >= 0 && cb >= 0) ex_ab[k] = touch(ca, cb);
+  }
+  B.n_extra = n_extra;
+  B.n_sp = (P + 255) / 256;
+  // uploads
+  BA_TRY(B.cam_col.upload(cam_col)); BA_TRY(B.pt_col.upload(pt_col));
+  BA_TRY(B.cm_start.upload(cm_start)); BA_TRY(B.cm_pt.upload(cm_pt)); BA_TRY(B.cm_pm.upload(cm_pm));
+  BA_TRY(B.cm_src.upload(cm_src)); BA_TRY(B.pt_start.upload(pt_start)); BA_TRY(B.pm_cam.upload(pm_cam));
+  BA_TRY(B.pm_src.upload(pm_src)); BA_TRY(B.item_a.upload(item_a)); BA_TRY(B.item_b.upload(item_b));
+  BA_TRY(B.unit_start.upload(unit_start)); BA_TRY(B.unit_len.upload(unit_len));
+  BA_TRY(B.seg_a.upload(seg_a)); BA_TRY(B.seg_b.upload(seg_b));
+  BA_TRY(B.seg_unit_start.upload(seg_unit_start)); BA_TRY(B.seg_extra_idx.upload(seg_extra_idx));
+  BA_TRY(B.sa.upload(std::vector<int>(sa, sa + E))); BA_TRY(B.sb.upload(std::vector<int>(sb, sb + E)));
+  BA_TRY(B.ex_aa.upload(ex_aa)); BA_TRY(B.ex_ab.upload(ex_ab)); BA_TRY(B.ex_bb.upload(ex_bb));
+  BA_TRY(B.diag_extra.upload(diag_extra));
+  BA_TRY(B.cm_uv.alloc(N)); BA_TRY(B.pm_uv.alloc(N)); BA_TRY(B.scale_meas.alloc(E));
+  for (int s = 0; s < 2; ++s) {
+    BA_TRY(B.cams[s].alloc((size_t)C * 7)); BA_TRY(B.pts[s].alloc((size_t)P * 3)); BA_TRY(B.camrt[s].alloc(C));
+  }
+  BA_TRY(B.Hpl.alloc((size_t)N * 18)); BA_TRY(B.Ebuf.alloc((size_t)N * 18));
+  BA_TRY(B.Hpp.alloc((size_t)Cf * 36)); BA_TRY(B.bp.alloc(B.n)); BA_TRY(B.bhat.alloc(B.n));
+  BA_TRY(B.Hll.alloc((size_t)Pf * 6)); BA_TRY(B.bl.alloc((size_t)Pf * 3)); BA_TRY(B.Hinv.alloc((size_t)Pf * 6));
+  BA_TRY(B.camp.alloc((size_t)C * B.max_chunks * kCamVals)); BA_TRY(B.cam_cost.alloc(C));
+  BA_TRY(B.S.alloc((size_t)B.n * B.n)); BA_TRY(B.dp.alloc(B.n)); BA_TRY(B.dl.alloc((size_t)Pf * 3));
+  BA_TRY(B.tmp3.alloc((size_t)N * 3)); BA_TRY(B.unit_partial.alloc((size_t)B.n_units * 36));
+  BA_TRY(B.extra.alloc((size_t)std::max(n_extra, 1) * 36)); BA_TRY(B.bp_extra.alloc(std::max(B.n, 1)));
+  BA_TRY(B.scale_cost.alloc(1)); BA_TRY(B.scale_partial.alloc(B.n_sp)); BA_TRY(B.res.alloc(8));
+  BA_TRY(B.p_glob.alloc(std::max(B.n, 1)));
+  BA_TRY(cudaMemset(B.S.p, 0, std::max<size_t>((size_t)B.n * B.n, 1) * sizeof(double)));
+  BA_TRY(cudaMemset(B.extra.p, 0, (size_t)std::max(n_extra, 1) * 36 * sizeof(double)));
+  BA_TRY(cudaMemset(B.bp_extra.p, 0, (size_t)std::max(B.n, 1) * sizeof(double)));
+  BA_TRY(cudaMemset(B.scale_cost.p, 0, sizeof(double)));
+  BA_TRY(cudaMemset(B.camp.p, 0, B.camp.n * sizeof(double)));
+  BA_TRY(cudaMallocHost(&B.res_host, 8 * sizeof(double)));
+  // PCG configuration: as many CTAs as keep their slab of S in shared memory, at most one per SM
+  {
+    const int nb = Cf;
+    const int sms = std::max(1, sm_count());
+    int max_smem = 0, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    const size_t budget = (size_t)std::max(max_smem - 2048, 16384);
+    auto smem_for = [&](int rows, bool slab) {
+      return sizeof(double) * ((size_t)B.n + 5 * (size_t)rows + 6 * (size_t)rows + 8 +
+                               (slab ? (size_t)rows * B.n : 0));
+    };
+    int bpc = std::max(1, (nb + sms - 1) / sms);  // blocks per CTA with one CTA per SM
+    // prefer fewer CTAs (cheaper barriers) while the slab still fits
+    int best = bpc;
+    for (int t = nb; t >= bpc; --t) {
+      if (smem_for(6 * t, true) <= budget) { best = t; break; }
+    }
+    B.pcg_slab = smem_for(6 * best, true) <= budget ? 1 : 0;
+    B.pcg_rows = 6 * std::max(best, 1);
+    B.pcg_G = std::max(1, (nb + best - 1) / std::max(best, 1));
+    B.pcg_smem = smem_for(B.pcg_rows, B.pcg_slab);
+    if (B.pcg_smem > budget) return VSLAM_ERR_BAD_ARG;
+    BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)B.pcg_smem));
+  }
+  BA_TRY(B.part.alloc((size_t)4 * B.pcg_G)); BA_TRY(B.bar.alloc(1)); BA_TRY(B.pcg_flags.alloc(4));
+  B.pcg_max_iter = std::max(200, 20 * B.n);
+  return VSLAM_OK;
+}
+
+static int ba_set_state(BA& B, const double* cams, const double* pts, const double* uv,
+                        const double* scale_meas, const double* K, cudaStream_t st) {
+  B.K = make_double4(K[0], K[1], K[2], K[3]);
+  B.cur = 0;
+  BA_TRY(cudaMemcpyAsync(B.cams[0].p, cams, (size_t)B.C * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  BA_TRY(cudaMemcpyAsync(B.pts[0].p, pts, (size_t)B.P * 3 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  if (B.E) BA_TRY(cudaMemcpyAsync(B.scale_meas.p, scale_meas, (size_t)B.E * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  if (B.N) {
+    const int blocks = (B.N + 255) / 256;
+    ba_gather_uv<<<blocks, 256, 0, st>>>(B.N, B.cm_src.p, reinterpret_cast<const double2*>(uv), B.cm_uv.p);
+    ba_gather_uv<<<blocks, 256, 0, st>>>(B.N, B.pm_src.p, reinterpret_cast<const double2*>(uv), B.pm_uv.p);
+  }
+  if (B.C) ba_prepare_cams<<<(B.C + 127) / 128, 128, 0, st>>>(B.cams[0].p, B.camrt[0].p, B.C);
+  B.linearized = false;
+  return check_launch("ba_set_state");
+}
+
+static int ba_readback(BA& B, cudaStream_t st) {
+  BA_TRY(cudaMemcpyAsync(B.res_host, B.res.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  BA_TRY(cudaStreamSynchronize(st));
+  return VSLAM_OK;
+}
+
+// buildSystem() on the current state; res_host[0] = cost, res_host[2] = max |diag H|.
+static int ba_linearize(BA& B, cudaStream_t st) {
+  const BAView V = B.view();
+  const int s = B.cur;
+  if (B.C == 0) return VSLAM_ERR_BAD_ARG;
+  dim3 grid(B.max_chunks, B.C);
+  ba_scale_edges<<<1, 32, 0, st>>>(B.E, B.sa.p, B.sb.p, B.scale_meas.p, B.cams[s].p, B.cam_col.p,
+                                   B.ex_aa.p, B.ex_ab.p, B.ex_bb.p, B.n_extra, B.Cf, 0, B.extra.p,
+                                   B.bp_extra.p, B.scale_cost.p);
+  ba_cam_pass<false><<<grid, kCamThreads, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hpl.p, B.camp.p);
+  ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp_extra.p, B.Hpp.p, B.bp.p, B.cam_cost.p);
+  if (B.P) ba_point_pass<<<(B.P + 127) / 128, 128, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hll.p, B.bl.p);
+  ba_max_diag<<<1, 256, 0, st>>>(B.Cf, B.Hpp.p, B.diag_extra.p, B.extra.p, B.Pf, B.Hll.p, B.res.p);
+  ba_finish<<<1, 32, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, 0, nullptr, 0, nullptr, nullptr, 0.0,
+                              nullptr, nullptr, B.res.p);
+  int rc = check_launch("ba_linearize");
+  if (rc) return rc;
+  B.linearized = true;
+  return ba_readback(B, st);
+}
+
+// One LM trial: solve (H + lambda I) d = b through Schur + PCG, write the trial state, evaluate it.
+// res_host: [0] trial cost, [1] computeScale, [3] pcg status, [4] pcg iterations.
+static int ba_trial(BA& B, double lambda, cudaStream_t st) {
+  if (!B.linearized) return VSLAM_ERR_BAD_ARG;
+  const BAView V = B.view();
+  const int s = B.cur, t = B.cur ^ 1;
+  dim3 grid(B.max_chunks, B.C);
+  if (B.Pf) {
+    ba_point_invert<<<(B.Pf + 127) / 128, 128, 0, st>>>(B.Pf, B.Hll.p, lambda, B.Hinv.p);
+    ba_compute_E<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.Hinv.p, B.bl.p, B.Ebuf.p, B.camp.p);
+    ba_bhat_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp.p, B.bhat.p);
+    if (B.n_units)
+      ba_schur_units<<<(B.n_units * 32 + 127) / 128, 128, 0, st>>>(B.Ebuf.p, B.Hpl.p, B.item_a.p, B.item_b.p,
+                                                                B.unit_start.p, B.unit_len.p, B.n_units,
+                                                                B.unit_partial.p);
+  } else if (B.n) {
+    BA_TRY(cudaMemcpyAsync(B.bhat.p, B.bp.p, (size_t)B.n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  }
+  if (B.n) {
+    ba_schur_finalize<<<(B.n_seg * 36 + 127) / 128, 128, 0, st>>>(
+        B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
+        B.extra.p, B.seg_extra_idx.p, lambda, B.S.p);
+    BA_TRY(cudaMemsetAsync(B.bar.p, 0, sizeof(unsigned), st));
+    BA_TRY(cudaMemsetAsync(B.pcg_flags.p, 0, 4 * sizeof(int), st));
+    PcgArgs A;
+    A.S = B.S.p; A.b = B.bhat.p; A.x = B.dp.p; A.n = B.n; A.rows = B.pcg_rows; A.G = B.pcg_G;
+    A.slab_in_smem = B.pcg_slab; A.max_iter = B.pcg_max_iter; A.tol = B.pcg_tol;
+    A.p_glob = B.p_glob.p; A.part = B.part.p; A.bar = B.bar.p; A.fail_flag = B.pcg_flags.p;
+    A.status = B.pcg_flags.p + 1; A.iters = B.pcg_flags.p + 2;
+    void* args[] = {&A};
+    if (B.pcg_G > 1) {
+      BA_TRY(cudaLaunchCooperativeKernel((void*)ba_pcg_kernel, dim3(B.pcg_G), dim3(kPcgThreads), args,
+                                         B.pcg_smem, st));
+    } else {
+      ba_pcg_kernel<<<1, kPcgThreads, B.pcg_smem, st>>>(A);
+    }
+  }
+  if (B.Pf) ba_backsub_cam<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.dp.p, B.tmp3.p);
+  if (B.P)
+    ba_backsub_pt<<<B.n_sp, 256, 0, st>>>(V, B.tmp3.p, B.Hinv.p, B.bl.p, lambda, B.pts[s].p, B.pts[t].p,
+                                          B.dl.p, B.scale_partial.p);
+  ba_update_cams<<<(B.C + 127) / 128, 128, 0, st>>>(V, B.cams[s].p, B.dp.p, B.cams[t].p, B.camrt[t].p);
+  ba_cam_pass<true><<<grid, kCamThreads, 0, st>>>(V, B.camrt[t].p, B.pts[t].p, nullptr, B.camp.p);
+  ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, nullptr, nullptr, nullptr, B.cam_cost.p);
+  ba_scale_edges<<<1, 32, 0, st>>>(B.E, B.sa.p, B.sb.p, B.scale_meas.p, B.cams[t].p, B.cam_col.p,
+                                   B.ex_aa.p, B.ex_ab.p, B.ex_bb.p, B.n_extra, B.Cf, 1, B.extra.p,
+                                   B.bp_extra.p, B.scale_cost.p);
+  ba_finish<<<1, 32, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0, B.scale_partial.p, B.n,
+                              B.dp.p, B.bp.p, lambda, B.pcg_flags.p + 1, B.pcg_flags.p + 2, B.res.p);
+  int rc = check_launch("ba_trial");
+  if (rc) return rc;
+  return ba_readback(B, st);
+}
+
+}  // namespace vslam
+
+using namespace vslam;
+
+struct vslam_ba { BA impl; };
+
+// OptimizationAlgorithmLevenberg::solve driven by SparseOptimizer::optimize(max_iterations)
+// (reference LocalBA.py:39-42).  stats: [0] initial cost, [1] final cost, [2] outer iterations,
+// [3] trials, [4] final lambda, [5] total PCG iterations, [6] rejected trials, [7] PCG breakdowns.
+static int ba_optimize(BA& B, int max_iterations, double* stats, cudaStream_t st) {
+  const double tau = 1e-5, good_lo = 1.0 / 3.0, good_hi = 2.0 / 3.0;
+  const int max_trials = 10;
+  double lambda = 0.0, ni = 2.0, cur = 0.0;
+  double initial = 0.0, pcg_total = 0.0, rejected = 0.0, breakdowns = 0.0;
+  int trials = 0, iters = 0;
+  for (int it = 0; it < max_iterations; ++it) {
+    int rc = ba_linearize(B, st);
+    if (rc) return rc;
+    cur = B.res_host[0];
+    if (it == 0) { initial = cur; lambda = tau * B.res_host[2]; ni = 2.0; }
+    double rho = 0.0;
+    int q = 0;
+    do {
+      rc = ba_trial(B, lambda, st);
+      if (rc) return rc;
+      double tmp = B.res_host[0];
+      const bool ok = B.res_host[3] != 1.0;
+      pcg_total += B.res_host[4];
+      if (!ok) { tmp = std::numeric_limits<double>::max(); breakdowns += 1; }
+      const double scale = B.res_host[1] + 1e-3;
+      rho = (cur - tmp) / scale;
+      ++trials;
+      if (rho > 0 && std::isfinite(tmp)) {
+        double alpha = 1.0 - std::pow(2 * rho - 1, 3);
+        alpha = std::min(alpha, good_hi);
+        lambda *= std::max(good_lo, alpha);
+        ni = 2.0;
+        cur = tmp;
+        B.cur ^= 1;  // discardTop(): the trial state becomes current
+        B.linearized = false;
+      } else {
+        lambda *= ni;
+        ni *= 2;
+        rejected += 1;  // pop(): current state untouched
+        if (!std::isfinite(lambda)) break;
+      }
+      ++q;
+    } while (rho < 0 && q < max_trials);
+    ++iters;
+    if (q == max_trials || rho == 0 || !std::isfinite(lambda)) break;
+  }
+  if (iters == 0) {  // max_iterations == 0: report the cost of the state as given
+    int rc = ba_linearize(B, st);
+    if (rc) return rc;
+    initial = cur = B.res_host[0];
+  }
+  if (stats) {
+    stats[0] = initial; stats[1] = cur; stats[2] = iters; stats[3] = trials; stats[4] = lambda;
+    stats[5] = pcg_total; stats[6] = rejected; stats[7] = breakdowns;
+  }
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_create(vslam_ba** out, int n_cams, int n_pts, int n_obs, int n_scale,
+                               const int32_t* obs_cam, const int32_t* obs_pt, const uint8_t* cam_fixed,
+                               const uint8_t* pt_fixed, const int32_t* scale_a, const int32_t* scale_b) {
+  if (!out || n_cams <= 0 || n_pts < 0 || n_obs < 0 || n_scale < 0) return VSLAM_ERR_BAD_ARG;
+  if ((n_obs && (!obs_cam || !obs_pt)) || (n_scale && (!scale_a || !scale_b))) return VSLAM_ERR_BAD_ARG;
+  if (sm_count() <= 0) return VSLAM_ERR_NO_DEVICE;
+  vslam_ba* h = new vslam_ba();
+  int rc = ba_build(h->impl, n_cams, n_pts, n_obs, n_scale, obs_cam, obs_pt, cam_fixed, pt_fixed,
+                    scale_a, scale_b);
+  if (rc) { delete h; return rc; }
+  *out = h;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_destroy(vslam_ba* h) {
+  delete h;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_set_state(vslam_ba* h, const double* cams, const double* pts, const double* obs_uv,
+                                  const double* scale_meas, const double* K, void* stream) {
+  if (!h || !cams || !K || (h->impl.P && !pts) || (h->impl.N && !obs_uv) || (h->impl.E && !scale_meas))
+    return VSLAM_ERR_BAD_ARG;
+  return ba_set_state(h->impl, cams, pts, obs_uv, scale_meas, K, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int vslam_ba_get_state(vslam_ba* h, double* cams, double* pts, void* stream) {
+  if (!h) return VSLAM_ERR_BAD_ARG;
+  BA& B = h->impl;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (cams) BA_TRY(cudaMemcpyAsync(cams, B.cams[B.cur].p, (size_t)B.C * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  if (pts && B.P) BA_TRY(cudaMemcpyAsync(pts, B.pts[B.cur].p, (size_t)B.P * 3 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_set_solver(vslam_ba* h, double pcg_tol, int pcg_max_iter) {
+  if (!h || !(pcg_tol > 0)) return VSLAM_ERR_BAD_ARG;
+  h->impl.pcg_tol = pcg_tol;
+  if (pcg_max_iter > 0) h->impl.pcg_max_iter = pcg_max_iter;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_linearize(vslam_ba* h, double* out2, void* stream) {
+  if (!h) return VSLAM_ERR_BAD_ARG;
+  int rc = ba_linearize(h->impl, static_cast<cudaStream_t>(stream));
+  if (rc) return rc;
+  if (out2) { out2[0] = h->impl.res_host[0]; out2[1] = h->impl.res_host[2]; }
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_trial(vslam_ba* h, double lambda, double* out4, void* stream) {
+  if (!h) return VSLAM_ERR_BAD_ARG;
+  int rc = ba_trial(h->impl, lambda, static_cast<cudaStream_t>(stream));
+  if (rc) return rc;
+  if (out4) {
+    out4[0] = h->impl.res_host[0]; out4[1] = h->impl.res_host[1];
+    out4[2] = h->impl.res_host[3]; out4[3] = h->impl.res_host[4];
+  }
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_accept(vslam_ba* h) {
+  if (!h) return VSLAM_ERR_BAD_ARG;
+  h->impl.cur ^= 1;
+  h->impl.linearized = false;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_optimize(vslam_ba* h, int max_iterations, double* stats8, void* stream) {
+  if (!h || max_iterations < 0) return VSLAM_ERR_BAD_ARG;
+  return ba_optimize(h->impl, max_iterations, stats8, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int vslam_ba_dims(vslam_ba* h, int32_t* out8) {
+  if (!h || !out8) return VSLAM_ERR_BAD_ARG;
+  const BA& B = h->impl;
+  out8[0] = B.Cf; out8[1] = B.Pf; out8[2] = B.n; out8[3] = B.n_items; out8[4] = B.n_units;
+  out8[5] = B.n_seg; out8[6] = B.pcg_G; out8[7] = B.pcg_rows;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_read(vslam_ba* h, int what, double* dst, int64_t capacity, void* stream) {
+  if (!h || !dst) return VSLAM_ERR_BAD_ARG;
+  BA& B = h->impl;
+  const double* src = nullptr;
+  size_t n = 0;
+  switch (what) {
+    case 0: src = B.Hpp.p; n = (size_t)B.Cf * 36; break;
+    case 1: src = B.bp.p; n = B.n; break;
+    case 2: src = B.Hll.p; n = (size_t)B.Pf * 6; break;
+    case 3: src = B.bl.p; n = (size_t)B.Pf * 3; break;
+    case 4: src = B.S.p; n = (size_t)B.n * B.n; break;
+    case 5: src = B.bhat.p; n = B.n; break;
+    case 6: src = B.dp.p; n = B.n; break;
+    case 7: src = B.dl.p; n = (size_t)B.Pf * 3; break;
+    case 8: src = B.cams[B.cur ^ 1].p; n = (size_t)B.C * 7; break;
+    case 9: src = B.pts[B.cur ^ 1].p; n = (size_t)B.P * 3; break;
+    default: return VSLAM_ERR_BAD_ARG;
+  }
+  if ((int64_t)n > capacity) return VSLAM_ERR_BAD_ARG;
+  if (n) BA_TRY(cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+  return VSLAM_OK;
+}
+
+// Stand-alone PCG on a caller-supplied dense SPD system (tests: fixture F1 = reference debug.txt).
+extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int n, double tol, int max_iter,
+                               int32_t* status_iters_host, void* stream) {
+  if (!S || !b || !x || n <= 0 || n % 6 || !status_iters_host) return VSLAM_ERR_BAD_ARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DevBuf<double> p_glob, part;
+  DevBuf<unsigned> bar;
+  DevBuf<int> flags;
+  BA_TRY(p_glob.alloc(n)); BA_TRY(part.alloc(4)); BA_TRY(bar.alloc(1)); BA_TRY(flags.alloc(4));
+  BA_TRY(cudaMemsetAsync(bar.p, 0, sizeof(unsigned), st));
+  BA_TRY(cudaMemsetAsync(flags.p, 0, 4 * sizeof(int), st));
+  PcgArgs A;
+  A.S = S; A.b = b; A.x = x; A.n = n; A.rows = n; A.G = 1; A.max_iter = max_iter; A.tol = tol;
+  A.p_glob = p_glob.p; A.part = part.p; A.bar = bar.p; A.fail_flag = flags.p; A.status = flags.p + 1;
+  A.iters = flags.p + 2;
+  size_t smem_slab = sizeof(double) * ((size_t)n + 11 * (size_t)n + 8 + (size_t)n * n);
+  size_t smem_noslab = sizeof(double) * ((size_t)n + 11 * (size_t)n + 8);
+  A.slab_in_smem = smem_slab <= 200 * 1024;
+  size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
+  BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
+  int rc = check_launch("ba_pcg_kernel");
+  if (rc) return rc;
+  int host[4];
+  BA_TRY(cudaMemcpyAsync(host, flags.p, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  BA_TRY(cudaStreamSynchronize(st));
+  status_iters_host[0] = host[1];
+  status_iters_host[1] = host[2];
+  return VSLAM_OK;
+}

@@ -1,0 +1,366 @@
+// Bundle-adjustment kernels: linearisation (fused residual + Jacobian + Huber + block accumulation),
+// Schur complement by sorted segments, back-substitution, state update, cost.
+// Semantics: SURVEY.md 8a-3 (g2o BlockSolver<6,3>); call sites reference src/v2/LocalBA.py:143-229.
+//
+// Two static orderings of the observations are kept in HBM (built once per problem):
+//   cm  camera-major  (cam, point)  -> per-camera reductions (Hpp, bp, E*bl), Hpl / E storage
+//   pm  point-major   (point, cam)  -> per-point reductions (Hll, bl, back-substitution)
+// Every reduction is a fixed-order tree (warp butterfly -> per-CTA -> ordered chunk sum), so
+// a BA run is bit-reproducible: no floating-point atomics anywhere.
+#pragma once
+#include "ba_math.cuh"
+
+namespace vslam {
+
+constexpr int kCamChunk = 1024;   // observations of one camera handled by one CTA
+constexpr int kCamThreads = 256;
+constexpr int kCamVals = 28;      // 21 Hpp upper + 6 bp + 1 cost
+constexpr int kUnitItems = 256;   // Schur items per warp work unit
+
+struct BAView {
+  int C, P, N, Cf, Pf, E, max_chunks;
+  double4 K;
+  const int* cam_col; const int* pt_col;
+  const int* cm_start; const int* cm_pt; const int* cm_pm; const double2* cm_uv;
+  const int* pt_start; const int* pm_cam; const double2* pm_uv;
+};
+
+__global__ void ba_prepare_cams(const double* __restrict__ cams, CamRT* __restrict__ out, int C) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  CamRT r;
+  quat_to_R(cams + 7 * c, r.R);
+  r.t[0] = cams[7 * c + 4]; r.t[1] = cams[7 * c + 5]; r.t[2] = cams[7 * c + 6];
+  out[c] = r;
+}
+
+__device__ __forceinline__ void load18(const double* p, double (&v)[18]) {
+  const double2* s = reinterpret_cast<const double2*>(p);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) { double2 t = s[i]; v[2 * i] = t.x; v[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ void store18(double* p, const double (&v)[18]) {
+  double2* s = reinterpret_cast<double2*>(p);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) s[i] = make_double2(v[2 * i], v[2 * i + 1]);
+}
+
+// Camera-major pass.  COST_ONLY = evaluate sum(rho) for a trial state; otherwise also accumulate
+// Hpp (upper 21) / bp per camera and write the Hpl blocks (w Jc^T Jp, 6x3 row-major).
+template <bool COST_ONLY>
+__global__ void __launch_bounds__(kCamThreads)
+ba_cam_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict__ pts,
+            double* __restrict__ Hpl, double* __restrict__ camp) {
+  __shared__ double red[(kCamThreads / 32) * kCamVals];
+  const int c = blockIdx.y, chunk = blockIdx.x;
+  const int start = V.cm_start[c] + chunk * kCamChunk;
+  const int end = min(V.cm_start[c + 1], start + kCamChunk);
+  if (start >= end) return;
+  const CamRT cam = camrt[c];
+  const bool cam_free = V.cam_col[c] >= 0;
+  double acc[kCamVals];
+#pragma unroll
+  for (int i = 0; i < kCamVals; ++i) acc[i] = 0.0;
+  for (int o = start + threadIdx.x; o < end; o += kCamThreads) {
+    const int p = V.cm_pt[o];
+    const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
+    const double2 uv = V.cm_uv[o];
+    double pc[3], e[2], rho, w;
+    to_camera(cam, X, pc);
+    if (!(fabs(pc[2]) > 1e-12)) continue;  // g2o aborts here; we drop the observation
+    residual(pc, V.K, uv.x, uv.y, e);
+    huber(e[0] * e[0] + e[1] * e[1], rho, w);
+    acc[27] += rho;
+    if (COST_ONLY || !cam_free) continue;
+    double Jc[2][6], Jp[2][3];
+    jacobians(cam, pc, V.K, Jc, Jp);
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+      for (int j = i; j < 6; ++j) acc[k++] += w * (Jc[0][i] * Jc[0][j] + Jc[1][i] * Jc[1][j]);
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) acc[21 + i] -= w * (Jc[0][i] * e[0] + Jc[1][i] * e[1]);
+    if (V.pt_col[p] >= 0) {
+      double h[18];
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) h[3 * i + j] = w * (Jc[0][i] * Jp[0][j] + Jc[1][i] * Jp[1][j]);
+      }
+      store18(Hpl + (size_t)o * 18, h);
+    }
+  }
+  block_reduce<kCamVals, kCamThreads>(acc, red);
+  if (threadIdx.x == 0) {
+    double* dst = camp + ((size_t)c * V.max_chunks + chunk) * kCamVals;
+#pragma unroll
+    for (int i = 0; i < kCamVals; ++i) dst[i] = acc[i];
+  }
+}
+
+// Ordered sum of the chunk partials of each camera -> Hpp [Cf][36] (full symmetric), bp [Cf][6]
+// (+ scale-edge part), per-camera cost.
+__global__ void ba_cam_finalize(BAView V, const double* __restrict__ camp,
+                                const double* __restrict__ bp_extra, double* __restrict__ Hpp,
+                                double* __restrict__ bp, double* __restrict__ cam_cost) {
+  const int c = blockIdx.x, i = threadIdx.x;
+  if (i >= kCamVals) return;
+  const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
+  const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
+  double s = 0.0;
+  for (int k = 0; k < n_chunks; ++k) s += camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
+  if (i == 27) { cam_cost[c] = s; return; }
+  const int col = V.cam_col[c];
+  if (col < 0 || Hpp == nullptr) return;
+  if (i >= 21) { bp[6 * col + (i - 21)] = s + bp_extra[6 * col + (i - 21)]; return; }
+  int r = 0, k = i;
+  while (k >= 6 - r) { k -= 6 - r; ++r; }
+  const int cc = r + k;
+  Hpp[36 * col + 6 * r + cc] = s;
+  Hpp[36 * col + 6 * cc + r] = s;
+}
+
+// Point-major pass: one thread per free point walks its observations (fixed order).
+__global__ void ba_point_pass(BAView V, const CamRT* __restrict__ camrt,
+                              const double* __restrict__ pts, double* __restrict__ Hll,
+                              double* __restrict__ bl) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= V.P) return;
+  const int col = V.pt_col[p];
+  if (col < 0) return;
+  const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
+  double h[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
+  for (int o = V.pt_start[p]; o < V.pt_start[p + 1]; ++o) {
+    const CamRT cam = camrt[V.pm_cam[o]];
+    const double2 uv = V.pm_uv[o];
+    double pc[3], e[2], rho, w;
+    to_camera(cam, X, pc);
+    if (!(fabs(pc[2]) > 1e-12)) continue;
+    residual(pc, V.K, uv.x, uv.y, e);
+    huber(e[0] * e[0] + e[1] * e[1], rho, w);
+    double Jc[2][6], Jp[2][3];
+    jacobians(cam, pc, V.K, Jc, Jp);
+    h[0] += w * (Jp[0][0] * Jp[0][0] + Jp[1][0] * Jp[1][0]);
+    h[1] += w * (Jp[0][0] * Jp[0][1] + Jp[1][0] * Jp[1][1]);
+    h[2] += w * (Jp[0][0] * Jp[0][2] + Jp[1][0] * Jp[1][2]);
+    h[3] += w * (Jp[0][1] * Jp[0][1] + Jp[1][1] * Jp[1][1]);
+    h[4] += w * (Jp[0][1] * Jp[0][2] + Jp[1][1] * Jp[1][2]);
+    h[5] += w * (Jp[0][2] * Jp[0][2] + Jp[1][2] * Jp[1][2]);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) b[j] -= w * (Jp[0][j] * e[0] + Jp[1][j] * e[1]);
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) Hll[6 * (size_t)col + j] = h[j];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) bl[3 * (size_t)col + j] = b[j];
+}
+
+__global__ void ba_point_invert(int Pf, const double* __restrict__ Hll, double lambda,
+                                double* __restrict__ Hinv) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= Pf) return;
+  double h[6], o[6];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) h[j] = Hll[6 * (size_t)p + j];
+  h[0] += lambda; h[3] += lambda; h[5] += lambda;
+  sym3_inverse(h, o);
+#pragma unroll
+  for (int j = 0; j < 6; ++j) Hinv[6 * (size_t)p + j] = o[j];
+}
+
+// E = Hpl * Hinv per observation (camera-major) and the per-camera partial of sum E * bl.
+__global__ void __launch_bounds__(kCamThreads)
+ba_compute_E(BAView V, const double* __restrict__ Hpl, const double* __restrict__ Hinv,
+             const double* __restrict__ bl, double* __restrict__ Eout, double* __restrict__ camp) {
+  __shared__ double red[(kCamThreads / 32) * 6];
+  const int c = blockIdx.y, chunk = blockIdx.x;
+  const int start = V.cm_start[c] + chunk * kCamChunk;
+  const int end = min(V.cm_start[c + 1], start + kCamChunk);
+  if (start >= end || V.cam_col[c] < 0) return;
+  double acc[6] = {0, 0, 0, 0, 0, 0};
+  for (int o = start + threadIdx.x; o < end; o += kCamThreads) {
+    const int pcol = V.pt_col[V.cm_pt[o]];
+    if (pcol < 0) continue;
+    double h[18], hi[6], b[3], e[18];
+    load18(Hpl + (size_t)o * 18, h);
+#pragma unroll
+    for (int j = 0; j < 6; ++j) hi[j] = Hinv[6 * (size_t)pcol + j];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) b[j] = bl[3 * (size_t)pcol + j];
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      sym3_mul(hi, &h[3 * r], &e[3 * r]);  // row r of Hpl times symmetric Hinv
+      acc[r] += e[3 * r] * b[0] + e[3 * r + 1] * b[1] + e[3 * r + 2] * b[2];
+    }
+    store18(Eout + (size_t)o * 18, e);
+  }
+  block_reduce<6, kCamThreads>(acc, red);
+  if (threadIdx.x == 0) {
+    double* dst = camp + ((size_t)c * V.max_chunks + chunk) * kCamVals;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) dst[i] = acc[i];
+  }
+}
+
+// bhat = bp - sum_j E_j bl_j   (ordered chunk sum)
+__global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp,
+                                 const double* __restrict__ bp, double* __restrict__ bhat) {
+  const int c = blockIdx.x, i = threadIdx.x;
+  const int col = V.cam_col[c];
+  if (i >= 6 || col < 0) return;
+  const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
+  const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
+  double s = 0.0;
+  for (int k = 0; k < n_chunks; ++k) s += camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
+  bhat[6 * col + i] = bp[6 * col + i] - s;
+}
+
+// Schur work units: one warp reduces <= kUnitItems products E_a * Hpl_b^T of one (cam a, cam b) key.
+__global__ void __launch_bounds__(128)
+ba_schur_units(const double* __restrict__ E, const double* __restrict__ Hpl,
+               const int* __restrict__ item_a, const int* __restrict__ item_b,
+               const int* __restrict__ unit_start, const int* __restrict__ unit_len, int n_units,
+               double* __restrict__ partial) {
+  const int u = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (u >= n_units) return;
+  const int s = unit_start[u], len = unit_len[u];
+  double acc[36];
+#pragma unroll
+  for (int i = 0; i < 36; ++i) acc[i] = 0.0;
+  for (int i = lane; i < len; i += 32) {
+    double ea[18], hb[18];
+    load18(E + (size_t)item_a[s + i] * 18, ea);
+    load18(Hpl + (size_t)item_b[s + i] * 18, hb);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+#pragma unroll
+      for (int c = 0; c < 6; ++c)
+        acc[6 * r + c] += ea[3 * r] * hb[3 * c] + ea[3 * r + 1] * hb[3 * c + 1] +
+                          ea[3 * r + 2] * hb[3 * c + 2];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 36; ++i) acc[i] = warp_sum(acc[i]);
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < 36; ++i) partial[(size_t)u * 36 + i] = acc[i];
+  }
+}
+
+// S block (a,b) = [a==b](Hpp_a + lambda I) + scale-edge block - sum of its units; mirrored.
+__global__ void ba_schur_finalize(int n_seg, int n, const int* __restrict__ seg_a,
+                                  const int* __restrict__ seg_b,
+                                  const int* __restrict__ seg_unit_start,
+                                  const double* __restrict__ partial,
+                                  const double* __restrict__ Hpp,
+                                  const double* __restrict__ extra,
+                                  const int* __restrict__ seg_extra_idx, double lambda,
+                                  double* __restrict__ S) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int seg = t / 36, e = t % 36;
+  if (seg >= n_seg) return;
+  const int a = seg_a[seg], b = seg_b[seg], r = e / 6, c = e % 6;
+  const int ex = seg_extra_idx[seg];
+  double v = ex >= 0 ? extra[(size_t)ex * 36 + e] : 0.0;
+  if (a == b) v += Hpp[36 * a + e] + (r == c ? lambda : 0.0);
+  double s = 0.0;
+  for (int u = seg_unit_start[seg]; u < seg_unit_start[seg + 1]; ++u) s += partial[(size_t)u * 36 + e];
+  v -= s;
+  S[(size_t)(6 * a + r) * n + 6 * b + c] = v;
+  if (a != b) S[(size_t)(6 * b + c) * n + 6 * a + r] = v;
+}
+
+// Back-substitution, camera-major half: v_o = Hpl_o^T dp_cam(o), scattered to the point-major slot.
+__global__ void __launch_bounds__(kCamThreads)
+ba_backsub_cam(BAView V, const double* __restrict__ Hpl, const double* __restrict__ dp,
+               double* __restrict__ tmp3) {
+  const int c = blockIdx.y, chunk = blockIdx.x;
+  const int start = V.cm_start[c] + chunk * kCamChunk;
+  const int end = min(V.cm_start[c + 1], start + kCamChunk);
+  const int col = V.cam_col[c];
+  if (start >= end || col < 0) return;
+  double d[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) d[i] = dp[6 * col + i];
+  for (int o = start + threadIdx.x; o < end; o += kCamThreads) {
+    if (V.pt_col[V.cm_pt[o]] < 0) continue;
+    double h[18];
+    load18(Hpl + (size_t)o * 18, h);
+    double v[3] = {0, 0, 0};
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+#pragma unroll
+      for (int j = 0; j < 3; ++j) v[j] += h[3 * r + j] * d[r];
+    }
+    double* dst = tmp3 + (size_t)V.cm_pm[o] * 3;
+    dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2];
+  }
+}
+
+// Back-substitution, point half: dl = Hinv (bl - sum_o v_o); trial point = point + dl.
+// Also the per-CTA partial of sum dl (lambda dl + bl)  (computeScale, landmark part).
+__global__ void __launch_bounds__(256)
+ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restrict__ Hinv,
+              const double* __restrict__ bl, double lambda, const double* __restrict__ pts,
+              double* __restrict__ pts_trial, double* __restrict__ dl_out,
+              double* __restrict__ scale_partial) {
+  __shared__ double red[8];
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  double sc[1] = {0.0};
+  if (p < V.P) {
+    const int col = V.pt_col[p];
+    double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
+    if (col >= 0) {
+      double r[3] = {bl[3 * (size_t)col], bl[3 * (size_t)col + 1], bl[3 * (size_t)col + 2]};
+      const double b0 = r[0], b1 = r[1], b2 = r[2];
+      for (int o = V.pt_start[p]; o < V.pt_start[p + 1]; ++o) {
+        if (V.cam_col[V.pm_cam[o]] < 0) continue;
+        r[0] -= tmp3[3 * (size_t)o]; r[1] -= tmp3[3 * (size_t)o + 1]; r[2] -= tmp3[3 * (size_t)o + 2];
+      }
+      double hi[6], d[3];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) hi[j] = Hinv[6 * (size_t)col + j];
+      sym3_mul(hi, r, d);
+      sc[0] = d[0] * (lambda * d[0] + b0) + d[1] * (lambda * d[1] + b1) + d[2] * (lambda * d[2] + b2);
+      X[0] += d[0]; X[1] += d[1]; X[2] += d[2];
+      dl_out[3 * (size_t)col] = d[0]; dl_out[3 * (size_t)col + 1] = d[1]; dl_out[3 * (size_t)col + 2] = d[2];
+    }
+    pts_trial[3 * p] = X[0]; pts_trial[3 * p + 1] = X[1]; pts_trial[3 * p + 2] = X[2];
+  }
+  block_reduce<1, 256>(sc, red);
+  if (threadIdx.x == 0) scale_partial[blockIdx.x] = sc[0];
+}
+
+// SBACam::update on every free camera (t += d[0:3]; q <- normalize(q * (sqrt(1-|v|^2), v))).
+__global__ void ba_update_cams(BAView V, const double* __restrict__ cams,
+                               const double* __restrict__ dp, double* __restrict__ cams_trial,
+                               CamRT* __restrict__ camrt_trial) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= V.C) return;
+  double q[4] = {cams[7 * c], cams[7 * c + 1], cams[7 * c + 2], cams[7 * c + 3]};
+  double t[3] = {cams[7 * c + 4], cams[7 * c + 5], cams[7 * c + 6]};
+  const int col = V.cam_col[c];
+  if (col >= 0) {
+    const double* d = dp + 6 * col;
+    t[0] += d[0]; t[1] += d[1]; t[2] += d[2];
+    const double vx = d[3], vy = d[4], vz = d[5];
+    const double vw = sqrt(1.0 - (vx * vx + vy * vy + vz * vz));
+    const double x = q[3] * vx + q[0] * vw + q[1] * vz - q[2] * vy;
+    const double y = q[3] * vy - q[0] * vz + q[1] * vw + q[2] * vx;
+    const double z = q[3] * vz + q[0] * vy - q[1] * vx + q[2] * vw;
+    const double w = q[3] * vw - q[0] * vx - q[1] * vy - q[2] * vz;
+    const double inv = 1.0 / sqrt(x * x + y * y + z * z + w * w);
+    q[0] = x * inv; q[1] = y * inv; q[2] = z * inv; q[3] = w * inv;
+  }
+  double* o = cams_trial + 7 * c;
+  o[0] = q[0]; o[1] = q[1]; o[2] = q[2]; o[3] = q[3]; o[4] = t[0]; o[5] = t[1]; o[6] = t[2];
+  CamRT r;
+  quat_to_R(q, r.R);
+  r.t[0] = t[0]; r.t[1] = t[1]; r.t[2] = t[2];
+  camrt_trial[c] = r;
+}
+
+}  // namespace vslam

@@ -1,0 +1,213 @@
+// Preconditioned conjugate gradients on the dense reduced camera system S x = b (n = 6 * free cams),
+// block-Jacobi (6x6) preconditioner.  Replaces g2o LinearSolverCholmodSE3 (reference
+// src/v2/LocalBA.py:23) as BASELINE.json's north_star prescribes.
+//
+// One cooperative launch: CTA g owns a slab of `rows` rows of S, kept in shared memory for the whole
+// solve, so an iteration moves only the search direction (n doubles) through L2.  Dot products are
+// per-CTA partials summed in a fixed order by every CTA after a grid barrier -> bit-reproducible.
+// A non-positive curvature p^T S p (or a non-SPD diagonal block) reports status 1: the LM loop
+// treats that exactly like g2o treats a failed Cholesky (rejected step; cf. reference debug.txt).
+#pragma once
+#include "common.cuh"
+
+namespace vslam {
+
+struct PcgArgs {
+  const double* S; const double* b; double* x;
+  int n, rows, G, slab_in_smem, max_iter;
+  double tol;
+  double* p_glob;     // [n]
+  double* part;       // [4 * G]
+  unsigned* bar;      // grid barrier counter (zeroed before launch)
+  int* fail_flag;     // zeroed before launch
+  int* status;        // out: 0 converged, 1 breakdown (indefinite), 2 max_iter reached
+  int* iters;         // out
+};
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target, int G) {
+  __syncthreads();
+  if (G > 1 && threadIdx.x == 0) {
+    target += (unsigned)G;
+    __threadfence();
+    atomicAdd(bar, 1u);
+    while (ld_acquire_u32(bar) < target) {}
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// In-place inverse of a 6x6 SPD matrix via Cholesky; returns false if a pivot is not positive.
+__device__ inline bool spd6_inverse(double* A /* 36 row-major */) {
+  double L[36];
+#pragma unroll 1
+  for (int j = 0; j < 6; ++j) {
+    double d = A[7 * j];
+    for (int k = 0; k < j; ++k) d -= L[6 * j + k] * L[6 * j + k];
+    if (!(d > 0.0)) return false;
+    d = sqrt(d);
+    L[7 * j] = d;
+    for (int i = j + 1; i < 6; ++i) {
+      double s = A[6 * i + j];
+      for (int k = 0; k < j; ++k) s -= L[6 * i + k] * L[6 * j + k];
+      L[6 * i + j] = s / d;
+    }
+  }
+  // inverse of L (lower), then A^-1 = L^-T L^-1
+  double Li[36];
+  for (int i = 0; i < 36; ++i) Li[i] = 0.0;
+  for (int j = 0; j < 6; ++j) {
+    Li[7 * j] = 1.0 / L[7 * j];
+    for (int i = j + 1; i < 6; ++i) {
+      double s = 0.0;
+      for (int k = j; k < i; ++k) s -= L[6 * i + k] * Li[6 * k + j];
+      Li[6 * i + j] = s / L[7 * i];
+    }
+  }
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) {
+      double s = 0.0;
+      for (int k = (i > j ? i : j); k < 6; ++k) s += Li[6 * k + i] * Li[6 * k + j];
+      A[6 * i + j] = s;
+    }
+  return true;
+}
+
+constexpr int kPcgThreads = 256;
+
+__device__ __forceinline__ double block_sum1(double v, double* red) {
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double s = 0.0;
+  for (int w = 0; w < kPcgThreads / 32; ++w) s += red[w];
+  __syncthreads();
+  return s;  // every thread holds the same, order-fixed sum
+}
+
+__device__ __forceinline__ double ordered_sum(const double* part, int G) {
+  double s = 0.0;
+  for (int g = 0; g < G; ++g) s += __ldcg(part + g);
+  return s;
+}
+
+__global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
+  extern __shared__ __align__(16) double sm[];
+  const int n = A.n, G = A.G, g = blockIdx.x, tid = threadIdx.x;
+  const int row0 = g * A.rows;
+  const int R = max(0, min(A.rows, n - row0));
+  double* p_full = sm;                 // [n]
+  double* xl = p_full + n;             // [rows] each
+  double* rl = xl + A.rows;
+  double* zl = rl + A.rows;
+  double* pl = zl + A.rows;
+  double* apl = pl + A.rows;
+  double* minv = apl + A.rows;         // [rows/6][36]
+  double* red = minv + 6 * A.rows;     // [8]
+  double* slab = red + 8;              // [rows][n] when slab_in_smem
+  __shared__ int s_fail;
+  unsigned target = 0;
+
+  if (tid == 0) s_fail = 0;
+  if (A.slab_in_smem) {
+    for (int i = tid; i < R * n; i += kPcgThreads) slab[i] = A.S[(size_t)row0 * n + i];
+  }
+  __syncthreads();
+  const double* Srows = A.slab_in_smem ? slab : A.S + (size_t)row0 * n;
+  // block-Jacobi preconditioner: invert the local diagonal 6x6 blocks
+  for (int bi = tid; bi < R / 6; bi += kPcgThreads) {
+    double blk[36];
+    for (int i = 0; i < 6; ++i)
+      for (int j = 0; j < 6; ++j) blk[6 * i + j] = Srows[(size_t)(6 * bi + i) * n + row0 + 6 * bi + j];
+    if (!spd6_inverse(blk)) s_fail = 1;
+    for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
+  }
+  __syncthreads();
+  if (tid == 0 && s_fail) atomicExch(A.fail_flag, 1);
+  // x = 0, r = b, z = M^-1 r, p = z
+  double rz_p = 0.0, bb_p = 0.0;
+  for (int i = tid; i < R; i += kPcgThreads) { xl[i] = 0.0; rl[i] = A.b[row0 + i]; }
+  __syncthreads();
+  for (int i = tid; i < R; i += kPcgThreads) {
+    const int bi = i / 6, ii = i % 6;
+    double z = 0.0;
+    for (int j = 0; j < 6; ++j) z += minv[36 * bi + 6 * ii + j] * rl[6 * bi + j];
+    zl[i] = z; pl[i] = z;
+    A.p_glob[row0 + i] = z;
+    rz_p += rl[i] * z;
+    bb_p += rl[i] * rl[i];
+  }
+  rz_p = block_sum1(rz_p, red);
+  bb_p = block_sum1(bb_p, red);
+  if (tid == 0) { A.part[g] = rz_p; A.part[G + g] = bb_p; }
+  grid_barrier(A.bar, target, G);
+  if (__ldcg(A.fail_flag)) {
+    for (int i = tid; i < R; i += kPcgThreads) A.x[row0 + i] = 0.0;
+    if (g == 0 && tid == 0) { *A.status = 1; *A.iters = 0; }
+    return;
+  }
+  double rz = ordered_sum(A.part, G);
+  const double bnorm2 = ordered_sum(A.part + G, G);
+  grid_barrier(A.bar, target, G);  // part[] may be rewritten from here on
+  int status = 2, it = 0;
+  if (!(bnorm2 > 0.0)) { status = 0; }
+  else {
+    const double thresh = A.tol * A.tol * bnorm2;
+    const int lane = tid & 31, wid = tid >> 5;
+    for (it = 0; it < A.max_iter; ++it) {
+      for (int i = tid; i < n; i += kPcgThreads) p_full[i] = __ldcg(A.p_glob + i);
+      __syncthreads();
+      // Ap for the local rows: one warp per row
+      for (int r = wid; r < R; r += kPcgThreads / 32) {
+        const double* row = Srows + (size_t)r * n;
+        double s = 0.0;
+        for (int j = lane; j < n; j += 32) s += row[j] * p_full[j];
+        s = warp_sum(s);
+        if (lane == 0) apl[r] = s;
+      }
+      __syncthreads();
+      double pap_p = 0.0;
+      for (int i = tid; i < R; i += kPcgThreads) pap_p += pl[i] * apl[i];
+      pap_p = block_sum1(pap_p, red);
+      if (tid == 0) A.part[2 * G + g] = pap_p;
+      grid_barrier(A.bar, target, G);
+      const double pap = ordered_sum(A.part + 2 * G, G);
+      if (!(pap > 0.0) || !isfinite(pap)) { status = 1; break; }
+      const double alpha = rz / pap;
+      for (int i = tid; i < R; i += kPcgThreads) { xl[i] += alpha * pl[i]; rl[i] -= alpha * apl[i]; }
+      __syncthreads();
+      double rzn_p = 0.0, rr_p = 0.0;
+      for (int i = tid; i < R; i += kPcgThreads) {
+        const int bi = i / 6, ii = i % 6;
+        double z = 0.0;
+        for (int j = 0; j < 6; ++j) z += minv[36 * bi + 6 * ii + j] * rl[6 * bi + j];
+        zl[i] = z;
+        rzn_p += rl[i] * z;
+        rr_p += rl[i] * rl[i];
+      }
+      rzn_p = block_sum1(rzn_p, red);
+      rr_p = block_sum1(rr_p, red);
+      if (tid == 0) { A.part[g] = rzn_p; A.part[G + g] = rr_p; }
+      grid_barrier(A.bar, target, G);
+      const double rzn = ordered_sum(A.part, G);
+      const double rr = ordered_sum(A.part + G, G);
+      if (rr <= thresh) { status = 0; ++it; break; }
+      const double beta = rzn / rz;
+      rz = rzn;
+      for (int i = tid; i < R; i += kPcgThreads) {
+        pl[i] = zl[i] + beta * pl[i];
+        A.p_glob[row0 + i] = pl[i];
+      }
+      grid_barrier(A.bar, target, G);
+    }
+  }
+  for (int i = tid; i < R; i += kPcgThreads) A.x[row0 + i] = (status == 1) ? 0.0 : xl[i];
+  if (g == 0 && tid == 0) { *A.status = status; *A.iters = it; }
+}
+
+}  // namespace vslam
