@@ -96,6 +96,46 @@ int vslam_microbench_popc(int iters, double* popc_per_s, void* stream);
 
 
 /* ------------------------------------------------------------------------- */
+/* 2. RANSAC pose (PnP)                                                       */
+/* ------------------------------------------------------------------------- */
+/*
+ * Together these replace cv2.solvePnPRansac(objectPoints, imagePoints, cameraMatrix, distCoeffs=[],
+ * rvec, tvec, useExtrinsicGuess=True) as called at reference src/v2/main.py:196-197 (defaults:
+ * 100 iterations, reprojectionError 8.0, confidence 0.99), batched over frame pairs.
+ *
+ *   X      dev f32 [batch][n_max][3]   object points (world), first n_pts[b] rows valid
+ *   uv     dev f32 [batch][n_max][2]   image points (pixels)
+ *   n_pts  dev i32 [batch]
+ *   K      host f64[4]                 fx, fy, cx, cy (no distortion, as the reference passes [])
+ *   words  dev u32 [batch][H][4]       harness-drawn random words; sample index j of hypothesis h is
+ *                                      (word * n) >> 32 with duplicates stepped to the next free index
+ *   hyps   dev f64 [batch][H][12]      world->camera [R|t], row-major 3x4
+ *   valid  dev u8  [batch][H]
+ */
+/* Minimal solver: P3P on three correspondences, the fourth picks among the solutions. */
+int vslam_pnp_hypotheses(const float* X, const float* uv, const int32_t* n_pts, int n_max, int batch,
+                         const uint32_t* words, int H, const double* K, double* hyps, uint8_t* valid,
+                         void* stream);
+/* Inlier count of every hypothesis; inlier iff |uv - proj|^2 <= thr^2 with OpenCV's float32
+ * semantics (PnPRansacCallback::computeError).  One warp per hypothesis.  counts dev i32 [batch][H]. */
+int vslam_pnp_score(const float* X, const float* uv, const int32_t* n_pts, int n_max, int batch,
+                    const double* hyps, const uint8_t* valid, int H, const double* K, double thr,
+                    int32_t* counts, void* stream);
+/*
+ * Selection with OpenCV's shrinking iteration budget (RANSACUpdateNumIters), inlier mask of the
+ * winner, then iterative refinement on the inliers from the caller's guess (cv2 "Stage B").
+ *   guess, pose  dev f64 [batch][6]   rvec (3) + tvec (3), world->camera
+ *   best         dev i32 [batch]      winning hypothesis or -1
+ *   inlier_bits  dev u32 [batch][ceil(n_max/32)]
+ *   n_inliers    dev i32 [batch];  status dev i32 [batch]: 0 ok, 1 no model, 2 refinement breakdown
+ */
+int vslam_pnp_select_refine(const float* X, const float* uv, const int32_t* n_pts, int n_max, int batch,
+                            const double* hyps, const uint8_t* valid, const int32_t* counts, int H,
+                            const double* K, double thr, double confidence, const double* guess,
+                            int max_refine_iters, int32_t* best, uint32_t* inlier_bits,
+                            int32_t* n_inliers, double* pose, int32_t* status, void* stream);
+
+/* ------------------------------------------------------------------------- */
 /* 3. Bundle adjustment                                                       */
 /* ------------------------------------------------------------------------- */
 /*

@@ -27,6 +27,11 @@ def _declare(lib):
     lib.vslam_match_filter.argtypes = [vp, vp, vp, i32, i32, f64, i32, vp, vp, vp, i32, vp]
     lib.vslam_microbench_popc.argtypes = [i32, C.POINTER(f64), vp]
     lib.vslam_hamming_set_variant.argtypes = [i32]
+    pd = C.POINTER(f64)
+    lib.vslam_pnp_hypotheses.argtypes = [vp, vp, vp, i32, i32, vp, i32, pd, vp, vp, vp]
+    lib.vslam_pnp_score.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, pd, f64, vp, vp]
+    lib.vslam_pnp_select_refine.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, i32, pd, f64, f64, vp, i32,
+                                            vp, vp, vp, vp, vp, vp]
     pp = C.POINTER(vp)
     lib.vslam_ba_create.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.vslam_ba_destroy.argtypes = [vp]

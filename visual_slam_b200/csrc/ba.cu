@@ -12,87 +12,104 @@
 
 namespace vslam {
 
-// scale edges (EdgeSBAScale + DCS, LocalBA.py:115-131): sequential, E is tiny.
-// cost_only = evaluate sum(rho) on the given cameras; else also fill the extra blocks / bp_extra.
-__global__ void ba_scale_edges(int E, const int* __restrict__ sa, const int* __restrict__ sb,
-                               const double* __restrict__ meas, const double* __restrict__ cams,
-                               const int* __restrict__ cam_col, const int* __restrict__ ex_aa,
-                               const int* __restrict__ ex_ab, const int* __restrict__ ex_bb,
-                               int n_extra, int Cf, int cost_only, double* __restrict__ extra,
-                               double* __restrict__ bp_extra, double* __restrict__ scale_cost) {
-  if (blockIdx.x != 0 || threadIdx.x != 0) return;
-  if (!cost_only) {
-    for (int i = 0; i < n_extra * 36; ++i) extra[i] = 0.0;
-    for (int i = 0; i < Cf * 6; ++i) bp_extra[i] = 0.0;
-  }
-  double cost = 0.0;
-  for (int k = 0; k < E; ++k) {
-    const double* ta = cams + 7 * sa[k] + 4;
-    const double* tb = cams + 7 * sb[k] + 4;
+// Scale edges (EdgeSBAScale + DCS, LocalBA.py:115-131).  One CTA: (1) thread per edge evaluates
+// residual / weight / direction, (2) thread per extra S block and per free camera gathers the
+// contributions of its incident edges in edge order (CSR built on the host) -> deterministic.
+struct ScaleView {
+  int E, n_extra, Cf;
+  const int* sa; const int* sb; const double* meas; const int* cam_col;
+  const int* inc_start; const int* inc_edge;   // per free camera: incident edge ids (ascending)
+  const int* extra_a; const int* extra_b;      // free-camera columns of each extra block (a <= b)
+  double* edge_w; double* edge_es; double* edge_u;  // [E], [E], [E][3]
+};
+
+__global__ void __launch_bounds__(256)
+ba_scale_edges(ScaleView V, const double* __restrict__ cams, int cost_only, double* __restrict__ extra,
+               double* __restrict__ bp_extra, double* __restrict__ scale_cost,
+               unsigned long long* __restrict__ maxdiag_bits) {
+  __shared__ double red[8];
+  double c[1] = {0.0};
+  for (int k = threadIdx.x; k < V.E; k += 256) {
+    const double* ta = cams + 7 * V.sa[k] + 4;
+    const double* tb = cams + 7 * V.sb[k] + 4;
     const double d[3] = {tb[0] - ta[0], tb[1] - ta[1], tb[2] - ta[2]};
     const double nrm = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
-    const double es = meas[k] - nrm;
+    const double es = V.meas[k] - nrm;
     double rho, w;
     dcs(es * es, rho, w);
-    cost += rho;
-    if (cost_only) continue;
-    const double u[3] = {d[0] / nrm, d[1] / nrm, d[2] / nrm};  // d e / d ta = +u, d e / d tb = -u
-    const int ca = cam_col[sa[k]], cb = cam_col[sb[k]];
-    for (int i = 0; i < 3; ++i) {
-      if (ca >= 0) bp_extra[6 * ca + i] += -w * u[i] * es;
-      if (cb >= 0) bp_extra[6 * cb + i] += w * u[i] * es;
-      for (int j = 0; j < 3; ++j) {
-        const double h = w * u[i] * u[j];
-        if (ex_aa[k] >= 0) extra[36 * ex_aa[k] + 6 * i + j] += h;
-        if (ex_bb[k] >= 0) extra[36 * ex_bb[k] + 6 * i + j] += h;
-        if (ex_ab[k] >= 0) extra[36 * ex_ab[k] + 6 * i + j] -= h;
-      }
+    c[0] += rho;
+    if (!cost_only) {
+      V.edge_w[k] = w; V.edge_es[k] = es;
+      V.edge_u[3 * k] = d[0] / nrm; V.edge_u[3 * k + 1] = d[1] / nrm; V.edge_u[3 * k + 2] = d[2] / nrm;
     }
   }
-  *scale_cost = cost;
-}
-
-// res[0] = sum cam_cost + scale cost; res[1] = computeScale: sum x (lambda x + b) over cams + points
-__global__ void ba_finish(int C, const double* __restrict__ cam_cost,
-                          const double* __restrict__ scale_cost, int n_sp,
-                          const double* __restrict__ scale_partial, int n, const double* __restrict__ dp,
-                          const double* __restrict__ bp, double lambda, const int* __restrict__ pcg_status,
-                          const int* __restrict__ pcg_iters, double* __restrict__ res) {
-  if (blockIdx.x != 0 || threadIdx.x != 0) return;
-  double c = 0.0;
-  for (int i = 0; i < C; ++i) c += cam_cost[i];
-  res[0] = c + *scale_cost;
-  if (dp) {
-    double s = 0.0;
-    for (int i = 0; i < n; ++i) s += dp[i] * (lambda * dp[i] + bp[i]);
-    for (int i = 0; i < n_sp; ++i) s += scale_partial[i];
-    res[1] = s;
-    res[3] = (double)*pcg_status;
-    res[4] = (double)*pcg_iters;
-  }
-}
-
-// computeLambdaInit: max |diag H| over free cameras (incl. scale-edge part) and free points.
-__global__ void ba_max_diag(int Cf, const double* __restrict__ Hpp, const int* __restrict__ diag_extra,
-                            const double* __restrict__ extra, int Pf, const double* __restrict__ Hll,
-                            double* __restrict__ res) {
-  __shared__ double red[8];
-  double m = 0.0;
-  for (int i = threadIdx.x; i < Cf * 6; i += blockDim.x) {
-    const int c = i / 6, k = i % 6;
-    double v = Hpp[36 * c + 7 * k];
-    if (diag_extra[c] >= 0) v += extra[36 * diag_extra[c] + 7 * k];
-    m = fmax(m, fabs(v));
-  }
-  for (int i = threadIdx.x; i < Pf; i += blockDim.x) {
-    m = fmax(m, fmax(fabs(Hll[6 * (size_t)i]), fmax(fabs(Hll[6 * (size_t)i + 3]), fabs(Hll[6 * (size_t)i + 5]))));
-  }
-  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
-  __syncthreads();
+  block_reduce<1, 256>(c, red);
   if (threadIdx.x == 0) {
-    for (int w = 0; w < (int)blockDim.x / 32; ++w) m = fmax(m, red[w]);
-    res[2] = m;
+    *scale_cost = c[0];
+    if (!cost_only) *maxdiag_bits = 0ull;
+  }
+  if (cost_only) return;
+  __threadfence_block();
+  __syncthreads();
+  for (int x = threadIdx.x; x < V.n_extra; x += 256) {
+    const int a = V.extra_a[x], b = V.extra_b[x];
+    double h[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int q = V.inc_start[a]; q < V.inc_start[a + 1]; ++q) {
+      const int k = V.inc_edge[q];
+      const int ca = V.cam_col[V.sa[k]], cb = V.cam_col[V.sb[k]];
+      double sgn;
+      if (a == b) sgn = 1.0;                                         // diagonal: every incident edge
+      else if ((ca == a && cb == b) || (ca == b && cb == a)) sgn = -1.0;  // off-diagonal: edges a-b
+      else continue;
+      const double w = V.edge_w[k];
+      const double* u = V.edge_u + 3 * k;
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) h[3 * i + j] += sgn * w * u[i] * u[j];
+    }
+    double* o = extra + 36 * (size_t)x;
+    for (int i = 0; i < 36; ++i) o[i] = 0.0;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) o[6 * i + j] = h[3 * i + j];
+  }
+  for (int col = threadIdx.x; col < V.Cf; col += 256) {
+    double g[3] = {0, 0, 0};
+    for (int q = V.inc_start[col]; q < V.inc_start[col + 1]; ++q) {
+      const int k = V.inc_edge[q];
+      // d e / d t_a = +u, d e / d t_b = -u ;  b += -w J e
+      const double sgn = (V.cam_col[V.sa[k]] == col) ? -1.0 : 1.0;
+      const double f = sgn * V.edge_w[k] * V.edge_es[k];
+      g[0] += f * V.edge_u[3 * k]; g[1] += f * V.edge_u[3 * k + 1]; g[2] += f * V.edge_u[3 * k + 2];
+    }
+    double* o = bp_extra + 6 * col;
+    o[0] = g[0]; o[1] = g[1]; o[2] = g[2]; o[3] = 0.0; o[4] = 0.0; o[5] = 0.0;
+  }
+}
+
+// res[0] = sum cam_cost + scale cost; res[1] = computeScale: sum x (lambda x + b) over cams + points.
+// One CTA, strided partials + fixed-order tree.
+__global__ void __launch_bounds__(256)
+ba_finish(int C, const double* __restrict__ cam_cost, const double* __restrict__ scale_cost, int n_sp,
+          const double* __restrict__ scale_partial, int n, const double* __restrict__ dp,
+          const double* __restrict__ bp, double lambda, const int* __restrict__ pcg_status,
+          const int* __restrict__ pcg_iters, const unsigned long long* __restrict__ maxdiag_bits,
+          double* __restrict__ res) {
+  __shared__ double red[16];
+  double v[2] = {0.0, 0.0};
+  for (int i = threadIdx.x; i < C; i += 256) v[0] += cam_cost[i];
+  if (dp) {
+    for (int i = threadIdx.x; i < n; i += 256) v[1] += dp[i] * (lambda * dp[i] + bp[i]);
+    for (int i = threadIdx.x; i < n_sp; i += 256) v[1] += scale_partial[i];
+  }
+  block_reduce<2, 256>(v, red);
+  if (threadIdx.x == 0) {
+    res[0] = v[0] + *scale_cost;
+    if (dp) {
+      res[1] = v[1];
+      res[3] = (double)*pcg_status;
+      res[4] = (double)*pcg_iters;
+    } else {
+      res[2] = __longlong_as_double((long long)*maxdiag_bits);  // computeLambdaInit's max |diag H|
+    }
   }
 }
 
@@ -125,7 +142,9 @@ struct BA {
   // structure
   DevBuf<int> cam_col, pt_col, cm_start, cm_pt, cm_pm, cm_src, pt_start, pm_cam, pm_src;
   DevBuf<int> item_a, item_b, unit_start, unit_len, seg_a, seg_b, seg_unit_start, seg_extra_idx;
-  DevBuf<int> sa, sb, ex_aa, ex_ab, ex_bb, diag_extra;
+  DevBuf<int> sa, sb, diag_extra, inc_start, inc_edge, extra_a, extra_b;
+  DevBuf<double> edge_w, edge_es, edge_u;
+  DevBuf<unsigned long long> maxdiag;
   DevBuf<double2> cm_uv, pm_uv;
   // state: [0] current, [1] trial
   DevBuf<double> cams[2], pts[2], scale_meas;
@@ -150,6 +169,13 @@ struct BA {
     V.cam_col = cam_col.p; V.pt_col = pt_col.p; V.cm_start = cm_start.p; V.cm_pt = cm_pt.p;
     V.cm_pm = cm_pm.p; V.cm_uv = cm_uv.p; V.pt_start = pt_start.p; V.pm_cam = pm_cam.p;
     V.pm_uv = pm_uv.p;
+    return V;
+  }
+  ScaleView scale_view() const {
+    ScaleView V;
+    V.E = E; V.n_extra = n_extra; V.Cf = Cf; V.sa = sa.p; V.sb = sb.p; V.meas = scale_meas.p;
+    V.cam_col = cam_col.p; V.inc_start = inc_start.p; V.inc_edge = inc_edge.p; V.extra_a = extra_a.p;
+    V.extra_b = extra_b.p; V.edge_w = edge_w.p; V.edge_es = edge_es.p; V.edge_u = edge_u.p;
     return V;
   }
   ~BA() { if (res_host) cudaFreeHost(res_host); }
@@ -227,7 +253,6 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   std::vector<char> present((size_t)Cf * Cf, 0);
   for (size_t k = 0; k < (size_t)Cf * Cf; ++k) present[k] = cnt[k + 1] > 0;
   for (int c = 0; c < Cf; ++c) present[(size_t)c * Cf + c] = 1;
-  std::vector<int> ex_aa(E, -1), ex_ab(E, -1), ex_bb(E, -1);
   for (int k = 0; k < E; ++k) {
     const int ca = cam_col[sa[k]], cb = cam_col[sb[k]];
     if (ca >= 0 && cb >= 0) present[(size_t)std::min(ca, cb) * Cf + std::max(ca, cb)] = 1;
@@ -255,19 +280,31 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     }
   seg_unit_start.push_back((int)unit_start.size());
   B.n_items = (int)n_items; B.n_units = (int)unit_start.size(); B.n_seg = (int)seg_a.size();
-  // extra (scale-edge) blocks: one per touched segment
-  std::vector<int> seg_extra_idx(B.n_seg, -1), diag_extra(Cf, -1);
+  // extra (scale-edge) blocks: one per touched segment; incident-edge CSR per free camera
+  std::vector<int> seg_extra_idx(B.n_seg, -1), diag_extra(Cf, -1), extra_a, extra_b;
   int n_extra = 0;
   auto touch = [&](int a, int b) {
-    int seg = seg_of_key[(size_t)std::min(a, b) * Cf + std::max(a, b)];
-    if (seg_extra_idx[seg] < 0) seg_extra_idx[seg] = n_extra++;
+    const int lo = std::min(a, b), hi = std::max(a, b);
+    int seg = seg_of_key[(size_t)lo * Cf + hi];
+    if (seg_extra_idx[seg] < 0) { seg_extra_idx[seg] = n_extra++; extra_a.push_back(lo); extra_b.push_back(hi); }
     return seg_extra_idx[seg];
   };
+  std::vector<int> inc_start(Cf + 1, 0), inc_edge;
   for (int k = 0; k < E; ++k) {
     const int ca = cam_col[sa[k]], cb = cam_col[sb[k]];
-    if (ca >= 0) { ex_aa[k] = touch(ca, ca); diag_extra[ca] = ex_aa[k]; }
-    if (cb >= 0) { ex_bb[k] = touch(cb, cb); diag_extra[cb] = ex_bb[k]; }
-    if (ca >= 0 && cb >= 0) ex_ab[k] = touch(ca, cb);
+    if (ca >= 0) { diag_extra[ca] = touch(ca, ca); inc_start[ca + 1]++; }
+    if (cb >= 0) { diag_extra[cb] = touch(cb, cb); inc_start[cb + 1]++; }
+    if (ca >= 0 && cb >= 0) touch(ca, cb);
+  }
+  for (int c = 0; c < Cf; ++c) inc_start[c + 1] += inc_start[c];
+  inc_edge.resize(inc_start[Cf]);
+  {
+    std::vector<int> fill(inc_start.begin(), inc_start.end() - 1);
+    for (int k = 0; k < E; ++k) {
+      const int ca = cam_col[sa[k]], cb = cam_col[sb[k]];
+      if (ca >= 0) inc_edge[fill[ca]++] = k;
+      if (cb >= 0) inc_edge[fill[cb]++] = k;
+    }
   }
   B.n_extra = n_extra;
   B.n_sp = (P + 255) / 256;
@@ -280,7 +317,9 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.seg_a.upload(seg_a)); BA_TRY(B.seg_b.upload(seg_b));
   BA_TRY(B.seg_unit_start.upload(seg_unit_start)); BA_TRY(B.seg_extra_idx.upload(seg_extra_idx));
   BA_TRY(B.sa.upload(std::vector<int>(sa, sa + E))); BA_TRY(B.sb.upload(std::vector<int>(sb, sb + E)));
-  BA_TRY(B.ex_aa.upload(ex_aa)); BA_TRY(B.ex_ab.upload(ex_ab)); BA_TRY(B.ex_bb.upload(ex_bb));
+  BA_TRY(B.inc_start.upload(inc_start)); BA_TRY(B.inc_edge.upload(inc_edge));
+  BA_TRY(B.extra_a.upload(extra_a)); BA_TRY(B.extra_b.upload(extra_b));
+  BA_TRY(B.edge_w.alloc(E)); BA_TRY(B.edge_es.alloc(E)); BA_TRY(B.edge_u.alloc((size_t)E * 3)); BA_TRY(B.maxdiag.alloc(1));
   BA_TRY(B.diag_extra.upload(diag_extra));
   BA_TRY(B.cm_uv.alloc(N)); BA_TRY(B.pm_uv.alloc(N)); BA_TRY(B.scale_meas.alloc(E));
   for (int s = 0; s < 2; ++s) {
@@ -360,15 +399,15 @@ static int ba_linearize(BA& B, cudaStream_t st) {
   const int s = B.cur;
   if (B.C == 0) return VSLAM_ERR_BAD_ARG;
   dim3 grid(B.max_chunks, B.C);
-  ba_scale_edges<<<1, 32, 0, st>>>(B.E, B.sa.p, B.sb.p, B.scale_meas.p, B.cams[s].p, B.cam_col.p,
-                                   B.ex_aa.p, B.ex_ab.p, B.ex_bb.p, B.n_extra, B.Cf, 0, B.extra.p,
-                                   B.bp_extra.p, B.scale_cost.p);
+  ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), B.cams[s].p, 0, B.extra.p, B.bp_extra.p, B.scale_cost.p,
+                                    B.maxdiag.p);
   ba_cam_pass<false><<<grid, kCamThreads, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hpl.p, B.camp.p);
-  ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp_extra.p, B.Hpp.p, B.bp.p, B.cam_cost.p);
-  if (B.P) ba_point_pass<<<(B.P + 127) / 128, 128, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hll.p, B.bl.p);
-  ba_max_diag<<<1, 256, 0, st>>>(B.Cf, B.Hpp.p, B.diag_extra.p, B.extra.p, B.Pf, B.Hll.p, B.res.p);
-  ba_finish<<<1, 32, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, 0, nullptr, 0, nullptr, nullptr, 0.0,
-                              nullptr, nullptr, B.res.p);
+  ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp_extra.p, B.diag_extra.p, B.extra.p, B.Hpp.p, B.bp.p,
+                                      B.cam_cost.p, B.maxdiag.p);
+  if (B.P) ba_point_pass<<<(B.P + 127) / 128, 128, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hll.p, B.bl.p,
+                                                            B.maxdiag.p);
+  ba_finish<<<1, 256, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, 0, nullptr, 0, nullptr, nullptr, 0.0,
+                               nullptr, nullptr, B.maxdiag.p, B.res.p);
   int rc = check_launch("ba_linearize");
   if (rc) return rc;
   B.linearized = true;
@@ -418,12 +457,13 @@ static int ba_trial(BA& B, double lambda, cudaStream_t st) {
                                           B.dl.p, B.scale_partial.p);
   ba_update_cams<<<(B.C + 127) / 128, 128, 0, st>>>(V, B.cams[s].p, B.dp.p, B.cams[t].p, B.camrt[t].p);
   ba_cam_pass<true><<<grid, kCamThreads, 0, st>>>(V, B.camrt[t].p, B.pts[t].p, nullptr, B.camp.p);
-  ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, nullptr, nullptr, nullptr, B.cam_cost.p);
-  ba_scale_edges<<<1, 32, 0, st>>>(B.E, B.sa.p, B.sb.p, B.scale_meas.p, B.cams[t].p, B.cam_col.p,
-                                   B.ex_aa.p, B.ex_ab.p, B.ex_bb.p, B.n_extra, B.Cf, 1, B.extra.p,
-                                   B.bp_extra.p, B.scale_cost.p);
-  ba_finish<<<1, 32, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0, B.scale_partial.p, B.n,
-                              B.dp.p, B.bp.p, lambda, B.pcg_flags.p + 1, B.pcg_flags.p + 2, B.res.p);
+  ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, nullptr, nullptr, nullptr, nullptr, nullptr, B.cam_cost.p,
+                                      nullptr);
+  ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), B.cams[t].p, 1, B.extra.p, B.bp_extra.p, B.scale_cost.p,
+                                    B.maxdiag.p);
+  ba_finish<<<1, 256, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0, B.scale_partial.p, B.n,
+                               B.dp.p, B.bp.p, lambda, B.pcg_flags.p + 1, B.pcg_flags.p + 2, B.maxdiag.p,
+                               B.res.p);
   int rc = check_launch("ba_trial");
   if (rc) return rc;
   return ba_readback(B, st);

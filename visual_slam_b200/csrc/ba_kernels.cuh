@@ -102,9 +102,15 @@ ba_cam_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict_
 
 // Ordered sum of the chunk partials of each camera -> Hpp [Cf][36] (full symmetric), bp [Cf][6]
 // (+ scale-edge part), per-camera cost.
+__device__ __forceinline__ void atomic_max_nonneg(unsigned long long* bits, double v) {
+  atomicMax(bits, (unsigned long long)__double_as_longlong(fabs(v)));  // exact and order-independent
+}
+
 __global__ void ba_cam_finalize(BAView V, const double* __restrict__ camp,
-                                const double* __restrict__ bp_extra, double* __restrict__ Hpp,
-                                double* __restrict__ bp, double* __restrict__ cam_cost) {
+                                const double* __restrict__ bp_extra, const int* __restrict__ diag_extra,
+                                const double* __restrict__ extra, double* __restrict__ Hpp,
+                                double* __restrict__ bp, double* __restrict__ cam_cost,
+                                unsigned long long* __restrict__ maxdiag_bits) {
   const int c = blockIdx.x, i = threadIdx.x;
   if (i >= kCamVals) return;
   const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
@@ -120,41 +126,50 @@ __global__ void ba_cam_finalize(BAView V, const double* __restrict__ camp,
   const int cc = r + k;
   Hpp[36 * col + 6 * r + cc] = s;
   Hpp[36 * col + 6 * cc + r] = s;
+  if (r == cc) {  // computeLambdaInit: diagonal of the full camera block (projection + scale edges)
+    const int ex = diag_extra[col];
+    atomic_max_nonneg(maxdiag_bits, s + (ex >= 0 ? extra[36 * (size_t)ex + 7 * r] : 0.0));
+  }
 }
 
 // Point-major pass: one thread per free point walks its observations (fixed order).
 __global__ void ba_point_pass(BAView V, const CamRT* __restrict__ camrt,
                               const double* __restrict__ pts, double* __restrict__ Hll,
-                              double* __restrict__ bl) {
+                              double* __restrict__ bl, unsigned long long* __restrict__ maxdiag_bits) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= V.P) return;
-  const int col = V.pt_col[p];
-  if (col < 0) return;
-  const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
-  double h[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
-  for (int o = V.pt_start[p]; o < V.pt_start[p + 1]; ++o) {
-    const CamRT cam = camrt[V.pm_cam[o]];
-    const double2 uv = V.pm_uv[o];
-    double pc[3], e[2], rho, w;
-    to_camera(cam, X, pc);
-    if (!(fabs(pc[2]) > 1e-12)) continue;
-    residual(pc, V.K, uv.x, uv.y, e);
-    huber(e[0] * e[0] + e[1] * e[1], rho, w);
-    double Jc[2][6], Jp[2][3];
-    jacobians(cam, pc, V.K, Jc, Jp);
-    h[0] += w * (Jp[0][0] * Jp[0][0] + Jp[1][0] * Jp[1][0]);
-    h[1] += w * (Jp[0][0] * Jp[0][1] + Jp[1][0] * Jp[1][1]);
-    h[2] += w * (Jp[0][0] * Jp[0][2] + Jp[1][0] * Jp[1][2]);
-    h[3] += w * (Jp[0][1] * Jp[0][1] + Jp[1][1] * Jp[1][1]);
-    h[4] += w * (Jp[0][1] * Jp[0][2] + Jp[1][1] * Jp[1][2]);
-    h[5] += w * (Jp[0][2] * Jp[0][2] + Jp[1][2] * Jp[1][2]);
+  const int col = (p < V.P) ? V.pt_col[p] : -1;
+  double m = 0.0;
+  if (col >= 0) {
+    const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
+    double h[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
+    for (int o = V.pt_start[p]; o < V.pt_start[p + 1]; ++o) {
+      const CamRT cam = camrt[V.pm_cam[o]];
+      const double2 uv = V.pm_uv[o];
+      double pc[3], e[2], rho, w;
+      to_camera(cam, X, pc);
+      if (!(fabs(pc[2]) > 1e-12)) continue;
+      residual(pc, V.K, uv.x, uv.y, e);
+      huber(e[0] * e[0] + e[1] * e[1], rho, w);
+      double Jc[2][6], Jp[2][3];
+      jacobians(cam, pc, V.K, Jc, Jp);
+      h[0] += w * (Jp[0][0] * Jp[0][0] + Jp[1][0] * Jp[1][0]);
+      h[1] += w * (Jp[0][0] * Jp[0][1] + Jp[1][0] * Jp[1][1]);
+      h[2] += w * (Jp[0][0] * Jp[0][2] + Jp[1][0] * Jp[1][2]);
+      h[3] += w * (Jp[0][1] * Jp[0][1] + Jp[1][1] * Jp[1][1]);
+      h[4] += w * (Jp[0][1] * Jp[0][2] + Jp[1][1] * Jp[1][2]);
+      h[5] += w * (Jp[0][2] * Jp[0][2] + Jp[1][2] * Jp[1][2]);
 #pragma unroll
-    for (int j = 0; j < 3; ++j) b[j] -= w * (Jp[0][j] * e[0] + Jp[1][j] * e[1]);
+      for (int j = 0; j < 3; ++j) b[j] -= w * (Jp[0][j] * e[0] + Jp[1][j] * e[1]);
+    }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) Hll[6 * (size_t)col + j] = h[j];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) bl[3 * (size_t)col + j] = b[j];
+    m = fmax(fabs(h[0]), fmax(fabs(h[3]), fabs(h[5])));
   }
-#pragma unroll
-  for (int j = 0; j < 6; ++j) Hll[6 * (size_t)col + j] = h[j];
-#pragma unroll
-  for (int j = 0; j < 3; ++j) bl[3 * (size_t)col + j] = b[j];
+  // computeLambdaInit: max |diag Hll|; warp max, then one order-independent atomic per warp
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomic_max_nonneg(maxdiag_bits, m);
 }
 
 __global__ void ba_point_invert(int Pf, const double* __restrict__ Hll, double lambda,

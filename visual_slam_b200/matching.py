@@ -99,3 +99,57 @@ class FeatureMatcher:
             e = np.asarray([])
             return matches, e, e.copy(), e.copy(), e.copy()
         return matches, kp1[kq], desc1[kq], kp2[kt], desc2[kt]
+
+
+class HostMatcher:
+    """End-to-end batched matcher for HOST descriptor buffers: pinned staging, H2D copy, kNN-2 +
+    ratio (+ cross-check) on the GPU, D2H of the compacted match lists.  Buffers are reused across
+    calls; copies and kernels of consecutive chunks overlap on two streams."""
+
+    def __init__(self, batch, nq, nt, ratio=0.8, cross_check=True, device="cuda:0", chunks=4):
+        _require_cuda()
+        self.device = torch.device(device)
+        self.batch, self.nq, self.nt = batch, nq, nt
+        self.ratio, self.cross_check = ratio, cross_check
+        self.chunks = max(1, min(chunks, batch))
+        self.q_pin = torch.empty((batch, nq, 32), dtype=torch.uint8).pin_memory()
+        self.t_pin = torch.empty((batch, nt, 32), dtype=torch.uint8).pin_memory()
+        self.keep_q_pin = torch.empty((batch, nq), dtype=torch.int32).pin_memory()
+        self.keep_t_pin = torch.empty((batch, nq), dtype=torch.int32).pin_memory()
+        self.n_keep_pin = torch.empty((batch,), dtype=torch.int32).pin_memory()
+        with torch.cuda.device(self.device):
+            self.q_dev = torch.empty((batch, nq, 32), dtype=torch.uint8, device=self.device)
+            self.t_dev = torch.empty((batch, nt, 32), dtype=torch.uint8, device=self.device)
+            self.streams = [torch.cuda.Stream(self.device) for _ in range(2)]
+        self.h2d_bytes = self.q_pin.numel() + self.t_pin.numel()
+        self.d2h_bytes = 4 * (self.keep_q_pin.numel() + self.keep_t_pin.numel() + self.n_keep_pin.numel())
+        self.launches_per_call = 3 * self.chunks if cross_check else 2 * self.chunks
+
+    def load(self, q, t):
+        """Copies caller arrays (numpy uint8 [batch, n, 32]) into the pinned staging buffers."""
+        self.q_pin.copy_(torch.from_numpy(np.ascontiguousarray(q)))
+        self.t_pin.copy_(torch.from_numpy(np.ascontiguousarray(t)))
+
+    def run(self):
+        """H2D -> match -> D2H for the staged batch; returns pinned (keep_q, keep_t, n_keep)."""
+        B = self.batch
+        step = (B + self.chunks - 1) // self.chunks
+        cur = torch.cuda.current_stream(self.device)
+        start = torch.cuda.Event()
+        start.record(cur)
+        for c in range(self.chunks):
+            lo, hi = c * step, min(B, (c + 1) * step)
+            if lo >= hi:
+                break
+            st = self.streams[c & 1]
+            st.wait_event(start)
+            with torch.cuda.stream(st):
+                self.q_dev[lo:hi].copy_(self.q_pin[lo:hi], non_blocking=True)
+                self.t_dev[lo:hi].copy_(self.t_pin[lo:hi], non_blocking=True)
+                out = match_batch(self.q_dev[lo:hi], self.t_dev[lo:hi], self.ratio, self.cross_check)
+                self.keep_q_pin[lo:hi].copy_(out["keep_q"], non_blocking=True)
+                self.keep_t_pin[lo:hi].copy_(out["keep_t"], non_blocking=True)
+                self.n_keep_pin[lo:hi].copy_(out["n_keep"], non_blocking=True)
+        for st in self.streams:
+            cur.wait_stream(st)
+        return self.keep_q_pin, self.keep_t_pin, self.n_keep_pin

@@ -32,3 +32,36 @@ def low_entropy_pair(nq, nt, seed=0):
     rng = np.random.default_rng(seed)
     return (rng.integers(0, 2, size=(nq, 32), dtype=np.uint8),
             rng.integers(0, 2, size=(nt, 32), dtype=np.uint8))
+
+
+ICL_K = (481.2, 480.0, 319.5, 239.5)
+
+
+def _rodrigues(r):
+    th = float(np.linalg.norm(r))
+    if th < 1e-300:
+        return np.eye(3)
+    k = np.asarray(r, dtype=np.float64) / th
+    Kx = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+    return np.eye(3) + np.sin(th) * Kx + (1 - np.cos(th)) * (Kx @ Kx)
+
+
+def tracking_pair(seed, n=2048, outlier_frac=0.3, pix_sigma=0.5, K=ICL_K, width=640, height=480):
+    """C5 geometry: n world points in the frustum of the current camera (depth 1-8 m),
+    world->camera pose = small motion away from identity (<= 2 deg, <= 5 cm), pixel noise sigma,
+    `outlier_frac` of the correspondences get uniform-random pixels (wrong matches).
+    Returns X [n,3] f32, uv [n,2] f32, rvec [3], tvec [3] (true world->camera), inlier mask [n]."""
+    rng = np.random.default_rng(seed)
+    fx, fy, cx, cy = K
+    rvec = rng.normal(size=3); rvec *= np.deg2rad(rng.uniform(0.2, 2.0)) / np.linalg.norm(rvec)
+    tvec = rng.normal(size=3); tvec *= rng.uniform(0.005, 0.05) / np.linalg.norm(tvec)
+    R = _rodrigues(rvec)
+    z = rng.uniform(1.0, 8.0, n)
+    u = rng.uniform(0, width, n); v = rng.uniform(0, height, n)
+    Xc = np.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], axis=1)
+    X = (Xc - tvec) @ R          # world = R^T (Xc - t)
+    uv = np.stack([u, v], axis=1) + rng.normal(0, pix_sigma, (n, 2))
+    inl = rng.random(n) >= outlier_frac
+    n_out = int((~inl).sum())
+    uv[~inl] = np.stack([rng.uniform(0, width, n_out), rng.uniform(0, height, n_out)], axis=1)
+    return X.astype(np.float32), uv.astype(np.float32), rvec, tvec, inl
