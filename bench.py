@@ -189,6 +189,64 @@ def ba_figures(torch):
     return out
 
 
+def tracking_figures(torch, dist, world, rank, dev, steps=3):
+    """C5: 8 sequences x 1000 frame pairs (matching + RANSAC PnP, 100 hypotheses) sharded by sequence over
+    the ranks; poses and inlier counts are gathered with NCCL.  Total work is fixed (strong scaling)."""
+    from visual_slam_b200 import synth
+    from visual_slam_b200.tracking import track_batch
+    n_seq, per_seq, n, H = 8, 1000, 2048, 100
+    my_seq = [s for s in range(n_seq) if s % world == rank]
+    pairs = len(my_seq) * per_seq
+    if pairs == 0:
+        pairs = 8  # idle rank still joins the collectives with a token batch
+    base = [synth.tracking_frame_pair(1000 * rank + i, n) for i in range(8)]
+    rep = (pairs + 7) // 8
+    dk, dc, X, kp = (torch.from_numpy(np.stack([b[i] for b in base])).to(dev).repeat(rep, 1, 1)[:pairs].contiguous()
+                     for i in range(4))
+    words = torch.from_numpy(np.random.default_rng(rank).integers(0, 2 ** 32, size=(pairs, H, 4), dtype=np.uint64)
+                             .astype(np.uint32).view(np.int32)).to(dev)
+    guess = torch.zeros((pairs, 6), dtype=torch.float64, device=dev)
+    chunk = 1000
+    K = synth.ICL_K
+
+    def one_pass():
+        poses, ninl = [], []
+        for lo in range(0, pairs, chunk):
+            hi = min(pairs, lo + chunk)
+            o = track_batch(dk[lo:hi], dc[lo:hi], X[lo:hi], kp[lo:hi], words[lo:hi], K, guess[lo:hi])
+            poses.append(o["pose"]); ninl.append(o["n_inliers"])
+        pose = torch.cat(poses); ni = torch.cat(ninl)
+        if world > 1:
+            cap = (n_seq + world - 1) // world * per_seq
+            buf = torch.zeros((cap, 7), dtype=torch.float64, device=dev)
+            buf[:pairs, :6] = pose; buf[:pairs, 6] = ni.double()
+            allb = torch.empty((world, cap, 7), dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(allb, buf)
+        return pose, ni
+
+    pose, ni = one_pass()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        pose, ni = one_pass()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    truth = np.stack([np.concatenate([b[4], b[5]]) for b in base])
+    err = (pose[:8].cpu().numpy() - truth)
+    return {"tracked_frames_per_s": n_seq * per_seq / (float(ms.item()) * 1e-3), "ms_per_pass": float(ms.item()),
+            "pairs_total": n_seq * per_seq, "hypotheses": H, "scaling": "strong (8 sequences sharded by rank)",
+            "max_pose_err_rad_m": [float(np.abs(err[:, :3]).max()), float(np.abs(err[:, 3:]).max())],
+            "median_inliers": float(ni.float().median().item())}
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -279,6 +337,8 @@ def run_gpu(args):
     e2e_value = world * B * NQ * e2e_steps / (float(e2e_ms.item()) * 1e-3)
     assert int(nk_pin.sum()) == n_keep_ref
 
+    tracking = None if args.skip_tracking else tracking_figures(torch, dist, world, rank, dev)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -306,6 +366,8 @@ def run_gpu(args):
                     "d2h_bytes_per_step": hm.d2h_bytes, "steps": e2e_steps},
             "gpu_launches": 3 * args.steps, "roofline": roofline,
             "pair_distances_per_s": world * B * NQ * NT * args.steps / (ms * 1e-3)}
+    if tracking:
+        line["tracking"] = tracking
     if world == 1:
         cpu = cpu_matching(12.0, 4000)
         cpu.pop("pairs"); cpu.pop("seconds")
@@ -330,6 +392,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--skip-ba", action="store_true")
+    ap.add_argument("--skip-tracking", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -135,6 +135,17 @@ int vslam_pnp_select_refine(const float* X, const float* uv, const int32_t* n_pt
                             int max_refine_iters, int32_t* best, uint32_t* inlier_bits,
                             int32_t* n_inliers, double* pose, int32_t* status, void* stream);
 
+/*
+ * Correspondence gather between matching and PnP (reference src/v2/main.py:187-188, frame.py:36-37):
+ * X[b][i] = map_xyz[b][keep_q[b][i]], uv[b][i] = kp_cur[b][keep_t[b][i]] for i < n_keep[b], zero after.
+ *   map_xyz dev f32 [batch][nq][3]  3-D map points of the query (key-frame) descriptors
+ *   kp_cur  dev f32 [batch][nt][2]  keypoints of the train (current-frame) descriptors
+ *   X dev f32 [batch][nq][3], uv dev f32 [batch][nq][2]  (n_max of the PnP calls = nq)
+ */
+int vslam_gather_correspondences(const int32_t* keep_q, const int32_t* keep_t, const int32_t* n_keep,
+                                 int nq, int nt, int batch, const float* map_xyz, const float* kp_cur,
+                                 float* X, float* uv, void* stream);
+
 /* ------------------------------------------------------------------------- */
 /* 3. Bundle adjustment                                                       */
 /* ------------------------------------------------------------------------- */

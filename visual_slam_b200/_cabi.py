@@ -32,6 +32,7 @@ def _declare(lib):
     lib.vslam_pnp_score.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, pd, f64, vp, vp]
     lib.vslam_pnp_select_refine.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, i32, pd, f64, f64, vp, i32,
                                             vp, vp, vp, vp, vp, vp]
+    lib.vslam_gather_correspondences.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp, vp]
     pp = C.POINTER(vp)
     lib.vslam_ba_create.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.vslam_ba_destroy.argtypes = [vp]

@@ -359,3 +359,39 @@ extern "C" int vslam_pnp_select_refine(const float* X, const float* uv, const in
       max_refine_iters > 0 ? max_refine_iters : 50, best, inlier_bits, n_inliers, pose, status);
   return check_launch("pnp_select_refine_kernel");
 }
+
+// Correspondence gather between matching and PnP (reference src/v2/main.py:187-188 and
+// frame.py:36-37): X[b][i] = map_xyz[b][keep_q[b][i]], uv[b][i] = kp_cur[b][keep_t[b][i]].
+namespace vslam {
+__global__ void gather_corr_kernel(const int32_t* __restrict__ keep_q, const int32_t* __restrict__ keep_t,
+                                   const int32_t* __restrict__ n_keep, int nq, int nt,
+                                   const float* __restrict__ map_xyz, const float* __restrict__ kp_cur,
+                                   float* __restrict__ X, float* __restrict__ uv) {
+  const int b = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  float x = 0.f, y = 0.f, z = 0.f, u = 0.f, v = 0.f;
+  if (i < n_keep[b]) {
+    const int q = keep_q[(size_t)b * nq + i], t = keep_t[(size_t)b * nq + i];
+    const float* xp = map_xyz + ((size_t)b * nq + q) * 3;
+    const float* up = kp_cur + ((size_t)b * nt + t) * 2;
+    x = xp[0]; y = xp[1]; z = xp[2]; u = up[0]; v = up[1];
+  }
+  float* xo = X + ((size_t)b * nq + i) * 3;
+  float* uo = uv + ((size_t)b * nq + i) * 2;
+  xo[0] = x; xo[1] = y; xo[2] = z; uo[0] = u; uo[1] = v;
+}
+}  // namespace vslam
+
+extern "C" int vslam_gather_correspondences(const int32_t* keep_q, const int32_t* keep_t,
+                                            const int32_t* n_keep, int nq, int nt, int batch,
+                                            const float* map_xyz, const float* kp_cur, float* X,
+                                            float* uv, void* stream) {
+  if (batch < 0 || nq < 0 || nt < 0) return VSLAM_ERR_BAD_ARG;
+  if (batch == 0 || nq == 0) return VSLAM_OK;
+  if (!keep_q || !keep_t || !n_keep || !map_xyz || !kp_cur || !X || !uv) return VSLAM_ERR_BAD_ARG;
+  dim3 grid((nq + 255) / 256, batch);
+  vslam::gather_corr_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      keep_q, keep_t, n_keep, nq, nt, map_xyz, kp_cur, X, uv);
+  return vslam::check_launch("gather_corr_kernel");
+}

@@ -65,3 +65,27 @@ def tracking_pair(seed, n=2048, outlier_frac=0.3, pix_sigma=0.5, K=ICL_K, width=
     n_out = int((~inl).sum())
     uv[~inl] = np.stack([rng.uniform(0, width, n_out), rng.uniform(0, height, n_out)], axis=1)
     return X.astype(np.float32), uv.astype(np.float32), rvec, tvec, inl
+
+
+def tracking_frame_pair(seed, n=2048, planted=0.7, flip=0.10, wrong_pix=0.10, pix_sigma=0.5, K=ICL_K,
+                        width=640, height=480):
+    """One C5 frame pair: a key frame's n mapped points (descriptor + 3-D position) and the current
+    frame's n features (descriptor + keypoint).  `planted` of the key-frame points reappear in the
+    current frame with noisy descriptors; `wrong_pix` of those carry a wrong pixel (PnP outliers).
+    Returns desc_kf u8[n,32], desc_cur u8[n,32], map_xyz f32[n,3], kp_cur f32[n,2], rvec, tvec."""
+    rng = np.random.default_rng(seed + 7919)
+    X, uv, rvec, tvec, _ = tracking_pair(seed, n, outlier_frac=0.0, pix_sigma=pix_sigma, K=K,
+                                         width=width, height=height)
+    desc_kf = rng.integers(0, 256, size=(n, 32), dtype=np.uint8)
+    desc_cur = rng.integers(0, 256, size=(n, 32), dtype=np.uint8)
+    kp_cur = np.stack([rng.uniform(0, width, n), rng.uniform(0, height, n)], axis=1).astype(np.float32)
+    n_pl = int(round(planted * n))
+    src = rng.permutation(n)[:n_pl]      # key-frame rows that reappear
+    dst = rng.permutation(n)[:n_pl]      # their rows in the current frame
+    noise = np.packbits(rng.random((n_pl, 256)) < flip, axis=1)
+    desc_cur[dst] = desc_kf[src] ^ noise
+    kp_cur[dst] = uv[src]
+    bad = rng.random(n_pl) < wrong_pix
+    kp_cur[dst[bad]] = np.stack([rng.uniform(0, width, int(bad.sum())),
+                                 rng.uniform(0, height, int(bad.sum()))], axis=1).astype(np.float32)
+    return desc_kf, desc_cur, X, kp_cur, rvec, tvec
