@@ -404,7 +404,7 @@ static int ba_linearize(BA& B, cudaStream_t st) {
   ba_cam_pass<false><<<grid, kCamThreads, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hpl.p, B.camp.p);
   ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp_extra.p, B.diag_extra.p, B.extra.p, B.Hpp.p, B.bp.p,
                                       B.cam_cost.p, B.maxdiag.p);
-  if (B.P) ba_point_pass<<<(B.P + 127) / 128, 128, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hll.p, B.bl.p,
+  if (B.P) ba_point_pass<<<(B.P * kPointLanes + 255) / 256, 256, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hll.p, B.bl.p,
                                                             B.maxdiag.p);
   ba_finish<<<1, 256, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, 0, nullptr, 0, nullptr, nullptr, 0.0,
                                nullptr, nullptr, B.maxdiag.p, B.res.p);

@@ -12,7 +12,7 @@
 
 namespace vslam {
 
-constexpr int kCamChunk = 1024;   // observations of one camera handled by one CTA
+constexpr int kCamChunk = 256;    // observations of one camera handled by one CTA (one per thread)
 constexpr int kCamThreads = 256;
 constexpr int kCamVals = 28;      // 21 Hpp upper + 6 bp + 1 cost
 constexpr int kUnitItems = 256;   // Schur items per warp work unit
@@ -45,58 +45,95 @@ __device__ __forceinline__ void store18(double* p, const double (&v)[18]) {
   for (int i = 0; i < 9; ++i) s[i] = make_double2(v[2 * i], v[2 * i + 1]);
 }
 
-// Camera-major pass.  COST_ONLY = evaluate sum(rho) for a trial state; otherwise also accumulate
-// Hpp (upper 21) / bp per camera and write the Hpl blocks (w Jc^T Jp, 6x3 row-major).
+// Sum over the 32 lanes of 32 per-lane values in 31 shuffles: after the call lane L holds the warp
+// total of value L in v[0].  Each step halves the live values (lanes with bit s keep the upper half
+// and ship the lower one).  The combination tree is fixed, so the result is deterministic.
+__device__ __forceinline__ void warp_transpose_sum32(double (&v)[32], int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const double send = up ? v[i] : v[i + s];
+      const double keep = up ? v[i + s] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+}
+
+// Camera-major pass, one thread per observation.  COST_ONLY = evaluate sum(rho) for a trial state;
+// otherwise also accumulate Hpp (upper 21) / bp per camera and write the Hpl blocks
+// (w Jc^T Jp, 6x3 row-major).  Values 0..20 Hpp upper, 21..26 bp, 27 cost.
 template <bool COST_ONLY>
 __global__ void __launch_bounds__(kCamThreads)
 ba_cam_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict__ pts,
             double* __restrict__ Hpl, double* __restrict__ camp) {
-  __shared__ double red[(kCamThreads / 32) * kCamVals];
+  __shared__ double red[(kCamThreads / 32) * 32];
   const int c = blockIdx.y, chunk = blockIdx.x;
   const int start = V.cm_start[c] + chunk * kCamChunk;
   const int end = min(V.cm_start[c + 1], start + kCamChunk);
   if (start >= end) return;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const CamRT cam = camrt[c];
   const bool cam_free = V.cam_col[c] >= 0;
-  double acc[kCamVals];
+  double v[32];
 #pragma unroll
-  for (int i = 0; i < kCamVals; ++i) acc[i] = 0.0;
-  for (int o = start + threadIdx.x; o < end; o += kCamThreads) {
+  for (int i = 0; i < 32; ++i) v[i] = 0.0;
+  const int o = start + threadIdx.x;
+  if (o < end) {
     const int p = V.cm_pt[o];
     const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
     const double2 uv = V.cm_uv[o];
     double pc[3], e[2], rho, w;
     to_camera(cam, X, pc);
-    if (!(fabs(pc[2]) > 1e-12)) continue;  // g2o aborts here; we drop the observation
-    residual(pc, V.K, uv.x, uv.y, e);
-    huber(e[0] * e[0] + e[1] * e[1], rho, w);
-    acc[27] += rho;
-    if (COST_ONLY || !cam_free) continue;
-    double Jc[2][6], Jp[2][3];
-    jacobians(cam, pc, V.K, Jc, Jp);
-    int k = 0;
+    if (fabs(pc[2]) > 1e-12) {  // g2o aborts on z = 0; we drop the observation
+      residual(pc, V.K, uv.x, uv.y, e);
+      huber(e[0] * e[0] + e[1] * e[1], rho, w);
+      v[27] = rho;
+      if (!COST_ONLY && cam_free) {
+        double Jc[2][6], Jp[2][3], W0[6], W1[6];
+        jacobians(cam, pc, V.K, Jc, Jp);
 #pragma unroll
-    for (int i = 0; i < 6; ++i) {
+        for (int i = 0; i < 6; ++i) { W0[i] = w * Jc[0][i]; W1[i] = w * Jc[1][i]; }
+        int k = 0;
 #pragma unroll
-      for (int j = i; j < 6; ++j) acc[k++] += w * (Jc[0][i] * Jc[0][j] + Jc[1][i] * Jc[1][j]);
-    }
+        for (int i = 0; i < 6; ++i) {
 #pragma unroll
-    for (int i = 0; i < 6; ++i) acc[21 + i] -= w * (Jc[0][i] * e[0] + Jc[1][i] * e[1]);
-    if (V.pt_col[p] >= 0) {
-      double h[18];
+          for (int j = i; j < 6; ++j) v[k++] = W0[i] * Jc[0][j] + W1[i] * Jc[1][j];
+        }
 #pragma unroll
-      for (int i = 0; i < 6; ++i) {
+        for (int i = 0; i < 6; ++i) v[21 + i] = -(W0[i] * e[0] + W1[i] * e[1]);
+        if (V.pt_col[p] >= 0) {
+          double h[18];
 #pragma unroll
-        for (int j = 0; j < 3; ++j) h[3 * i + j] = w * (Jc[0][i] * Jp[0][j] + Jc[1][i] * Jp[1][j]);
+          for (int i = 0; i < 6; ++i) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) h[3 * i + j] = W0[i] * Jp[0][j] + W1[i] * Jp[1][j];
+          }
+          store18(Hpl + (size_t)o * 18, h);
+        }
       }
-      store18(Hpl + (size_t)o * 18, h);
     }
   }
-  block_reduce<kCamVals, kCamThreads>(acc, red);
-  if (threadIdx.x == 0) {
-    double* dst = camp + ((size_t)c * V.max_chunks + chunk) * kCamVals;
+  if (COST_ONLY) {
+    double s = warp_sum(v[27]);
+    if (lane == 0) red[wid] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int w8 = 0; w8 < kCamThreads / 32; ++w8) t += red[w8];
+      camp[((size_t)c * V.max_chunks + chunk) * kCamVals + 27] = t;
+    }
+    return;
+  }
+  warp_transpose_sum32(v, lane);
+  red[wid * 32 + lane] = v[0];
+  __syncthreads();
+  if (threadIdx.x < kCamVals) {
+    double t = 0.0;
 #pragma unroll
-    for (int i = 0; i < kCamVals; ++i) dst[i] = acc[i];
+    for (int w8 = 0; w8 < kCamThreads / 32; ++w8) t += red[w8 * 32 + threadIdx.x];
+    camp[((size_t)c * V.max_chunks + chunk) * kCamVals + threadIdx.x] = t;
   }
 }
 
@@ -132,17 +169,24 @@ __global__ void ba_cam_finalize(BAView V, const double* __restrict__ camp,
   }
 }
 
-// Point-major pass: one thread per free point walks its observations (fixed order).
-__global__ void ba_point_pass(BAView V, const CamRT* __restrict__ camrt,
-                              const double* __restrict__ pts, double* __restrict__ Hll,
-                              double* __restrict__ bl, unsigned long long* __restrict__ maxdiag_bits) {
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+// Point-major pass: a quad of 4 lanes per point; lane q takes observations q, q+4, ... of the point,
+// the quad is reduced by two butterfly steps (fixed order -> deterministic).
+constexpr int kPointLanes = 4;
+
+__global__ void __launch_bounds__(256)
+ba_point_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict__ pts,
+              double* __restrict__ Hll, double* __restrict__ bl,
+              unsigned long long* __restrict__ maxdiag_bits) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  const int p = g / kPointLanes, q = g % kPointLanes;
   const int col = (p < V.P) ? V.pt_col[p] : -1;
-  double m = 0.0;
+  double acc[9];
+#pragma unroll
+  for (int j = 0; j < 9; ++j) acc[j] = 0.0;
   if (col >= 0) {
     const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
-    double h[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
-    for (int o = V.pt_start[p]; o < V.pt_start[p + 1]; ++o) {
+    const int o_end = V.pt_start[p + 1];
+    for (int o = V.pt_start[p] + q; o < o_end; o += kPointLanes) {
       const CamRT cam = camrt[V.pm_cam[o]];
       const double2 uv = V.pm_uv[o];
       double pc[3], e[2], rho, w;
@@ -152,20 +196,30 @@ __global__ void ba_point_pass(BAView V, const CamRT* __restrict__ camrt,
       huber(e[0] * e[0] + e[1] * e[1], rho, w);
       double Jc[2][6], Jp[2][3];
       jacobians(cam, pc, V.K, Jc, Jp);
-      h[0] += w * (Jp[0][0] * Jp[0][0] + Jp[1][0] * Jp[1][0]);
-      h[1] += w * (Jp[0][0] * Jp[0][1] + Jp[1][0] * Jp[1][1]);
-      h[2] += w * (Jp[0][0] * Jp[0][2] + Jp[1][0] * Jp[1][2]);
-      h[3] += w * (Jp[0][1] * Jp[0][1] + Jp[1][1] * Jp[1][1]);
-      h[4] += w * (Jp[0][1] * Jp[0][2] + Jp[1][1] * Jp[1][2]);
-      h[5] += w * (Jp[0][2] * Jp[0][2] + Jp[1][2] * Jp[1][2]);
+      const double w0[3] = {w * Jp[0][0], w * Jp[0][1], w * Jp[0][2]};
+      const double w1[3] = {w * Jp[1][0], w * Jp[1][1], w * Jp[1][2]};
+      acc[0] += w0[0] * Jp[0][0] + w1[0] * Jp[1][0];
+      acc[1] += w0[0] * Jp[0][1] + w1[0] * Jp[1][1];
+      acc[2] += w0[0] * Jp[0][2] + w1[0] * Jp[1][2];
+      acc[3] += w0[1] * Jp[0][1] + w1[1] * Jp[1][1];
+      acc[4] += w0[1] * Jp[0][2] + w1[1] * Jp[1][2];
+      acc[5] += w0[2] * Jp[0][2] + w1[2] * Jp[1][2];
 #pragma unroll
-      for (int j = 0; j < 3; ++j) b[j] -= w * (Jp[0][j] * e[0] + Jp[1][j] * e[1]);
+      for (int j = 0; j < 3; ++j) acc[6 + j] -= w0[j] * e[0] + w1[j] * e[1];
     }
+  }
 #pragma unroll
-    for (int j = 0; j < 6; ++j) Hll[6 * (size_t)col + j] = h[j];
+  for (int j = 0; j < 9; ++j) {
+    acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
+    acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
+  }
+  double m = 0.0;
+  if (col >= 0 && q == 0) {
 #pragma unroll
-    for (int j = 0; j < 3; ++j) bl[3 * (size_t)col + j] = b[j];
-    m = fmax(fabs(h[0]), fmax(fabs(h[3]), fabs(h[5])));
+    for (int j = 0; j < 6; ++j) Hll[6 * (size_t)col + j] = acc[j];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) bl[3 * (size_t)col + j] = acc[6 + j];
+    m = fmax(fabs(acc[0]), fmax(fabs(acc[3]), fabs(acc[5])));
   }
   // computeLambdaInit: max |diag Hll|; warp max, then one order-independent atomic per warp
   for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
