@@ -152,7 +152,7 @@ struct BA {
   int cur = 0;
   // system
   DevBuf<double> Hpl, Ebuf, Hpp, bp, bhat, Hll, bl, Hinv, camp, cam_cost, S, dp, dl, tmp3;
-  DevBuf<double> unit_partial, seg_extra_dense, extra, bp_extra, scale_cost, scale_partial, res, p_glob, part;
+  DevBuf<double> unit_partial, seg_extra_dense, extra, bp_extra, scale_cost, scale_partial, res, p_glob, w_loc, part;
   DevBuf<unsigned> bar;
   DevBuf<int> pcg_flags;  // [0] fail flag, [1] status, [2] iters
   double* res_host = nullptr;  // pinned [8]
@@ -333,7 +333,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.tmp3.alloc((size_t)N * 3)); BA_TRY(B.unit_partial.alloc((size_t)B.n_units * 36));
   BA_TRY(B.extra.alloc((size_t)std::max(n_extra, 1) * 36)); BA_TRY(B.bp_extra.alloc(std::max(B.n, 1)));
   BA_TRY(B.scale_cost.alloc(1)); BA_TRY(B.scale_partial.alloc(B.n_sp)); BA_TRY(B.res.alloc(8));
-  BA_TRY(B.p_glob.alloc(std::max(B.n, 1)));
+  BA_TRY(B.p_glob.alloc(std::max(B.n, 1))); BA_TRY(B.w_loc.alloc(std::max(B.n, 1)));
   BA_TRY(cudaMemset(B.S.p, 0, std::max<size_t>((size_t)B.n * B.n, 1) * sizeof(double)));
   BA_TRY(cudaMemset(B.extra.p, 0, (size_t)std::max(n_extra, 1) * 36 * sizeof(double)));
   BA_TRY(cudaMemset(B.bp_extra.p, 0, (size_t)std::max(B.n, 1) * sizeof(double)));
@@ -349,7 +349,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     const size_t budget = (size_t)std::max(max_smem - 2048, 16384);
     auto smem_for = [&](int rows, bool slab) {
-      return sizeof(double) * ((size_t)B.n + 5 * (size_t)rows + 6 * (size_t)rows + 8 +
+      return sizeof(double) * ((size_t)B.n + 6 * (size_t)rows + 6 * (size_t)rows + 8 +
                                (slab ? (size_t)rows * B.n : 0));
     };
     int bpc = std::max(1, (nb + sms - 1) / sms);  // blocks per CTA with one CTA per SM
@@ -441,7 +441,7 @@ static int ba_trial(BA& B, double lambda, cudaStream_t st) {
     PcgArgs A;
     A.S = B.S.p; A.b = B.bhat.p; A.x = B.dp.p; A.n = B.n; A.rows = B.pcg_rows; A.G = B.pcg_G;
     A.slab_in_smem = B.pcg_slab; A.max_iter = B.pcg_max_iter; A.tol = B.pcg_tol;
-    A.p_glob = B.p_glob.p; A.part = B.part.p; A.bar = B.bar.p; A.fail_flag = B.pcg_flags.p;
+    A.p_glob = B.p_glob.p; A.w_loc = B.w_loc.p; A.part = B.part.p; A.bar = B.bar.p; A.fail_flag = B.pcg_flags.p;
     A.status = B.pcg_flags.p + 1; A.iters = B.pcg_flags.p + 2;
     void* args[] = {&A};
     if (B.pcg_G > 1) {
@@ -641,18 +641,18 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
                                int32_t* status_iters_host, void* stream) {
   if (!S || !b || !x || n <= 0 || n % 6 || !status_iters_host) return VSLAM_ERR_BAD_ARG;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  DevBuf<double> p_glob, part;
+  DevBuf<double> p_glob, w_loc, part;
   DevBuf<unsigned> bar;
   DevBuf<int> flags;
-  BA_TRY(p_glob.alloc(n)); BA_TRY(part.alloc(4)); BA_TRY(bar.alloc(1)); BA_TRY(flags.alloc(4));
+  BA_TRY(p_glob.alloc(n)); BA_TRY(w_loc.alloc(n)); BA_TRY(part.alloc(4)); BA_TRY(bar.alloc(1)); BA_TRY(flags.alloc(4));
   BA_TRY(cudaMemsetAsync(bar.p, 0, sizeof(unsigned), st));
   BA_TRY(cudaMemsetAsync(flags.p, 0, 4 * sizeof(int), st));
   PcgArgs A;
   A.S = S; A.b = b; A.x = x; A.n = n; A.rows = n; A.G = 1; A.max_iter = max_iter; A.tol = tol;
-  A.p_glob = p_glob.p; A.part = part.p; A.bar = bar.p; A.fail_flag = flags.p; A.status = flags.p + 1;
+  A.p_glob = p_glob.p; A.w_loc = w_loc.p; A.part = part.p; A.bar = bar.p; A.fail_flag = flags.p; A.status = flags.p + 1;
   A.iters = flags.p + 2;
-  size_t smem_slab = sizeof(double) * ((size_t)n + 11 * (size_t)n + 8 + (size_t)n * n);
-  size_t smem_noslab = sizeof(double) * ((size_t)n + 11 * (size_t)n + 8);
+  size_t smem_slab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8 + (size_t)n * n);
+  size_t smem_noslab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8);
   A.slab_in_smem = smem_slab <= 200 * 1024;
   size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
   BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

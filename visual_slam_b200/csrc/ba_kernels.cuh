@@ -69,6 +69,7 @@ __global__ void __launch_bounds__(kCamThreads)
 ba_cam_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict__ pts,
             double* __restrict__ Hpl, double* __restrict__ camp) {
   __shared__ double red[(kCamThreads / 32) * 32];
+  __shared__ __align__(16) double stage[COST_ONLY ? 2 : kCamThreads * 18];  // Hpl blocks of the CTA
   const int c = blockIdx.y, chunk = blockIdx.x;
   const int start = V.cm_start[c] + chunk * kCamChunk;
   const int end = min(V.cm_start[c + 1], start + kCamChunk);
@@ -80,6 +81,9 @@ ba_cam_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict_
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = 0.0;
   const int o = start + threadIdx.x;
+  double h[18];
+#pragma unroll
+  for (int i = 0; i < 18; ++i) h[i] = 0.0;
   if (o < end) {
     const int p = V.cm_pt[o];
     const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
@@ -103,17 +107,22 @@ ba_cam_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict_
         }
 #pragma unroll
         for (int i = 0; i < 6; ++i) v[21 + i] = -(W0[i] * e[0] + W1[i] * e[1]);
-        if (V.pt_col[p] >= 0) {
-          double h[18];
 #pragma unroll
-          for (int i = 0; i < 6; ++i) {
+        for (int i = 0; i < 6; ++i) {
 #pragma unroll
-            for (int j = 0; j < 3; ++j) h[3 * i + j] = W0[i] * Jp[0][j] + W1[i] * Jp[1][j];
-          }
-          store18(Hpl + (size_t)o * 18, h);
+          for (int j = 0; j < 3; ++j) h[3 * i + j] = W0[i] * Jp[0][j] + W1[i] * Jp[1][j];
         }
       }
     }
+  }
+  if (!COST_ONLY && cam_free) store18(stage + threadIdx.x * 18, h);  // 144 B stride: conflict-free STS.128
+  if (!COST_ONLY && cam_free) {
+    // the CTA's blocks are contiguous in HBM (camera-major): write them with coalesced 128-bit stores
+    __syncthreads();
+    const int n_blk = end - start;
+    double2* dst = reinterpret_cast<double2*>(Hpl + (size_t)start * 18);
+    const double2* src = reinterpret_cast<const double2*>(stage);
+    for (int i = threadIdx.x; i < n_blk * 9; i += kCamThreads) dst[i] = src[i];
   }
   if (COST_ONLY) {
     double s = warp_sum(v[27]);
@@ -221,9 +230,16 @@ ba_point_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restric
     for (int j = 0; j < 3; ++j) bl[3 * (size_t)col + j] = acc[6 + j];
     m = fmax(fabs(acc[0]), fmax(fabs(acc[3]), fabs(acc[5])));
   }
-  // computeLambdaInit: max |diag Hll|; warp max, then one order-independent atomic per warp
+  // computeLambdaInit: max |diag Hll|; CTA max, then ONE order-independent atomic per CTA
+  // (same-address atomics serialise in L2: one per warp cost more than the whole pass)
+  __shared__ double smax[8];
   for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
-  if ((threadIdx.x & 31) == 0) atomic_max_nonneg(maxdiag_bits, m);
+  if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) m = fmax(m, smax[w]);
+    if (m > 0.0) atomic_max_nonneg(maxdiag_bits, m);
+  }
 }
 
 __global__ void ba_point_invert(int Pf, const double* __restrict__ Hll, double lambda,

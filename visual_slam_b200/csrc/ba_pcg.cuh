@@ -16,8 +16,9 @@ struct PcgArgs {
   const double* S; const double* b; double* x;
   int n, rows, G, slab_in_smem, max_iter;
   double tol;
-  double* p_glob;     // [n]
-  double* part;       // [4 * G]
+  double* p_glob;     // [n]  published u = M^-1 r
+  double* w_loc;      // [n]  rows of S u, each CTA touches only its own rows
+  double* part;       // [3 * G]
   unsigned* bar;      // grid barrier counter (zeroed before launch)
   int* fail_flag;     // zeroed before launch
   int* status;        // out: 0 converged, 1 breakdown (indefinite), 2 max_iter reached
@@ -90,27 +91,45 @@ __device__ __forceinline__ double block_sum1(double v, double* red) {
   return s;  // every thread holds the same, order-fixed sum
 }
 
-__device__ __forceinline__ double ordered_sum(const double* part, int G) {
-  double s = 0.0;
-  for (int g = 0; g < G; ++g) s += __ldcg(part + g);
-  return s;
+// Sum of the G per-CTA partials of K quantities laid out as part[k * G + g]: warp 0 strides over g,
+// butterfly-reduces, and publishes through shared memory.  Fixed shape -> deterministic, and only one
+// warp per CTA touches L2.
+template <int K>
+__device__ __forceinline__ void gather_sums(const double* part, int G, double* sh /* [K] */, double (&out)[K]) {
+  if (threadIdx.x < 32) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      double s = 0.0;
+      for (int g = threadIdx.x; g < G; g += 32) s += __ldcg(part + k * G + g);
+      s = warp_sum(s);
+      if (threadIdx.x == 0) sh[k] = s;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < K; ++k) out[k] = sh[k];
+  __syncthreads();
 }
 
+// Chronopoulos-Gear preconditioned CG: one matrix-vector product and ONE fused reduction per
+// iteration, i.e. two grid barriers (publish u = M^-1 r; reduce (r,u), (Au,u), (r,r)).
 __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
   extern __shared__ __align__(16) double sm[];
   const int n = A.n, G = A.G, g = blockIdx.x, tid = threadIdx.x;
   const int row0 = g * A.rows;
   const int R = max(0, min(A.rows, n - row0));
-  double* p_full = sm;                 // [n]
-  double* xl = p_full + n;             // [rows] each
+  double* u_full = sm;                 // [n]
+  double* xl = u_full + n;             // [rows] each
   double* rl = xl + A.rows;
-  double* zl = rl + A.rows;
-  double* pl = zl + A.rows;
-  double* apl = pl + A.rows;
-  double* minv = apl + A.rows;         // [rows/6][36]
+  double* ul = rl + A.rows;
+  double* pl = ul + A.rows;
+  double* sl = pl + A.rows;            // s = A p (recurrence)
+  double* wl = sl + A.rows;            // w = S u, local rows
+  double* minv = wl + A.rows;          // [rows/6][36]
   double* red = minv + 6 * A.rows;     // [8]
   double* slab = red + 8;              // [rows][n] when slab_in_smem
   __shared__ int s_fail;
+  __shared__ double s_sum[3];
   unsigned target = 0;
 
   if (tid == 0) s_fail = 0;
@@ -127,84 +146,71 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
     if (!spd6_inverse(blk)) s_fail = 1;
     for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
   }
+  for (int i = tid; i < R; i += kPcgThreads) { xl[i] = 0.0; rl[i] = A.b[row0 + i]; pl[i] = 0.0; sl[i] = 0.0; }
   __syncthreads();
   if (tid == 0 && s_fail) atomicExch(A.fail_flag, 1);
-  // x = 0, r = b, z = M^-1 r, p = z
-  double rz_p = 0.0, bb_p = 0.0;
-  for (int i = tid; i < R; i += kPcgThreads) { xl[i] = 0.0; rl[i] = A.b[row0 + i]; }
-  __syncthreads();
-  for (int i = tid; i < R; i += kPcgThreads) {
-    const int bi = i / 6, ii = i % 6;
-    double z = 0.0;
-    for (int j = 0; j < 6; ++j) z += minv[36 * bi + 6 * ii + j] * rl[6 * bi + j];
-    zl[i] = z; pl[i] = z;
-    A.p_glob[row0 + i] = z;
-    rz_p += rl[i] * z;
-    bb_p += rl[i] * rl[i];
-  }
-  rz_p = block_sum1(rz_p, red);
-  bb_p = block_sum1(bb_p, red);
-  if (tid == 0) { A.part[g] = rz_p; A.part[G + g] = bb_p; }
-  grid_barrier(A.bar, target, G);
-  if (__ldcg(A.fail_flag)) {
-    for (int i = tid; i < R; i += kPcgThreads) A.x[row0 + i] = 0.0;
-    if (g == 0 && tid == 0) { *A.status = 1; *A.iters = 0; }
-    return;
-  }
-  double rz = ordered_sum(A.part, G);
-  const double bnorm2 = ordered_sum(A.part + G, G);
-  grid_barrier(A.bar, target, G);  // part[] may be rewritten from here on
+  const int lane = tid & 31, wid = tid >> 5;
   int status = 2, it = 0;
-  if (!(bnorm2 > 0.0)) { status = 0; }
-  else {
-    const double thresh = A.tol * A.tol * bnorm2;
-    const int lane = tid & 31, wid = tid >> 5;
-    for (it = 0; it < A.max_iter; ++it) {
-      for (int i = tid; i < n; i += kPcgThreads) p_full[i] = __ldcg(A.p_glob + i);
-      __syncthreads();
-      // Ap for the local rows: one warp per row
-      for (int r = wid; r < R; r += kPcgThreads / 32) {
-        const double* row = Srows + (size_t)r * n;
-        double s = 0.0;
-        for (int j = lane; j < n; j += 32) s += row[j] * p_full[j];
-        s = warp_sum(s);
-        if (lane == 0) apl[r] = s;
-      }
-      __syncthreads();
-      double pap_p = 0.0;
-      for (int i = tid; i < R; i += kPcgThreads) pap_p += pl[i] * apl[i];
-      pap_p = block_sum1(pap_p, red);
-      if (tid == 0) A.part[2 * G + g] = pap_p;
-      grid_barrier(A.bar, target, G);
-      const double pap = ordered_sum(A.part + 2 * G, G);
-      if (!(pap > 0.0) || !isfinite(pap)) { status = 1; break; }
-      const double alpha = rz / pap;
-      for (int i = tid; i < R; i += kPcgThreads) { xl[i] += alpha * pl[i]; rl[i] -= alpha * apl[i]; }
-      __syncthreads();
-      double rzn_p = 0.0, rr_p = 0.0;
-      for (int i = tid; i < R; i += kPcgThreads) {
-        const int bi = i / 6, ii = i % 6;
-        double z = 0.0;
-        for (int j = 0; j < 6; ++j) z += minv[36 * bi + 6 * ii + j] * rl[6 * bi + j];
-        zl[i] = z;
-        rzn_p += rl[i] * z;
-        rr_p += rl[i] * rl[i];
-      }
-      rzn_p = block_sum1(rzn_p, red);
-      rr_p = block_sum1(rr_p, red);
-      if (tid == 0) { A.part[g] = rzn_p; A.part[G + g] = rr_p; }
-      grid_barrier(A.bar, target, G);
-      const double rzn = ordered_sum(A.part, G);
-      const double rr = ordered_sum(A.part + G, G);
-      if (rr <= thresh) { status = 0; ++it; break; }
-      const double beta = rzn / rz;
-      rz = rzn;
-      for (int i = tid; i < R; i += kPcgThreads) {
-        pl[i] = zl[i] + beta * pl[i];
-        A.p_glob[row0 + i] = pl[i];
-      }
-      grid_barrier(A.bar, target, G);
+  double gamma_old = 0.0, alpha_old = 0.0, thresh = 0.0;
+  for (it = 0; it <= A.max_iter; ++it) {
+    // u = M^-1 r (block local), published for the other CTAs
+    for (int i = tid; i < R; i += kPcgThreads) {
+      const int bi = i / 6, ii = i % 6;
+      double z = 0.0;
+      for (int j = 0; j < 6; ++j) z += minv[36 * bi + 6 * ii + j] * rl[6 * bi + j];
+      ul[i] = z;
+      A.p_glob[row0 + i] = z;
     }
+    grid_barrier(A.bar, target, G);
+    if (it == 0 && __ldcg(A.fail_flag)) { status = 1; break; }
+    for (int i = tid; i < n; i += kPcgThreads) u_full[i] = __ldcg(A.p_glob + i);
+    __syncthreads();
+    // w = S u for the local rows: one warp per row
+    double gam_p = 0.0, del_p = 0.0, rr_p = 0.0;
+    for (int r = wid; r < R; r += kPcgThreads / 32) {
+      const double* row = Srows + (size_t)r * n;
+      double s = 0.0;
+      for (int j = lane; j < n; j += 32) s += row[j] * u_full[j];
+      s = warp_sum(s);
+      if (lane == 0) wl[r] = s;
+    }
+    __syncthreads();
+    for (int i = tid; i < R; i += kPcgThreads) {
+      const double w = wl[i];
+      gam_p += rl[i] * ul[i];
+      del_p += w * ul[i];
+      rr_p += rl[i] * rl[i];
+    }
+    gam_p = block_sum1(gam_p, red);
+    del_p = block_sum1(del_p, red);
+    rr_p = block_sum1(rr_p, red);
+    if (tid == 0) { A.part[g] = gam_p; A.part[G + g] = del_p; A.part[2 * G + g] = rr_p; }
+    grid_barrier(A.bar, target, G);
+    double sums[3];
+    gather_sums<3>(A.part, G, s_sum, sums);
+    const double gamma = sums[0], delta = sums[1], rr = sums[2];
+    if (it == 0) {
+      if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
+      thresh = A.tol * A.tol * rr;
+    }
+    if (rr <= thresh && it > 0) { status = 0; break; }
+    if (it == A.max_iter) break;
+    double beta = 0.0, pap = delta;
+    if (it > 0) {
+      beta = gamma / gamma_old;
+      pap = delta - beta * gamma / alpha_old;        // = p^T S p in exact arithmetic
+    }
+    if (!(pap > 0.0) || !isfinite(pap) || !(gamma > 0.0)) { status = 1; break; }
+    const double alpha = gamma / pap;
+    for (int i = tid; i < R; i += kPcgThreads) {
+      const double p = ul[i] + beta * pl[i];
+      const double s = wl[i] + beta * sl[i];
+      pl[i] = p; sl[i] = s;
+      xl[i] += alpha * p;
+      rl[i] -= alpha * s;
+    }
+    __syncthreads();
+    gamma_old = gamma; alpha_old = alpha;
   }
   for (int i = tid; i < R; i += kPcgThreads) A.x[row0 + i] = (status == 1) ? 0.0 : xl[i];
   if (g == 0 && tid == 0) { *A.status = status; *A.iters = it; }
