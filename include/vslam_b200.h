@@ -147,6 +147,58 @@ int vslam_gather_correspondences(const int32_t* keep_q, const int32_t* keep_t, c
                                  float* X, float* uv, void* stream);
 
 /* ------------------------------------------------------------------------- */
+/* 2b. Two-view geometry (map initialisation)                                 */
+/* ------------------------------------------------------------------------- */
+/*
+ * cv2.undistortPoints(pts, cameraMatrix=K, distCoeffs=None) as called at reference
+ * src/v2/helper_functions.py:49-50: out = (float)(((double)u - cx) * (1/fx)), bit-exact.
+ *   uv, out  dev f32 [n][2];  K host f64[4] = fx, fy, cx, cy
+ */
+int vslam_undistort_points(const float* uv, int64_t n, const double* K, float* out, void* stream);
+
+/*
+ * Together these replace cv2.findEssentialMat(pts1, pts2, method=RANSAC, prob=0.999, threshold=thr)
+ * (reference src/v2/helper_functions.py:52; focal 1, pp 0, at most 1000 iterations), batched.
+ *   x1, x2   dev f32 [batch][n_max][2]  normalised coordinates (outputs of vslam_undistort_points)
+ *   n_pts    dev i32 [batch]
+ *   words    dev u32 [batch][H][5]      harness-drawn random words, sampling rule as for PnP (k = 5)
+ *   models   dev f64 [batch][H][10][9]  essential matrices of every sample (unit Frobenius norm,
+ *                                       canonical sign and order), row-major, zero-padded
+ *   n_models dev i32 [batch][H]         0..10
+ * Five-point solver: Nister (null space, ten cubic constraints, degree-10 polynomial) + a
+ * Gauss-Newton polish of every root on the constraints.
+ */
+int vslam_essential_hypotheses(const float* x1, const float* x2, const int32_t* n_pts, int n_max,
+                               int batch, const uint32_t* words, int H, double* models,
+                               int32_t* n_models, void* stream);
+/* Inlier count of every model: inlier iff (float)Sampson <= (float)(thr*thr), OpenCV's semantics
+ * (EMEstimatorCallback::computeError).  One warp per model.  counts dev i32 [batch][H][10]. */
+int vslam_essential_score(const float* x1, const float* x2, const int32_t* n_pts, int n_max, int batch,
+                          const double* models, const int32_t* n_models, int H, double thr,
+                          int32_t* counts, void* stream);
+/*
+ * Selection with OpenCV's shrinking budget (RANSACUpdateNumIters, 5 model points), inlier mask of the
+ * winner and the epiline score of estimateEssential (helper_functions.py:54-68).
+ *   best dev i32 [batch] (sample*10 + model, or -1);  E dev f64 [batch][9];
+ *   mask dev u8 [batch][n_max] in {0,1};  n_inliers dev i32 [batch];  score dev f64 [batch]
+ */
+int vslam_essential_select(const float* x1, const float* x2, const int32_t* n_pts, int n_max, int batch,
+                           const double* models, const int32_t* n_models, const int32_t* counts, int H,
+                           double thr, double confidence, int32_t* best, double* E, uint8_t* mask,
+                           int32_t* n_inliers, double* score, void* stream);
+/*
+ * cv2.recoverPose(E, p1, p2, cameraMatrix=K, distanceThresh) (reference helper_functions.py:176).
+ *   E dev f64 [batch][9];  p1, p2 dev f32 [batch][n_max][2] PIXEL coordinates;  K host f64[4]
+ *   R dev f64 [batch][9];  t dev f64 [batch][3] (unit);  mask dev u8 [batch][n_max] in {0,255}
+ *   tri dev f64 [batch][4][n_max]  homogeneous points in the first camera's frame (unit columns,
+ *       sign free -- callers de-homogenise, main.py:123-124)
+ *   good dev i32 [batch][5]  survivors of the chosen candidate, then of the four candidates
+ */
+int vslam_recover_pose(const double* E, const float* p1, const float* p2, const int32_t* n_pts, int n_max,
+                       int batch, const double* K, double distance_thresh, double* R, double* t,
+                       uint8_t* mask, double* tri, int32_t* good, void* stream);
+
+/* ------------------------------------------------------------------------- */
 /* 3. Bundle adjustment                                                       */
 /* ------------------------------------------------------------------------- */
 /*

@@ -33,6 +33,12 @@ def _declare(lib):
     lib.vslam_pnp_select_refine.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, i32, pd, f64, f64, vp, i32,
                                             vp, vp, vp, vp, vp, vp]
     lib.vslam_gather_correspondences.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp, vp]
+    lib.vslam_undistort_points.argtypes = [vp, C.c_int64, pd, vp, vp]
+    lib.vslam_essential_hypotheses.argtypes = [vp, vp, vp, i32, i32, vp, i32, vp, vp, vp]
+    lib.vslam_essential_score.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, f64, vp, vp]
+    lib.vslam_essential_select.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, i32, f64, f64, vp, vp, vp, vp,
+                                           vp, vp]
+    lib.vslam_recover_pose.argtypes = [vp, vp, vp, vp, i32, i32, pd, f64, vp, vp, vp, vp, vp, vp]
     pp = C.POINTER(vp)
     lib.vslam_ba_create.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.vslam_ba_destroy.argtypes = [vp]

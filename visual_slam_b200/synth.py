@@ -89,3 +89,25 @@ def tracking_frame_pair(seed, n=2048, planted=0.7, flip=0.10, wrong_pix=0.10, pi
     kp_cur[dst[bad]] = np.stack([rng.uniform(0, width, int(bad.sum())),
                                  rng.uniform(0, height, int(bad.sum()))], axis=1).astype(np.float32)
     return desc_kf, desc_cur, X, kp_cur, rvec, tvec
+
+
+def two_view_pair(seed, n=400, outlier_frac=0.2, pix_sigma=0.5, K=ICL_K, width=640, height=480):
+    """Map-initialisation geometry (reference src/v2/main.py:88-138): n points seen from the first camera
+    (identity) and from a second one that moved sideways by 0.2-0.5 m with a small rotation, pixel noise
+    sigma, `outlier_frac` wrong matches (uniform pixels in image 2).
+    Returns p1 [n,2] f32, p2 [n,2] f32 (pixels), R [3,3], t [3] (x2 ~ R x1 + t), inlier mask [n]."""
+    rng = np.random.default_rng(seed + 104729)
+    fx, fy, cx, cy = K
+    rvec = rng.normal(size=3); rvec *= np.deg2rad(rng.uniform(0.5, 4.0)) / np.linalg.norm(rvec)
+    t = rng.normal(size=3) * np.array([1.0, 0.4, 0.4]); t *= rng.uniform(0.2, 0.5) / np.linalg.norm(t)
+    R = _rodrigues(rvec)
+    z = rng.uniform(1.5, 8.0, n)
+    u = rng.uniform(20, width - 20, n); v = rng.uniform(20, height - 20, n)
+    X = np.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], axis=1)
+    Xc = X @ R.T + t
+    p1 = np.stack([u, v], axis=1) + rng.normal(0, pix_sigma, (n, 2))
+    p2 = np.stack([fx * Xc[:, 0] / Xc[:, 2] + cx, fy * Xc[:, 1] / Xc[:, 2] + cy], axis=1) + rng.normal(0, pix_sigma, (n, 2))
+    inl = rng.random(n) >= outlier_frac
+    n_out = int((~inl).sum())
+    p2[~inl] = np.stack([rng.uniform(0, width, n_out), rng.uniform(0, height, n_out)], axis=1)
+    return p1.astype(np.float32), p2.astype(np.float32), R, t, inl
