@@ -17,6 +17,7 @@ namespace vslam {
 // contributions of its incident edges in edge order (CSR built on the host) -> deterministic.
 struct ScaleView {
   int E, n_extra, Cf;
+  const LMState* st; const double* cams2[2];
   const int* sa; const int* sb; const double* meas; const int* cam_col;
   const int* inc_start; const int* inc_edge;   // per free camera: incident edge ids (ascending)
   const int* extra_a; const int* extra_b;      // free-camera columns of each extra block (a <= b)
@@ -24,10 +25,12 @@ struct ScaleView {
 };
 
 __global__ void __launch_bounds__(256)
-ba_scale_edges(ScaleView V, const double* __restrict__ cams, int cost_only, double* __restrict__ extra,
+ba_scale_edges(ScaleView V, int cost_only, double* __restrict__ extra,
                double* __restrict__ bp_extra, double* __restrict__ scale_cost,
                unsigned long long* __restrict__ maxdiag_bits) {
   __shared__ double red[8];
+  if (V.st->done || (!cost_only && !V.st->dirty)) return;
+  const double* __restrict__ cams = V.cams2[cost_only ? (V.st->cur ^ 1) : V.st->cur];
   double c[1] = {0.0};
   for (int k = threadIdx.x; k < V.E; k += 256) {
     const double* ta = cams + 7 * V.sa[k] + 4;
@@ -85,32 +88,107 @@ ba_scale_edges(ScaleView V, const double* __restrict__ cams, int cost_only, doub
   }
 }
 
-// res[0] = sum cam_cost + scale cost; res[1] = computeScale: sum x (lambda x + b) over cams + points.
-// One CTA, strided partials + fixed-order tree.
+// Controller after buildSystem(): total cost of the current state, computeLambdaInit on the first
+// linearisation (lambda = tau * max |diag H|).  One CTA, strided partials + fixed-order tree.
 __global__ void __launch_bounds__(256)
-ba_finish(int C, const double* __restrict__ cam_cost, const double* __restrict__ scale_cost, int n_sp,
-          const double* __restrict__ scale_partial, int n, const double* __restrict__ dp,
-          const double* __restrict__ bp, double lambda, const int* __restrict__ pcg_status,
-          const int* __restrict__ pcg_iters, const unsigned long long* __restrict__ maxdiag_bits,
-          double* __restrict__ res) {
+ba_lin_controller(LMState* __restrict__ st, int C, const double* __restrict__ cam_cost,
+                  const double* __restrict__ scale_cost,
+                  const unsigned long long* __restrict__ maxdiag_bits) {
+  __shared__ double red[8];
+  if (st->done || !st->dirty) return;
+  double v[1] = {0.0};
+  for (int i = threadIdx.x; i < C; i += 256) v[0] += cam_cost[i];
+  block_reduce<1, 256>(v, red);
+  if (threadIdx.x == 0) {
+    const double cost = v[0] + *scale_cost;
+    const double md = __longlong_as_double((long long)*maxdiag_bits);
+    st->cur_cost = cost;
+    st->max_diag = md;
+    if (st->first && !st->manual) {
+      st->initial_cost = cost;
+      st->lambda = 1e-5 * md;   // tau (OptimizationAlgorithmLevenberg default)
+      st->ni = 2.0;
+      st->first = 0;
+    }
+    st->dirty = 0;
+  }
+}
+
+// Controller after a trial: cost of the trial state, computeScale, then the Levenberg-Marquardt
+// accept / reject logic of g2o (OptimizationAlgorithmLevenberg::solve) entirely on the device.
+__global__ void __launch_bounds__(256)
+ba_trial_controller(LMState* __restrict__ st, int C, const double* __restrict__ cam_cost,
+                    const double* __restrict__ scale_cost, int n_sp,
+                    const double* __restrict__ scale_partial, int n, const double* __restrict__ dp,
+                    const double* __restrict__ bp, const int* __restrict__ pcg_status,
+                    const int* __restrict__ pcg_iters) {
   __shared__ double red[16];
+  if (st->done) return;
+  const double lambda = st->lambda;
   double v[2] = {0.0, 0.0};
   for (int i = threadIdx.x; i < C; i += 256) v[0] += cam_cost[i];
-  if (dp) {
-    for (int i = threadIdx.x; i < n; i += 256) v[1] += dp[i] * (lambda * dp[i] + bp[i]);
-    for (int i = threadIdx.x; i < n_sp; i += 256) v[1] += scale_partial[i];
-  }
+  for (int i = threadIdx.x; i < n; i += 256) v[1] += dp[i] * (lambda * dp[i] + bp[i]);
+  for (int i = threadIdx.x; i < n_sp; i += 256) v[1] += scale_partial[i];
   block_reduce<2, 256>(v, red);
-  if (threadIdx.x == 0) {
-    res[0] = v[0] + *scale_cost;
-    if (dp) {
-      res[1] = v[1];
-      res[3] = (double)*pcg_status;
-      res[4] = (double)*pcg_iters;
-    } else {
-      res[2] = __longlong_as_double((long long)*maxdiag_bits);  // computeLambdaInit's max |diag H|
-    }
+  if (threadIdx.x != 0) return;
+  double tmp = v[0] + *scale_cost;
+  const int status = n ? *pcg_status : 0, its = n ? *pcg_iters : 0;
+  st->last_cost = tmp; st->last_scale = v[1]; st->last_pcg_status = status; st->last_pcg_iters = its;
+  if (st->manual) return;
+  const bool ok = status != 1;
+  st->pcg_total += (double)its;
+  if (!ok) { tmp = 1.7976931348623157e308; st->breakdowns += 1.0; }
+  const double scale = v[1] + 1e-3;
+  const double rho = (st->cur_cost - tmp) / scale;
+  st->last_rho = rho;
+  st->trials += 1;
+  const bool accepted = rho > 0.0 && isfinite(tmp);
+  if (accepted) {
+    double alpha = 1.0 - pow(2.0 * rho - 1.0, 3.0);
+    alpha = fmin(alpha, 2.0 / 3.0);
+    st->lambda = lambda * fmax(1.0 / 3.0, alpha);
+    st->ni = 2.0;
+    st->cur_cost = tmp;
+    st->cur ^= 1;          // discardTop(): the trial state becomes current
+    st->dirty = 1;
+  } else {
+    st->lambda = lambda * st->ni;   // pop(): current state untouched, the system stays valid
+    st->ni *= 2.0;
+    st->rejected += 1.0;
   }
+  const bool lam_bad = !accepted && !isfinite(st->lambda);
+  int q = st->q;
+  if (!lam_bad) q += 1;
+  if (!lam_bad && rho < 0.0 && q < 10) { st->q = q; return; }   // next trial of the same outer iteration
+  st->iters += 1;
+  const bool stop = (q == 10) || rho == 0.0 || !isfinite(st->lambda);
+  st->q = 0;
+  if (!accepted) st->dirty = 1;   // g2o rebuilds the system at the start of every outer iteration
+  if (stop || st->iters >= st->max_iterations) st->done = 1;
+}
+
+// (Re)initialises the controller for optimize(max_iterations); keeps `cur`.
+__global__ void ba_lm_reset(LMState* st, int max_iterations, int manual) {
+  st->dirty = 1; st->done = 0; st->manual = manual; st->first = 1;
+  st->iters = 0; st->trials = 0; st->q = 0; st->max_iterations = max_iterations;
+  st->last_pcg_status = 0; st->last_pcg_iters = 0;
+  st->lambda = 0.0; st->ni = 2.0; st->cur_cost = 0.0; st->initial_cost = 0.0; st->max_diag = 0.0;
+  st->pcg_total = 0.0; st->rejected = 0.0; st->breakdowns = 0.0;
+  st->last_cost = 0.0; st->last_scale = 0.0; st->last_rho = 0.0;
+}
+// Stage API pokes: op 0 = force a rebuild, 1 = set lambda, 2 = accept the trial state.
+__global__ void ba_lm_poke(LMState* st, int op, double value) {
+  if (op == 0) { st->dirty = 1; st->done = 0; st->manual = 1; }
+  else if (op == 1) { st->lambda = value; st->done = 0; st->manual = 1; }
+  else if (op == 2) { st->cur ^= 1; st->dirty = 1; }
+  else if (op == 3) { st->cur = 0; }
+}
+// Copies the current (which = 0) or trial (1) state out.
+__global__ void ba_copy_state(const LMState* __restrict__ st, int which, const double* __restrict__ a0,
+                              const double* __restrict__ a1, double* __restrict__ dst, size_t n) {
+  const double* src = ((st->cur ^ which) & 1) ? a1 : a0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = src[i];
 }
 
 __global__ void ba_gather_uv(int N, const int* __restrict__ src, const double2* __restrict__ uv,
@@ -149,23 +227,27 @@ struct BA {
   // state: [0] current, [1] trial
   DevBuf<double> cams[2], pts[2], scale_meas;
   DevBuf<CamRT> camrt[2];
-  int cur = 0;
+  DevBuf<LMState> lm;            // device-resident LM controller state
+  LMState* lm_host = nullptr;    // pinned mirror, valid after ba_sync_state()
+  cudaGraphExec_t step_graph = nullptr;   // one LM trial slot (rebuild-if-dirty + trial + controller)
+  bool graph_tried = false;
+  cudaStream_t graph_stream = nullptr;
   // system
   DevBuf<double> Hpl, Ebuf, Hpp, bp, bhat, Hll, bl, Hinv, camp, cam_cost, S, dp, dl, tmp3;
   DevBuf<double> unit_partial, seg_extra_dense, extra, bp_extra, scale_cost, scale_partial, res, p_glob, w_loc, part;
   DevBuf<unsigned> bar;
   DevBuf<int> pcg_flags;  // [0] fail flag, [1] status, [2] iters
-  double* res_host = nullptr;  // pinned [8]
   // PCG launch configuration
   int pcg_G = 1, pcg_rows = 6, pcg_slab = 1;
   size_t pcg_smem = 0;
   double pcg_tol = 1e-10;
   int pcg_max_iter = 0;
-  bool linearized = false;
 
   BAView view() const {
     BAView V;
     V.C = C; V.P = P; V.N = N; V.Cf = Cf; V.Pf = Pf; V.E = E; V.max_chunks = max_chunks; V.K = K;
+    V.st = lm.p;
+    for (int i = 0; i < 2; ++i) { V.cams[i] = cams[i].p; V.pts[i] = pts[i].p; V.camrt[i] = camrt[i].p; }
     V.cam_col = cam_col.p; V.pt_col = pt_col.p; V.cm_start = cm_start.p; V.cm_pt = cm_pt.p;
     V.cm_pm = cm_pm.p; V.cm_uv = cm_uv.p; V.pt_start = pt_start.p; V.pm_cam = pm_cam.p;
     V.pm_uv = pm_uv.p;
@@ -173,12 +255,16 @@ struct BA {
   }
   ScaleView scale_view() const {
     ScaleView V;
+    V.st = lm.p; V.cams2[0] = cams[0].p; V.cams2[1] = cams[1].p;
     V.E = E; V.n_extra = n_extra; V.Cf = Cf; V.sa = sa.p; V.sb = sb.p; V.meas = scale_meas.p;
     V.cam_col = cam_col.p; V.inc_start = inc_start.p; V.inc_edge = inc_edge.p; V.extra_a = extra_a.p;
     V.extra_b = extra_b.p; V.edge_w = edge_w.p; V.edge_es = edge_es.p; V.edge_u = edge_u.p;
     return V;
   }
-  ~BA() { if (res_host) cudaFreeHost(res_host); }
+  ~BA() {
+    if (step_graph) cudaGraphExecDestroy(step_graph);
+    if (lm_host) cudaFreeHost(lm_host);
+  }
 };
 
 static void counting_sort(const std::vector<int>& in, const int* key, int n_keys, std::vector<int>& out) {
@@ -339,7 +425,10 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(cudaMemset(B.bp_extra.p, 0, (size_t)std::max(B.n, 1) * sizeof(double)));
   BA_TRY(cudaMemset(B.scale_cost.p, 0, sizeof(double)));
   BA_TRY(cudaMemset(B.camp.p, 0, B.camp.n * sizeof(double)));
-  BA_TRY(cudaMallocHost(&B.res_host, 8 * sizeof(double)));
+  BA_TRY(B.lm.alloc(1));
+  BA_TRY(cudaMemset(B.lm.p, 0, sizeof(LMState)));
+  BA_TRY(cudaMallocHost(&B.lm_host, sizeof(LMState)));
+  std::memset(B.lm_host, 0, sizeof(LMState));
   // PCG configuration: as many CTAs as keep their slab of S in shared memory, at most one per SM
   {
     const int nb = Cf;
@@ -372,8 +461,14 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
 
 static int ba_set_state(BA& B, const double* cams, const double* pts, const double* uv,
                         const double* scale_meas, const double* K, cudaStream_t st) {
-  B.K = make_double4(K[0], K[1], K[2], K[3]);
-  B.cur = 0;
+  const double4 Knew = make_double4(K[0], K[1], K[2], K[3]);
+  if (Knew.x != B.K.x || Knew.y != B.K.y || Knew.z != B.K.z || Knew.w != B.K.w) {
+    if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }  // K is baked into the nodes
+    B.graph_tried = false;
+  }
+  B.K = Knew;
+  ba_lm_reset<<<1, 1, 0, st>>>(B.lm.p, 0, 1);
+  ba_lm_poke<<<1, 1, 0, st>>>(B.lm.p, 3, 0.0);
   BA_TRY(cudaMemcpyAsync(B.cams[0].p, cams, (size_t)B.C * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
   BA_TRY(cudaMemcpyAsync(B.pts[0].p, pts, (size_t)B.P * 3 * sizeof(double), cudaMemcpyDeviceToDevice, st));
   if (B.E) BA_TRY(cudaMemcpyAsync(B.scale_meas.p, scale_meas, (size_t)B.E * sizeof(double), cudaMemcpyDeviceToDevice, st));
@@ -383,50 +478,40 @@ static int ba_set_state(BA& B, const double* cams, const double* pts, const doub
     ba_gather_uv<<<blocks, 256, 0, st>>>(B.N, B.pm_src.p, reinterpret_cast<const double2*>(uv), B.pm_uv.p);
   }
   if (B.C) ba_prepare_cams<<<(B.C + 127) / 128, 128, 0, st>>>(B.cams[0].p, B.camrt[0].p, B.C);
-  B.linearized = false;
   return check_launch("ba_set_state");
 }
 
-static int ba_readback(BA& B, cudaStream_t st) {
-  BA_TRY(cudaMemcpyAsync(B.res_host, B.res.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
+static int ba_sync_state(BA& B, cudaStream_t st) {
+  BA_TRY(cudaMemcpyAsync(B.lm_host, B.lm.p, sizeof(LMState), cudaMemcpyDeviceToHost, st));
   BA_TRY(cudaStreamSynchronize(st));
   return VSLAM_OK;
 }
 
-// buildSystem() on the current state; res_host[0] = cost, res_host[2] = max |diag H|.
-static int ba_linearize(BA& B, cudaStream_t st) {
+// buildSystem() on the current state (every kernel returns at once unless LMState::dirty).
+static int enqueue_linearize(BA& B, cudaStream_t st) {
   const BAView V = B.view();
-  const int s = B.cur;
-  if (B.C == 0) return VSLAM_ERR_BAD_ARG;
   dim3 grid(B.max_chunks, B.C);
-  ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), B.cams[s].p, 0, B.extra.p, B.bp_extra.p, B.scale_cost.p,
-                                    B.maxdiag.p);
-  ba_cam_pass<false><<<grid, kCamThreads, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hpl.p, B.camp.p);
+  ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 0, B.extra.p, B.bp_extra.p, B.scale_cost.p, B.maxdiag.p);
+  ba_cam_pass<false><<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.camp.p);
   ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp_extra.p, B.diag_extra.p, B.extra.p, B.Hpp.p, B.bp.p,
                                       B.cam_cost.p, B.maxdiag.p);
-  if (B.P) ba_point_pass<<<(B.P * kPointLanes + 255) / 256, 256, 0, st>>>(V, B.camrt[s].p, B.pts[s].p, B.Hll.p, B.bl.p,
-                                                            B.maxdiag.p);
-  ba_finish<<<1, 256, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, 0, nullptr, 0, nullptr, nullptr, 0.0,
-                               nullptr, nullptr, B.maxdiag.p, B.res.p);
-  int rc = check_launch("ba_linearize");
-  if (rc) return rc;
-  B.linearized = true;
-  return ba_readback(B, st);
+  if (B.P) ba_point_pass<<<(B.P * kPointLanes + 255) / 256, 256, 0, st>>>(V, B.Hll.p, B.bl.p, B.maxdiag.p);
+  ba_lin_controller<<<1, 256, 0, st>>>(B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.maxdiag.p);
+  return check_launch("ba_linearize");
 }
 
-// One LM trial: solve (H + lambda I) d = b through Schur + PCG, write the trial state, evaluate it.
-// res_host: [0] trial cost, [1] computeScale, [3] pcg status, [4] pcg iterations.
-static int ba_trial(BA& B, double lambda, cudaStream_t st) {
-  if (!B.linearized) return VSLAM_ERR_BAD_ARG;
+// One LM trial at LMState::lambda: solve (H + lambda I) d = b through Schur + PCG, write the trial
+// state, evaluate it, then the controller decides (accept / reject / terminate) on the device.
+static int enqueue_trial(BA& B, cudaStream_t st) {
   const BAView V = B.view();
-  const int s = B.cur, t = B.cur ^ 1;
+  const LMState* lm = B.lm.p;
   dim3 grid(B.max_chunks, B.C);
   if (B.Pf) {
-    ba_point_invert<<<(B.Pf + 127) / 128, 128, 0, st>>>(B.Pf, B.Hll.p, lambda, B.Hinv.p);
+    ba_point_invert<<<(B.Pf + 127) / 128, 128, 0, st>>>(lm, B.Pf, B.Hll.p, B.Hinv.p);
     ba_compute_E<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.Hinv.p, B.bl.p, B.Ebuf.p, B.camp.p);
     ba_bhat_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp.p, B.bhat.p);
     if (B.n_units)
-      ba_schur_units<<<(B.n_units * 32 + 127) / 128, 128, 0, st>>>(B.Ebuf.p, B.Hpl.p, B.item_a.p, B.item_b.p,
+      ba_schur_units<<<(B.n_units * 32 + 127) / 128, 128, 0, st>>>(lm, B.Ebuf.p, B.Hpl.p, B.item_a.p, B.item_b.p,
                                                                 B.unit_start.p, B.unit_len.p, B.n_units,
                                                                 B.unit_partial.p);
   } else if (B.n) {
@@ -434,11 +519,12 @@ static int ba_trial(BA& B, double lambda, cudaStream_t st) {
   }
   if (B.n) {
     ba_schur_finalize<<<(B.n_seg * 36 + 127) / 128, 128, 0, st>>>(
-        B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
-        B.extra.p, B.seg_extra_idx.p, lambda, B.S.p);
+        lm, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
+        B.extra.p, B.seg_extra_idx.p, B.S.p);
     BA_TRY(cudaMemsetAsync(B.bar.p, 0, sizeof(unsigned), st));
     BA_TRY(cudaMemsetAsync(B.pcg_flags.p, 0, 4 * sizeof(int), st));
-    PcgArgs A;
+    PcgArgs A{};
+    A.done = &B.lm.p->done;
     A.S = B.S.p; A.b = B.bhat.p; A.x = B.dp.p; A.n = B.n; A.rows = B.pcg_rows; A.G = B.pcg_G;
     A.slab_in_smem = B.pcg_slab; A.max_iter = B.pcg_max_iter; A.tol = B.pcg_tol;
     A.p_glob = B.p_glob.p; A.w_loc = B.w_loc.p; A.part = B.part.p; A.bar = B.bar.p; A.fail_flag = B.pcg_flags.p;
@@ -452,21 +538,51 @@ static int ba_trial(BA& B, double lambda, cudaStream_t st) {
     }
   }
   if (B.Pf) ba_backsub_cam<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.dp.p, B.tmp3.p);
-  if (B.P)
-    ba_backsub_pt<<<B.n_sp, 256, 0, st>>>(V, B.tmp3.p, B.Hinv.p, B.bl.p, lambda, B.pts[s].p, B.pts[t].p,
-                                          B.dl.p, B.scale_partial.p);
-  ba_update_cams<<<(B.C + 127) / 128, 128, 0, st>>>(V, B.cams[s].p, B.dp.p, B.cams[t].p, B.camrt[t].p);
-  ba_cam_pass<true><<<grid, kCamThreads, 0, st>>>(V, B.camrt[t].p, B.pts[t].p, nullptr, B.camp.p);
+  if (B.P) ba_backsub_pt<<<B.n_sp, 256, 0, st>>>(V, B.tmp3.p, B.Hinv.p, B.bl.p, B.dl.p, B.scale_partial.p);
+  ba_update_cams<<<(B.C + 127) / 128, 128, 0, st>>>(V, B.dp.p);
+  ba_cam_pass<true><<<grid, kCamThreads, 0, st>>>(V, nullptr, B.camp.p);
   ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, nullptr, nullptr, nullptr, nullptr, nullptr, B.cam_cost.p,
                                       nullptr);
-  ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), B.cams[t].p, 1, B.extra.p, B.bp_extra.p, B.scale_cost.p,
-                                    B.maxdiag.p);
-  ba_finish<<<1, 256, 0, st>>>(B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0, B.scale_partial.p, B.n,
-                               B.dp.p, B.bp.p, lambda, B.pcg_flags.p + 1, B.pcg_flags.p + 2, B.maxdiag.p,
-                               B.res.p);
-  int rc = check_launch("ba_trial");
+  ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 1, B.extra.p, B.bp_extra.p, B.scale_cost.p, B.maxdiag.p);
+  ba_trial_controller<<<1, 256, 0, st>>>(B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0,
+                                         B.scale_partial.p, B.n, B.dp.p, B.bp.p, B.pcg_flags.p + 1,
+                                         B.pcg_flags.p + 2);
+  return check_launch("ba_trial");
+}
+
+static int enqueue_step(BA& B, cudaStream_t st) {
+  int rc = enqueue_linearize(B, st);
   if (rc) return rc;
-  return ba_readback(B, st);
+  return enqueue_trial(B, st);
+}
+
+// Captures one LM trial slot into a CUDA graph (all arguments are fixed device pointers; lambda and
+// the buffer roles live in LMState).  On any capture problem the step is launched kernel by kernel.
+static void try_capture_step(BA& B) {
+  if (B.graph_tried) return;
+  B.graph_tried = true;
+  cudaStream_t cs = nullptr;
+  if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return; }
+  cudaGraph_t graph = nullptr;
+  bool ok = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+  if (ok) {
+    const int rc = enqueue_step(B, cs);
+    const cudaError_t e = cudaStreamEndCapture(cs, &graph);
+    ok = (rc == VSLAM_OK) && (e == cudaSuccess) && graph != nullptr;
+  }
+  if (ok) ok = cudaGraphInstantiate(&B.step_graph, graph, 0) == cudaSuccess;
+  if (graph) cudaGraphDestroy(graph);
+  if (!ok) { B.step_graph = nullptr; cudaGetLastError(); }
+  cudaStreamDestroy(cs);
+}
+
+static int launch_steps(BA& B, int count, cudaStream_t st) {
+  try_capture_step(B);
+  for (int i = 0; i < count; ++i) {
+    if (B.step_graph) BA_TRY(cudaGraphLaunch(B.step_graph, st));
+    else { int rc = enqueue_step(B, st); if (rc) return rc; }
+  }
+  return VSLAM_OK;
 }
 
 }  // namespace vslam
@@ -476,58 +592,39 @@ using namespace vslam;
 struct vslam_ba { BA impl; };
 
 // OptimizationAlgorithmLevenberg::solve driven by SparseOptimizer::optimize(max_iterations)
-// (reference LocalBA.py:39-42).  stats: [0] initial cost, [1] final cost, [2] outer iterations,
+// (reference LocalBA.py:39-42).  The whole loop runs on the device: `max_iterations` trial slots are
+// enqueued back to back (one CUDA graph launch each), the state is read once, and more slots follow
+// only if a trial was rejected.  stats: [0] initial cost, [1] final cost, [2] outer iterations,
 // [3] trials, [4] final lambda, [5] total PCG iterations, [6] rejected trials, [7] PCG breakdowns.
 static int ba_optimize(BA& B, int max_iterations, double* stats, cudaStream_t st) {
-  const double tau = 1e-5, good_lo = 1.0 / 3.0, good_hi = 2.0 / 3.0;
-  const int max_trials = 10;
-  double lambda = 0.0, ni = 2.0, cur = 0.0;
-  double initial = 0.0, pcg_total = 0.0, rejected = 0.0, breakdowns = 0.0;
-  int trials = 0, iters = 0;
-  for (int it = 0; it < max_iterations; ++it) {
-    int rc = ba_linearize(B, st);
+  if (B.C == 0) return VSLAM_ERR_BAD_ARG;
+  ba_lm_reset<<<1, 1, 0, st>>>(B.lm.p, max_iterations, max_iterations == 0 ? 1 : 0);
+  if (max_iterations == 0) {   // report the cost of the state as given
+    int rc = enqueue_linearize(B, st);
     if (rc) return rc;
-    cur = B.res_host[0];
-    if (it == 0) { initial = cur; lambda = tau * B.res_host[2]; ni = 2.0; }
-    double rho = 0.0;
-    int q = 0;
-    do {
-      rc = ba_trial(B, lambda, st);
-      if (rc) return rc;
-      double tmp = B.res_host[0];
-      const bool ok = B.res_host[3] != 1.0;
-      pcg_total += B.res_host[4];
-      if (!ok) { tmp = std::numeric_limits<double>::max(); breakdowns += 1; }
-      const double scale = B.res_host[1] + 1e-3;
-      rho = (cur - tmp) / scale;
-      ++trials;
-      if (rho > 0 && std::isfinite(tmp)) {
-        double alpha = 1.0 - std::pow(2 * rho - 1, 3);
-        alpha = std::min(alpha, good_hi);
-        lambda *= std::max(good_lo, alpha);
-        ni = 2.0;
-        cur = tmp;
-        B.cur ^= 1;  // discardTop(): the trial state becomes current
-        B.linearized = false;
-      } else {
-        lambda *= ni;
-        ni *= 2;
-        rejected += 1;  // pop(): current state untouched
-        if (!std::isfinite(lambda)) break;
-      }
-      ++q;
-    } while (rho < 0 && q < max_trials);
-    ++iters;
-    if (q == max_trials || rho == 0 || !std::isfinite(lambda)) break;
-  }
-  if (iters == 0) {  // max_iterations == 0: report the cost of the state as given
-    int rc = ba_linearize(B, st);
+    rc = ba_sync_state(B, st);
     if (rc) return rc;
-    initial = cur = B.res_host[0];
+    if (stats) {
+      for (int i = 0; i < 8; ++i) stats[i] = 0.0;
+      stats[0] = stats[1] = B.lm_host->cur_cost;
+    }
+    return VSLAM_OK;
   }
+  int budget = max_iterations * 10 + 1;   // at most 10 trials per outer iteration
+  int batch = max_iterations;
+  while (true) {
+    int rc = launch_steps(B, batch, st);
+    if (rc) return rc;
+    rc = ba_sync_state(B, st);
+    if (rc) return rc;
+    budget -= batch;
+    if (B.lm_host->done || budget <= 0) break;
+    batch = std::max(1, std::min(budget, max_iterations - B.lm_host->iters));
+  }
+  const LMState& L = *B.lm_host;
   if (stats) {
-    stats[0] = initial; stats[1] = cur; stats[2] = iters; stats[3] = trials; stats[4] = lambda;
-    stats[5] = pcg_total; stats[6] = rejected; stats[7] = breakdowns;
+    stats[0] = L.initial_cost; stats[1] = L.cur_cost; stats[2] = L.iters; stats[3] = L.trials;
+    stats[4] = L.lambda; stats[5] = L.pcg_total; stats[6] = L.rejected; stats[7] = L.breakdowns;
   }
   return VSLAM_OK;
 }
@@ -562,42 +659,60 @@ extern "C" int vslam_ba_get_state(vslam_ba* h, double* cams, double* pts, void* 
   if (!h) return VSLAM_ERR_BAD_ARG;
   BA& B = h->impl;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (cams) BA_TRY(cudaMemcpyAsync(cams, B.cams[B.cur].p, (size_t)B.C * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
-  if (pts && B.P) BA_TRY(cudaMemcpyAsync(pts, B.pts[B.cur].p, (size_t)B.P * 3 * sizeof(double), cudaMemcpyDeviceToDevice, st));
-  return VSLAM_OK;
+  if (cams) ba_copy_state<<<64, 256, 0, st>>>(B.lm.p, 0, B.cams[0].p, B.cams[1].p, cams, (size_t)B.C * 7);
+  if (pts && B.P) ba_copy_state<<<148 * 4, 256, 0, st>>>(B.lm.p, 0, B.pts[0].p, B.pts[1].p, pts, (size_t)B.P * 3);
+  return check_launch("ba_copy_state");
 }
 
 extern "C" int vslam_ba_set_solver(vslam_ba* h, double pcg_tol, int pcg_max_iter) {
   if (!h || !(pcg_tol > 0)) return VSLAM_ERR_BAD_ARG;
-  h->impl.pcg_tol = pcg_tol;
-  if (pcg_max_iter > 0) h->impl.pcg_max_iter = pcg_max_iter;
+  BA& B = h->impl;
+  const int mi = pcg_max_iter > 0 ? pcg_max_iter : B.pcg_max_iter;
+  if (pcg_tol != B.pcg_tol || mi != B.pcg_max_iter) {   // both are baked into the captured step
+    if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }
+    B.graph_tried = false;
+  }
+  B.pcg_tol = pcg_tol;
+  B.pcg_max_iter = mi;
   return VSLAM_OK;
 }
 
 extern "C" int vslam_ba_linearize(vslam_ba* h, double* out2, void* stream) {
   if (!h) return VSLAM_ERR_BAD_ARG;
-  int rc = ba_linearize(h->impl, static_cast<cudaStream_t>(stream));
+  BA& B = h->impl;
+  if (B.C == 0) return VSLAM_ERR_BAD_ARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ba_lm_poke<<<1, 1, 0, st>>>(B.lm.p, 0, 0.0);
+  int rc = enqueue_linearize(B, st);
   if (rc) return rc;
-  if (out2) { out2[0] = h->impl.res_host[0]; out2[1] = h->impl.res_host[2]; }
+  rc = ba_sync_state(B, st);
+  if (rc) return rc;
+  if (out2) { out2[0] = B.lm_host->cur_cost; out2[1] = B.lm_host->max_diag; }
   return VSLAM_OK;
 }
 
 extern "C" int vslam_ba_trial(vslam_ba* h, double lambda, double* out4, void* stream) {
   if (!h) return VSLAM_ERR_BAD_ARG;
-  int rc = ba_trial(h->impl, lambda, static_cast<cudaStream_t>(stream));
+  BA& B = h->impl;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ba_lm_poke<<<1, 1, 0, st>>>(B.lm.p, 1, lambda);
+  int rc = enqueue_linearize(B, st);   // no-op unless the state changed since the last rebuild
+  if (rc) return rc;
+  rc = enqueue_trial(B, st);
+  if (rc) return rc;
+  rc = ba_sync_state(B, st);
   if (rc) return rc;
   if (out4) {
-    out4[0] = h->impl.res_host[0]; out4[1] = h->impl.res_host[1];
-    out4[2] = h->impl.res_host[3]; out4[3] = h->impl.res_host[4];
+    out4[0] = B.lm_host->last_cost; out4[1] = B.lm_host->last_scale;
+    out4[2] = (double)B.lm_host->last_pcg_status; out4[3] = (double)B.lm_host->last_pcg_iters;
   }
   return VSLAM_OK;
 }
 
 extern "C" int vslam_ba_accept(vslam_ba* h) {
   if (!h) return VSLAM_ERR_BAD_ARG;
-  h->impl.cur ^= 1;
-  h->impl.linearized = false;
-  return VSLAM_OK;
+  ba_lm_poke<<<1, 1, 0, 0>>>(h->impl.lm.p, 2, 0.0);   // legacy default stream: ordered after prior work
+  return check_launch("ba_lm_poke");
 }
 
 extern "C" int vslam_ba_optimize(vslam_ba* h, int max_iterations, double* stats8, void* stream) {
@@ -627,8 +742,16 @@ extern "C" int vslam_ba_read(vslam_ba* h, int what, double* dst, int64_t capacit
     case 5: src = B.bhat.p; n = B.n; break;
     case 6: src = B.dp.p; n = B.n; break;
     case 7: src = B.dl.p; n = (size_t)B.Pf * 3; break;
-    case 8: src = B.cams[B.cur ^ 1].p; n = (size_t)B.C * 7; break;
-    case 9: src = B.pts[B.cur ^ 1].p; n = (size_t)B.P * 3; break;
+    case 8:
+      n = (size_t)B.C * 7;
+      if ((int64_t)n > capacity) return VSLAM_ERR_BAD_ARG;
+      ba_copy_state<<<64, 256, 0, static_cast<cudaStream_t>(stream)>>>(B.lm.p, 1, B.cams[0].p, B.cams[1].p, dst, n);
+      return check_launch("ba_copy_state");
+    case 9:
+      n = (size_t)B.P * 3;
+      if ((int64_t)n > capacity) return VSLAM_ERR_BAD_ARG;
+      ba_copy_state<<<148 * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(B.lm.p, 1, B.pts[0].p, B.pts[1].p, dst, n);
+      return check_launch("ba_copy_state");
     default: return VSLAM_ERR_BAD_ARG;
   }
   if ((int64_t)n > capacity) return VSLAM_ERR_BAD_ARG;
@@ -647,7 +770,7 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
   BA_TRY(p_glob.alloc(n)); BA_TRY(w_loc.alloc(n)); BA_TRY(part.alloc(4)); BA_TRY(bar.alloc(1)); BA_TRY(flags.alloc(4));
   BA_TRY(cudaMemsetAsync(bar.p, 0, sizeof(unsigned), st));
   BA_TRY(cudaMemsetAsync(flags.p, 0, 4 * sizeof(int), st));
-  PcgArgs A;
+  PcgArgs A{};
   A.S = S; A.b = b; A.x = x; A.n = n; A.rows = n; A.G = 1; A.max_iter = max_iter; A.tol = tol;
   A.p_glob = p_glob.p; A.w_loc = w_loc.p; A.part = part.p; A.bar = bar.p; A.fail_flag = flags.p; A.status = flags.p + 1;
   A.iters = flags.p + 2;

@@ -17,9 +17,27 @@ constexpr int kCamThreads = 256;
 constexpr int kCamVals = 28;      // 21 Hpp upper + 6 bp + 1 cost
 constexpr int kUnitItems = 256;   // Schur items per warp work unit
 
+// Levenberg-Marquardt controller state, resident in HBM: every kernel of an LM step reads it, the
+// two controller kernels (ba_lin_controller / ba_trial_controller) are the only writers.  A whole
+// optimize() call is enqueued without host round trips (one CUDA graph launch per trial slot).
+struct LMState {
+  int cur;             // index of the CURRENT state buffers (the trial state is cur ^ 1)
+  int dirty;           // 1: the system must be rebuilt from the current state before the next trial
+  int done;            // 1: the optimisation has terminated; every kernel returns at once
+  int manual;          // 1: stage API (vslam_ba_linearize/trial): controllers only record results
+  int first;           // 1 until lambda has been initialised (computeLambdaInit)
+  int iters, trials, q, max_iterations;
+  int last_pcg_status, last_pcg_iters, pad_;
+  double lambda, ni, cur_cost, initial_cost, max_diag;
+  double pcg_total, rejected, breakdowns;
+  double last_cost, last_scale, last_rho;
+};
+
 struct BAView {
   int C, P, N, Cf, Pf, E, max_chunks;
   double4 K;
+  const LMState* st;
+  double* cams[2]; double* pts[2]; CamRT* camrt[2];
   const int* cam_col; const int* pt_col;
   const int* cm_start; const int* cm_pt; const int* cm_pm; const double2* cm_uv;
   const int* pt_start; const int* pm_cam; const double2* pm_uv;
@@ -66,8 +84,11 @@ __device__ __forceinline__ void warp_transpose_sum32(double (&v)[32], int lane) 
 // (w Jc^T Jp, 6x3 row-major).  Values 0..20 Hpp upper, 21..26 bp, 27 cost.
 template <bool COST_ONLY>
 __global__ void __launch_bounds__(kCamThreads)
-ba_cam_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict__ pts,
-            double* __restrict__ Hpl, double* __restrict__ camp) {
+ba_cam_pass(BAView V, double* __restrict__ Hpl, double* __restrict__ camp) {
+  if (V.st->done || (!COST_ONLY && !V.st->dirty)) return;
+  const int sb = COST_ONLY ? (V.st->cur ^ 1) : V.st->cur;   // trial state for the cost-only pass
+  const CamRT* __restrict__ camrt = V.camrt[sb];
+  const double* __restrict__ pts = V.pts[sb];
   __shared__ double red[(kCamThreads / 32) * 32];
   __shared__ __align__(16) double stage[COST_ONLY ? 2 : kCamThreads * 18];  // Hpl blocks of the CTA
   const int c = blockIdx.y, chunk = blockIdx.x;
@@ -158,6 +179,7 @@ __global__ void ba_cam_finalize(BAView V, const double* __restrict__ camp,
                                 double* __restrict__ bp, double* __restrict__ cam_cost,
                                 unsigned long long* __restrict__ maxdiag_bits) {
   const int c = blockIdx.x, i = threadIdx.x;
+  if (V.st->done || (Hpp != nullptr && !V.st->dirty)) return;
   if (i >= kCamVals) return;
   const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
   const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
@@ -183,9 +205,11 @@ __global__ void ba_cam_finalize(BAView V, const double* __restrict__ camp,
 constexpr int kPointLanes = 4;
 
 __global__ void __launch_bounds__(256)
-ba_point_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restrict__ pts,
-              double* __restrict__ Hll, double* __restrict__ bl,
+ba_point_pass(BAView V, double* __restrict__ Hll, double* __restrict__ bl,
               unsigned long long* __restrict__ maxdiag_bits) {
+  if (V.st->done || !V.st->dirty) return;
+  const CamRT* __restrict__ camrt = V.camrt[V.st->cur];
+  const double* __restrict__ pts = V.pts[V.st->cur];
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   const int p = g / kPointLanes, q = g % kPointLanes;
   const int col = (p < V.P) ? V.pt_col[p] : -1;
@@ -242,8 +266,10 @@ ba_point_pass(BAView V, const CamRT* __restrict__ camrt, const double* __restric
   }
 }
 
-__global__ void ba_point_invert(int Pf, const double* __restrict__ Hll, double lambda,
+__global__ void ba_point_invert(const LMState* __restrict__ st, int Pf, const double* __restrict__ Hll,
                                 double* __restrict__ Hinv) {
+  if (st->done) return;
+  const double lambda = st->lambda;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= Pf) return;
   double h[6], o[6];
@@ -260,6 +286,7 @@ __global__ void __launch_bounds__(kCamThreads)
 ba_compute_E(BAView V, const double* __restrict__ Hpl, const double* __restrict__ Hinv,
              const double* __restrict__ bl, double* __restrict__ Eout, double* __restrict__ camp) {
   __shared__ double red[(kCamThreads / 32) * 6];
+  if (V.st->done) return;
   const int c = blockIdx.y, chunk = blockIdx.x;
   const int start = V.cm_start[c] + chunk * kCamChunk;
   const int end = min(V.cm_start[c + 1], start + kCamChunk);
@@ -294,7 +321,7 @@ __global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp,
                                  const double* __restrict__ bp, double* __restrict__ bhat) {
   const int c = blockIdx.x, i = threadIdx.x;
   const int col = V.cam_col[c];
-  if (i >= 6 || col < 0) return;
+  if (V.st->done || i >= 6 || col < 0) return;
   const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
   const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
   double s = 0.0;
@@ -304,13 +331,13 @@ __global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp,
 
 // Schur work units: one warp reduces <= kUnitItems products E_a * Hpl_b^T of one (cam a, cam b) key.
 __global__ void __launch_bounds__(128)
-ba_schur_units(const double* __restrict__ E, const double* __restrict__ Hpl,
+ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ E, const double* __restrict__ Hpl,
                const int* __restrict__ item_a, const int* __restrict__ item_b,
                const int* __restrict__ unit_start, const int* __restrict__ unit_len, int n_units,
                double* __restrict__ partial) {
   const int u = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (u >= n_units) return;
+  if (st->done || u >= n_units) return;
   const int s = unit_start[u], len = unit_len[u];
   double acc[36];
 #pragma unroll
@@ -336,14 +363,15 @@ ba_schur_units(const double* __restrict__ E, const double* __restrict__ Hpl,
 }
 
 // S block (a,b) = [a==b](Hpp_a + lambda I) + scale-edge block - sum of its units; mirrored.
-__global__ void ba_schur_finalize(int n_seg, int n, const int* __restrict__ seg_a,
+__global__ void ba_schur_finalize(const LMState* __restrict__ st, int n_seg, int n, const int* __restrict__ seg_a,
                                   const int* __restrict__ seg_b,
                                   const int* __restrict__ seg_unit_start,
                                   const double* __restrict__ partial,
                                   const double* __restrict__ Hpp,
                                   const double* __restrict__ extra,
-                                  const int* __restrict__ seg_extra_idx, double lambda,
-                                  double* __restrict__ S) {
+                                  const int* __restrict__ seg_extra_idx, double* __restrict__ S) {
+  if (st->done) return;
+  const double lambda = st->lambda;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int seg = t / 36, e = t % 36;
   if (seg >= n_seg) return;
@@ -366,7 +394,7 @@ ba_backsub_cam(BAView V, const double* __restrict__ Hpl, const double* __restric
   const int start = V.cm_start[c] + chunk * kCamChunk;
   const int end = min(V.cm_start[c + 1], start + kCamChunk);
   const int col = V.cam_col[c];
-  if (start >= end || col < 0) return;
+  if (V.st->done || start >= end || col < 0) return;
   double d[6];
 #pragma unroll
   for (int i = 0; i < 6; ++i) d[i] = dp[6 * col + i];
@@ -389,10 +417,13 @@ ba_backsub_cam(BAView V, const double* __restrict__ Hpl, const double* __restric
 // Also the per-CTA partial of sum dl (lambda dl + bl)  (computeScale, landmark part).
 __global__ void __launch_bounds__(256)
 ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restrict__ Hinv,
-              const double* __restrict__ bl, double lambda, const double* __restrict__ pts,
-              double* __restrict__ pts_trial, double* __restrict__ dl_out,
+              const double* __restrict__ bl, double* __restrict__ dl_out,
               double* __restrict__ scale_partial) {
   __shared__ double red[8];
+  if (V.st->done) return;
+  const double lambda = V.st->lambda;
+  const double* __restrict__ pts = V.pts[V.st->cur];
+  double* __restrict__ pts_trial = V.pts[V.st->cur ^ 1];
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   double sc[1] = {0.0};
   if (p < V.P) {
@@ -420,11 +451,12 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
 }
 
 // SBACam::update on every free camera (t += d[0:3]; q <- normalize(q * (sqrt(1-|v|^2), v))).
-__global__ void ba_update_cams(BAView V, const double* __restrict__ cams,
-                               const double* __restrict__ dp, double* __restrict__ cams_trial,
-                               CamRT* __restrict__ camrt_trial) {
+__global__ void ba_update_cams(BAView V, const double* __restrict__ dp) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= V.C) return;
+  if (V.st->done || c >= V.C) return;
+  const double* __restrict__ cams = V.cams[V.st->cur];
+  double* __restrict__ cams_trial = V.cams[V.st->cur ^ 1];
+  CamRT* __restrict__ camrt_trial = V.camrt[V.st->cur ^ 1];
   double q[4] = {cams[7 * c], cams[7 * c + 1], cams[7 * c + 2], cams[7 * c + 3]};
   double t[3] = {cams[7 * c + 4], cams[7 * c + 5], cams[7 * c + 6]};
   const int col = V.cam_col[c];

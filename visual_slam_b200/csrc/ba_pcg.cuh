@@ -13,6 +13,7 @@
 namespace vslam {
 
 struct PcgArgs {
+  const int* done;    // optional (&LMState::done): the solve is skipped when the LM loop has terminated
   const double* S; const double* b; double* x;
   int n, rows, G, slab_in_smem, max_iter;
   double tol;
@@ -91,6 +92,20 @@ __device__ __forceinline__ double block_sum1(double v, double* red) {
   return s;  // every thread holds the same, order-fixed sum
 }
 
+// Three block sums with one barrier pair; every thread ends with the same, order-fixed sums.
+__device__ __forceinline__ void block_sum3(double& a, double& b, double& c, double* red3) {
+  a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+  if ((threadIdx.x & 31) == 0) {
+    const int w = threadIdx.x >> 5;
+    red3[3 * w] = a; red3[3 * w + 1] = b; red3[3 * w + 2] = c;
+  }
+  __syncthreads();
+  double sa = 0.0, sb = 0.0, sc = 0.0;
+  for (int w = 0; w < kPcgThreads / 32; ++w) { sa += red3[3 * w]; sb += red3[3 * w + 1]; sc += red3[3 * w + 2]; }
+  __syncthreads();
+  a = sa; b = sb; c = sc;
+}
+
 // Sum of the G per-CTA partials of K quantities laid out as part[k * G + g]: warp 0 strides over g,
 // butterfly-reduces, and publishes through shared memory.  Fixed shape -> deterministic, and only one
 // warp per CTA touches L2.
@@ -115,6 +130,7 @@ __device__ __forceinline__ void gather_sums(const double* part, int G, double* s
 // iteration, i.e. two grid barriers (publish u = M^-1 r; reduce (r,u), (Au,u), (r,r)).
 __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
   extern __shared__ __align__(16) double sm[];
+  if (A.done != nullptr && *A.done) return;   // uniform over the grid: nobody writes it meanwhile
   const int n = A.n, G = A.G, g = blockIdx.x, tid = threadIdx.x;
   const int row0 = g * A.rows;
   const int R = max(0, min(A.rows, n - row0));
@@ -130,6 +146,7 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
   double* slab = red + 8;              // [rows][n] when slab_in_smem
   __shared__ int s_fail;
   __shared__ double s_sum[3];
+  __shared__ double red3[3 * (kPcgThreads / 32)];
   unsigned target = 0;
 
   if (tid == 0) s_fail = 0;
@@ -159,11 +176,13 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
       double z = 0.0;
       for (int j = 0; j < 6; ++j) z += minv[36 * bi + 6 * ii + j] * rl[6 * bi + j];
       ul[i] = z;
-      A.p_glob[row0 + i] = z;
+      if (G > 1) A.p_glob[row0 + i] = z; else u_full[i] = z;
     }
-    grid_barrier(A.bar, target, G);
-    if (it == 0 && __ldcg(A.fail_flag)) { status = 1; break; }
-    for (int i = tid; i < n; i += kPcgThreads) u_full[i] = __ldcg(A.p_glob + i);
+    if (G > 1) {
+      grid_barrier(A.bar, target, G);
+      if (it == 0 && __ldcg(A.fail_flag)) { status = 1; break; }
+      for (int i = tid; i < n; i += kPcgThreads) u_full[i] = __ldcg(A.p_glob + i);
+    } else if (it == 0 && s_fail) { status = 1; break; }
     __syncthreads();
     // w = S u for the local rows: one warp per row
     double gam_p = 0.0, del_p = 0.0, rr_p = 0.0;
@@ -181,13 +200,13 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
       del_p += w * ul[i];
       rr_p += rl[i] * rl[i];
     }
-    gam_p = block_sum1(gam_p, red);
-    del_p = block_sum1(del_p, red);
-    rr_p = block_sum1(rr_p, red);
-    if (tid == 0) { A.part[g] = gam_p; A.part[G + g] = del_p; A.part[2 * G + g] = rr_p; }
-    grid_barrier(A.bar, target, G);
-    double sums[3];
-    gather_sums<3>(A.part, G, s_sum, sums);
+    block_sum3(gam_p, del_p, rr_p, red3);
+    double sums[3] = {gam_p, del_p, rr_p};
+    if (G > 1) {
+      if (tid == 0) { A.part[g] = gam_p; A.part[G + g] = del_p; A.part[2 * G + g] = rr_p; }
+      grid_barrier(A.bar, target, G);
+      gather_sums<3>(A.part, G, s_sum, sums);
+    }
     const double gamma = sums[0], delta = sums[1], rr = sums[2];
     if (it == 0) {
       if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
