@@ -31,7 +31,9 @@ def close(a, b, rtol=1e-9):
 @pytest.mark.parametrize("args", [dict(n_cams=4, n_pts=60, obs_per_pt=3.0, seed=1),
                                   dict(n_cams=10, n_pts=5000, obs_per_pt=6.0, seed=0),
                                   dict(n_cams=7, n_pts=300, obs_per_pt=4.0, seed=2, with_scale=False),
-                                  dict(n_cams=6, n_pts=500, obs_per_pt=4.0, seed=3, motion_only=True)])
+                                  dict(n_cams=6, n_pts=500, obs_per_pt=4.0, seed=3, motion_only=True),
+                                  # points seen by more than 32 cameras take the strided point-role path
+                                  dict(n_cams=48, n_pts=120, obs_per_pt=40.0, seed=4)])
 def test_linearize_and_one_trial_match_restatement(args):
     p = synthetic_ba(**args)
     eng = BAEngine(p)

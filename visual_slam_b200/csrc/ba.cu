@@ -88,32 +88,6 @@ ba_scale_edges(ScaleView V, int cost_only, double* __restrict__ extra,
   }
 }
 
-// Controller after buildSystem(): total cost of the current state, computeLambdaInit on the first
-// linearisation (lambda = tau * max |diag H|).  One CTA, strided partials + fixed-order tree.
-__global__ void __launch_bounds__(256)
-ba_lin_controller(LMState* __restrict__ st, int C, const double* __restrict__ cam_cost,
-                  const double* __restrict__ scale_cost,
-                  const unsigned long long* __restrict__ maxdiag_bits) {
-  __shared__ double red[8];
-  if (st->done || !st->dirty) return;
-  double v[1] = {0.0};
-  for (int i = threadIdx.x; i < C; i += 256) v[0] += cam_cost[i];
-  block_reduce<1, 256>(v, red);
-  if (threadIdx.x == 0) {
-    const double cost = v[0] + *scale_cost;
-    const double md = __longlong_as_double((long long)*maxdiag_bits);
-    st->cur_cost = cost;
-    st->max_diag = md;
-    if (st->first && !st->manual) {
-      st->initial_cost = cost;
-      st->lambda = 1e-5 * md;   // tau (OptimizationAlgorithmLevenberg default)
-      st->ni = 2.0;
-      st->first = 0;
-    }
-    st->dirty = 0;
-  }
-}
-
 // Controller after a trial: cost of the trial state, computeScale, then the Levenberg-Marquardt
 // accept / reject logic of g2o (OptimizationAlgorithmLevenberg::solve) entirely on the device.
 __global__ void __launch_bounds__(256)
@@ -194,7 +168,7 @@ __global__ void ba_copy_state(const LMState* __restrict__ st, int which, const d
 __global__ void ba_gather_uv(int N, const int* __restrict__ src, const double2* __restrict__ uv,
                              double2* __restrict__ out) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < N) out[i] = uv[src[i]];
+  if (i < N) out[i] = (src[i] >= 0) ? uv[src[i]] : make_double2(0.0, 0.0);
 }
 
 template <typename T>
@@ -221,6 +195,15 @@ struct BA {
   DevBuf<int> cam_col, pt_col, cm_start, cm_pt, cm_pm, cm_src, pt_start, pm_cam, pm_src;
   DevBuf<int> item_a, item_b, unit_start, unit_len, seg_a, seg_b, seg_unit_start, seg_extra_idx;
   DevBuf<int> sa, sb, diag_extra, inc_start, inc_edge, extra_a, extra_b;
+  DevBuf<int> lin_role, wk_cam, wk_start, wk_chunk, cam_chunk_off;   // fused linearisation work lists
+  DevBuf<unsigned> cam_ticket, lin_ticket;
+  DevBuf<int2> long_item;
+  DevBuf<int> pm_pt, px_pt, px_cam, px_src;
+  DevBuf<double2> px_uv;
+  int n_pt_items = 0, n_long = 0, cams_in_smem = 0;
+  size_t lin_smem = 0;
+  DevBuf<double> cam_maxd, pt_maxd;
+  int lin_nA = 0, lin_nB = 0;
   DevBuf<double> edge_w, edge_es, edge_u;
   DevBuf<unsigned long long> maxdiag;
   DevBuf<double2> cm_uv, pm_uv;
@@ -252,6 +235,18 @@ struct BA {
     V.cm_pm = cm_pm.p; V.cm_uv = cm_uv.p; V.pt_start = pt_start.p; V.pm_cam = pm_cam.p;
     V.pm_uv = pm_uv.p;
     return V;
+  }
+  LinArgs lin_args() const {
+    LinArgs A;
+    A.nA = lin_nA; A.nB = lin_nB; A.role = lin_role.p; A.wk_cam = wk_cam.p; A.wk_start = wk_start.p;
+    A.wk_chunk = wk_chunk.p; A.cam_chunk_off = cam_chunk_off.p; A.cam_ticket = cam_ticket.p;
+    A.lin_ticket = lin_ticket.p; A.Hpl = Hpl.p; A.camp = camp.p; A.Hpp = Hpp.p; A.bp = bp.p;
+    A.cam_cost = cam_cost.p; A.cam_maxd = cam_maxd.p; A.Hll = Hll.p; A.bl = bl.p; A.pt_maxd = pt_maxd.p;
+    A.bp_extra = bp_extra.p; A.diag_extra = diag_extra.p; A.extra = extra.p; A.scale_cost = scale_cost.p;
+    A.st_rw = lm.p;
+    A.n_pt_items = n_pt_items; A.px_pt = px_pt.p; A.px_cam = px_cam.p; A.px_uv = px_uv.p;
+    A.n_long = n_long; A.long_item = long_item.p; A.pm_pt = pm_pt.p; A.cams_in_smem = cams_in_smem;
+    return A;
   }
   ScaleView scale_view() const {
     ScaleView V;
@@ -394,6 +389,61 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   }
   B.n_extra = n_extra;
   B.n_sp = (P + 255) / 256;
+  // fused linearisation: camera chunks (every camera owns at least one, possibly empty) and point
+  // blocks, interleaved in proportion so that both roles are resident at the same time
+  std::vector<int> wk_cam, wk_start, wk_chunk, cam_chunk_off(C + 1, 0), lin_role;
+  for (int c = 0; c < C; ++c) {
+    const int n_obs_c = cm_start[c + 1] - cm_start[c];
+    const int nch = std::max(1, (n_obs_c + kLinChunk - 1) / kLinChunk);
+    cam_chunk_off[c + 1] = cam_chunk_off[c] + nch;
+    for (int k = 0; k < nch; ++k) {
+      wk_cam.push_back(c); wk_start.push_back(cm_start[c] + k * kLinChunk); wk_chunk.push_back(k);
+    }
+  }
+  B.lin_nA = (int)wk_cam.size();
+  // point-role work items: runs of whole free points with <= 32 observations in total, laid out in
+  // 32 padded slots each; points with more observations go to the long list
+  std::vector<int2> long_item;
+  std::vector<int> pm_pt(N), px_pt, px_cam, px_src;
+  for (int p = 0; p < P; ++p)
+    for (int i = pt_start[p]; i < pt_start[p + 1]; ++i) pm_pt[i] = p;
+  {
+    int fill = 32;   // slots used in the open item (32 = none open)
+    for (int p = 0; p < P; ++p) {
+      const int np = pt_start[p + 1] - pt_start[p];
+      if (pt_col[p] < 0 || np == 0) continue;
+      if (np > 32) { long_item.push_back(make_int2(pt_start[p], np)); continue; }
+      if (fill + np > 32) {   // open a new item
+        px_pt.resize(px_pt.size() + 32, -1); px_cam.resize(px_cam.size() + 32, 0); px_src.resize(px_src.size() + 32, -1);
+        fill = 0;
+      }
+      const size_t base = px_pt.size() - 32 + fill;
+      for (int i = 0; i < np; ++i) {
+        px_pt[base + i] = p; px_cam[base + i] = pm_cam[pt_start[p] + i]; px_src[base + i] = pm_src[pt_start[p] + i];
+      }
+      fill += np;
+    }
+  }
+  B.n_pt_items = (int)(px_pt.size() / 32);
+  B.n_long = (int)long_item.size();
+  const int items_per_cta = (kLinThreads / 32) * kPtItemsPerWarp;
+  B.lin_nB = (B.n_pt_items + items_per_cta - 1) / items_per_cta;
+  if (B.n_long > 0) B.lin_nB = std::max(B.lin_nB, std::min(B.n_long, 4 * std::max(1, sm_count())));
+  B.cams_in_smem = (C <= kCamSmemMax) ? 1 : 0;
+  B.lin_smem = B.cams_in_smem ? (size_t)C * sizeof(CamRT) : 0;
+  BA_TRY(cudaFuncSetAttribute(ba_linearize_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)(kCamSmemMax * sizeof(CamRT))));
+  {
+    const long long tot = (long long)B.lin_nA + B.lin_nB;
+    lin_role.resize(tot);
+    int a = 0, b = 0;
+    for (long long i = 0; i < tot; ++i) {
+      // point block when the running share of point blocks falls behind
+      const bool want_b = (long long)(b + 1) * tot <= (i + 1) * (long long)B.lin_nB;
+      if ((want_b && b < B.lin_nB) || a >= B.lin_nA) lin_role[i] = -1 - b++;
+      else lin_role[i] = a++;
+    }
+  }
   // uploads
   BA_TRY(B.cam_col.upload(cam_col)); BA_TRY(B.pt_col.upload(pt_col));
   BA_TRY(B.cm_start.upload(cm_start)); BA_TRY(B.cm_pt.upload(cm_pt)); BA_TRY(B.cm_pm.upload(cm_pm));
@@ -407,6 +457,14 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.extra_a.upload(extra_a)); BA_TRY(B.extra_b.upload(extra_b));
   BA_TRY(B.edge_w.alloc(E)); BA_TRY(B.edge_es.alloc(E)); BA_TRY(B.edge_u.alloc((size_t)E * 3)); BA_TRY(B.maxdiag.alloc(1));
   BA_TRY(B.diag_extra.upload(diag_extra));
+  BA_TRY(B.lin_role.upload(lin_role)); BA_TRY(B.wk_cam.upload(wk_cam)); BA_TRY(B.wk_start.upload(wk_start));
+  BA_TRY(B.wk_chunk.upload(wk_chunk)); BA_TRY(B.cam_chunk_off.upload(cam_chunk_off));
+  BA_TRY(B.long_item.upload(long_item)); BA_TRY(B.pm_pt.upload(pm_pt)); BA_TRY(B.px_pt.upload(px_pt));
+  BA_TRY(B.px_cam.upload(px_cam)); BA_TRY(B.px_src.upload(px_src)); BA_TRY(B.px_uv.alloc(px_pt.size()));
+  BA_TRY(B.cam_ticket.alloc(C)); BA_TRY(B.lin_ticket.alloc(1)); BA_TRY(B.cam_maxd.alloc(C));
+  BA_TRY(B.pt_maxd.alloc(std::max(B.lin_nB, 1)));
+  BA_TRY(cudaMemset(B.cam_ticket.p, 0, (size_t)C * sizeof(unsigned)));
+  BA_TRY(cudaMemset(B.lin_ticket.p, 0, sizeof(unsigned)));
   BA_TRY(B.cm_uv.alloc(N)); BA_TRY(B.pm_uv.alloc(N)); BA_TRY(B.scale_meas.alloc(E));
   for (int s = 0; s < 2; ++s) {
     BA_TRY(B.cams[s].alloc((size_t)C * 7)); BA_TRY(B.pts[s].alloc((size_t)P * 3)); BA_TRY(B.camrt[s].alloc(C));
@@ -414,12 +472,14 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.Hpl.alloc((size_t)N * 18)); BA_TRY(B.Ebuf.alloc((size_t)N * 18));
   BA_TRY(B.Hpp.alloc((size_t)Cf * 36)); BA_TRY(B.bp.alloc(B.n)); BA_TRY(B.bhat.alloc(B.n));
   BA_TRY(B.Hll.alloc((size_t)Pf * 6)); BA_TRY(B.bl.alloc((size_t)Pf * 3)); BA_TRY(B.Hinv.alloc((size_t)Pf * 6));
-  BA_TRY(B.camp.alloc((size_t)C * B.max_chunks * kCamVals)); BA_TRY(B.cam_cost.alloc(C));
+  BA_TRY(B.camp.alloc(std::max((size_t)C * B.max_chunks, (size_t)B.lin_nA) * kCamVals)); BA_TRY(B.cam_cost.alloc(C));
   BA_TRY(B.S.alloc((size_t)B.n * B.n)); BA_TRY(B.dp.alloc(B.n)); BA_TRY(B.dl.alloc((size_t)Pf * 3));
   BA_TRY(B.tmp3.alloc((size_t)N * 3)); BA_TRY(B.unit_partial.alloc((size_t)B.n_units * 36));
   BA_TRY(B.extra.alloc((size_t)std::max(n_extra, 1) * 36)); BA_TRY(B.bp_extra.alloc(std::max(B.n, 1)));
   BA_TRY(B.scale_cost.alloc(1)); BA_TRY(B.scale_partial.alloc(B.n_sp)); BA_TRY(B.res.alloc(8));
   BA_TRY(B.p_glob.alloc(std::max(B.n, 1))); BA_TRY(B.w_loc.alloc(std::max(B.n, 1)));
+  BA_TRY(cudaMemset(B.Hll.p, 0, std::max<size_t>((size_t)Pf * 6, 1) * sizeof(double)));   // free points without
+  BA_TRY(cudaMemset(B.bl.p, 0, std::max<size_t>((size_t)Pf * 3, 1) * sizeof(double)));    // observations stay 0
   BA_TRY(cudaMemset(B.S.p, 0, std::max<size_t>((size_t)B.n * B.n, 1) * sizeof(double)));
   BA_TRY(cudaMemset(B.extra.p, 0, (size_t)std::max(n_extra, 1) * 36 * sizeof(double)));
   BA_TRY(cudaMemset(B.bp_extra.p, 0, (size_t)std::max(B.n, 1) * sizeof(double)));
@@ -476,6 +536,8 @@ static int ba_set_state(BA& B, const double* cams, const double* pts, const doub
     const int blocks = (B.N + 255) / 256;
     ba_gather_uv<<<blocks, 256, 0, st>>>(B.N, B.cm_src.p, reinterpret_cast<const double2*>(uv), B.cm_uv.p);
     ba_gather_uv<<<blocks, 256, 0, st>>>(B.N, B.pm_src.p, reinterpret_cast<const double2*>(uv), B.pm_uv.p);
+    const int nx = B.n_pt_items * 32;
+    if (nx) ba_gather_uv<<<(nx + 255) / 256, 256, 0, st>>>(nx, B.px_src.p, reinterpret_cast<const double2*>(uv), B.px_uv.p);
   }
   if (B.C) ba_prepare_cams<<<(B.C + 127) / 128, 128, 0, st>>>(B.cams[0].p, B.camrt[0].p, B.C);
   return check_launch("ba_set_state");
@@ -491,12 +553,8 @@ static int ba_sync_state(BA& B, cudaStream_t st) {
 static int enqueue_linearize(BA& B, cudaStream_t st) {
   const BAView V = B.view();
   dim3 grid(B.max_chunks, B.C);
-  ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 0, B.extra.p, B.bp_extra.p, B.scale_cost.p, B.maxdiag.p);
-  ba_cam_pass<false><<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.camp.p);
-  ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp_extra.p, B.diag_extra.p, B.extra.p, B.Hpp.p, B.bp.p,
-                                      B.cam_cost.p, B.maxdiag.p);
-  if (B.P) ba_point_pass<<<(B.P * kPointLanes + 255) / 256, 256, 0, st>>>(V, B.Hll.p, B.bl.p, B.maxdiag.p);
-  ba_lin_controller<<<1, 256, 0, st>>>(B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.maxdiag.p);
+  if (B.E) ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 0, B.extra.p, B.bp_extra.p, B.scale_cost.p, B.maxdiag.p);
+  ba_linearize_kernel<false><<<B.lin_nA + B.lin_nB, kLinThreads, B.lin_smem, st>>>(V, B.lin_args());
   return check_launch("ba_linearize");
 }
 
@@ -540,10 +598,8 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
   if (B.Pf) ba_backsub_cam<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.dp.p, B.tmp3.p);
   if (B.P) ba_backsub_pt<<<B.n_sp, 256, 0, st>>>(V, B.tmp3.p, B.Hinv.p, B.bl.p, B.dl.p, B.scale_partial.p);
   ba_update_cams<<<(B.C + 127) / 128, 128, 0, st>>>(V, B.dp.p);
-  ba_cam_pass<true><<<grid, kCamThreads, 0, st>>>(V, nullptr, B.camp.p);
-  ba_cam_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, nullptr, nullptr, nullptr, nullptr, nullptr, B.cam_cost.p,
-                                      nullptr);
-  ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 1, B.extra.p, B.bp_extra.p, B.scale_cost.p, B.maxdiag.p);
+  ba_linearize_kernel<true><<<B.lin_nA, kLinThreads, 0, st>>>(V, B.lin_args());
+  if (B.E) ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 1, B.extra.p, B.bp_extra.p, B.scale_cost.p, B.maxdiag.p);
   ba_trial_controller<<<1, 256, 0, st>>>(B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0,
                                          B.scale_partial.p, B.n, B.dp.p, B.bp.p, B.pcg_flags.p + 1,
                                          B.pcg_flags.p + 2);

@@ -16,6 +16,7 @@ constexpr int kCamChunk = 256;    // observations of one camera handled by one C
 constexpr int kCamThreads = 256;
 constexpr int kCamVals = 28;      // 21 Hpp upper + 6 bp + 1 cost
 constexpr int kUnitItems = 256;   // Schur items per warp work unit
+constexpr int kPointLanes = 4;    // lanes cooperating on one point in the point role
 
 // Levenberg-Marquardt controller state, resident in HBM: every kernel of an LM step reads it, the
 // two controller kernels (ba_lin_controller / ba_trial_controller) are the only writers.  A whole
@@ -79,158 +80,249 @@ __device__ __forceinline__ void warp_transpose_sum32(double (&v)[32], int lane) 
   }
 }
 
-// Camera-major pass, one thread per observation.  COST_ONLY = evaluate sum(rho) for a trial state;
-// otherwise also accumulate Hpp (upper 21) / bp per camera and write the Hpl blocks
-// (w Jc^T Jp, 6x3 row-major).  Values 0..20 Hpp upper, 21..26 bp, 27 cost.
+// ---- fused linearisation ---------------------------------------------------------------------
+// ONE launch builds the whole system: camera-role CTAs (chunks of kLinChunk observations of one
+// camera, kLinObs per thread, next observation prefetched) produce the Hpl blocks and the per-chunk
+// Hpp / bp / cost partials; point-role CTAs (a quad of lanes per point) produce Hll / bl.  The two
+// roles are interleaved in the grid so that the write-heavy camera pass and the latency-bound point
+// pass overlap.  The last chunk of a camera to finish (ticket counter) folds that camera's partials in
+// chunk order; the last CTA of the grid runs the controller (cost, computeLambdaInit).  All sums are
+// fixed-order trees -> bit-reproducible, no floating-point atomics.
+constexpr int kLinThreads = 128;
+constexpr int kLinObs = 8;
+constexpr int kPtItemsPerWarp = 8;   // point-role work items (<= 32 observations each) per warp
+constexpr int kCamSmemMax = 340;     // cameras kept in shared memory by the point role (96 B each)
+constexpr int kLinChunk = kLinThreads * kLinObs;
+
+struct LinArgs {
+  int nA, nB;                       // camera-role / point-role CTAs
+  const int* role;                  // [nA + nB]: >= 0 camera chunk index, < 0 point block -1 - b
+  const int* wk_cam; const int* wk_start; const int* wk_chunk;   // per camera chunk
+  const int* cam_chunk_off;         // [C + 1] first partial row of each camera
+  // point role, regular items: 32 padded slots each (whole points, <= 32 observations in total)
+  int n_pt_items; const int* px_pt; const int* px_cam; const double2* px_uv;   // [n_pt_items * 32], pt -1 = pad
+  // points with more than 32 observations: (first point-major observation, count), strided path
+  int n_long; const int2* long_item; const int* pm_pt;
+  int cams_in_smem;
+  unsigned* cam_ticket;             // [C], zero between launches
+  unsigned* lin_ticket;             // [1]
+  double* Hpl; double* camp; double* Hpp; double* bp; double* cam_cost; double* cam_maxd;
+  double* Hll; double* bl; double* pt_maxd;
+  const double* bp_extra; const int* diag_extra; const double* extra; const double* scale_cost;
+  LMState* st_rw;
+};
+
+// Controller after buildSystem(): total cost of the current state, computeLambdaInit on the first
+// linearisation (lambda = tau * max |diag H|).  Runs in the last CTA of the fused kernel.
+__device__ __forceinline__ void lin_controller(const BAView& V, const LinArgs& A, double* red /*[8]*/) {
+  double v[2] = {0.0, 0.0};
+  for (int i = threadIdx.x; i < V.C; i += kLinThreads) {
+    v[0] += __ldcg(A.cam_cost + i);
+    v[1] = fmax(v[1], __ldcg(A.cam_maxd + i));
+  }
+  for (int i = threadIdx.x; i < A.nB; i += kLinThreads) v[1] = fmax(v[1], __ldcg(A.pt_maxd + i));
+  v[0] = warp_sum(v[0]);
+  for (int o = 16; o > 0; o >>= 1) v[1] = fmax(v[1], __shfl_xor_sync(0xffffffffu, v[1], o));
+  if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = v[0]; red[4 + (threadIdx.x >> 5)] = v[1]; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    LMState* st = A.st_rw;
+    const double cost = ((red[0] + red[1]) + (red[2] + red[3])) + __ldcg(A.scale_cost);
+    const double md = fmax(fmax(red[4], red[5]), fmax(red[6], red[7]));
+    st->cur_cost = cost;
+    st->max_diag = md;
+    if (st->first && !st->manual) {
+      st->initial_cost = cost;
+      st->lambda = 1e-5 * md;   // tau (OptimizationAlgorithmLevenberg default)
+      st->ni = 2.0;
+      st->first = 0;
+    }
+    st->dirty = 0;
+  }
+}
+
 template <bool COST_ONLY>
-__global__ void __launch_bounds__(kCamThreads)
-ba_cam_pass(BAView V, double* __restrict__ Hpl, double* __restrict__ camp) {
+__global__ void __launch_bounds__(kLinThreads, 4)
+ba_linearize_kernel(BAView V, LinArgs A) {
+  __shared__ __align__(16) double stage[COST_ONLY ? 2 : (kLinThreads / 32) * 32 * 18];
+  __shared__ double red[(kLinThreads / 32) * 32];
+  __shared__ CamRT s_cam;
+  __shared__ int s_flag;
   if (V.st->done || (!COST_ONLY && !V.st->dirty)) return;
-  const int sb = COST_ONLY ? (V.st->cur ^ 1) : V.st->cur;   // trial state for the cost-only pass
+  const int sb = COST_ONLY ? (V.st->cur ^ 1) : V.st->cur;   // the cost-only pass evaluates the trial state
   const CamRT* __restrict__ camrt = V.camrt[sb];
   const double* __restrict__ pts = V.pts[sb];
-  __shared__ double red[(kCamThreads / 32) * 32];
-  __shared__ __align__(16) double stage[COST_ONLY ? 2 : kCamThreads * 18];  // Hpl blocks of the CTA
-  const int c = blockIdx.y, chunk = blockIdx.x;
-  const int start = V.cm_start[c] + chunk * kCamChunk;
-  const int end = min(V.cm_start[c + 1], start + kCamChunk);
-  if (start >= end) return;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const CamRT cam = camrt[c];
-  const bool cam_free = V.cam_col[c] >= 0;
-  double v[32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int role = COST_ONLY ? (int)blockIdx.x : A.role[blockIdx.x];
+  bool take_ticket = false;
+
+  if (role >= 0) {
+    // ------------------------------------------------ camera role
+    const int c = A.wk_cam[role], chunk = A.wk_chunk[role];
+    const int start = A.wk_start[role];
+    const int end = min(V.cm_start[c + 1], start + kLinChunk);
+    if (tid < 12) reinterpret_cast<double*>(&s_cam)[tid] = reinterpret_cast<const double*>(camrt + c)[tid];
+    const bool cam_free = V.cam_col[c] >= 0;
+    double v[32];
 #pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = 0.0;
-  const int o = start + threadIdx.x;
-  double h[18];
+    for (int i = 0; i < 32; ++i) v[i] = 0.0;
+    // two-stage software pipeline (warps issue in order, so a dependent address must never be
+    // computed right after its index load): the point INDEX is loaded two observations ahead, the
+    // point itself one observation ahead, and both are in flight under the current arithmetic.
+    int o = start + tid;
+    double X[3] = {0.0, 0.0, 1.0};
+    double2 uv = make_double2(0.0, 0.0);
+    int p_next = 0;
+    if (o + kLinThreads < end) p_next = V.cm_pt[o + kLinThreads];
+    if (o < end) {
+      const int p = V.cm_pt[o];
+      uv = V.cm_uv[o];
+      X[0] = pts[3 * p]; X[1] = pts[3 * p + 1]; X[2] = pts[3 * p + 2];
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int k = 0; k < kLinObs; ++k) {
+      const bool valid = o < end;
+      const double Xc[3] = {X[0], X[1], X[2]};
+      const double2 uvc = uv;
+      const int o_next = o + kLinThreads;
+      const int p_cur = p_next;
+      if (k + 2 < kLinObs && o_next + kLinThreads < end) p_next = V.cm_pt[o_next + kLinThreads];
+      if (k + 1 < kLinObs && o_next < end) {   // p_cur arrived during the previous observation
+        uv = V.cm_uv[o_next];
+        X[0] = pts[3 * p_cur]; X[1] = pts[3 * p_cur + 1]; X[2] = pts[3 * p_cur + 2];
+      }
+      double h[18];
 #pragma unroll
-  for (int i = 0; i < 18; ++i) h[i] = 0.0;
-  if (o < end) {
-    const int p = V.cm_pt[o];
-    const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
-    const double2 uv = V.cm_uv[o];
-    double pc[3], e[2], rho, w;
-    to_camera(cam, X, pc);
-    if (fabs(pc[2]) > 1e-12) {  // g2o aborts on z = 0; we drop the observation
-      residual(pc, V.K, uv.x, uv.y, e);
-      huber(e[0] * e[0] + e[1] * e[1], rho, w);
-      v[27] = rho;
-      if (!COST_ONLY && cam_free) {
-        double Jc[2][6], Jp[2][3], W0[6], W1[6];
-        jacobians(cam, pc, V.K, Jc, Jp);
+      for (int i = 0; i < 18; ++i) h[i] = 0.0;
+      if (valid) {
+        double pc[3], e[2], rho, w;
+        to_camera(s_cam, Xc, pc);
+        if (fabs(pc[2]) > 1e-12) {  // g2o aborts on z = 0; we drop the observation
+          residual(pc, V.K, uvc.x, uvc.y, e);
+          huber(e[0] * e[0] + e[1] * e[1], rho, w);
+          v[27] += rho;
+          if (!COST_ONLY && cam_free) {
+            double Jc[2][6], Jp[2][3], W0[6], W1[6];
+            jacobians(s_cam, pc, V.K, Jc, Jp);
 #pragma unroll
-        for (int i = 0; i < 6; ++i) { W0[i] = w * Jc[0][i]; W1[i] = w * Jc[1][i]; }
-        int k = 0;
+            for (int i = 0; i < 6; ++i) { W0[i] = w * Jc[0][i]; W1[i] = w * Jc[1][i]; }
+            int q = 0;
 #pragma unroll
-        for (int i = 0; i < 6; ++i) {
+            for (int i = 0; i < 6; ++i) {
 #pragma unroll
-          for (int j = i; j < 6; ++j) v[k++] = W0[i] * Jc[0][j] + W1[i] * Jc[1][j];
-        }
+              for (int j = i; j < 6; ++j) { v[q] += W0[i] * Jc[0][j] + W1[i] * Jc[1][j]; ++q; }
+            }
 #pragma unroll
-        for (int i = 0; i < 6; ++i) v[21 + i] = -(W0[i] * e[0] + W1[i] * e[1]);
+            for (int i = 0; i < 6; ++i) v[21 + i] -= W0[i] * e[0] + W1[i] * e[1];
 #pragma unroll
-        for (int i = 0; i < 6; ++i) {
+            for (int i = 0; i < 6; ++i) {
 #pragma unroll
-          for (int j = 0; j < 3; ++j) h[3 * i + j] = W0[i] * Jp[0][j] + W1[i] * Jp[1][j];
+              for (int j = 0; j < 3; ++j) h[3 * i + j] = W0[i] * Jp[0][j] + W1[i] * Jp[1][j];
+            }
+          }
         }
       }
+      if (!COST_ONLY && cam_free) {
+        // the warp's 32 blocks are contiguous in HBM (camera-major): stage them in the warp's own
+        // slice of shared memory (144 B stride: conflict-free STS.128), write with coalesced STG.128
+        double* ws = stage + wid * (32 * 18);
+        const int base = o - lane;                       // first observation of this warp's row
+        const int n_blk = max(0, min(32, end - base));
+        __syncwarp();
+        store18(ws + lane * 18, h);
+        __syncwarp();
+        double2* dst = reinterpret_cast<double2*>(A.Hpl + (size_t)base * 18);
+        const double2* src = reinterpret_cast<const double2*>(ws);
+        for (int i = lane; i < n_blk * 9; i += 32) dst[i] = src[i];
+      }
+      o = o_next;
     }
-  }
-  if (!COST_ONLY && cam_free) store18(stage + threadIdx.x * 18, h);  // 144 B stride: conflict-free STS.128
-  if (!COST_ONLY && cam_free) {
-    // the CTA's blocks are contiguous in HBM (camera-major): write them with coalesced 128-bit stores
-    __syncthreads();
-    const int n_blk = end - start;
-    double2* dst = reinterpret_cast<double2*>(Hpl + (size_t)start * 18);
-    const double2* src = reinterpret_cast<const double2*>(stage);
-    for (int i = threadIdx.x; i < n_blk * 9; i += kCamThreads) dst[i] = src[i];
-  }
-  if (COST_ONLY) {
-    double s = warp_sum(v[27]);
-    if (lane == 0) red[wid] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      double t = 0.0;
-      for (int w8 = 0; w8 < kCamThreads / 32; ++w8) t += red[w8];
-      camp[((size_t)c * V.max_chunks + chunk) * kCamVals + 27] = t;
+    // chunk partial: 28 values
+    if (COST_ONLY) {
+      double s = warp_sum(v[27]);
+      if (lane == 0) red[wid] = s;
+      __syncthreads();
+      if (tid == 0) A.camp[(size_t)(A.cam_chunk_off[c] + chunk) * kCamVals + 27] = (red[0] + red[1]) + (red[2] + red[3]);
+    } else {
+      warp_transpose_sum32(v, lane);
+      red[wid * 32 + lane] = v[0];
+      __syncthreads();
+      if (tid < kCamVals)
+        A.camp[(size_t)(A.cam_chunk_off[c] + chunk) * kCamVals + tid] =
+            (red[tid] + red[32 + tid]) + (red[64 + tid] + red[96 + tid]);
     }
-    return;
-  }
-  warp_transpose_sum32(v, lane);
-  red[wid * 32 + lane] = v[0];
-  __syncthreads();
-  if (threadIdx.x < kCamVals) {
-    double t = 0.0;
-#pragma unroll
-    for (int w8 = 0; w8 < kCamThreads / 32; ++w8) t += red[w8 * 32 + threadIdx.x];
-    camp[((size_t)c * V.max_chunks + chunk) * kCamVals + threadIdx.x] = t;
-  }
-}
-
-// Ordered sum of the chunk partials of each camera -> Hpp [Cf][36] (full symmetric), bp [Cf][6]
-// (+ scale-edge part), per-camera cost.
-__device__ __forceinline__ void atomic_max_nonneg(unsigned long long* bits, double v) {
-  atomicMax(bits, (unsigned long long)__double_as_longlong(fabs(v)));  // exact and order-independent
-}
-
-__global__ void ba_cam_finalize(BAView V, const double* __restrict__ camp,
-                                const double* __restrict__ bp_extra, const int* __restrict__ diag_extra,
-                                const double* __restrict__ extra, double* __restrict__ Hpp,
-                                double* __restrict__ bp, double* __restrict__ cam_cost,
-                                unsigned long long* __restrict__ maxdiag_bits) {
-  const int c = blockIdx.x, i = threadIdx.x;
-  if (V.st->done || (Hpp != nullptr && !V.st->dirty)) return;
-  if (i >= kCamVals) return;
-  const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
-  const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
-  double s = 0.0;
-  for (int k = 0; k < n_chunks; ++k) s += camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
-  if (i == 27) { cam_cost[c] = s; return; }
-  const int col = V.cam_col[c];
-  if (col < 0 || Hpp == nullptr) return;
-  if (i >= 21) { bp[6 * col + (i - 21)] = s + bp_extra[6 * col + (i - 21)]; return; }
-  int r = 0, k = i;
-  while (k >= 6 - r) { k -= 6 - r; ++r; }
-  const int cc = r + k;
-  Hpp[36 * col + 6 * r + cc] = s;
-  Hpp[36 * col + 6 * cc + r] = s;
-  if (r == cc) {  // computeLambdaInit: diagonal of the full camera block (projection + scale edges)
-    const int ex = diag_extra[col];
-    atomic_max_nonneg(maxdiag_bits, s + (ex >= 0 ? extra[36 * (size_t)ex + 7 * r] : 0.0));
-  }
-}
-
-// Point-major pass: a quad of 4 lanes per point; lane q takes observations q, q+4, ... of the point,
-// the quad is reduced by two butterfly steps (fixed order -> deterministic).
-constexpr int kPointLanes = 4;
-
-__global__ void __launch_bounds__(256)
-ba_point_pass(BAView V, double* __restrict__ Hll, double* __restrict__ bl,
-              unsigned long long* __restrict__ maxdiag_bits) {
-  if (V.st->done || !V.st->dirty) return;
-  const CamRT* __restrict__ camrt = V.camrt[V.st->cur];
-  const double* __restrict__ pts = V.pts[V.st->cur];
-  const int g = blockIdx.x * blockDim.x + threadIdx.x;
-  const int p = g / kPointLanes, q = g % kPointLanes;
-  const int col = (p < V.P) ? V.pt_col[p] : -1;
-  double acc[9];
-#pragma unroll
-  for (int j = 0; j < 9; ++j) acc[j] = 0.0;
-  if (col >= 0) {
-    const double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
-    const int o_end = V.pt_start[p + 1];
-    for (int o = V.pt_start[p] + q; o < o_end; o += kPointLanes) {
-      const CamRT cam = camrt[V.pm_cam[o]];
-      const double2 uv = V.pm_uv[o];
-      double pc[3], e[2], rho, w;
+    // last chunk of this camera folds the partials (chunk order -> deterministic)
+    __threadfence();
+    __syncthreads();
+    const int n_chunks = A.cam_chunk_off[c + 1] - A.cam_chunk_off[c];
+    if (tid == 0) {
+      const unsigned t = atomicAdd(A.cam_ticket + c, 1u);
+      s_flag = (t == (unsigned)(n_chunks - 1));
+      if (s_flag) A.cam_ticket[c] = 0u;
+    }
+    __syncthreads();
+    if (s_flag) {
+      __threadfence();
+      if (tid < kCamVals) {
+        double s = 0.0;
+        const double* base = A.camp + (size_t)A.cam_chunk_off[c] * kCamVals + tid;
+        for (int k = 0; k < n_chunks; ++k) s += __ldcg(base + (size_t)k * kCamVals);
+        red[tid] = s;
+      }
+      __syncthreads();
+      if (tid == 27) A.cam_cost[c] = red[27];
+      if (!COST_ONLY) {
+        const int col = V.cam_col[c];
+        if (col >= 0 && tid < 27) {
+          if (tid >= 21) {
+            A.bp[6 * col + (tid - 21)] = red[tid] + A.bp_extra[6 * col + (tid - 21)];
+          } else {
+            int r = 0, k = tid;
+            while (k >= 6 - r) { k -= 6 - r; ++r; }
+            const int cc = r + k;
+            A.Hpp[36 * col + 6 * r + cc] = red[tid];
+            A.Hpp[36 * col + 6 * cc + r] = red[tid];
+          }
+        }
+        if (tid == 0) {   // computeLambdaInit: diagonal of the full camera block (projection + scale edges)
+          double m = 0.0;
+          if (col >= 0) {
+            const int ex = A.diag_extra[col];
+            const int dpos[6] = {0, 6, 11, 15, 18, 20};
+            for (int r = 0; r < 6; ++r)
+              m = fmax(m, fabs(red[dpos[r]] + (ex >= 0 ? A.extra[36 * (size_t)ex + 7 * r] : 0.0)));
+          }
+          A.cam_maxd[c] = m;
+        }
+      }
+      take_ticket = !COST_ONLY;
+    }
+  } else {
+    // ------------------------------------------------ point role (never reached when COST_ONLY)
+    // One lane per observation (point-major order): a warp item is a run of whole points with at
+    // most 32 observations (or one long point, strided); per-point sums by a segmented scan over the
+    // lanes -- fixed shape, deterministic.  Cameras come from shared memory when they fit.
+    extern __shared__ __align__(16) double s_cams[];   // [C][12] when A.cams_in_smem
+    const int b = -1 - role;
+    if (A.cams_in_smem) {
+      const double2* src = reinterpret_cast<const double2*>(camrt);
+      double2* dst = reinterpret_cast<double2*>(s_cams);
+      for (int i = tid; i < V.C * 6; i += kLinThreads) dst[i] = src[i];
+      __syncthreads();
+    }
+    const CamRT* __restrict__ cam_tab = A.cams_in_smem ? reinterpret_cast<const CamRT*>(s_cams) : camrt;
+    double m = 0.0;
+    auto accumulate = [&](const CamRT& cam, const double* X, double2 uv, double* acc) {
+      double pc[3], e[2], rho, wgt;
       to_camera(cam, X, pc);
-      if (!(fabs(pc[2]) > 1e-12)) continue;
+      if (!(fabs(pc[2]) > 1e-12)) return;
       residual(pc, V.K, uv.x, uv.y, e);
-      huber(e[0] * e[0] + e[1] * e[1], rho, w);
+      huber(e[0] * e[0] + e[1] * e[1], rho, wgt);
       double Jc[2][6], Jp[2][3];
       jacobians(cam, pc, V.K, Jc, Jp);
-      const double w0[3] = {w * Jp[0][0], w * Jp[0][1], w * Jp[0][2]};
-      const double w1[3] = {w * Jp[1][0], w * Jp[1][1], w * Jp[1][2]};
+      const double w0[3] = {wgt * Jp[0][0], wgt * Jp[0][1], wgt * Jp[0][2]};
+      const double w1[3] = {wgt * Jp[1][0], wgt * Jp[1][1], wgt * Jp[1][2]};
       acc[0] += w0[0] * Jp[0][0] + w1[0] * Jp[1][0];
       acc[1] += w0[0] * Jp[0][1] + w1[0] * Jp[1][1];
       acc[2] += w0[0] * Jp[0][2] + w1[0] * Jp[1][2];
@@ -239,30 +331,95 @@ ba_point_pass(BAView V, double* __restrict__ Hll, double* __restrict__ bl,
       acc[5] += w0[2] * Jp[0][2] + w1[2] * Jp[1][2];
 #pragma unroll
       for (int j = 0; j < 3; ++j) acc[6 + j] -= w0[j] * e[0] + w1[j] * e[1];
+    };
+    auto store_point = [&](int key, const double* acc) {
+      const int col = V.pt_col[key];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) A.Hll[6 * (size_t)col + j] = acc[j];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) A.bl[3 * (size_t)col + j] = acc[6 + j];
+      m = fmax(m, fmax(fabs(acc[0]), fmax(fabs(acc[3]), fabs(acc[5]))));
+    };
+    // regular items, software-pipelined like the camera role: slot indices two items ahead, the
+    // point coordinates one item ahead (slots are at fixed addresses: no header load in the chain)
+    const int item0 = (b * (kLinThreads / 32) + wid) * kPtItemsPerWarp;
+    const int n_it = max(0, min(kPtItemsPerWarp, A.n_pt_items - item0));
+    int p_c = -1, ci_c = 0, p_n = -1, ci_n = 0;
+    double2 uv_c = make_double2(0.0, 0.0), uv_n = uv_c;
+    double Xc[3] = {0.0, 0.0, 1.0};
+    if (n_it > 0) {
+      const size_t s0 = (size_t)item0 * 32 + lane;
+      p_c = A.px_pt[s0]; ci_c = A.px_cam[s0]; uv_c = A.px_uv[s0];
+      if (n_it > 1) { p_n = A.px_pt[s0 + 32]; ci_n = A.px_cam[s0 + 32]; uv_n = A.px_uv[s0 + 32]; }
+      if (p_c >= 0) { Xc[0] = pts[3 * p_c]; Xc[1] = pts[3 * p_c + 1]; Xc[2] = pts[3 * p_c + 2]; }
     }
-  }
+#pragma unroll 1
+    for (int it = 0; it < n_it; ++it) {
+      // issue: coordinates of item it+1 (its indices arrived during the previous item), indices of it+2
+      double Xn[3] = {0.0, 0.0, 1.0};
+      if (p_n >= 0) { Xn[0] = pts[3 * p_n]; Xn[1] = pts[3 * p_n + 1]; Xn[2] = pts[3 * p_n + 2]; }
+      int p_2 = -1, ci_2 = 0;
+      double2 uv_2 = make_double2(0.0, 0.0);
+      if (it + 2 < n_it) {
+        const size_t s2 = (size_t)(item0 + it + 2) * 32 + lane;
+        p_2 = A.px_pt[s2]; ci_2 = A.px_cam[s2]; uv_2 = A.px_uv[s2];
+      }
+      double acc[9];
 #pragma unroll
-  for (int j = 0; j < 9; ++j) {
-    acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
-    acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
-  }
-  double m = 0.0;
-  if (col >= 0 && q == 0) {
+      for (int j = 0; j < 9; ++j) acc[j] = 0.0;
+      const int key = p_c;
+      if (key >= 0) accumulate(cam_tab[ci_c], Xc, uv_c, acc);
+      // inclusive segmented scan; the last lane of a segment holds the point's sums
 #pragma unroll
-    for (int j = 0; j < 6; ++j) Hll[6 * (size_t)col + j] = acc[j];
+      for (int d = 1; d < 32; d <<= 1) {
+        const int ku = __shfl_up_sync(0xffffffffu, key, d);
+        const bool take = (lane >= d) && (ku == key) && (key >= 0);
 #pragma unroll
-    for (int j = 0; j < 3; ++j) bl[3 * (size_t)col + j] = acc[6 + j];
-    m = fmax(fabs(acc[0]), fmax(fabs(acc[3]), fabs(acc[5])));
+        for (int j = 0; j < 9; ++j) {
+          const double u = __shfl_up_sync(0xffffffffu, acc[j], d);
+          if (take) acc[j] += u;
+        }
+      }
+      const int kn = __shfl_down_sync(0xffffffffu, key, 1);
+      if ((key >= 0) && (lane == 31 || kn != key)) store_point(key, acc);
+      p_c = p_n; ci_c = ci_n; uv_c = uv_n; Xc[0] = Xn[0]; Xc[1] = Xn[1]; Xc[2] = Xn[2];
+      p_n = p_2; ci_n = ci_2; uv_n = uv_2;
+    }
+    // long points (> 32 observations): one warp each, strided, plain butterfly
+    for (int li = b * (kLinThreads / 32) + wid; li < A.n_long; li += A.nB * (kLinThreads / 32)) {
+      const int2 w = A.long_item[li];
+      double acc[9];
+#pragma unroll
+      for (int j = 0; j < 9; ++j) acc[j] = 0.0;
+      const int key = A.pm_pt[w.x];
+      const double X[3] = {pts[3 * key], pts[3 * key + 1], pts[3 * key + 2]};
+      for (int o = w.x + lane; o < w.x + w.y; o += 32) accumulate(cam_tab[V.pm_cam[o]], X, V.pm_uv[o], acc);
+#pragma unroll
+      for (int j = 0; j < 9; ++j) acc[j] = warp_sum(acc[j]);
+      if (lane == 0) store_point(key, acc);
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) red[wid] = m;
+    __syncthreads();
+    if (tid == 0) A.pt_maxd[b] = fmax(fmax(red[0], red[1]), fmax(red[2], red[3]));
+    take_ticket = true;
   }
-  // computeLambdaInit: max |diag Hll|; CTA max, then ONE order-independent atomic per CTA
-  // (same-address atomics serialise in L2: one per warp cost more than the whole pass)
-  __shared__ double smax[8];
-  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
-  if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    for (int w = 1; w < 8; ++w) m = fmax(m, smax[w]);
-    if (m > 0.0) atomic_max_nonneg(maxdiag_bits, m);
+
+  if (!COST_ONLY) {
+    // the last CTA of the grid (camera finalisers + point blocks) runs the controller
+    if (!take_ticket) return;     // uniform per CTA
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned t = atomicAdd(A.lin_ticket, 1u);
+      s_flag = (t == (unsigned)(V.C + A.nB - 1));
+      if (s_flag) *A.lin_ticket = 0u;
+    }
+    __syncthreads();
+    if (s_flag) {
+      __threadfence();
+      lin_controller(V, A, red);
+    }
   }
 }
 
