@@ -37,4 +37,12 @@ for name in which:
     t = time.time(); tr = eng.trial(1e-5 * lin["max_diag"]); torch.cuda.synchronize(); tt = time.time() - t
     print("  linearize %.3f ms (%.1f GB/s algorithmic), trial %.3f ms, pcg iters %d status %d" % (
         tl * 1e3, p.linearize_bytes() / tl / 1e9, tt * 1e3, tr["pcg_iters"], tr["pcg_status"]))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    eng.trial(1e-5 * lin["max_diag"])
+    for stage in ("linearize", "schur", "trial"):
+        ms = eng.time_stage(stage, 6, flush)[1:]
+        msw = eng.time_stage(stage, 6, None)[1:]
+        extra = " (%.1f GB/s algorithmic cold)" % (p.linearize_bytes() / (np.median(ms) * 1e-3) / 1e9) if stage == "linearize" else ""
+        print("  %-9s cold %.1f us  warm %.1f us%s" % (stage, np.median(ms) * 1e3, np.median(msw) * 1e3, extra))
+    del flush
     eng.close()

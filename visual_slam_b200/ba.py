@@ -82,6 +82,17 @@ class BAEngine:
             _cabi.check(_cabi.lib().vslam_ba_linearize(self._h, out, _cabi.stream_ptr()))
         return {"cost": out[0], "max_diag": out[1]}
 
+    def time_stage(self, stage, reps=5, flush=None):
+        """CUDA-event times (ms) of `reps` launches of one stage: "linearize" (the fused kernel alone),
+        "schur" or "trial"; `flush` is an optional device tensor overwritten before each launch (L2)."""
+        code = {"linearize": 0, "schur": 1, "trial": 2}[stage]
+        out = (C.c_float * reps)()
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().vslam_ba_time_stage(
+                self._h, code, int(reps), _cabi.ptr(flush) if flush is not None else None,
+                flush.numel() * flush.element_size() if flush is not None else 0, out, _cabi.stream_ptr()))
+        return list(out)
+
     def trial(self, lam):
         out = (C.c_double * 4)()
         with torch.cuda.device(self.device):

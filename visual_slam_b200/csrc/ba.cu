@@ -12,82 +12,6 @@
 
 namespace vslam {
 
-// Scale edges (EdgeSBAScale + DCS, LocalBA.py:115-131).  One CTA: (1) thread per edge evaluates
-// residual / weight / direction, (2) thread per extra S block and per free camera gathers the
-// contributions of its incident edges in edge order (CSR built on the host) -> deterministic.
-struct ScaleView {
-  int E, n_extra, Cf;
-  const LMState* st; const double* cams2[2];
-  const int* sa; const int* sb; const double* meas; const int* cam_col;
-  const int* inc_start; const int* inc_edge;   // per free camera: incident edge ids (ascending)
-  const int* extra_a; const int* extra_b;      // free-camera columns of each extra block (a <= b)
-  double* edge_w; double* edge_es; double* edge_u;  // [E], [E], [E][3]
-};
-
-__global__ void __launch_bounds__(256)
-ba_scale_edges(ScaleView V, int cost_only, double* __restrict__ extra,
-               double* __restrict__ bp_extra, double* __restrict__ scale_cost,
-               unsigned long long* __restrict__ maxdiag_bits) {
-  __shared__ double red[8];
-  if (V.st->done || (!cost_only && !V.st->dirty)) return;
-  const double* __restrict__ cams = V.cams2[cost_only ? (V.st->cur ^ 1) : V.st->cur];
-  double c[1] = {0.0};
-  for (int k = threadIdx.x; k < V.E; k += 256) {
-    const double* ta = cams + 7 * V.sa[k] + 4;
-    const double* tb = cams + 7 * V.sb[k] + 4;
-    const double d[3] = {tb[0] - ta[0], tb[1] - ta[1], tb[2] - ta[2]};
-    const double nrm = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
-    const double es = V.meas[k] - nrm;
-    double rho, w;
-    dcs(es * es, rho, w);
-    c[0] += rho;
-    if (!cost_only) {
-      V.edge_w[k] = w; V.edge_es[k] = es;
-      V.edge_u[3 * k] = d[0] / nrm; V.edge_u[3 * k + 1] = d[1] / nrm; V.edge_u[3 * k + 2] = d[2] / nrm;
-    }
-  }
-  block_reduce<1, 256>(c, red);
-  if (threadIdx.x == 0) {
-    *scale_cost = c[0];
-    if (!cost_only) *maxdiag_bits = 0ull;
-  }
-  if (cost_only) return;
-  __threadfence_block();
-  __syncthreads();
-  for (int x = threadIdx.x; x < V.n_extra; x += 256) {
-    const int a = V.extra_a[x], b = V.extra_b[x];
-    double h[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-    for (int q = V.inc_start[a]; q < V.inc_start[a + 1]; ++q) {
-      const int k = V.inc_edge[q];
-      const int ca = V.cam_col[V.sa[k]], cb = V.cam_col[V.sb[k]];
-      double sgn;
-      if (a == b) sgn = 1.0;                                         // diagonal: every incident edge
-      else if ((ca == a && cb == b) || (ca == b && cb == a)) sgn = -1.0;  // off-diagonal: edges a-b
-      else continue;
-      const double w = V.edge_w[k];
-      const double* u = V.edge_u + 3 * k;
-      for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) h[3 * i + j] += sgn * w * u[i] * u[j];
-    }
-    double* o = extra + 36 * (size_t)x;
-    for (int i = 0; i < 36; ++i) o[i] = 0.0;
-    for (int i = 0; i < 3; ++i)
-      for (int j = 0; j < 3; ++j) o[6 * i + j] = h[3 * i + j];
-  }
-  for (int col = threadIdx.x; col < V.Cf; col += 256) {
-    double g[3] = {0, 0, 0};
-    for (int q = V.inc_start[col]; q < V.inc_start[col + 1]; ++q) {
-      const int k = V.inc_edge[q];
-      // d e / d t_a = +u, d e / d t_b = -u ;  b += -w J e
-      const double sgn = (V.cam_col[V.sa[k]] == col) ? -1.0 : 1.0;
-      const double f = sgn * V.edge_w[k] * V.edge_es[k];
-      g[0] += f * V.edge_u[3 * k]; g[1] += f * V.edge_u[3 * k + 1]; g[2] += f * V.edge_u[3 * k + 2];
-    }
-    double* o = bp_extra + 6 * col;
-    o[0] = g[0]; o[1] = g[1]; o[2] = g[2]; o[3] = 0.0; o[4] = 0.0; o[5] = 0.0;
-  }
-}
-
 // Controller after a trial: cost of the trial state, computeScale, then the Levenberg-Marquardt
 // accept / reject logic of g2o (OptimizationAlgorithmLevenberg::solve) entirely on the device.
 __global__ void __launch_bounds__(256)
@@ -195,18 +119,17 @@ struct BA {
   DevBuf<int> cam_col, pt_col, cm_start, cm_pt, cm_pm, cm_src, pt_start, pm_cam, pm_src;
   DevBuf<int> item_a, item_b, unit_start, unit_len, seg_a, seg_b, seg_unit_start, seg_extra_idx;
   DevBuf<int> sa, sb, diag_extra, inc_start, inc_edge, extra_a, extra_b;
-  DevBuf<int> lin_role, wk_cam, wk_start, wk_chunk, cam_chunk_off;   // fused linearisation work lists
+  // fused linearisation work lists
+  DevBuf<LinWork> lin_work, cam_work;
   DevBuf<unsigned> cam_ticket, lin_ticket;
-  DevBuf<int2> long_item;
-  DevBuf<int> pm_pt, px_pt, px_cam, px_src;
-  DevBuf<double2> px_uv;
-  int n_pt_items = 0, n_long = 0, cams_in_smem = 0;
+  DevBuf<int> pw_first, item_row, ell_pt, ell_cam, ell_src;
+  DevBuf<double2> ell_uv;
+  int n_pt_warps = 0, n_ell_rows = 0, cams_in_smem = 0, lin_ctas = 0;
   size_t lin_smem = 0;
-  DevBuf<double> cam_maxd, pt_maxd;
+  DevBuf<double> pt_maxd;
   int lin_nA = 0, lin_nB = 0;
   DevBuf<double> edge_w, edge_es, edge_u;
-  DevBuf<unsigned long long> maxdiag;
-  DevBuf<double2> cm_uv, pm_uv;
+  DevBuf<double2> cm_uv;
   // state: [0] current, [1] trial
   DevBuf<double> cams[2], pts[2], scale_meas;
   DevBuf<CamRT> camrt[2];
@@ -233,19 +156,20 @@ struct BA {
     for (int i = 0; i < 2; ++i) { V.cams[i] = cams[i].p; V.pts[i] = pts[i].p; V.camrt[i] = camrt[i].p; }
     V.cam_col = cam_col.p; V.pt_col = pt_col.p; V.cm_start = cm_start.p; V.cm_pt = cm_pt.p;
     V.cm_pm = cm_pm.p; V.cm_uv = cm_uv.p; V.pt_start = pt_start.p; V.pm_cam = pm_cam.p;
-    V.pm_uv = pm_uv.p;
     return V;
   }
   LinArgs lin_args() const {
     LinArgs A;
-    A.nA = lin_nA; A.nB = lin_nB; A.role = lin_role.p; A.wk_cam = wk_cam.p; A.wk_start = wk_start.p;
-    A.wk_chunk = wk_chunk.p; A.cam_chunk_off = cam_chunk_off.p; A.cam_ticket = cam_ticket.p;
-    A.lin_ticket = lin_ticket.p; A.Hpl = Hpl.p; A.camp = camp.p; A.Hpp = Hpp.p; A.bp = bp.p;
-    A.cam_cost = cam_cost.p; A.cam_maxd = cam_maxd.p; A.Hll = Hll.p; A.bl = bl.p; A.pt_maxd = pt_maxd.p;
+    A.work = lin_work.p; A.cam_work = cam_work.p;
+    A.n_pt_ctas = lin_nB; A.n_pt_warps = n_pt_warps; A.n_tickets = C + lin_nB + (E > 0 ? 1 : 0);
+    A.cams_in_smem = cams_in_smem; A.has_scale = E > 0 ? 1 : 0;
+    A.pw_first = pw_first.p; A.item_row = item_row.p; A.ell_pt = ell_pt.p; A.ell_cam = ell_cam.p;
+    A.ell_uv = ell_uv.p;
+    A.cam_ticket = cam_ticket.p; A.lin_ticket = lin_ticket.p;
+    A.Hpl = Hpl.p; A.camp = camp.p; A.Hpp = Hpp.p; A.bp = bp.p; A.cam_cost = cam_cost.p;
+    A.Hll = Hll.p; A.bl = bl.p; A.pt_maxd = pt_maxd.p;
     A.bp_extra = bp_extra.p; A.diag_extra = diag_extra.p; A.extra = extra.p; A.scale_cost = scale_cost.p;
     A.st_rw = lm.p;
-    A.n_pt_items = n_pt_items; A.px_pt = px_pt.p; A.px_cam = px_cam.p; A.px_uv = px_uv.p;
-    A.n_long = n_long; A.long_item = long_item.p; A.pm_pt = pm_pt.p; A.cams_in_smem = cams_in_smem;
     return A;
   }
   ScaleView scale_view() const {
@@ -254,6 +178,7 @@ struct BA {
     V.E = E; V.n_extra = n_extra; V.Cf = Cf; V.sa = sa.p; V.sb = sb.p; V.meas = scale_meas.p;
     V.cam_col = cam_col.p; V.inc_start = inc_start.p; V.inc_edge = inc_edge.p; V.extra_a = extra_a.p;
     V.extra_b = extra_b.p; V.edge_w = edge_w.p; V.edge_es = edge_es.p; V.edge_u = edge_u.p;
+    V.extra = extra.p; V.bp_extra = bp_extra.p; V.scale_cost = scale_cost.p;
     return V;
   }
   ~BA() {
@@ -389,60 +314,79 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   }
   B.n_extra = n_extra;
   B.n_sp = (P + 255) / 256;
-  // fused linearisation: camera chunks (every camera owns at least one, possibly empty) and point
-  // blocks, interleaved in proportion so that both roles are resident at the same time
-  std::vector<int> wk_cam, wk_start, wk_chunk, cam_chunk_off(C + 1, 0), lin_role;
-  for (int c = 0; c < C; ++c) {
-    const int n_obs_c = cm_start[c + 1] - cm_start[c];
-    const int nch = std::max(1, (n_obs_c + kLinChunk - 1) / kLinChunk);
-    cam_chunk_off[c + 1] = cam_chunk_off[c] + nch;
-    for (int k = 0; k < nch; ++k) {
-      wk_cam.push_back(c); wk_start.push_back(cm_start[c] + k * kLinChunk); wk_chunk.push_back(k);
-    }
-  }
-  B.lin_nA = (int)wk_cam.size();
-  // point-role work items: runs of whole free points with <= 32 observations in total, laid out in
-  // 32 padded slots each; points with more observations go to the long list
-  std::vector<int2> long_item;
-  std::vector<int> pm_pt(N), px_pt, px_cam, px_src;
-  for (int p = 0; p < P; ++p)
-    for (int i = pt_start[p]; i < pt_start[p + 1]; ++i) pm_pt[i] = p;
+  // fused linearisation: camera chunks (every camera owns at least one, possibly empty), point blocks
+  // and the scale-edge CTA, interleaved in proportion so that all roles are resident at the same time
+  std::vector<LinWork> cam_work, lin_work;
   {
-    int fill = 32;   // slots used in the open item (32 = none open)
-    for (int p = 0; p < P; ++p) {
-      const int np = pt_start[p + 1] - pt_start[p];
-      if (pt_col[p] < 0 || np == 0) continue;
-      if (np > 32) { long_item.push_back(make_int2(pt_start[p], np)); continue; }
-      if (fill + np > 32) {   // open a new item
-        px_pt.resize(px_pt.size() + 32, -1); px_cam.resize(px_cam.size() + 32, 0); px_src.resize(px_src.size() + 32, -1);
-        fill = 0;
+    int row = 0;
+    for (int c = 0; c < C; ++c) {
+      const int n_obs_c = cm_start[c + 1] - cm_start[c];
+      const int nch = std::max(1, (n_obs_c + kLinChunk - 1) / kLinChunk);
+      for (int k = 0; k < nch; ++k) {
+        LinWork w{};
+        w.kind = 0; w.cam = c; w.start = cm_start[c] + k * kLinChunk;
+        w.end = std::min(cm_start[c + 1], w.start + kLinChunk);
+        w.row = row + k; w.n_chunks = nch; w.first_row = row; w.col = cam_col[c];
+        cam_work.push_back(w);
       }
-      const size_t base = px_pt.size() - 32 + fill;
-      for (int i = 0; i < np; ++i) {
-        px_pt[base + i] = p; px_cam[base + i] = pm_cam[pt_start[p] + i]; px_src[base + i] = pm_src[pt_start[p] + i];
-      }
-      fill += np;
+      row += nch;
     }
   }
-  B.n_pt_items = (int)(px_pt.size() / 32);
-  B.n_long = (int)long_item.size();
-  const int items_per_cta = (kLinThreads / 32) * kPtItemsPerWarp;
-  B.lin_nB = (B.n_pt_items + items_per_cta - 1) / items_per_cta;
-  if (B.n_long > 0) B.lin_nB = std::max(B.lin_nB, std::min(B.n_long, 4 * std::max(1, sm_count())));
+  B.lin_nA = (int)cam_work.size();
+  // point role, ELL layout: free points with observations sorted by degree (descending, stable), 32
+  // per item (one per lane); row j of an item holds the j-th observation of each of its points
+  std::vector<int> pw_first, item_row, ell_pt, ell_cam, ell_src;
+  {
+    std::vector<int> fp;
+    for (int p = 0; p < P; ++p)
+      if (pt_col[p] >= 0 && pt_start[p + 1] > pt_start[p]) fp.push_back(p);
+    std::stable_sort(fp.begin(), fp.end(), [&](int a, int b) {
+      return pt_start[a + 1] - pt_start[a] > pt_start[b + 1] - pt_start[b];
+    });
+    const int n_it = ((int)fp.size() + 31) / 32;
+    item_row.assign(n_it + 1, 0);
+    ell_pt.assign((size_t)n_it * 32, -1);
+    for (int it = 0; it < n_it; ++it) {
+      const int p0 = fp[(size_t)it * 32];
+      item_row[it + 1] = item_row[it] + (pt_start[p0 + 1] - pt_start[p0]);
+    }
+    ell_cam.assign((size_t)item_row[n_it] * 32, -1);
+    ell_src.assign((size_t)item_row[n_it] * 32, -1);
+    for (size_t q = 0; q < fp.size(); ++q) {
+      const int p = fp[q], it = (int)(q / 32), l = (int)(q % 32);
+      ell_pt[(size_t)it * 32 + l] = p;
+      for (int j = 0; j < pt_start[p + 1] - pt_start[p]; ++j) {
+        ell_cam[((size_t)item_row[it] + j) * 32 + l] = pm_cam[pt_start[p] + j];
+        ell_src[((size_t)item_row[it] + j) * 32 + l] = pm_src[pt_start[p] + j];
+      }
+    }
+    // warps take runs of items of about kPtRowsPerWarp rows
+    pw_first.push_back(0);
+    int rows = 0;
+    for (int it = 0; it < n_it; ++it) {
+      rows += item_row[it + 1] - item_row[it];
+      if (rows >= kPtRowsPerWarp || it + 1 == n_it) { pw_first.push_back(it + 1); rows = 0; }
+    }
+    B.n_pt_warps = (int)pw_first.size() - 1;
+    B.n_ell_rows = item_row[n_it];
+  }
+  B.lin_nB = (B.n_pt_warps + kLinWarps - 1) / kLinWarps;
   B.cams_in_smem = (C <= kCamSmemMax) ? 1 : 0;
-  B.lin_smem = B.cams_in_smem ? (size_t)C * sizeof(CamRT) : 0;
+  B.lin_smem = std::max((size_t)kLinWarps * kStageDoubles * sizeof(double),
+                        B.cams_in_smem ? (size_t)C * kCamTabStride * sizeof(double) : 0);
   BA_TRY(cudaFuncSetAttribute(ba_linearize_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)(kCamSmemMax * sizeof(CamRT))));
+                              (int)(kCamSmemMax * kCamTabStride * sizeof(double))));
   {
+    if (E > 0) { LinWork w{}; w.kind = 2; lin_work.push_back(w); }
     const long long tot = (long long)B.lin_nA + B.lin_nB;
-    lin_role.resize(tot);
     int a = 0, b = 0;
     for (long long i = 0; i < tot; ++i) {
       // point block when the running share of point blocks falls behind
       const bool want_b = (long long)(b + 1) * tot <= (i + 1) * (long long)B.lin_nB;
-      if ((want_b && b < B.lin_nB) || a >= B.lin_nA) lin_role[i] = -1 - b++;
-      else lin_role[i] = a++;
+      if ((want_b && b < B.lin_nB) || a >= B.lin_nA) { LinWork w{}; w.kind = 1; w.cam = b++; lin_work.push_back(w); }
+      else lin_work.push_back(cam_work[a++]);
     }
+    B.lin_ctas = (int)lin_work.size();
   }
   // uploads
   BA_TRY(B.cam_col.upload(cam_col)); BA_TRY(B.pt_col.upload(pt_col));
@@ -455,17 +399,16 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.sa.upload(std::vector<int>(sa, sa + E))); BA_TRY(B.sb.upload(std::vector<int>(sb, sb + E)));
   BA_TRY(B.inc_start.upload(inc_start)); BA_TRY(B.inc_edge.upload(inc_edge));
   BA_TRY(B.extra_a.upload(extra_a)); BA_TRY(B.extra_b.upload(extra_b));
-  BA_TRY(B.edge_w.alloc(E)); BA_TRY(B.edge_es.alloc(E)); BA_TRY(B.edge_u.alloc((size_t)E * 3)); BA_TRY(B.maxdiag.alloc(1));
+  BA_TRY(B.edge_w.alloc(E)); BA_TRY(B.edge_es.alloc(E)); BA_TRY(B.edge_u.alloc((size_t)E * 3));
   BA_TRY(B.diag_extra.upload(diag_extra));
-  BA_TRY(B.lin_role.upload(lin_role)); BA_TRY(B.wk_cam.upload(wk_cam)); BA_TRY(B.wk_start.upload(wk_start));
-  BA_TRY(B.wk_chunk.upload(wk_chunk)); BA_TRY(B.cam_chunk_off.upload(cam_chunk_off));
-  BA_TRY(B.long_item.upload(long_item)); BA_TRY(B.pm_pt.upload(pm_pt)); BA_TRY(B.px_pt.upload(px_pt));
-  BA_TRY(B.px_cam.upload(px_cam)); BA_TRY(B.px_src.upload(px_src)); BA_TRY(B.px_uv.alloc(px_pt.size()));
-  BA_TRY(B.cam_ticket.alloc(C)); BA_TRY(B.lin_ticket.alloc(1)); BA_TRY(B.cam_maxd.alloc(C));
+  BA_TRY(B.lin_work.upload(lin_work)); BA_TRY(B.cam_work.upload(cam_work));
+  BA_TRY(B.pw_first.upload(pw_first)); BA_TRY(B.item_row.upload(item_row)); BA_TRY(B.ell_pt.upload(ell_pt));
+  BA_TRY(B.ell_cam.upload(ell_cam)); BA_TRY(B.ell_src.upload(ell_src)); BA_TRY(B.ell_uv.alloc(ell_cam.size()));
+  BA_TRY(B.cam_ticket.alloc(C)); BA_TRY(B.lin_ticket.alloc(1));
   BA_TRY(B.pt_maxd.alloc(std::max(B.lin_nB, 1)));
   BA_TRY(cudaMemset(B.cam_ticket.p, 0, (size_t)C * sizeof(unsigned)));
   BA_TRY(cudaMemset(B.lin_ticket.p, 0, sizeof(unsigned)));
-  BA_TRY(B.cm_uv.alloc(N)); BA_TRY(B.pm_uv.alloc(N)); BA_TRY(B.scale_meas.alloc(E));
+  BA_TRY(B.cm_uv.alloc(N)); BA_TRY(B.scale_meas.alloc(E));
   for (int s = 0; s < 2; ++s) {
     BA_TRY(B.cams[s].alloc((size_t)C * 7)); BA_TRY(B.pts[s].alloc((size_t)P * 3)); BA_TRY(B.camrt[s].alloc(C));
   }
@@ -535,9 +478,8 @@ static int ba_set_state(BA& B, const double* cams, const double* pts, const doub
   if (B.N) {
     const int blocks = (B.N + 255) / 256;
     ba_gather_uv<<<blocks, 256, 0, st>>>(B.N, B.cm_src.p, reinterpret_cast<const double2*>(uv), B.cm_uv.p);
-    ba_gather_uv<<<blocks, 256, 0, st>>>(B.N, B.pm_src.p, reinterpret_cast<const double2*>(uv), B.pm_uv.p);
-    const int nx = B.n_pt_items * 32;
-    if (nx) ba_gather_uv<<<(nx + 255) / 256, 256, 0, st>>>(nx, B.px_src.p, reinterpret_cast<const double2*>(uv), B.px_uv.p);
+    const int nx = B.n_ell_rows * 32;
+    if (nx) ba_gather_uv<<<(nx + 255) / 256, 256, 0, st>>>(nx, B.ell_src.p, reinterpret_cast<const double2*>(uv), B.ell_uv.p);
   }
   if (B.C) ba_prepare_cams<<<(B.C + 127) / 128, 128, 0, st>>>(B.cams[0].p, B.camrt[0].p, B.C);
   return check_launch("ba_set_state");
@@ -553,14 +495,12 @@ static int ba_sync_state(BA& B, cudaStream_t st) {
 static int enqueue_linearize(BA& B, cudaStream_t st) {
   const BAView V = B.view();
   dim3 grid(B.max_chunks, B.C);
-  if (B.E) ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 0, B.extra.p, B.bp_extra.p, B.scale_cost.p, B.maxdiag.p);
-  ba_linearize_kernel<false><<<B.lin_nA + B.lin_nB, kLinThreads, B.lin_smem, st>>>(V, B.lin_args());
+  ba_linearize_kernel<false><<<B.lin_ctas, kLinThreads, B.lin_smem, st>>>(V, B.lin_args(), B.scale_view());
   return check_launch("ba_linearize");
 }
 
-// One LM trial at LMState::lambda: solve (H + lambda I) d = b through Schur + PCG, write the trial
-// state, evaluate it, then the controller decides (accept / reject / terminate) on the device.
-static int enqueue_trial(BA& B, cudaStream_t st) {
+// Schur complement of the damped system: Hinv, E = Hpl Hinv, bhat, S (sorted-segment reduction).
+static int enqueue_schur(BA& B, cudaStream_t st) {
   const BAView V = B.view();
   const LMState* lm = B.lm.p;
   dim3 grid(B.max_chunks, B.C);
@@ -575,10 +515,23 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
   } else if (B.n) {
     BA_TRY(cudaMemcpyAsync(B.bhat.p, B.bp.p, (size_t)B.n * sizeof(double), cudaMemcpyDeviceToDevice, st));
   }
-  if (B.n) {
+  if (B.n)
     ba_schur_finalize<<<(B.n_seg * 36 + 127) / 128, 128, 0, st>>>(
         lm, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
         B.extra.p, B.seg_extra_idx.p, B.S.p);
+  return check_launch("ba_schur");
+}
+
+// One LM trial at LMState::lambda: solve (H + lambda I) d = b through Schur + PCG, write the trial
+// state, evaluate it, then the controller decides (accept / reject / terminate) on the device.
+static int enqueue_trial(BA& B, cudaStream_t st) {
+  const BAView V = B.view();
+  dim3 grid(B.max_chunks, B.C);
+  {
+    const int rc = enqueue_schur(B, st);
+    if (rc) return rc;
+  }
+  if (B.n) {
     BA_TRY(cudaMemsetAsync(B.bar.p, 0, sizeof(unsigned), st));
     BA_TRY(cudaMemsetAsync(B.pcg_flags.p, 0, 4 * sizeof(int), st));
     PcgArgs A{};
@@ -598,8 +551,8 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
   if (B.Pf) ba_backsub_cam<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.dp.p, B.tmp3.p);
   if (B.P) ba_backsub_pt<<<B.n_sp, 256, 0, st>>>(V, B.tmp3.p, B.Hinv.p, B.bl.p, B.dl.p, B.scale_partial.p);
   ba_update_cams<<<(B.C + 127) / 128, 128, 0, st>>>(V, B.dp.p);
-  ba_linearize_kernel<true><<<B.lin_nA, kLinThreads, 0, st>>>(V, B.lin_args());
-  if (B.E) ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 1, B.extra.p, B.bp_extra.p, B.scale_cost.p, B.maxdiag.p);
+  ba_linearize_kernel<true><<<B.lin_nA, kLinThreads, 0, st>>>(V, B.lin_args(), B.scale_view());
+  if (B.E) ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 1);
   ba_trial_controller<<<1, 256, 0, st>>>(B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0,
                                          B.scale_partial.p, B.n, B.dp.p, B.bp.p, B.pcg_flags.p + 1,
                                          B.pcg_flags.p + 2);
@@ -745,6 +698,38 @@ extern "C" int vslam_ba_linearize(vslam_ba* h, double* out2, void* stream) {
   if (rc) return rc;
   if (out2) { out2[0] = B.lm_host->cur_cost; out2[1] = B.lm_host->max_diag; }
   return VSLAM_OK;
+}
+
+// Times `reps` launches of one stage with CUDA events on `stream` (the stream the kernels run on):
+// stage 0 = the fused linearisation kernel alone (buildSystem), 1 = Schur complement assembly
+// (point inverse + E + units + finalize), 2 = one whole LM trial.  Before every launch flush_bytes of
+// flush_buf are overwritten (L2 flush; skipped when null).  ms_out[reps] (host).  Synchronises.
+extern "C" int vslam_ba_time_stage(vslam_ba* h, int stage, int reps, void* flush_buf, int64_t flush_bytes,
+                                   float* ms_out, void* stream) {
+  if (!h || reps < 1 || !ms_out || stage < 0 || stage > 2) return VSLAM_ERR_BAD_ARG;
+  BA& B = h->impl;
+  if (B.C == 0) return VSLAM_ERR_BAD_ARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaEvent_t e0, e1;
+  BA_TRY(cudaEventCreate(&e0)); BA_TRY(cudaEventCreate(&e1));
+  int rc = VSLAM_OK;
+  for (int r = 0; r < reps && rc == VSLAM_OK; ++r) {
+    ba_lm_poke<<<1, 1, 0, st>>>(B.lm.p, 0, 0.0);
+    if (stage != 0) rc = enqueue_linearize(B, st);
+    if (flush_buf && flush_bytes > 0) cudaMemsetAsync(flush_buf, r & 0xff, (size_t)flush_bytes, st);
+    cudaEventRecord(e0, st);
+    if (rc == VSLAM_OK) {
+      if (stage == 0) rc = enqueue_linearize(B, st);
+      else if (stage == 1) rc = enqueue_schur(B, st);
+      else rc = enqueue_trial(B, st);
+    }
+    cudaEventRecord(e1, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { set_cuda_error(e, "vslam_ba_time_stage"); rc = VSLAM_ERR_CUDA; break; }
+    cudaEventElapsedTime(&ms_out[r], e0, e1);
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return rc;
 }
 
 extern "C" int vslam_ba_trial(vslam_ba* h, double lambda, double* out4, void* stream) {

@@ -80,54 +80,206 @@ __device__ __forceinline__ void warp_transpose_sum32(double (&v)[32], int lane) 
   }
 }
 
+// ---- scale edges (EdgeSBAScale + DCS, LocalBA.py:115-131) -----------------------------------
+// One CTA: (1) thread per edge evaluates residual / weight / direction, (2) thread per extra S block
+// and per free camera gathers the contributions of its incident edges in edge order (CSR built on the
+// host) -> deterministic.
+struct ScaleView {
+  int E, n_extra, Cf;
+  const LMState* st; const double* cams2[2];
+  const int* sa; const int* sb; const double* meas; const int* cam_col;
+  const int* inc_start; const int* inc_edge;   // per free camera: incident edge ids (ascending)
+  const int* extra_a; const int* extra_b;      // free-camera columns of each extra block (a <= b)
+  double* edge_w; double* edge_es; double* edge_u;  // [E], [E], [E][3]
+  double* extra; double* bp_extra; double* scale_cost;
+};
+
+template <int THREADS>
+__device__ __forceinline__ void scale_edges_body(const ScaleView& V, bool cost_only, double* red /*[THREADS/32]*/) {
+  const double* __restrict__ cams = V.cams2[cost_only ? (V.st->cur ^ 1) : V.st->cur];
+  double c[1] = {0.0};
+  for (int k = threadIdx.x; k < V.E; k += THREADS) {
+    const double* ta = cams + 7 * V.sa[k] + 4;
+    const double* tb = cams + 7 * V.sb[k] + 4;
+    const double d[3] = {tb[0] - ta[0], tb[1] - ta[1], tb[2] - ta[2]};
+    const double nrm = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    const double es = V.meas[k] - nrm;
+    double rho, w;
+    dcs(es * es, rho, w);
+    c[0] += rho;
+    if (!cost_only) {
+      V.edge_w[k] = w; V.edge_es[k] = es;
+      V.edge_u[3 * k] = d[0] / nrm; V.edge_u[3 * k + 1] = d[1] / nrm; V.edge_u[3 * k + 2] = d[2] / nrm;
+    }
+  }
+  block_reduce<1, THREADS>(c, red);
+  if (threadIdx.x == 0) *V.scale_cost = c[0];
+  if (cost_only) return;
+  __threadfence_block();
+  __syncthreads();
+  for (int x = threadIdx.x; x < V.n_extra; x += THREADS) {
+    const int a = V.extra_a[x], b = V.extra_b[x];
+    double h[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int q = V.inc_start[a]; q < V.inc_start[a + 1]; ++q) {
+      const int k = V.inc_edge[q];
+      const int ca = V.cam_col[V.sa[k]], cb = V.cam_col[V.sb[k]];
+      double sgn;
+      if (a == b) sgn = 1.0;                                         // diagonal: every incident edge
+      else if ((ca == a && cb == b) || (ca == b && cb == a)) sgn = -1.0;  // off-diagonal: edges a-b
+      else continue;
+      const double w = V.edge_w[k];
+      const double* u = V.edge_u + 3 * k;
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) h[3 * i + j] += sgn * w * u[i] * u[j];
+    }
+    double* o = V.extra + 36 * (size_t)x;
+    for (int i = 0; i < 36; ++i) o[i] = 0.0;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) o[6 * i + j] = h[3 * i + j];
+  }
+  for (int col = threadIdx.x; col < V.Cf; col += THREADS) {
+    double g[3] = {0, 0, 0};
+    for (int q = V.inc_start[col]; q < V.inc_start[col + 1]; ++q) {
+      const int k = V.inc_edge[q];
+      // d e / d t_a = +u, d e / d t_b = -u ;  b += -w J e
+      const double sgn = (V.cam_col[V.sa[k]] == col) ? -1.0 : 1.0;
+      const double f = sgn * V.edge_w[k] * V.edge_es[k];
+      g[0] += f * V.edge_u[3 * k]; g[1] += f * V.edge_u[3 * k + 1]; g[2] += f * V.edge_u[3 * k + 2];
+    }
+    double* o = V.bp_extra + 6 * col;
+    o[0] = g[0]; o[1] = g[1]; o[2] = g[2]; o[3] = 0.0; o[4] = 0.0; o[5] = 0.0;
+  }
+}
+
+__global__ void __launch_bounds__(256) ba_scale_edges(ScaleView V, int cost_only) {
+  __shared__ double red[8];
+  if (V.st->done || (!cost_only && !V.st->dirty)) return;
+  scale_edges_body<256>(V, cost_only != 0, red);
+}
+
 // ---- fused linearisation ---------------------------------------------------------------------
-// ONE launch builds the whole system: camera-role CTAs (chunks of kLinChunk observations of one
-// camera, kLinObs per thread, next observation prefetched) produce the Hpl blocks and the per-chunk
-// Hpp / bp / cost partials; point-role CTAs (a quad of lanes per point) produce Hll / bl.  The two
-// roles are interleaved in the grid so that the write-heavy camera pass and the latency-bound point
-// pass overlap.  The last chunk of a camera to finish (ticket counter) folds that camera's partials in
-// chunk order; the last CTA of the grid runs the controller (cost, computeLambdaInit).  All sums are
-// fixed-order trees -> bit-reproducible, no floating-point atomics.
+// ONE launch builds the whole system.  The grid mixes three kinds of CTA (work descriptors built on
+// the host, interleaved so that all kinds are resident together):
+//   camera chunks  kLinChunk observations of one camera in camera-major order, kLinObs per thread, the
+//                  next observation prefetched: the 6x3 Hpl blocks (staged per warp in shared memory,
+//                  written with ONE bulk async store per 32 blocks) and the chunk's Hpp / bp / cost
+//                  partial (28 values, transposed warp reduction);
+//   point blocks   one LANE per point over an ELL layout (points sorted by degree, 32 per item, row j
+//                  of an item = the j-th observation of each of its points, coalesced): Hll / bl are
+//                  plain per-lane sums, no cross-lane traffic; cameras come from shared memory;
+//   scale edges    one CTA (EdgeSBAScale blocks).
+// Every observation is evaluated once per role; the translation half of the camera Jacobian is -Jp,
+// so Hpp_tt, Hpl_t and Hll share the six values of w Jp^T Jp.  The last chunk of a camera to finish
+// (ticket counter) folds that camera's partials in chunk order; the last CTA of the grid runs the
+// controller (scale-edge terms, cost, computeLambdaInit).  All sums are fixed-order -> bit-reproducible,
+// no floating-point atomics.
 constexpr int kLinThreads = 128;
+constexpr int kLinWarps = kLinThreads / 32;
 constexpr int kLinObs = 8;
-constexpr int kPtItemsPerWarp = 8;   // point-role work items (<= 32 observations each) per warp
-constexpr int kCamSmemMax = 340;     // cameras kept in shared memory by the point role (96 B each)
 constexpr int kLinChunk = kLinThreads * kLinObs;
+constexpr int kStageDoubles = 32 * 18;          // one warp's 32 Hpl blocks (4608 B)
+constexpr int kPtRowsPerWarp = 16;              // ELL rows a point-role warp aims for
+constexpr int kCamTabStride = 14;               // doubles per camera in the point role's table (112 B)
+constexpr int kCamSmemMax = 1800;               // cameras kept in shared memory by the point role
+
+struct __align__(16) LinWork {   // one per CTA of the fused grid
+  int kind;        // 0 camera chunk, 1 point block, 2 scale edges
+  int cam;         // camera (kind 0) / point block index (kind 1)
+  int start, end;  // camera-major observation range of the chunk
+  int row;         // row of the chunk's partial in camp
+  int n_chunks;    // chunks of this camera
+  int first_row;   // first partial row of this camera
+  int col;         // free-camera column or -1
+};
 
 struct LinArgs {
-  int nA, nB;                       // camera-role / point-role CTAs
-  const int* role;                  // [nA + nB]: >= 0 camera chunk index, < 0 point block -1 - b
-  const int* wk_cam; const int* wk_start; const int* wk_chunk;   // per camera chunk
-  const int* cam_chunk_off;         // [C + 1] first partial row of each camera
-  // point role, regular items: 32 padded slots each (whole points, <= 32 observations in total)
-  int n_pt_items; const int* px_pt; const int* px_cam; const double2* px_uv;   // [n_pt_items * 32], pt -1 = pad
-  // points with more than 32 observations: (first point-major observation, count), strided path
-  int n_long; const int2* long_item; const int* pm_pt;
-  int cams_in_smem;
+  const LinWork* work;              // fused grid: [n_ctas]
+  const LinWork* cam_work;          // camera chunks only (cost-only grid)
+  int n_pt_ctas, n_pt_warps, n_tickets, cams_in_smem, has_scale;
+  // point role (ELL): warp w owns items [pw_first[w], pw_first[w+1]); item it owns rows
+  // [item_row[it], item_row[it+1]) of 32 slots; slot = (camera or -1, measurement)
+  const int* pw_first; const int* item_row; const int* ell_pt; const int* ell_cam; const double2* ell_uv;
   unsigned* cam_ticket;             // [C], zero between launches
   unsigned* lin_ticket;             // [1]
-  double* Hpl; double* camp; double* Hpp; double* bp; double* cam_cost; double* cam_maxd;
+  double* Hpl; double* camp; double* Hpp; double* bp; double* cam_cost;
   double* Hll; double* bl; double* pt_maxd;
   const double* bp_extra; const int* diag_extra; const double* extra; const double* scale_cost;
   LMState* st_rw;
 };
 
-// Controller after buildSystem(): total cost of the current state, computeLambdaInit on the first
-// linearisation (lambda = tau * max |diag H|).  Runs in the last CTA of the fused kernel.
+// bulk async copy shared -> global (SASS UBLKCP), bulk-group completion
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem),
+               "r"(smem_u32(src_smem)), "r"(bytes)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// Residual, Huber weight and the reduced Jacobians of one observation.  Returns false when the point
+// is on the camera plane (g2o aborts there; we drop the observation).
+//   Jp[2][3] = d e / d X (= -translation columns of the camera Jacobian), Jr[2][3] = rotation columns.
+__device__ __forceinline__ bool eval_obs(const double* __restrict__ R, const double* __restrict__ t,
+                                         const double* X, double2 uv, const double4 K, bool want_jr,
+                                         double* e, double& rho, double& w, double (&Jp)[2][3],
+                                         double (&Jr)[2][3]) {
+  const double dx = X[0] - t[0], dy = X[1] - t[1], dz = X[2] - t[2];
+  const double px = R[0] * dx + R[3] * dy + R[6] * dz;
+  const double py = R[1] * dx + R[4] * dy + R[7] * dz;
+  const double pz = R[2] * dx + R[5] * dy + R[8] * dz;
+  if (!(fabs(pz) > 1e-12)) return false;
+  const double iz = 1.0 / pz;
+  e[0] = K.x * px * iz + K.z - uv.x;
+  e[1] = K.y * py * iz + K.w - uv.y;
+  const double chi2 = e[0] * e[0] + e[1] * e[1];
+  // Huber (robust_kernel_impl): rho = chi2, w = 1 inside; rho = 2 d sqrt(chi2) - d^2, w = d / sqrt(chi2)
+  const double d = sqrt(kHuberDelta2);
+  const double r = rsqrt(fmax(chi2, kHuberDelta2));
+  const bool inl = chi2 <= kHuberDelta2;
+  w = inl ? 1.0 : d * r;
+  rho = inl ? chi2 : 2.0 * d * (chi2 * r) - kHuberDelta2;
+  const double ipz2 = iz * iz;
+  const double a = ipz2 * K.x, b = ipz2 * K.y;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {   // w2n column k = row k of R
+    Jp[0][k] = (pz * R[3 * k + 0] - px * R[3 * k + 2]) * a;
+    Jp[1][k] = (pz * R[3 * k + 1] - py * R[3 * k + 2]) * b;
+  }
+  if (want_jr) {
+    // dR/dk (X - t) = A_k pc: A_x pc = (0, 2pz, -2py); A_y pc = (-2pz, 0, 2px); A_z pc = (2py, -2px, 0)
+    const double a2 = 2.0 * a, b2 = 2.0 * b, pz2 = pz * pz;
+    Jr[0][0] = px * py * a2;           Jr[1][0] = (pz2 + py * py) * b2;
+    Jr[0][1] = -(pz2 + px * px) * a2;  Jr[1][1] = -(py * px) * b2;
+    Jr[0][2] = pz * py * a2;           Jr[1][2] = -(pz * px) * b2;
+  }
+  return true;
+}
+
+// Controller after buildSystem(): scale-edge terms of bp, total cost of the current state,
+// computeLambdaInit on the first linearisation (lambda = tau * max |diag H|).  Last CTA of the grid.
 __device__ __forceinline__ void lin_controller(const BAView& V, const LinArgs& A, double* red /*[8]*/) {
   double v[2] = {0.0, 0.0};
-  for (int i = threadIdx.x; i < V.C; i += kLinThreads) {
-    v[0] += __ldcg(A.cam_cost + i);
-    v[1] = fmax(v[1], __ldcg(A.cam_maxd + i));
+  for (int i = threadIdx.x; i < V.C; i += kLinThreads) v[0] += __ldcg(A.cam_cost + i);
+  for (int i = threadIdx.x; i < 6 * V.Cf; i += kLinThreads) {
+    const int col = i / 6, r = i - 6 * col;
+    double dg = __ldcg(A.Hpp + 36 * (size_t)col + 7 * r);
+    if (A.has_scale) {
+      const int ex = A.diag_extra[col];
+      if (ex >= 0) dg += __ldcg(A.extra + 36 * (size_t)ex + 7 * r);
+      A.bp[i] = __ldcg(A.bp + i) + __ldcg(A.bp_extra + i);
+    }
+    v[1] = fmax(v[1], fabs(dg));
   }
-  for (int i = threadIdx.x; i < A.nB; i += kLinThreads) v[1] = fmax(v[1], __ldcg(A.pt_maxd + i));
+  for (int i = threadIdx.x; i < A.n_pt_ctas; i += kLinThreads) v[1] = fmax(v[1], __ldcg(A.pt_maxd + i));
   v[0] = warp_sum(v[0]);
   for (int o = 16; o > 0; o >>= 1) v[1] = fmax(v[1], __shfl_xor_sync(0xffffffffu, v[1], o));
   if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = v[0]; red[4 + (threadIdx.x >> 5)] = v[1]; }
   __syncthreads();
   if (threadIdx.x == 0) {
     LMState* st = A.st_rw;
-    const double cost = ((red[0] + red[1]) + (red[2] + red[3])) + __ldcg(A.scale_cost);
+    const double cost = ((red[0] + red[1]) + (red[2] + red[3])) + (A.has_scale ? __ldcg(A.scale_cost) : 0.0);
     const double md = fmax(fmax(red[4], red[5]), fmax(red[6], red[7]));
     st->cur_cost = cost;
     st->max_diag = md;
@@ -141,28 +293,30 @@ __device__ __forceinline__ void lin_controller(const BAView& V, const LinArgs& A
   }
 }
 
+__device__ __forceinline__ constexpr int hpp_u(int i, int j) { return i * 6 - (i * (i - 1)) / 2 + (j - i); }
+
 template <bool COST_ONLY>
 __global__ void __launch_bounds__(kLinThreads, 4)
-ba_linearize_kernel(BAView V, LinArgs A) {
-  __shared__ __align__(16) double stage[COST_ONLY ? 2 : (kLinThreads / 32) * 32 * 18];
-  __shared__ double red[(kLinThreads / 32) * 32];
-  __shared__ CamRT s_cam;
+ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
+  extern __shared__ __align__(128) double dyn_smem[];   // camera role: Hpl stage; point role: camera table
+  __shared__ double red[kLinWarps * 32];
+  __shared__ __align__(16) CamRT s_cam;
   __shared__ int s_flag;
+  const int4* wsrc = reinterpret_cast<const int4*>((COST_ONLY ? A.cam_work : A.work) + blockIdx.x);
+  const int4 w0 = __ldg(wsrc), w1 = __ldg(wsrc + 1);
   if (V.st->done || (!COST_ONLY && !V.st->dirty)) return;
   const int sb = COST_ONLY ? (V.st->cur ^ 1) : V.st->cur;   // the cost-only pass evaluates the trial state
   const CamRT* __restrict__ camrt = V.camrt[sb];
   const double* __restrict__ pts = V.pts[sb];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int role = COST_ONLY ? (int)blockIdx.x : A.role[blockIdx.x];
+  const int kind = w0.x;
   bool take_ticket = false;
 
-  if (role >= 0) {
-    // ------------------------------------------------ camera role
-    const int c = A.wk_cam[role], chunk = A.wk_chunk[role];
-    const int start = A.wk_start[role];
-    const int end = min(V.cm_start[c + 1], start + kLinChunk);
+  if (kind == 0) {
+    // ------------------------------------------------ camera chunk
+    const int c = w0.y, start = w0.z, end = w0.w, row = w1.x, n_chunks = w1.y, first_row = w1.z, col = w1.w;
     if (tid < 12) reinterpret_cast<double*>(&s_cam)[tid] = reinterpret_cast<const double*>(camrt + c)[tid];
-    const bool cam_free = V.cam_col[c] >= 0;
+    const bool cam_free = col >= 0;
     double v[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = 0.0;
@@ -179,6 +333,7 @@ ba_linearize_kernel(BAView V, LinArgs A) {
       uv = V.cm_uv[o];
       X[0] = pts[3 * p]; X[1] = pts[3 * p + 1]; X[2] = pts[3 * p + 2];
     }
+    double* ws = dyn_smem + wid * kStageDoubles;
     __syncthreads();
 #pragma unroll 1
     for (int k = 0; k < kLinObs; ++k) {
@@ -196,45 +351,47 @@ ba_linearize_kernel(BAView V, LinArgs A) {
 #pragma unroll
       for (int i = 0; i < 18; ++i) h[i] = 0.0;
       if (valid) {
-        double pc[3], e[2], rho, w;
-        to_camera(s_cam, Xc, pc);
-        if (fabs(pc[2]) > 1e-12) {  // g2o aborts on z = 0; we drop the observation
-          residual(pc, V.K, uvc.x, uvc.y, e);
-          huber(e[0] * e[0] + e[1] * e[1], rho, w);
+        double e[2], rho, w, Jp[2][3], Jr[2][3];
+        if (eval_obs(s_cam.R, s_cam.t, Xc, uvc, V.K, !COST_ONLY, e, rho, w, Jp, Jr)) {
           v[27] += rho;
           if (!COST_ONLY && cam_free) {
-            double Jc[2][6], Jp[2][3], W0[6], W1[6];
-            jacobians(s_cam, pc, V.K, Jc, Jp);
+            double wp0[3], wp1[3], wr0[3], wr1[3];
 #pragma unroll
-            for (int i = 0; i < 6; ++i) { W0[i] = w * Jc[0][i]; W1[i] = w * Jc[1][i]; }
-            int q = 0;
-#pragma unroll
-            for (int i = 0; i < 6; ++i) {
-#pragma unroll
-              for (int j = i; j < 6; ++j) { v[q] += W0[i] * Jc[0][j] + W1[i] * Jc[1][j]; ++q; }
+            for (int i = 0; i < 3; ++i) {
+              wp0[i] = w * Jp[0][i]; wp1[i] = w * Jp[1][i];
+              wr0[i] = w * Jr[0][i]; wr1[i] = w * Jr[1][i];
             }
 #pragma unroll
-            for (int i = 0; i < 6; ++i) v[21 + i] -= W0[i] * e[0] + W1[i] * e[1];
+            for (int i = 0; i < 3; ++i) {
 #pragma unroll
-            for (int i = 0; i < 6; ++i) {
+              for (int j = i; j < 3; ++j) {
+                const double a = wp0[i] * Jp[0][j] + wp1[i] * Jp[1][j];     // (w Jp^T Jp)_ij
+                v[hpp_u(i, j)] += a;                                         // Hpp translation block
+                h[3 * i + j] = -a; h[3 * j + i] = -a;                        // Hpl translation rows
+                v[hpp_u(3 + i, 3 + j)] += wr0[i] * Jr[0][j] + wr1[i] * Jr[1][j];
+              }
 #pragma unroll
-              for (int j = 0; j < 3; ++j) h[3 * i + j] = W0[i] * Jp[0][j] + W1[i] * Jp[1][j];
+              for (int j = 0; j < 3; ++j) {
+                v[hpp_u(i, 3 + j)] -= wp0[i] * Jr[0][j] + wp1[i] * Jr[1][j];
+                h[9 + 3 * i + j] = wr0[i] * Jp[0][j] + wr1[i] * Jp[1][j];   // Hpl rotation rows
+              }
+              v[21 + i] += wp0[i] * e[0] + wp1[i] * e[1];                    // bp = -Jc^T w e
+              v[24 + i] -= wr0[i] * e[0] + wr1[i] * e[1];
             }
           }
         }
       }
       if (!COST_ONLY && cam_free) {
-        // the warp's 32 blocks are contiguous in HBM (camera-major): stage them in the warp's own
-        // slice of shared memory (144 B stride: conflict-free STS.128), write with coalesced STG.128
-        double* ws = stage + wid * (32 * 18);
+        // the warp's 32 blocks are contiguous in HBM (camera-major): stage them in the warp's slice of
+        // shared memory (144 B stride: conflict-free STS.128) and hand them to one bulk async store
         const int base = o - lane;                       // first observation of this warp's row
         const int n_blk = max(0, min(32, end - base));
+        if (lane == 0) bulk_wait_read0();                // the previous store has left the stage
         __syncwarp();
         store18(ws + lane * 18, h);
+        fence_async_smem();
         __syncwarp();
-        double2* dst = reinterpret_cast<double2*>(A.Hpl + (size_t)base * 18);
-        const double2* src = reinterpret_cast<const double2*>(ws);
-        for (int i = lane; i < n_blk * 9; i += 32) dst[i] = src[i];
+        if (lane == 0 && n_blk > 0) bulk_s2g(A.Hpl + (size_t)base * 18, ws, (uint32_t)n_blk * 144u);
       }
       o = o_next;
     }
@@ -243,19 +400,18 @@ ba_linearize_kernel(BAView V, LinArgs A) {
       double s = warp_sum(v[27]);
       if (lane == 0) red[wid] = s;
       __syncthreads();
-      if (tid == 0) A.camp[(size_t)(A.cam_chunk_off[c] + chunk) * kCamVals + 27] = (red[0] + red[1]) + (red[2] + red[3]);
+      if (tid == 0) A.camp[(size_t)row * kCamVals + 27] = (red[0] + red[1]) + (red[2] + red[3]);
     } else {
       warp_transpose_sum32(v, lane);
       red[wid * 32 + lane] = v[0];
       __syncthreads();
       if (tid < kCamVals)
-        A.camp[(size_t)(A.cam_chunk_off[c] + chunk) * kCamVals + tid] =
-            (red[tid] + red[32 + tid]) + (red[64 + tid] + red[96 + tid]);
+        A.camp[(size_t)row * kCamVals + tid] = (red[tid] + red[32 + tid]) + (red[64 + tid] + red[96 + tid]);
+      if (lane == 0 && cam_free) bulk_wait0();           // Hpl stores complete before the ticket
     }
     // last chunk of this camera folds the partials (chunk order -> deterministic)
     __threadfence();
     __syncthreads();
-    const int n_chunks = A.cam_chunk_off[c + 1] - A.cam_chunk_off[c];
     if (tid == 0) {
       const unsigned t = atomicAdd(A.cam_ticket + c, 1u);
       s_flag = (t == (unsigned)(n_chunks - 1));
@@ -266,153 +422,114 @@ ba_linearize_kernel(BAView V, LinArgs A) {
       __threadfence();
       if (tid < kCamVals) {
         double s = 0.0;
-        const double* base = A.camp + (size_t)A.cam_chunk_off[c] * kCamVals + tid;
+        const double* base = A.camp + (size_t)first_row * kCamVals + tid;
         for (int k = 0; k < n_chunks; ++k) s += __ldcg(base + (size_t)k * kCamVals);
-        red[tid] = s;
-      }
-      __syncthreads();
-      if (tid == 27) A.cam_cost[c] = red[27];
-      if (!COST_ONLY) {
-        const int col = V.cam_col[c];
-        if (col >= 0 && tid < 27) {
+        if (tid == 27) A.cam_cost[c] = s;
+        if (!COST_ONLY && col >= 0 && tid < 27) {
           if (tid >= 21) {
-            A.bp[6 * col + (tid - 21)] = red[tid] + A.bp_extra[6 * col + (tid - 21)];
+            A.bp[6 * col + (tid - 21)] = s;
           } else {
             int r = 0, k = tid;
             while (k >= 6 - r) { k -= 6 - r; ++r; }
             const int cc = r + k;
-            A.Hpp[36 * col + 6 * r + cc] = red[tid];
-            A.Hpp[36 * col + 6 * cc + r] = red[tid];
+            A.Hpp[36 * col + 6 * r + cc] = s;
+            A.Hpp[36 * col + 6 * cc + r] = s;
           }
-        }
-        if (tid == 0) {   // computeLambdaInit: diagonal of the full camera block (projection + scale edges)
-          double m = 0.0;
-          if (col >= 0) {
-            const int ex = A.diag_extra[col];
-            const int dpos[6] = {0, 6, 11, 15, 18, 20};
-            for (int r = 0; r < 6; ++r)
-              m = fmax(m, fabs(red[dpos[r]] + (ex >= 0 ? A.extra[36 * (size_t)ex + 7 * r] : 0.0)));
-          }
-          A.cam_maxd[c] = m;
         }
       }
       take_ticket = !COST_ONLY;
     }
-  } else {
-    // ------------------------------------------------ point role (never reached when COST_ONLY)
-    // One lane per observation (point-major order): a warp item is a run of whole points with at
-    // most 32 observations (or one long point, strided); per-point sums by a segmented scan over the
-    // lanes -- fixed shape, deterministic.  Cameras come from shared memory when they fit.
-    extern __shared__ __align__(16) double s_cams[];   // [C][12] when A.cams_in_smem
-    const int b = -1 - role;
+  } else if (kind == 1) {
+    // ------------------------------------------------ point block (never reached when COST_ONLY)
+    const int b = w0.y;
     if (A.cams_in_smem) {
-      const double2* src = reinterpret_cast<const double2*>(camrt);
-      double2* dst = reinterpret_cast<double2*>(s_cams);
-      for (int i = tid; i < V.C * 6; i += kLinThreads) dst[i] = src[i];
+      for (int i = tid; i < V.C * 6; i += kLinThreads) {
+        const int c = i / 6, k = i - 6 * c;
+        reinterpret_cast<double2*>(dyn_smem + (size_t)c * kCamTabStride)[k] =
+            reinterpret_cast<const double2*>(camrt + c)[k];
+      }
       __syncthreads();
     }
-    const CamRT* __restrict__ cam_tab = A.cams_in_smem ? reinterpret_cast<const CamRT*>(s_cams) : camrt;
     double m = 0.0;
-    auto accumulate = [&](const CamRT& cam, const double* X, double2 uv, double* acc) {
-      double pc[3], e[2], rho, wgt;
-      to_camera(cam, X, pc);
-      if (!(fabs(pc[2]) > 1e-12)) return;
-      residual(pc, V.K, uv.x, uv.y, e);
-      huber(e[0] * e[0] + e[1] * e[1], rho, wgt);
-      double Jc[2][6], Jp[2][3];
-      jacobians(cam, pc, V.K, Jc, Jp);
-      const double w0[3] = {wgt * Jp[0][0], wgt * Jp[0][1], wgt * Jp[0][2]};
-      const double w1[3] = {wgt * Jp[1][0], wgt * Jp[1][1], wgt * Jp[1][2]};
-      acc[0] += w0[0] * Jp[0][0] + w1[0] * Jp[1][0];
-      acc[1] += w0[0] * Jp[0][1] + w1[0] * Jp[1][1];
-      acc[2] += w0[0] * Jp[0][2] + w1[0] * Jp[1][2];
-      acc[3] += w0[1] * Jp[0][1] + w1[1] * Jp[1][1];
-      acc[4] += w0[1] * Jp[0][2] + w1[1] * Jp[1][2];
-      acc[5] += w0[2] * Jp[0][2] + w1[2] * Jp[1][2];
-#pragma unroll
-      for (int j = 0; j < 3; ++j) acc[6 + j] -= w0[j] * e[0] + w1[j] * e[1];
-    };
-    auto store_point = [&](int key, const double* acc) {
-      const int col = V.pt_col[key];
-#pragma unroll
-      for (int j = 0; j < 6; ++j) A.Hll[6 * (size_t)col + j] = acc[j];
-#pragma unroll
-      for (int j = 0; j < 3; ++j) A.bl[3 * (size_t)col + j] = acc[6 + j];
-      m = fmax(m, fmax(fabs(acc[0]), fmax(fabs(acc[3]), fabs(acc[5]))));
-    };
-    // regular items, software-pipelined like the camera role: slot indices two items ahead, the
-    // point coordinates one item ahead (slots are at fixed addresses: no header load in the chain)
-    const int item0 = (b * (kLinThreads / 32) + wid) * kPtItemsPerWarp;
-    const int n_it = max(0, min(kPtItemsPerWarp, A.n_pt_items - item0));
-    int p_c = -1, ci_c = 0, p_n = -1, ci_n = 0;
-    double2 uv_c = make_double2(0.0, 0.0), uv_n = uv_c;
-    double Xc[3] = {0.0, 0.0, 1.0};
-    if (n_it > 0) {
-      const size_t s0 = (size_t)item0 * 32 + lane;
-      p_c = A.px_pt[s0]; ci_c = A.px_cam[s0]; uv_c = A.px_uv[s0];
-      if (n_it > 1) { p_n = A.px_pt[s0 + 32]; ci_n = A.px_cam[s0 + 32]; uv_n = A.px_uv[s0 + 32]; }
-      if (p_c >= 0) { Xc[0] = pts[3 * p_c]; Xc[1] = pts[3 * p_c + 1]; Xc[2] = pts[3 * p_c + 2]; }
-    }
+    const int wg = b * kLinWarps + wid;
+    if (wg < A.n_pt_warps) {
+      const int it0 = A.pw_first[wg], it1 = A.pw_first[wg + 1];
+      int row_n = 0, row_n1 = 0, p_n = -1;
+      if (it0 < it1) { row_n = A.item_row[it0]; row_n1 = A.item_row[it0 + 1]; p_n = A.ell_pt[(size_t)it0 * 32 + lane]; }
 #pragma unroll 1
-    for (int it = 0; it < n_it; ++it) {
-      // issue: coordinates of item it+1 (its indices arrived during the previous item), indices of it+2
-      double Xn[3] = {0.0, 0.0, 1.0};
-      if (p_n >= 0) { Xn[0] = pts[3 * p_n]; Xn[1] = pts[3 * p_n + 1]; Xn[2] = pts[3 * p_n + 2]; }
-      int p_2 = -1, ci_2 = 0;
-      double2 uv_2 = make_double2(0.0, 0.0);
-      if (it + 2 < n_it) {
-        const size_t s2 = (size_t)(item0 + it + 2) * 32 + lane;
-        p_2 = A.px_pt[s2]; ci_2 = A.px_cam[s2]; uv_2 = A.px_uv[s2];
-      }
-      double acc[9];
+      for (int it = it0; it < it1; ++it) {
+        const int row0 = row_n, row1 = row_n1, p = p_n;
+        if (it + 1 < it1) {   // header of the next item
+          row_n = row1; row_n1 = A.item_row[it + 2]; p_n = A.ell_pt[(size_t)(it + 1) * 32 + lane];
+        }
+        double X[3] = {0.0, 0.0, 1.0};
+        if (p >= 0) { X[0] = pts[3 * p]; X[1] = pts[3 * p + 1]; X[2] = pts[3 * p + 2]; }
+        double acc[9];
 #pragma unroll
-      for (int j = 0; j < 9; ++j) acc[j] = 0.0;
-      const int key = p_c;
-      if (key >= 0) accumulate(cam_tab[ci_c], Xc, uv_c, acc);
-      // inclusive segmented scan; the last lane of a segment holds the point's sums
+        for (int j = 0; j < 9; ++j) acc[j] = 0.0;
+        int c_n = A.ell_cam[(size_t)row0 * 32 + lane];
+        double2 uv_n = A.ell_uv[(size_t)row0 * 32 + lane];
+#pragma unroll 1
+        for (int r = row0; r < row1; ++r) {
+          const int c = c_n;
+          const double2 uv = uv_n;
+          if (r + 1 < row1) { c_n = A.ell_cam[(size_t)(r + 1) * 32 + lane]; uv_n = A.ell_uv[(size_t)(r + 1) * 32 + lane]; }
+          if (c >= 0) {
+            double Rt[12];
+            if (A.cams_in_smem) {
+              const double2* s = reinterpret_cast<const double2*>(dyn_smem + (size_t)c * kCamTabStride);
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const int ku = __shfl_up_sync(0xffffffffu, key, d);
-        const bool take = (lane >= d) && (ku == key) && (key >= 0);
+              for (int k = 0; k < 6; ++k) { const double2 q = s[k]; Rt[2 * k] = q.x; Rt[2 * k + 1] = q.y; }
+            } else {
+              const double2* s = reinterpret_cast<const double2*>(camrt + c);
 #pragma unroll
-        for (int j = 0; j < 9; ++j) {
-          const double u = __shfl_up_sync(0xffffffffu, acc[j], d);
-          if (take) acc[j] += u;
+              for (int k = 0; k < 6; ++k) { const double2 q = __ldg(s + k); Rt[2 * k] = q.x; Rt[2 * k + 1] = q.y; }
+            }
+            double e[2], rho, w, Jp[2][3], Jr[2][3];
+            if (eval_obs(Rt, Rt + 9, X, uv, V.K, false, e, rho, w, Jp, Jr)) {
+              double wp0[3], wp1[3];
+#pragma unroll
+              for (int i = 0; i < 3; ++i) { wp0[i] = w * Jp[0][i]; wp1[i] = w * Jp[1][i]; }
+              acc[0] += wp0[0] * Jp[0][0] + wp1[0] * Jp[1][0];
+              acc[1] += wp0[0] * Jp[0][1] + wp1[0] * Jp[1][1];
+              acc[2] += wp0[0] * Jp[0][2] + wp1[0] * Jp[1][2];
+              acc[3] += wp0[1] * Jp[0][1] + wp1[1] * Jp[1][1];
+              acc[4] += wp0[1] * Jp[0][2] + wp1[1] * Jp[1][2];
+              acc[5] += wp0[2] * Jp[0][2] + wp1[2] * Jp[1][2];
+#pragma unroll
+              for (int j = 0; j < 3; ++j) acc[6 + j] -= wp0[j] * e[0] + wp1[j] * e[1];
+            }
+          }
+        }
+        if (p >= 0) {
+          const int pc = V.pt_col[p];
+#pragma unroll
+          for (int j = 0; j < 6; ++j) A.Hll[6 * (size_t)pc + j] = acc[j];
+#pragma unroll
+          for (int j = 0; j < 3; ++j) A.bl[3 * (size_t)pc + j] = acc[6 + j];
+          m = fmax(m, fmax(fabs(acc[0]), fmax(fabs(acc[3]), fabs(acc[5]))));
         }
       }
-      const int kn = __shfl_down_sync(0xffffffffu, key, 1);
-      if ((key >= 0) && (lane == 31 || kn != key)) store_point(key, acc);
-      p_c = p_n; ci_c = ci_n; uv_c = uv_n; Xc[0] = Xn[0]; Xc[1] = Xn[1]; Xc[2] = Xn[2];
-      p_n = p_2; ci_n = ci_2; uv_n = uv_2;
-    }
-    // long points (> 32 observations): one warp each, strided, plain butterfly
-    for (int li = b * (kLinThreads / 32) + wid; li < A.n_long; li += A.nB * (kLinThreads / 32)) {
-      const int2 w = A.long_item[li];
-      double acc[9];
-#pragma unroll
-      for (int j = 0; j < 9; ++j) acc[j] = 0.0;
-      const int key = A.pm_pt[w.x];
-      const double X[3] = {pts[3 * key], pts[3 * key + 1], pts[3 * key + 2]};
-      for (int o = w.x + lane; o < w.x + w.y; o += 32) accumulate(cam_tab[V.pm_cam[o]], X, V.pm_uv[o], acc);
-#pragma unroll
-      for (int j = 0; j < 9; ++j) acc[j] = warp_sum(acc[j]);
-      if (lane == 0) store_point(key, acc);
     }
     for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
     if (lane == 0) red[wid] = m;
     __syncthreads();
     if (tid == 0) A.pt_maxd[b] = fmax(fmax(red[0], red[1]), fmax(red[2], red[3]));
     take_ticket = true;
+  } else {
+    // ------------------------------------------------ scale edges
+    scale_edges_body<kLinThreads>(SV, false, red);
+    take_ticket = true;
   }
 
   if (!COST_ONLY) {
-    // the last CTA of the grid (camera finalisers + point blocks) runs the controller
+    // the last CTA of the grid (camera finalisers + point blocks + scale edges) runs the controller
     if (!take_ticket) return;     // uniform per CTA
     __threadfence();
     __syncthreads();
     if (tid == 0) {
       const unsigned t = atomicAdd(A.lin_ticket, 1u);
-      s_flag = (t == (unsigned)(V.C + A.nB - 1));
+      s_flag = (t == (unsigned)(A.n_tickets - 1));
       if (s_flag) *A.lin_ticket = 0u;
     }
     __syncthreads();
