@@ -244,6 +244,9 @@ int vslam_ba_linearize(vslam_ba* ba, double* out2, void* stream);
  * L2.  ms_out[reps] on the host.  Synchronises the stream. */
 int vslam_ba_time_stage(vslam_ba* ba, int stage, int reps, void* flush_buf, int64_t flush_bytes,
                         float* ms_out, void* stream);
+/* Profiling: one linearisation with per-CTA %globaltimer stamps; out[3*i..] (host) = {kind (0 camera
+ * chunk, 1 point block, 2 scale edges), start_ns, end_ns} for CTA i of the fused grid, *n = CTA count. */
+int vslam_ba_trace_linearize(vslam_ba* ba, int64_t* out, int64_t capacity, int32_t* n, void* stream);
 /* One damped solve + trial update: out4 (host) = {trial cost, computeScale(), PCG status
  * (0 converged, 1 breakdown, 2 iteration cap), PCG iterations}.  Synchronises the stream. */
 int vslam_ba_trial(vslam_ba* ba, double lambda, double* out4, void* stream);

@@ -48,6 +48,7 @@ def _declare(lib):
     lib.vslam_ba_optimize.argtypes = [vp, i32, C.POINTER(f64), vp]
     lib.vslam_ba_linearize.argtypes = [vp, C.POINTER(f64), vp]
     lib.vslam_ba_trial.argtypes = [vp, f64, C.POINTER(f64), vp]
+    lib.vslam_ba_trace_linearize.argtypes = [vp, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_int32), vp]
     lib.vslam_ba_time_stage.argtypes = [vp, i32, i32, vp, C.c_int64, C.POINTER(C.c_float), vp]
     lib.vslam_ba_accept.argtypes = [vp]
     lib.vslam_ba_dims.argtypes = [vp, C.POINTER(C.c_int32)]

@@ -93,6 +93,18 @@ class BAEngine:
                 flush.numel() * flush.element_size() if flush is not None else 0, out, _cabi.stream_ptr()))
         return list(out)
 
+    def trace_linearize(self):
+        """Per-CTA (kind, start_ns, end_ns) of one fused linearisation launch (profiling)."""
+        cap = 3 * (1 << 20)
+        out = (C.c_int64 * cap)()
+        n = C.c_int32(0)
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().vslam_ba_trace_linearize(self._h, out, cap, C.byref(n), _cabi.stream_ptr()))
+        import numpy as np
+        a = np.ctypeslib.as_array(out)
+        self.last_trace_marks = a[3 * n.value:3 * n.value + 7].copy()   # stamp before, controller end, stamp after, controller start
+        return a[:3 * n.value].reshape(-1, 3).copy()
+
     def trial(self, lam):
         out = (C.c_double * 4)()
         with torch.cuda.device(self.device):

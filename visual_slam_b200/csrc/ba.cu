@@ -127,6 +127,7 @@ struct BA {
   int n_pt_warps = 0, n_ell_rows = 0, cams_in_smem = 0, lin_ctas = 0;
   size_t lin_smem = 0;
   DevBuf<double> pt_maxd;
+  DevBuf<long long> trace;       // allocated by vslam_ba_trace_linearize only
   int lin_nA = 0, lin_nB = 0;
   DevBuf<double> edge_w, edge_es, edge_u;
   DevBuf<double2> cm_uv;
@@ -169,7 +170,7 @@ struct BA {
     A.Hpl = Hpl.p; A.camp = camp.p; A.Hpp = Hpp.p; A.bp = bp.p; A.cam_cost = cam_cost.p;
     A.Hll = Hll.p; A.bl = bl.p; A.pt_maxd = pt_maxd.p;
     A.bp_extra = bp_extra.p; A.diag_extra = diag_extra.p; A.extra = extra.p; A.scale_cost = scale_cost.p;
-    A.st_rw = lm.p;
+    A.st_rw = lm.p; A.trace = trace.p;
     return A;
   }
   ScaleView scale_view() const {
@@ -372,7 +373,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   }
   B.lin_nB = (B.n_pt_warps + kLinWarps - 1) / kLinWarps;
   B.cams_in_smem = (C <= kCamSmemMax) ? 1 : 0;
-  B.lin_smem = std::max((size_t)kLinWarps * kStageDoubles * sizeof(double),
+  B.lin_smem = std::max((size_t)kLinCamSmem,
                         B.cams_in_smem ? (size_t)C * kCamTabStride * sizeof(double) : 0);
   BA_TRY(cudaFuncSetAttribute(ba_linearize_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)(kCamSmemMax * kCamTabStride * sizeof(double))));
@@ -551,7 +552,7 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
   if (B.Pf) ba_backsub_cam<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.dp.p, B.tmp3.p);
   if (B.P) ba_backsub_pt<<<B.n_sp, 256, 0, st>>>(V, B.tmp3.p, B.Hinv.p, B.bl.p, B.dl.p, B.scale_partial.p);
   ba_update_cams<<<(B.C + 127) / 128, 128, 0, st>>>(V, B.dp.p);
-  ba_linearize_kernel<true><<<B.lin_nA, kLinThreads, 0, st>>>(V, B.lin_args(), B.scale_view());
+  ba_linearize_kernel<true><<<B.lin_nA, kLinThreads, kLinCostSmem, st>>>(V, B.lin_args(), B.scale_view());
   if (B.E) ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 1);
   ba_trial_controller<<<1, 256, 0, st>>>(B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0,
                                          B.scale_partial.p, B.n, B.dp.p, B.bp.p, B.pcg_flags.p + 1,
@@ -730,6 +731,40 @@ extern "C" int vslam_ba_time_stage(vslam_ba* h, int stage, int reps, void* flush
   }
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   return rc;
+}
+
+// Profiling: runs one linearisation with per-CTA globaltimer stamps.  out (host) receives, per CTA of
+// the fused grid, {kind, start_ns, end_ns} relative to the earliest start; returns the CTA count in *n.
+extern "C" int vslam_ba_trace_linearize(vslam_ba* h, int64_t* out, int64_t capacity, int32_t* n, void* stream) {
+  if (!h || !out || !n) return VSLAM_ERR_BAD_ARG;
+  BA& B = h->impl;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  *n = B.lin_ctas;
+  if (capacity < (int64_t)3 * B.lin_ctas) return VSLAM_ERR_BAD_ARG;
+  if (!B.trace.p) BA_TRY(B.trace.alloc((size_t)2 * B.lin_ctas + 8));
+  BA_TRY(cudaMemsetAsync(B.trace.p, 0, ((size_t)2 * B.lin_ctas + 8) * sizeof(long long), st));
+  ba_lm_poke<<<1, 1, 0, st>>>(B.lm.p, 0, 0.0);
+  ba_stamp<<<1, 1, 0, st>>>(B.trace.p + 2 * B.lin_ctas + 1);
+  int rc = enqueue_linearize(B, st);
+  if (rc) return rc;
+  ba_stamp<<<1, 1, 0, st>>>(B.trace.p + 2 * B.lin_ctas + 2);
+  std::vector<long long> t((size_t)2 * B.lin_ctas + 8);
+  std::vector<LinWork> w(B.lin_ctas);
+  BA_TRY(cudaMemcpyAsync(t.data(), B.trace.p, t.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
+  BA_TRY(cudaMemcpyAsync(w.data(), B.lin_work.p, w.size() * sizeof(LinWork), cudaMemcpyDeviceToHost, st));
+  BA_TRY(cudaStreamSynchronize(st));
+  cudaFree(B.trace.p); B.trace.p = nullptr;
+  long long t0 = std::numeric_limits<long long>::max();
+  for (int i = 0; i < B.lin_ctas; ++i) if (t[2 * i]) t0 = std::min(t0, t[2 * i]);
+  for (int i = 0; i < B.lin_ctas; ++i) {
+    out[3 * i] = w[i].kind; out[3 * i + 1] = t[2 * i] - t0; out[3 * i + 2] = t[2 * i + 1] - t0;
+  }
+  if (capacity >= (int64_t)3 * B.lin_ctas + 7) {
+    for (int k = 3; k < 7; ++k) out[3 * B.lin_ctas + k] = t[2 * B.lin_ctas + k] - t0;   // stamp kernel before, controller end, stamp kernel after
+    out[3 * B.lin_ctas] = t[2 * B.lin_ctas + 1] - t0; out[3 * B.lin_ctas + 1] = t[2 * B.lin_ctas] - t0;
+    out[3 * B.lin_ctas + 2] = t[2 * B.lin_ctas + 2] - t0;
+  }
+  return VSLAM_OK;
 }
 
 extern "C" int vslam_ba_trial(vslam_ba* h, double lambda, double* out4, void* stream) {

@@ -178,7 +178,13 @@ constexpr int kLinWarps = kLinThreads / 32;
 constexpr int kLinObs = 8;
 constexpr int kLinChunk = kLinThreads * kLinObs;
 constexpr int kStageDoubles = 32 * 18;          // one warp's 32 Hpl blocks (4608 B)
-constexpr int kPtRowsPerWarp = 16;              // ELL rows a point-role warp aims for
+constexpr bool kBulkStore = true;               // Hpl stage -> HBM by bulk async store (else LDS + STG.128)
+constexpr int kRing = 3;                        // input ring depth (observations in flight per thread)
+constexpr int kRingDoubles = 32 * 5;            // one warp-observation of inputs: X[32][3] + uv[32][2]
+constexpr int kHplStages = 1;                   // Hpl stages per warp
+constexpr int kLinCamSmem = kLinWarps * (kHplStages * kStageDoubles + kRing * kRingDoubles) * 8;
+constexpr int kLinCostSmem = kLinWarps * kRing * kRingDoubles * 8;                     // cost-only launch: ring only   // camera-role bytes
+constexpr int kPtRowsPerWarp = 8;               // ELL rows a point-role warp aims for
 constexpr int kCamTabStride = 14;               // doubles per camera in the point role's table (112 B)
 constexpr int kCamSmemMax = 1800;               // cameras kept in shared memory by the point role
 
@@ -205,7 +211,18 @@ struct LinArgs {
   double* Hll; double* bl; double* pt_maxd;
   const double* bp_extra; const int* diag_extra; const double* extra; const double* scale_cost;
   LMState* st_rw;
+  long long* trace;                 // optional [n_ctas][2] globaltimer stamps (profiling), else null
 };
+
+__device__ __forceinline__ long long globaltimer_ns();
+__global__ void ba_stamp(long long* dst);
+__device__ __forceinline__ long long globaltimer_ns() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__global__ void ba_stamp(long long* dst) { *dst = globaltimer_ns(); }
 
 // bulk async copy shared -> global (SASS UBLKCP), bulk-group completion
 __device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
@@ -215,8 +232,40 @@ __device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, u
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void cp_async8(void* dst_smem, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// Branch-free FP64 reciprocal / reciprocal square root for finite normal arguments: hardware seed
+// (MUFU.RCP64H / RSQ64H, ~2^-20) + two Newton steps (error ~1 ulp).  The IEEE division / sqrt of the
+// compiler expands to the same seed plus a slow-path call that costs branches in every warp.
+__device__ __forceinline__ double fast_rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+}
+__device__ __forceinline__ double fast_rsqrt(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double h = 0.5 * x;
+  double e = fma(-h * y, y, 0.5);
+  y = fma(y, e, y);
+  e = fma(-h * y, y, 0.5);
+  return fma(y, e, y);
+}
 
 // Residual, Huber weight and the reduced Jacobians of one observation.  Returns false when the point
 // is on the camera plane (g2o aborts there; we drop the observation).
@@ -230,13 +279,13 @@ __device__ __forceinline__ bool eval_obs(const double* __restrict__ R, const dou
   const double py = R[1] * dx + R[4] * dy + R[7] * dz;
   const double pz = R[2] * dx + R[5] * dy + R[8] * dz;
   if (!(fabs(pz) > 1e-12)) return false;
-  const double iz = 1.0 / pz;
+  const double iz = fast_rcp(pz);
   e[0] = K.x * px * iz + K.z - uv.x;
   e[1] = K.y * py * iz + K.w - uv.y;
   const double chi2 = e[0] * e[0] + e[1] * e[1];
   // Huber (robust_kernel_impl): rho = chi2, w = 1 inside; rho = 2 d sqrt(chi2) - d^2, w = d / sqrt(chi2)
   const double d = sqrt(kHuberDelta2);
-  const double r = rsqrt(fmax(chi2, kHuberDelta2));
+  const double r = fast_rsqrt(fmax(chi2, kHuberDelta2));
   const bool inl = chi2 <= kHuberDelta2;
   w = inl ? 1.0 : d * r;
   rho = inl ? chi2 : 2.0 * d * (chi2 * r) - kHuberDelta2;
@@ -260,19 +309,72 @@ __device__ __forceinline__ bool eval_obs(const double* __restrict__ R, const dou
 // Controller after buildSystem(): scale-edge terms of bp, total cost of the current state,
 // computeLambdaInit on the first linearisation (lambda = tau * max |diag H|).  Last CTA of the grid.
 __device__ __forceinline__ void lin_controller(const BAView& V, const LinArgs& A, double* red /*[8]*/) {
+  // read-only loops first (independent loads pipeline freely), the bp update last
+  if (A.trace && threadIdx.x == 0) A.trace[2 * gridDim.x + 4] = globaltimer_ns();
+  // every load of a batch is issued before the first use: the values were just written by other SMs
+  // and each L2 round trip costs ~0.5 us, so the loops must not serialise them
   double v[2] = {0.0, 0.0};
-  for (int i = threadIdx.x; i < V.C; i += kLinThreads) v[0] += __ldcg(A.cam_cost + i);
-  for (int i = threadIdx.x; i < 6 * V.Cf; i += kLinThreads) {
-    const int col = i / 6, r = i - 6 * col;
-    double dg = __ldcg(A.Hpp + 36 * (size_t)col + 7 * r);
-    if (A.has_scale) {
-      const int ex = A.diag_extra[col];
-      if (ex >= 0) dg += __ldcg(A.extra + 36 * (size_t)ex + 7 * r);
-      A.bp[i] = __ldcg(A.bp + i) + __ldcg(A.bp_extra + i);
+  constexpr int U = 8;
+  const int n6 = 6 * V.Cf;
+  for (int i0 = 0; i0 < V.C; i0 += U * kLinThreads) {
+    double a[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * kLinThreads + threadIdx.x;
+      a[u] = i < V.C ? __ldcg(A.cam_cost + i) : 0.0;
     }
-    v[1] = fmax(v[1], fabs(dg));
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[0] += a[u];
   }
-  for (int i = threadIdx.x; i < A.n_pt_ctas; i += kLinThreads) v[1] = fmax(v[1], __ldcg(A.pt_maxd + i));
+  for (int i0 = 0; i0 < n6; i0 += U * kLinThreads) {
+    double a[U], x[U];
+    int ex[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * kLinThreads + threadIdx.x;
+      const int col = i / 6, r = i - 6 * col;
+      a[u] = i < n6 ? __ldcg(A.Hpp + 36 * (size_t)col + 7 * r) : 0.0;
+      ex[u] = (i < n6 && A.has_scale) ? __ldg(A.diag_extra + col) : -1;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * kLinThreads + threadIdx.x;
+      const int r = i % 6;
+      x[u] = ex[u] >= 0 ? __ldcg(A.extra + 36 * (size_t)ex[u] + 7 * r) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[1] = fmax(v[1], fabs(a[u] + x[u]));
+  }
+  for (int i0 = 0; i0 < A.n_pt_ctas; i0 += U * kLinThreads) {
+    double a[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * kLinThreads + threadIdx.x;
+      a[u] = i < A.n_pt_ctas ? __ldcg(A.pt_maxd + i) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[1] = fmax(v[1], a[u]);
+  }
+  if (A.trace && threadIdx.x == 0) A.trace[2 * gridDim.x + 5] = globaltimer_ns() + (v[0] > 1e300) + (v[1] > 1e300);
+  if (A.has_scale) {
+    double* __restrict__ bp = A.bp;
+    const double* __restrict__ bpx = A.bp_extra;
+    for (int i0 = 0; i0 < 6 * V.Cf; i0 += 4 * kLinThreads) {
+      double a[4], b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * kLinThreads + threadIdx.x;
+        a[u] = i < 6 * V.Cf ? __ldcg(bp + i) : 0.0;
+        b[u] = i < 6 * V.Cf ? __ldcg(bpx + i) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * kLinThreads + threadIdx.x;
+        if (i < 6 * V.Cf) bp[i] = a[u] + b[u];
+      }
+    }
+  }
+  if (A.trace && threadIdx.x == 0) A.trace[2 * gridDim.x + 6] = globaltimer_ns();
   v[0] = warp_sum(v[0]);
   for (int o = 16; o > 0; o >>= 1) v[1] = fmax(v[1], __shfl_xor_sync(0xffffffffu, v[1], o));
   if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = v[0]; red[4 + (threadIdx.x >> 5)] = v[1]; }
@@ -311,6 +413,7 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int kind = w0.x;
   bool take_ticket = false;
+  if (!COST_ONLY && A.trace && tid == 0) A.trace[2 * blockIdx.x] = globaltimer_ns();
 
   if (kind == 0) {
     // ------------------------------------------------ camera chunk
@@ -320,80 +423,139 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
     double v[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = 0.0;
-    // two-stage software pipeline (warps issue in order, so a dependent address must never be
-    // computed right after its index load): the point INDEX is loaded two observations ahead, the
-    // point itself one observation ahead, and both are in flight under the current arithmetic.
-    int o = start + tid;
-    double X[3] = {0.0, 0.0, 1.0};
-    double2 uv = make_double2(0.0, 0.0);
+    // Inputs travel through a per-warp ring in shared memory filled by cp.async (LDGSTS): the point
+    // index is loaded kRing + 1 observations ahead (register), the point and its measurement kRing
+    // observations ahead (shared memory), so a memory round trip of a microsecond stays hidden and no
+    // registers are held across it.
+    const int o0 = start + tid;
+    double* ring = dyn_smem + wid * (kRing * kRingDoubles);
+    // Hpl stages of this warp; absent in the cost-only launch
+    double* ws0 = dyn_smem + kLinWarps * kRing * kRingDoubles + wid * (kHplStages * kStageDoubles);
+    auto issue = [&](int k, int p) {   // observation k of this thread -> ring slot k % kRing
+      const int o = o0 + k * kLinThreads;
+      if (k < kLinObs && o < end) {
+        double* slot = ring + (k % kRing) * kRingDoubles;
+        const double* px = pts + 3 * (size_t)p;
+        cp_async8(slot + lane * 3, px); cp_async8(slot + lane * 3 + 1, px + 1); cp_async8(slot + lane * 3 + 2, px + 2);
+        cp_async16(slot + 96 + lane * 2, V.cm_uv + o);
+      }
+      cp_async_commit();
+    };
     int p_next = 0;
-    if (o + kLinThreads < end) p_next = V.cm_pt[o + kLinThreads];
-    if (o < end) {
-      const int p = V.cm_pt[o];
-      uv = V.cm_uv[o];
-      X[0] = pts[3 * p]; X[1] = pts[3 * p + 1]; X[2] = pts[3 * p + 2];
+    {
+      int pk[kRing + 1];
+#pragma unroll
+      for (int k = 0; k <= kRing; ++k) {
+        const int o = o0 + k * kLinThreads;
+        pk[k] = (k < kLinObs && o < end) ? V.cm_pt[o] : 0;
+      }
+#pragma unroll
+      for (int k = 0; k < kRing; ++k) issue(k, pk[k]);
+      p_next = pk[kRing];
     }
-    double* ws = dyn_smem + wid * kStageDoubles;
     __syncthreads();
 #pragma unroll 1
     for (int k = 0; k < kLinObs; ++k) {
+      const int o = o0 + k * kLinThreads;
       const bool valid = o < end;
-      const double Xc[3] = {X[0], X[1], X[2]};
-      const double2 uvc = uv;
-      const int o_next = o + kLinThreads;
-      const int p_cur = p_next;
-      if (k + 2 < kLinObs && o_next + kLinThreads < end) p_next = V.cm_pt[o_next + kLinThreads];
-      if (k + 1 < kLinObs && o_next < end) {   // p_cur arrived during the previous observation
-        uv = V.cm_uv[o_next];
-        X[0] = pts[3 * p_cur]; X[1] = pts[3 * p_cur + 1]; X[2] = pts[3 * p_cur + 2];
+      cp_async_wait<kRing - 1>();                       // this thread's slot k has landed
+      double Xc[3] = {0.0, 0.0, 1.0};
+      double2 uvc = make_double2(0.0, 0.0);
+      if (valid) {
+        const double* slot = ring + (k % kRing) * kRingDoubles;
+        Xc[0] = slot[lane * 3]; Xc[1] = slot[lane * 3 + 1]; Xc[2] = slot[lane * 3 + 2];
+        uvc = *reinterpret_cast<const double2*>(slot + 96 + lane * 2);
       }
-      double h[18];
-#pragma unroll
-      for (int i = 0; i < 18; ++i) h[i] = 0.0;
+      {
+        const int p_use = p_next;                       // index of observation k + kRing
+        const int o2 = o0 + (k + kRing + 1) * kLinThreads;
+        if (k + kRing + 1 < kLinObs && o2 < end) p_next = V.cm_pt[o2];
+        issue(k + kRing, p_use);                        // refills the slot just read
+      }
+      const bool want_hpl = !COST_ONLY && cam_free;
+      double* ws = ws0 + (k % kHplStages) * kStageDoubles;
+      double2* wsl = reinterpret_cast<double2*>(ws + lane * 18);
+      if (want_hpl) {
+        if (kBulkStore && lane == 0) {                   // the last store from this stage has left it
+          if (kHplStages == 1) bulk_wait_read0(); else bulk_wait_read1();
+        }
+        __syncwarp();
+      }
+      bool ok = false;
       if (valid) {
         double e[2], rho, w, Jp[2][3], Jr[2][3];
-        if (eval_obs(s_cam.R, s_cam.t, Xc, uvc, V.K, !COST_ONLY, e, rho, w, Jp, Jr)) {
+        ok = eval_obs(s_cam.R, s_cam.t, Xc, uvc, V.K, !COST_ONLY, e, rho, w, Jp, Jr);
+        if (ok) {
           v[27] += rho;
-          if (!COST_ONLY && cam_free) {
-            double wp0[3], wp1[3], wr0[3], wr1[3];
+          if (want_hpl) {
+            // blocks go to the warp's stage as soon as they exist (keeps the live set small)
+            double wp0[3], wp1[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) { wp0[i] = w * Jp[0][i]; wp1[i] = w * Jp[1][i]; }
+            double a[6];   // (w Jp^T Jp) upper: 00 01 02 11 12 22
+            a[0] = wp0[0] * Jp[0][0] + wp1[0] * Jp[1][0];
+            a[1] = wp0[0] * Jp[0][1] + wp1[0] * Jp[1][1];
+            a[2] = wp0[0] * Jp[0][2] + wp1[0] * Jp[1][2];
+            a[3] = wp0[1] * Jp[0][1] + wp1[1] * Jp[1][1];
+            a[4] = wp0[1] * Jp[0][2] + wp1[1] * Jp[1][2];
+            a[5] = wp0[2] * Jp[0][2] + wp1[2] * Jp[1][2];
+            v[hpp_u(0, 0)] += a[0]; v[hpp_u(0, 1)] += a[1]; v[hpp_u(0, 2)] += a[2];
+            v[hpp_u(1, 1)] += a[3]; v[hpp_u(1, 2)] += a[4]; v[hpp_u(2, 2)] += a[5];
+            // Hpl translation rows = -(w Jp^T Jp)
+            wsl[0] = make_double2(-a[0], -a[1]); wsl[1] = make_double2(-a[2], -a[1]);
+            wsl[2] = make_double2(-a[3], -a[4]); wsl[3] = make_double2(-a[2], -a[4]);
+            const double h8 = -a[5];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) v[21 + i] = fma(wp0[i], e[0], fma(wp1[i], e[1], v[21 + i]));   // bp = -Jc^T w e
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
-              wp0[i] = w * Jp[0][i]; wp1[i] = w * Jp[1][i];
-              wr0[i] = w * Jr[0][i]; wr1[i] = w * Jr[1][i];
+#pragma unroll
+              for (int j = 0; j < 3; ++j)
+                v[hpp_u(i, 3 + j)] = fma(-wp0[i], Jr[0][j], fma(-wp1[i], Jr[1][j], v[hpp_u(i, 3 + j)]));
             }
+            double wr0[3], wr1[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) { wr0[i] = w * Jr[0][i]; wr1[i] = w * Jr[1][i]; }
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
 #pragma unroll
-              for (int j = i; j < 3; ++j) {
-                const double a = wp0[i] * Jp[0][j] + wp1[i] * Jp[1][j];     // (w Jp^T Jp)_ij
-                v[hpp_u(i, j)] += a;                                         // Hpp translation block
-                h[3 * i + j] = -a; h[3 * j + i] = -a;                        // Hpl translation rows
-                v[hpp_u(3 + i, 3 + j)] += wr0[i] * Jr[0][j] + wr1[i] * Jr[1][j];
-              }
-#pragma unroll
-              for (int j = 0; j < 3; ++j) {
-                v[hpp_u(i, 3 + j)] -= wp0[i] * Jr[0][j] + wp1[i] * Jr[1][j];
-                h[9 + 3 * i + j] = wr0[i] * Jp[0][j] + wr1[i] * Jp[1][j];   // Hpl rotation rows
-              }
-              v[21 + i] += wp0[i] * e[0] + wp1[i] * e[1];                    // bp = -Jc^T w e
-              v[24 + i] -= wr0[i] * e[0] + wr1[i] * e[1];
+              for (int j = i; j < 3; ++j)
+                v[hpp_u(3 + i, 3 + j)] = fma(wr0[i], Jr[0][j], fma(wr1[i], Jr[1][j], v[hpp_u(3 + i, 3 + j)]));
+              v[24 + i] = fma(-wr0[i], e[0], fma(-wr1[i], e[1], v[24 + i]));
             }
+            // Hpl rotation rows
+            double r[9];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+#pragma unroll
+              for (int j = 0; j < 3; ++j) r[3 * i + j] = wr0[i] * Jp[0][j] + wr1[i] * Jp[1][j];
+            }
+            wsl[4] = make_double2(h8, r[0]); wsl[5] = make_double2(r[1], r[2]);
+            wsl[6] = make_double2(r[3], r[4]); wsl[7] = make_double2(r[5], r[6]);
+            wsl[8] = make_double2(r[7], r[8]);
           }
         }
       }
-      if (!COST_ONLY && cam_free) {
-        // the warp's 32 blocks are contiguous in HBM (camera-major): stage them in the warp's slice of
-        // shared memory (144 B stride: conflict-free STS.128) and hand them to one bulk async store
+      if (want_hpl) {
+        // the warp's 32 blocks are contiguous in HBM (camera-major): staged in the warp's slice of
+        // shared memory (144 B stride: conflict-free STS.128), written by one bulk async store
+        if (!ok) {
+#pragma unroll
+          for (int i = 0; i < 9; ++i) wsl[i] = make_double2(0.0, 0.0);
+        }
         const int base = o - lane;                       // first observation of this warp's row
         const int n_blk = max(0, min(32, end - base));
-        if (lane == 0) bulk_wait_read0();                // the previous store has left the stage
-        __syncwarp();
-        store18(ws + lane * 18, h);
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0 && n_blk > 0) bulk_s2g(A.Hpl + (size_t)base * 18, ws, (uint32_t)n_blk * 144u);
+        if (kBulkStore) {
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0 && n_blk > 0) bulk_s2g(A.Hpl + (size_t)base * 18, ws, (uint32_t)n_blk * 144u);
+        } else {
+          __syncwarp();
+          double2* dst = reinterpret_cast<double2*>(A.Hpl + (size_t)base * 18);
+          const double2* srcp = reinterpret_cast<const double2*>(ws);
+          for (int i = lane; i < n_blk * 9; i += 32) dst[i] = srcp[i];
+        }
       }
-      o = o_next;
     }
     // chunk partial: 28 values
     if (COST_ONLY) {
@@ -407,19 +569,19 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
       __syncthreads();
       if (tid < kCamVals)
         A.camp[(size_t)row * kCamVals + tid] = (red[tid] + red[32 + tid]) + (red[64 + tid] + red[96 + tid]);
-      if (lane == 0 && cam_free) bulk_wait0();           // Hpl stores complete before the ticket
+      if (lane == 0 && cam_free) bulk_wait_read0();      // the stage is free; the kernel boundary publishes Hpl
     }
     // last chunk of this camera folds the partials (chunk order -> deterministic)
-    __threadfence();
     __syncthreads();
     if (tid == 0) {
+      fence_acq_rel_gpu();   // cumulative over the CTA's writes (ordered before it by the barrier)
       const unsigned t = atomicAdd(A.cam_ticket + c, 1u);
       s_flag = (t == (unsigned)(n_chunks - 1));
       if (s_flag) A.cam_ticket[c] = 0u;
     }
     __syncthreads();
     if (s_flag) {
-      __threadfence();
+      fence_acq_rel_gpu();
       if (tid < kCamVals) {
         double s = 0.0;
         const double* base = A.camp + (size_t)first_row * kCamVals + tid;
@@ -467,38 +629,54 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
         double acc[9];
 #pragma unroll
         for (int j = 0; j < 9; ++j) acc[j] = 0.0;
-        int c_n = A.ell_cam[(size_t)row0 * 32 + lane];
-        double2 uv_n = A.ell_uv[(size_t)row0 * 32 + lane];
+        auto accumulate = [&](int c, double2 uv) {
+          if (c < 0) return;
+          double Rt[12];
+          if (A.cams_in_smem) {
+            const double2* s = reinterpret_cast<const double2*>(dyn_smem + (size_t)c * kCamTabStride);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { const double2 q = s[k]; Rt[2 * k] = q.x; Rt[2 * k + 1] = q.y; }
+          } else {
+            const double2* s = reinterpret_cast<const double2*>(camrt + c);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { const double2 q = __ldg(s + k); Rt[2 * k] = q.x; Rt[2 * k + 1] = q.y; }
+          }
+          double e[2], rho, w, Jp[2][3], Jr[2][3];
+          if (!eval_obs(Rt, Rt + 9, X, uv, V.K, false, e, rho, w, Jp, Jr)) return;
+          double wp0[3], wp1[3];
+#pragma unroll
+          for (int i = 0; i < 3; ++i) { wp0[i] = w * Jp[0][i]; wp1[i] = w * Jp[1][i]; }
+          acc[0] = fma(wp0[0], Jp[0][0], fma(wp1[0], Jp[1][0], acc[0]));
+          acc[1] = fma(wp0[0], Jp[0][1], fma(wp1[0], Jp[1][1], acc[1]));
+          acc[2] = fma(wp0[0], Jp[0][2], fma(wp1[0], Jp[1][2], acc[2]));
+          acc[3] = fma(wp0[1], Jp[0][1], fma(wp1[1], Jp[1][1], acc[3]));
+          acc[4] = fma(wp0[1], Jp[0][2], fma(wp1[1], Jp[1][2], acc[4]));
+          acc[5] = fma(wp0[2], Jp[0][2], fma(wp1[2], Jp[1][2], acc[5]));
+#pragma unroll
+          for (int j = 0; j < 3; ++j) acc[6 + j] = fma(-wp0[j], e[0], fma(-wp1[j], e[1], acc[6 + j]));
+        };
+        // four register sets in rotation (no loop-carried copy behind a load): the loads of rows
+        // r+4 .. r+7 are in flight under the arithmetic of rows r .. r+3
+        const size_t sl = (size_t)row0 * 32 + lane;
+        int cq[4];
+        double2 uq[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          cq[u] = -1; uq[u] = make_double2(0.0, 0.0);
+          if (row0 + u < row1) { cq[u] = A.ell_cam[sl + 32 * u]; uq[u] = A.ell_uv[sl + 32 * u]; }
+        }
 #pragma unroll 1
-        for (int r = row0; r < row1; ++r) {
-          const int c = c_n;
-          const double2 uv = uv_n;
-          if (r + 1 < row1) { c_n = A.ell_cam[(size_t)(r + 1) * 32 + lane]; uv_n = A.ell_uv[(size_t)(r + 1) * 32 + lane]; }
-          if (c >= 0) {
-            double Rt[12];
-            if (A.cams_in_smem) {
-              const double2* s = reinterpret_cast<const double2*>(dyn_smem + (size_t)c * kCamTabStride);
+        for (int r = row0; r < row1; r += 4) {
 #pragma unroll
-              for (int k = 0; k < 6; ++k) { const double2 q = s[k]; Rt[2 * k] = q.x; Rt[2 * k + 1] = q.y; }
-            } else {
-              const double2* s = reinterpret_cast<const double2*>(camrt + c);
-#pragma unroll
-              for (int k = 0; k < 6; ++k) { const double2 q = __ldg(s + k); Rt[2 * k] = q.x; Rt[2 * k + 1] = q.y; }
+          for (int u = 0; u < 4; ++u) {
+            const int c0 = cq[u];
+            const double2 uv0 = uq[u];
+            cq[u] = -1;
+            if (r + 4 + u < row1) {
+              const size_t s2 = (size_t)(r + 4 + u) * 32 + lane;
+              cq[u] = A.ell_cam[s2]; uq[u] = A.ell_uv[s2];
             }
-            double e[2], rho, w, Jp[2][3], Jr[2][3];
-            if (eval_obs(Rt, Rt + 9, X, uv, V.K, false, e, rho, w, Jp, Jr)) {
-              double wp0[3], wp1[3];
-#pragma unroll
-              for (int i = 0; i < 3; ++i) { wp0[i] = w * Jp[0][i]; wp1[i] = w * Jp[1][i]; }
-              acc[0] += wp0[0] * Jp[0][0] + wp1[0] * Jp[1][0];
-              acc[1] += wp0[0] * Jp[0][1] + wp1[0] * Jp[1][1];
-              acc[2] += wp0[0] * Jp[0][2] + wp1[0] * Jp[1][2];
-              acc[3] += wp0[1] * Jp[0][1] + wp1[1] * Jp[1][1];
-              acc[4] += wp0[1] * Jp[0][2] + wp1[1] * Jp[1][2];
-              acc[5] += wp0[2] * Jp[0][2] + wp1[2] * Jp[1][2];
-#pragma unroll
-              for (int j = 0; j < 3; ++j) acc[6 + j] -= wp0[j] * e[0] + wp1[j] * e[1];
-            }
+            accumulate(c0, uv0);
           }
         }
         if (p >= 0) {
@@ -522,20 +700,23 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
     take_ticket = true;
   }
 
+  if (!COST_ONLY && A.trace && tid == 0) A.trace[2 * blockIdx.x + 1] = globaltimer_ns();
   if (!COST_ONLY) {
     // the last CTA of the grid (camera finalisers + point blocks + scale edges) runs the controller
     if (!take_ticket) return;     // uniform per CTA
-    __threadfence();
     __syncthreads();
     if (tid == 0) {
+      fence_acq_rel_gpu();
       const unsigned t = atomicAdd(A.lin_ticket, 1u);
       s_flag = (t == (unsigned)(A.n_tickets - 1));
       if (s_flag) *A.lin_ticket = 0u;
     }
     __syncthreads();
     if (s_flag) {
-      __threadfence();
+      if (A.trace && tid == 0) A.trace[2 * gridDim.x + 3] = globaltimer_ns();
+      fence_acq_rel_gpu();
       lin_controller(V, A, red);
+      if (A.trace && tid == 0) A.trace[2 * gridDim.x] = globaltimer_ns();
     }
   }
 }
