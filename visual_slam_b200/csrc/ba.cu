@@ -140,7 +140,7 @@ struct BA {
   bool graph_tried = false;
   cudaStream_t graph_stream = nullptr;
   // system
-  DevBuf<double> Hpl, Ebuf, Hpp, bp, bhat, Hll, bl, Hinv, camp, cam_cost, S, dp, dl, tmp3;
+  DevBuf<double> Hpl, Gbuf, Hpp, bp, bhat, Hll, bl, Hinv, Wfac, camp, cam_cost, S, dp, dl, tmp3;
   DevBuf<double> unit_partial, seg_extra_dense, extra, bp_extra, scale_cost, scale_partial, res, p_glob, w_loc, part;
   DevBuf<unsigned> bar;
   DevBuf<int> pcg_flags;  // [0] fail flag, [1] status, [2] iters
@@ -375,6 +375,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   B.cams_in_smem = (C <= kCamSmemMax) ? 1 : 0;
   B.lin_smem = std::max((size_t)kLinCamSmem,
                         B.cams_in_smem ? (size_t)C * kCamTabStride * sizeof(double) : 0);
+  BA_TRY(cudaFuncSetAttribute(ba_schur_units, cudaFuncAttributeMaxDynamicSharedMemorySize, kSchurSmem));
   BA_TRY(cudaFuncSetAttribute(ba_linearize_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)(kCamSmemMax * kCamTabStride * sizeof(double))));
   {
@@ -413,9 +414,9 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   for (int s = 0; s < 2; ++s) {
     BA_TRY(B.cams[s].alloc((size_t)C * 7)); BA_TRY(B.pts[s].alloc((size_t)P * 3)); BA_TRY(B.camrt[s].alloc(C));
   }
-  BA_TRY(B.Hpl.alloc((size_t)N * 18)); BA_TRY(B.Ebuf.alloc((size_t)N * 18));
+  BA_TRY(B.Hpl.alloc((size_t)N * 18)); BA_TRY(B.Gbuf.alloc((size_t)N * 18));
   BA_TRY(B.Hpp.alloc((size_t)Cf * 36)); BA_TRY(B.bp.alloc(B.n)); BA_TRY(B.bhat.alloc(B.n));
-  BA_TRY(B.Hll.alloc((size_t)Pf * 6)); BA_TRY(B.bl.alloc((size_t)Pf * 3)); BA_TRY(B.Hinv.alloc((size_t)Pf * 6));
+  BA_TRY(B.Hll.alloc((size_t)Pf * 6)); BA_TRY(B.bl.alloc((size_t)Pf * 3)); BA_TRY(B.Hinv.alloc((size_t)Pf * 6)); BA_TRY(B.Wfac.alloc((size_t)Pf * 6));
   BA_TRY(B.camp.alloc(std::max((size_t)C * B.max_chunks, (size_t)B.lin_nA) * kCamVals)); BA_TRY(B.cam_cost.alloc(C));
   BA_TRY(B.S.alloc((size_t)B.n * B.n)); BA_TRY(B.dp.alloc(B.n)); BA_TRY(B.dl.alloc((size_t)Pf * 3));
   BA_TRY(B.tmp3.alloc((size_t)N * 3)); BA_TRY(B.unit_partial.alloc((size_t)B.n_units * 36));
@@ -500,19 +501,19 @@ static int enqueue_linearize(BA& B, cudaStream_t st) {
   return check_launch("ba_linearize");
 }
 
-// Schur complement of the damped system: Hinv, E = Hpl Hinv, bhat, S (sorted-segment reduction).
+// Schur complement of the damped system: Hinv = W W^T, G = Hpl W, bhat, S = Hpp - sum G G^T
+// (sorted-segment reduction).
 static int enqueue_schur(BA& B, cudaStream_t st) {
   const BAView V = B.view();
   const LMState* lm = B.lm.p;
   dim3 grid(B.max_chunks, B.C);
   if (B.Pf) {
-    ba_point_invert<<<(B.Pf + 127) / 128, 128, 0, st>>>(lm, B.Pf, B.Hll.p, B.Hinv.p);
-    ba_compute_E<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.Hinv.p, B.bl.p, B.Ebuf.p, B.camp.p);
+    ba_point_invert<<<(B.Pf + 127) / 128, 128, 0, st>>>(lm, B.Pf, B.Hll.p, B.Hinv.p, B.Wfac.p);
+    ba_compute_G<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.Wfac.p, B.bl.p, B.Gbuf.p, B.camp.p);
     ba_bhat_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp.p, B.bhat.p);
     if (B.n_units)
-      ba_schur_units<<<(B.n_units * 32 + 127) / 128, 128, 0, st>>>(lm, B.Ebuf.p, B.Hpl.p, B.item_a.p, B.item_b.p,
-                                                                B.unit_start.p, B.unit_len.p, B.n_units,
-                                                                B.unit_partial.p);
+      ba_schur_units<<<(B.n_units + kSchurWarps - 1) / kSchurWarps, kSchurWarps * 32, kSchurSmem, st>>>(
+          lm, B.Gbuf.p, B.item_a.p, B.item_b.p, B.unit_start.p, B.unit_len.p, B.n_units, B.unit_partial.p);
   } else if (B.n) {
     BA_TRY(cudaMemcpyAsync(B.bhat.p, B.bp.p, (size_t)B.n * sizeof(double), cudaMemcpyDeviceToDevice, st));
   }

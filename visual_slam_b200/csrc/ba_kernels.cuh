@@ -721,8 +721,10 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
   }
 }
 
+// Per free point: Hinv = (Hll + lambda I)^-1 (back-substitution) and the upper-triangular factor W
+// with W W^T = Hinv (W = C^-T, C the Cholesky factor of Hll + lambda I), stored (00 01 02 11 12 22).
 __global__ void ba_point_invert(const LMState* __restrict__ st, int Pf, const double* __restrict__ Hll,
-                                double* __restrict__ Hinv) {
+                                double* __restrict__ Hinv, double* __restrict__ Wf) {
   if (st->done) return;
   const double lambda = st->lambda;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -734,12 +736,28 @@ __global__ void ba_point_invert(const LMState* __restrict__ st, int Pf, const do
   sym3_inverse(h, o);
 #pragma unroll
   for (int j = 0; j < 6; ++j) Hinv[6 * (size_t)p + j] = o[j];
+  // Cholesky h = C C^T (lower), then Cinv; W = Cinv^T
+  const double c00 = sqrt(h[0]);
+  const double i00 = 1.0 / c00;
+  const double c10 = h[1] * i00, c20 = h[2] * i00;
+  const double c11 = sqrt(h[3] - c10 * c10);
+  const double i11 = 1.0 / c11;
+  const double c21 = (h[4] - c20 * c10) * i11;
+  const double c22 = sqrt(h[5] - c20 * c20 - c21 * c21);
+  const double i22 = 1.0 / c22;
+  // Cinv (lower): rows (i00, 0, 0), (-c10 i00 i11, i11, 0), ((c10 c21 i11 - c20) i00 i22, -c21 i11 i22, i22)
+  const double m10 = -c10 * i00 * i11;
+  const double m21 = -c21 * i11 * i22;
+  const double m20 = -(c20 * i00 + c21 * m10) * i22;
+  double* w = Wf + 6 * (size_t)p;    // W[k][j] = Cinv[j][k], j >= k
+  w[0] = i00; w[1] = m10; w[2] = m20; w[3] = i11; w[4] = m21; w[5] = i22;
 }
 
-// E = Hpl * Hinv per observation (camera-major) and the per-camera partial of sum E * bl.
+// G = Hpl * W per observation (camera-major), so that Hpl Hinv Hpl^T = G G^T, and the per-camera
+// partial of sum Hpl Hinv bl = sum G (W^T bl).
 __global__ void __launch_bounds__(kCamThreads)
-ba_compute_E(BAView V, const double* __restrict__ Hpl, const double* __restrict__ Hinv,
-             const double* __restrict__ bl, double* __restrict__ Eout, double* __restrict__ camp) {
+ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict__ Wf,
+             const double* __restrict__ bl, double* __restrict__ Gout, double* __restrict__ camp) {
   __shared__ double red[(kCamThreads / 32) * 6];
   if (V.st->done) return;
   const int c = blockIdx.y, chunk = blockIdx.x;
@@ -750,18 +768,25 @@ ba_compute_E(BAView V, const double* __restrict__ Hpl, const double* __restrict_
   for (int o = start + threadIdx.x; o < end; o += kCamThreads) {
     const int pcol = V.pt_col[V.cm_pt[o]];
     if (pcol < 0) continue;
-    double h[18], hi[6], b[3], e[18];
+    double h[18], w[6], b[3], g[18];
     load18(Hpl + (size_t)o * 18, h);
 #pragma unroll
-    for (int j = 0; j < 6; ++j) hi[j] = Hinv[6 * (size_t)pcol + j];
+    for (int j = 0; j < 6; ++j) w[j] = Wf[6 * (size_t)pcol + j];
 #pragma unroll
     for (int j = 0; j < 3; ++j) b[j] = bl[3 * (size_t)pcol + j];
+    // y = W^T bl  (W upper: 00 01 02 11 12 22)
+    const double y0 = w[0] * b[0];
+    const double y1 = w[1] * b[0] + w[3] * b[1];
+    const double y2 = w[2] * b[0] + w[4] * b[1] + w[5] * b[2];
 #pragma unroll
     for (int r = 0; r < 6; ++r) {
-      sym3_mul(hi, &h[3 * r], &e[3 * r]);  // row r of Hpl times symmetric Hinv
-      acc[r] += e[3 * r] * b[0] + e[3 * r + 1] * b[1] + e[3 * r + 2] * b[2];
+      const double h0 = h[3 * r], h1 = h[3 * r + 1], h2 = h[3 * r + 2];
+      g[3 * r] = h0 * w[0];
+      g[3 * r + 1] = h0 * w[1] + h1 * w[3];
+      g[3 * r + 2] = h0 * w[2] + h1 * w[4] + h2 * w[5];
+      acc[r] += g[3 * r] * y0 + g[3 * r + 1] * y1 + g[3 * r + 2] * y2;
     }
-    store18(Eout + (size_t)o * 18, e);
+    store18(Gout + (size_t)o * 18, g);
   }
   block_reduce<6, kCamThreads>(acc, red);
   if (threadIdx.x == 0) {
@@ -771,7 +796,7 @@ ba_compute_E(BAView V, const double* __restrict__ Hpl, const double* __restrict_
   }
 }
 
-// bhat = bp - sum_j E_j bl_j   (ordered chunk sum)
+// bhat = bp - sum_j Hpl_j Hinv_j bl_j   (ordered chunk sum)
 __global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp,
                                  const double* __restrict__ bp, double* __restrict__ bhat) {
   const int c = blockIdx.x, i = threadIdx.x;
@@ -784,30 +809,84 @@ __global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp,
   bhat[6 * col + i] = bp[6 * col + i] - s;
 }
 
-// Schur work units: one warp reduces <= kUnitItems products E_a * Hpl_b^T of one (cam a, cam b) key.
-__global__ void __launch_bounds__(128)
-ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ E, const double* __restrict__ Hpl,
+// Schur work units: one warp reduces <= kUnitItems products G_a * G_b^T of one (cam a, cam b) key,
+// one item per lane and round.  The 64 blocks of a round (144 B each, scattered in HBM) are fetched
+// COOPERATIVELY: consecutive lanes copy consecutive 16-byte pieces of a block with cp.async (LDGSTS),
+// so one instruction touches ~5 lines instead of 32, into a kSchurStages-deep ring in shared memory
+// (lane-per-block reads at 144 B stride are conflict-free).  Item indices are prefetched one round
+// further ahead.  (One bulk async copy per block was measured slower: the TMA unit retires about one
+// small copy per 15 cycles per SM.)
+constexpr int kSchurStages = 3;
+constexpr int kSchurWarps = 4;
+constexpr int kSchurStageDoubles = 2 * 32 * 18;   // A blocks [32][18] then B blocks [32][18]
+constexpr int kSchurSmem = kSchurWarps * kSchurStages * kSchurStageDoubles * 8;
+
+__global__ void __launch_bounds__(kSchurWarps * 32, 2)
+ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
                const int* __restrict__ item_a, const int* __restrict__ item_b,
                const int* __restrict__ unit_start, const int* __restrict__ unit_len, int n_units,
                double* __restrict__ partial) {
-  const int u = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
+  extern __shared__ __align__(128) double sch_smem[];
+  const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int u = blockIdx.x * kSchurWarps + wid;
   if (st->done || u >= n_units) return;
-  const int s = unit_start[u], len = unit_len[u];
+  double* ring = sch_smem + (size_t)wid * kSchurStages * kSchurStageDoubles;
+  const int s0 = unit_start[u], len = unit_len[u];
+  const int n_it = (len + 31) >> 5;
+  auto load_idx = [&](int it, int& ia, int& ib) {
+    const int i = it * 32 + lane;
+    ia = -1; ib = -1;
+    if (it < n_it && i < len) { ia = item_a[s0 + i]; ib = item_b[s0 + i]; }
+  };
+  auto issue = [&](int it, int ia, int ib) {   // round `it` -> stage it % kSchurStages
+    if (it < n_it) {
+      double* stg = ring + (it % kSchurStages) * kSchurStageDoubles;
+#pragma unroll
+      for (int j = 0; j < 18; ++j) {
+        const int q = j * 32 + lane;                 // 16-byte piece of the stage
+        const int b = (q * 7282) >> 16;              // q / 9: block 0..63 (A blocks, then B blocks)
+        const int r = q - 9 * b;
+        const int idx = __shfl_sync(0xffffffffu, j < 9 ? ia : ib, b & 31);
+        if (idx >= 0) cp_async16(stg + 2 * q, G + (size_t)idx * 18 + 2 * r);
+      }
+    }
+    cp_async_commit();
+  };
+  int ia_n, ib_n;
+  {
+    int ia[kSchurStages], ib[kSchurStages];
+#pragma unroll
+    for (int s = 0; s < kSchurStages; ++s) load_idx(s, ia[s], ib[s]);
+    load_idx(kSchurStages, ia_n, ib_n);
+#pragma unroll
+    for (int s = 0; s < kSchurStages; ++s) issue(s, ia[s], ib[s]);
+  }
   double acc[36];
 #pragma unroll
   for (int i = 0; i < 36; ++i) acc[i] = 0.0;
-  for (int i = lane; i < len; i += 32) {
-    double ea[18], hb[18];
-    load18(E + (size_t)item_a[s + i] * 18, ea);
-    load18(Hpl + (size_t)item_b[s + i] * 18, hb);
+#pragma unroll 1
+  for (int it = 0; it < n_it; ++it) {
+    const int i = it * 32 + lane;
+    const double* stg = ring + (it % kSchurStages) * kSchurStageDoubles;
+    cp_async_wait<kSchurStages - 1>();
+    __syncwarp();                                    // every lane's pieces of this round have landed
+    if (i < len) {
+      double ga[18], gb[18];
+      load18(stg + lane * 18, ga);
+      load18(stg + 32 * 18 + lane * 18, gb);
 #pragma unroll
-    for (int r = 0; r < 6; ++r) {
+      for (int r = 0; r < 6; ++r) {
 #pragma unroll
-      for (int c = 0; c < 6; ++c)
-        acc[6 * r + c] += ea[3 * r] * hb[3 * c] + ea[3 * r + 1] * hb[3 * c + 1] +
-                          ea[3 * r + 2] * hb[3 * c + 2];
+        for (int c = 0; c < 6; ++c)
+          acc[6 * r + c] = fma(ga[3 * r], gb[3 * c], fma(ga[3 * r + 1], gb[3 * c + 1],
+                           fma(ga[3 * r + 2], gb[3 * c + 2], acc[6 * r + c])));
+      }
     }
+    // refill this stage with round it + kSchurStages (indices arrived a round ago)
+    const int ia_u = ia_n, ib_u = ib_n;
+    load_idx(it + kSchurStages + 1, ia_n, ib_n);
+    __syncwarp();                                    // all lanes are done reading the stage
+    issue(it + kSchurStages, ia_u, ib_u);
   }
 #pragma unroll
   for (int i = 0; i < 36; ++i) acc[i] = warp_sum(acc[i]);
