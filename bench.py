@@ -26,6 +26,11 @@ sys.path.insert(0, ROOT)
 PAIRS_PER_GPU = 1184          # 8 x 148: 4736 CTAs of 512 queries each
 NQ = NT = 2048
 RATIO = 0.8
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures
+HAMMING_DRAM_BYTES_PER_PAIR = (83026176 + 4331264) / 592.0
+HAMMING_TRAFFIC_SOURCE = "profiles/r1_hamming_knn2_ncu_full.txt (592 pairs per launch, scaled to this launch)"
+BA_LIN_DRAM_BYTES_C4 = 44561920 + 94828288
+BA_LIN_TRAFFIC_SOURCE = "profiles/r1_ba_linearize_ncu_full.txt (C4, one launch; part of Hpl is still dirty in L2)"
 METRIC = "hamming_matches_per_s"
 UNIT = "query descriptors matched/s (kNN-2 + ratio + cross-check, 2048x2048x256-bit pairs)"
 
@@ -166,23 +171,20 @@ def ba_figures(torch):
             ms = e0.elapsed_time(e1)
             if rep > 0:
                 best = ms if best is None else min(best, ms)
-        # linearisation alone (buildSystem), flushing L2 between repetitions
+        # the fused linearisation kernel alone (buildSystem): CUDA events recorded by the library on the
+        # launching stream right around the kernel, L2 flushed (256 MB overwrite) before every launch
         flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
-        lin_ms = []
-        for rep in range(6):
-            flush.zero_()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            eng.linearize()
-            e1.record()
-            torch.cuda.synchronize()
-            if rep > 0:
-                lin_ms.append(e0.elapsed_time(e1))
-        lin = float(np.median(lin_ms))
+        eng.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
+        lin0 = eng.linearize()
+        eng.trial(1e-5 * lin0["max_diag"])
+        lin = float(np.median(eng.time_stage("linearize", 8, flush)[1:]))
+        schur_ms = float(np.median(eng.time_stage("schur", 6, flush)[1:]))
+        trial_ms = float(np.median(eng.time_stage("trial", 6, flush)[1:]))
         out[name] = {"lm_iters_per_s": st["iterations"] / (best * 1e-3), "ms_per_optimize10": best,
                      "trials": st["trials"], "pcg_iterations": st["pcg_iterations"],
                      "final_cost": st["final_cost"], "n_cams": p.n_cams, "n_pts": p.n_pts, "n_obs": p.n_obs,
-                     "linearize_ms": lin, "linearize_bytes": p.linearize_bytes(),
+                     "linearize_ms": lin, "schur_ms": schur_ms, "trial_ms": trial_ms,
+                     "linearize_bytes": p.linearize_bytes(),
                      "linearize_gbs": p.linearize_bytes() / (lin * 1e-3) / 1e9}
         eng.close()
         del flush
@@ -352,7 +354,8 @@ def run_gpu(args):
     achieved = popc_per_launch / (knn_ms * 1e-3) / 1e9
     roofline = {"bound": "alu-popc (integer pipe; SURVEY 8d: 8 popc.b32 per 256-bit pair distance)",
                 "kernel": "hamming_knn2_kernel", "achieved": achieved, "peak": probe.value / 1e9,
-                "unit": "Gpopc/s", "frac": achieved / (probe.value / 1e9), "traffic": None,
+                "unit": "Gpopc/s", "frac": achieved / (probe.value / 1e9),
+                "traffic": HAMMING_DRAM_BYTES_PER_PAIR * B, "traffic_source": HAMMING_TRAFFIC_SOURCE,
                 "peak_source": "vslam_microbench_popc measured in this run (MEASURED_PEAKS.json has no "
                                "integer-pipe entry)",
                 "note": "frac > 1 is expected: the kernel needs 4 POPC + 16 LOP3 per pair distance "
@@ -376,9 +379,12 @@ def run_gpu(args):
             ba = ba_figures(torch)
             line["ba"] = ba
             hbm = peaks.get("hbm_gbs", 6650.0)
-            line["roofline_ba"] = {"bound": "hbm", "kernel": "ba_cam_pass+ba_point_pass (linearise, C4)",
+            line["roofline_ba"] = {"bound": "hbm", "kernel": "ba_linearize_kernel<false> (fused linearisation, C4)",
                                    "achieved": ba["c4"]["linearize_gbs"], "peak": hbm, "unit": "GB/s",
-                                   "frac": ba["c4"]["linearize_gbs"] / hbm, "traffic": None,
+                                   "frac": ba["c4"]["linearize_gbs"] / hbm,
+                                   "algorithmic_bytes": ba["c4"]["linearize_bytes"],
+                                   "traffic": BA_LIN_DRAM_BYTES_C4, "traffic_source": BA_LIN_TRAFFIC_SOURCE,
+                                   "kernel_ms": ba["c4"]["linearize_ms"],
                                    "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)"}
     print(json.dumps(line))
     if world > 1:
