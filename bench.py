@@ -262,6 +262,10 @@ def run_gpu(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL_DEBUG=VERSION (set in some images) makes NCCL print its version on STDOUT, next to the one
+        # JSON line the driver parses; anything the user asked for explicitly (INFO, TRACE) is kept
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     lib = _cabi.lib()
     B = PAIRS_PER_GPU
