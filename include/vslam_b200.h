@@ -198,6 +198,23 @@ int vslam_recover_pose(const double* E, const float* p1, const float* p2, const 
                        int batch, const double* K, double distance_thresh, double* R, double* t,
                        uint8_t* mask, double* tri, int32_t* good, void* stream);
 
+/*
+ * Batched two-view triangulation + cheirality/depth filter: the per-point loop of
+ * reference src/v2/helper_functions.py:281-291 (`triangulate`: rows u*P[2]-P[0], v*P[2]-P[1] of both
+ * views, np.linalg.svd, vt[3]) and the filter that follows it at src/v2/main.py:284-306.
+ *   proj  dev f64 [batch][2][12]  the two 3x4 projection matrices (row-major)
+ *   extr  dev f64 [batch][2][12]  world->camera 3x4 matrices for the depth test, or NULL (then depth
+ *                                 and good must be NULL)
+ *   x1,x2 dev f64 [batch][n_max][2] pixel coordinates;  n_pts dev i32 [batch]
+ *   Xh    dev f64 [batch][n_max][4] unit homogeneous point (sign: largest component positive; the
+ *                                   reference's sign is LAPACK's, callers divide by w at main.py:285)
+ *   X3    dev f64 [batch][n_max][3] Xh[:3]/Xh[3] (may be NULL);  depth dev f64 [batch][n_max][2] (may be NULL)
+ *   good  dev u8  [batch][n_max]    1 iff 0 < z1 < z_max and 0 < z2 < z_max (main.py:306 uses z_max = 1)
+ */
+int vslam_triangulate(const double* proj, const double* extr, const double* x1, const double* x2,
+                      const int32_t* n_pts, int n_max, int batch, double z_max, double* Xh, double* X3,
+                      double* depth, uint8_t* good, void* stream);
+
 /* ------------------------------------------------------------------------- */
 /* 3. Bundle adjustment                                                       */
 /* ------------------------------------------------------------------------- */

@@ -1,0 +1,91 @@
+"""Two-view triangulation: oracle vs the reference's own outputs (CPU), CUDA kernel vs oracle (GPU)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import triangulate as otri
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "triangulate_ref.npz")
+
+
+def _cases():
+    g = np.load(GOLD)
+    for c in range(3):
+        yield {k: g["%s_%d" % (k, c)] for k in ("P1", "P2", "T1", "T2", "x1", "x2", "tri")}
+
+
+def _dehom(X):
+    return X[:, :3] / X[:, 3:]
+
+
+def test_oracle_reproduces_reference_outputs():
+    for c in _cases():
+        mine = otri.triangulate(c["P1"], c["P2"], c["x1"], c["x2"])
+        # same LAPACK underneath: identical up to the sign convention of the singular vector
+        s = np.sign(np.sum(mine * c["tri"], axis=1))[:, None]
+        assert np.abs(mine * s - c["tri"]).max() < 1e-12
+
+
+def test_filter_matches_reference_expression():
+    c = list(_cases())[2]
+    X3, depth, good = otri.dehomogenise_and_filter(c["tri"], c["T1"], c["T2"])
+    X = c["tri"] / c["tri"][:, 3:]
+    proj1 = np.vstack([c["T1"], [0, 0, 0, 1]]) @ X.T
+    proj2 = np.vstack([c["T2"], [0, 0, 0, 1]]) @ X.T
+    ref = np.where((proj1[2] > 0) & (proj2[2] > 0) & (proj2[2] < 1) & (proj1[2] < 1))[0]   # main.py:306
+    assert np.array_equal(np.nonzero(good)[0], ref)
+    assert 0 < len(ref) < len(X)
+
+
+@pytest.mark.gpu
+def test_kernel_matches_reference_and_oracle():
+    from visual_slam_b200.triangulate import triangulate, triangulate_and_filter
+    for c in _cases():
+        Xh = triangulate(c["P1"], c["P2"], c["x1"], c["x2"])
+        assert Xh.shape == c["tri"].shape
+        assert np.abs(np.linalg.norm(Xh, axis=1) - 1).max() < 1e-12
+        ref = _dehom(c["tri"])
+        assert np.abs(_dehom(Xh) - ref).max() <= 1e-9 * max(1.0, np.abs(ref).max())
+        X3, idx = triangulate_and_filter(c["P1"], c["P2"], c["T1"], c["T2"], c["x1"], c["x2"])
+        _, _, good = otri.dehomogenise_and_filter(c["tri"], c["T1"], c["T2"])
+        assert np.array_equal(idx, np.nonzero(good)[0])
+        assert np.abs(X3 - ref).max() <= 1e-9 * max(1.0, np.abs(ref).max())
+
+
+@pytest.mark.gpu
+def test_batched_ragged_and_empty():
+    import torch
+    from visual_slam_b200.triangulate import triangulate_batch
+    cs = list(_cases())
+    n_max = max(len(c["x1"]) for c in cs)
+    B = len(cs) + 1                      # last pair is empty
+    proj = np.zeros((B, 2, 3, 4)); extr = np.zeros((B, 2, 3, 4))
+    x1 = np.zeros((B, n_max, 2)); x2 = np.zeros((B, n_max, 2)); n = np.zeros(B, dtype=np.int32)
+    for b, c in enumerate(cs):
+        k = len(c["x1"])
+        proj[b, 0], proj[b, 1], extr[b, 0], extr[b, 1] = c["P1"], c["P2"], c["T1"], c["T2"]
+        x1[b, :k], x2[b, :k], n[b] = c["x1"], c["x2"], k
+    proj[-1] = proj[0]; extr[-1] = extr[0]
+    d = lambda a: torch.from_numpy(a).cuda()
+    Xh, X3, depth, good = triangulate_batch(d(proj), d(x1), d(x2), d(n), d(extr), 1.0)
+    for b, c in enumerate(cs):
+        k = len(c["x1"])
+        ref = _dehom(c["tri"])
+        assert np.abs(X3[b, :k].cpu().numpy() - ref).max() <= 1e-9 * max(1.0, np.abs(ref).max())
+        _, dep, g = otri.dehomogenise_and_filter(c["tri"], c["T1"], c["T2"])
+        assert np.array_equal(good[b, :k].cpu().numpy().astype(bool), g)
+        assert np.abs(depth[b, :k].cpu().numpy() - dep).max() < 1e-8
+        assert not good[b, k:].any()       # padding untouched
+    assert not Xh[-1].any() and not good[-1].any()
+
+
+def test_shape_errors_raise_before_any_device_work():
+    from visual_slam_b200.triangulate import triangulate
+    import torch
+    if not torch.cuda.is_available():
+        with pytest.raises(Exception):
+            triangulate(np.eye(3, 4), np.eye(3, 4), np.zeros((4, 2)), np.zeros((4, 2)))
+    with pytest.raises(ValueError):
+        from visual_slam_b200.triangulate import _one
+        _one(np.eye(4, 4)[:2], np.eye(3, 4), np.zeros((4, 2)), np.zeros((4, 2)), None, 1.0, "cpu")

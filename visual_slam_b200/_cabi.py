@@ -39,6 +39,7 @@ def _declare(lib):
     lib.vslam_essential_select.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, i32, f64, f64, vp, vp, vp, vp,
                                            vp, vp]
     lib.vslam_recover_pose.argtypes = [vp, vp, vp, vp, i32, i32, pd, f64, vp, vp, vp, vp, vp, vp]
+    lib.vslam_triangulate.argtypes = [vp, vp, vp, vp, vp, i32, i32, f64, vp, vp, vp, vp, vp]
     pp = C.POINTER(vp)
     lib.vslam_ba_create.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.vslam_ba_destroy.argtypes = [vp]
