@@ -89,6 +89,18 @@ __global__ void ba_copy_state(const LMState* __restrict__ st, int which, const d
     dst[i] = src[i];
 }
 
+// Public point arrays are [P][3]; the state buffers are padded to [P][4] (see load_point).
+__global__ void ba_pad_points(const double* __restrict__ src, double* __restrict__ dst, int P) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < P) *reinterpret_cast<double4*>(dst + 4 * (size_t)p) = make_double4(src[3 * (size_t)p], src[3 * (size_t)p + 1], src[3 * (size_t)p + 2], 0.0);
+}
+__global__ void ba_unpad_points(const LMState* __restrict__ st, int which, const double* __restrict__ a0,
+                                const double* __restrict__ a1, double* __restrict__ dst, int P) {
+  const double* src = ((st->cur ^ which) & 1) ? a1 : a0;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < P) { dst[3 * (size_t)p] = src[4 * (size_t)p]; dst[3 * (size_t)p + 1] = src[4 * (size_t)p + 1]; dst[3 * (size_t)p + 2] = src[4 * (size_t)p + 2]; }
+}
+
 __global__ void ba_gather_uv(int N, const int* __restrict__ src, const double2* __restrict__ uv,
                              double2* __restrict__ out) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -341,8 +353,13 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     std::vector<int> fp;
     for (int p = 0; p < P; ++p)
       if (pt_col[p] >= 0 && pt_start[p + 1] > pt_start[p]) fp.push_back(p);
+    // ... then by camera list: the 32 points of an item then mostly see the SAME camera in a row, and
+    // equal shared-memory addresses are a broadcast instead of a bank conflict in the camera table
     std::stable_sort(fp.begin(), fp.end(), [&](int a, int b) {
-      return pt_start[a + 1] - pt_start[a] > pt_start[b + 1] - pt_start[b];
+      const int da = pt_start[a + 1] - pt_start[a], db = pt_start[b + 1] - pt_start[b];
+      if (da != db) return da > db;
+      return std::lexicographical_compare(pm_cam.begin() + pt_start[a], pm_cam.begin() + pt_start[a + 1],
+                                          pm_cam.begin() + pt_start[b], pm_cam.begin() + pt_start[b + 1]);
     });
     const int n_it = ((int)fp.size() + 31) / 32;
     item_row.assign(n_it + 1, 0);
@@ -412,7 +429,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(cudaMemset(B.lin_ticket.p, 0, sizeof(unsigned)));
   BA_TRY(B.cm_uv.alloc(N)); BA_TRY(B.scale_meas.alloc(E));
   for (int s = 0; s < 2; ++s) {
-    BA_TRY(B.cams[s].alloc((size_t)C * 7)); BA_TRY(B.pts[s].alloc((size_t)P * 3)); BA_TRY(B.camrt[s].alloc(C));
+    BA_TRY(B.cams[s].alloc((size_t)C * 7)); BA_TRY(B.pts[s].alloc((size_t)P * 4)); BA_TRY(B.camrt[s].alloc(C));   // points padded to 32 bytes
   }
   BA_TRY(B.Hpl.alloc((size_t)N * 18)); BA_TRY(B.Gbuf.alloc((size_t)N * 18));
   BA_TRY(B.Hpp.alloc((size_t)Cf * 36)); BA_TRY(B.bp.alloc(B.n)); BA_TRY(B.bhat.alloc(B.n));
@@ -475,7 +492,7 @@ static int ba_set_state(BA& B, const double* cams, const double* pts, const doub
   ba_lm_reset<<<1, 1, 0, st>>>(B.lm.p, 0, 1);
   ba_lm_poke<<<1, 1, 0, st>>>(B.lm.p, 3, 0.0);
   BA_TRY(cudaMemcpyAsync(B.cams[0].p, cams, (size_t)B.C * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
-  BA_TRY(cudaMemcpyAsync(B.pts[0].p, pts, (size_t)B.P * 3 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  if (B.P) ba_pad_points<<<(B.P + 255) / 256, 256, 0, st>>>(pts, B.pts[0].p, B.P);
   if (B.E) BA_TRY(cudaMemcpyAsync(B.scale_meas.p, scale_meas, (size_t)B.E * sizeof(double), cudaMemcpyDeviceToDevice, st));
   if (B.N) {
     const int blocks = (B.N + 255) / 256;
@@ -671,7 +688,7 @@ extern "C" int vslam_ba_get_state(vslam_ba* h, double* cams, double* pts, void* 
   BA& B = h->impl;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (cams) ba_copy_state<<<64, 256, 0, st>>>(B.lm.p, 0, B.cams[0].p, B.cams[1].p, cams, (size_t)B.C * 7);
-  if (pts && B.P) ba_copy_state<<<148 * 4, 256, 0, st>>>(B.lm.p, 0, B.pts[0].p, B.pts[1].p, pts, (size_t)B.P * 3);
+  if (pts && B.P) ba_unpad_points<<<(B.P + 255) / 256, 256, 0, st>>>(B.lm.p, 0, B.pts[0].p, B.pts[1].p, pts, B.P);
   return check_launch("ba_copy_state");
 }
 
@@ -827,8 +844,8 @@ extern "C" int vslam_ba_read(vslam_ba* h, int what, double* dst, int64_t capacit
     case 9:
       n = (size_t)B.P * 3;
       if ((int64_t)n > capacity) return VSLAM_ERR_BAD_ARG;
-      ba_copy_state<<<148 * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(B.lm.p, 1, B.pts[0].p, B.pts[1].p, dst, n);
-      return check_launch("ba_copy_state");
+      ba_unpad_points<<<(B.P + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(B.lm.p, 1, B.pts[0].p, B.pts[1].p, dst, B.P);
+      return check_launch("ba_unpad_points");
     default: return VSLAM_ERR_BAD_ARG;
   }
   if ((int64_t)n > capacity) return VSLAM_ERR_BAD_ARG;

@@ -179,11 +179,9 @@ constexpr int kLinObs = 8;
 constexpr int kLinChunk = kLinThreads * kLinObs;
 constexpr int kStageDoubles = 32 * 18;          // one warp's 32 Hpl blocks (4608 B)
 constexpr bool kBulkStore = true;               // Hpl stage -> HBM by bulk async store (else LDS + STG.128)
-constexpr int kRing = 3;                        // input ring depth (observations in flight per thread)
-constexpr int kRingDoubles = 32 * 5;            // one warp-observation of inputs: X[32][3] + uv[32][2]
 constexpr int kHplStages = 1;                   // Hpl stages per warp
-constexpr int kLinCamSmem = kLinWarps * (kHplStages * kStageDoubles + kRing * kRingDoubles) * 8;
-constexpr int kLinCostSmem = kLinWarps * kRing * kRingDoubles * 8;                     // cost-only launch: ring only   // camera-role bytes
+constexpr int kLinCamSmem = kLinWarps * kHplStages * kStageDoubles * 8;   // camera-role bytes
+constexpr int kLinCostSmem = 0;                  // the cost-only launch stages nothing   // camera-role bytes
 constexpr int kPtRowsPerWarp = 8;               // ELL rows a point-role warp aims for
 constexpr int kCamTabStride = 14;               // doubles per camera in the point role's table (112 B)
 constexpr int kCamSmemMax = 1800;               // cameras kept in shared memory by the point role
@@ -243,6 +241,13 @@ __device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// One point = one 32-byte sector of the padded state array [P][4]: a single 256-bit load (LDG.E.256)
+// instead of three 8-byte loads that each cost a pass through the L1 data pipe per distinct line.
+__device__ __forceinline__ void load_point(const double* __restrict__ pts4, int p, double (&X)[3]) {
+  double pad;
+  asm volatile("ld.global.v4.f64 {%0, %1, %2, %3}, [%4];"
+               : "=d"(X[0]), "=d"(X[1]), "=d"(X[2]), "=d"(pad) : "l"(pts4 + 4 * (size_t)p));
+}
 __device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -423,54 +428,33 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
     double v[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = 0.0;
-    // Inputs travel through a per-warp ring in shared memory filled by cp.async (LDGSTS): the point
-    // index is loaded kRing + 1 observations ahead (register), the point and its measurement kRing
-    // observations ahead (shared memory), so a memory round trip of a microsecond stays hidden and no
-    // registers are held across it.
-    const int o0 = start + tid;
-    double* ring = dyn_smem + wid * (kRing * kRingDoubles);
-    // Hpl stages of this warp; absent in the cost-only launch
-    double* ws0 = dyn_smem + kLinWarps * kRing * kRingDoubles + wid * (kHplStages * kStageDoubles);
-    auto issue = [&](int k, int p) {   // observation k of this thread -> ring slot k % kRing
-      const int o = o0 + k * kLinThreads;
-      if (k < kLinObs && o < end) {
-        double* slot = ring + (k % kRing) * kRingDoubles;
-        const double* px = pts + 3 * (size_t)p;
-        cp_async8(slot + lane * 3, px); cp_async8(slot + lane * 3 + 1, px + 1); cp_async8(slot + lane * 3 + 2, px + 2);
-        cp_async16(slot + 96 + lane * 2, V.cm_uv + o);
-      }
-      cp_async_commit();
-    };
+    // two-stage software pipeline (warps issue in order, so a dependent address must never be
+    // computed right after its index load): the point INDEX is loaded two observations ahead, the
+    // point itself (one 256-bit load) and its measurement one observation ahead; both are in flight
+    // under the current arithmetic.
+    int o = start + tid;
+    double X[3] = {0.0, 0.0, 1.0};
+    double2 uv = make_double2(0.0, 0.0);
     int p_next = 0;
-    {
-      int pk[kRing + 1];
-#pragma unroll
-      for (int k = 0; k <= kRing; ++k) {
-        const int o = o0 + k * kLinThreads;
-        pk[k] = (k < kLinObs && o < end) ? V.cm_pt[o] : 0;
-      }
-#pragma unroll
-      for (int k = 0; k < kRing; ++k) issue(k, pk[k]);
-      p_next = pk[kRing];
+    if (o + kLinThreads < end) p_next = V.cm_pt[o + kLinThreads];
+    if (o < end) {
+      const int p = V.cm_pt[o];
+      uv = V.cm_uv[o];
+      load_point(pts, p, X);
     }
+    double* ws0 = dyn_smem + wid * (kHplStages * kStageDoubles);
     __syncthreads();
 #pragma unroll 1
     for (int k = 0; k < kLinObs; ++k) {
-      const int o = o0 + k * kLinThreads;
       const bool valid = o < end;
-      cp_async_wait<kRing - 1>();                       // this thread's slot k has landed
-      double Xc[3] = {0.0, 0.0, 1.0};
-      double2 uvc = make_double2(0.0, 0.0);
-      if (valid) {
-        const double* slot = ring + (k % kRing) * kRingDoubles;
-        Xc[0] = slot[lane * 3]; Xc[1] = slot[lane * 3 + 1]; Xc[2] = slot[lane * 3 + 2];
-        uvc = *reinterpret_cast<const double2*>(slot + 96 + lane * 2);
-      }
-      {
-        const int p_use = p_next;                       // index of observation k + kRing
-        const int o2 = o0 + (k + kRing + 1) * kLinThreads;
-        if (k + kRing + 1 < kLinObs && o2 < end) p_next = V.cm_pt[o2];
-        issue(k + kRing, p_use);                        // refills the slot just read
+      const double Xc[3] = {X[0], X[1], X[2]};
+      const double2 uvc = uv;
+      const int o_next = o + kLinThreads;
+      const int p_cur = p_next;
+      if (k + 2 < kLinObs && o_next + kLinThreads < end) p_next = V.cm_pt[o_next + kLinThreads];
+      if (k + 1 < kLinObs && o_next < end) {   // p_cur arrived during the previous observation
+        uv = V.cm_uv[o_next];
+        load_point(pts, p_cur, X);
       }
       const bool want_hpl = !COST_ONLY && cam_free;
       double* ws = ws0 + (k % kHplStages) * kStageDoubles;
@@ -556,6 +540,7 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
           for (int i = lane; i < n_blk * 9; i += 32) dst[i] = srcp[i];
         }
       }
+      o = o_next;
     }
     // chunk partial: 28 values
     if (COST_ONLY) {
@@ -625,7 +610,7 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
           row_n = row1; row_n1 = A.item_row[it + 2]; p_n = A.ell_pt[(size_t)(it + 1) * 32 + lane];
         }
         double X[3] = {0.0, 0.0, 1.0};
-        if (p >= 0) { X[0] = pts[3 * p]; X[1] = pts[3 * p + 1]; X[2] = pts[3 * p + 2]; }
+        if (p >= 0) load_point(pts, p, X);
         double acc[9];
 #pragma unroll
         for (int j = 0; j < 9; ++j) acc[j] = 0.0;
@@ -962,7 +947,7 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
   double sc[1] = {0.0};
   if (p < V.P) {
     const int col = V.pt_col[p];
-    double X[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
+    double X[3] = {pts[4 * (size_t)p], pts[4 * (size_t)p + 1], pts[4 * (size_t)p + 2]};
     if (col >= 0) {
       double r[3] = {bl[3 * (size_t)col], bl[3 * (size_t)col + 1], bl[3 * (size_t)col + 2]};
       const double b0 = r[0], b1 = r[1], b2 = r[2];
@@ -978,7 +963,7 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
       X[0] += d[0]; X[1] += d[1]; X[2] += d[2];
       dl_out[3 * (size_t)col] = d[0]; dl_out[3 * (size_t)col + 1] = d[1]; dl_out[3 * (size_t)col + 2] = d[2];
     }
-    pts_trial[3 * p] = X[0]; pts_trial[3 * p + 1] = X[1]; pts_trial[3 * p + 2] = X[2];
+    *reinterpret_cast<double4*>(pts_trial + 4 * (size_t)p) = make_double4(X[0], X[1], X[2], 0.0);
   }
   block_reduce<1, 256>(sc, red);
   if (threadIdx.x == 0) scale_partial[blockIdx.x] = sc[0];
