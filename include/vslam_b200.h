@@ -255,10 +255,11 @@ int vslam_ba_optimize(vslam_ba* ba, int max_iterations, double* stats8, void* st
 /* The stages of one LM iteration, exposed for parity tests and profiling. */
 /* buildSystem(): out2 (host) = {robust cost, max |diag H|}.  Synchronises the stream. */
 int vslam_ba_linearize(vslam_ba* ba, double* out2, void* stream);
-/* Profiling: times `reps` launches of one stage with CUDA events recorded on `stream` around the
- * stage's own kernels: 0 = fused linearisation kernel (buildSystem), 1 = Schur assembly, 2 = one whole
- * LM trial.  flush_buf/flush_bytes (device, may be NULL/0) are overwritten before each launch to evict
- * L2.  ms_out[reps] on the host.  Synchronises the stream. */
+/* Profiling: times one stage with CUDA events recorded on `stream` around the stage's own kernels:
+ * 0 = fused linearisation kernel (buildSystem), 1 = Schur assembly, 2 = one whole LM trial: each of the
+ * `reps` launches bracketed on its own after flush_buf/flush_bytes (device, may be NULL/0) are
+ * overwritten to evict L2, ms_out[reps];  3 = the fused linearisation kernel `reps` times back to back
+ * between one pair of events, ms_out[0] = average per launch.  ms_out on the host.  Synchronises. */
 int vslam_ba_time_stage(vslam_ba* ba, int stage, int reps, void* flush_buf, int64_t flush_bytes,
                         float* ms_out, void* stream);
 /* Profiling: one linearisation with per-CTA %globaltimer stamps; out[3*i..] (host) = {kind (0 camera

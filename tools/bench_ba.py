@@ -44,5 +44,7 @@ for name in which:
         msw = eng.time_stage(stage, 6, None)[1:]
         extra = " (%.1f GB/s algorithmic cold)" % (p.linearize_bytes() / (np.median(ms) * 1e-3) / 1e9) if stage == "linearize" else ""
         print("  %-9s cold %.1f us  warm %.1f us%s" % (stage, np.median(ms) * 1e3, np.median(msw) * 1e3, extra))
+    b2b = eng.time_stage("linearize_back_to_back", 20)[0]
+    print("  linearize back-to-back x20: %.1f us per launch (%.1f GB/s algorithmic)" % (b2b * 1e3, p.linearize_bytes() / (b2b * 1e-3) / 1e9))
     del flush
     eng.close()

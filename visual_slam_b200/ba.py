@@ -85,13 +85,13 @@ class BAEngine:
     def time_stage(self, stage, reps=5, flush=None):
         """CUDA-event times (ms) of `reps` launches of one stage: "linearize" (the fused kernel alone),
         "schur" or "trial"; `flush` is an optional device tensor overwritten before each launch (L2)."""
-        code = {"linearize": 0, "schur": 1, "trial": 2}[stage]
+        code = {"linearize": 0, "schur": 1, "trial": 2, "linearize_back_to_back": 3}[stage]
         out = (C.c_float * reps)()
         with torch.cuda.device(self.device):
             _cabi.check(_cabi.lib().vslam_ba_time_stage(
                 self._h, code, int(reps), _cabi.ptr(flush) if flush is not None else None,
                 flush.numel() * flush.element_size() if flush is not None else 0, out, _cabi.stream_ptr()))
-        return list(out)
+        return list(out)[:1] if code == 3 else list(out)
 
     def trace_linearize(self):
         """Per-CTA (kind, start_ns, end_ns) of one fused linearisation launch (profiling)."""

@@ -18,14 +18,15 @@ __global__ void __launch_bounds__(256)
 ba_trial_controller(LMState* __restrict__ st, int C, const double* __restrict__ cam_cost,
                     const double* __restrict__ scale_cost, int n_sp,
                     const double* __restrict__ scale_partial, int n, const double* __restrict__ dp,
-                    const double* __restrict__ bp, const int* __restrict__ pcg_status,
+                    const double* __restrict__ bp, const double* __restrict__ bp_extra,
+                    const int* __restrict__ pcg_status,
                     const int* __restrict__ pcg_iters) {
   __shared__ double red[16];
   if (st->done) return;
   const double lambda = st->lambda;
   double v[2] = {0.0, 0.0};
   for (int i = threadIdx.x; i < C; i += 256) v[0] += cam_cost[i];
-  for (int i = threadIdx.x; i < n; i += 256) v[1] += dp[i] * (lambda * dp[i] + bp[i]);
+  for (int i = threadIdx.x; i < n; i += 256) v[1] += dp[i] * (lambda * dp[i] + (bp[i] + bp_extra[i]));
   for (int i = threadIdx.x; i < n_sp; i += 256) v[1] += scale_partial[i];
   block_reduce<2, 256>(v, red);
   if (threadIdx.x != 0) return;
@@ -87,6 +88,11 @@ __global__ void ba_copy_state(const LMState* __restrict__ st, int which, const d
   const double* src = ((st->cur ^ which) & 1) ? a1 : a0;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     dst[i] = src[i];
+}
+
+__global__ void ba_add2(const double* __restrict__ a, const double* __restrict__ b, double* __restrict__ o, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) o[i] = a[i] + b[i];
 }
 
 // Public point arrays are [P][3]; the state buffers are padded to [P][4] (see load_point).
@@ -153,7 +159,7 @@ struct BA {
   cudaStream_t graph_stream = nullptr;
   // system
   DevBuf<double> Hpl, Gbuf, Hpp, bp, bhat, Hll, bl, Hinv, Wfac, camp, cam_cost, S, dp, dl, tmp3;
-  DevBuf<double> unit_partial, seg_extra_dense, extra, bp_extra, scale_cost, scale_partial, res, p_glob, w_loc, part;
+  DevBuf<double> unit_partial, seg_extra_dense, extra, extra_diag, bp_extra, scale_cost, scale_partial, res, p_glob, w_loc, part;
   DevBuf<unsigned> bar;
   DevBuf<int> pcg_flags;  // [0] fail flag, [1] status, [2] iters
   // PCG launch configuration
@@ -181,8 +187,8 @@ struct BA {
     A.cam_ticket = cam_ticket.p; A.lin_ticket = lin_ticket.p;
     A.Hpl = Hpl.p; A.camp = camp.p; A.Hpp = Hpp.p; A.bp = bp.p; A.cam_cost = cam_cost.p;
     A.Hll = Hll.p; A.bl = bl.p; A.pt_maxd = pt_maxd.p;
-    A.bp_extra = bp_extra.p; A.diag_extra = diag_extra.p; A.extra = extra.p; A.scale_cost = scale_cost.p;
-    A.st_rw = lm.p; A.trace = trace.p;
+    A.extra_diag = extra_diag.p; A.scale_cost = scale_cost.p;
+    A.st_rw = lm.p; A.trace = trace.p; A.force = 0;
     return A;
   }
   ScaleView scale_view() const {
@@ -191,7 +197,7 @@ struct BA {
     V.E = E; V.n_extra = n_extra; V.Cf = Cf; V.sa = sa.p; V.sb = sb.p; V.meas = scale_meas.p;
     V.cam_col = cam_col.p; V.inc_start = inc_start.p; V.inc_edge = inc_edge.p; V.extra_a = extra_a.p;
     V.extra_b = extra_b.p; V.edge_w = edge_w.p; V.edge_es = edge_es.p; V.edge_u = edge_u.p;
-    V.extra = extra.p; V.bp_extra = bp_extra.p; V.scale_cost = scale_cost.p;
+    V.extra = extra.p; V.bp_extra = bp_extra.p; V.scale_cost = scale_cost.p; V.extra_diag = extra_diag.p;
     return V;
   }
   ~BA() {
@@ -437,7 +443,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.camp.alloc(std::max((size_t)C * B.max_chunks, (size_t)B.lin_nA) * kCamVals)); BA_TRY(B.cam_cost.alloc(C));
   BA_TRY(B.S.alloc((size_t)B.n * B.n)); BA_TRY(B.dp.alloc(B.n)); BA_TRY(B.dl.alloc((size_t)Pf * 3));
   BA_TRY(B.tmp3.alloc((size_t)N * 3)); BA_TRY(B.unit_partial.alloc((size_t)B.n_units * 36));
-  BA_TRY(B.extra.alloc((size_t)std::max(n_extra, 1) * 36)); BA_TRY(B.bp_extra.alloc(std::max(B.n, 1)));
+  BA_TRY(B.extra.alloc((size_t)std::max(n_extra, 1) * 36)); BA_TRY(B.bp_extra.alloc(std::max(B.n, 1))); BA_TRY(B.extra_diag.alloc(std::max(3 * Cf, 1)));
   BA_TRY(B.scale_cost.alloc(1)); BA_TRY(B.scale_partial.alloc(B.n_sp)); BA_TRY(B.res.alloc(8));
   BA_TRY(B.p_glob.alloc(std::max(B.n, 1))); BA_TRY(B.w_loc.alloc(std::max(B.n, 1)));
   BA_TRY(cudaMemset(B.Hll.p, 0, std::max<size_t>((size_t)Pf * 6, 1) * sizeof(double)));   // free points without
@@ -445,6 +451,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(cudaMemset(B.S.p, 0, std::max<size_t>((size_t)B.n * B.n, 1) * sizeof(double)));
   BA_TRY(cudaMemset(B.extra.p, 0, (size_t)std::max(n_extra, 1) * 36 * sizeof(double)));
   BA_TRY(cudaMemset(B.bp_extra.p, 0, (size_t)std::max(B.n, 1) * sizeof(double)));
+  BA_TRY(cudaMemset(B.extra_diag.p, 0, (size_t)std::max(3 * Cf, 1) * sizeof(double)));
   BA_TRY(cudaMemset(B.scale_cost.p, 0, sizeof(double)));
   BA_TRY(cudaMemset(B.camp.p, 0, B.camp.n * sizeof(double)));
   BA_TRY(B.lm.alloc(1));
@@ -527,12 +534,12 @@ static int enqueue_schur(BA& B, cudaStream_t st) {
   if (B.Pf) {
     ba_point_invert<<<(B.Pf + 127) / 128, 128, 0, st>>>(lm, B.Pf, B.Hll.p, B.Hinv.p, B.Wfac.p);
     ba_compute_G<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.Wfac.p, B.bl.p, B.Gbuf.p, B.camp.p);
-    ba_bhat_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp.p, B.bhat.p);
+    ba_bhat_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp.p, B.bp_extra.p, B.bhat.p);
     if (B.n_units)
       ba_schur_units<<<(B.n_units + kSchurWarps - 1) / kSchurWarps, kSchurWarps * 32, kSchurSmem, st>>>(
           lm, B.Gbuf.p, B.item_a.p, B.item_b.p, B.unit_start.p, B.unit_len.p, B.n_units, B.unit_partial.p);
   } else if (B.n) {
-    BA_TRY(cudaMemcpyAsync(B.bhat.p, B.bp.p, (size_t)B.n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    ba_add2<<<(B.n + 255) / 256, 256, 0, st>>>(B.bp.p, B.bp_extra.p, B.bhat.p, B.n);
   }
   if (B.n)
     ba_schur_finalize<<<(B.n_seg * 36 + 127) / 128, 128, 0, st>>>(
@@ -573,7 +580,7 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
   ba_linearize_kernel<true><<<B.lin_nA, kLinThreads, kLinCostSmem, st>>>(V, B.lin_args(), B.scale_view());
   if (B.E) ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 1);
   ba_trial_controller<<<1, 256, 0, st>>>(B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0,
-                                         B.scale_partial.p, B.n, B.dp.p, B.bp.p, B.pcg_flags.p + 1,
+                                         B.scale_partial.p, B.n, B.dp.p, B.bp.p, B.bp_extra.p, B.pcg_flags.p + 1,
                                          B.pcg_flags.p + 2);
   return check_launch("ba_trial");
 }
@@ -719,19 +726,39 @@ extern "C" int vslam_ba_linearize(vslam_ba* h, double* out2, void* stream) {
   return VSLAM_OK;
 }
 
-// Times `reps` launches of one stage with CUDA events on `stream` (the stream the kernels run on):
-// stage 0 = the fused linearisation kernel alone (buildSystem), 1 = Schur complement assembly
-// (point inverse + E + units + finalize), 2 = one whole LM trial.  Before every launch flush_bytes of
-// flush_buf are overwritten (L2 flush; skipped when null).  ms_out[reps] (host).  Synchronises.
+// Times one stage with CUDA events on `stream` (the stream the kernels run on): stage 0 = the fused
+// linearisation kernel alone (buildSystem), 1 = Schur complement assembly (point inverse + G + units +
+// finalize), 2 = one whole LM trial, 3 = the fused linearisation kernel launched `reps` times back to
+// back between ONE pair of events (ms_out[0] = average per launch; its working set at C4, 194 MB, is
+// larger than the L2, and nothing but the kernel runs inside the timed region).  For stages 0-2 every
+// launch is bracketed on its own (ms_out[reps]) after flush_bytes of flush_buf are overwritten (L2
+// flush; skipped when null).  Synchronises.
 extern "C" int vslam_ba_time_stage(vslam_ba* h, int stage, int reps, void* flush_buf, int64_t flush_bytes,
                                    float* ms_out, void* stream) {
-  if (!h || reps < 1 || !ms_out || stage < 0 || stage > 2) return VSLAM_ERR_BAD_ARG;
+  if (!h || reps < 1 || !ms_out || stage < 0 || stage > 3) return VSLAM_ERR_BAD_ARG;
   BA& B = h->impl;
   if (B.C == 0) return VSLAM_ERR_BAD_ARG;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaEvent_t e0, e1;
   BA_TRY(cudaEventCreate(&e0)); BA_TRY(cudaEventCreate(&e1));
   int rc = VSLAM_OK;
+  if (stage == 3) {
+    ba_lm_poke<<<1, 1, 0, st>>>(B.lm.p, 0, 0.0);
+    LinArgs A = B.lin_args();
+    A.force = 1;
+    const BAView V = B.view();
+    const ScaleView SV = B.scale_view();
+    ba_linearize_kernel<false><<<B.lin_ctas, kLinThreads, B.lin_smem, st>>>(V, A, SV);   // warm-up
+    cudaEventRecord(e0, st);
+    for (int r = 0; r < reps; ++r) ba_linearize_kernel<false><<<B.lin_ctas, kLinThreads, B.lin_smem, st>>>(V, A, SV);
+    cudaEventRecord(e1, st);
+    rc = check_launch("ba_linearize");
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { set_cuda_error(e, "vslam_ba_time_stage"); rc = VSLAM_ERR_CUDA; }
+    else { cudaEventElapsedTime(&ms_out[0], e0, e1); ms_out[0] /= (float)reps; }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return rc;
+  }
   for (int r = 0; r < reps && rc == VSLAM_OK; ++r) {
     ba_lm_poke<<<1, 1, 0, st>>>(B.lm.p, 0, 0.0);
     if (stage != 0) rc = enqueue_linearize(B, st);
@@ -829,7 +856,11 @@ extern "C" int vslam_ba_read(vslam_ba* h, int what, double* dst, int64_t capacit
   size_t n = 0;
   switch (what) {
     case 0: src = B.Hpp.p; n = (size_t)B.Cf * 36; break;
-    case 1: src = B.bp.p; n = B.n; break;
+    case 1:   // b = projection part + scale-edge part
+      n = B.n;
+      if ((int64_t)n > capacity) return VSLAM_ERR_BAD_ARG;
+      if (n) ba_add2<<<(B.n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(B.bp.p, B.bp_extra.p, dst, B.n);
+      return check_launch("ba_add2");
     case 2: src = B.Hll.p; n = (size_t)B.Pf * 6; break;
     case 3: src = B.bl.p; n = (size_t)B.Pf * 3; break;
     case 4: src = B.S.p; n = (size_t)B.n * B.n; break;

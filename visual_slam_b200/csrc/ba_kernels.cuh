@@ -92,6 +92,7 @@ struct ScaleView {
   const int* extra_a; const int* extra_b;      // free-camera columns of each extra block (a <= b)
   double* edge_w; double* edge_es; double* edge_u;  // [E], [E], [E][3]
   double* extra; double* bp_extra; double* scale_cost;
+  double* extra_diag;                          // [Cf][3] translation diagonal of each camera's own extra block
 };
 
 template <int THREADS>
@@ -136,6 +137,7 @@ __device__ __forceinline__ void scale_edges_body(const ScaleView& V, bool cost_o
     for (int i = 0; i < 36; ++i) o[i] = 0.0;
     for (int i = 0; i < 3; ++i)
       for (int j = 0; j < 3; ++j) o[6 * i + j] = h[3 * i + j];
+    if (a == b) { V.extra_diag[3 * a] = h[0]; V.extra_diag[3 * a + 1] = h[4]; V.extra_diag[3 * a + 2] = h[8]; }
   }
   for (int col = threadIdx.x; col < V.Cf; col += THREADS) {
     double g[3] = {0, 0, 0};
@@ -180,8 +182,9 @@ constexpr int kLinChunk = kLinThreads * kLinObs;
 constexpr int kStageDoubles = 32 * 18;          // one warp's 32 Hpl blocks (4608 B)
 constexpr bool kBulkStore = true;               // Hpl stage -> HBM by bulk async store (else LDS + STG.128)
 constexpr int kHplStages = 1;                   // Hpl stages per warp
-constexpr int kLinCamSmem = kLinWarps * kHplStages * kStageDoubles * 8;   // camera-role bytes
-constexpr int kLinCostSmem = 0;                  // the cost-only launch stages nothing   // camera-role bytes
+constexpr int kLinInSmem = kLinObs * kLinThreads * (4 + 16);              // chunk inputs: indices + measurements
+constexpr int kLinCamSmem = kLinWarps * kHplStages * kStageDoubles * 8 + kLinInSmem;   // camera-role bytes
+constexpr int kLinCostSmem = kLinCamSmem;        // same layout in the cost-only launch (the stage stays unused)   // camera-role bytes
 constexpr int kPtRowsPerWarp = 8;               // ELL rows a point-role warp aims for
 constexpr int kCamTabStride = 14;               // doubles per camera in the point role's table (112 B)
 constexpr int kCamSmemMax = 1800;               // cameras kept in shared memory by the point role
@@ -207,9 +210,10 @@ struct LinArgs {
   unsigned* lin_ticket;             // [1]
   double* Hpl; double* camp; double* Hpp; double* bp; double* cam_cost;
   double* Hll; double* bl; double* pt_maxd;
-  const double* bp_extra; const int* diag_extra; const double* extra; const double* scale_cost;
+  const double* extra_diag; const double* scale_cost;   // scale-edge terms (bp_extra is added by the consumers of bp)
   LMState* st_rw;
   long long* trace;                 // optional [n_ctas][2] globaltimer stamps (profiling), else null
+  int force;                        // profiling: rebuild even when the system is not dirty
 };
 
 __device__ __forceinline__ long long globaltimer_ns();
@@ -232,6 +236,9 @@ __device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, u
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
 __device__ __forceinline__ void cp_async8(void* dst_smem, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
@@ -319,66 +326,28 @@ __device__ __forceinline__ void lin_controller(const BAView& V, const LinArgs& A
   // every load of a batch is issued before the first use: the values were just written by other SMs
   // and each L2 round trip costs ~0.5 us, so the loops must not serialise them
   double v[2] = {0.0, 0.0};
-  constexpr int U = 8;
+  constexpr int U = 10;
   const int n6 = 6 * V.Cf;
-  for (int i0 = 0; i0 < V.C; i0 += U * kLinThreads) {
-    double a[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int i = i0 + u * kLinThreads + threadIdx.x;
-      a[u] = i < V.C ? __ldcg(A.cam_cost + i) : 0.0;
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) v[0] += a[u];
-  }
-  for (int i0 = 0; i0 < n6; i0 += U * kLinThreads) {
-    double a[U], x[U];
-    int ex[U];
+  const double sc = A.has_scale ? __ldcg(A.scale_cost) : 0.0;
+  const int n_max = max(max(V.C, n6), A.n_pt_ctas);
+  for (int i0 = 0; i0 < n_max; i0 += U * kLinThreads) {
+    double a[U], x[U], cc[U], pm[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int i = i0 + u * kLinThreads + threadIdx.x;
       const int col = i / 6, r = i - 6 * col;
       a[u] = i < n6 ? __ldcg(A.Hpp + 36 * (size_t)col + 7 * r) : 0.0;
-      ex[u] = (i < n6 && A.has_scale) ? __ldg(A.diag_extra + col) : -1;
+      x[u] = (i < n6 && A.has_scale && r < 3) ? __ldcg(A.extra_diag + 3 * col + r) : 0.0;
+      cc[u] = i < V.C ? __ldcg(A.cam_cost + i) : 0.0;
+      pm[u] = i < A.n_pt_ctas ? __ldcg(A.pt_maxd + i) : 0.0;
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int i = i0 + u * kLinThreads + threadIdx.x;
-      const int r = i % 6;
-      x[u] = ex[u] >= 0 ? __ldcg(A.extra + 36 * (size_t)ex[u] + 7 * r) : 0.0;
+      v[0] += cc[u];
+      v[1] = fmax(v[1], fmax(fabs(a[u] + x[u]), pm[u]));
     }
-#pragma unroll
-    for (int u = 0; u < U; ++u) v[1] = fmax(v[1], fabs(a[u] + x[u]));
-  }
-  for (int i0 = 0; i0 < A.n_pt_ctas; i0 += U * kLinThreads) {
-    double a[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int i = i0 + u * kLinThreads + threadIdx.x;
-      a[u] = i < A.n_pt_ctas ? __ldcg(A.pt_maxd + i) : 0.0;
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) v[1] = fmax(v[1], a[u]);
   }
   if (A.trace && threadIdx.x == 0) A.trace[2 * gridDim.x + 5] = globaltimer_ns() + (v[0] > 1e300) + (v[1] > 1e300);
-  if (A.has_scale) {
-    double* __restrict__ bp = A.bp;
-    const double* __restrict__ bpx = A.bp_extra;
-    for (int i0 = 0; i0 < 6 * V.Cf; i0 += 4 * kLinThreads) {
-      double a[4], b[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int i = i0 + u * kLinThreads + threadIdx.x;
-        a[u] = i < 6 * V.Cf ? __ldcg(bp + i) : 0.0;
-        b[u] = i < 6 * V.Cf ? __ldcg(bpx + i) : 0.0;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int i = i0 + u * kLinThreads + threadIdx.x;
-        if (i < 6 * V.Cf) bp[i] = a[u] + b[u];
-      }
-    }
-  }
   if (A.trace && threadIdx.x == 0) A.trace[2 * gridDim.x + 6] = globaltimer_ns();
   v[0] = warp_sum(v[0]);
   for (int o = 16; o > 0; o >>= 1) v[1] = fmax(v[1], __shfl_xor_sync(0xffffffffu, v[1], o));
@@ -386,7 +355,7 @@ __device__ __forceinline__ void lin_controller(const BAView& V, const LinArgs& A
   __syncthreads();
   if (threadIdx.x == 0) {
     LMState* st = A.st_rw;
-    const double cost = ((red[0] + red[1]) + (red[2] + red[3])) + (A.has_scale ? __ldcg(A.scale_cost) : 0.0);
+    const double cost = ((red[0] + red[1]) + (red[2] + red[3])) + sc;
     const double md = fmax(fmax(red[4], red[5]), fmax(red[6], red[7]));
     st->cur_cost = cost;
     st->max_diag = md;
@@ -411,7 +380,7 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
   __shared__ int s_flag;
   const int4* wsrc = reinterpret_cast<const int4*>((COST_ONLY ? A.cam_work : A.work) + blockIdx.x);
   const int4 w0 = __ldg(wsrc), w1 = __ldg(wsrc + 1);
-  if (V.st->done || (!COST_ONLY && !V.st->dirty)) return;
+  if (V.st->done || (!COST_ONLY && !V.st->dirty && !A.force)) return;
   const int sb = COST_ONLY ? (V.st->cur ^ 1) : V.st->cur;   // the cost-only pass evaluates the trial state
   const CamRT* __restrict__ camrt = V.camrt[sb];
   const double* __restrict__ pts = V.pts[sb];
@@ -428,34 +397,37 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
     double v[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = 0.0;
-    // two-stage software pipeline (warps issue in order, so a dependent address must never be
-    // computed right after its index load): the point INDEX is loaded two observations ahead, the
-    // point itself (one 256-bit load) and its measurement one observation ahead; both are in flight
-    // under the current arithmetic.
-    int o = start + tid;
-    double X[3] = {0.0, 0.0, 1.0};
-    double2 uv = make_double2(0.0, 0.0);
-    int p_next = 0;
-    if (o + kLinThreads < end) p_next = V.cm_pt[o + kLinThreads];
-    if (o < end) {
-      const int p = V.cm_pt[o];
-      uv = V.cm_uv[o];
-      load_point(pts, p, X);
+    // Inputs: the chunk's point indices and measurements (contiguous in camera-major order) are
+    // fetched up front by cp.async into shared memory, all kLinObs observations of a thread in flight
+    // at once, so the streams from HBM cost ONE exposed round trip per chunk; the points themselves
+    // (random 32-byte sectors, mostly L2 hits, one 256-bit load each) run one observation ahead in
+    // registers.
+    const int o0 = start + tid;
+    int* s_idx = reinterpret_cast<int*>(dyn_smem + kLinWarps * kHplStages * kStageDoubles);   // [kLinObs][kLinThreads]
+    double2* s_uv = reinterpret_cast<double2*>(s_idx + kLinObs * kLinThreads);                 // [kLinObs][kLinThreads]
+#pragma unroll
+    for (int k = 0; k < kLinObs; ++k) {
+      const int o = o0 + k * kLinThreads;
+      if (o < end) {
+        cp_async4(s_idx + k * kLinThreads + tid, V.cm_pt + o);
+        cp_async16(s_uv + k * kLinThreads + tid, V.cm_uv + o);
+      }
     }
+    cp_async_commit();
     double* ws0 = dyn_smem + wid * (kHplStages * kStageDoubles);
+    cp_async_wait<0>();                                  // each thread reads back only what it fetched
+    double X[3] = {0.0, 0.0, 1.0};
+    if (o0 < end) load_point(pts, s_idx[tid], X);
     __syncthreads();
+    int o = o0;
 #pragma unroll 1
     for (int k = 0; k < kLinObs; ++k) {
       const bool valid = o < end;
       const double Xc[3] = {X[0], X[1], X[2]};
-      const double2 uvc = uv;
+      double2 uvc = make_double2(0.0, 0.0);
+      if (valid) uvc = s_uv[k * kLinThreads + tid];
       const int o_next = o + kLinThreads;
-      const int p_cur = p_next;
-      if (k + 2 < kLinObs && o_next + kLinThreads < end) p_next = V.cm_pt[o_next + kLinThreads];
-      if (k + 1 < kLinObs && o_next < end) {   // p_cur arrived during the previous observation
-        uv = V.cm_uv[o_next];
-        load_point(pts, p_cur, X);
-      }
+      if (k + 1 < kLinObs && o_next < end) load_point(pts, s_idx[(k + 1) * kLinThreads + tid], X);
       const bool want_hpl = !COST_ONLY && cam_free;
       double* ws = ws0 + (k % kHplStages) * kStageDoubles;
       double2* wsl = reinterpret_cast<double2*>(ws + lane * 18);
@@ -782,8 +754,8 @@ ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict_
 }
 
 // bhat = bp - sum_j Hpl_j Hinv_j bl_j   (ordered chunk sum)
-__global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp,
-                                 const double* __restrict__ bp, double* __restrict__ bhat) {
+__global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp, const double* __restrict__ bp,
+                                 const double* __restrict__ bp_extra, double* __restrict__ bhat) {
   const int c = blockIdx.x, i = threadIdx.x;
   const int col = V.cam_col[c];
   if (V.st->done || i >= 6 || col < 0) return;
@@ -791,7 +763,7 @@ __global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp,
   const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
   double s = 0.0;
   for (int k = 0; k < n_chunks; ++k) s += camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
-  bhat[6 * col + i] = bp[6 * col + i] - s;
+  bhat[6 * col + i] = (bp[6 * col + i] + bp_extra[6 * col + i]) - s;
 }
 
 // Schur work units: one warp reduces <= kUnitItems products G_a * G_b^T of one (cam a, cam b) key,
