@@ -206,6 +206,8 @@ struct BA {
   }
 };
 
+static size_t pcg_small_smem(int n) { return sizeof(double) * ((size_t)n * n + 6 * (size_t)n + 128); }
+
 static void counting_sort(const std::vector<int>& in, const int* key, int n_keys, std::vector<int>& out) {
   std::vector<int> cnt(n_keys + 1, 0);
   for (int i : in) cnt[key[i] + 1]++;
@@ -570,6 +572,8 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
     if (B.pcg_G > 1) {
       BA_TRY(cudaLaunchCooperativeKernel((void*)ba_pcg_kernel, dim3(B.pcg_G), dim3(kPcgThreads), args,
                                          B.pcg_smem, st));
+    } else if (B.n <= kPcgSmallMax) {
+      ba_pcg_small_kernel<<<1, 32, pcg_small_smem(B.n), st>>>(A);
     } else {
       ba_pcg_kernel<<<1, kPcgThreads, B.pcg_smem, st>>>(A);
     }
@@ -904,7 +908,8 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
   A.slab_in_smem = smem_slab <= 200 * 1024;
   size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
   BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
+  if (n <= kPcgSmallMax) ba_pcg_small_kernel<<<1, 32, pcg_small_smem(n), st>>>(A);
+  else ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
   int rc = check_launch("ba_pcg_kernel");
   if (rc) return rc;
   int host[4];

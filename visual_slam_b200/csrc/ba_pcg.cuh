@@ -235,4 +235,97 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
   if (g == 0 && tid == 0) { *A.status = status; *A.iters = it; }
 }
 
+// Small systems (n <= kPcgSmallMax, e.g. the 9 free cameras of a local window): the same
+// Chronopoulos-Gear iteration in ONE warp, two rows per lane, S in shared memory (read by column:
+// S is symmetric, so lanes read consecutive addresses), no block barriers at all: an iteration
+// costs two __syncwarp and three shuffle reductions instead of five __syncthreads.
+constexpr int kPcgSmallMax = 64;
+
+__global__ void __launch_bounds__(32) ba_pcg_small_kernel(PcgArgs A) {
+  extern __shared__ __align__(16) double sm[];
+  if (A.done != nullptr && *A.done) return;
+  const int n = A.n, lane = threadIdx.x;
+  double* Ss = sm;                     // [n][n]
+  double* minv = Ss + n * n;           // [n/6][36]
+  double* rs = minv + 6 * n;           // [64]
+  double* us = rs + 64;                // [64]
+  for (int i = lane; i < n * n; i += 32) Ss[i] = A.S[i];
+  rs[lane] = 0.0; rs[lane + 32] = 0.0; us[lane] = 0.0; us[lane + 32] = 0.0;
+  __syncwarp();
+  int fail = 0;
+  for (int bi = lane; bi < n / 6; bi += 32) {
+    double blk[36];
+    for (int i = 0; i < 6; ++i)
+      for (int j = 0; j < 6; ++j) blk[6 * i + j] = Ss[(6 * bi + i) * n + 6 * bi + j];
+    if (!spd6_inverse(blk)) fail = 1;
+    for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
+  }
+  fail = __any_sync(0xffffffffu, fail);
+  __syncwarp();
+  const int i0 = lane, i1 = lane + 32;
+  const bool h0 = i0 < n, h1 = i1 < n;
+  double x0 = 0.0, x1 = 0.0, p0 = 0.0, p1 = 0.0, s0 = 0.0, s1 = 0.0;
+  double r0 = h0 ? A.b[i0] : 0.0, r1 = h1 ? A.b[i1] : 0.0;
+  int status = fail ? 1 : 2, it = 0;
+  double gamma_old = 0.0, alpha_old = 0.0, thresh = 0.0;
+  if (!fail) {
+    for (it = 0; it <= A.max_iter; ++it) {
+      rs[i0] = r0; rs[i1] = r1;
+      __syncwarp();
+      double u0 = 0.0, u1 = 0.0;
+      if (h0) {
+        const double* m = minv + 36 * (i0 / 6) + 6 * (i0 % 6);
+        const double* rr6 = rs + 6 * (i0 / 6);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) u0 += m[j] * rr6[j];
+      }
+      if (h1) {
+        const double* m = minv + 36 * (i1 / 6) + 6 * (i1 % 6);
+        const double* rr6 = rs + 6 * (i1 / 6);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) u1 += m[j] * rr6[j];
+      }
+      us[i0] = u0; us[i1] = u1;
+      __syncwarp();
+      // w = S u, rows i0 and i1 (two accumulators each)
+      double wa = 0.0, wb = 0.0, wc = 0.0, wd = 0.0;
+      const double* c0 = Ss + (h0 ? i0 : 0);
+      const double* c1 = Ss + (h1 ? i1 : 0);
+      int j = 0;
+      for (; j + 1 < n; j += 2) {
+        const double ua = us[j], ub = us[j + 1];
+        wa = fma(c0[j * n], ua, wa); wb = fma(c0[(j + 1) * n], ub, wb);
+        wc = fma(c1[j * n], ua, wc); wd = fma(c1[(j + 1) * n], ub, wd);
+      }
+      if (j < n) { wa = fma(c0[j * n], us[j], wa); wc = fma(c1[j * n], us[j], wc); }
+      const double w0 = h0 ? wa + wb : 0.0, w1 = h1 ? wc + wd : 0.0;
+      const double gamma = warp_sum(r0 * u0 + r1 * u1);
+      const double delta = warp_sum(w0 * u0 + w1 * u1);
+      const double rr = warp_sum(r0 * r0 + r1 * r1);
+      if (it == 0) {
+        if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
+        thresh = A.tol * A.tol * rr;
+      }
+      if (rr <= thresh && it > 0) { status = 0; break; }
+      if (it == A.max_iter) break;
+      double beta = 0.0, pap = delta;
+      if (it > 0) {
+        beta = gamma / gamma_old;
+        pap = delta - beta * gamma / alpha_old;        // = p^T S p in exact arithmetic
+      }
+      if (!(pap > 0.0) || !isfinite(pap) || !(gamma > 0.0)) { status = 1; break; }
+      const double alpha = gamma / pap;
+      p0 = u0 + beta * p0; p1 = u1 + beta * p1;
+      s0 = w0 + beta * s0; s1 = w1 + beta * s1;
+      x0 += alpha * p0; x1 += alpha * p1;
+      r0 -= alpha * s0; r1 -= alpha * s1;
+      gamma_old = gamma; alpha_old = alpha;
+      __syncwarp();
+    }
+  }
+  if (h0) A.x[i0] = (status == 1) ? 0.0 : x0;
+  if (h1) A.x[i1] = (status == 1) ? 0.0 : x1;
+  if (lane == 0) { *A.status = status; *A.iters = it; }
+}
+
 }  // namespace vslam
