@@ -337,16 +337,22 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   B.n_sp = (P + 255) / 256;
   // fused linearisation: camera chunks (every camera owns at least one, possibly empty), point blocks
   // and the scale-edge CTA, interleaved in proportion so that all roles are resident at the same time
+  // small problems get smaller chunks (fewer observations per thread, more CTAs in flight): the grid
+  // should offer about four CTAs per SM before a thread takes a second observation
+  const int slots = 4 * std::max(1, sm_count());
+  const int obs_iters = std::min(kLinObs, std::max(1, (N + kLinThreads * slots - 1) / (kLinThreads * slots)));
+  const int lin_chunk = kLinThreads * obs_iters;
+  const int pt_rows_target = std::min(kPtRowsPerWarp, std::max(2, (N / 32 + 2 * slots * kLinWarps - 1) / (2 * slots * kLinWarps)));
   std::vector<LinWork> cam_work, lin_work;
   {
     int row = 0;
     for (int c = 0; c < C; ++c) {
       const int n_obs_c = cm_start[c + 1] - cm_start[c];
-      const int nch = std::max(1, (n_obs_c + kLinChunk - 1) / kLinChunk);
+      const int nch = std::max(1, (n_obs_c + lin_chunk - 1) / lin_chunk);
       for (int k = 0; k < nch; ++k) {
         LinWork w{};
-        w.kind = 0; w.cam = c; w.start = cm_start[c] + k * kLinChunk;
-        w.end = std::min(cm_start[c + 1], w.start + kLinChunk);
+        w.kind = 0; w.cam = c; w.start = cm_start[c] + k * lin_chunk;
+        w.end = std::min(cm_start[c + 1], w.start + lin_chunk);
         w.row = row + k; w.n_chunks = nch; w.first_row = row; w.col = cam_col[c];
         cam_work.push_back(w);
       }
@@ -391,7 +397,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     int rows = 0;
     for (int it = 0; it < n_it; ++it) {
       rows += item_row[it + 1] - item_row[it];
-      if (rows >= kPtRowsPerWarp || it + 1 == n_it) { pw_first.push_back(it + 1); rows = 0; }
+      if (rows >= pt_rows_target || it + 1 == n_it) { pw_first.push_back(it + 1); rows = 0; }
     }
     B.n_pt_warps = (int)pw_first.size() - 1;
     B.n_ell_rows = item_row[n_it];
@@ -573,7 +579,7 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
       BA_TRY(cudaLaunchCooperativeKernel((void*)ba_pcg_kernel, dim3(B.pcg_G), dim3(kPcgThreads), args,
                                          B.pcg_smem, st));
     } else if (B.n <= kPcgSmallMax) {
-      ba_pcg_small_kernel<<<1, 32, pcg_small_smem(B.n), st>>>(A);
+      ba_pcg_small_kernel<<<1, kPcgSmallThreads, pcg_small_smem(B.n), st>>>(A);
     } else {
       ba_pcg_kernel<<<1, kPcgThreads, B.pcg_smem, st>>>(A);
     }
@@ -908,7 +914,7 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
   A.slab_in_smem = smem_slab <= 200 * 1024;
   size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
   BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  if (n <= kPcgSmallMax) ba_pcg_small_kernel<<<1, 32, pcg_small_smem(n), st>>>(A);
+  if (n <= kPcgSmallMax) ba_pcg_small_kernel<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
   else ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
   int rc = check_launch("ba_pcg_kernel");
   if (rc) return rc;

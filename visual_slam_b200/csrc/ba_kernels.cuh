@@ -420,8 +420,9 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
     if (o0 < end) load_point(pts, s_idx[tid], X);
     __syncthreads();
     int o = o0;
+    const int n_iter = min(kLinObs, (end - start + kLinThreads - 1) / kLinThreads);   // the host sizes chunks to the problem
 #pragma unroll 1
-    for (int k = 0; k < kLinObs; ++k) {
+    for (int k = 0; k < n_iter; ++k) {
       const bool valid = o < end;
       const double Xc[3] = {X[0], X[1], X[2]};
       double2 uvc = make_double2(0.0, 0.0);

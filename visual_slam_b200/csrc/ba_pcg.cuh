@@ -241,17 +241,25 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
 // costs two __syncwarp and three shuffle reductions instead of five __syncthreads.
 constexpr int kPcgSmallMax = 64;
 
-__global__ void __launch_bounds__(32) ba_pcg_small_kernel(PcgArgs A) {
+constexpr int kPcgSmallThreads = 128;   // all four warps fetch S; warp 0 iterates
+
+__global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_kernel(PcgArgs A) {
   extern __shared__ __align__(16) double sm[];
   if (A.done != nullptr && *A.done) return;
-  const int n = A.n, lane = threadIdx.x;
+  const int n = A.n, lane = threadIdx.x & 31;
   double* Ss = sm;                     // [n][n]
   double* minv = Ss + n * n;           // [n/6][36]
   double* rs = minv + 6 * n;           // [64]
   double* us = rs + 64;                // [64]
-  for (int i = lane; i < n * n; i += 32) Ss[i] = A.S[i];
-  rs[lane] = 0.0; rs[lane + 32] = 0.0; us[lane] = 0.0; us[lane + 32] = 0.0;
-  __syncwarp();
+  {
+    const double2* src = reinterpret_cast<const double2*>(A.S);   // n is a multiple of 6: n*n is even
+    double2* dst = reinterpret_cast<double2*>(Ss);
+#pragma unroll 4
+    for (int i = threadIdx.x; i < (n * n) / 2; i += kPcgSmallThreads) dst[i] = __ldcg(src + i);
+  }
+  if (threadIdx.x < 64) { rs[threadIdx.x] = 0.0; us[threadIdx.x] = 0.0; }
+  __syncthreads();
+  if (threadIdx.x >= 32) return;
   int fail = 0;
   for (int bi = lane; bi < n / 6; bi += 32) {
     double blk[36];
@@ -291,13 +299,16 @@ __global__ void __launch_bounds__(32) ba_pcg_small_kernel(PcgArgs A) {
       double wa = 0.0, wb = 0.0, wc = 0.0, wd = 0.0;
       const double* c0 = Ss + (h0 ? i0 : 0);
       const double* c1 = Ss + (h1 ? i1 : 0);
-      int j = 0;
-      for (; j + 1 < n; j += 2) {
-        const double ua = us[j], ub = us[j + 1];
-        wa = fma(c0[j * n], ua, wa); wb = fma(c0[(j + 1) * n], ub, wb);
-        wc = fma(c1[j * n], ua, wc); wd = fma(c1[(j + 1) * n], ub, wd);
+      for (int j = 0; j < n; j += 6) {             // n is a multiple of 6; 18 independent loads per step
+        double a0[6], a1[6], uu[6];
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { a0[q] = c0[(j + q) * n]; a1[q] = c1[(j + q) * n]; uu[q] = us[j + q]; }
+#pragma unroll
+        for (int q = 0; q < 6; q += 2) {
+          wa = fma(a0[q], uu[q], wa); wb = fma(a0[q + 1], uu[q + 1], wb);
+          wc = fma(a1[q], uu[q], wc); wd = fma(a1[q + 1], uu[q + 1], wd);
+        }
       }
-      if (j < n) { wa = fma(c0[j * n], us[j], wa); wc = fma(c1[j * n], us[j], wc); }
       const double w0 = h0 ? wa + wb : 0.0, w1 = h1 ? wc + wd : 0.0;
       const double gamma = warp_sum(r0 * u0 + r1 * u1);
       const double delta = warp_sum(w0 * u0 + w1 * u1);
