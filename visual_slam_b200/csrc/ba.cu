@@ -15,7 +15,7 @@ namespace vslam {
 // Controller after a trial: cost of the trial state, computeScale, then the Levenberg-Marquardt
 // accept / reject logic of g2o (OptimizationAlgorithmLevenberg::solve) entirely on the device.
 __global__ void __launch_bounds__(256)
-ba_trial_controller(LMState* __restrict__ st, int C, const double* __restrict__ cam_cost,
+ba_trial_controller(ScaleView SV, int has_scale, LMState* __restrict__ st, int C, const double* __restrict__ cam_cost,
                     const double* __restrict__ scale_cost, int n_sp,
                     const double* __restrict__ scale_partial, int n, const double* __restrict__ dp,
                     const double* __restrict__ bp, const double* __restrict__ bp_extra,
@@ -23,6 +23,10 @@ ba_trial_controller(LMState* __restrict__ st, int C, const double* __restrict__ 
                     const int* __restrict__ pcg_iters) {
   __shared__ double red[16];
   if (st->done) return;
+  if (has_scale) {   // cost of the scale edges at the trial state (EdgeSBAScale + DCS)
+    scale_edges_body<256>(SV, true, red);
+    __syncthreads();
+  }
   const double lambda = st->lambda;
   double v[2] = {0.0, 0.0};
   for (int i = threadIdx.x; i < C; i += 256) v[0] += cam_cost[i];
@@ -542,17 +546,16 @@ static int enqueue_schur(BA& B, cudaStream_t st) {
   if (B.Pf) {
     ba_point_invert<<<(B.Pf + 127) / 128, 128, 0, st>>>(lm, B.Pf, B.Hll.p, B.Hinv.p, B.Wfac.p);
     ba_compute_G<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.Wfac.p, B.bl.p, B.Gbuf.p, B.camp.p);
-    ba_bhat_finalize<<<B.C, 32, 0, st>>>(V, B.camp.p, B.bp.p, B.bp_extra.p, B.bhat.p);
     if (B.n_units)
       ba_schur_units<<<(B.n_units + kSchurWarps - 1) / kSchurWarps, kSchurWarps * 32, kSchurSmem, st>>>(
           lm, B.Gbuf.p, B.item_a.p, B.item_b.p, B.unit_start.p, B.unit_len.p, B.n_units, B.unit_partial.p);
-  } else if (B.n) {
-    ba_add2<<<(B.n + 255) / 256, 256, 0, st>>>(B.bp.p, B.bp_extra.p, B.bhat.p, B.n);
   }
-  if (B.n)
-    ba_schur_finalize<<<(B.n_seg * 36 + 127) / 128, 128, 0, st>>>(
-        lm, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
-        B.extra.p, B.seg_extra_idx.p, B.S.p);
+  if (B.n) {
+    BhatArgs Bh{B.Pf ? B.camp.p : nullptr, B.bp.p, B.bp_extra.p, B.bhat.p};
+    ba_schur_finalize<<<(B.n_seg * 36 + B.C * 6 + 127) / 128, 128, 0, st>>>(
+        V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
+        B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
+  }
   return check_launch("ba_schur");
 }
 
@@ -585,11 +588,13 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
     }
   }
   if (B.Pf) ba_backsub_cam<<<grid, kCamThreads, 0, st>>>(V, B.Hpl.p, B.dp.p, B.tmp3.p);
-  if (B.P) ba_backsub_pt<<<B.n_sp, 256, 0, st>>>(V, B.tmp3.p, B.Hinv.p, B.bl.p, B.dl.p, B.scale_partial.p);
-  ba_update_cams<<<(B.C + 127) / 128, 128, 0, st>>>(V, B.dp.p);
+  {
+    const int n_pt_blocks = B.P ? B.n_sp : 0;
+    ba_backsub_pt<<<n_pt_blocks + (B.C + 255) / 256, 256, 0, st>>>(V, B.tmp3.p, B.Hinv.p, B.bl.p, B.dl.p,
+                                                                 B.scale_partial.p, B.dp.p, n_pt_blocks);
+  }
   ba_linearize_kernel<true><<<B.lin_nA, kLinThreads, kLinCostSmem, st>>>(V, B.lin_args(), B.scale_view());
-  if (B.E) ba_scale_edges<<<1, 256, 0, st>>>(B.scale_view(), 1);
-  ba_trial_controller<<<1, 256, 0, st>>>(B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0,
+  ba_trial_controller<<<1, 256, 0, st>>>(B.scale_view(), B.E > 0 ? 1 : 0, B.lm.p, B.C, B.cam_cost.p, B.scale_cost.p, B.P ? B.n_sp : 0,
                                          B.scale_partial.p, B.n, B.dp.p, B.bp.p, B.bp_extra.p, B.pcg_flags.p + 1,
                                          B.pcg_flags.p + 2);
   return check_launch("ba_trial");

@@ -754,19 +754,6 @@ ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict_
   }
 }
 
-// bhat = bp - sum_j Hpl_j Hinv_j bl_j   (ordered chunk sum)
-__global__ void ba_bhat_finalize(BAView V, const double* __restrict__ camp, const double* __restrict__ bp,
-                                 const double* __restrict__ bp_extra, double* __restrict__ bhat) {
-  const int c = blockIdx.x, i = threadIdx.x;
-  const int col = V.cam_col[c];
-  if (V.st->done || i >= 6 || col < 0) return;
-  const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
-  const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
-  double s = 0.0;
-  for (int k = 0; k < n_chunks; ++k) s += camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
-  bhat[6 * col + i] = (bp[6 * col + i] + bp_extra[6 * col + i]) - s;
-}
-
 // Schur work units: one warp reduces <= kUnitItems products G_a * G_b^T of one (cam a, cam b) key,
 // one item per lane and round.  The 64 blocks of a round (144 B each, scattered in HBM) are fetched
 // COOPERATIVELY: consecutive lanes copy consecutive 16-byte pieces of a block with cp.async (LDGSTS),
@@ -855,18 +842,36 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
 }
 
 // S block (a,b) = [a==b](Hpp_a + lambda I) + scale-edge block - sum of its units; mirrored.
-__global__ void ba_schur_finalize(const LMState* __restrict__ st, int n_seg, int n, const int* __restrict__ seg_a,
+struct BhatArgs {   // bhat = (bp + bp_extra) - sum_j Hpl_j Hinv_j bl_j  (ordered chunk sum of ba_compute_G's partials)
+  const double* camp; const double* bp; const double* bp_extra; double* bhat;
+};
+__global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restrict__ seg_a,
                                   const int* __restrict__ seg_b,
                                   const int* __restrict__ seg_unit_start,
                                   const double* __restrict__ partial,
                                   const double* __restrict__ Hpp,
                                   const double* __restrict__ extra,
-                                  const int* __restrict__ seg_extra_idx, double* __restrict__ S) {
-  if (st->done) return;
-  const double lambda = st->lambda;
+                                  const int* __restrict__ seg_extra_idx, double* __restrict__ S, BhatArgs Bh) {
+  if (V.st->done) return;
+  const double lambda = V.st->lambda;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int seg = t / 36, e = t % 36;
-  if (seg >= n_seg) return;
+  if (seg >= n_seg) {
+    // the threads behind the S blocks build bhat (one per camera and row)
+    const int tb = t - n_seg * 36;
+    const int c = tb / 6, i = tb - 6 * c;
+    if (Bh.bhat == nullptr || c >= V.C) return;
+    const int col = V.cam_col[c];
+    if (col < 0) return;
+    double s = 0.0;
+    if (Bh.camp != nullptr) {
+      const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
+      const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
+      for (int k = 0; k < n_chunks; ++k) s += Bh.camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
+    }
+    Bh.bhat[6 * col + i] = (Bh.bp[6 * col + i] + Bh.bp_extra[6 * col + i]) - s;
+    return;
+  }
   const int a = seg_a[seg], b = seg_b[seg], r = e / 6, c = e % 6;
   const int ex = seg_extra_idx[seg];
   double v = ex >= 0 ? extra[(size_t)ex * 36 + e] : 0.0;
@@ -905,14 +910,47 @@ ba_backsub_cam(BAView V, const double* __restrict__ Hpl, const double* __restric
   }
 }
 
+// SBACam::update on every free camera (t += d[0:3]; q <- normalize(q * (sqrt(1-|v|^2), v))).
+__device__ __forceinline__ void update_cams_body(const BAView& V, const double* __restrict__ dp, int c) {
+  if (c >= V.C) return;
+  const double* __restrict__ cams = V.cams[V.st->cur];
+  double* __restrict__ cams_trial = V.cams[V.st->cur ^ 1];
+  CamRT* __restrict__ camrt_trial = V.camrt[V.st->cur ^ 1];
+  double q[4] = {cams[7 * c], cams[7 * c + 1], cams[7 * c + 2], cams[7 * c + 3]};
+  double t[3] = {cams[7 * c + 4], cams[7 * c + 5], cams[7 * c + 6]};
+  const int col = V.cam_col[c];
+  if (col >= 0) {
+    const double* d = dp + 6 * col;
+    t[0] += d[0]; t[1] += d[1]; t[2] += d[2];
+    const double vx = d[3], vy = d[4], vz = d[5];
+    const double vw = sqrt(1.0 - (vx * vx + vy * vy + vz * vz));
+    const double x = q[3] * vx + q[0] * vw + q[1] * vz - q[2] * vy;
+    const double y = q[3] * vy - q[0] * vz + q[1] * vw + q[2] * vx;
+    const double z = q[3] * vz + q[0] * vy - q[1] * vx + q[2] * vw;
+    const double w = q[3] * vw - q[0] * vx - q[1] * vy - q[2] * vz;
+    const double inv = 1.0 / sqrt(x * x + y * y + z * z + w * w);
+    q[0] = x * inv; q[1] = y * inv; q[2] = z * inv; q[3] = w * inv;
+  }
+  double* o = cams_trial + 7 * c;
+  o[0] = q[0]; o[1] = q[1]; o[2] = q[2]; o[3] = q[3]; o[4] = t[0]; o[5] = t[1]; o[6] = t[2];
+  CamRT r;
+  quat_to_R(q, r.R);
+  r.t[0] = t[0]; r.t[1] = t[1]; r.t[2] = t[2];
+  camrt_trial[c] = r;
+}
+
 // Back-substitution, point half: dl = Hinv (bl - sum_o v_o); trial point = point + dl.
 // Also the per-CTA partial of sum dl (lambda dl + bl)  (computeScale, landmark part).
 __global__ void __launch_bounds__(256)
 ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restrict__ Hinv,
               const double* __restrict__ bl, double* __restrict__ dl_out,
-              double* __restrict__ scale_partial) {
+              double* __restrict__ scale_partial, const double* __restrict__ dp, int n_pt_blocks) {
   __shared__ double red[8];
   if (V.st->done) return;
+  if ((int)blockIdx.x >= n_pt_blocks) {   // the blocks behind the points update the cameras (SBACam::update)
+    update_cams_body(V, dp, ((int)blockIdx.x - n_pt_blocks) * 256 + (int)threadIdx.x);
+    return;
+  }
   const double lambda = V.st->lambda;
   const double* __restrict__ pts = V.pts[V.st->cur];
   double* __restrict__ pts_trial = V.pts[V.st->cur ^ 1];
@@ -940,36 +978,6 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
   }
   block_reduce<1, 256>(sc, red);
   if (threadIdx.x == 0) scale_partial[blockIdx.x] = sc[0];
-}
-
-// SBACam::update on every free camera (t += d[0:3]; q <- normalize(q * (sqrt(1-|v|^2), v))).
-__global__ void ba_update_cams(BAView V, const double* __restrict__ dp) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (V.st->done || c >= V.C) return;
-  const double* __restrict__ cams = V.cams[V.st->cur];
-  double* __restrict__ cams_trial = V.cams[V.st->cur ^ 1];
-  CamRT* __restrict__ camrt_trial = V.camrt[V.st->cur ^ 1];
-  double q[4] = {cams[7 * c], cams[7 * c + 1], cams[7 * c + 2], cams[7 * c + 3]};
-  double t[3] = {cams[7 * c + 4], cams[7 * c + 5], cams[7 * c + 6]};
-  const int col = V.cam_col[c];
-  if (col >= 0) {
-    const double* d = dp + 6 * col;
-    t[0] += d[0]; t[1] += d[1]; t[2] += d[2];
-    const double vx = d[3], vy = d[4], vz = d[5];
-    const double vw = sqrt(1.0 - (vx * vx + vy * vy + vz * vz));
-    const double x = q[3] * vx + q[0] * vw + q[1] * vz - q[2] * vy;
-    const double y = q[3] * vy - q[0] * vz + q[1] * vw + q[2] * vx;
-    const double z = q[3] * vz + q[0] * vy - q[1] * vx + q[2] * vw;
-    const double w = q[3] * vw - q[0] * vx - q[1] * vy - q[2] * vz;
-    const double inv = 1.0 / sqrt(x * x + y * y + z * z + w * w);
-    q[0] = x * inv; q[1] = y * inv; q[2] = z * inv; q[3] = w * inv;
-  }
-  double* o = cams_trial + 7 * c;
-  o[0] = q[0]; o[1] = q[1]; o[2] = q[2]; o[3] = q[3]; o[4] = t[0]; o[5] = t[1]; o[6] = t[2];
-  CamRT r;
-  quat_to_R(q, r.R);
-  r.t[0] = t[0]; r.t[1] = t[1]; r.t[2] = t[2];
-  camrt_trial[c] = r;
 }
 
 }  // namespace vslam
