@@ -236,21 +236,24 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
 }
 
 // Small systems (n <= kPcgSmallMax, e.g. the 9 free cameras of a local window): the same
-// Chronopoulos-Gear iteration in ONE warp, two rows per lane, S in shared memory (read by column:
-// S is symmetric, so lanes read consecutive addresses), no block barriers at all: an iteration
-// costs two __syncwarp and three shuffle reductions instead of five __syncthreads.
+// Chronopoulos-Gear iteration in ONE CTA of four warps with S in shared memory.  Warp 0 owns the
+// vectors (two rows per lane, in registers) and the scalar recurrences; the matrix-vector product is
+// split by COLUMN range over the four warps (S is symmetric, so a lane reads consecutive addresses)
+// and the four partials are added in warp order -> deterministic.  Two block barriers per iteration,
+// one division on the critical path (p^T S p = delta - beta^2 * previous p^T S p).
 constexpr int kPcgSmallMax = 64;
-
-constexpr int kPcgSmallThreads = 128;   // all four warps fetch S; warp 0 iterates
+constexpr int kPcgSmallThreads = 128;
 
 __global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_kernel(PcgArgs A) {
   extern __shared__ __align__(16) double sm[];
+  __shared__ int s_stop;
   if (A.done != nullptr && *A.done) return;
-  const int n = A.n, lane = threadIdx.x & 31;
+  const int n = A.n, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   double* Ss = sm;                     // [n][n]
   double* minv = Ss + n * n;           // [n/6][36]
   double* rs = minv + 6 * n;           // [64]
   double* us = rs + 64;                // [64]
+  double* part = us + 64;              // [4][64]
   {
     const double2* src = reinterpret_cast<const double2*>(A.S);   // n is a multiple of 6: n*n is even
     double2* dst = reinterpret_cast<double2*>(Ss);
@@ -258,85 +261,103 @@ __global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_kernel(PcgArgs 
     for (int i = threadIdx.x; i < (n * n) / 2; i += kPcgSmallThreads) dst[i] = __ldcg(src + i);
   }
   if (threadIdx.x < 64) { rs[threadIdx.x] = 0.0; us[threadIdx.x] = 0.0; }
+  if (threadIdx.x == 0) s_stop = 0;
   __syncthreads();
-  if (threadIdx.x >= 32) return;
   int fail = 0;
-  for (int bi = lane; bi < n / 6; bi += 32) {
+  for (int bi = threadIdx.x; bi < n / 6; bi += kPcgSmallThreads) {
     double blk[36];
     for (int i = 0; i < 6; ++i)
       for (int j = 0; j < 6; ++j) blk[6 * i + j] = Ss[(6 * bi + i) * n + 6 * bi + j];
     if (!spd6_inverse(blk)) fail = 1;
     for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
   }
-  fail = __any_sync(0xffffffffu, fail);
-  __syncwarp();
+  fail = __syncthreads_or(fail);
   const int i0 = lane, i1 = lane + 32;
   const bool h0 = i0 < n, h1 = i1 < n;
-  double x0 = 0.0, x1 = 0.0, p0 = 0.0, p1 = 0.0, s0 = 0.0, s1 = 0.0;
-  double r0 = h0 ? A.b[i0] : 0.0, r1 = h1 ? A.b[i1] : 0.0;
+  // column range of this warp (multiples of 2 so that the inner step is two columns)
+  const int cols = ((n + 7) / 8) * 2;
+  const int j0 = min(n, wid * cols), j1 = min(n, j0 + cols);
+  const double* c0 = Ss + (h0 ? i0 : 0);
+  const double* c1 = Ss + (h1 ? i1 : 0);
+  // warp 0 state
+  double x0 = 0.0, x1 = 0.0, p0 = 0.0, p1 = 0.0, s0 = 0.0, s1 = 0.0, u0 = 0.0, u1 = 0.0;
+  double r0 = 0.0, r1 = 0.0;
+  if (wid == 0) { r0 = h0 ? A.b[i0] : 0.0; r1 = h1 ? A.b[i1] : 0.0; }
   int status = fail ? 1 : 2, it = 0;
-  double gamma_old = 0.0, alpha_old = 0.0, thresh = 0.0;
+  double inv_gamma_old = 0.0, pap_old = 0.0, thresh = 0.0;
   if (!fail) {
-    for (it = 0; it <= A.max_iter; ++it) {
-      rs[i0] = r0; rs[i1] = r1;
-      __syncwarp();
-      double u0 = 0.0, u1 = 0.0;
-      if (h0) {
-        const double* m = minv + 36 * (i0 / 6) + 6 * (i0 % 6);
-        const double* rr6 = rs + 6 * (i0 / 6);
-#pragma unroll
-        for (int j = 0; j < 6; ++j) u0 += m[j] * rr6[j];
-      }
-      if (h1) {
-        const double* m = minv + 36 * (i1 / 6) + 6 * (i1 % 6);
-        const double* rr6 = rs + 6 * (i1 / 6);
-#pragma unroll
-        for (int j = 0; j < 6; ++j) u1 += m[j] * rr6[j];
-      }
-      us[i0] = u0; us[i1] = u1;
-      __syncwarp();
-      // w = S u, rows i0 and i1 (two accumulators each)
-      double wa = 0.0, wb = 0.0, wc = 0.0, wd = 0.0;
-      const double* c0 = Ss + (h0 ? i0 : 0);
-      const double* c1 = Ss + (h1 ? i1 : 0);
-      for (int j = 0; j < n; j += 6) {             // n is a multiple of 6; 18 independent loads per step
-        double a0[6], a1[6], uu[6];
-#pragma unroll
-        for (int q = 0; q < 6; ++q) { a0[q] = c0[(j + q) * n]; a1[q] = c1[(j + q) * n]; uu[q] = us[j + q]; }
-#pragma unroll
-        for (int q = 0; q < 6; q += 2) {
-          wa = fma(a0[q], uu[q], wa); wb = fma(a0[q + 1], uu[q + 1], wb);
-          wc = fma(a1[q], uu[q], wc); wd = fma(a1[q + 1], uu[q + 1], wd);
+    for (it = 0;; ++it) {
+      if (wid == 0) {
+        rs[i0] = r0; rs[i1] = r1;
+        __syncwarp();
+        u0 = 0.0; u1 = 0.0;
+        if (h0) {
+          const double* m = minv + 36 * (i0 / 6) + 6 * (i0 % 6);
+          const double* rr6 = rs + 6 * (i0 / 6);
+          u0 = (m[0] * rr6[0] + m[1] * rr6[1]) + (m[2] * rr6[2] + m[3] * rr6[3]) + (m[4] * rr6[4] + m[5] * rr6[5]);
         }
+        if (h1) {
+          const double* m = minv + 36 * (i1 / 6) + 6 * (i1 % 6);
+          const double* rr6 = rs + 6 * (i1 / 6);
+          u1 = (m[0] * rr6[0] + m[1] * rr6[1]) + (m[2] * rr6[2] + m[3] * rr6[3]) + (m[4] * rr6[4] + m[5] * rr6[5]);
+        }
+        us[i0] = u0; us[i1] = u1;
       }
-      const double w0 = h0 ? wa + wb : 0.0, w1 = h1 ? wc + wd : 0.0;
-      const double gamma = warp_sum(r0 * u0 + r1 * u1);
-      const double delta = warp_sum(w0 * u0 + w1 * u1);
-      const double rr = warp_sum(r0 * r0 + r1 * r1);
-      if (it == 0) {
-        if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
-        thresh = A.tol * A.tol * rr;
+      __syncthreads();
+      if (s_stop) break;
+      {   // partial w = S[:, j0:j1] u[j0:j1] for rows i0, i1
+        double wa = 0.0, wb = 0.0, wc = 0.0, wd = 0.0;
+        int j = j0;
+#pragma unroll 4
+        for (; j + 1 < j1; j += 2) {
+          const double ua = us[j], ub = us[j + 1];
+          wa = fma(c0[j * n], ua, wa); wb = fma(c0[(j + 1) * n], ub, wb);
+          wc = fma(c1[j * n], ua, wc); wd = fma(c1[(j + 1) * n], ub, wd);
+        }
+        if (j < j1) { wa = fma(c0[j * n], us[j], wa); wc = fma(c1[j * n], us[j], wc); }
+        part[wid * 64 + i0] = h0 ? wa + wb : 0.0;
+        part[wid * 64 + i1] = h1 ? wc + wd : 0.0;
       }
-      if (rr <= thresh && it > 0) { status = 0; break; }
-      if (it == A.max_iter) break;
-      double beta = 0.0, pap = delta;
-      if (it > 0) {
-        beta = gamma / gamma_old;
-        pap = delta - beta * gamma / alpha_old;        // = p^T S p in exact arithmetic
+      __syncthreads();
+      if (wid == 0) {
+        const double w0 = (part[i0] + part[64 + i0]) + (part[128 + i0] + part[192 + i0]);
+        const double w1 = (part[i1] + part[64 + i1]) + (part[128 + i1] + part[192 + i1]);
+        const double gamma = warp_sum(r0 * u0 + r1 * u1);
+        const double delta = warp_sum(w0 * u0 + w1 * u1);
+        const double rr = warp_sum(r0 * r0 + r1 * r1);
+        bool stop = false;
+        if (it == 0) {
+          if (!(rr > 0.0)) { status = 0; stop = true; }      // b == 0: x = 0
+          thresh = A.tol * A.tol * rr;
+        }
+        if (!stop && rr <= thresh && it > 0) { status = 0; stop = true; }
+        if (!stop && it == A.max_iter) stop = true;
+        if (!stop) {
+          double beta = 0.0, pap = delta;
+          if (it > 0) {
+            beta = gamma * inv_gamma_old;
+            pap = delta - beta * beta * pap_old;           // = p^T S p in exact arithmetic
+          }
+          if (!(pap > 0.0) || !isfinite(pap) || !(gamma > 0.0)) { status = 1; stop = true; }
+          else {
+            const double alpha = gamma / pap;
+            inv_gamma_old = 1.0 / gamma; pap_old = pap;
+            p0 = u0 + beta * p0; p1 = u1 + beta * p1;
+            s0 = w0 + beta * s0; s1 = w1 + beta * s1;
+            x0 += alpha * p0; x1 += alpha * p1;
+            r0 -= alpha * s0; r1 -= alpha * s1;
+          }
+        }
+        if (stop && lane == 0) s_stop = 1;
+        if (stop) --it;   // the loop header counts this pass again
       }
-      if (!(pap > 0.0) || !isfinite(pap) || !(gamma > 0.0)) { status = 1; break; }
-      const double alpha = gamma / pap;
-      p0 = u0 + beta * p0; p1 = u1 + beta * p1;
-      s0 = w0 + beta * s0; s1 = w1 + beta * s1;
-      x0 += alpha * p0; x1 += alpha * p1;
-      r0 -= alpha * s0; r1 -= alpha * s1;
-      gamma_old = gamma; alpha_old = alpha;
-      __syncwarp();
     }
   }
-  if (h0) A.x[i0] = (status == 1) ? 0.0 : x0;
-  if (h1) A.x[i1] = (status == 1) ? 0.0 : x1;
-  if (lane == 0) { *A.status = status; *A.iters = it; }
+  if (wid == 0) {
+    if (h0) A.x[i0] = (status == 1) ? 0.0 : x0;
+    if (h1) A.x[i1] = (status == 1) ? 0.0 : x1;
+    if (lane == 0) { *A.status = status; *A.iters = it; }
+  }
 }
 
 }  // namespace vslam
