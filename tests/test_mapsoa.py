@@ -1,0 +1,97 @@
+"""MapSoA: packing equals the drop-in's graph; BA through it equals the drop-in's BA."""
+import numpy as np
+import pytest
+
+from visual_slam_b200.ba_problem import synthetic_ba
+from map_helpers import _Cam, _map_from_problem
+
+
+def _canon(prob):
+    order = np.lexsort((prob.obs_pt, prob.obs_cam))
+    return prob.obs_cam[order], prob.obs_pt[order], prob.obs_uv[order]
+
+
+def test_packing_matches_the_drop_in_graph_builder():
+    from visual_slam_b200.ba import BundleAdjustment
+    from visual_slam_b200.mapsoa import MapSoA
+    p = synthetic_ba(6, 200, 4.0, seed=5)
+    m = _map_from_problem(p)
+    ba = BundleAdjustment.__new__(BundleAdjustment)          # graph construction only: no device needed
+    ba.fx, ba.fy, ba.cx, ba.cy = _Cam.fx, _Cam.fy, _Cam.cx, _Cam.cy
+    ba._poses, ba._points, ba._edges, ba._scale, ba._result = {}, {}, [], [], None
+    frame_ids = list(m.frames.keys())
+    for fid in frame_ids:
+        fr = m.GetFrame(fid)
+        ba.add_pose(fid, fr.GetPose(), fixed=(fid == 0))
+        if fid != 0:
+            for par in fr.GetParentIDs():
+                ba.AddScalingEdge(par, fid, fr.GetTransitionWithParentID(par))
+    ba._add_points_and_edges(m, frame_ids, list(m.points_3d.keys()), fixed=False)
+    ref, _, _ = ba._problem()
+    soa = MapSoA.from_map(m)
+    got = soa.problem((_Cam.fx, _Cam.fy, _Cam.cx, _Cam.cy))
+    assert soa.n_frames == p.n_cams and soa.n_points == p.n_pts and soa.n_observations == p.n_obs
+    assert np.allclose(got.cams, ref.cams, atol=1e-15) and np.array_equal(got.pts, ref.pts)
+    for a, b in zip(_canon(got), _canon(ref)):
+        assert np.array_equal(a, b)
+    assert np.array_equal(got.cam_fixed, ref.cam_fixed) and np.array_equal(got.pt_fixed, ref.pt_fixed)
+    assert sorted(zip(got.scale_a, got.scale_b, got.scale_meas)) == sorted(zip(ref.scale_a, ref.scale_b, ref.scale_meas))
+    mo = soa.problem((_Cam.fx, _Cam.fy, _Cam.cx, _Cam.cy), motion_only=True)
+    assert mo.pt_fixed.all() and mo.n_scale == 0
+
+
+def test_incremental_api_and_error_conventions():
+    from visual_slam_b200.mapsoa import MapSoA
+    s = MapSoA()
+    s.AddFrame(0, np.eye(4), keyframe=True)
+    with pytest.raises(Exception, match="Duplicate frame warning"):
+        s.AddFrame(0, np.eye(4))
+    with pytest.raises(Exception, match="No point yet added"):
+        s.AddObservation(3, 0, (1.0, 2.0))
+    s.AddPoint3D(3, [0, 0, 2.0])
+    with pytest.raises(Exception, match="No frame yet added"):
+        s.AddObservation(3, 9, (1.0, 2.0))
+    for k in range(100):                                   # growth past the initial capacity
+        s.AddPoint3D(10 + k, [k, 0, 3.0])
+        s.AddObservation(10 + k, 0, (k, k))
+    assert s.n_points == 101 and s.n_observations == 100
+    T = np.eye(4); T[:3, 3] = [1, 2, 3]
+    s.UpdatePose(T, 0)
+    assert np.allclose(s.GetPose(0), T)
+    s.UpdatePoint3D([7, 8, 9], 3)
+    assert np.array_equal(s.GetAll3DPoints()[0], [7, 8, 9])
+
+
+@pytest.mark.gpu
+def test_ba_through_mapsoa_equals_the_drop_in():
+    from visual_slam_b200.ba import BundleAdjustment
+    from visual_slam_b200.mapsoa import MapSoA
+    p = synthetic_ba(5, 300, 4.0, seed=13)
+    m = _map_from_problem(p)
+    soa = MapSoA.from_map(m)
+    ba = BundleAdjustment(_Cam())
+    ba.localBundleAdjustement(m)                            # mutates m
+    sink = _map_from_problem(p)
+    st = soa.localBundleAdjustement(_Cam(), sink=sink)
+    assert st["final_cost"] == ba.stats["final_cost"]       # same arrays, same kernels: bit-identical
+    for c in range(p.n_cams):
+        assert np.allclose(sink.frames[c].pose, m.frames[c].pose, atol=1e-12)
+        assert np.allclose(soa.GetPose(c), m.frames[c].pose, atol=1e-12)
+    assert np.allclose(soa.GetAll3DPoints(), np.array([m.points_3d[j].location_3d for j in range(p.n_pts)]), atol=1e-12)
+    # unchanged structure: the solver object is reused (state upload only) and converges further
+    eng = soa._engine[1]
+    st2 = soa.localBundleAdjustement(_Cam())
+    assert soa._engine[1] is eng and st2["initial_cost"] <= st["final_cost"] * (1 + 1e-9)
+    # a structural change rebuilds it
+    soa.AddPoint3D(10 ** 6, [0.0, 0.0, 3.0])
+    soa.AddObservation(10 ** 6, 1, (300.0, 200.0)); soa.AddObservation(10 ** 6, 2, (310.0, 205.0))
+    soa.localBundleAdjustement(_Cam())
+    assert soa._engine[1] is not eng
+    # motion only
+    p2 = synthetic_ba(5, 300, 4.0, seed=14, motion_only=True)
+    m2 = _map_from_problem(p2); m2.frames[0].kf = True
+    soa2 = MapSoA.from_map(m2)
+    ba2 = BundleAdjustment(_Cam()); ba2.motionOnlyBundleAdjustement(m2)
+    st3 = soa2.motionOnlyBundleAdjustement(_Cam())
+    assert st3["final_cost"] == ba2.stats["final_cost"]
+    soa.close(); soa2.close()
