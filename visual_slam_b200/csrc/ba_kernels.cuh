@@ -797,12 +797,13 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
     }
     cp_async_commit();
   };
-  int ia_n, ib_n;
+  int ia_n, ib_n, ia_m, ib_m;   // indices of rounds it + kSchurStages and it + kSchurStages + 1
   {
     int ia[kSchurStages], ib[kSchurStages];
 #pragma unroll
     for (int s = 0; s < kSchurStages; ++s) load_idx(s, ia[s], ib[s]);
     load_idx(kSchurStages, ia_n, ib_n);
+    load_idx(kSchurStages + 1, ia_m, ib_m);
 #pragma unroll
     for (int s = 0; s < kSchurStages; ++s) issue(s, ia[s], ib[s]);
   }
@@ -829,15 +830,20 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
     }
     // refill this stage with round it + kSchurStages (indices arrived a round ago)
     const int ia_u = ia_n, ib_u = ib_n;
-    load_idx(it + kSchurStages + 1, ia_n, ib_n);
+    ia_n = ia_m; ib_n = ib_m;
+    load_idx(it + kSchurStages + 2, ia_m, ib_m);     // two rounds ahead of its use
     __syncwarp();                                    // all lanes are done reading the stage
     issue(it + kSchurStages, ia_u, ib_u);
   }
+  // 36 warp sums: 32 of them by the transposed butterfly (31 shuffles instead of 160), 4 plain
+  {
+    double tail[4] = {acc[32], acc[33], acc[34], acc[35]};
+    double (&head)[32] = reinterpret_cast<double (&)[32]>(acc);
+    warp_transpose_sum32(head, lane);                // lane L now holds the total of entry L in head[0]
 #pragma unroll
-  for (int i = 0; i < 36; ++i) acc[i] = warp_sum(acc[i]);
-  if (lane == 0) {
-#pragma unroll
-    for (int i = 0; i < 36; ++i) partial[(size_t)u * 36 + i] = acc[i];
+    for (int i = 0; i < 4; ++i) tail[i] = warp_sum(tail[i]);
+    partial[(size_t)u * 36 + lane] = head[0];
+    if (lane < 4) partial[(size_t)u * 36 + 32 + lane] = lane == 0 ? tail[0] : lane == 1 ? tail[1] : lane == 2 ? tail[2] : tail[3];
   }
 }
 
