@@ -761,12 +761,12 @@ ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict_
 // (lane-per-block reads at 144 B stride are conflict-free).  Item indices are prefetched one round
 // further ahead.  (One bulk async copy per block was measured slower: the TMA unit retires about one
 // small copy per 15 cycles per SM.)
-constexpr int kSchurStages = 3;
+constexpr int kSchurStages = 2;
 constexpr int kSchurWarps = 4;
 constexpr int kSchurStageDoubles = 2 * 32 * 18;   // A blocks [32][18] then B blocks [32][18]
 constexpr int kSchurSmem = kSchurWarps * kSchurStages * kSchurStageDoubles * 8;
 
-__global__ void __launch_bounds__(kSchurWarps * 32, 2)
+__global__ void __launch_bounds__(kSchurWarps * 32, 3)
 ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
                const int* __restrict__ item_a, const int* __restrict__ item_b,
                const int* __restrict__ unit_start, const int* __restrict__ unit_len, int n_units,
