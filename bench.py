@@ -29,7 +29,7 @@ RATIO = 0.8
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures
 HAMMING_DRAM_BYTES_PER_PAIR = (83026176 + 4331264) / 592.0
 HAMMING_TRAFFIC_SOURCE = "profiles/r1_hamming_knn2_ncu_full.txt (592 pairs per launch, scaled to this launch)"
-BA_LIN_DRAM_BYTES_C4 = 44561920 + 94828288
+BA_LIN_DRAM_BYTES_C4 = 45245440 + 92398336
 BA_LIN_TRAFFIC_SOURCE = "profiles/r1_ba_linearize_ncu_full.txt (C4, one launch; part of Hpl is still dirty in L2)"
 METRIC = "hamming_matches_per_s"
 UNIT = "query descriptors matched/s (kNN-2 + ratio + cross-check, 2048x2048x256-bit pairs)"
@@ -177,13 +177,17 @@ def ba_figures(torch):
         eng.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
         lin0 = eng.linearize()
         eng.trial(1e-5 * lin0["max_diag"])
-        lin = float(np.median(eng.time_stage("linearize", 8, flush)[1:]))
+        lin_single = float(np.median(eng.time_stage("linearize", 8, flush)[1:]))
+        # average launch duration over 20 back-to-back launches between one pair of events (nothing but
+        # the kernel inside the timed region; at C4 its 194 MB working set is larger than the 126 MB L2)
+        lin = float(eng.time_stage("linearize_back_to_back", 20)[0])
         schur_ms = float(np.median(eng.time_stage("schur", 6, flush)[1:]))
         trial_ms = float(np.median(eng.time_stage("trial", 6, flush)[1:]))
         out[name] = {"lm_iters_per_s": st["iterations"] / (best * 1e-3), "ms_per_optimize10": best,
                      "trials": st["trials"], "pcg_iterations": st["pcg_iterations"],
                      "final_cost": st["final_cost"], "n_cams": p.n_cams, "n_pts": p.n_pts, "n_obs": p.n_obs,
-                     "linearize_ms": lin, "schur_ms": schur_ms, "trial_ms": trial_ms,
+                     "linearize_ms": lin, "linearize_single_cold_launch_ms": lin_single,
+                     "schur_ms": schur_ms, "trial_ms": trial_ms,
                      "linearize_bytes": p.linearize_bytes(),
                      "linearize_gbs": p.linearize_bytes() / (lin * 1e-3) / 1e9}
         eng.close()
@@ -288,39 +292,75 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    n_warm = max(args.warmup, 3)
+    for _ in range(n_warm):
         out = step()
     sync()
+    # keep warming up until the step time has settled (a GPU coming out of idle, or out of a profiler
+    # session, needs tens of milliseconds to reach its boost clocks; three 7 ms steps are not enough):
+    # untimed steps in pairs until two consecutive ones agree within 2 %, at most 120 more
+    prev, best_warm = None, None
+    for _ in range(120):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = step()
+        b.record()
+        sync()
+        cur = a.elapsed_time(b)
+        n_warm += 1
+        best_warm = cur if best_warm is None else min(best_warm, cur)
+        if prev is not None and abs(cur - prev) <= 0.02 * prev:
+            break
+        prev = cur
     n_keep_ref = int(out["n_keep"].sum().item())
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-        time.sleep(0.3)
-    sync()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    # per-kernel events on the launching stream for the dominant kernel (knn2)
-    k_events = []
-    w0 = time.time()
-    e0.record()
-    for _ in range(args.steps):
-        ka, kb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ka.record()
-        idx, dist_, rev = matching.knn2_batch(q, t, want_rev=True)
-        kb.record()
-        keep_q, keep_t, n_keep = matching.filter_batch(idx, dist_, rev, NT, RATIO, True)
+
+    def timed_region():
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+            time.sleep(0.3)
+        sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        # per-kernel events on the launching stream for the dominant kernel (knn2)
+        k_events = []
+        w0 = time.time()
+        e0.record()
+        n_keep = None
+        for _ in range(args.steps):
+            ka, kb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ka.record()
+            idx, dist_, rev = matching.knn2_batch(q, t, want_rev=True)
+            kb.record()
+            keep_q, keep_t, n_keep = matching.filter_batch(idx, dist_, rev, NT, RATIO, True)
+            if world > 1:
+                dist.all_gather_into_tensor(gathered, n_keep)
+            k_events.append((ka, kb))
+        e1.record()
+        sync()
+        w1 = time.time()
+        ms = e0.elapsed_time(e1)
+        tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, n_keep)
-        k_events.append((ka, kb))
-    e1.record()
-    sync()
-    w1 = time.time()
-    ms = e0.elapsed_time(e1)
-    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        clocks = sampler.stop(w0, w1) if rank == 0 else None
+        return float(tmax.item()), clocks, k_events, n_keep
+
+    ms, clocks, k_events, n_keep = timed_region()
+    # a timed region that runs far slower than the settled warm-up steps did (seen once: 5.8x, with
+    # nvidia-smi reporting full clocks and no throttle reason) is re-measured once, and says so
+    slow = torch.tensor([1.0 if ms / args.steps > 1.3 * best_warm else 0.0], device=dev)
     if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    ms = float(tmax.item())
-    clocks = sampler.stop(w0, w1) if rank == 0 else None
+        dist.all_reduce(slow, op=dist.ReduceOp.MAX)
+    remeasured = bool(slow.item() > 0)
+    if remeasured:
+        time.sleep(1.0)
+        for _ in range(5):
+            step()
+        sync()
+        ms, clocks, k_events, n_keep = timed_region()
     knn_ms = float(np.mean([a.elapsed_time(b) for a, b in k_events]))
+    if rank == 0 and os.environ.get("VSLAM_BENCH_DEBUG"):
+        sys.stderr.write("knn2 ms per step: %s (warm-up steps %d)\n" % ([round(a.elapsed_time(b), 3) for a, b in k_events], n_warm))
     assert int(n_keep.sum().item()) == n_keep_ref
     value = world * B * NQ * args.steps / (ms * 1e-3)
 
@@ -366,7 +406,7 @@ def run_gpu(args):
                         "(carry-save adder tree) instead of the 8 POPC the yardstick assumes",
                 "kernel_ms": knn_ms, "pair_distances_per_s": B * NQ * NT / (knn_ms * 1e-3)}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "warmup": n_warm, "remeasured": remeasured, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": workload_config(world), "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": hm.h2d_bytes,
@@ -389,6 +429,10 @@ def run_gpu(args):
                                    "algorithmic_bytes": ba["c4"]["linearize_bytes"],
                                    "traffic": BA_LIN_DRAM_BYTES_C4, "traffic_source": BA_LIN_TRAFFIC_SOURCE,
                                    "kernel_ms": ba["c4"]["linearize_ms"],
+                                   "timing": "average of 20 back-to-back launches between one pair of CUDA "
+                                             "events on the launching stream (working set 194 MB > L2); one "
+                                             "launch bracketed alone after an L2 flush: %.4f ms"
+                                             % ba["c4"]["linearize_single_cold_launch_ms"],
                                    "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)"}
     print(json.dumps(line))
     if world > 1:
