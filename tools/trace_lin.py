@@ -27,3 +27,15 @@ print("end-time percentiles us:", [round(float(np.percentile(ends, q)), 1) for q
 late = np.argsort(-t[:, 2])[:8]
 for i in late:
     print("  cta %5d kind %d start %.1f end %.1f" % (i, t[i, 0], t[i, 1] / 1e3, t[i, 2] / 1e3))
+# duration against start time, and the number of resident CTAs over time
+st, en = t[:, 1] / 1e3, t[:, 2] / 1e3
+edges = np.arange(0, st.max() + 5, 5.0)
+for kind, nm in ((0, "camera"), (1, "point")):
+    m = t[:, 0] == kind
+    row = []
+    for a, b in zip(edges[:-1], edges[1:]):
+        s = m & (st >= a) & (st < b)
+        row.append("%4.1f-%4.1f: n=%4d med %.1f" % (a, b, s.sum(), np.median((en - st)[s]) if s.any() else 0.0))
+    print(nm, "duration by start time |", " | ".join(row))
+grid = np.arange(0, en.max(), 2.5)
+print("resident CTAs at t:", [(float(x), int(((st <= x) & (en > x)).sum())) for x in grid])
