@@ -215,6 +215,18 @@ int vslam_triangulate(const double* proj, const double* extr, const double* x1, 
                       const int32_t* n_pts, int n_max, int batch, double z_max, double* Xh, double* X3,
                       double* depth, uint8_t* good, void* stream);
 
+/*
+ * Unmatched-feature selection: indices of the rows of kp1 that are "not in" kp2, reference
+ * src/v2/helper_functions.py:316-326 (`GetListDiff`, used at src/v2/main.py:239).
+ *   kp1   dev f64 [n1][2], kp2 dev f64 [n2][2]   pixel coordinates (exact comparison)
+ *   mode  0: the reference's effective test, numpy `x not in kp2` = no row of kp2 shares EITHER coordinate
+ *            with x;  1: row-wise test (both coordinates equal), what the reference's dead loop spells out
+ *   keep      dev u8  [n1]  scratch / 1 where the row is kept
+ *   keep_idx  dev i32 [n1]  ascending kept indices, first *n_keep valid;  n_keep dev i32 [1]
+ */
+int vslam_list_diff(const double* kp1, int n1, const double* kp2, int n2, int mode, uint8_t* keep,
+                    int32_t* keep_idx, int32_t* n_keep, void* stream);
+
 /* ------------------------------------------------------------------------- */
 /* 3. Bundle adjustment                                                       */
 /* ------------------------------------------------------------------------- */

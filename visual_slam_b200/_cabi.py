@@ -40,6 +40,7 @@ def _declare(lib):
                                            vp, vp]
     lib.vslam_recover_pose.argtypes = [vp, vp, vp, vp, i32, i32, pd, f64, vp, vp, vp, vp, vp, vp]
     lib.vslam_triangulate.argtypes = [vp, vp, vp, vp, vp, i32, i32, f64, vp, vp, vp, vp, vp]
+    lib.vslam_list_diff.argtypes = [vp, i32, vp, i32, i32, vp, vp, vp, vp]
     pp = C.POINTER(vp)
     lib.vslam_ba_create.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.vslam_ba_destroy.argtypes = [vp]

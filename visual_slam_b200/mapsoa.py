@@ -130,6 +130,46 @@ class MapSoA:
     def GetAll3DPoints(self):
         return self._pts.view().copy()
 
+    # ---- key-frame bookkeeping ---------------------------------------------------
+    def GetNVisibleFrames(self):
+        """Per point row: the number of distinct frames observing it (point.py:58-59)."""
+        C = max(self._cams.n, 1)
+        pairs = np.unique(self._op.view().astype(np.int64) * C + self._oc.view())
+        return np.bincount(pairs // C, minlength=self._pts.n)
+
+    def DiscardOutlierMapPoints(self, n_visible_frames=3):
+        """map.py:124-131: drop the map points seen in fewer than n_visible_frames frames, together with
+        their observations; the order of the remaining points is kept.  Vectorised (no per-point probes)."""
+        keep = self.GetNVisibleFrames() >= n_visible_frames
+        if keep.all():
+            return 0
+        new_row = np.cumsum(keep) - 1
+        ok = keep[self._op.view()]
+        oc, op, uv = self._oc.view()[ok], new_row[self._op.view()[ok]].astype(np.int32), self._uv.view()[ok]
+        pts = self._pts.view()[keep]
+        self._pids = [pid for pid, k in zip(self._pids, keep) if k]
+        self._pidx = {pid: r for r, pid in enumerate(self._pids)}
+        for g, v in ((self._oc, oc), (self._op, op), (self._uv, uv), (self._pts, pts)):
+            g.a[:len(v)] = v
+            g.n = len(v)
+        self._version += 1
+        return int((~keep).sum())
+
+    def GetImagePointsWithFrameID(self, frame_id):
+        """map.py:28-44: (image_points, descriptors, locations_3d, point_ids) of the map points seen by
+        frame_id, in map order.  Descriptors are not kept in the arrays: that slot is None."""
+        row = self._fidx[frame_id]
+        sel = np.nonzero(self._oc.view() == row)[0]
+        # a point keeps ONE correspondence per frame (Point.frames is a dict: the last one added wins)
+        op = self._op.view()[sel]
+        order = np.lexsort((sel, op))
+        sel, op = sel[order], op[order]
+        last = np.ones(len(op), bool)
+        last[:-1] = op[1:] != op[:-1]
+        sel, op = sel[last], op[last]
+        ids = np.array([self._pids[r] for r in op])
+        return self._uv.view()[sel].copy(), None, self._pts.view()[op].copy(), ids
+
     def problem(self, K, motion_only=False):
         """The BAProblem of the whole map: vectorised, no per-element Python work."""
         C, P = self._cams.n, self._pts.n
