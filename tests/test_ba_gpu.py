@@ -154,3 +154,49 @@ def test_drop_in_bundle_adjustment_class_local_and_motion_only():
     ba3.localBundleAdjustement(m3, scale=True)
     med = np.median(np.linalg.norm(ref.pts, axis=1))
     assert np.allclose(np.array([m3.points_3d[j].location_3d for j in range(p.n_pts)]), ref.pts / med, atol=1e-5)
+
+
+def _subset(p, keep):
+    return BAProblem(p.cams, p.pts, p.obs_cam[keep], p.obs_pt[keep], p.obs_uv[keep], p.K, p.cam_fixed, None,
+                     None, None, None)
+
+
+def test_degenerate_structures_are_handled_like_the_restatement():
+    """Structure-only BA, a free camera nobody observes, points seen once, nothing free, an empty problem."""
+    p = synthetic_ba(5, 200, 4.0, seed=1)
+    all_fixed = np.ones(p.n_cams, bool)
+    a = BAProblem(p.cams, p.pts, p.obs_cam, p.obs_pt, p.obs_uv, p.K, all_fixed, None, None, None, None)
+    b = _subset(p, p.obs_cam != 4)
+    c = _subset(p, ~((p.obs_pt < 20) & (p.obs_cam > 0)))
+    for q in (a, b, c):
+        ref, got = q.copy(), q.copy()
+        h = oba.optimize(ref, 5)
+        st = solve_problem(got, 5)
+        assert abs(st["final_cost"] - h["final_cost"]) <= 1e-4 * h["final_cost"]
+        assert abs(oba.cost(got) - st["final_cost"]) <= 1e-9 * st["final_cost"]
+        assert st["final_cost"] < st["initial_cost"]
+    d = BAProblem(p.cams.copy(), p.pts.copy(), p.obs_cam, p.obs_pt, p.obs_uv, p.K, all_fixed, np.ones(p.n_pts, bool),
+                  None, None, None)
+    st = solve_problem(d, 5)                      # nothing to optimise: state and cost untouched
+    assert st["final_cost"] == st["initial_cost"] and np.array_equal(d.cams, p.cams) and np.array_equal(d.pts, p.pts)
+    e = synthetic_ba(1, 50, 1.0, seed=2, with_scale=False)   # no point is seen twice: no observations at all
+    assert e.n_obs == 0 and solve_problem(e, 5)["final_cost"] == 0.0
+
+
+def test_c4_full_size_properties():
+    """BASELINE configs[3] (200 key frames, 1e5 points, ~1e6 observations): size-independent checks."""
+    p = synthetic_ba(n_cams=200, n_pts=100000, obs_per_pt=10.0, seed=1)
+    a, b = p.copy(), p.copy()
+    sa, sb = solve_problem(a, 5), solve_problem(b, 5)
+    assert sa == sb and np.array_equal(a.cams, b.cams) and np.array_equal(a.pts, b.pts)   # bit-reproducible
+    assert sa["final_cost"] < 0.5 * sa["initial_cost"]
+    assert abs(oba.cost(a) - sa["final_cost"]) <= 1e-9 * sa["final_cost"]               # independent recomputation
+    assert abs(oba.cost(p) - sa["initial_cost"]) <= 1e-9 * sa["initial_cost"]
+    # the gradient of the linearised system against the restatement's vectorised residuals: b = -J^T W e
+    eng = BAEngine(p)
+    lin = eng.linearize()
+    assert abs(lin["cost"] - oba.cost(p)) <= 1e-11 * lin["cost"]
+    bl = eng.read("bl").cpu().numpy()
+    Hll = eng.read("Hll").cpu().numpy()
+    assert np.isfinite(bl).all() and (Hll[:, [0, 3, 5]] > 0).all()      # every free point is constrained
+    eng.close()
