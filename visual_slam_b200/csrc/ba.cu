@@ -210,7 +210,7 @@ struct BA {
   }
 };
 
-static size_t pcg_small_smem(int n) { return sizeof(double) * ((size_t)n * n + 6 * (size_t)n + 128 + 256); }
+static size_t pcg_small_smem(int n) { return sizeof(double) * ((size_t)n * n + 6 * (size_t)n + 16 * 64); }   // S, M^-1, r/u copies, partials
 
 static void counting_sort(const std::vector<int>& in, const int* key, int n_keys, std::vector<int>& out) {
   std::vector<int> cnt(n_keys + 1, 0);

@@ -44,39 +44,59 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target, in
   __syncthreads();
 }
 
-// In-place inverse of a 6x6 SPD matrix via Cholesky; returns false if a pivot is not positive.
-__device__ inline bool spd6_inverse(double* A /* 36 row-major */) {
-  double L[36];
-#pragma unroll 1
-  for (int j = 0; j < 6; ++j) {
-    double d = A[7 * j];
-    for (int k = 0; k < j; ++k) d -= L[6 * j + k] * L[6 * j + k];
-    if (!(d > 0.0)) return false;
-    d = sqrt(d);
-    L[7 * j] = d;
-    for (int i = j + 1; i < 6; ++i) {
-      double s = A[6 * i + j];
-      for (int k = 0; k < j; ++k) s -= L[6 * i + k] * L[6 * j + k];
-      L[6 * i + j] = s / d;
-    }
+// In-place inverse of a 6x6 SPD matrix via Cholesky; returns false if a pivot is not positive (or not a
+// finite normal number).  Columns are template instances so that every index is a constant and all three
+// 6x6 arrays stay in registers (the looped form lived in local memory and cost ~12 us per call); one
+// reciprocal square root per pivot instead of a sqrt and divisions.
+template <int J>
+__device__ __forceinline__ void spd6_chol_col(const double (&A)[36], double (&L)[36], double (&ri)[6], bool& ok) {
+  double d = A[7 * J];
+#pragma unroll
+  for (int k = 0; k < J; ++k) d = fma(-L[6 * J + k], L[6 * J + k], d);
+  ok = ok && (d > 1e-290) && (d < 1e290);
+  ri[J] = fast_rsqrt(ok ? d : 1.0);
+  L[7 * J] = d * ri[J];
+#pragma unroll
+  for (int i = J + 1; i < 6; ++i) {
+    double t = A[6 * i + J];
+#pragma unroll
+    for (int k = 0; k < J; ++k) t = fma(-L[6 * i + k], L[6 * J + k], t);
+    L[6 * i + J] = t * ri[J];
   }
+}
+template <int J>
+__device__ __forceinline__ void spd6_linv_col(const double (&L)[36], const double (&ri)[6], double (&Li)[36]) {
+  Li[7 * J] = ri[J];
+#pragma unroll
+  for (int i = J + 1; i < 6; ++i) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = J; k < i; ++k) t = fma(-L[6 * i + k], Li[6 * k + J], t);
+    Li[6 * i + J] = t * ri[i];
+  }
+}
+template <int I>
+__device__ __forceinline__ void spd6_ltl_row(const double (&Li)[36], double (&A)[36]) {
+#pragma unroll
+  for (int j = I; j < 6; ++j) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = j; k < 6; ++k) t = fma(Li[6 * k + I], Li[6 * k + j], t);
+    A[6 * I + j] = t;
+    A[6 * j + I] = t;
+  }
+}
+__device__ __forceinline__ bool spd6_inverse(double (&A)[36] /* row-major */) {
+  double L[36], Li[36], ri[6];
+  bool ok = true;
+  spd6_chol_col<0>(A, L, ri, ok); spd6_chol_col<1>(A, L, ri, ok); spd6_chol_col<2>(A, L, ri, ok);
+  spd6_chol_col<3>(A, L, ri, ok); spd6_chol_col<4>(A, L, ri, ok); spd6_chol_col<5>(A, L, ri, ok);
+  if (!ok) return false;
   // inverse of L (lower), then A^-1 = L^-T L^-1
-  double Li[36];
-  for (int i = 0; i < 36; ++i) Li[i] = 0.0;
-  for (int j = 0; j < 6; ++j) {
-    Li[7 * j] = 1.0 / L[7 * j];
-    for (int i = j + 1; i < 6; ++i) {
-      double s = 0.0;
-      for (int k = j; k < i; ++k) s -= L[6 * i + k] * Li[6 * k + j];
-      Li[6 * i + j] = s / L[7 * i];
-    }
-  }
-  for (int i = 0; i < 6; ++i)
-    for (int j = 0; j < 6; ++j) {
-      double s = 0.0;
-      for (int k = (i > j ? i : j); k < 6; ++k) s += Li[6 * k + i] * Li[6 * k + j];
-      A[6 * i + j] = s;
-    }
+  spd6_linv_col<0>(L, ri, Li); spd6_linv_col<1>(L, ri, Li); spd6_linv_col<2>(L, ri, Li);
+  spd6_linv_col<3>(L, ri, Li); spd6_linv_col<4>(L, ri, Li); spd6_linv_col<5>(L, ri, Li);
+  spd6_ltl_row<0>(Li, A); spd6_ltl_row<1>(Li, A); spd6_ltl_row<2>(Li, A);
+  spd6_ltl_row<3>(Li, A); spd6_ltl_row<4>(Li, A); spd6_ltl_row<5>(Li, A);
   return true;
 }
 
@@ -158,9 +178,13 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
   // block-Jacobi preconditioner: invert the local diagonal 6x6 blocks
   for (int bi = tid; bi < R / 6; bi += kPcgThreads) {
     double blk[36];
-    for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
       for (int j = 0; j < 6; ++j) blk[6 * i + j] = Srows[(size_t)(6 * bi + i) * n + row0 + 6 * bi + j];
+    }
     if (!spd6_inverse(blk)) s_fail = 1;
+#pragma unroll
     for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
   }
   for (int i = tid; i < R; i += kPcgThreads) { xl[i] = 0.0; rl[i] = A.b[row0 + i]; pl[i] = 0.0; sl[i] = 0.0; }
@@ -236,121 +260,127 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
 }
 
 // Small systems (n <= kPcgSmallMax, e.g. the 9 free cameras of a local window): the same
-// Chronopoulos-Gear iteration in ONE CTA of four warps with S in shared memory.  Warp 0 owns the
-// vectors (two rows per lane, in registers) and the scalar recurrences; the matrix-vector product is
-// split by COLUMN range over the four warps (S is symmetric, so a lane reads consecutive addresses)
-// and the four partials are added in warp order -> deterministic.  Two block barriers per iteration,
-// one division on the critical path (p^T S p = delta - beta^2 * previous p^T S p).
+// Chronopoulos-Gear iteration in ONE CTA of four warps with S in shared memory.  EVERY warp keeps the
+// vectors (two rows per lane, in registers) and runs the scalar recurrences redundantly -- identical
+// instructions on identical data, so all warps agree bit for bit and nobody waits for an owner; the
+// matrix-vector product is split by COLUMN range over the four warps (S is symmetric, so a lane reads
+// consecutive addresses) and the four partials are added in warp order -> deterministic.  ONE block
+// barrier per iteration (partials double-buffered), reciprocals instead of divisions on the critical
+// path (p^T S p = delta - beta^2 * previous p^T S p).  Setup: S arrives by cp.async while nine lanes
+// invert the diagonal blocks straight from global memory.
 constexpr int kPcgSmallMax = 64;
 constexpr int kPcgSmallThreads = 128;
+constexpr int kPcgSmallWarps = kPcgSmallThreads / 32;
 
 __global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_kernel(PcgArgs A) {
   extern __shared__ __align__(16) double sm[];
-  __shared__ int s_stop;
   if (A.done != nullptr && *A.done) return;
   const int n = A.n, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  double* Ss = sm;                     // [n][n]
-  double* minv = Ss + n * n;           // [n/6][36]
-  double* rs = minv + 6 * n;           // [64]
-  double* us = rs + 64;                // [64]
-  double* part = us + 64;              // [4][64]
+  double* Ss = sm;                                  // [n][n]
+  double* minv = Ss + n * n;                        // [n/6][36]
+  double* rs = minv + 6 * n + wid * 64;             // [warps][64] each warp's own copy of r
+  double* us = minv + 6 * n + (kPcgSmallWarps + wid) * 64;   // [warps][64] ... of u
+  double* part = minv + 6 * n + 2 * kPcgSmallWarps * 64;     // [2][warps][64]
   {
     const double2* src = reinterpret_cast<const double2*>(A.S);   // n is a multiple of 6: n*n is even
     double2* dst = reinterpret_cast<double2*>(Ss);
-#pragma unroll 4
-    for (int i = threadIdx.x; i < (n * n) / 2; i += kPcgSmallThreads) dst[i] = __ldcg(src + i);
+    if ((reinterpret_cast<uintptr_t>(A.S) & 15) == 0) {
+      for (int i = threadIdx.x; i < (n * n) / 2; i += kPcgSmallThreads) cp_async16(dst + i, src + i);
+    } else {                                        // caller's view starts on an odd element
+      for (int i = threadIdx.x; i < n * n; i += kPcgSmallThreads) Ss[i] = __ldcg(A.S + i);
+    }
+    cp_async_commit();
   }
-  if (threadIdx.x < 64) { rs[threadIdx.x] = 0.0; us[threadIdx.x] = 0.0; }
-  if (threadIdx.x == 0) s_stop = 0;
-  __syncthreads();
   int fail = 0;
-  for (int bi = threadIdx.x; bi < n / 6; bi += kPcgSmallThreads) {
+  if (threadIdx.x < n / 6) {                        // n <= 64: at most ten blocks, all in warp 0
+    const int bi = threadIdx.x;
     double blk[36];
-    for (int i = 0; i < 6; ++i)
-      for (int j = 0; j < 6; ++j) blk[6 * i + j] = Ss[(6 * bi + i) * n + 6 * bi + j];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) blk[6 * i + j] = __ldcg(A.S + (size_t)(6 * bi + i) * n + 6 * bi + j);
+    }
     if (!spd6_inverse(blk)) fail = 1;
+#pragma unroll
     for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
   }
+  rs[lane] = 0.0; rs[lane + 32] = 0.0; us[lane] = 0.0; us[lane + 32] = 0.0;
+  cp_async_wait<0>();
   fail = __syncthreads_or(fail);
   const int i0 = lane, i1 = lane + 32;
   const bool h0 = i0 < n, h1 = i1 < n;
+  // preconditioner rows of this lane, in registers
+  double m0[6], m1[6];
+  const int b0 = h0 ? i0 / 6 : 0, b1 = h1 ? i1 / 6 : 0;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    m0[k] = h0 ? minv[36 * b0 + 6 * (i0 - 6 * b0) + k] : 0.0;
+    m1[k] = h1 ? minv[36 * b1 + 6 * (i1 - 6 * b1) + k] : 0.0;
+  }
   // column range of this warp (multiples of 2 so that the inner step is two columns)
-  const int cols = ((n + 7) / 8) * 2;
+  const int cols = ((n + 7) / 8) * 2;               // <= 16
   const int j0 = min(n, wid * cols), j1 = min(n, j0 + cols);
   const double* c0 = Ss + (h0 ? i0 : 0);
   const double* c1 = Ss + (h1 ? i1 : 0);
-  // warp 0 state
-  double x0 = 0.0, x1 = 0.0, p0 = 0.0, p1 = 0.0, s0 = 0.0, s1 = 0.0, u0 = 0.0, u1 = 0.0;
-  double r0 = 0.0, r1 = 0.0;
-  if (wid == 0) { r0 = h0 ? A.b[i0] : 0.0; r1 = h1 ? A.b[i1] : 0.0; }
-  int status = fail ? 1 : 2, it = 0;
+  double x0 = 0.0, x1 = 0.0, p0 = 0.0, p1 = 0.0, s0 = 0.0, s1 = 0.0;
+  double r0 = h0 ? A.b[i0] : 0.0, r1 = h1 ? A.b[i1] : 0.0;
+  int status = fail ? 1 : 2, it = 0, buf = 0;
   double inv_gamma_old = 0.0, pap_old = 0.0, thresh = 0.0;
   if (!fail) {
     for (it = 0;; ++it) {
-      if (wid == 0) {
-        rs[i0] = r0; rs[i1] = r1;
-        __syncwarp();
-        u0 = 0.0; u1 = 0.0;
-        if (h0) {
-          const double* m = minv + 36 * (i0 / 6) + 6 * (i0 % 6);
-          const double* rr6 = rs + 6 * (i0 / 6);
-          u0 = (m[0] * rr6[0] + m[1] * rr6[1]) + (m[2] * rr6[2] + m[3] * rr6[3]) + (m[4] * rr6[4] + m[5] * rr6[5]);
-        }
-        if (h1) {
-          const double* m = minv + 36 * (i1 / 6) + 6 * (i1 % 6);
-          const double* rr6 = rs + 6 * (i1 / 6);
-          u1 = (m[0] * rr6[0] + m[1] * rr6[1]) + (m[2] * rr6[2] + m[3] * rr6[3]) + (m[4] * rr6[4] + m[5] * rr6[5]);
-        }
-        us[i0] = u0; us[i1] = u1;
-      }
-      __syncthreads();
-      if (s_stop) break;
+      // u = M^-1 r through the warp's own shared-memory copy of r
+      rs[i0] = r0; rs[i1] = r1;
+      __syncwarp();
+      const double* ra = rs + 6 * b0;
+      const double* rb = rs + 6 * b1;
+      const double u0 = (m0[0] * ra[0] + m0[1] * ra[1]) + (m0[2] * ra[2] + m0[3] * ra[3]) + (m0[4] * ra[4] + m0[5] * ra[5]);
+      const double u1 = (m1[0] * rb[0] + m1[1] * rb[1]) + (m1[2] * rb[2] + m1[3] * rb[3]) + (m1[4] * rb[4] + m1[5] * rb[5]);
+      us[i0] = u0; us[i1] = u1;
+      __syncwarp();
       {   // partial w = S[:, j0:j1] u[j0:j1] for rows i0, i1
         double wa = 0.0, wb = 0.0, wc = 0.0, wd = 0.0;
-        int j = j0;
-#pragma unroll 4
-        for (; j + 1 < j1; j += 2) {
-          const double ua = us[j], ub = us[j + 1];
-          wa = fma(c0[j * n], ua, wa); wb = fma(c0[(j + 1) * n], ub, wb);
-          wc = fma(c1[j * n], ua, wc); wd = fma(c1[(j + 1) * n], ub, wd);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int j = j0 + 2 * q;
+          if (j + 1 < j1) {
+            const double ua = us[j], ub = us[j + 1];
+            wa = fma(c0[j * n], ua, wa); wb = fma(c0[(j + 1) * n], ub, wb);
+            wc = fma(c1[j * n], ua, wc); wd = fma(c1[(j + 1) * n], ub, wd);
+          } else if (j < j1) {
+            const double ua = us[j];
+            wa = fma(c0[j * n], ua, wa); wc = fma(c1[j * n], ua, wc);
+          }
         }
-        if (j < j1) { wa = fma(c0[j * n], us[j], wa); wc = fma(c1[j * n], us[j], wc); }
-        part[wid * 64 + i0] = h0 ? wa + wb : 0.0;
-        part[wid * 64 + i1] = h1 ? wc + wd : 0.0;
+        double* pw = part + (buf * kPcgSmallWarps + wid) * 64;
+        pw[i0] = h0 ? wa + wb : 0.0;
+        pw[i1] = h1 ? wc + wd : 0.0;
       }
       __syncthreads();
-      if (wid == 0) {
-        const double w0 = (part[i0] + part[64 + i0]) + (part[128 + i0] + part[192 + i0]);
-        const double w1 = (part[i1] + part[64 + i1]) + (part[128 + i1] + part[192 + i1]);
-        const double gamma = warp_sum(r0 * u0 + r1 * u1);
-        const double delta = warp_sum(w0 * u0 + w1 * u1);
-        const double rr = warp_sum(r0 * r0 + r1 * r1);
-        bool stop = false;
-        if (it == 0) {
-          if (!(rr > 0.0)) { status = 0; stop = true; }      // b == 0: x = 0
-          thresh = A.tol * A.tol * rr;
-        }
-        if (!stop && rr <= thresh && it > 0) { status = 0; stop = true; }
-        if (!stop && it == A.max_iter) stop = true;
-        if (!stop) {
-          double beta = 0.0, pap = delta;
-          if (it > 0) {
-            beta = gamma * inv_gamma_old;
-            pap = delta - beta * beta * pap_old;           // = p^T S p in exact arithmetic
-          }
-          if (!(pap > 0.0) || !isfinite(pap) || !(gamma > 0.0)) { status = 1; stop = true; }
-          else {
-            const double alpha = gamma / pap;
-            inv_gamma_old = 1.0 / gamma; pap_old = pap;
-            p0 = u0 + beta * p0; p1 = u1 + beta * p1;
-            s0 = w0 + beta * s0; s1 = w1 + beta * s1;
-            x0 += alpha * p0; x1 += alpha * p1;
-            r0 -= alpha * s0; r1 -= alpha * s1;
-          }
-        }
-        if (stop && lane == 0) s_stop = 1;
-        if (stop) --it;   // the loop header counts this pass again
+      const double* pr = part + buf * kPcgSmallWarps * 64;
+      buf ^= 1;
+      const double w0 = (pr[i0] + pr[64 + i0]) + (pr[128 + i0] + pr[192 + i0]);
+      const double w1 = (pr[i1] + pr[64 + i1]) + (pr[128 + i1] + pr[192 + i1]);
+      const double gamma = warp_sum(r0 * u0 + r1 * u1);
+      const double delta = warp_sum(w0 * u0 + w1 * u1);
+      const double rr = warp_sum(r0 * r0 + r1 * r1);
+      if (it == 0) {
+        if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
+        thresh = A.tol * A.tol * rr;
       }
+      if (rr <= thresh && it > 0) { status = 0; break; }
+      if (it == A.max_iter) break;
+      double beta = 0.0, pap = delta;
+      if (it > 0) {
+        beta = gamma * inv_gamma_old;
+        pap = delta - beta * beta * pap_old;           // = p^T S p in exact arithmetic
+      }
+      if (!(pap > 1e-290) || !(pap < 1e290) || !(gamma > 1e-290) || !(gamma < 1e290)) { status = 1; break; }
+      const double alpha = gamma * fast_rcp(pap);
+      inv_gamma_old = fast_rcp(gamma); pap_old = pap;
+      p0 = u0 + beta * p0; p1 = u1 + beta * p1;
+      s0 = w0 + beta * s0; s1 = w1 + beta * s1;
+      x0 += alpha * p0; x1 += alpha * p1;
+      r0 -= alpha * s0; r1 -= alpha * s1;
     }
   }
   if (wid == 0) {
