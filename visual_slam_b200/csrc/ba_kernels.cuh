@@ -199,7 +199,14 @@ struct __align__(16) LinWork {   // one per CTA of the fused grid
   int col;         // free-camera column or -1
 };
 
+struct TrialArgs {   // what the LM controller needs besides the trial cost (cost-only launch)
+  int n_sp, n;
+  const double* scale_partial; const double* dp; const double* bp; const double* bp_extra;
+  const int* pcg_status; const int* pcg_iters;
+};
+
 struct LinArgs {
+  TrialArgs trial;
   const LinWork* work;              // fused grid: [n_ctas]
   const LinWork* cam_work;          // camera chunks only (cost-only grid)
   int n_pt_ctas, n_pt_warps, n_tickets, cams_in_smem, has_scale;
@@ -257,6 +264,13 @@ __device__ __forceinline__ void load_point(const double* __restrict__ pts4, int 
 }
 __device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// Programmatic dependent launch: every kernel of an LM step is launched with the programmatic-stream-
+// serialization attribute, so its CTAs may become resident while the previous kernel is still draining.
+// pdl_wait() returns once the previous grid has completed and its writes are visible (a no-op for a plain
+// launch) -- nothing another kernel of the step writes may be read before it; pdl_trigger() lets the NEXT
+// kernel be scheduled.  Waiting first keeps the look-ahead at one kernel.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // Branch-free FP64 reciprocal / reciprocal square root for finite normal arguments: hardware seed
 // (MUFU.RCP64H / RSQ64H, ~2^-20) + two Newton steps (error ~1 ulp).  The IEEE division / sqrt of the
@@ -369,6 +383,60 @@ __device__ __forceinline__ void lin_controller(const BAView& V, const LinArgs& A
   }
 }
 
+// Controller after a trial (last CTA of the cost-only launch): cost of the trial state, computeScale,
+// then the Levenberg-Marquardt accept / reject logic of g2o (OptimizationAlgorithmLevenberg::solve)
+// entirely on the device.
+__device__ __forceinline__ void trial_controller(const BAView& V, const LinArgs& A, const ScaleView& SV,
+                                                 double* red /*[2 * kLinWarps]*/) {
+  LMState* st = A.st_rw;
+  const TrialArgs& T = A.trial;
+  if (A.has_scale) {   // cost of the scale edges at the trial state (EdgeSBAScale + DCS)
+    scale_edges_body<kLinThreads>(SV, true, red);
+    __syncthreads();
+  }
+  const double lambda = st->lambda;
+  double v[2] = {0.0, 0.0};
+  for (int i = threadIdx.x; i < V.C; i += kLinThreads) v[0] += __ldcg(A.cam_cost + i);
+  for (int i = threadIdx.x; i < T.n; i += kLinThreads) v[1] += T.dp[i] * (lambda * T.dp[i] + (T.bp[i] + T.bp_extra[i]));
+  for (int i = threadIdx.x; i < T.n_sp; i += kLinThreads) v[1] += T.scale_partial[i];
+  block_reduce<2, kLinThreads>(v, red);
+  if (threadIdx.x != 0) return;
+  double tmp = v[0] + (A.has_scale ? *A.scale_cost : 0.0);
+  const int status = T.n ? *T.pcg_status : 0, its = T.n ? *T.pcg_iters : 0;
+  st->last_cost = tmp; st->last_scale = v[1]; st->last_pcg_status = status; st->last_pcg_iters = its;
+  if (st->manual) return;
+  const bool ok = status != 1;
+  st->pcg_total += (double)its;
+  if (!ok) { tmp = 1.7976931348623157e308; st->breakdowns += 1.0; }
+  const double scale = v[1] + 1e-3;
+  const double rho = (st->cur_cost - tmp) / scale;
+  st->last_rho = rho;
+  st->trials += 1;
+  const bool accepted = rho > 0.0 && isfinite(tmp);
+  if (accepted) {
+    double alpha = 1.0 - pow(2.0 * rho - 1.0, 3.0);
+    alpha = fmin(alpha, 2.0 / 3.0);
+    st->lambda = lambda * fmax(1.0 / 3.0, alpha);
+    st->ni = 2.0;
+    st->cur_cost = tmp;
+    st->cur ^= 1;          // discardTop(): the trial state becomes current
+    st->dirty = 1;
+  } else {
+    st->lambda = lambda * st->ni;   // pop(): current state untouched, the system stays valid
+    st->ni *= 2.0;
+    st->rejected += 1.0;
+  }
+  const bool lam_bad = !accepted && !isfinite(st->lambda);
+  int q = st->q;
+  if (!lam_bad) q += 1;
+  if (!lam_bad && rho < 0.0 && q < 10) { st->q = q; return; }   // next trial of the same outer iteration
+  st->iters += 1;
+  const bool stop = (q == 10) || rho == 0.0 || !isfinite(st->lambda);
+  st->q = 0;
+  if (!accepted) st->dirty = 1;   // g2o rebuilds the system at the start of every outer iteration
+  if (stop || st->iters >= st->max_iterations) st->done = 1;
+}
+
 __device__ __forceinline__ constexpr int hpp_u(int i, int j) { return i * 6 - (i * (i - 1)) / 2 + (j - i); }
 
 template <bool COST_ONLY>
@@ -379,7 +447,9 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
   __shared__ __align__(16) CamRT s_cam;
   __shared__ int s_flag;
   const int4* wsrc = reinterpret_cast<const int4*>((COST_ONLY ? A.cam_work : A.work) + blockIdx.x);
-  const int4 w0 = __ldg(wsrc), w1 = __ldg(wsrc + 1);
+  const int4 w0 = __ldg(wsrc), w1 = __ldg(wsrc + 1);   // (static work list: may be read before the wait)
+  pdl_wait();
+  pdl_trigger();
   if (V.st->done || (!COST_ONLY && !V.st->dirty && !A.force)) return;
   const int sb = COST_ONLY ? (V.st->cur ^ 1) : V.st->cur;   // the cost-only pass evaluates the trial state
   const CamRT* __restrict__ camrt = V.camrt[sb];
@@ -557,7 +627,7 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
           }
         }
       }
-      take_ticket = !COST_ONLY;
+      take_ticket = true;
     }
   } else if (kind == 1) {
     // ------------------------------------------------ point block (never reached when COST_ONLY)
@@ -659,23 +729,23 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
   }
 
   if (!COST_ONLY && A.trace && tid == 0) A.trace[2 * blockIdx.x + 1] = globaltimer_ns();
-  if (!COST_ONLY) {
-    // the last CTA of the grid (camera finalisers + point blocks + scale edges) runs the controller
-    if (!take_ticket) return;     // uniform per CTA
-    __syncthreads();
-    if (tid == 0) {
-      fence_acq_rel_gpu();
-      const unsigned t = atomicAdd(A.lin_ticket, 1u);
-      s_flag = (t == (unsigned)(A.n_tickets - 1));
-      if (s_flag) *A.lin_ticket = 0u;
-    }
-    __syncthreads();
-    if (s_flag) {
-      if (A.trace && tid == 0) A.trace[2 * gridDim.x + 3] = globaltimer_ns();
-      fence_acq_rel_gpu();
-      lin_controller(V, A, red);
-      if (A.trace && tid == 0) A.trace[2 * gridDim.x] = globaltimer_ns();
-    }
+  // the last CTA of the grid (camera finalisers + point blocks + scale edges; camera finalisers only in
+  // the cost-only launch) runs the controller
+  if (!take_ticket) return;     // uniform per CTA
+  __syncthreads();
+  if (tid == 0) {
+    fence_acq_rel_gpu();
+    const unsigned t = atomicAdd(A.lin_ticket, 1u);
+    s_flag = (t == (unsigned)((COST_ONLY ? V.C : A.n_tickets) - 1));
+    if (s_flag) *A.lin_ticket = 0u;
+  }
+  __syncthreads();
+  if (s_flag) {
+    if (!COST_ONLY && A.trace && tid == 0) A.trace[2 * gridDim.x + 3] = globaltimer_ns();
+    fence_acq_rel_gpu();
+    if (COST_ONLY) trial_controller(V, A, SV, red);
+    else lin_controller(V, A, red);
+    if (!COST_ONLY && A.trace && tid == 0) A.trace[2 * gridDim.x] = globaltimer_ns();
   }
 }
 
@@ -683,6 +753,8 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
 // with W W^T = Hinv (W = C^-T, C the Cholesky factor of Hll + lambda I), stored (00 01 02 11 12 22).
 __global__ void ba_point_invert(const LMState* __restrict__ st, int Pf, const double* __restrict__ Hll,
                                 double* __restrict__ Hinv, double* __restrict__ Wf) {
+  pdl_wait();
+  pdl_trigger();
   if (st->done) return;
   const double lambda = st->lambda;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -717,6 +789,8 @@ __global__ void __launch_bounds__(kCamThreads)
 ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict__ Wf,
              const double* __restrict__ bl, double* __restrict__ Gout, double* __restrict__ camp) {
   __shared__ double red[(kCamThreads / 32) * 6];
+  pdl_wait();
+  pdl_trigger();
   if (V.st->done) return;
   const int c = blockIdx.y, chunk = blockIdx.x;
   const int start = V.cm_start[c] + chunk * kCamChunk;
@@ -774,6 +848,8 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
   extern __shared__ __align__(128) double sch_smem[];
   const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int u = blockIdx.x * kSchurWarps + wid;
+  pdl_wait();
+  pdl_trigger();
   if (st->done || u >= n_units) return;
   double* ring = sch_smem + (size_t)wid * kSchurStages * kSchurStageDoubles;
   const int s0 = unit_start[u], len = unit_len[u];
@@ -850,6 +926,7 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
 // S block (a,b) = [a==b](Hpp_a + lambda I) + scale-edge block - sum of its units; mirrored.
 struct BhatArgs {   // bhat = (bp + bp_extra) - sum_j Hpl_j Hinv_j bl_j  (ordered chunk sum of ba_compute_G's partials)
   const double* camp; const double* bp; const double* bp_extra; double* bhat;
+  unsigned* pcg_bar; int* pcg_flags;   // reset here for the solve that follows (no memset nodes in the step)
 };
 __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restrict__ seg_a,
                                   const int* __restrict__ seg_b,
@@ -858,6 +935,12 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
                                   const double* __restrict__ Hpp,
                                   const double* __restrict__ extra,
                                   const int* __restrict__ seg_extra_idx, double* __restrict__ S, BhatArgs Bh) {
+  pdl_wait();
+  pdl_trigger();
+  if (blockIdx.x == 0 && threadIdx.x == 0) {   // PCG bookkeeping of this trial: grid-barrier counter, fail / status / iterations
+    *Bh.pcg_bar = 0u;
+    Bh.pcg_flags[0] = 0; Bh.pcg_flags[1] = 0; Bh.pcg_flags[2] = 0; Bh.pcg_flags[3] = 0;
+  }
   if (V.st->done) return;
   const double lambda = V.st->lambda;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -893,6 +976,8 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
 __global__ void __launch_bounds__(kCamThreads)
 ba_backsub_cam(BAView V, const double* __restrict__ Hpl, const double* __restrict__ dp,
                double* __restrict__ tmp3) {
+  pdl_wait();
+  pdl_trigger();
   const int c = blockIdx.y, chunk = blockIdx.x;
   const int start = V.cm_start[c] + chunk * kCamChunk;
   const int end = min(V.cm_start[c + 1], start + kCamChunk);
@@ -952,6 +1037,8 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
               const double* __restrict__ bl, double* __restrict__ dl_out,
               double* __restrict__ scale_partial, const double* __restrict__ dp, int n_pt_blocks) {
   __shared__ double red[8];
+  pdl_wait();
+  pdl_trigger();
   if (V.st->done) return;
   if ((int)blockIdx.x >= n_pt_blocks) {   // the blocks behind the points update the cameras (SBACam::update)
     update_cams_body(V, dp, ((int)blockIdx.x - n_pt_blocks) * 256 + (int)threadIdx.x);

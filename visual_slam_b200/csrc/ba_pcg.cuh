@@ -150,6 +150,7 @@ __device__ __forceinline__ void gather_sums(const double* part, int G, double* s
 // iteration, i.e. two grid barriers (publish u = M^-1 r; reduce (r,u), (Au,u), (r,r)).
 __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
   extern __shared__ __align__(16) double sm[];
+  pdl_wait();                                   // (no trigger: the cooperative grid keeps the SMs to itself)
   if (A.done != nullptr && *A.done) return;   // uniform over the grid: nobody writes it meanwhile
   const int n = A.n, G = A.G, g = blockIdx.x, tid = threadIdx.x;
   const int row0 = g * A.rows;
@@ -274,6 +275,8 @@ constexpr int kPcgSmallWarps = kPcgSmallThreads / 32;
 
 __global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_kernel(PcgArgs A) {
   extern __shared__ __align__(16) double sm[];
+  pdl_wait();
+  pdl_trigger();
   if (A.done != nullptr && *A.done) return;
   const int n = A.n, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   double* Ss = sm;                                  // [n][n]
