@@ -227,6 +227,32 @@ int vslam_triangulate(const double* proj, const double* extr, const double* x1, 
 int vslam_list_diff(const double* kp1, int n1, const double* kp2, int n2, int mode, uint8_t* keep,
                     int32_t* keep_idx, int32_t* n_keep, void* stream);
 
+/*
+ * Feature extraction: reference src/v2/frame.py:5-14 (`FeatureExtractor.compute_features`,
+ * ORB variant of frame.py:8) = cv2.goodFeaturesToTrack(mean-of-channels grey, max_corners, quality,
+ * min_distance) -> cv2.KeyPoint(x, y, size 20) [angle -1] -> cv2.ORB_create().compute -> KeyPoint_convert.
+ * Bit-exact against OpenCV 4.13 (corner order, key points, descriptors).
+ *   img        dev u8  [batch][H][W][3]  BGR, interleaved (cv2.imread layout)
+ *   max_corners, quality, min_distance   goodFeaturesToTrack arguments (frame.py:11: 3000, 0.01, 7);
+ *                                        min_distance must be an integer value or < 1
+ *   cos_a, sin_a                         float(cos), float(sin) of float(angle) * float(pi/180), the key point
+ *                                        angle ORB rotates its pattern by (KeyPoint default: -1 degree)
+ *   pattern    dev i8  [512][2]          the 256 rBRIEF test pairs (x, y), OpenCV's published table
+ *   workspace  dev, vslam_features_workspace_bytes(batch, H, W, min_distance) bytes, 256-byte aligned
+ *   eig        dev f32 [batch][H][W]     cv2.cornerMinEigenVal(grey, 3, ksize=3)         (output)
+ *   blur       dev u8  [batch][H][W]     the blurred level image ORB samples             (output)
+ *   corners    dev f32 [batch][max_corners][2], n_corners dev i32 [batch]   goodFeaturesToTrack result
+ *   kp         dev f32 [batch][max_corners][2], n_kp dev i32 [batch]        key points ORB keeps (31-px border)
+ *   desc       dev u8  [batch][max_corners][32]                             their descriptors
+ *   status     dev i32 [batch] or NULL   1 if an internal list overflowed (cannot happen for valid input)
+ */
+long long vslam_features_workspace_bytes(int batch, int H, int W, double min_distance);
+int vslam_extract_features(const uint8_t* img, int batch, int H, int W, int max_corners, double quality,
+                           double min_distance, float cos_a, float sin_a, const int8_t* pattern,
+                           void* workspace, long long workspace_bytes, float* eig, uint8_t* blur,
+                           float* corners, int32_t* n_corners, float* kp, uint8_t* desc, int32_t* n_kp,
+                           int32_t* status, void* stream);
+
 /* ------------------------------------------------------------------------- */
 /* 3. Bundle adjustment                                                       */
 /* ------------------------------------------------------------------------- */

@@ -1,0 +1,35 @@
+"""Generates tests/golden/features_icl.npz by RUNNING THE REFERENCE's own FeatureExtractor
+(/root/reference/src/v2/frame.py:5-14) on ICL-NUIM frames, with its extractor set to the ORB variant the
+file itself names (frame.py:8, `self.extractor = cv2.ORB_create()`).  Also stores what cv2 returns for the
+intermediate goodFeaturesToTrack call of frame.py:11.  Run in the build container only (the GPU box has no
+/root/reference); the .npz (images included, so the test needs nothing else) is committed.
+
+Run from the repo root:  python tests/golden/make_features_golden.py
+"""
+import os
+import sys
+
+import cv2
+import numpy as np
+
+sys.path.insert(0, "/root/reference/src/v2")
+import frame as ref_frame  # noqa: E402
+
+out = {"cv2_version": np.array(cv2.__version__)}
+fx = ref_frame.FeatureExtractor()
+fx.extractor = cv2.ORB_create()          # frame.py:8
+for name, path, crop in [("icl1", "/root/reference/data/ICL_NUIM/rgb/1.png", None),
+                         ("icl32_crop", "/root/reference/data/ICL_NUIM/rgb/32.png", (40, 401, 100, 547))]:
+    img = cv2.imread(path)
+    if crop:
+        img = np.ascontiguousarray(img[crop[0]:crop[1], crop[2]:crop[3]])   # odd sizes: 361 x 447
+    kp, des = fx.compute_features(img)
+    corners = cv2.goodFeaturesToTrack(np.mean(img, axis=2).astype(np.uint8), 3000, qualityLevel=0.01, minDistance=7)
+    out[name + "_img"] = img
+    out[name + "_kp"] = kp
+    out[name + "_des"] = des
+    out[name + "_corners"] = corners.reshape(-1, 2)
+    print(name, img.shape, "corners", corners.shape[0], "kp", kp.shape, "des", des.shape)
+path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "features_icl.npz")
+np.savez_compressed(path, **out)
+print("written", path, os.path.getsize(path))

@@ -1,0 +1,194 @@
+"""Feature extraction.  CPU: the oracle against the reference's own FeatureExtractor outputs
+(golden) and against live cv2, stage by stage.  GPU: the CUDA path through the C ABI against the oracle, the
+golden vectors and live cv2 -- bit-exact key points (order included) and descriptors."""
+import os
+
+import cv2
+import numpy as np
+import pytest
+
+from oracle import features as of
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "features_icl.npz")
+NAMES = ["icl1", "icl32_crop"]
+
+
+def _cv2_features(img, max_corners=3000, quality=0.01, min_distance=7):
+    """frame.py:10-14 with cv2.ORB_create() (frame.py:8), straight cv2 calls."""
+    pts = cv2.goodFeaturesToTrack(np.mean(img, axis=2).astype(np.uint8), max_corners, qualityLevel=quality,
+                                  minDistance=min_distance)
+    pts = np.zeros((0, 1, 2), np.float32) if pts is None else pts
+    kps = [cv2.KeyPoint(x=float(f[0][0]), y=float(f[0][1]), size=20) for f in pts]
+    kp, des = cv2.ORB_create().compute(img, kps)
+    des = np.zeros((0, 32), np.uint8) if des is None else des
+    return pts.reshape(-1, 2), np.asarray(cv2.KeyPoint_convert(kp), np.float32).reshape(-1, 2), des
+
+
+def _images():
+    rng = np.random.default_rng(17)
+    g = np.load(GOLD)
+    yield "icl1", g["icl1_img"]
+    yield "noise", rng.integers(0, 256, (120, 200, 3), dtype=np.uint8)                     # > 3000 candidates / cap
+    yield "smooth_odd", cv2.GaussianBlur(rng.integers(0, 256, (211, 333, 3), dtype=np.uint8), (5, 5), 1.2)
+    flat = np.full((100, 140, 3), 77, np.uint8)
+    yield "flat", flat                                                                       # no corners at all
+    sq = flat.copy(); sq[40:60, 50:90] = 200
+    yield "plateaus", sq                                                                     # exact ties
+    chk = (np.indices((160, 224)).sum(0) // 16 % 2 * 255).astype(np.uint8)
+    yield "checker", np.repeat(chk[:, :, None], 3, axis=2)                                   # many equal responses
+
+
+def test_constants_match_cv2():
+    assert np.array_equal(of.GAUSS7, cv2.getGaussianKernel(7, 2, cv2.CV_32F).ravel())
+    from visual_slam_b200.orb_pattern import ORB_PATTERN
+    assert np.array_equal(ORB_PATTERN, of.load_pattern())
+    # the table against cv2 itself: a descriptor of a random patch at angle 0 read back pair by pair
+    rng = np.random.default_rng(0)
+    img = rng.integers(0, 256, (101, 101), dtype=np.uint8)
+    _, des = cv2.ORB_create().compute(img, [cv2.KeyPoint(x=50.0, y=50.0, size=20, angle=0.0)])
+    bl = cv2.sepFilter2D(img, cv2.CV_8U, of.GAUSS7, of.GAUSS7, borderType=cv2.BORDER_REFLECT_101).astype(int)
+    p = ORB_PATTERN.astype(int)
+    bits = bl[50 + p[0::2, 1], 50 + p[0::2, 0]] < bl[50 + p[1::2, 1], 50 + p[1::2, 0]]
+    assert np.array_equal(np.packbits(bits, bitorder="little"), des[0])
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_oracle_reproduces_reference_feature_extractor(name):
+    g = np.load(GOLD)
+    img = g[name + "_img"]
+    corners = of.good_features_to_track(of.gray_mean(img))
+    assert np.array_equal(corners, g[name + "_corners"])
+    kp, des = of.compute_features(img)
+    assert kp.dtype == np.float32 and np.array_equal(kp, g[name + "_kp"])
+    assert np.array_equal(des, g[name + "_des"])
+
+
+def test_oracle_stages_match_live_cv2():
+    for name, img in _images():
+        gm = of.gray_mean(img)
+        assert np.array_equal(gm, np.mean(img, axis=2).astype(np.uint8)), name
+        assert np.array_equal(of.gray_bgr(img), cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)), name
+        eig = of.corner_min_eigen_val(gm)
+        assert np.array_equal(eig, cv2.cornerMinEigenVal(gm, 3, ksize=3)), name
+        gb = of.gray_bgr(img)
+        assert np.array_equal(of.gaussian_blur7(gb), cv2.sepFilter2D(gb, cv2.CV_8U, of.GAUSS7, of.GAUSS7,
+                                                                     borderType=cv2.BORDER_REFLECT_101)), name
+        corners, kp, des = _cv2_features(img)
+        assert np.array_equal(of.good_features_to_track(gm, eig=eig), corners), name
+        okp, odes = of.compute_features(img)
+        assert np.array_equal(okp, kp) and np.array_equal(odes, des), name
+
+
+def test_oracle_other_arguments_and_angles():
+    g = np.load(GOLD)
+    img = g["icl32_crop_img"]
+    gm = of.gray_mean(img)
+    for mc, q, d in [(50, 0.01, 7), (3000, 0.1, 3), (3000, 0.001, 0), (200, 0.02, 12)]:
+        want = cv2.goodFeaturesToTrack(gm, mc, qualityLevel=q, minDistance=d).reshape(-1, 2)
+        assert np.array_equal(of.good_features_to_track(gm, mc, q, float(d)), want), (mc, q, d)
+    pts = of.good_features_to_track(gm)
+    pts = pts[of.border_keep(pts, img.shape[1], img.shape[0])]
+    bl = of.gaussian_blur7(of.gray_bgr(img))
+    for ang in (0.0, -1.0, 33.3, 180.0, 271.0):
+        kps = [cv2.KeyPoint(x=float(p[0]), y=float(p[1]), size=20, angle=ang) for p in pts]
+        _, des = cv2.ORB_create().compute(img, kps)
+        assert np.array_equal(of.orb_descriptors(bl, pts, np.full(len(pts), ang, np.float32)), des), ang
+
+
+# ------------------------------------------------------------------------------------------ GPU
+def _gpu_run(imgs, **kw):
+    import torch
+    from visual_slam_b200.features import extract_features_batch
+    o = extract_features_batch(torch.from_numpy(np.ascontiguousarray(imgs)).cuda(), **kw)
+    torch.cuda.synchronize()
+    assert int(o["status"].abs().sum()) == 0
+    return {k: v.cpu().numpy() for k, v in o.items() if not k.startswith("_")}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", NAMES)
+def test_gpu_matches_reference_golden(name):
+    from visual_slam_b200.features import FeatureExtractor
+    g = np.load(GOLD)
+    kp, des = FeatureExtractor().compute_features(g[name + "_img"])
+    assert kp.dtype == np.float32 and des.dtype == np.uint8
+    assert np.array_equal(kp, g[name + "_kp"])
+    assert np.array_equal(des, g[name + "_des"])
+
+
+@pytest.mark.gpu
+def test_gpu_stages_bit_exact_vs_oracle_and_cv2():
+    for name, img in _images():
+        o = _gpu_run(img[None])
+        gm = of.gray_mean(img)
+        eig = of.corner_min_eigen_val(gm)
+        assert np.array_equal(o["eig"][0].view(np.uint32), eig.view(np.uint32)), name
+        assert np.array_equal(o["blur"][0], of.gaussian_blur7(of.gray_bgr(img))), name
+        corners, kp, des = _cv2_features(img)
+        n = int(o["n_corners"][0])
+        assert n == len(corners) and np.array_equal(o["corners"][0, :n], corners), name
+        m = int(o["n_kp"][0])
+        assert m == len(kp) and np.array_equal(o["kp"][0, :m], kp), name
+        assert np.array_equal(o["desc"][0, :m], des), name
+        okp, odes = of.compute_features(img)
+        assert np.array_equal(o["kp"][0, :m], okp) and np.array_equal(o["desc"][0, :m], odes), name
+
+
+@pytest.mark.gpu
+def test_gpu_batch_equals_single_frames_and_other_arguments():
+    rng = np.random.default_rng(5)
+    imgs = np.stack([cv2.GaussianBlur(rng.integers(0, 256, (240, 320, 3), dtype=np.uint8), (5, 5), s)
+                     for s in (0.8, 1.2, 2.0, 3.0, 1.0)])
+    for kw in [dict(), dict(max_corners=100, quality=0.05, min_distance=3.0), dict(min_distance=0.0, max_corners=5000),
+               dict(angle=33.3)]:
+        o = _gpu_run(imgs, **kw)
+        mc, q, d = kw.get("max_corners", 3000), kw.get("quality", 0.01), kw.get("min_distance", 7.0)
+        for b, img in enumerate(imgs):
+            gm = of.gray_mean(img)
+            want = cv2.goodFeaturesToTrack(gm, mc, qualityLevel=q, minDistance=d).reshape(-1, 2)
+            n = int(o["n_corners"][b])
+            assert n == len(want) and np.array_equal(o["corners"][b, :n], want), (kw, b)
+            pts = want[of.border_keep(want, img.shape[1], img.shape[0])]
+            kps = [cv2.KeyPoint(x=float(p[0]), y=float(p[1]), size=20, angle=kw.get("angle", -1.0)) for p in pts]
+            _, des = cv2.ORB_create().compute(img, kps)
+            m = int(o["n_kp"][b])
+            assert m == len(pts) and np.array_equal(o["kp"][b, :m], pts), (kw, b)
+            assert np.array_equal(o["desc"][b, :m], des), (kw, b)
+
+
+@pytest.mark.gpu
+def test_gpu_full_size_batch_properties():
+    """64 VGA frames: idempotence (same input -> same output), corners sorted by response, pairwise distance >= 7,
+    every key point inside ORB's border, descriptors of the matching pipeline's shape."""
+    rng = np.random.default_rng(9)
+    base = cv2.GaussianBlur(rng.integers(0, 256, (480, 640, 3), dtype=np.uint8), (7, 7), 2.0)
+    imgs = np.stack([np.roll(base, 3 * i, axis=1) for i in range(64)])
+    o1, o2 = _gpu_run(imgs), _gpu_run(imgs)
+    for k in ("n_corners", "n_kp", "eig", "blur"):
+        assert np.array_equal(o1[k], o2[k])
+    for b in (0, 31, 63):
+        n, m = int(o1["n_corners"][b]), int(o1["n_kp"][b])
+        assert np.array_equal(o1["corners"][b, :n], o2["corners"][b, :n])
+        assert np.array_equal(o1["desc"][b, :m], o2["desc"][b, :m])
+        c = o1["corners"][b, :n].astype(np.int64)
+        resp = o1["eig"][b][c[:, 1], c[:, 0]]
+        assert np.all(np.diff(resp) <= 0)
+        d2 = ((c[:, None, :] - c[None, :, :]) ** 2).sum(-1) + np.eye(n, dtype=np.int64) * 10 ** 6
+        assert d2.min() >= 49
+        kp = o1["kp"][b, :m]
+        assert kp[:, 0].min() >= 31 and kp[:, 0].max() < 640 - 31 and kp[:, 1].min() >= 31 and kp[:, 1].max() < 480 - 31
+    corners, kp, des = _cv2_features(imgs[40])
+    m = int(o1["n_kp"][40])
+    assert m == len(kp) and np.array_equal(o1["kp"][40, :m], kp) and np.array_equal(o1["desc"][40, :m], des)
+
+
+@pytest.mark.gpu
+def test_gpu_rejects_bad_arguments():
+    import torch
+    from visual_slam_b200.features import FeatureExtractor, extract_features_batch
+    with pytest.raises(ValueError):
+        FeatureExtractor().compute_features(np.zeros((480, 640), np.uint8))
+    with pytest.raises(ValueError):
+        extract_features_batch(torch.zeros((1, 64, 64, 3), dtype=torch.uint8, device="cuda"), min_distance=7.5)
+    with pytest.raises(ValueError):
+        extract_features_batch(torch.zeros((1, 64, 64, 3), dtype=torch.float32, device="cuda"))

@@ -41,6 +41,10 @@ def _declare(lib):
     lib.vslam_recover_pose.argtypes = [vp, vp, vp, vp, i32, i32, pd, f64, vp, vp, vp, vp, vp, vp]
     lib.vslam_triangulate.argtypes = [vp, vp, vp, vp, vp, i32, i32, f64, vp, vp, vp, vp, vp]
     lib.vslam_list_diff.argtypes = [vp, i32, vp, i32, i32, vp, vp, vp, vp]
+    lib.vslam_features_workspace_bytes.argtypes = [i32, i32, i32, f64]
+    lib.vslam_features_workspace_bytes.restype = C.c_longlong
+    lib.vslam_extract_features.argtypes = [vp, i32, i32, i32, i32, f64, f64, C.c_float, C.c_float, vp, vp,
+                                           C.c_longlong, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     pp = C.POINTER(vp)
     lib.vslam_ba_create.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.vslam_ba_destroy.argtypes = [vp]
