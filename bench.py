@@ -195,6 +195,75 @@ def ba_figures(torch):
     return out
 
 
+def cpu_features(frames_u8, seconds_budget):
+    """The reference's own CPU path for feature extraction (frame.py:10-14 with cv2.ORB_create(), frame.py:8),
+    on the host cores, bounded sample."""
+    import cv2
+    orb = cv2.ORB_create()
+    t0, n = time.perf_counter(), 0
+    while True:
+        img = frames_u8[n % len(frames_u8)]
+        pts = cv2.goodFeaturesToTrack(np.mean(img, axis=2).astype(np.uint8), 3000, qualityLevel=0.01, minDistance=7)
+        kps = [cv2.KeyPoint(x=f[0][0], y=f[0][1], size=20) for f in pts]
+        kp, des = orb.compute(img, kps)
+        cv2.KeyPoint_convert(kp)
+        n += 1
+        el = time.perf_counter() - t0
+        if el > seconds_budget:
+            break
+    return {"frames_per_s": n / el, "frames": n, "seconds": el, "cores": os.cpu_count(),
+            "cv2_threads": cv2.getNumThreads(), "kind": "reference (cv2 calls of frame.py:10-14, ORB variant)"}
+
+
+def features_figures(torch, batch=64, steps=5):
+    """N3: goodFeaturesToTrack + ORB.compute on `batch` synthetic VGA frames per step.  Device-resident
+    frames/s (CUDA events), end to end from pinned host memory (H2D of the frames, D2H of key points +
+    descriptors inside the timed region), algorithmic bytes per frame for the HBM view, and the reference's cv2
+    path on the host cores."""
+    from visual_slam_b200 import synth
+    from visual_slam_b200.features import extract_features_batch
+    H, W = 480, 640
+    host = synth.frames(batch, H, W, seed=3)
+    pin = torch.from_numpy(host).pin_memory()
+    dev = pin.cuda()
+    for _ in range(3):
+        o = extract_features_batch(dev)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        o = extract_features_batch(dev)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    n_kp = o["n_kp"].cpu().numpy()
+    kp_pin = torch.empty(o["kp"].shape, dtype=torch.float32).pin_memory()
+    de_pin = torch.empty(o["desc"].shape, dtype=torch.uint8).pin_memory()
+    nk_pin = torch.empty(o["n_kp"].shape, dtype=torch.int32).pin_memory()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        d = pin.cuda(non_blocking=True)
+        o = extract_features_batch(d)
+        kp_pin.copy_(o["kp"], non_blocking=True)
+        de_pin.copy_(o["desc"], non_blocking=True)
+        nk_pin.copy_(o["n_kp"], non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1) / steps
+    # algorithmic traffic per frame: BGR read 3, two greys written 2 + read 2, response written 4 + read 4,
+    # blur written 1 (bytes per pixel); key points + descriptors 40 B each
+    alg = H * W * 16 + int(n_kp.mean()) * 40
+    cpu = cpu_features(host, 4.0)
+    return {"frames_per_s": batch / (ms * 1e-3), "ms_per_batch": ms, "batch": batch, "height": H, "width": W,
+            "keypoints_per_frame": float(n_kp.mean()),
+            "e2e_frames_per_s": batch / (e2e_ms * 1e-3), "h2d_bytes_per_step": int(pin.numel()),
+            "d2h_bytes_per_step": int(kp_pin.numel() * 4 + de_pin.numel() + nk_pin.numel() * 4),
+            "algorithmic_bytes_per_frame": alg, "algorithmic_gbs": batch * alg / (ms * 1e-3) / 1e9,
+            "gpu_launches_per_step": 7, "data": "synthetic block-texture frames (synth.frames), 3000-corner cap binds",
+            "cpu_reference": cpu}
+
+
 def tracking_figures(torch, dist, world, rank, dev, steps=3):
     """C5: 8 sequences x 1000 frame pairs (matching + RANSAC PnP, 100 hypotheses) sharded by sequence over
     the ranks; poses and inlier counts are gathered with NCCL.  Total work is fixed (strong scaling)."""
@@ -419,6 +488,8 @@ def run_gpu(args):
         cpu = cpu_matching(12.0, 4000)
         cpu.pop("pairs"); cpu.pop("seconds")
         line["cpu_baseline"] = cpu
+        if not args.skip_features:
+            line["features"] = features_figures(torch)
         if not args.skip_ba:
             ba = ba_figures(torch)
             line["ba"] = ba
@@ -447,6 +518,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--skip-ba", action="store_true")
     ap.add_argument("--skip-tracking", action="store_true")
+    ap.add_argument("--skip-features", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

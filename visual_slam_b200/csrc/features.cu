@@ -75,6 +75,7 @@ feat_gray_kernel(const uint8_t* __restrict__ img, long long n_px, int px_per_img
 //   cov = (dx*dx, dx*dy, dy*dy) float; box rows: (l + m) + r in double; box columns: running double sum
 //   eig = (a + c) - sqrt((a - c)^2 + b^2), a = A/2, c = C/2, float, not contracted.
 constexpr int kEigT = 64;
+constexpr int kEigChunk = 8;
 
 __global__ void __launch_bounds__(kEigT)
 feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restrict__ eig, int* __restrict__ counters) {
@@ -89,19 +90,32 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
   const float s1 = __int_as_float(0x39ab5601), s2 = __int_as_float(0x3a2b5601);
   const bool vec_col = cc < (W / 32) * 32;
 
-  auto row_terms = [&](int q, float& rx, float& R) {
-    const uint8_t* gr = g + (size_t)q * W;
-    const float l = (float)__ldg(gr + xm), m = (float)__ldg(gr + cc), r = (float)__ldg(gr + xp);
+  auto terms = [&](unsigned lb, unsigned mb, unsigned rb, float& rx, float& R) {
+    const float l = (float)lb, m = (float)mb, r = (float)rb;
     rx = __fsub_rn(r, l);
     // OpenCV's uint8 -> float32 row filter fuses in its 32-pixel vector body and rounds every product in the
     // scalar tail (oracle/features.py: row_vector_width)
     R = vec_col ? __fmaf_rn(s1, r, __fmaf_rn(s2, m, __fmul_rn(s1, l)))
                 : __fadd_rn(__fadd_rn(__fmul_rn(s1, l), __fmul_rn(s2, m)), __fmul_rn(s1, r));
   };
+  auto row_terms = [&](int q, float& rx, float& R) {
+    const uint8_t* gr = g + (size_t)q * W;
+    terms(__ldg(gr + xm), __ldg(gr + cc), __ldg(gr + xp), rx, R);
+  };
+  // the rows of the NEXT chunk of kEigChunk iterations are fetched while the current chunk is worked on
+  unsigned cur[kEigChunk][3], nxt[kEigChunk][3];
+  auto load_chunk = [&](int r0, unsigned (&buf)[kEigChunk][3]) {
+#pragma unroll
+    for (int j = 0; j < kEigChunk; ++j) {
+      const uint8_t* gr = g + (size_t)reflect101(min(r0 + j + 2, H + 1), H) * W;
+      buf[j][0] = __ldg(gr + xm); buf[j][1] = __ldg(gr + cc); buf[j][2] = __ldg(gr + xp);
+    }
+  };
   float rx0, R0, rx1, R1, rx2, R2;
   row_terms(1, rx0, R0);  // row -1 reflects to row 1
   row_terms(0, rx1, R1);
   rx2 = rx0; R2 = R0;
+  load_chunk(0, cur);
   double rsa[3] = {0, 0, 0}, rsb[3] = {0, 0, 0}, sum[3] = {0, 0, 0};
   float vmax = -INFINITY;
 
@@ -115,9 +129,14 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
     vmax = fmaxf(vmax, e);
   };
 
-  for (int r = 0; r < H; ++r) {
+  for (int r0 = 0; r0 < H; r0 += kEigChunk) {
+   if (r0 + kEigChunk < H) load_chunk(r0 + kEigChunk, nxt);
+#pragma unroll
+   for (int j = 0; j < kEigChunk; ++j) {
+    const int r = r0 + j;
+    if (r >= H) break;
     float rxn, Rn;
-    row_terms(reflect101(r + 2, H), rxn, Rn);  // prefetch the row after next
+    terms(cur[j][0], cur[j][1], cur[j][2], rxn, Rn);  // row r + 2
     const float dx = __fmaf_rn(__fadd_rn(rx0, rx2), s1, __fmul_rn(rx1, s2));
     const float dy = __fsub_rn(R2, R0);
     const int buf = r & 1;
@@ -147,6 +166,9 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
       for (int k = 0; k < 3; ++k) { rsa[k] = rsb[k]; rsb[k] = rsc[k]; }
     }
     rx0 = rx1; R0 = R1; rx1 = rx2; R1 = R2; rx2 = rxn; R2 = Rn;
+   }
+#pragma unroll
+   for (int j = 0; j < kEigChunk; ++j) { cur[j][0] = nxt[j][0]; cur[j][1] = nxt[j][1]; cur[j][2] = nxt[j][2]; }
   }
   if (owner) {  // last row: row H reflects to row H-2, which is rsa after the final shift
     double s0[3];
@@ -159,143 +181,186 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
   if ((tid & 31) == 0) atomicMax(&counters[4 * b + 0], key);
 }
 
-// ---- K3: threshold + strict 3x3 local maxima -> candidate list and status image ------------------
-__global__ void __launch_bounds__(256)
-feat_candidates_kernel(const float* __restrict__ eig, int H, int W, double quality, uint8_t* __restrict__ stat,
-                       int* __restrict__ cand, int* __restrict__ counters) {
+// ---- K3: goodFeaturesToTrack's selection, one thread-block cluster per image ----------------------
+// cv2: threshold the response at float(max * quality), keep strict-or-equal 3x3 local maxima of interior
+// pixels (dilate), walk them in order (value desc, address desc) and keep one iff no kept corner of higher
+// order lies at squared distance < d2.  Equivalent fixed point: a candidate is KEPT once every higher-order
+// candidate within range is DROPPED, and DROPPED once one of them is KEPT; decisions are final, so the rounds
+// may read each other's writes.  A kept neighbour within range is necessarily of higher order (it could not
+// have been kept while this one was undecided otherwise), so only undecided neighbours need a key compare.
+// The status image lives in the SHARED MEMORY OF THE CLUSTER: CTA k owns a band of H/8 rows (one byte per
+// pixel: 0 none/dropped, 1 undecided, 2 kept); windows that cross a band edge read the neighbour CTA's band
+// through distributed shared memory; the termination vote is a DSMEM read of eight flags.
+constexpr int kSupCtas = 8;
+constexpr int kSupThreads = 512;
+
+__global__ void __cluster_dims__(kSupCtas, 1, 1) __launch_bounds__(kSupThreads)
+feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, double quality, int radius, int d2,
+                   int* __restrict__ lists, unsigned long long* acc_key, int acc_cap, int* counters) {
+  cg::cluster_group cluster = cg::this_cluster();
+  extern __shared__ __align__(16) uint8_t band[];  // [Hb][Wp]
+  __shared__ int slot[2];
+  __shared__ int n_list[2];
   const int b = blockIdx.y;
-  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  const int rank = (int)cluster.block_rank();
   const float* e = eig + (size_t)b * H * W;
-  bool is_cand = false;
-  if (pix < H * W) {
-    const int y = pix / W, x = pix - y * W;
-    if (y >= 1 && y < H - 1 && x >= 1 && x < W - 1) {
-      const float thr = (float)((double)key_float(counters[4 * b + 0]) * quality);
-      const float v = e[pix];
-      const float ev = v > thr ? v : 0.0f;  // threshold(THRESH_TOZERO)
-      if (ev != 0.0f) {
-        float mx = ev;                      // dilate 3x3 of the thresholded image
+  const unsigned* ebits = reinterpret_cast<const unsigned*>(e);
+  unsigned long long* acc = acc_key + (size_t)b * acc_cap;
+  const int y_lo = rank * Hb, y_hi = min(H, y_lo + Hb);
+  const float thr = (float)((double)key_float(counters[4 * b + 0]) * quality);
+  // two work lists of this CTA (undecided candidates of its band, as band offsets r * Wp + x), ping-pong
+  int* list[2];
+  list[0] = lists + ((size_t)(b * kSupCtas + rank) * 2) * Hb * Wp;
+  list[1] = list[0] + (size_t)Hb * Wp;
+  if (threadIdx.x < 2) n_list[threadIdx.x] = 0;
+  __syncthreads();
+
+  // candidates of this band: ev = v > thr ? v : 0 (THRESH_TOZERO); candidate iff ev != 0 and ev == dilate3x3(ev')
+  // <=> v > thr, v > 0 and v >= every neighbour (a neighbour <= thr cannot exceed v)
+  for (int i0 = 0; i0 < Hb * Wp; i0 += kSupThreads) {   // Hb * Wp is a multiple of 4; whole warps reach the ballot
+    const int idx = i0 + threadIdx.x;
+    const int r = idx / Wp, x = idx - r * Wp, y = y_lo + r;
+    bool flag = false;
+    if (idx < Hb * Wp && y < y_hi && y >= 1 && y < H - 1 && x >= 1 && x < W - 1) {
+      const float v = e[y * W + x];
+      if (v > thr && v > 0.0f) {
+        float mx = v;
 #pragma unroll
         for (int dy = -1; dy <= 1; ++dy)
 #pragma unroll
-          for (int dx = -1; dx <= 1; ++dx) {
-            const float n = e[pix + dy * W + dx];
-            mx = fmaxf(mx, n > thr ? n : 0.0f);
-          }
-        is_cand = ev == mx && ev > 0.0f;    // (a negative response cannot be a corner)
+          for (int dx = -1; dx <= 1; ++dx) mx = fmaxf(mx, e[(y + dy) * W + x + dx]);
+        flag = mx == v;
       }
     }
-    stat[(size_t)b * H * W + pix] = is_cand ? 1 : 0;
+    if (idx < Hb * Wp) band[idx] = flag ? 1 : 0;
+    const unsigned m = __ballot_sync(0xffffffffu, flag);
+    if (m) {
+      const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(&n_list[0], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (flag) list[0][base + __popc(m & ((1u << lane) - 1))] = idx;
+    }
   }
-  const unsigned m = __ballot_sync(0xffffffffu, is_cand);
-  if (m) {
-    const int lane = threadIdx.x & 31;
-    int base = 0;
-    if (lane == __ffs(m) - 1) base = atomicAdd(&counters[4 * b + 1], __popc(m));
-    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-    if (is_cand) cand[(size_t)b * H * W + base + __popc(m & ((1u << lane) - 1))] = pix;
-  }
-}
-
-// ---- K4: greedy minimum-distance selection as parallel rounds over a cluster ---------------------
-// cv2 walks the candidates in order (value desc, address desc) and keeps one iff no kept candidate of
-// higher order lies at squared distance < d2.  Equivalent fixed point: a candidate is KEPT once every
-// higher-order candidate within range is DROPPED, and DROPPED once one of them is KEPT.  Decisions are
-// final, so rounds may read each other's writes.  status: 0 none, 1 undecided, 2 kept, 3 dropped.
-constexpr int kSupCtas = 8;
-constexpr int kSupThreads = 512;
-constexpr int kRankTile = 1024;
-
-__global__ void __cluster_dims__(kSupCtas, 1, 1) __launch_bounds__(kSupThreads)
-feat_suppress_kernel(const float* __restrict__ eig, uint8_t* stat, const int* __restrict__ cand, int H, int W,
-                     int radius, int d2, unsigned long long* acc_key, int acc_cap, int max_corners,
-                     float2* __restrict__ corners, int* __restrict__ n_corners, int* counters) {
-  cg::cluster_group cluster = cg::this_cluster();
-  __shared__ int slot[2];
-  __shared__ unsigned long long tile[kRankTile];
-  const int b = blockIdx.y;
-  const int rank = (int)cluster.block_rank();
-  const int gtid = rank * kSupThreads + threadIdx.x, gsize = kSupCtas * kSupThreads;
-  const size_t img_off = (size_t)b * H * W;
-  const unsigned* ebits = reinterpret_cast<const unsigned*>(eig) + img_off;
-  uint8_t* st = stat + img_off;
-  const int* cl = cand + img_off;
-  unsigned long long* acc = acc_key + (size_t)b * acc_cap;
-  const int n = counters[4 * b + 1];
+  cluster.sync();
 
   for (int round = 0;; ++round) {
-    int pending = 0;
-    for (int i = gtid; i < n; i += gsize) {
-      const int pix = cl[i];
-      if (__ldcg(st + pix) != 1) continue;
-      const int y = pix / W, x = pix - y * W;
-      const unsigned v = ebits[pix];
-      bool drop = false, wait = false;
-      const int y0 = max(0, y - radius), y1 = min(H - 1, y + radius);
-      const int x0 = max(0, x - radius), x1 = min(W - 1, x + radius);
-      for (int yy = y0; yy <= y1 && !drop; ++yy) {
-        const int dy2 = (yy - y) * (yy - y);
-        for (int xx = x0; xx <= x1; ++xx) {
-          if (dy2 + (xx - x) * (xx - x) >= d2) continue;
-          const int q = yy * W + xx;
-          const int sq = __ldcg(st + q);
-          if (sq == 0 || sq == 3 || q == pix) continue;
-          const unsigned vq = ebits[q];
-          if (vq > v || (vq == v && q > pix)) {
-            if (sq == 2) { drop = true; break; }
-            wait = true;
+    const int src = round & 1, dst = src ^ 1;
+    const int n = n_list[src];
+    const int* in = list[src];
+    int* outl = list[dst];
+    for (int i0 = 0; i0 < n; i0 += kSupThreads) {   // uniform trip count: the ballots below need whole warps
+      const int i = i0 + threadIdx.x;
+      bool wait = false;
+      int idx = 0;
+      if (i < n) {
+        idx = in[i];
+        const int r = idx / Wp, x = idx - r * Wp, y = y_lo + r, pix = y * W + x;
+        const unsigned v = ebits[pix];
+        bool drop = false;
+        const int yy0 = max(0, y - radius), yy1 = min(H - 1, y + radius);
+        const int xa = max(0, x - radius) & ~3, xe = min(Wp, x + radius + 1);
+        for (int yy = yy0; yy <= yy1 && !drop; ++yy) {
+          const int owner = yy / Hb;
+          const uint8_t* row = (owner == rank ? band : cluster.map_shared_rank(band, owner)) + (yy - owner * Hb) * Wp;
+          const int dy2 = (yy - y) * (yy - y);
+          for (int xw = xa; xw < xe && !drop; xw += 4) {
+            const unsigned ww = *reinterpret_cast<const unsigned*>(row + xw);
+            if (!ww) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const unsigned st = (ww >> (8 * j)) & 0xffu;
+              const int xx = xw + j;
+              if (!st || dy2 + (xx - x) * (xx - x) >= d2 || (yy == y && xx == x)) continue;
+              if (st == 2u) { drop = true; break; }
+              const int q = yy * W + xx;
+              const unsigned vq = ebits[q];
+              if (vq > v || (vq == v && q > pix)) wait = true;
+            }
           }
         }
+        if (drop) {
+          band[idx] = 0;
+          wait = false;
+        } else if (!wait) {
+          band[idx] = 2;
+          const int pos = atomicAdd(&counters[4 * b + 2], 1);
+          if (pos < acc_cap) acc[pos] = ((unsigned long long)v << 32) | (unsigned)pix;
+        }
       }
-      if (drop) {
-        __stcg(st + pix, (uint8_t)3);
-      } else if (!wait) {
-        __stcg(st + pix, (uint8_t)2);
-        const int k = atomicAdd(&counters[4 * b + 2], 1);
-        if (k < acc_cap) acc[k] = ((unsigned long long)v << 32) | (unsigned)pix;
-      } else {
-        ++pending;
+      const unsigned m = __ballot_sync(0xffffffffu, wait);
+      if (m) {
+        const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(&n_list[dst], __popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (wait) outl[base + __popc(m & ((1u << lane) - 1))] = idx;
       }
     }
-    const int any = __syncthreads_or(pending > 0);
-    if (threadIdx.x == 0) slot[round & 1] = any;
+    __syncthreads();
+    if (threadIdx.x == 0) { slot[round & 1] = n_list[dst] > 0; n_list[src] = 0; }
     cluster.sync();
     int total = 0;
 #pragma unroll
     for (int k = 0; k < kSupCtas; ++k) total |= *cluster.map_shared_rank(&slot[round & 1], k);
     if (!total) break;
   }
-  cluster.sync();
-  // order of the kept corners = number of kept corners of higher order (counting rank, O(A^2))
-  const int n_acc_raw = __ldcg(&counters[4 * b + 2]);
-  const int A = min(n_acc_raw, acc_cap);
-  if (gtid == 0) {
-    if (n_acc_raw > acc_cap) counters[4 * b + 3] = 1;
-    n_corners[b] = min(A, max_corners);
-  }
-  const int passes = (A + gsize - 1) / gsize;
-  for (int p = 0; p < passes; ++p) {
-    const int i = p * gsize + gtid;
-    const unsigned long long key = i < A ? __ldcg(acc + i) : 0ull;
-    int higher = 0;
-    for (int t0 = 0; t0 < A; t0 += kRankTile) {
-      const int m = min(kRankTile, A - t0);
-      __syncthreads();
-      for (int j = threadIdx.x; j < m; j += kSupThreads) tile[j] = __ldcg(acc + t0 + j);
-      __syncthreads();
-      if (i < A)
-        for (int j = 0; j < m; ++j) higher += tile[j] > key;
-    }
-    if (i < A && higher < max_corners) {
-      const int pix = (int)(key & 0xffffffffu);
-      const int y = pix / W;
-      corners[(size_t)b * max_corners + higher] = make_float2((float)(pix - y * W), (float)y);
-    }
-  }
   cluster.sync();  // no CTA leaves while its shared memory may still be read
 }
 
-// ---- K5: the blur ORB applies to its level image ---------------------------------------------------
+// Order of the kept corners: descending (response, address) = descending 64-bit key.  One CTA per image, bitonic
+// sort in shared memory (the list holds at most ~7.3k corners at VGA); first max_corners are the result.
+constexpr int kSortMax = 8192;
+constexpr int kSortThreads = 1024;
+
+__global__ void __launch_bounds__(kSortThreads)
+feat_order_kernel(const unsigned long long* __restrict__ acc_key, int acc_cap, int W, int max_corners,
+                  float2* __restrict__ corners, int* __restrict__ n_corners, int* __restrict__ counters) {
+  extern __shared__ __align__(16) unsigned long long keys[];
+  const int b = blockIdx.x;
+  const unsigned long long* acc = acc_key + (size_t)b * acc_cap;
+  const int n_raw = counters[4 * b + 2];
+  const int A = min(n_raw, acc_cap);
+  if (threadIdx.x == 0) {
+    if (n_raw > acc_cap) counters[4 * b + 3] = 1;
+    n_corners[b] = min(A, max_corners);
+  }
+  float2* out = corners + (size_t)b * max_corners;
+  if (A > kSortMax) {  // (only reachable without a minimum distance on large frames) counting rank
+    for (int i = threadIdx.x; i < A; i += kSortThreads) {
+      const unsigned long long key = acc[i];
+      int higher = 0;
+      for (int j = 0; j < A; ++j) higher += acc[j] > key;
+      if (higher < max_corners) {
+        const int pix = (int)(key & 0xffffffffu), y = pix / W;
+        out[higher] = make_float2((float)(pix - y * W), (float)y);
+      }
+    }
+    return;
+  }
+  int N = 32;
+  while (N < A) N <<= 1;
+  for (int i = threadIdx.x; i < N; i += kSortThreads) keys[i] = i < A ? acc[i] : 0ull;
+  __syncthreads();
+  for (int k = 2; k <= N; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < N / 2; t += kSortThreads) {
+        const int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1)), hi = lo | j;
+        const unsigned long long a = keys[lo], c = keys[hi];
+        const bool desc = (lo & k) == 0;           // descending blocks first -> whole array descending
+        if ((a < c) == desc) { keys[lo] = c; keys[hi] = a; }
+      }
+      __syncthreads();
+    }
+  }
+  const int n_out = min(A, max_corners);
+  for (int i = threadIdx.x; i < n_out; i += kSortThreads) {
+    const int pix = (int)(keys[i] & 0xffffffffu), y = pix / W;
+    out[i] = make_float2((float)(pix - y * W), (float)y);
+  }
+}
+
+// ---- K4: the blur ORB applies to its level image ---------------------------------------------------
 // float32 separable 7x7, sigma 2 (taps = cv2.getGaussianKernel(7, 2, CV_32F)), REFLECT_101;
 // rows: s = k0*p0, s = fma(k_i, p_i, s); columns: s = k3*c, s = fma(k_{3+j}, up_j + down_j, s);
 // saturate_cast<uchar> = round-half-even.
@@ -341,7 +406,7 @@ feat_blur_kernel(const uint8_t* __restrict__ gray, int H, int W, uint8_t* __rest
   }
 }
 
-// ---- K6a: KeyPointsFilter::runByImageBorder(31), order kept ---------------------------------------
+// ---- K5a: KeyPointsFilter::runByImageBorder(31), order kept ---------------------------------------
 __global__ void __launch_bounds__(1024)
 feat_border_compact_kernel(const float2* __restrict__ corners, const int* __restrict__ n_corners, int max_corners,
                            int H, int W, float2* __restrict__ kp, int* __restrict__ n_kp) {
@@ -377,7 +442,7 @@ feat_border_compact_kernel(const float2* __restrict__ corners, const int* __rest
   if (threadIdx.x == 0) n_kp[b] = base_s;
 }
 
-// ---- K6b: rBRIEF, WTA_K = 2 -----------------------------------------------------------------------
+// ---- K5b: rBRIEF, WTA_K = 2 -----------------------------------------------------------------------
 // One warp per key point, one descriptor byte per lane (16 pattern points = 8 tests).  Offsets:
 // x = px*a - py*b, y = px*b + py*a in float32 without contraction, round-half-even (cvRound).
 constexpr int kOrbWarps = 8;
@@ -411,11 +476,15 @@ feat_orb_kernel(const uint8_t* __restrict__ blur, int H, int W, const float2* __
   }
 }
 
+// the status band of one CTA must fit its shared memory (8 CTAs per image: frames up to ~1.6 Mpixel)
+constexpr size_t kMaxBandBytes = 200 * 1024;
+
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct FeatLayout {
-  size_t gm, gb, stat, cand, acc, counters, total;
-  int acc_cap;
+  size_t gm, gb, lists, acc, counters, total;
+  int acc_cap, Hb, Wp;
+  size_t band_bytes;
 };
 
 static FeatLayout feat_layout(int batch, int H, int W, double min_distance) {
@@ -432,8 +501,10 @@ static FeatLayout feat_layout(int batch, int H, int W, double min_distance) {
   size_t o = 0;
   L.gm = o; o = align256(o + px);
   L.gb = o; o = align256(o + px);
-  L.stat = o; o = align256(o + px);
-  L.cand = o; o = align256(o + px * sizeof(int));
+  L.Hb = (H + kSupCtas - 1) / kSupCtas;
+  L.Wp = (W + 3) & ~3;
+  L.band_bytes = (size_t)L.Hb * L.Wp;
+  L.lists = o; o = align256(o + (size_t)batch * kSupCtas * 2 * L.band_bytes * sizeof(int));
   L.acc = o; o = align256(o + (size_t)batch * L.acc_cap * sizeof(unsigned long long));
   L.counters = o; o = align256(o + (size_t)batch * 4 * sizeof(int));
   L.total = o;
@@ -444,6 +515,7 @@ static FeatLayout feat_layout(int batch, int H, int W, double min_distance) {
 
 extern "C" long long vslam_features_workspace_bytes(int batch, int H, int W, double min_distance) {
   if (batch < 1 || H < 16 || W < 16 || (long long)H * W > (1ll << 30)) return -1;
+  if (vslam::feat_layout(batch, H, W, min_distance).band_bytes > vslam::kMaxBandBytes) return -1;
   return (long long)vslam::feat_layout(batch, H, W, min_distance).total;
 }
 
@@ -461,13 +533,11 @@ extern "C" int vslam_extract_features(const uint8_t* img, int batch, int H, int 
   // plain distance test exactly when d is an integer (or < 1: no test at all)
   if (min_distance >= 1.0 && min_distance != (double)(int)min_distance) return VSLAM_ERR_BAD_ARG;
   const FeatLayout L = feat_layout(batch, H, W, min_distance);
-  if (workspace_bytes < (long long)L.total) return VSLAM_ERR_BAD_ARG;
+  if (workspace_bytes < (long long)L.total || L.band_bytes > kMaxBandBytes) return VSLAM_ERR_BAD_ARG;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   uint8_t* gm = ws + L.gm;
   uint8_t* gb = ws + L.gb;
-  uint8_t* stat = ws + L.stat;
-  int* cand = reinterpret_cast<int*>(ws + L.cand);
   unsigned long long* acc = reinterpret_cast<unsigned long long*>(ws + L.acc);
   int* counters = reinterpret_cast<int*>(ws + L.counters);
   const long long n_px = (long long)batch * H * W;
@@ -477,15 +547,27 @@ extern "C" int vslam_extract_features(const uint8_t* img, int batch, int H, int 
   feat_gray_kernel<<<(unsigned)((gthreads + 255) / 256), 256, 0, st>>>(img, n_px, px, gm, gb, counters, batch);
   feat_eig_kernel<<<dim3((W + kEigT - 3) / (kEigT - 2), batch), kEigT, 0, st>>>(gm, H, W, eig, counters);
   feat_blur_kernel<<<dim3((W + kBlurW - 1) / kBlurW, (H + kBlurH - 1) / kBlurH, batch), 256, 0, st>>>(gb, H, W, blur);
-  feat_candidates_kernel<<<dim3((px + 255) / 256, batch), 256, 0, st>>>(eig, H, W, quality, stat, cand, counters);
   int radius = 0, d2 = 0;
   if (min_distance >= 1.0) {
     d2 = (int)(min_distance * min_distance);
     while ((radius + 1) * (radius + 1) < d2) ++radius;
   }
-  feat_suppress_kernel<<<dim3(kSupCtas, batch), kSupThreads, 0, st>>>(
-      eig, stat, cand, H, W, radius, d2, acc, L.acc_cap, max_corners, reinterpret_cast<float2*>(corners),
-      n_corners, counters);
+  static size_t band_attr = 48 * 1024;
+  if (L.band_bytes > band_attr) {
+    VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)kMaxBandBytes));
+    band_attr = kMaxBandBytes;
+  }
+  feat_select_kernel<<<dim3(kSupCtas, batch), kSupThreads, L.band_bytes, st>>>(
+      eig, H, W, L.Hb, L.Wp, quality, radius, d2, reinterpret_cast<int*>(ws + L.lists), acc, L.acc_cap, counters);
+  static bool sort_attr = false;
+  if (!sort_attr) {
+    VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)(kSortMax * sizeof(unsigned long long))));
+    sort_attr = true;
+  }
+  feat_order_kernel<<<batch, kSortThreads, kSortMax * sizeof(unsigned long long), st>>>(
+      acc, L.acc_cap, W, max_corners, reinterpret_cast<float2*>(corners), n_corners, counters);
   feat_border_compact_kernel<<<batch, 1024, 0, st>>>(reinterpret_cast<const float2*>(corners), n_corners,
                                                      max_corners, H, W, reinterpret_cast<float2*>(kp), n_kp);
   feat_orb_kernel<<<dim3((max_corners + kOrbWarps * 4 - 1) / (kOrbWarps * 4), batch), kOrbWarps * 32, 0, st>>>(

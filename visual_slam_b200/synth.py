@@ -111,3 +111,18 @@ def two_view_pair(seed, n=400, outlier_frac=0.2, pix_sigma=0.5, K=ICL_K, width=6
     n_out = int((~inl).sum())
     p2[~inl] = np.stack([rng.uniform(0, width, n_out), rng.uniform(0, height, n_out)], axis=1)
     return p1.astype(np.float32), p2.astype(np.float32), R, t, inl
+
+
+def frames(n, H=480, W=640, seed=0, block=8):
+    """Synthetic BGR frames for the feature-extraction figures: random 8x8-pixel colour blocks (corners at the
+    block junctions, ~4800 candidates so that goodFeaturesToTrack's 3000 cap of frame.py:11 binds) plus +-3
+    grey levels of pixel noise.  uint8 (n, H, W, 3)."""
+    rng = np.random.default_rng(seed)
+    hb, wb = (H + block - 1) // block, (W + block - 1) // block
+    out = np.empty((n, H, W, 3), np.uint8)
+    for i in range(n):
+        coarse = rng.integers(20, 236, (hb, wb, 3), dtype=np.int16)
+        img = np.repeat(np.repeat(coarse, block, axis=0), block, axis=1)[:H, :W]
+        img = img + rng.integers(-3, 4, (H, W, 3), dtype=np.int16)
+        out[i] = np.clip(img, 0, 255).astype(np.uint8)
+    return out
