@@ -194,7 +194,7 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
 constexpr int kSupCtas = 8;
 constexpr int kSupThreads = 512;
 
-__global__ void __cluster_dims__(kSupCtas, 1, 1) __launch_bounds__(kSupThreads)
+__global__ void __cluster_dims__(kSupCtas, 1, 1) __launch_bounds__(kSupThreads, 4)
 feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, double quality, int radius, int d2,
                    int* __restrict__ lists, unsigned long long* acc_key, int acc_cap, int* counters) {
   cg::cluster_group cluster = cg::this_cluster();
@@ -216,32 +216,44 @@ feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, 
   __syncthreads();
 
   // candidates of this band: ev = v > thr ? v : 0 (THRESH_TOZERO); candidate iff ev != 0 and ev == dilate3x3(ev')
-  // <=> v > thr, v > 0 and v >= every neighbour (a neighbour <= thr cannot exceed v)
-  for (int i0 = 0; i0 < Hb * Wp; i0 += kSupThreads) {   // Hb * Wp is a multiple of 4; whole warps reach the ballot
-    const int idx = i0 + threadIdx.x;
-    const int r = idx / Wp, x = idx - r * Wp, y = y_lo + r;
-    bool flag = false;
-    if (idx < Hb * Wp && y < y_hi && y >= 1 && y < H - 1 && x >= 1 && x < W - 1) {
-      const float v = e[y * W + x];
-      if (v > thr && v > 0.0f) {
-        float mx = v;
+  // <=> v > thr, v > 0 and v >= every neighbour (a neighbour <= thr cannot exceed v).  Four pixels per thread.
+  unsigned* bandw = reinterpret_cast<unsigned*>(band);
+  const bool vec = (W & 3) == 0;
+  const int Wq = Wp / 4;
+  for (int r = threadIdx.x >> 5; r < Hb; r += kSupThreads / 32)
+   for (int xq = threadIdx.x & 31; xq < Wq; xq += 32) {
+    const int x = xq * 4, y = y_lo + r;
+    unsigned word = 0;
+    if (y < y_hi && y >= 1 && y < H - 1 && x < W) {
+      float v4[4];
+      if (vec) {
+        const float4 t = *reinterpret_cast<const float4*>(e + (size_t)y * W + x);
+        v4[0] = t.x; v4[1] = t.y; v4[2] = t.z; v4[3] = t.w;
+      } else {
 #pragma unroll
-        for (int dy = -1; dy <= 1; ++dy)
+        for (int k = 0; k < 4; ++k) v4[k] = x + k < W ? e[(size_t)y * W + x + k] : 0.0f;
+      }
 #pragma unroll
-          for (int dx = -1; dx <= 1; ++dx) mx = fmaxf(mx, e[(y + dy) * W + x + dx]);
-        flag = mx == v;
+      for (int k = 0; k < 4; ++k) {
+        const int xx = x + k;
+        const float v = v4[k];
+        if (v > thr && v > 0.0f && xx >= 1 && xx < W - 1) {
+          float mx = v;
+#pragma unroll
+          for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) mx = fmaxf(mx, e[(size_t)(y + dy) * W + xx + dx]);
+          if (mx == v) word |= 1u << (8 * k);
+        }
       }
     }
-    if (idx < Hb * Wp) band[idx] = flag ? 1 : 0;
-    const unsigned m = __ballot_sync(0xffffffffu, flag);
-    if (m) {
-      const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
-      int base = 0;
-      if (lane == leader) base = atomicAdd(&n_list[0], __popc(m));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (flag) list[0][base + __popc(m & ((1u << lane) - 1))] = idx;
+    bandw[r * Wq + xq] = word;
+    if (word) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if ((word >> (8 * k)) & 1u) list[0][atomicAdd(&n_list[0], 1)] = (r << 16) | (x + k);
     }
-  }
+   }
   cluster.sync();
 
   for (int round = 0;; ++round) {
@@ -255,35 +267,43 @@ feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, 
       int idx = 0;
       if (i < n) {
         idx = in[i];
-        const int r = idx / Wp, x = idx - r * Wp, y = y_lo + r, pix = y * W + x;
+        const int r = idx >> 16, x = idx & 0xffff, y = y_lo + r, pix = y * W + x;
         const unsigned v = ebits[pix];
         bool drop = false;
         const int yy0 = max(0, y - radius), yy1 = min(H - 1, y + radius);
-        const int xa = max(0, x - radius) & ~3, xe = min(Wp, x + radius + 1);
-        for (int yy = yy0; yy <= yy1 && !drop; ++yy) {
-          const int owner = yy / Hb;
-          const uint8_t* row = (owner == rank ? band : cluster.map_shared_rank(band, owner)) + (yy - owner * Hb) * Wp;
+        const int xa = max(0, x - radius) & ~15, xe = min(Wp, x + radius + 1);
+        int owner = rank, rr = r - (y - yy0);   // band and row inside it of the first window row, no division
+        while (rr < 0) { --owner; rr += Hb; }
+        for (int yy = yy0; yy <= yy1 && !drop; ++yy, ++rr) {
+          if (rr == Hb) { ++owner; rr = 0; }
+          const uint8_t* row = (owner == rank ? band : cluster.map_shared_rank(band, owner)) + rr * Wp;
           const int dy2 = (yy - y) * (yy - y);
-          for (int xw = xa; xw < xe && !drop; xw += 4) {
-            const unsigned ww = *reinterpret_cast<const unsigned*>(row + xw);
-            if (!ww) continue;
+          for (int xw = xa; xw < xe && !drop; xw += 16) {
+            const uint4 w16 = *reinterpret_cast<const uint4*>(row + xw);
+            if (!(w16.x | w16.y | w16.z | w16.w)) continue;
+            const unsigned wv[4] = {w16.x, w16.y, w16.z, w16.w};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const unsigned st = (ww >> (8 * j)) & 0xffu;
-              const int xx = xw + j;
-              if (!st || dy2 + (xx - x) * (xx - x) >= d2 || (yy == y && xx == x)) continue;
-              if (st == 2u) { drop = true; break; }
-              const int q = yy * W + xx;
-              const unsigned vq = ebits[q];
-              if (vq > v || (vq == v && q > pix)) wait = true;
+            for (int jw = 0; jw < 4 && !drop; ++jw) {
+              const unsigned ww = wv[jw];
+              if (!ww) continue;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const unsigned st = (ww >> (8 * j)) & 0xffu;
+                const int xx = xw + 4 * jw + j;
+                if (!st || dy2 + (xx - x) * (xx - x) >= d2 || (yy == y && xx == x)) continue;
+                if (st == 2u) { drop = true; break; }
+                const int q = yy * W + xx;
+                const unsigned vq = ebits[q];
+                if (vq > v || (vq == v && q > pix)) wait = true;
+              }
             }
           }
         }
         if (drop) {
-          band[idx] = 0;
+          band[r * Wp + x] = 0;
           wait = false;
         } else if (!wait) {
-          band[idx] = 2;
+          band[r * Wp + x] = 2;
           const int pos = atomicAdd(&counters[4 * b + 2], 1);
           if (pos < acc_cap) acc[pos] = ((unsigned long long)v << 32) | (unsigned)pix;
         }
@@ -368,41 +388,62 @@ constexpr int kBlurW = 64, kBlurH = 32;
 
 __global__ void __launch_bounds__(256)
 feat_blur_kernel(const uint8_t* __restrict__ gray, int H, int W, uint8_t* __restrict__ blur) {
-  __shared__ float in[kBlurH + 6][kBlurW + 6 + 2];
-  __shared__ float hz[kBlurH + 6][kBlurW];
+  __shared__ __align__(16) float in[kBlurH + 6][kBlurW + 8];
+  __shared__ __align__(16) float hz[kBlurH + 6][kBlurW];
   const float k0 = __int_as_float(0x3d8fafb1), k1 = __int_as_float(0x3e06387e), k2 = __int_as_float(0x3e434a39),
               k3 = __int_as_float(0x3e5d4ae0);
   const float kk[7] = {k0, k1, k2, k3, k2, k1, k0};
   const int b = blockIdx.z, x0 = blockIdx.x * kBlurW, y0 = blockIdx.y * kBlurH;
   const uint8_t* g = gray + (size_t)b * H * W;
-  for (int i = threadIdx.x; i < (kBlurH + 6) * (kBlurW + 6); i += 256) {
-    const int r = i / (kBlurW + 6), c = i - r * (kBlurW + 6);
-    const int y = reflect101(min(y0 + r - 3, H + 2), H), x = reflect101(min(x0 + c - 3, W + 2), W);
-    in[r][c] = (float)__ldg(g + (size_t)y * W + x);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < (kBlurH + 6) * kBlurW; i += 256) {
-    const int r = i / kBlurW, c = i - r * kBlurW;
-    float s = __fmul_rn(kk[0], in[r][c]);
-    if (x0 + c < (W / 32) * 32) {  // vector body of OpenCV's row filter: fused; scalar tail: products rounded
-#pragma unroll
-      for (int t = 1; t < 7; ++t) s = __fmaf_rn(kk[t], in[r][c + t], s);
-    } else {
-#pragma unroll
-      for (int t = 1; t < 7; ++t) s = __fadd_rn(s, __fmul_rn(kk[t], in[r][c + t]));
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  {  // tile + 3-pixel apron, uint8 -> float
+    const int xa = reflect101(min(x0 + tx - 3, W + 2), W), xb = reflect101(min(x0 + tx + 61, W + 2), W);
+    for (int r = ty; r < kBlurH + 6; r += 4) {
+      const uint8_t* gr = g + (size_t)reflect101(min(y0 + r - 3, H + 2), H) * W;
+      in[r][tx] = (float)__ldg(gr + xa);
+      if (tx < 6) in[r][64 + tx] = (float)__ldg(gr + xb);
     }
-    hz[r][c] = s;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < kBlurH * kBlurW; i += 256) {
-    const int r = i / kBlurW, c = i - r * kBlurW;
-    const int y = y0 + r, x = x0 + c;
-    if (y >= H || x >= W) continue;
-    float s = __fmul_rn(kk[3], hz[r + 3][c]);
+  {  // rows: four adjacent outputs per thread from twelve inputs (three 128-bit shared loads)
+    const int q = threadIdx.x & 15;
+    const bool fused = x0 + 4 * q < (W / 32) * 32;  // vector body of OpenCV's row filter; its scalar tail rounds products
+    for (int r = threadIdx.x >> 4; r < kBlurH + 6; r += 16) {
+      const float4 a = *reinterpret_cast<const float4*>(&in[r][4 * q]);
+      const float4 c = *reinterpret_cast<const float4*>(&in[r][4 * q + 4]);
+      const float4 d = *reinterpret_cast<const float4*>(&in[r][4 * q + 8]);
+      const float v[12] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w, d.x, d.y, d.z, d.w};
+      float o[4];
 #pragma unroll
-    for (int j = 1; j <= 3; ++j) s = __fmaf_rn(kk[3 + j], __fadd_rn(hz[r + 3 + j][c], hz[r + 3 - j][c]), s);
-    const int v = __float2int_rn(s);
-    blur[(size_t)b * H * W + (size_t)y * W + x] = (uint8_t)min(255, max(0, v));
+      for (int e = 0; e < 4; ++e) {
+        float s = __fmul_rn(kk[0], v[e]);
+        if (fused) {
+#pragma unroll
+          for (int t = 1; t < 7; ++t) s = __fmaf_rn(kk[t], v[e + t], s);
+        } else {
+#pragma unroll
+          for (int t = 1; t < 7; ++t) s = __fadd_rn(s, __fmul_rn(kk[t], v[e + t]));
+        }
+        o[e] = s;
+      }
+      *reinterpret_cast<float4*>(&hz[r][4 * q]) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+  }
+  __syncthreads();
+  {  // columns: eight vertically adjacent outputs per thread from fourteen inputs
+    float v[14];
+#pragma unroll
+    for (int j = 0; j < 14; ++j) v[j] = hz[ty * 8 + j][tx];
+    const int x = x0 + tx;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int y = y0 + ty * 8 + e;
+      float s = __fmul_rn(kk[3], v[e + 3]);
+#pragma unroll
+      for (int j = 1; j <= 3; ++j) s = __fmaf_rn(kk[3 + j], __fadd_rn(v[e + 3 + j], v[e + 3 - j]), s);
+      const int o = __float2int_rn(s);
+      if (y < H && x < W) blur[(size_t)b * H * W + (size_t)y * W + x] = (uint8_t)min(255, max(0, o));
+    }
   }
 }
 
@@ -502,7 +543,7 @@ static FeatLayout feat_layout(int batch, int H, int W, double min_distance) {
   L.gm = o; o = align256(o + px);
   L.gb = o; o = align256(o + px);
   L.Hb = (H + kSupCtas - 1) / kSupCtas;
-  L.Wp = (W + 3) & ~3;
+  L.Wp = (W + 15) & ~15;
   L.band_bytes = (size_t)L.Hb * L.Wp;
   L.lists = o; o = align256(o + (size_t)batch * kSupCtas * 2 * L.band_bytes * sizeof(int));
   L.acc = o; o = align256(o + (size_t)batch * L.acc_cap * sizeof(unsigned long long));
@@ -525,7 +566,7 @@ extern "C" int vslam_extract_features(const uint8_t* img, int batch, int H, int 
                                       float* corners, int32_t* n_corners, float* kp, uint8_t* desc,
                                       int32_t* n_kp, int32_t* status, void* stream) {
   using namespace vslam;
-  if (batch < 1 || H < 16 || W < 16 || max_corners < 1 || (long long)H * W > (1ll << 30)) return VSLAM_ERR_BAD_ARG;
+  if (batch < 1 || H < 16 || W < 16 || W > 32768 || max_corners < 1 || (long long)H * W > (1ll << 30)) return VSLAM_ERR_BAD_ARG;
   if (!img || !pattern || !workspace || !eig || !blur || !corners || !n_corners || !kp || !desc || !n_kp)
     return VSLAM_ERR_BAD_ARG;
   if (!(quality > 0.0) || min_distance < 0.0) return VSLAM_ERR_BAD_ARG;
