@@ -30,6 +30,20 @@ for name, path, crop in [("icl1", "/root/reference/data/ICL_NUIM/rgb/1.png", Non
     out[name + "_des"] = des
     out[name + "_corners"] = corners.reshape(-1, 2)
     print(name, img.shape, "corners", corners.shape[0], "kp", kp.shape, "des", des.shape)
+# C1 front end on the frame pair 1 -> 32: the reference's FeatureExtractor (ORB) and its FeatureMatcher with the
+# Hamming norm the ORB variant needs (frame.py:18 -> cv2.BFMatcher(cv2.NORM_HAMMING)), both classes unmodified
+img32 = cv2.imread("/root/reference/data/ICL_NUIM/rgb/32.png")
+kp1, des1 = out["icl1_kp"], out["icl1_des"]
+kp32, des32 = fx.compute_features(img32)
+fm = ref_frame.FeatureMatcher()
+fm.matcher = cv2.BFMatcher(cv2.NORM_HAMMING)
+matches, p1, f1, p2, f2 = fm.match_features(kp1, des1, kp32, des32)
+out["icl32_img"], out["icl32_kp"], out["icl32_des"] = img32, kp32, des32
+out["pair_query"] = np.array([m[0].queryIdx for m in matches], np.int32)
+out["pair_train"] = np.array([m[0].trainIdx for m in matches], np.int32)
+out["pair_dist"] = np.array([m[0].distance for m in matches], np.float32)
+out["pair_pts1"], out["pair_pts2"], out["pair_ft1"], out["pair_ft2"] = p1, p2, f1, f2
+print("pair 1->32: kp", kp1.shape[0], kp32.shape[0], "ratio matches", len(matches))
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "features_icl.npz")
 np.savez_compressed(path, **out)
 print("written", path, os.path.getsize(path))

@@ -192,3 +192,34 @@ def test_gpu_rejects_bad_arguments():
         extract_features_batch(torch.zeros((1, 64, 64, 3), dtype=torch.uint8, device="cuda"), min_distance=7.5)
     with pytest.raises(ValueError):
         extract_features_batch(torch.zeros((1, 64, 64, 3), dtype=torch.float32, device="cuda"))
+
+
+def test_oracle_front_end_pair_matches_reference():
+    """C1 front end on ICL-NUIM frames 1 -> 32: oracle features + oracle matcher == the reference's own classes."""
+    from oracle import matching as om
+    g = np.load(GOLD)
+    kp1, des1 = of.compute_features(g["icl1_img"])
+    kp2, des2 = of.compute_features(g["icl32_img"])
+    assert np.array_equal(kp2, g["icl32_kp"]) and np.array_equal(des2, g["icl32_des"])
+    idx, dist = om.knn2_numpy(des1, des2)
+    kq, kt = om.filter_numpy(idx, dist, 0.8, None)
+    assert np.array_equal(kq, g["pair_query"]) and np.array_equal(kt, g["pair_train"])
+
+
+@pytest.mark.gpu
+def test_gpu_front_end_pair_matches_reference():
+    """The drop-in chain FeatureExtractor -> FeatureMatcher on the device against the reference's own chain
+    (tests/golden/make_features_golden.py): same key points, descriptors, matches and gathered arrays."""
+    from visual_slam_b200 import FeatureMatcher
+    from visual_slam_b200.features import FeatureExtractor
+    g = np.load(GOLD)
+    fx, fm = FeatureExtractor(), FeatureMatcher()
+    kp1, des1 = fx.compute_features(g["icl1_img"])
+    kp2, des2 = fx.compute_features(g["icl32_img"])
+    assert np.array_equal(kp2, g["icl32_kp"]) and np.array_equal(des2, g["icl32_des"])
+    matches, p1, f1, p2, f2 = fm.match_features(kp1, des1, kp2, des2)
+    assert np.array_equal([m[0].queryIdx for m in matches], g["pair_query"])
+    assert np.array_equal([m[0].trainIdx for m in matches], g["pair_train"])
+    assert np.array_equal(np.array([m[0].distance for m in matches], np.float32), g["pair_dist"])
+    assert np.array_equal(p1, g["pair_pts1"]) and np.array_equal(p2, g["pair_pts2"])
+    assert np.array_equal(f1, g["pair_ft1"]) and np.array_equal(f2, g["pair_ft2"])
