@@ -223,3 +223,23 @@ def test_gpu_front_end_pair_matches_reference():
     assert np.array_equal(np.array([m[0].distance for m in matches], np.float32), g["pair_dist"])
     assert np.array_equal(p1, g["pair_pts1"]) and np.array_equal(p2, g["pair_pts2"])
     assert np.array_equal(f1, g["pair_ft1"]) and np.array_equal(f2, g["pair_ft2"])
+
+
+@pytest.mark.gpu
+def test_gpu_host_extractor_equals_direct_call():
+    """HostFeatureExtractor (pinned staging, chunks on two streams, reused buffers) == one direct batch call."""
+    import torch
+    from visual_slam_b200 import synth
+    from visual_slam_b200.features import HostFeatureExtractor
+    frames = synth.frames(7, 120, 160, seed=21)
+    want = _gpu_run(frames)
+    hx = HostFeatureExtractor(7, 120, 160, chunks=3)
+    hx.load(frames)
+    for _ in range(2):                      # second run reuses every buffer
+        kp, desc, n_kp = hx.run()
+        torch.cuda.synchronize()
+        assert np.array_equal(n_kp.numpy(), want["n_kp"])
+        for b in range(7):
+            n = int(n_kp[b])
+            assert np.array_equal(kp[b, :n].numpy(), want["kp"][b, :n])
+            assert np.array_equal(desc[b, :n].numpy(), want["desc"][b, :n])

@@ -237,7 +237,10 @@ feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, 
       for (int k = 0; k < 4; ++k) {
         const int xx = x + k;
         const float v = v4[k];
-        if (v > thr && v > 0.0f && xx >= 1 && xx < W - 1) {
+        bool maybe = v > thr && v > 0.0f && xx >= 1 && xx < W - 1;
+        if (k > 0) maybe = maybe && v4[k - 1] <= v;       // horizontal neighbours already in registers
+        if (k < 3) maybe = maybe && v4[k + 1] <= v;
+        if (maybe) {
           float mx = v;
 #pragma unroll
           for (int dy = -1; dy <= 1; ++dy)
@@ -283,19 +286,20 @@ feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, 
             if (!(w16.x | w16.y | w16.z | w16.w)) continue;
             const unsigned wv[4] = {w16.x, w16.y, w16.z, w16.w};
 #pragma unroll
-            for (int jw = 0; jw < 4 && !drop; ++jw) {
-              const unsigned ww = wv[jw];
-              if (!ww) continue;
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const unsigned st = (ww >> (8 * j)) & 0xffu;
+            for (int jw = 0; jw < 4; ++jw) {
+              unsigned m = wv[jw] & 0x03030303u;   // visit only the non-zero status bytes
+              while (m) {
+                const int bit = __ffs(m) - 1, j = bit >> 3;
+                const unsigned st = (m >> (8 * j)) & 3u;
+                m &= ~(0xffu << (8 * j));
                 const int xx = xw + 4 * jw + j;
-                if (!st || dy2 + (xx - x) * (xx - x) >= d2 || (yy == y && xx == x)) continue;
+                if (dy2 + (xx - x) * (xx - x) >= d2 || (yy == y && xx == x)) continue;
                 if (st == 2u) { drop = true; break; }
                 const int q = yy * W + xx;
                 const unsigned vq = ebits[q];
                 if (vq > v || (vq == v && q > pix)) wait = true;
               }
+              if (drop) break;
             }
           }
         }

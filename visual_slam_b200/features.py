@@ -33,10 +33,34 @@ def _angle_terms(angle_deg):
     return float(np.float32(math.cos(float(ang)))), float(np.float32(math.sin(float(ang))))
 
 
-def extract_features_batch(imgs, max_corners=3000, quality=0.01, min_distance=7.0, angle=-1.0):
+class FeatureBuffers:
+    """Scratch + result buffers of one extract_features_batch call shape, reusable across calls."""
+
+    def __init__(self, batch, H, W, max_corners=3000, min_distance=7.0, device="cuda"):
+        lib = _cabi.lib()
+        self.shape = (batch, H, W, max_corners, float(min_distance))
+        self.ws_bytes = lib.vslam_features_workspace_bytes(batch, H, W, float(min_distance))
+        if self.ws_bytes < 0:
+            raise ValueError("unsupported frame size %dx%d (16 <= side, at most ~1.6 Mpixel)" % (W, H))
+        dev = torch.device(device)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=dev)
+        self.out = {
+            "eig": torch.empty((batch, H, W), dtype=torch.float32, device=dev),
+            "blur": torch.empty((batch, H, W), dtype=torch.uint8, device=dev),
+            "corners": torch.empty((batch, max_corners, 2), dtype=torch.float32, device=dev),
+            "n_corners": torch.empty(batch, dtype=torch.int32, device=dev),
+            "kp": torch.empty((batch, max_corners, 2), dtype=torch.float32, device=dev),
+            "desc": torch.empty((batch, max_corners, 32), dtype=torch.uint8, device=dev),
+            "n_kp": torch.empty(batch, dtype=torch.int32, device=dev),
+            "status": torch.empty(batch, dtype=torch.int32, device=dev),
+        }
+
+
+def extract_features_batch(imgs, max_corners=3000, quality=0.01, min_distance=7.0, angle=-1.0, buffers=None):
     """imgs: uint8 CUDA tensor (B, H, W, 3), BGR.  Returns a dict of CUDA tensors:
     kp (B, max_corners, 2) f32 + n_kp (B,) i32 + desc (B, max_corners, 32) u8 (rows >= n_kp are undefined),
-    corners / n_corners (goodFeaturesToTrack before ORB's border filter), eig (B, H, W) f32, blur (B, H, W) u8."""
+    corners / n_corners (goodFeaturesToTrack before ORB's border filter), eig (B, H, W) f32, blur (B, H, W) u8.
+    `buffers` (a FeatureBuffers of the same shape) makes the call allocation-free; its tensors are returned."""
     if imgs.dtype != torch.uint8 or not imgs.is_cuda or imgs.dim() != 4 or imgs.shape[3] != 3:
         raise ValueError("imgs must be a uint8 CUDA tensor of shape (B, H, W, 3)")
     if min_distance >= 1 and float(min_distance) != int(min_distance):
@@ -47,29 +71,74 @@ def extract_features_batch(imgs, max_corners=3000, quality=0.01, min_distance=7.
     B, H, W, _ = imgs.shape
     dev = imgs.device
     lib = _cabi.lib()
-    ws_bytes = lib.vslam_features_workspace_bytes(B, H, W, float(min_distance))
-    if ws_bytes < 0:
-        raise ValueError("unsupported image size %dx%d" % (W, H))
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    out = {
-        "eig": torch.empty((B, H, W), dtype=torch.float32, device=dev),
-        "blur": torch.empty((B, H, W), dtype=torch.uint8, device=dev),
-        "corners": torch.empty((B, max_corners, 2), dtype=torch.float32, device=dev),
-        "n_corners": torch.empty(B, dtype=torch.int32, device=dev),
-        "kp": torch.empty((B, max_corners, 2), dtype=torch.float32, device=dev),
-        "desc": torch.empty((B, max_corners, 32), dtype=torch.uint8, device=dev),
-        "n_kp": torch.empty(B, dtype=torch.int32, device=dev),
-        "status": torch.empty(B, dtype=torch.int32, device=dev),
-    }
+    if buffers is None:
+        buffers = FeatureBuffers(B, H, W, max_corners, min_distance, dev)
+    elif buffers.shape != (B, H, W, max_corners, float(min_distance)):
+        raise ValueError("buffers were made for another call shape")
+    out = dict(buffers.out)
     ca, sa = _angle_terms(angle)
     with torch.cuda.device(dev):
         _cabi.check(lib.vslam_extract_features(
             imgs.data_ptr(), B, H, W, int(max_corners), float(quality), float(min_distance), ca, sa,
-            _pattern_on(dev).data_ptr(), ws.data_ptr(), ws_bytes, out["eig"].data_ptr(), out["blur"].data_ptr(),
-            out["corners"].data_ptr(), out["n_corners"].data_ptr(), out["kp"].data_ptr(), out["desc"].data_ptr(),
-            out["n_kp"].data_ptr(), out["status"].data_ptr(), _cabi.stream_ptr()))
-    out["_workspace"] = ws  # keeps the scratch alive until the caller has synchronised
+            _pattern_on(dev).data_ptr(), buffers.ws.data_ptr(), buffers.ws_bytes, out["eig"].data_ptr(),
+            out["blur"].data_ptr(), out["corners"].data_ptr(), out["n_corners"].data_ptr(), out["kp"].data_ptr(),
+            out["desc"].data_ptr(), out["n_kp"].data_ptr(), out["status"].data_ptr(), _cabi.stream_ptr()))
+    out["_workspace"] = buffers.ws  # keeps the scratch alive until the caller has synchronised
     return out
+
+
+class HostFeatureExtractor:
+    """End-to-end batched extractor for HOST frames: pinned staging, H2D copy of the BGR frames, the device
+    pipeline, D2H of key points + descriptors + counts.  The batch is cut into chunks whose copies and kernels
+    overlap on two streams; every buffer is allocated once."""
+
+    def __init__(self, batch, H, W, max_corners=3000, quality=0.01, min_distance=7.0, device="cuda:0", chunks=3):
+        self.device = torch.device(device)
+        self.batch, self.H, self.W = batch, H, W
+        self.max_corners, self.quality, self.min_distance = max_corners, quality, min_distance
+        self.chunks = max(1, min(chunks, batch))
+        self.step = (batch + self.chunks - 1) // self.chunks
+        self.img_pin = torch.empty((batch, H, W, 3), dtype=torch.uint8).pin_memory()
+        self.kp_pin = torch.empty((batch, max_corners, 2), dtype=torch.float32).pin_memory()
+        self.desc_pin = torch.empty((batch, max_corners, 32), dtype=torch.uint8).pin_memory()
+        self.n_kp_pin = torch.empty((batch,), dtype=torch.int32).pin_memory()
+        with torch.cuda.device(self.device):
+            self.img_dev = torch.empty((batch, H, W, 3), dtype=torch.uint8, device=self.device)
+            self.streams = [torch.cuda.Stream(self.device) for _ in range(2)]
+            self.bufs = {}
+            for c in range(self.chunks):
+                n = min(batch, (c + 1) * self.step) - c * self.step
+                if n > 0 and (c & 1, n) not in self.bufs:   # one set per stream and chunk size
+                    self.bufs[(c & 1, n)] = FeatureBuffers(n, H, W, max_corners, min_distance, self.device)
+        self.h2d_bytes = self.img_pin.numel()
+        self.d2h_bytes = self.kp_pin.numel() * 4 + self.desc_pin.numel() + self.n_kp_pin.numel() * 4
+        self.launches_per_call = 7 * self.chunks
+
+    def load(self, frames):
+        """Copies caller frames (numpy uint8 [batch, H, W, 3], BGR) into the pinned staging buffer."""
+        self.img_pin.copy_(torch.from_numpy(np.ascontiguousarray(frames)))
+
+    def run(self):
+        """H2D -> extract -> D2H for the staged batch; returns pinned (kp, desc, n_kp)."""
+        cur = torch.cuda.current_stream(self.device)
+        start = torch.cuda.Event()
+        start.record(cur)
+        for c in range(self.chunks):
+            lo, hi = c * self.step, min(self.batch, (c + 1) * self.step)
+            if lo >= hi:
+                break
+            st = self.streams[c & 1]
+            st.wait_event(start)
+            with torch.cuda.stream(st):
+                self.img_dev[lo:hi].copy_(self.img_pin[lo:hi], non_blocking=True)
+                o = extract_features_batch(self.img_dev[lo:hi], self.max_corners, self.quality, self.min_distance,
+                                           buffers=self.bufs[(c & 1, hi - lo)])
+                self.kp_pin[lo:hi].copy_(o["kp"], non_blocking=True)
+                self.desc_pin[lo:hi].copy_(o["desc"], non_blocking=True)
+                self.n_kp_pin[lo:hi].copy_(o["n_kp"], non_blocking=True)
+        for st in self.streams:
+            cur.wait_stream(st)
+        return self.kp_pin, self.desc_pin, self.n_kp_pin
 
 
 class FeatureExtractor:
