@@ -243,3 +243,20 @@ def test_gpu_host_extractor_equals_direct_call():
             n = int(n_kp[b])
             assert np.array_equal(kp[b, :n].numpy(), want["kp"][b, :n])
             assert np.array_equal(desc[b, :n].numpy(), want["desc"][b, :n])
+
+
+@pytest.mark.gpu
+def test_gpu_large_batch_of_odd_frames_uses_throughput_variant():
+    """100 frames of 75 x 203 (odd width: scalar-tail columns of OpenCV's row filters; enough strips that the
+    one-thread-per-column response kernel is dispatched): response bit-exact vs the oracle, features vs cv2."""
+    rng = np.random.default_rng(31)
+    imgs = np.stack([cv2.GaussianBlur(rng.integers(0, 256, (75, 203, 3), dtype=np.uint8), (3, 3), 0.8)
+                     for _ in range(100)])
+    o = _gpu_run(imgs)
+    for b in (0, 57, 99):
+        eig = of.corner_min_eigen_val(of.gray_mean(imgs[b]))
+        assert np.array_equal(o["eig"][b].view(np.uint32), eig.view(np.uint32)), b
+        corners, kp, des = _cv2_features(imgs[b])
+        n, m = int(o["n_corners"][b]), int(o["n_kp"][b])
+        assert n == len(corners) and np.array_equal(o["corners"][b, :n], corners), b
+        assert m == len(kp) and np.array_equal(o["kp"][b, :m], kp) and np.array_equal(o["desc"][b, :m], des), b

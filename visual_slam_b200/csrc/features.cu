@@ -69,16 +69,158 @@ feat_gray_kernel(const uint8_t* __restrict__ img, long long n_px, int px_per_img
 }
 
 // ---- K2: cornerMinEigenVal(blockSize 3, Sobel 3, REFLECT_101) --------------------------------------
-// One thread per column (plus one halo column either side of the strip), walking down the image.
 //   Sobel d/dx: rows (-1,0,1) exact; columns (s,2s,s): fma(up + down, s1, mid * s2)
 //   Sobel d/dy: rows (s,2s,s): fma(s1, right, fma(s2, mid, s1 * left)); columns (-1,0,1) exact
 //   cov = (dx*dx, dx*dy, dy*dy) float; box rows: (l + m) + r in double; box columns: running double sum
 //   eig = (a + c) - sqrt((a - c)^2 + b^2), a = A/2, c = C/2, float, not contracted.
-constexpr int kEigT = 64;
+// The box filter's column sum is a RUNNING float64 sum (sum += new row; out = float(sum); sum -= old row), so the
+// rows of one column cannot be split -- but everything up to the row sums can.  Warp-specialised: a CTA owns a
+// strip of 62 columns; six PRODUCER warps take the rows round-robin and turn them into float64 row sums in a
+// 12-slot shared-memory ring (full/empty mbarriers per slot); two CONSUMER warps (one thread per column) walk
+// down the frame doing only the running sum and the eigenvalue formula.
+constexpr int kEigT = 64;       // strip width including one halo column either side
+constexpr int kEigProd = 6;     // producer warps
+constexpr int kEigRing = 12;    // ring slots (a multiple of kEigProd)
+constexpr int kEigThreads = (2 + kEigProd) * 32;
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(kEigThreads)
+feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restrict__ eig, int* __restrict__ counters) {
+  __shared__ double ring[kEigRing][3][kEigT];
+  __shared__ float prod[kEigProd][3][kEigT];
+  __shared__ uint64_t full[kEigRing], empty[kEigRing];
+  const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int c0 = blockIdx.x * (kEigT - 2) - 1;  // image column of strip index 0
+  const uint8_t* g = gray + (size_t)b * H * W;
+  if (tid == 0) {
+    for (int s = 0; s < kEigRing; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 2); }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (wid >= 2) {
+    // ------------------------------------------------------------------ producers: row -> row sums
+    const int w = wid - 2;
+    const float s1 = __int_as_float(0x39ab5601), s2 = __int_as_float(0x3a2b5601);  // float(1/3060), float(2/3060)
+    int cc[2], xm[2], xp[2];
+    bool vec_col[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      cc[h] = reflect101(min(c0 + h * 32 + lane, W), W);
+      xm[h] = reflect101(cc[h] - 1, W);
+      xp[h] = reflect101(cc[h] + 1, W);
+      // OpenCV's uint8 -> float32 row filter fuses in its 32-pixel vector body and rounds every product in the
+      // scalar tail (oracle/features.py: row_vector_width)
+      vec_col[h] = cc[h] < (W / 32) * 32;
+    }
+    for (int r = w; r < H; r += kEigProd) {
+      const int slot = r % kEigRing, use = r / kEigRing;
+      const uint8_t* gm_ = g + (size_t)reflect101(r - 1, H) * W;
+      const uint8_t* gc_ = g + (size_t)r * W;
+      const uint8_t* gp_ = g + (size_t)reflect101(r + 1, H) * W;
+      float p[2][3];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const float ul = (float)__ldg(gm_ + xm[h]), um = (float)__ldg(gm_ + cc[h]), ur = (float)__ldg(gm_ + xp[h]);
+        const float ml = (float)__ldg(gc_ + xm[h]), mr = (float)__ldg(gc_ + xp[h]);
+        const float dl = (float)__ldg(gp_ + xm[h]), dm = (float)__ldg(gp_ + cc[h]), dr = (float)__ldg(gp_ + xp[h]);
+        const float rx_u = __fsub_rn(ur, ul), rx_m = __fsub_rn(mr, ml), rx_d = __fsub_rn(dr, dl);
+        float R_u, R_d;
+        if (vec_col[h]) {
+          R_u = __fmaf_rn(s1, ur, __fmaf_rn(s2, um, __fmul_rn(s1, ul)));
+          R_d = __fmaf_rn(s1, dr, __fmaf_rn(s2, dm, __fmul_rn(s1, dl)));
+        } else {
+          R_u = __fadd_rn(__fadd_rn(__fmul_rn(s1, ul), __fmul_rn(s2, um)), __fmul_rn(s1, ur));
+          R_d = __fadd_rn(__fadd_rn(__fmul_rn(s1, dl), __fmul_rn(s2, dm)), __fmul_rn(s1, dr));
+        }
+        const float dx = __fmaf_rn(__fadd_rn(rx_u, rx_d), s1, __fmul_rn(rx_m, s2));
+        const float dy = __fsub_rn(R_d, R_u);
+        p[h][0] = __fmul_rn(dx, dx); p[h][1] = __fmul_rn(dx, dy); p[h][2] = __fmul_rn(dy, dy);
+      }
+      mbar_wait(&empty[slot], (uint32_t)((use & 1) ^ 1));  // the consumers are done with the slot's previous row
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) prod[w][k][h * 32 + lane] = p[h][k];
+      __syncwarp();
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int i = h * 32 + lane;
+        if (i >= 1 && i <= kEigT - 2) {
+#pragma unroll
+          for (int k = 0; k < 3; ++k)
+            ring[slot][k][i] = ((double)prod[w][k][i - 1] + (double)prod[w][k][i]) + (double)prod[w][k][i + 1];
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[slot]);
+    }
+    return;
+  }
+
+  // -------------------------------------------------------------------- consumers: the running column sum
+  const int c = c0 + tid;
+  const bool owner = tid >= 1 && tid <= kEigT - 2 && c < W;
+  float* out = eig + (size_t)b * H * W;
+  double rsa[3] = {0, 0, 0}, rsb[3] = {0, 0, 0}, sum[3] = {0, 0, 0};
+  float vmax = -INFINITY;
+  auto emit = [&](int y, const double* s0) {
+    const float A = (float)s0[0], B = (float)s0[1], C = (float)s0[2];
+    const float a = __fmul_rn(A, 0.5f), cq = __fmul_rn(C, 0.5f);
+    float t = __fsub_rn(a, cq);
+    t = __fadd_rn(__fmul_rn(t, t), __fmul_rn(B, B));
+    const float e = __fsub_rn(__fadd_rn(a, cq), __fsqrt_rn(t));
+    out[(size_t)y * W + c] = e;
+    vmax = fmaxf(vmax, e);
+  };
+  for (int r = 0; r < H; ++r) {
+    const int slot = r % kEigRing, use = r / kEigRing;
+    mbar_wait(&full[slot], (uint32_t)(use & 1));
+    double rsc[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) rsc[k] = ring[slot][k][tid];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[slot]);
+    if (owner) {
+      if (r == 1) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) sum[k] = (0.0 + rsc[k]) + rsb[k];  // padded rows -1 (= row 1) and 0
+      }
+      if (r >= 1) {
+        double s0[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          s0[k] = sum[k] + rsc[k];
+          sum[k] = s0[k] - (r == 1 ? rsc[k] : rsa[k]);  // minus row y-1 (row -1 reflects to row 1)
+        }
+        emit(r - 1, s0);
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { rsa[k] = rsb[k]; rsb[k] = rsc[k]; }
+    }
+  }
+  if (owner) {  // last row: row H reflects to row H-2, which is rsa after the final shift
+    double s0[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) s0[k] = sum[k] + rsa[k];
+    emit(H - 1, s0);
+  }
+  int key = owner ? float_key(vmax) : INT_MIN;
+  key = __reduce_max_sync(0xffffffffu, key);
+  if (lane == 0) atomicMax(&counters[4 * b + 0], key);
+}
+
+// Throughput variant of K2 for large batches (enough strips to fill the GPU on their own): one thread per column
+// does everything for its column -- Sobel in a three-row register window, the three products exchanged through
+// double-buffered shared memory (one barrier per row), input rows fetched eight rows ahead.  Fewer instructions
+// per row than the warp-specialised kernel (no ring, no mbarrier waits), but a ~6x longer serial chain.
 constexpr int kEigChunk = 8;
 
 __global__ void __launch_bounds__(kEigT)
-feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restrict__ eig, int* __restrict__ counters) {
+feat_eig_walk_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restrict__ eig, int* __restrict__ counters) {
   __shared__ float sm[2][3][kEigT];
   const int b = blockIdx.y, tid = threadIdx.x;
   const int c = blockIdx.x * (kEigT - 2) + tid - 1;
@@ -590,7 +732,11 @@ extern "C" int vslam_extract_features(const uint8_t* img, int batch, int H, int 
 
   const long long gthreads = (n_px + 3) / 4 > batch ? (n_px + 3) / 4 : batch;
   feat_gray_kernel<<<(unsigned)((gthreads + 255) / 256), 256, 0, st>>>(img, n_px, px, gm, gb, counters, batch);
-  feat_eig_kernel<<<dim3((W + kEigT - 3) / (kEigT - 2), batch), kEigT, 0, st>>>(gm, H, W, eig, counters);
+  const int strips = (W + kEigT - 3) / (kEigT - 2);
+  if ((long long)strips * batch < 2ll * sm_count())   // latency variant: rows in parallel, short serial chain
+    feat_eig_kernel<<<dim3(strips, batch), kEigThreads, 0, st>>>(gm, H, W, eig, counters);
+  else                                                // throughput variant: one thread per column
+    feat_eig_walk_kernel<<<dim3(strips, batch), kEigT, 0, st>>>(gm, H, W, eig, counters);
   feat_blur_kernel<<<dim3((W + kBlurW - 1) / kBlurW, (H + kBlurH - 1) / kBlurH, batch), 256, 0, st>>>(gb, H, W, blur);
   int radius = 0, d2 = 0;
   if (min_distance >= 1.0) {
