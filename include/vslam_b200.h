@@ -245,8 +245,12 @@ int vslam_list_diff(const double* kp1, int n1, const double* kp2, int n2, int mo
  *   kp         dev f32 [batch][max_corners][2], n_kp dev i32 [batch]        key points ORB keeps (31-px border)
  *   desc       dev u8  [batch][max_corners][32]                             their descriptors
  *   status     dev i32 [batch] or NULL   1 if an internal list overflowed (cannot happen for valid input)
+ *
+ * vslam_features_set_variant: which response kernel runs -- 0 automatic (by batch size), 1 warp-specialised
+ * (latency), 2 one thread per column (throughput).  Both are bit-identical; tests and tuning only.
  */
 long long vslam_features_workspace_bytes(int batch, int H, int W, double min_distance);
+int vslam_features_set_variant(int variant);
 int vslam_extract_features(const uint8_t* img, int batch, int H, int W, int max_corners, double quality,
                            double min_distance, float cos_a, float sin_a, const int8_t* pattern,
                            void* workspace, long long workspace_bytes, float* eig, uint8_t* blur,

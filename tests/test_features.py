@@ -260,3 +260,25 @@ def test_gpu_large_batch_of_odd_frames_uses_throughput_variant():
         n, m = int(o["n_corners"][b]), int(o["n_kp"][b])
         assert n == len(corners) and np.array_equal(o["corners"][b, :n], corners), b
         assert m == len(kp) and np.array_equal(o["kp"][b, :m], kp) and np.array_equal(o["desc"][b, :m], des), b
+
+
+@pytest.mark.gpu
+def test_gpu_both_response_kernels_are_bit_identical():
+    """The warp-specialised and the one-thread-per-column response kernels forced on the same frames."""
+    from visual_slam_b200 import _cabi
+    rng = np.random.default_rng(41)
+    imgs = np.stack([cv2.GaussianBlur(rng.integers(0, 256, (97, 203, 3), dtype=np.uint8), (3, 3), 0.9)
+                     for _ in range(6)])
+    lib = _cabi.lib()
+    try:
+        outs = []
+        for variant in (1, 2):
+            _cabi.check(lib.vslam_features_set_variant(variant))
+            outs.append(_gpu_run(imgs))
+    finally:
+        _cabi.check(lib.vslam_features_set_variant(0))
+    eig = of.corner_min_eigen_val(of.gray_mean(imgs[3]))
+    for o in outs:
+        assert np.array_equal(o["eig"][3].view(np.uint32), eig.view(np.uint32))
+    assert np.array_equal(outs[0]["eig"].view(np.uint32), outs[1]["eig"].view(np.uint32))
+    assert np.array_equal(outs[0]["n_kp"], outs[1]["n_kp"])

@@ -43,6 +43,7 @@ def _declare(lib):
     lib.vslam_list_diff.argtypes = [vp, i32, vp, i32, i32, vp, vp, vp, vp]
     lib.vslam_features_workspace_bytes.argtypes = [i32, i32, i32, f64]
     lib.vslam_features_workspace_bytes.restype = C.c_longlong
+    lib.vslam_features_set_variant.argtypes = [i32]
     lib.vslam_extract_features.argtypes = [vp, i32, i32, i32, i32, f64, f64, C.c_float, C.c_float, vp, vp,
                                            C.c_longlong, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     pp = C.POINTER(vp)

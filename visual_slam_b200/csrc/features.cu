@@ -75,12 +75,12 @@ feat_gray_kernel(const uint8_t* __restrict__ img, long long n_px, int px_per_img
 //   eig = (a + c) - sqrt((a - c)^2 + b^2), a = A/2, c = C/2, float, not contracted.
 // The box filter's column sum is a RUNNING float64 sum (sum += new row; out = float(sum); sum -= old row), so the
 // rows of one column cannot be split -- but everything up to the row sums can.  Warp-specialised: a CTA owns a
-// strip of 62 columns; six PRODUCER warps take the rows round-robin and turn them into float64 row sums in a
-// 12-slot shared-memory ring (full/empty mbarriers per slot); two CONSUMER warps (one thread per column) walk
+// strip of 62 columns; fourteen PRODUCER warps take the rows round-robin and turn them into float64 row sums in a
+// 14-slot shared-memory ring (full/empty mbarriers per slot); two CONSUMER warps (one thread per column) walk
 // down the frame doing only the running sum and the eigenvalue formula.
 constexpr int kEigT = 64;       // strip width including one halo column either side
-constexpr int kEigProd = 6;     // producer warps
-constexpr int kEigRing = 12;    // ring slots (a multiple of kEigProd)
+constexpr int kEigProd = 14;    // producer warps
+constexpr int kEigRing = 14;    // ring slots (a multiple of kEigProd)
 constexpr int kEigThreads = (2 + kEigProd) * 32;
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
@@ -666,6 +666,8 @@ feat_orb_kernel(const uint8_t* __restrict__ blur, int H, int W, const float2* __
 // the status band of one CTA must fit its shared memory (8 CTAs per image: frames up to ~1.6 Mpixel)
 constexpr size_t kMaxBandBytes = 200 * 1024;
 
+static int g_eig_variant = 0;  // 0 auto, 1 warp-specialised, 2 column walk (vslam_features_set_variant; tests, tuning)
+
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct FeatLayout {
@@ -700,6 +702,12 @@ static FeatLayout feat_layout(int batch, int H, int W, double min_distance) {
 
 }  // namespace vslam
 
+extern "C" int vslam_features_set_variant(int variant) {
+  if (variant < 0 || variant > 2) return VSLAM_ERR_BAD_ARG;
+  vslam::g_eig_variant = variant;
+  return VSLAM_OK;
+}
+
 extern "C" long long vslam_features_workspace_bytes(int batch, int H, int W, double min_distance) {
   if (batch < 1 || H < 16 || W < 16 || (long long)H * W > (1ll << 30)) return -1;
   if (vslam::feat_layout(batch, H, W, min_distance).band_bytes > vslam::kMaxBandBytes) return -1;
@@ -733,7 +741,8 @@ extern "C" int vslam_extract_features(const uint8_t* img, int batch, int H, int 
   const long long gthreads = (n_px + 3) / 4 > batch ? (n_px + 3) / 4 : batch;
   feat_gray_kernel<<<(unsigned)((gthreads + 255) / 256), 256, 0, st>>>(img, n_px, px, gm, gb, counters, batch);
   const int strips = (W + kEigT - 3) / (kEigT - 2);
-  if ((long long)strips * batch < 2ll * sm_count())   // latency variant: rows in parallel, short serial chain
+  const bool ws_variant = g_eig_variant == 1 || (g_eig_variant == 0 && (long long)strips * batch < 2ll * sm_count());
+  if (ws_variant)                                     // latency variant: rows in parallel, short serial chain
     feat_eig_kernel<<<dim3(strips, batch), kEigThreads, 0, st>>>(gm, H, W, eig, counters);
   else                                                // throughput variant: one thread per column
     feat_eig_walk_kernel<<<dim3(strips, batch), kEigT, 0, st>>>(gm, H, W, eig, counters);
