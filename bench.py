@@ -215,7 +215,7 @@ def cpu_features(frames_u8, seconds_budget):
             "cv2_threads": cv2.getNumThreads(), "kind": "reference (cv2 calls of frame.py:10-14, ORB variant)"}
 
 
-def features_figures(torch, batch=64, steps=5):
+def features_figures(torch, batch=64, steps=5, dist=None, world=1, rank=0):
     """N3: goodFeaturesToTrack + ORB.compute on `batch` synthetic VGA frames per step.  Device-resident
     frames/s (CUDA events), end to end from pinned host memory (H2D of the frames, D2H of key points +
     descriptors inside the timed region), algorithmic bytes per frame for the HBM view, and the reference's cv2
@@ -223,7 +223,7 @@ def features_figures(torch, batch=64, steps=5):
     from visual_slam_b200 import synth
     from visual_slam_b200.features import FeatureBuffers, HostFeatureExtractor, extract_features_batch
     H, W = 480, 640
-    host = synth.frames(batch, H, W, seed=3)
+    host = synth.frames(batch, H, W, seed=3 + rank)      # frames are independent units: each rank has its own
     pin = torch.from_numpy(host).pin_memory()
     dev = pin.cuda()
     bufs = FeatureBuffers(batch, H, W, device=dev.device)
@@ -238,7 +238,13 @@ def features_figures(torch, batch=64, steps=5):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     n_kp = o["n_kp"].cpu().numpy()
-    hx = HostFeatureExtractor(batch, H, W, chunks=3)
+    if world > 1:                                         # device time of the slowest rank, NCCL gather of the counts
+        t = torch.tensor([ms], dtype=torch.float64, device=dev.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        counts = torch.empty(world * batch, dtype=torch.int32, device=dev.device)
+        dist.all_gather_into_tensor(counts, o["n_kp"])
+    hx = HostFeatureExtractor(batch, H, W, chunks=3, device=dev.device)
     hx.load(host)
     for _ in range(2):
         hx.run()
@@ -250,16 +256,23 @@ def features_figures(torch, batch=64, steps=5):
     torch.cuda.synchronize()
     e2e_ms = e0.elapsed_time(e1) / steps
     assert np.array_equal(nk_pin.numpy(), n_kp)
+    if world > 1:
+        t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    if rank != 0:
+        return None
     # algorithmic traffic per frame: BGR read 3, two greys written 2 + read 2, response written 4 + read 4,
     # blur written 1 (bytes per pixel); key points + descriptors 40 B each
     alg = H * W * 16 + int(n_kp.mean()) * 40
-    cpu = cpu_features(host, 4.0)
-    return {"frames_per_s": batch / (ms * 1e-3), "ms_per_batch": ms, "batch": batch, "height": H, "width": W,
+    cpu = cpu_features(host, 4.0) if world == 1 else None
+    return {"frames_per_s": world * batch / (ms * 1e-3), "ms_per_batch": ms, "batch_per_gpu": batch, "n_gpus": world,
+            "scaling": "weak (frames sharded by rank, NCCL all_gather of the key-point counts)", "height": H, "width": W,
             "keypoints_per_frame": float(n_kp.mean()),
-            "e2e_frames_per_s": batch / (e2e_ms * 1e-3), "h2d_bytes_per_step": int(hx.h2d_bytes),
+            "e2e_frames_per_s": world * batch / (e2e_ms * 1e-3), "h2d_bytes_per_step": int(hx.h2d_bytes),
             "d2h_bytes_per_step": int(hx.d2h_bytes), "e2e_path": "HostFeatureExtractor (pinned host -> H2D -> "
             "pipeline -> D2H, 3 chunks on two streams; PCIe-bound)",
-            "algorithmic_bytes_per_frame": alg, "algorithmic_gbs": batch * alg / (ms * 1e-3) / 1e9,
+            "algorithmic_bytes_per_frame": alg, "algorithmic_gbs_per_gpu": batch * alg / (ms * 1e-3) / 1e9,
             "gpu_launches_per_step": 7, "data": "synthetic block-texture frames (synth.frames), 3000-corner cap binds",
             "cpu_reference": cpu}
 
@@ -453,6 +466,9 @@ def run_gpu(args):
     assert int(nk_pin.sum()) == n_keep_ref
 
     tracking = None if args.skip_tracking else tracking_figures(torch, dist, world, rank, dev)
+    features = None
+    if not args.skip_features and world > 1:
+        features = features_figures(torch, dist=dist, world=world, rank=rank)
 
     if rank != 0:
         if world > 1:
@@ -489,7 +505,7 @@ def run_gpu(args):
         cpu.pop("pairs"); cpu.pop("seconds")
         line["cpu_baseline"] = cpu
         if not args.skip_features:
-            line["features"] = features_figures(torch)
+            features = features_figures(torch)
         if not args.skip_ba:
             ba = ba_figures(torch)
             line["ba"] = ba
@@ -505,6 +521,8 @@ def run_gpu(args):
                                              "launch bracketed alone after an L2 flush: %.4f ms"
                                              % ba["c4"]["linearize_single_cold_launch_ms"],
                                    "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)"}
+    if features:
+        line["features"] = features
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -752,20 +752,14 @@ extern "C" int vslam_extract_features(const uint8_t* img, int batch, int H, int 
     d2 = (int)(min_distance * min_distance);
     while ((radius + 1) * (radius + 1) < d2) ++radius;
   }
-  static size_t band_attr = 48 * 1024;
-  if (L.band_bytes > band_attr) {
+  // (set on every call: the attribute is per device and a process may drive several)
+  if (L.band_bytes > 48 * 1024)
     VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)kMaxBandBytes));
-    band_attr = kMaxBandBytes;
-  }
   feat_select_kernel<<<dim3(kSupCtas, batch), kSupThreads, L.band_bytes, st>>>(
       eig, H, W, L.Hb, L.Wp, quality, radius, d2, reinterpret_cast<int*>(ws + L.lists), acc, L.acc_cap, counters);
-  static bool sort_attr = false;
-  if (!sort_attr) {
-    VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)(kSortMax * sizeof(unsigned long long))));
-    sort_attr = true;
-  }
+  VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)(kSortMax * sizeof(unsigned long long))));
   feat_order_kernel<<<batch, kSortThreads, kSortMax * sizeof(unsigned long long), st>>>(
       acc, L.acc_cap, W, max_corners, reinterpret_cast<float2*>(corners), n_corners, counters);
   feat_border_compact_kernel<<<batch, 1024, 0, st>>>(reinterpret_cast<const float2*>(corners), n_corners,
