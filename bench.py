@@ -352,6 +352,8 @@ def run_gpu(args):
         # JSON line the driver parses; anything the user asked for explicitly (INFO, TRACE) is kept
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
             os.environ["NCCL_DEBUG"] = "WARN"
+        # (WARN still prints the version banner: send whatever NCCL logs to stderr, stdout carries the JSON line only)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     lib = _cabi.lib()
     B = PAIRS_PER_GPU
