@@ -282,3 +282,31 @@ def test_gpu_both_response_kernels_are_bit_identical():
         assert np.array_equal(o["eig"][3].view(np.uint32), eig.view(np.uint32))
     assert np.array_equal(outs[0]["eig"].view(np.uint32), outs[1]["eig"].view(np.uint32))
     assert np.array_equal(outs[0]["n_kp"], outs[1]["n_kp"])
+
+
+@pytest.mark.gpu
+def test_gpu_tiny_and_large_frames():
+    """A 40 x 50 frame (bands thinner than the suppression radius, no key point survives ORB's border), a
+    1280 x 960 frame (status band > 48 KB: opt-in shared memory) and a frame too large for the band."""
+    import torch
+    from visual_slam_b200.features import extract_features_batch
+    rng = np.random.default_rng(77)
+    tiny = cv2.GaussianBlur(rng.integers(0, 256, (40, 50, 3), dtype=np.uint8), (3, 3), 0.8)
+    o = _gpu_run(tiny[None])
+    corners, kp, des = _cv2_features(tiny)
+    n = int(o["n_corners"][0])
+    assert n == len(corners) > 0 and np.array_equal(o["corners"][0, :n], corners)
+    assert int(o["n_kp"][0]) == len(kp) == 0
+    big = cv2.resize(synth_frame(), (1280, 960), interpolation=cv2.INTER_LINEAR)
+    o = _gpu_run(big[None])
+    corners, kp, des = _cv2_features(big)
+    n, m = int(o["n_corners"][0]), int(o["n_kp"][0])
+    assert n == len(corners) and np.array_equal(o["corners"][0, :n], corners)
+    assert m == len(kp) and np.array_equal(o["kp"][0, :m], kp) and np.array_equal(o["desc"][0, :m], des)
+    with pytest.raises(ValueError):
+        extract_features_batch(torch.zeros((1, 1200, 1600, 3), dtype=torch.uint8, device="cuda"))
+
+
+def synth_frame():
+    from visual_slam_b200 import synth
+    return synth.frames(1, 480, 640, seed=12)[0]
