@@ -44,6 +44,15 @@ out["pair_train"] = np.array([m[0].trainIdx for m in matches], np.int32)
 out["pair_dist"] = np.array([m[0].distance for m in matches], np.float32)
 out["pair_pts1"], out["pair_pts2"], out["pair_ft1"], out["pair_ft2"] = p1, p2, f1, f2
 print("pair 1->32: kp", kp1.shape[0], kp32.shape[0], "ratio matches", len(matches))
+# ... and the reference's own map-initialisation calls on those matches (main.py:103,111 with the ICL intrinsics)
+import helper_functions as ref_hf  # noqa: E402
+K = np.matrix([[481.20, 0, 319.5], [0, 480.0, 239.5], [0, 0, 1]])
+E, inl, score = ref_hf.estimateEssential(p1, p2, K, essTh=3.0 / K[0, 0])
+sel = inl.ravel() == 1
+R, t, frac, tri, ip1, ip2, if1, if2 = ref_hf.estimateRelativePose(E, p1[sel], p2[sel], f1[sel], f2[sel], K, "Essential")
+out["pair_E"], out["pair_inliers"], out["pair_R"], out["pair_t"] = E, inl, R, t
+out["pair_valid_fraction"] = np.array(frac)
+print("essential inliers", int(sel.sum()), "of", len(sel), "valid fraction", frac)
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "features_icl.npz")
 np.savez_compressed(path, **out)
 print("written", path, os.path.getsize(path))

@@ -310,3 +310,31 @@ def test_gpu_tiny_and_large_frames():
 def synth_frame():
     from visual_slam_b200 import synth
     return synth.frames(1, 480, 640, seed=12)[0]
+
+
+@pytest.mark.gpu
+def test_gpu_map_initialisation_chain_on_icl_pair():
+    """C1 slice, frames 1 -> 32: device features -> device matches -> estimateEssential -> estimateRelativePose,
+    against the reference's own chain (tests/golden/make_features_golden.py).  The matches are identical; the
+    essential-matrix RANSAC draws its own samples (cv2's are not seedable), so E is checked through its inlier
+    support, and recoverPose is checked on the reference's E, where it is deterministic."""
+    from visual_slam_b200 import FeatureMatcher
+    from visual_slam_b200.features import FeatureExtractor
+    from visual_slam_b200.twoview import estimateEssential, estimateRelativePose
+    g = np.load(GOLD)
+    K = np.matrix([[481.20, 0, 319.5], [0, 480.0, 239.5], [0, 0, 1]])
+    fx, fm = FeatureExtractor(), FeatureMatcher()
+    kp1, des1 = fx.compute_features(g["icl1_img"])
+    kp2, des2 = fx.compute_features(g["icl32_img"])
+    _, p1, f1, p2, f2 = fm.match_features(kp1, des1, kp2, des2)
+    assert np.array_equal(p1, g["pair_pts1"]) and np.array_equal(p2, g["pair_pts2"])
+    E, inl, _ = estimateEssential(p1, p2, K, essTh=3.0 / K[0, 0])
+    n_ref = int(g["pair_inliers"].sum())
+    assert E is not None and abs(np.linalg.norm(E) - 1.0) < 1e-9
+    assert int(inl.sum()) >= 0.9 * n_ref, (int(inl.sum()), n_ref)
+    sel = g["pair_inliers"].ravel() == 1
+    R, t, frac, tri, ip1, ip2, if1, if2 = estimateRelativePose(g["pair_E"], p1[sel], p2[sel], f1[sel], f2[sel], K,
+                                                               "Essential")
+    assert np.abs(np.asarray(R) - g["pair_R"]).max() < 1e-6
+    assert np.abs(np.asarray(t).ravel() - g["pair_t"].ravel()).max() < 1e-6
+    assert abs(frac - float(g["pair_valid_fraction"])) < 1e-12
