@@ -71,6 +71,17 @@ int vslam_hamming_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt,
                        int batch, void* stream);
 
 /*
+ * The same for RAGGED batches (frames with different key-point counts, as vslam_extract_features produces
+ * them): q / t are padded to nq_stride / nt_stride rows per pair, nq_arr / nt_arr (dev i32 [batch]) give the
+ * number of real rows of each pair.  Rows beyond the count never match and are never matched: their idx / dist
+ * entries are -1 (so vslam_match_filter drops them) and their rev_key entries stay 0xFFFFFFFF.  A pair with
+ * fewer than 2 train rows yields -1 second entries exactly like nt < 2 above.
+ */
+int vslam_hamming_knn2_ragged(const uint8_t* q, int nq_stride, const int32_t* nq_arr, const uint8_t* t,
+                              int nt_stride, const int32_t* nt_arr, int32_t* idx, int32_t* dist,
+                              uint32_t* rev_key, int batch, void* stream);
+
+/*
  * Lowe ratio test (+ optional mutual-nearest cross-check) and order-preserving
  * compaction.  Replaces the Python loop src/v2/frame.py:30-42.
  *

@@ -338,3 +338,28 @@ def test_gpu_map_initialisation_chain_on_icl_pair():
     assert np.abs(np.asarray(R) - g["pair_R"]).max() < 1e-6
     assert np.abs(np.asarray(t).ravel() - g["pair_t"].ravel()).max() < 1e-6
     assert abs(frac - float(g["pair_valid_fraction"])) < 1e-12
+
+
+@pytest.mark.gpu
+def test_gpu_frontend_batch_device_resident_chain():
+    """features.frontend_batch (frames -> features of both -> ragged matching, nothing leaves the device) on the
+    ICL-NUIM pair and on a second, different pair in the same batch, against the reference's chain / the oracle."""
+    import torch
+    from oracle import matching as om
+    from visual_slam_b200 import synth
+    from visual_slam_b200.features import frontend_batch
+    g = np.load(GOLD)
+    other = synth.frames(2, 480, 640, seed=55)
+    a = np.stack([g["icl1_img"], other[0]])
+    b = np.stack([g["icl32_img"], np.roll(other[0], 5, axis=1)])
+    fa, fb, m = frontend_batch(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda())
+    torch.cuda.synchronize()
+    n = int(m["n_keep"][0])
+    assert np.array_equal(m["keep_q"][0, :n].cpu().numpy(), g["pair_query"])
+    assert np.array_equal(m["keep_t"][0, :n].cpu().numpy(), g["pair_train"])
+    na, nb = int(fa["n_kp"][1]), int(fb["n_kp"][1])
+    oi, od = om.knn2_numpy(fa["desc"][1, :na].cpu().numpy(), fb["desc"][1, :nb].cpu().numpy())
+    kq, kt = om.filter_numpy(oi, od, 0.8, None)
+    n1 = int(m["n_keep"][1])
+    assert n1 == len(kq) > 100 and np.array_equal(m["keep_q"][1, :n1].cpu().numpy(), kq)
+    assert np.array_equal(m["keep_t"][1, :n1].cpu().numpy(), kt)

@@ -95,3 +95,41 @@ def test_c2_full_size_batch_properties():
     assert (g1["n_keep"] > 0.6 * 2048).all() and (g1["n_keep"] <= 0.7 * 2048 + 1).all()
     d = g1["dist"]
     assert (d[..., 0] <= d[..., 1]).all() and (d >= 0).all() and (d <= 256).all()
+
+
+@pytest.mark.gpu
+def test_ragged_batch_matches_oracle_per_pair():
+    """vslam_hamming_knn2_ragged: pairs padded to a common stride with per-pair row counts (what the feature
+    extractor hands over).  Every pair must equal the oracle on its real rows; padding rows are -1 and never win."""
+    import torch
+    from oracle import matching as om
+    from visual_slam_b200 import match_batch, synth
+    stride_q, stride_t = 1100, 1030
+    counts = [(1100, 1030), (513, 1030), (512, 511), (1, 2), (700, 1), (0, 50), (40, 0), (1024, 1029)]
+    B = len(counts)
+    rng = np.random.default_rng(12)
+    q = rng.integers(0, 256, (B, stride_q, 32), dtype=np.uint8)      # padding rows hold arbitrary bytes
+    t = rng.integers(0, 256, (B, stride_t, 32), dtype=np.uint8)
+    for b, (nq, nt) in enumerate(counts):
+        qq, tt, _ = synth.descriptors_pair(max(nq, 1), max(nt, 1), seed=100 + b)
+        q[b, :nq] = qq[:nq]
+        t[b, :nt] = tt[:nt]
+    nq_d = torch.tensor([c[0] for c in counts], dtype=torch.int32, device="cuda")
+    nt_d = torch.tensor([c[1] for c in counts], dtype=torch.int32, device="cuda")
+    for cross in (False, True):
+        out = match_batch(torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda(), 0.8, cross, n_q=nq_d, n_t=nt_d)
+        torch.cuda.synchronize()
+        idx, dist = out["idx"].cpu().numpy(), out["dist"].cpu().numpy()
+        for b, (nq, nt) in enumerate(counts):
+            assert (idx[b, nq:] == -1).all() and (dist[b, nq:] == -1).all(), (b, cross)
+            n = int(out["n_keep"][b])
+            if nq == 0 or nt == 0:
+                assert n == 0 and (idx[b, :nq] == -1).all()
+                continue
+            oi, od = om.knn2_numpy(q[b, :nq], t[b, :nt])
+            assert np.array_equal(idx[b, :nq], oi) and np.array_equal(dist[b, :nq], od), (b, cross)
+            rev_idx = om.rev_nearest_numpy(q[b, :nq], t[b, :nt])[0] if cross else None
+            kq, kt = om.filter_numpy(oi, od, 0.8, rev_idx)
+            assert n == len(kq), (b, cross)
+            assert np.array_equal(out["keep_q"][b, :n].cpu().numpy(), kq), (b, cross)
+            assert np.array_equal(out["keep_t"][b, :n].cpu().numpy(), kt), (b, cross)

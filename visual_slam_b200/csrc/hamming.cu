@@ -60,9 +60,10 @@ __device__ __forceinline__ uint32_t hamming256(const uint32_t (&q)[8], const uin
 
 template <int THREADS, int QPT, int TT, bool CSA, bool REV>
 __global__ void __launch_bounds__(THREADS)
-hamming_knn2_kernel(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ t, int nt,
+hamming_knn2_kernel(const uint8_t* __restrict__ q, int nq_stride, const uint8_t* __restrict__ t, int nt_stride,
                     int32_t* __restrict__ idx, int32_t* __restrict__ dist,
-                    uint32_t* __restrict__ rev_key) {
+                    uint32_t* __restrict__ rev_key, const int32_t* __restrict__ nq_arr,
+                    const int32_t* __restrict__ nt_arr) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   auto tile = [&](int b) { return reinterpret_cast<uint4*>(smem_raw + (size_t)b * TT * 32); };
   uint32_t* rev_s = reinterpret_cast<uint32_t*>(smem_raw + (size_t)2 * TT * 32);
@@ -72,9 +73,23 @@ hamming_knn2_kernel(const uint8_t* __restrict__ q, int nq, const uint8_t* __rest
   const int lane = tid & 31;
   const int pair = blockIdx.y;
   const int q_base = blockIdx.x * (THREADS * QPT);
-  const uint8_t* qp = q + (size_t)pair * nq * 32;
-  const uint8_t* tp = t + (size_t)pair * nt * 32;
+  const uint8_t* qp = q + (size_t)pair * nq_stride * 32;
+  const uint8_t* tp = t + (size_t)pair * nt_stride * 32;
+  // ragged batches: rows [n, stride) of a pair are padding (per-pair counts from the feature extractor)
+  const int nq = nq_arr ? min(max(nq_arr[pair], 0), nq_stride) : nq_stride;
+  const int nt = nt_arr ? min(max(nt_arr[pair], 0), nt_stride) : nt_stride;
 
+  if (q_base >= nq) {  // a CTA of padding queries only (ragged batch): nothing to match
+#pragma unroll
+    for (int j = 0; j < QPT; ++j) {
+      const int qi = q_base + j * THREADS + tid;
+      if (qi < nq_stride) {
+        reinterpret_cast<int2*>(idx)[(size_t)pair * nq_stride + qi] = make_int2(-1, -1);
+        reinterpret_cast<int2*>(dist)[(size_t)pair * nq_stride + qi] = make_int2(-1, -1);
+      }
+    }
+    return;
+  }
   const int n_tiles = (nt + TT - 1) / TT;
   if (tid == 0) {
     mbar_init(&bars[0], 1);
@@ -151,7 +166,7 @@ hamming_knn2_kernel(const uint8_t* __restrict__ q, int nq, const uint8_t* __rest
       for (int i = tid; i < rows; i += THREADS) {
         uint32_t k = rev_s[i];
         rev_s[i] = 0xFFFFFFFFu;
-        if (k < kInvalidQ) atomicMin(&rev_key[(size_t)pair * nt + t0 + i], k);
+        if (k < kInvalidQ) atomicMin(&rev_key[(size_t)pair * nt_stride + t0 + i], k);
       }
       __syncthreads();
     }
@@ -160,13 +175,14 @@ hamming_knn2_kernel(const uint8_t* __restrict__ q, int nq, const uint8_t* __rest
 #pragma unroll
   for (int j = 0; j < QPT; ++j) {
     int qi = q_base + j * THREADS + tid;
-    if (qi < nq) {
+    if (qi < nq_stride) {
+      if (qi >= nq) b1[j] = b2[j] = 0xFFFFFFFFu;   // padding query: no match
       int2 oi, od;
       oi.x = (b1[j] == 0xFFFFFFFFu) ? -1 : (int)(b1[j] & kIdxMask);
       od.x = (b1[j] == 0xFFFFFFFFu) ? -1 : (int)(b1[j] >> kKeyShift);
       oi.y = (b2[j] == 0xFFFFFFFFu) ? -1 : (int)(b2[j] & kIdxMask);
       od.y = (b2[j] == 0xFFFFFFFFu) ? -1 : (int)(b2[j] >> kKeyShift);
-      size_t o = (size_t)pair * nq + qi;
+      size_t o = (size_t)pair * nq_stride + qi;
       reinterpret_cast<int2*>(idx)[o] = oi;
       reinterpret_cast<int2*>(dist)[o] = od;
     }
@@ -247,18 +263,19 @@ __global__ void __launch_bounds__(256) popc_probe_kernel(int iters, uint32_t see
 
 template <int THREADS, int QPT, int TT, bool CSA>
 static int launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
-                       int32_t* dist, uint32_t* rev_key, int batch, cudaStream_t st) {
+                       int32_t* dist, uint32_t* rev_key, int batch, cudaStream_t st,
+                       const int32_t* nq_arr = nullptr, const int32_t* nt_arr = nullptr) {
   dim3 grid((nq + THREADS * QPT - 1) / (THREADS * QPT), batch);
   if (rev_key) {
     size_t smem = (size_t)2 * TT * 32 + TT * 4 + 16;
     auto k = hamming_knn2_kernel<THREADS, QPT, TT, CSA, true>;
     VSLAM_CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, THREADS, smem, st>>>(q, nq, t, nt, idx, dist, rev_key);
+    k<<<grid, THREADS, smem, st>>>(q, nq, t, nt, idx, dist, rev_key, nq_arr, nt_arr);
   } else {
     size_t smem = (size_t)2 * TT * 32 + 16;
     auto k = hamming_knn2_kernel<THREADS, QPT, TT, CSA, false>;
     VSLAM_CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, THREADS, smem, st>>>(q, nq, t, nt, idx, dist, rev_key);
+    k<<<grid, THREADS, smem, st>>>(q, nq, t, nt, idx, dist, rev_key, nq_arr, nt_arr);
   }
   return check_launch("hamming_knn2_kernel");
 }
@@ -271,8 +288,9 @@ using namespace vslam;
 static int g_variant = 0;
 extern "C" int vslam_hamming_set_variant(int v) { g_variant = v; return VSLAM_OK; }
 
-extern "C" int vslam_hamming_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
-                                  int32_t* dist, uint32_t* rev_key, int batch, void* stream) {
+static int hamming_knn2_impl(const uint8_t* q, int nq, const int32_t* nq_arr, const uint8_t* t, int nt,
+                            const int32_t* nt_arr, int32_t* idx, int32_t* dist, uint32_t* rev_key, int batch,
+                            void* stream) {
   if (nq < 0 || nt < 0 || batch < 0) return VSLAM_ERR_BAD_ARG;
   if (nq > VSLAM_HAMMING_MAX_N || nt > VSLAM_HAMMING_MAX_N) return VSLAM_ERR_BAD_ARG;
   if (batch == 0 || nq == 0) return VSLAM_OK;
@@ -291,14 +309,26 @@ extern "C" int vslam_hamming_knn2(const uint8_t* q, int nq, const uint8_t* t, in
     if (rc) return rc;
   }
   switch (g_variant) {
-    case 1: return launch_knn2<128, 4, 512, false>(q, nq, t, nt, idx, dist, rev_key, batch, st);
-    case 2: return launch_knn2<256, 4, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st);
-    case 3: return launch_knn2<128, 8, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st);
-    case 4: return launch_knn2<128, 2, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st);
-    case 5: return launch_knn2<256, 2, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st);
-    case 6: return launch_knn2<128, 4, 1024, true>(q, nq, t, nt, idx, dist, rev_key, batch, st);
-    default: return launch_knn2<128, 4, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st);
+    case 1: return launch_knn2<128, 4, 512, false>(q, nq, t, nt, idx, dist, rev_key, batch, st, nq_arr, nt_arr);
+    case 2: return launch_knn2<256, 4, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st, nq_arr, nt_arr);
+    case 3: return launch_knn2<128, 8, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st, nq_arr, nt_arr);
+    case 4: return launch_knn2<128, 2, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st, nq_arr, nt_arr);
+    case 5: return launch_knn2<256, 2, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st, nq_arr, nt_arr);
+    case 6: return launch_knn2<128, 4, 1024, true>(q, nq, t, nt, idx, dist, rev_key, batch, st, nq_arr, nt_arr);
+    default: return launch_knn2<128, 4, 512, true>(q, nq, t, nt, idx, dist, rev_key, batch, st, nq_arr, nt_arr);
   }
+}
+
+extern "C" int vslam_hamming_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
+                                  int32_t* dist, uint32_t* rev_key, int batch, void* stream) {
+  return hamming_knn2_impl(q, nq, nullptr, t, nt, nullptr, idx, dist, rev_key, batch, stream);
+}
+
+extern "C" int vslam_hamming_knn2_ragged(const uint8_t* q, int nq_stride, const int32_t* nq_arr, const uint8_t* t,
+                                         int nt_stride, const int32_t* nt_arr, int32_t* idx, int32_t* dist,
+                                         uint32_t* rev_key, int batch, void* stream) {
+  if (!nq_arr || !nt_arr) return VSLAM_ERR_BAD_ARG;
+  return hamming_knn2_impl(q, nq_stride, nq_arr, t, nt_stride, nt_arr, idx, dist, rev_key, batch, stream);
 }
 
 extern "C" int vslam_match_filter(const int32_t* idx, const int32_t* dist, const uint32_t* rev_key,

@@ -158,3 +158,16 @@ class FeatureExtractor:
             raise _cabi.VslamError("feature extraction: internal list overflow")
         n = int(o["n_kp"][0])
         return o["kp"][0, :n].cpu().numpy(), o["desc"][0, :n].cpu().numpy()
+
+
+def frontend_batch(frames_a, frames_b, ratio=0.8, cross_check=False, max_corners=3000, quality=0.01,
+                   min_distance=7.0):
+    """The per-frame front end of the reference's loop (src/v2/main.py:96,185: compute_features on both frames,
+    then match_features) for a batch of frame pairs, device-resident throughout: frames (B, H, W, 3) uint8 CUDA
+    -> key points + descriptors of both -> ragged kNN-2 + ratio (+ cross-check).  Returns the two feature dicts
+    and the match dict (keep_q / keep_t index the key points of frames_a / frames_b; n_keep per pair)."""
+    from .matching import match_batch
+    fa = extract_features_batch(frames_a, max_corners, quality, min_distance)
+    fb = extract_features_batch(frames_b, max_corners, quality, min_distance)
+    m = match_batch(fa["desc"], fb["desc"], ratio, cross_check, n_q=fa["n_kp"], n_t=fb["n_kp"])
+    return fa, fb, m

@@ -16,8 +16,17 @@ def _require_cuda():
         raise _cabi.VslamError("visual_slam_b200 needs a CUDA device (no CPU fallback)")
 
 
-def knn2_batch(q, t, want_rev=True):
-    """q: uint8 cuda [B, nq, 32]; t: uint8 cuda [B, nt, 32].
+def _counts(n, B, limit, device, what):
+    if n is None:
+        return None
+    if n.dtype != torch.int32 or not n.is_cuda or n.shape != (B,):
+        raise ValueError("%s must be an int32 CUDA tensor of shape (batch,)" % what)
+    return n.contiguous()
+
+
+def knn2_batch(q, t, want_rev=True, n_q=None, n_t=None):
+    """q: uint8 cuda [B, nq, 32]; t: uint8 cuda [B, nt, 32].  n_q / n_t (int32 cuda [B], both or neither): real
+    rows per pair of a ragged batch, the rest is padding (never matches: idx / dist -1).
 
     Returns (idx int32 [B,nq,2], dist int32 [B,nq,2], rev_key uint32-as-int32 [B,nt] or None),
     ordered exactly like cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) (frame.py:23)."""
@@ -34,10 +43,18 @@ def knn2_batch(q, t, want_rev=True):
     idx = torch.empty((B, nq, 2), dtype=torch.int32, device=q.device)
     dist = torch.empty((B, nq, 2), dtype=torch.int32, device=q.device)
     rev = torch.empty((B, nt), dtype=torch.int32, device=q.device) if want_rev else None
+    n_q, n_t = _counts(n_q, B, nq, q.device, "n_q"), _counts(n_t, B, nt, q.device, "n_t")
+    if (n_q is None) != (n_t is None):
+        raise ValueError("give both n_q and n_t, or neither")
     with torch.cuda.device(q.device):
-        _cabi.check(_cabi.lib().vslam_hamming_knn2(
-            _cabi.ptr(q), nq, _cabi.ptr(t), nt, _cabi.ptr(idx), _cabi.ptr(dist), _cabi.ptr(rev),
-            B, _cabi.stream_ptr()))
+        if n_q is None:
+            _cabi.check(_cabi.lib().vslam_hamming_knn2(
+                _cabi.ptr(q), nq, _cabi.ptr(t), nt, _cabi.ptr(idx), _cabi.ptr(dist), _cabi.ptr(rev),
+                B, _cabi.stream_ptr()))
+        else:
+            _cabi.check(_cabi.lib().vslam_hamming_knn2_ragged(
+                _cabi.ptr(q), nq, _cabi.ptr(n_q), _cabi.ptr(t), nt, _cabi.ptr(n_t), _cabi.ptr(idx), _cabi.ptr(dist),
+                _cabi.ptr(rev), B, _cabi.stream_ptr()))
     return idx, dist, rev
 
 
@@ -57,9 +74,10 @@ def filter_batch(idx, dist, rev, nt, ratio=0.8, cross_check=False):
     return keep_q, keep_t, n_keep
 
 
-def match_batch(q, t, ratio=0.8, cross_check=False):
-    """Batched kNN-2 + ratio (+ cross-check).  Returns a dict of device tensors."""
-    idx, dist, rev = knn2_batch(q, t, want_rev=cross_check)
+def match_batch(q, t, ratio=0.8, cross_check=False, n_q=None, n_t=None):
+    """Batched kNN-2 + ratio (+ cross-check).  Returns a dict of device tensors.  n_q / n_t: per-pair row counts of a
+    ragged batch (e.g. the n_kp of features.extract_features_batch)."""
+    idx, dist, rev = knn2_batch(q, t, want_rev=cross_check, n_q=n_q, n_t=n_t)
     keep_q, keep_t, n_keep = filter_batch(idx, dist, rev, t.shape[1], ratio, cross_check)
     return {"idx": idx, "dist": dist, "rev_key": rev, "keep_q": keep_q, "keep_t": keep_t,
             "n_keep": n_keep}
