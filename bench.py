@@ -266,6 +266,24 @@ def features_figures(torch, batch=64, steps=5, dist=None, world=1, rank=0):
     # blur written 1 (bytes per pixel); key points + descriptors 40 B each
     alg = H * W * 16 + int(n_kp.mean()) * 40
     cpu = cpu_features(host, 4.0) if world == 1 else None
+    frontend = None
+    if world == 1 and batch >= 2:
+        # the loop's front end from pixels (main.py:96,185): features of both frames of a pair + ragged matching
+        from visual_slam_b200.features import frontend_batch
+        half = batch // 2
+        fa_, fb_ = dev[:half], dev[half:2 * half]
+        for _ in range(2):
+            frontend_batch(fa_, fb_)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            _, _, mm = frontend_batch(fa_, fb_)
+        e1.record()
+        torch.cuda.synchronize()
+        fms = e0.elapsed_time(e1) / steps
+        frontend = {"frame_pairs_per_s": half / (fms * 1e-3), "ms_per_batch": fms, "pairs": half,
+                    "matches_per_pair": float(mm["n_keep"].float().mean().item()), "gpu_launches_per_step": 16,
+                    "what": "extract_features_batch x2 + vslam_hamming_knn2_ragged + ratio filter, device-resident"}
     return {"frames_per_s": world * batch / (ms * 1e-3), "ms_per_batch": ms, "batch_per_gpu": batch, "n_gpus": world,
             "scaling": "weak (frames sharded by rank, NCCL all_gather of the key-point counts)", "height": H, "width": W,
             "keypoints_per_frame": float(n_kp.mean()),
@@ -274,7 +292,7 @@ def features_figures(torch, batch=64, steps=5, dist=None, world=1, rank=0):
             "pipeline -> D2H, 3 chunks on two streams; PCIe-bound)",
             "algorithmic_bytes_per_frame": alg, "algorithmic_gbs_per_gpu": batch * alg / (ms * 1e-3) / 1e9,
             "gpu_launches_per_step": 7, "data": "synthetic block-texture frames (synth.frames), 3000-corner cap binds",
-            "cpu_reference": cpu}
+            "cpu_reference": cpu, "frontend": frontend}
 
 
 def tracking_figures(torch, dist, world, rank, dev, steps=3):
