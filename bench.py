@@ -272,12 +272,13 @@ def features_figures(torch, batch=64, steps=5, dist=None, world=1, rank=0):
         from visual_slam_b200.features import frontend_batch
         half = batch // 2
         fa_, fb_ = dev[:half], dev[half:2 * half]
+        fbufs = (FeatureBuffers(half, H, W, device=dev.device), FeatureBuffers(half, H, W, device=dev.device))
         for _ in range(2):
-            frontend_batch(fa_, fb_)
+            frontend_batch(fa_, fb_, buffers=fbufs)
         torch.cuda.synchronize()
         e0.record()
         for _ in range(steps):
-            _, _, mm = frontend_batch(fa_, fb_)
+            _, _, mm = frontend_batch(fa_, fb_, buffers=fbufs)
         e1.record()
         torch.cuda.synchronize()
         fms = e0.elapsed_time(e1) / steps

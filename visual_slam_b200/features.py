@@ -147,13 +147,17 @@ class FeatureExtractor:
     def __init__(self, device="cuda", max_corners=3000, quality=0.01, min_distance=7):
         self.device = device
         self.max_corners, self.quality, self.min_distance = max_corners, quality, min_distance
+        self._buffers = {}   # frame shape -> FeatureBuffers (the reference calls this once per frame of one camera)
 
     def compute_features(self, img):
         img = np.asarray(img)
         if img.dtype != np.uint8 or img.ndim != 3 or img.shape[2] != 3:
             raise ValueError("img must be a uint8 array of shape (H, W, 3) (cv2.imread layout)")
+        key = img.shape[:2]
+        if key not in self._buffers:
+            self._buffers[key] = FeatureBuffers(1, key[0], key[1], self.max_corners, self.min_distance, self.device)
         o = extract_features_batch(torch.from_numpy(np.ascontiguousarray(img))[None].to(self.device),
-                                   self.max_corners, self.quality, self.min_distance)
+                                   self.max_corners, self.quality, self.min_distance, buffers=self._buffers[key])
         if int(o["status"][0]) != 0:
             raise _cabi.VslamError("feature extraction: internal list overflow")
         n = int(o["n_kp"][0])
@@ -161,13 +165,14 @@ class FeatureExtractor:
 
 
 def frontend_batch(frames_a, frames_b, ratio=0.8, cross_check=False, max_corners=3000, quality=0.01,
-                   min_distance=7.0):
+                   min_distance=7.0, buffers=(None, None)):
     """The per-frame front end of the reference's loop (src/v2/main.py:96,185: compute_features on both frames,
     then match_features) for a batch of frame pairs, device-resident throughout: frames (B, H, W, 3) uint8 CUDA
     -> key points + descriptors of both -> ragged kNN-2 + ratio (+ cross-check).  Returns the two feature dicts
-    and the match dict (keep_q / keep_t index the key points of frames_a / frames_b; n_keep per pair)."""
+    and the match dict (keep_q / keep_t index the key points of frames_a / frames_b; n_keep per pair).
+    `buffers`: two FeatureBuffers (one per side) to make the feature stage allocation-free."""
     from .matching import match_batch
-    fa = extract_features_batch(frames_a, max_corners, quality, min_distance)
-    fb = extract_features_batch(frames_b, max_corners, quality, min_distance)
+    fa = extract_features_batch(frames_a, max_corners, quality, min_distance, buffers=buffers[0])
+    fb = extract_features_batch(frames_b, max_corners, quality, min_distance, buffers=buffers[1])
     m = match_batch(fa["desc"], fb["desc"], ratio, cross_check, n_q=fa["n_kp"], n_t=fb["n_kp"])
     return fa, fb, m
