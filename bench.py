@@ -149,6 +149,42 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def cpu_ba_restatement():
+    """the NumPy/SciPy restatement of the reference optimiser's semantics on C3, timed on the host.
+    It is NOT g2o (absent from the image); a reported baseline only."""
+    from oracle import ba as oba
+    from visual_slam_b200.ba_problem import synthetic_ba
+    p = synthetic_ba(n_cams=10, n_pts=5000, obs_per_pt=6.0, seed=0)
+    t0 = time.perf_counter()
+    h = oba.optimize(p, 10)
+    el = time.perf_counter() - t0
+    return {"lm_iters_per_s": h["iterations"] / el, "seconds": el, "iterations": h["iterations"],
+            "final_cost": h["final_cost"], "cores": os.cpu_count(),
+            "kind": "port: oracle/ba.py, NumPy/SciPy restatement of g2o SBA + Levenberg (NOT g2o), C3"}
+
+
+def cpu_pnp(seconds_budget):
+    """the reference's own pose call, cv2.solvePnPRansac(useExtrinsicGuess=True) (main.py:196-197),
+    on C5-style correspondences, one pair after the other on the host."""
+    import cv2
+    from visual_slam_b200 import synth
+    sets = [synth.tracking_pair(s, 2048) for s in range(4)]
+    fx, fy, cx, cy = synth.ICL_K
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1.0]])
+    t0, n = time.perf_counter(), 0
+    while True:
+        X, uv = sets[n % 4][0], sets[n % 4][1]
+        cv2.solvePnPRansac(objectPoints=X.reshape(-1, 1, 3), imagePoints=uv.reshape(-1, 1, 2), cameraMatrix=K,
+                           distCoeffs=np.array([]), rvec=np.zeros((3, 1)), tvec=np.zeros((3, 1)),
+                           useExtrinsicGuess=True)
+        n += 1
+        el = time.perf_counter() - t0
+        if el > seconds_budget:
+            break
+    return {"pairs_per_s": n / el, "pairs": n, "seconds": el, "cores": os.cpu_count(),
+            "kind": "reference: cv2.solvePnPRansac, 2048 correspondences per pair, default 100 iterations"}
+
+
 def ba_figures(torch):
     """BA LM iterations/s at C3 (and C4 when memory/time allow), device-timed with CUDA events,
     plus the linearisation roofline at C4."""
@@ -553,8 +589,11 @@ def run_gpu(args):
         line["cpu_baseline"] = cpu
         if not args.skip_features:
             features = features_figures(torch)
+        if tracking:
+            tracking["cpu_pnp"] = cpu_pnp(3.0)
         if not args.skip_ba:
             ba = ba_figures(torch)
+            ba["cpu_restatement_c3"] = cpu_ba_restatement()
             line["ba"] = ba
             hbm = peaks.get("hbm_gbs", 6650.0)
             line["roofline_ba"] = {"bound": "hbm", "kernel": "ba_linearize_kernel<false> (fused linearisation, C4)",
