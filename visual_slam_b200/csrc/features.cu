@@ -334,9 +334,11 @@ feat_eig_walk_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __re
 // pixel: 0 none/dropped, 1 undecided, 2 kept); windows that cross a band edge read the neighbour CTA's band
 // through distributed shared memory; the termination vote is a DSMEM read of eight flags.
 constexpr int kSupCtas = 8;
-constexpr int kSupThreads = 512;
+constexpr int kSupThreads = 512;        // large batches: four CTAs per SM, every cluster of the batch resident
+constexpr int kSupThreadsSmall = 1024;  // small batches: the SMs are idle anyway, halve the passes per round
 
-__global__ void __cluster_dims__(kSupCtas, 1, 1) __launch_bounds__(kSupThreads, 4)
+template <int THREADS>
+__global__ void __cluster_dims__(kSupCtas, 1, 1) __launch_bounds__(THREADS, 2048 / THREADS)
 feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, double quality, int radius, int d2,
                    int* __restrict__ lists, unsigned long long* acc_key, int acc_cap, int* counters) {
   cg::cluster_group cluster = cg::this_cluster();
@@ -362,7 +364,7 @@ feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, 
   unsigned* bandw = reinterpret_cast<unsigned*>(band);
   const bool vec = (W & 3) == 0;
   const int Wq = Wp / 4;
-  for (int r = threadIdx.x >> 5; r < Hb; r += kSupThreads / 32)
+  for (int r = threadIdx.x >> 5; r < Hb; r += THREADS / 32)
    for (int xq = threadIdx.x & 31; xq < Wq; xq += 32) {
     const int x = xq * 4, y = y_lo + r;
     unsigned word = 0;
@@ -406,7 +408,7 @@ feat_select_kernel(const float* __restrict__ eig, int H, int W, int Hb, int Wp, 
     const int n = n_list[src];
     const int* in = list[src];
     int* outl = list[dst];
-    for (int i0 = 0; i0 < n; i0 += kSupThreads) {   // uniform trip count: the ballots below need whole warps
+    for (int i0 = 0; i0 < n; i0 += THREADS) {   // uniform trip count: the ballots below need whole warps
       const int i = i0 + threadIdx.x;
       bool wait = false;
       int idx = 0;
@@ -753,11 +755,18 @@ extern "C" int vslam_extract_features(const uint8_t* img, int batch, int H, int 
     while ((radius + 1) * (radius + 1) < d2) ++radius;
   }
   // (set on every call: the attribute is per device and a process may drive several)
+  const bool small_batch = (long long)batch * kSupCtas <= sm_count();
+  auto select_small = feat_select_kernel<kSupThreadsSmall>;
+  auto select_large = feat_select_kernel<kSupThreads>;
   if (L.band_bytes > 48 * 1024)
-    VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)kMaxBandBytes));
-  feat_select_kernel<<<dim3(kSupCtas, batch), kSupThreads, L.band_bytes, st>>>(
-      eig, H, W, L.Hb, L.Wp, quality, radius, d2, reinterpret_cast<int*>(ws + L.lists), acc, L.acc_cap, counters);
+    VSLAM_CUDA_TRY(cudaFuncSetAttribute(small_batch ? select_small : select_large,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxBandBytes));
+  if (small_batch)
+    select_small<<<dim3(kSupCtas, batch), kSupThreadsSmall, L.band_bytes, st>>>(
+        eig, H, W, L.Hb, L.Wp, quality, radius, d2, reinterpret_cast<int*>(ws + L.lists), acc, L.acc_cap, counters);
+  else
+    select_large<<<dim3(kSupCtas, batch), kSupThreads, L.band_bytes, st>>>(
+        eig, H, W, L.Hb, L.Wp, quality, radius, d2, reinterpret_cast<int*>(ws + L.lists), acc, L.acc_cap, counters);
   VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)(kSortMax * sizeof(unsigned long long))));
   feat_order_kernel<<<batch, kSortThreads, kSortMax * sizeof(unsigned long long), st>>>(
