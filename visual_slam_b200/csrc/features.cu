@@ -90,7 +90,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 __global__ void __launch_bounds__(kEigThreads)
 feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restrict__ eig, int* __restrict__ counters) {
   __shared__ double ring[kEigRing][3][kEigT];
-  __shared__ float prod[kEigProd][3][kEigT];
+  __shared__ double prod[kEigProd][3][kEigT];  // float products, widened once
   __shared__ uint64_t full[kEigRing], empty[kEigRing];
   const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int c0 = blockIdx.x * (kEigT - 2) - 1;  // image column of strip index 0
@@ -144,7 +144,7 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
 #pragma unroll
       for (int h = 0; h < 2; ++h)
 #pragma unroll
-        for (int k = 0; k < 3; ++k) prod[w][k][h * 32 + lane] = p[h][k];
+        for (int k = 0; k < 3; ++k) prod[w][k][h * 32 + lane] = (double)p[h][k];
       __syncwarp();
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
@@ -152,7 +152,7 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
         if (i >= 1 && i <= kEigT - 2) {
 #pragma unroll
           for (int k = 0; k < 3; ++k)
-            ring[slot][k][i] = ((double)prod[w][k][i - 1] + (double)prod[w][k][i]) + (double)prod[w][k][i + 1];
+            ring[slot][k][i] = (prod[w][k][i - 1] + prod[w][k][i]) + prod[w][k][i + 1];
         }
       }
       __syncwarp();
@@ -221,7 +221,7 @@ constexpr int kEigChunk = 8;
 
 __global__ void __launch_bounds__(kEigT)
 feat_eig_walk_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restrict__ eig, int* __restrict__ counters) {
-  __shared__ float sm[2][3][kEigT];
+  __shared__ double sm[2][3][kEigT];  // the float products, already widened (one conversion per value, not three)
   const int b = blockIdx.y, tid = threadIdx.x;
   const int c = blockIdx.x * (kEigT - 2) + tid - 1;
   const bool owner = tid >= 1 && tid <= kEigT - 2 && c < W;
@@ -282,15 +282,16 @@ feat_eig_walk_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __re
     const float dx = __fmaf_rn(__fadd_rn(rx0, rx2), s1, __fmul_rn(rx1, s2));
     const float dy = __fsub_rn(R2, R0);
     const int buf = r & 1;
-    sm[buf][0][tid] = __fmul_rn(dx, dx);
-    sm[buf][1][tid] = __fmul_rn(dx, dy);
-    sm[buf][2][tid] = __fmul_rn(dy, dy);
+    const double pxx = (double)__fmul_rn(dx, dx), pxy = (double)__fmul_rn(dx, dy), pyy = (double)__fmul_rn(dy, dy);
+    sm[buf][0][tid] = pxx;
+    sm[buf][1][tid] = pxy;
+    sm[buf][2][tid] = pyy;
     __syncthreads();
     if (owner) {
       double rsc[3];
 #pragma unroll
       for (int k = 0; k < 3; ++k)
-        rsc[k] = ((double)sm[buf][k][tid - 1] + (double)sm[buf][k][tid]) + (double)sm[buf][k][tid + 1];
+        rsc[k] = (sm[buf][k][tid - 1] + (k == 0 ? pxx : k == 1 ? pxy : pyy)) + sm[buf][k][tid + 1];
       if (r == 1) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) sum[k] = (0.0 + rsc[k]) + rsb[k];  // padded rows -1 (= row 1) and 0
