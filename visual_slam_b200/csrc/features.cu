@@ -77,7 +77,8 @@ feat_gray_kernel(const uint8_t* __restrict__ img, long long n_px, int px_per_img
 // rows of one column cannot be split -- but everything up to the row sums can.  Warp-specialised: a CTA owns a
 // strip of 62 columns; fourteen PRODUCER warps take the rows round-robin and turn them into float64 row sums in a
 // 14-slot shared-memory ring (full/empty mbarriers per slot); two CONSUMER warps (one thread per column) walk
-// down the frame doing only the running sum and the eigenvalue formula.
+// down the frame doing ONLY the running sum (six dependent float64 adds per row) and leave the column sums in the
+// slot; the slot's producer turns them into eigenvalues before it reuses the slot.
 constexpr int kEigT = 64;       // strip width including one halo column either side
 constexpr int kEigProd = 14;    // producer warps
 constexpr int kEigRing = 14;    // ring slots (a multiple of kEigProd)
@@ -85,6 +86,15 @@ constexpr int kEigThreads = (2 + kEigProd) * 32;
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// eig = (a + c) - sqrt((a - c)^2 + b^2) with a = A/2, c = C/2 from the three float64 column sums of one pixel
+__device__ __forceinline__ float min_eig_from_sums(double sA, double sB, double sC) {
+  const float A = (float)sA, B = (float)sB, C = (float)sC;
+  const float a = __fmul_rn(A, 0.5f), cq = __fmul_rn(C, 0.5f);
+  float t = __fsub_rn(a, cq);
+  t = __fadd_rn(__fmul_rn(t, t), __fmul_rn(B, B));
+  return __fsub_rn(__fadd_rn(a, cq), __fsqrt_rn(t));
 }
 
 __global__ void __launch_bounds__(kEigThreads)
@@ -116,6 +126,23 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
       // scalar tail (oracle/features.py: row_vector_width)
       vec_col[h] = cc[h] < (W / 32) * 32;
     }
+    float* out = eig + (size_t)b * H * W;
+    float vmax = -INFINITY;
+    // the consumers leave the float64 column sums of a row in its ring slot; the slot's producer turns them into
+    // eigenvalues (output row = ring row - 1) before it reuses the slot, so the serial consumer chain stays short
+    auto finish = [&](int slot, int row) {
+      if (row < 1) return;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int i = h * 32 + lane, c = c0 + i;
+        if (i >= 1 && i <= kEigT - 2 && c < W) {
+          const float e = min_eig_from_sums(ring[slot][0][i], ring[slot][1][i], ring[slot][2][i]);
+          out[(size_t)(row - 1) * W + c] = e;
+          vmax = fmaxf(vmax, e);
+        }
+      }
+    };
+    int last_row = -1;
     for (int r = w; r < H; r += kEigProd) {
       const int slot = r % kEigRing, use = r / kEigRing;
       const uint8_t* gm_ = g + (size_t)reflect101(r - 1, H) * W;
@@ -141,6 +168,8 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
         p[h][0] = __fmul_rn(dx, dx); p[h][1] = __fmul_rn(dx, dy); p[h][2] = __fmul_rn(dy, dy);
       }
       mbar_wait(&empty[slot], (uint32_t)((use & 1) ^ 1));  // the consumers are done with the slot's previous row
+      if (use > 0) finish(slot, r - kEigRing);
+      __syncwarp();
 #pragma unroll
       for (int h = 0; h < 2; ++h)
 #pragma unroll
@@ -157,7 +186,15 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&full[slot]);
+      last_row = r;
     }
+    if (last_row >= 0) {  // the last row of this warp's slot
+      mbar_wait(&empty[last_row % kEigRing], (uint32_t)((last_row / kEigRing) & 1));
+      finish(last_row % kEigRing, last_row);
+    }
+    int pkey = float_key(vmax);
+    pkey = __reduce_max_sync(0xffffffffu, pkey);
+    if (lane == 0) atomicMax(&counters[4 * b + 0], pkey);
     return;
   }
 
@@ -167,46 +204,38 @@ feat_eig_kernel(const uint8_t* __restrict__ gray, int H, int W, float* __restric
   float* out = eig + (size_t)b * H * W;
   double rsa[3] = {0, 0, 0}, rsb[3] = {0, 0, 0}, sum[3] = {0, 0, 0};
   float vmax = -INFINITY;
-  auto emit = [&](int y, const double* s0) {
-    const float A = (float)s0[0], B = (float)s0[1], C = (float)s0[2];
-    const float a = __fmul_rn(A, 0.5f), cq = __fmul_rn(C, 0.5f);
-    float t = __fsub_rn(a, cq);
-    t = __fadd_rn(__fmul_rn(t, t), __fmul_rn(B, B));
-    const float e = __fsub_rn(__fadd_rn(a, cq), __fsqrt_rn(t));
-    out[(size_t)y * W + c] = e;
-    vmax = fmaxf(vmax, e);
-  };
   for (int r = 0; r < H; ++r) {
     const int slot = r % kEigRing, use = r / kEigRing;
     mbar_wait(&full[slot], (uint32_t)(use & 1));
-    double rsc[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) rsc[k] = ring[slot][k][tid];
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[slot]);
     if (owner) {
+      double rsc[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) rsc[k] = ring[slot][k][tid];
       if (r == 1) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) sum[k] = (0.0 + rsc[k]) + rsb[k];  // padded rows -1 (= row 1) and 0
       }
       if (r >= 1) {
-        double s0[3];
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-          s0[k] = sum[k] + rsc[k];
-          sum[k] = s0[k] - (r == 1 ? rsc[k] : rsa[k]);  // minus row y-1 (row -1 reflects to row 1)
+          const double s0 = sum[k] + rsc[k];
+          sum[k] = s0 - (r == 1 ? rsc[k] : rsa[k]);  // minus row y-1 (row -1 reflects to row 1)
+          ring[slot][k][tid] = s0;                    // column sums of output row r-1, finished by the producer
         }
-        emit(r - 1, s0);
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k) { rsa[k] = rsb[k]; rsb[k] = rsc[k]; }
     }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[slot]);
   }
   if (owner) {  // last row: row H reflects to row H-2, which is rsa after the final shift
     double s0[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) s0[k] = sum[k] + rsa[k];
-    emit(H - 1, s0);
+    const float e = min_eig_from_sums(s0[0], s0[1], s0[2]);
+    out[(size_t)(H - 1) * W + c] = e;
+    vmax = e;
   }
   int key = owner ? float_key(vmax) : INT_MIN;
   key = __reduce_max_sync(0xffffffffu, key);
