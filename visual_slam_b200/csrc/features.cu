@@ -573,6 +573,45 @@ feat_order_kernel(const unsigned long long* __restrict__ acc_key, int acc_cap, i
   }
 }
 
+// Latency variant of the ordering for small batches (the SMs are idle anyway): rank by counting, one key per thread,
+// 64 threads per CTA so that one frame's ~3.5k kept corners spread over ~56 SMs; all keys stream through 8 KB
+// tiles of shared memory (warp-wide broadcast reads).
+constexpr int kCountThreads = 64;
+constexpr int kCountTile = 1024;
+
+__global__ void __launch_bounds__(kCountThreads)
+feat_order_count_kernel(const unsigned long long* __restrict__ acc_key, int acc_cap, int W, int max_corners,
+                        float2* __restrict__ corners, int* __restrict__ n_corners, int* __restrict__ counters) {
+  __shared__ unsigned long long tile[kCountTile];
+  const int b = blockIdx.y;
+  const unsigned long long* acc = acc_key + (size_t)b * acc_cap;
+  const int n_raw = counters[4 * b + 2];
+  const int A = min(n_raw, acc_cap);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (n_raw > acc_cap) counters[4 * b + 3] = 1;
+    n_corners[b] = min(A, max_corners);
+  }
+  if ((int)blockIdx.x * kCountThreads >= A) return;
+  const int i = blockIdx.x * kCountThreads + threadIdx.x;
+  const unsigned long long key = i < A ? acc[i] : 0ull;
+  int h0 = 0, h1 = 0, h2 = 0, h3 = 0;
+  for (int t0 = 0; t0 < A; t0 += kCountTile) {
+    const int m = min(kCountTile, A - t0);
+    __syncthreads();
+    for (int j = threadIdx.x; j < kCountTile; j += kCountThreads) tile[j] = j < m ? acc[t0 + j] : 0ull;
+    __syncthreads();
+#pragma unroll 4
+    for (int j = 0; j < kCountTile; j += 4) {   // padding keys are 0: never greater than a real key
+      h0 += tile[j] > key; h1 += tile[j + 1] > key; h2 += tile[j + 2] > key; h3 += tile[j + 3] > key;
+    }
+  }
+  const int higher = (h0 + h1) + (h2 + h3);
+  if (i < A && higher < max_corners) {
+    const int pix = (int)(key & 0xffffffffu), y = pix / W;
+    corners[(size_t)b * max_corners + higher] = make_float2((float)(pix - y * W), (float)y);
+  }
+}
+
 // ---- K4: the blur ORB applies to its level image ---------------------------------------------------
 // float32 separable 7x7, sigma 2 (taps = cv2.getGaussianKernel(7, 2, CV_32F)), REFLECT_101;
 // rows: s = k0*p0, s = fma(k_i, p_i, s); columns: s = k3*c, s = fma(k_{3+j}, up_j + down_j, s);
@@ -812,10 +851,15 @@ extern "C" int vslam_extract_features(const uint8_t* img, int batch, int H, int 
   else
     select_large<<<dim3(kSupCtas, batch), kSupThreads, L.band_bytes, st>>>(
         eig, H, W, L.Hb, L.Wp, quality, radius, d2, reinterpret_cast<int*>(ws + L.lists), acc, L.acc_cap, counters);
-  VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)(kSortMax * sizeof(unsigned long long))));
-  feat_order_kernel<<<batch, kSortThreads, kSortMax * sizeof(unsigned long long), st>>>(
-      acc, L.acc_cap, W, max_corners, reinterpret_cast<float2*>(corners), n_corners, counters);
+  if (batch <= 4) {   // measured: 27 us against 35 us for one frame, break-even at ~6 frames
+    feat_order_count_kernel<<<dim3((L.acc_cap + kCountThreads - 1) / kCountThreads, batch), kCountThreads, 0, st>>>(
+        acc, L.acc_cap, W, max_corners, reinterpret_cast<float2*>(corners), n_corners, counters);
+  } else {
+    VSLAM_CUDA_TRY(cudaFuncSetAttribute(feat_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)(kSortMax * sizeof(unsigned long long))));
+    feat_order_kernel<<<batch, kSortThreads, kSortMax * sizeof(unsigned long long), st>>>(
+        acc, L.acc_cap, W, max_corners, reinterpret_cast<float2*>(corners), n_corners, counters);
+  }
   feat_border_compact_kernel<<<batch, 1024, 0, st>>>(reinterpret_cast<const float2*>(corners), n_corners,
                                                      max_corners, H, W, reinterpret_cast<float2*>(kp), n_kp);
   feat_orb_kernel<<<dim3((max_corners + kOrbWarps * 4 - 1) / (kOrbWarps * 4), batch), kOrbWarps * 32, 0, st>>>(
