@@ -26,6 +26,7 @@ sys.path.insert(0, ROOT)
 PAIRS_PER_GPU = 1184          # 8 x 148: 4736 CTAs of 512 queries each
 NQ = NT = 2048
 RATIO = 0.8
+PREHEAT_STEPS = 24            # fixed, untimed, before the W warm-up steps (identical on every rank)
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures
 HAMMING_DRAM_BYTES_PER_PAIR = (83026176 + 4331264) / 592.0
 HAMMING_TRAFFIC_SOURCE = "profiles/r1_hamming_knn2_ncu_full.txt (592 pairs per launch, scaled to this launch)"
@@ -100,50 +101,110 @@ def measured_peaks():
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the reference's own path (cv2 BFMatcher + the ratio loop of frame.py:30-42), host cores
 # ------------------------------------------------------------------------------------------------
-def cpu_matching(seconds_budget, max_pairs):
+_CPU_PAIRS = None
+
+
+def _cpu_pairs():
+    """The 8 seeded C2 pairs the CPU legs cycle through; generated once, outside every timed loop."""
+    global _CPU_PAIRS
+    if _CPU_PAIRS is None:
+        from visual_slam_b200 import synth
+        _CPU_PAIRS = [synth.descriptors_pair(NQ, NT, seed=b)[:2] for b in range(8)]
+    return _CPU_PAIRS
+
+
+def cpu_matching(seconds_budget, max_pairs, wrapper=True, threads=None):
+    """Times the reference's CPU matcher on C2 pairs: cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) alone
+    (wrapper=False) or followed by the ratio loop of frame.py:30-42 (wrapper=True, what match_features does).
+    Data generation and one warm-up match happen before the clock starts; only timed matches are counted."""
     import cv2
     from oracle import matching as om
-    from visual_slam_b200 import synth
-    pairs = [synth.descriptors_pair(NQ, NT, seed=b)[:2] for b in range(8)]
+    pairs = _cpu_pairs()
     kp = np.zeros((NQ, 2), np.float32)
-    om.match_features_cv2(kp, pairs[0][0], kp, pairs[0][1], RATIO)  # warm-up
-    n, t0 = 0, time.perf_counter()
-    while n < max_pairs and time.perf_counter() - t0 < seconds_budget:
-        q, t = pairs[n % 8]
-        om.match_features_cv2(kp, q, kp, t, RATIO)
-        n += 1
-    dt = time.perf_counter() - t0
-    return {"value": n * NQ / dt, "unit": UNIT, "cores": cv2.getNumThreads(), "kind": "port",
-            "sample": "%d frame pairs of the same workload through cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) "
-                      "+ the reference's Python ratio loop (frame.py:30-42 restated), %.1f s, os.cpu_count=%d; "
-                      "no cross-check (the reference has none)" % (n, dt, os.cpu_count()),
+    all_threads = cv2.getNumThreads()
+    if threads is not None:
+        cv2.setNumThreads(threads)
+    try:
+        bf = cv2.BFMatcher(cv2.NORM_HAMMING)
+        run = ((lambda q, t: om.match_features_cv2(kp, q, kp, t, RATIO)) if wrapper
+               else (lambda q, t: bf.knnMatch(q, t, k=2)))
+        run(*pairs[0])                                       # warm-up, untimed
+        n, t0 = 0, time.perf_counter()
+        while n < max_pairs and time.perf_counter() - t0 < seconds_budget:
+            run(*pairs[n % 8])
+            n += 1
+        dt = time.perf_counter() - t0
+        used = cv2.getNumThreads()
+    finally:
+        cv2.setNumThreads(all_threads)
+    return {"value": n * NQ / dt, "unit": UNIT, "cores": used, "kind": "port",
+            "sample": "%d frame pairs of the same workload through cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2)%s, "
+                      "%.1f s, %d cv2 thread(s), os.cpu_count=%d; no cross-check (the reference has none)" % (
+                          n, " + the reference's Python ratio loop (frame.py:30-42 restated)" if wrapper else " alone",
+                          dt, used, os.cpu_count()),
             "pairs": n, "seconds": dt}
 
 
+def cpu_matching_variants():
+    """knnMatch alone and the full wrapper, at all cv2 threads and at one thread."""
+    out = {}
+    for name, wrapper, threads, budget in (("knnmatch_alone_all_threads", False, None, 3.0),
+                                            ("knnmatch_alone_1_thread", False, 1, 3.0),
+                                            ("wrapper_1_thread", True, 1, 3.0)):
+        r = cpu_matching(budget, 4000, wrapper=wrapper, threads=threads)
+        out[name] = {"value": r["value"], "cores": r["cores"], "pairs": r["pairs"], "seconds": r["seconds"],
+                     "ms_per_pair": r["seconds"] / max(r["pairs"], 1) * 1e3}
+    return out
+
+
+REF_PAIRS_PER_STEP = 24
+
+
 def run_reference(args):
+    """--impl reference: the reference's CPU path (cv2 + its ratio loop) on a bounded sample of the workload per
+    step; the timed region holds nothing but the matches that are counted."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    per_step = 24
-    for _ in range(args.warmup):
-        cpu_matching(1e9, 2)
+    import cv2
+    from oracle import matching as om
+    pairs = _cpu_pairs()
+    kp = np.zeros((NQ, 2), np.float32)
+    per_step = REF_PAIRS_PER_STEP
+    for w in range(max(args.warmup, 1)):
+        for i in range(2):
+            q_, t_ = pairs[(2 * w + i) % 8]
+            om.match_features_cv2(kp, q_, kp, t_, RATIO)
+    step_ms = []
     t0 = time.perf_counter()
-    tot_pairs = 0
-    for _ in range(args.steps):
-        r = cpu_matching(1e9, per_step)
-        tot_pairs += r["pairs"]
+    for s in range(args.steps):
+        ts = time.perf_counter()
+        for i in range(per_step):
+            q_, t_ = pairs[(s * per_step + i) % 8]
+            om.match_features_cv2(kp, q_, kp, t_, RATIO)
+        step_ms.append((time.perf_counter() - ts) * 1e3)
     dt = time.perf_counter() - t0
-    value = tot_pairs * NQ / dt
+    value = args.steps * per_step * NQ / dt
+    cores = cv2.getNumThreads()
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "ms_per_step_stats": _stats(step_ms),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-            "data": "synthetic", "config": dict(workload_config(args.gpus), sample_pairs_per_step=per_step),
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": r["cores"], "kind": "port",
-                             "sample": "each step = %d frame pairs of the workload (bounded sample); %s" % (
-                                 per_step, r["sample"])},
+            "data": "synthetic", "config": workload_config(args.gpus),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": "each step = %d frame pairs of the workload (bounded sample of its %d) through "
+                                       "cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) + the reference's Python ratio loop "
+                                       "(frame.py:30-42 restated in oracle/matching.py), %d cv2 threads, os.cpu_count=%d; "
+                                       "inputs generated and one warm-up match done before the clock starts"
+                                       % (per_step, PAIRS_PER_GPU, cores, os.cpu_count())},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def _stats(ms):
+    a = np.asarray(ms, dtype=np.float64)
+    return {"min": float(a.min()), "median": float(np.median(a)), "max": float(a.max()), "n": int(a.size)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -457,26 +518,19 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # Every rank runs the SAME fixed number of steps everywhere below: each step carries an NCCL collective, so no
+    # rank-local measurement may decide how many there are.  PREHEAT untimed steps first (a GPU coming out of idle
+    # needs tens of milliseconds to reach its boost clocks), then the W warm-up steps that were asked for.
     n_warm = max(args.warmup, 3)
-    for _ in range(n_warm):
-        out = step()
-    sync()
-    # keep warming up until the step time has settled (a GPU coming out of idle, or out of a profiler
-    # session, needs tens of milliseconds to reach its boost clocks; three 7 ms steps are not enough):
-    # untimed steps in pairs until two consecutive ones agree within 2 %, at most 120 more
-    prev, best_warm = None, None
-    for _ in range(120):
+    warm_ms = []
+    for i in range(PREHEAT_STEPS + n_warm):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         out = step()
         b.record()
         sync()
-        cur = a.elapsed_time(b)
-        n_warm += 1
-        best_warm = cur if best_warm is None else min(best_warm, cur)
-        if prev is not None and abs(cur - prev) <= 0.02 * prev:
-            break
-        prev = cur
+        warm_ms.append(a.elapsed_time(b))
+    best_warm = min(warm_ms[PREHEAT_STEPS // 2:])
     n_keep_ref = int(out["n_keep"].sum().item())
 
     def timed_region():
@@ -485,13 +539,13 @@ def run_gpu(args):
             sampler.start()
             time.sleep(0.3)
         sync()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        # per-kernel events on the launching stream for the dominant kernel (knn2)
+        # events on the launching stream: e[i] before step i (e[K] after the last), ka/kb around the dominant kernel
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
         k_events = []
         w0 = time.time()
-        e0.record()
         n_keep = None
-        for _ in range(args.steps):
+        for i in range(args.steps):
+            e[i].record()
             ka, kb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ka.record()
             idx, dist_, rev = matching.knn2_batch(q, t, want_rev=True)
@@ -500,19 +554,20 @@ def run_gpu(args):
             if world > 1:
                 dist.all_gather_into_tensor(gathered, n_keep)
             k_events.append((ka, kb))
-        e1.record()
+        e[args.steps].record()
         sync()
         w1 = time.time()
-        ms = e0.elapsed_time(e1)
+        ms = e[0].elapsed_time(e[args.steps])
         tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         clocks = sampler.stop(w0, w1) if rank == 0 else None
-        return float(tmax.item()), clocks, k_events, n_keep
+        step_ms = [e[i].elapsed_time(e[i + 1]) for i in range(args.steps)]
+        return float(tmax.item()), clocks, k_events, n_keep, step_ms
 
-    ms, clocks, k_events, n_keep = timed_region()
-    # a timed region that runs far slower than the settled warm-up steps did (seen once: 5.8x, with
-    # nvidia-smi reporting full clocks and no throttle reason) is re-measured once, and says so
+    ms, clocks, k_events, n_keep, step_ms = timed_region()
+    # a timed region that runs far slower than the settled warm-up steps did (seen once: 5.8x, with nvidia-smi
+    # reporting full clocks and no throttle reason) is re-measured once, and says so; the decision is all-reduced
     slow = torch.tensor([1.0 if ms / args.steps > 1.3 * best_warm else 0.0], device=dev)
     if world > 1:
         dist.all_reduce(slow, op=dist.ReduceOp.MAX)
@@ -522,10 +577,11 @@ def run_gpu(args):
         for _ in range(5):
             step()
         sync()
-        ms, clocks, k_events, n_keep = timed_region()
-    knn_ms = float(np.mean([a.elapsed_time(b) for a, b in k_events]))
+        ms, clocks, k_events, n_keep, step_ms = timed_region()
+    knn_each = [a.elapsed_time(b) for a, b in k_events]
+    knn_ms = float(np.mean(knn_each))
     if rank == 0 and os.environ.get("VSLAM_BENCH_DEBUG"):
-        sys.stderr.write("knn2 ms per step: %s (warm-up steps %d)\n" % ([round(a.elapsed_time(b), 3) for a, b in k_events], n_warm))
+        sys.stderr.write("knn2 ms per step: %s\n" % [round(v, 3) for v in knn_each])
     assert int(n_keep.sum().item()) == n_keep_ref
     value = world * B * NQ * args.steps / (ms * 1e-3)
 
@@ -574,7 +630,10 @@ def run_gpu(args):
                         "(carry-save adder tree) instead of the 8 POPC the yardstick assumes",
                 "kernel_ms": knn_ms, "pair_distances_per_s": B * NQ * NT / (knn_ms * 1e-3)}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": n_warm, "remeasured": remeasured, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "warmup": n_warm, "preheat_steps": PREHEAT_STEPS, "remeasured": remeasured,
+            "ms_per_step": ms / args.steps, "ms_per_step_stats": _stats(step_ms),
+            "kernel_ms_stats": _stats(knn_each), "warmup_ms_stats": _stats(warm_ms[PREHEAT_STEPS:]),
+            "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": workload_config(world), "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": hm.h2d_bytes,
@@ -586,6 +645,7 @@ def run_gpu(args):
     if world == 1:
         cpu = cpu_matching(12.0, 4000)
         cpu.pop("pairs"); cpu.pop("seconds")
+        cpu["variants"] = cpu_matching_variants()
         line["cpu_baseline"] = cpu
         if not args.skip_features:
             features = features_figures(torch)

@@ -62,6 +62,43 @@ def test_incremental_api_and_error_conventions():
     assert np.array_equal(s.GetAll3DPoints()[0], [7, 8, 9])
 
 
+def test_repeated_observation_replaces_the_first_like_point_frames_dict():
+    """Point.frames is a dict keyed by frame id (reference src/v2/point.py:14-46): the last observation of a
+    (point, frame) wins and BA sees ONE edge."""
+    from visual_slam_b200.mapsoa import MapSoA
+    s = MapSoA()
+    s.AddFrame(0, np.eye(4), keyframe=True); s.AddFrame(1, np.eye(4))
+    s.AddPoint3D(5, [0, 0, 2.0]); s.AddPoint3D(6, [1, 0, 2.0])
+    s.AddObservation(5, 0, (1.0, 2.0)); s.AddObservation(6, 0, (9.0, 9.0)); s.AddObservation(5, 1, (3.0, 4.0))
+    v = s._version
+    s.AddObservation(5, 0, (7.0, 8.0))                      # same (point, frame): replaces, no structural change
+    assert s.n_observations == 3 and s._version == v
+    prob = s.problem((1, 1, 0, 0))
+    assert prob.n_obs == 3
+    row = np.nonzero((prob.obs_pt == 0) & (prob.obs_cam == 0))[0]
+    assert len(row) == 1 and np.array_equal(prob.obs_uv[row[0]], [7.0, 8.0])
+    uv, _, _, ids = s.GetImagePointsWithFrameID(0)
+    assert list(ids) == [5, 6] and np.array_equal(uv[0], [7.0, 8.0])
+    assert np.array_equal(s.GetNVisibleFrames(), [2, 1])
+    # the (point, frame) index survives culling: point 6 (one frame) goes, point 5 keeps its rows
+    assert s.DiscardOutlierMapPoints(2) == 1
+    s.AddObservation(5, 1, (30.0, 40.0))
+    assert s.n_observations == 2 and np.array_equal(s.problem((1, 1, 0, 0)).obs_uv[1], [30.0, 40.0])
+
+
+def test_R_to_quat_normalises_like_the_sbacam_constructor():
+    from visual_slam_b200.ba_problem import R_to_quat, quat_to_R
+    rng = np.random.default_rng(3)
+    for _ in range(20):
+        a = rng.normal(size=3); th = np.linalg.norm(a); k = a / th
+        Kx = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+        R = np.eye(3) + np.sin(th) * Kx + (1 - np.cos(th)) * Kx @ Kx
+        q = R_to_quat(R * (1 + 1e-3) + rng.normal(0, 1e-4, (3, 3)))   # scaled, slightly non-orthonormal
+        assert abs(np.linalg.norm(q) - 1) < 1e-15 and q[3] >= 0
+        assert np.abs(quat_to_R(q) - R).max() < 2e-3
+        assert np.abs(quat_to_R(R_to_quat(R)) - R).max() < 1e-14
+
+
 @pytest.mark.gpu
 def test_ba_through_mapsoa_equals_the_drop_in():
     from visual_slam_b200.ba import BundleAdjustment

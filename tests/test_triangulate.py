@@ -80,6 +80,17 @@ def test_batched_ragged_and_empty():
     assert not Xh[-1].any() and not good[-1].any()
 
 
+@pytest.mark.gpu
+def test_no_correspondences_returns_an_empty_array_like_the_reference():
+    """helper_functions.py:281-291 on N = 0 returns np.array([]) reshaped by its caller; the drop-in gives (0, 4)."""
+    from visual_slam_b200.triangulate import triangulate, triangulate_and_filter
+    P = np.hstack([np.eye(3), np.zeros((3, 1))])
+    out = triangulate(P, P, np.zeros((0, 2)), np.zeros((0, 2)))
+    assert out.shape == (0, 4)
+    X3, good = triangulate_and_filter(P, P, P, P, np.zeros((0, 2)), np.zeros((0, 2)))
+    assert X3.shape == (0, 3) and len(good) == 0
+
+
 def test_shape_errors_raise_before_any_device_work():
     from visual_slam_b200.triangulate import triangulate
     import torch

@@ -7,7 +7,9 @@ import numpy as np
 
 
 def R_to_quat(R):
-    """Rotation matrix -> unit quaternion (x, y, z, w), w >= 0 branch of Eigen's conversion."""
+    """Rotation matrix -> UNIT quaternion (x, y, z, w) with w >= 0: Eigen's conversion followed by the
+    normalisation and sign choice g2o's SBACam / SE3Quat constructors apply (LocalBA.py:57-58), so that a
+    slightly non-orthonormal R (cv2.recoverPose output, products of 4x4 poses) still gives a rotation."""
     R = np.asarray(R, dtype=np.float64)
     tr = R[0, 0] + R[1, 1] + R[2, 2]
     if tr > 0:
@@ -22,7 +24,9 @@ def R_to_quat(R):
         q[j] = (R[j, i] + R[i, j]) / s
         q[k] = (R[k, i] + R[i, k]) / s
         q[3] = (R[k, j] - R[j, k]) / s
-    return np.asarray(q, dtype=np.float64)
+    q = np.asarray(q, dtype=np.float64)
+    q = q / np.linalg.norm(q)
+    return -q if q[3] < 0 else q
 
 
 def quat_to_R(q):

@@ -45,7 +45,7 @@ essential_hypotheses_kernel(const float* __restrict__ x1, const float* __restric
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= total) return;
   const int b = g / H;
-  const int n = n_pts[b];
+  const int n = min(max(n_pts[b], 0), n_max);   // counts beyond the buffers are clamped
   int count = 0;
   double m[kEssMaxModels][9];
   if (n >= kEssSample) {
@@ -91,7 +91,7 @@ essential_score_kernel(const float* __restrict__ x1, const float* __restrict__ x
                        float thr2, int32_t* __restrict__ counts) {
   extern __shared__ __align__(16) float2 sp2[];  // [n] x1 then [n] x2
   const int b = blockIdx.y;
-  const int n = n_pts[b];
+  const int n = min(max(n_pts[b], 0), n_max);   // counts beyond the buffers are clamped
   float2* s1 = sp2;
   float2* s2 = sp2 + n_max;
   const float2* g1 = reinterpret_cast<const float2*>(x1) + (size_t)b * n_max;
@@ -158,7 +158,7 @@ essential_select_kernel(const float* __restrict__ x1, const float* __restrict__ 
   __shared__ double s_red[kSelThreads / 32];
   __shared__ int s_redi[kSelThreads / 32];
   const int b = blockIdx.x, tid = threadIdx.x;
-  const int n = n_pts[b];
+  const int n = min(max(n_pts[b], 0), n_max);   // counts beyond the buffers are clamped
   for (int i = tid; i < H * kEssMaxModels; i += kSelThreads) {
     const int h = i / kEssMaxModels, m = i % kEssMaxModels;
     s_counts[i] = (m < n_models[(size_t)b * H + h]) ? counts[((size_t)b * H + h) * kEssMaxModels + m] : -1;
@@ -237,7 +237,7 @@ recover_pose_kernel(const double* __restrict__ E_in, const float* __restrict__ p
   __shared__ int s_cnt[kPoseThreads / 32][4];
   __shared__ int s_sel;
   const int b = blockIdx.x, tid = threadIdx.x;
-  const int n = n_pts[b];
+  const int n = min(max(n_pts[b], 0), n_max);   // counts beyond the buffers are clamped
   if (tid == 0) decompose_essential(E_in + 9 * b, s_R[0], s_R[1], s_t);
   __syncthreads();
   const float2* g1 = reinterpret_cast<const float2*>(p1) + (size_t)b * n_max;

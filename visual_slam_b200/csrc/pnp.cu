@@ -32,7 +32,7 @@ pnp_hypotheses_kernel(const float* __restrict__ X, const float* __restrict__ uv,
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= total) return;
   const int b = g / H;
-  const int n = n_pts[b];
+  const int n = min(max(n_pts[b], 0), n_max);   // counts beyond the buffers are clamped
   double* out = hyps + (size_t)g * 12;
   bool ok = false;
   if (n >= kSampleSize) {
@@ -70,7 +70,7 @@ pnp_score_kernel(const float* __restrict__ X, const float* __restrict__ uv,
                  const uint8_t* __restrict__ valid, double4 K, float thr2, int32_t* __restrict__ counts) {
   extern __shared__ __align__(16) float sp[];  // [n][3] then [n][2]
   const int b = blockIdx.y;
-  const int n = n_pts[b];
+  const int n = min(max(n_pts[b], 0), n_max);   // counts beyond the buffers are clamped
   float* sX = sp;
   float* sU = sp + (size_t)n_max * 3;
   const float* gX = X + (size_t)b * n_max * 3;
@@ -163,7 +163,7 @@ pnp_select_refine_kernel(const float* __restrict__ X, const float* __restrict__ 
   __shared__ double s_sys[kRefineVals];
   __shared__ int s_flag;
   const int b = blockIdx.x, tid = threadIdx.x;
-  const int n = n_pts[b];
+  const int n = min(max(n_pts[b], 0), n_max);   // counts beyond the buffers are clamped
   const int words = (n_max + 31) / 32;
   const float* gX = X + (size_t)b * n_max * 3;
   const float* gU = uv + (size_t)b * n_max * 2;

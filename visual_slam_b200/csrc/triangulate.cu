@@ -94,7 +94,7 @@ triangulate_kernel(const double* __restrict__ proj, const double* __restrict__ e
   }
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_pts[b]) return;
+  if (i >= min(n_pts[b], n_max)) return;
   const size_t o = (size_t)b * n_max + i;
   const double u1 = x1[2 * o], v1 = x1[2 * o + 1], u2 = x2[2 * o], v2 = x2[2 * o + 1];
   // rows of A (helper_functions.py:285-288): u * P[2] - P[0], v * P[2] - P[1] for both views;
@@ -127,9 +127,10 @@ triangulate_kernel(const double* __restrict__ proj, const double* __restrict__ e
 extern "C" int vslam_triangulate(const double* proj, const double* extr, const double* x1, const double* x2,
                                  const int32_t* n_pts, int n_max, int batch, double z_max, double* Xh,
                                  double* X3, double* depth, uint8_t* good, void* stream) {
-  if (!proj || !x1 || !x2 || !n_pts || !Xh || n_max < 0 || batch < 0) return VSLAM_ERR_BAD_ARG;
+  if (n_max < 0 || batch < 0) return VSLAM_ERR_BAD_ARG;
+  if (n_max == 0 || batch == 0) return VSLAM_OK;   // nothing to do: the reference returns an empty (0, 4) array
+  if (!proj || !x1 || !x2 || !n_pts || !Xh) return VSLAM_ERR_BAD_ARG;
   if (!extr && (depth || good)) return VSLAM_ERR_BAD_ARG;
-  if (n_max == 0 || batch == 0) return VSLAM_OK;
   dim3 grid((n_max + 127) / 128, batch);
   vslam::triangulate_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(
       proj, extr, x1, x2, n_pts, n_max, z_max, Xh, X3, depth, good);

@@ -46,6 +46,7 @@ class MapSoA:
         self._uv = _Grow(2, np.float64)
         self._sa, self._sb, self._sm = _Grow(0, np.int32), _Grow(0, np.int32), _Grow(0, np.float64)
         self._fidx, self._pidx = {}, {}          # external id -> row
+        self._orow = {}                          # (point row, frame row) -> observation row
         self._fids, self._pids = [], []
         self._version = 0                        # bumped on every structural change
         self._engine = None                      # (key, BAEngine)
@@ -81,8 +82,15 @@ class MapSoA:
             raise Exception("No point yet added")             # map.py:92
         if frame_id not in self._fidx:
             raise Exception("No frame yet added")             # map.py:79
-        self._oc.append(self._fidx[frame_id])
-        self._op.append(self._pidx[point_id])
+        f, p = self._fidx[frame_id], self._pidx[point_id]
+        row = self._orow.get((p, f))
+        if row is not None:
+            # Point.frames is a dict keyed by frame id (point.py:14-46): a second observation of the same
+            # (point, frame) replaces the first -- one BA edge, the last uv; the structure does not change
+            self._uv.a[row] = np.asarray(uv, dtype=np.float64).reshape(2)
+            return
+        self._orow[(p, f)] = self._oc.append(f)
+        self._op.append(p)
         self._uv.append(np.asarray(uv, dtype=np.float64).reshape(2))
         self._version += 1
 
@@ -152,6 +160,7 @@ class MapSoA:
         for g, v in ((self._oc, oc), (self._op, op), (self._uv, uv), (self._pts, pts)):
             g.a[:len(v)] = v
             g.n = len(v)
+        self._orow = {(int(p), int(f)): r for r, (p, f) in enumerate(zip(op, oc))}
         self._version += 1
         return int((~keep).sum())
 
