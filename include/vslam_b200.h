@@ -158,6 +158,36 @@ int vslam_gather_correspondences(const int32_t* keep_q, const int32_t* keep_t, c
                                  float* X, float* uv, void* stream);
 
 /* ------------------------------------------------------------------------- */
+/* 2a. Pose plumbing around the PnP call                                      */
+/* ------------------------------------------------------------------------- */
+/*
+ * cv2.Rodrigues both ways, batched (reference src/v2/helper_functions.py:269-278: transformMatrix builds
+ * [Rodrigues(rvec) | tvec], Rtorvec is the matrix -> vector direction).  Operation order follows OpenCV's
+ * cv::Rodrigues; the matrix -> vector direction first projects its input on SO(3) (U V^T of the SVD) as
+ * OpenCV does.
+ *   rvec dev f64 [batch][3];  R dev f64 [batch][9] row-major
+ */
+int vslam_rodrigues(const double* rvec, double* R, int batch, void* stream);
+int vslam_rodrigues_inverse(const double* R, double* rvec, int batch, void* stream);
+/*
+ * reference src/v2/main.py:199-204: T = transformMatrix(rvec, tvec) (world -> camera) and its inverse
+ * W_T_curr = [R^T | -R^T t] (camera -> world, what Frame.pose stores), plus the (qx, qy, qz, qw, tx, ty, tz)
+ * form of W_T_curr that bundle adjustment consumes (SBACam(orientation, position), LocalBA.py:57-58), so that
+ * vslam_pnp_select_refine's output feeds the map / BA arrays on the device.  Any of the three outputs may be
+ * NULL (not all).
+ *   pose6 dev f64 [batch][6] (rvec, tvec);  w2c, c2w dev f64 [batch][16] row-major 4x4;  cam7 dev f64 [batch][7]
+ */
+int vslam_pose_camera_to_world(const double* pose6, double* w2c, double* c2w, double* cam7, int batch,
+                               void* stream);
+/*
+ * reference src/v2/main.py:191-194: the extrinsic guess handed to solvePnPRansac is the PREVIOUS frame's
+ * camera -> world pose, rvec_guess = Rodrigues(W_T_prev[0:3, 0:3]), tvec_guess = W_T_prev[0:3, 3] (the
+ * convention mismatch is the reference's and only seeds Stage B).
+ *   c2w dev f64 [batch][16];  pose6 dev f64 [batch][6]
+ */
+int vslam_pose_guess(const double* c2w, double* pose6, int batch, void* stream);
+
+/* ------------------------------------------------------------------------- */
 /* 2b. Two-view geometry (map initialisation)                                 */
 /* ------------------------------------------------------------------------- */
 /*

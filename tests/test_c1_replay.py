@@ -1,0 +1,320 @@
+"""C1: the reference's tracking loop replayed over ICL-NUIM frames 1..85 (map initialisation at frame 18, key
+frames inserted at 39, 60 and 81) against tests/golden/c1_replay.npz, which holds what the reference's own modules
+returned stage by stage (tests/golden/make_c1_replay_golden.py; BA through the reference's LocalBA.py over the
+CPU restatement -- "restatement, not g2o").  The loop itself is tests/c1_loop.py (main.py:73-348 restated).
+
+CPU tests: the oracles are pinned to the record, and the drop-in BA *wrapper* (graph construction from the Map,
+fixed flags, scale edges, median-depth rescale, write-back) reproduces the reference's LocalBA.py when both sit
+on the same arithmetic.  GPU tests: every stage of the loop through the drop-ins -- teacher-forced (each stage is
+fed the recorded inputs, so one stage's permitted differences do not leak into the next comparison) and
+free-running (our own results carried forward, drift bounded).
+"""
+import copy
+import os
+
+import cv2
+import numpy as np
+import pytest
+
+import c1_containers as cc
+import c1_loop
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c1_replay.npz")
+K4 = (481.2, 480.0, 319.5, 239.5)
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return dict(np.load(GOLD))
+
+
+class Playback:
+    """Rebuilds each stage's return objects from the record."""
+
+    def __init__(self, g):
+        self.g = g
+
+    def features(self, i):
+        return self.g["kp_%d" % i], self.g["desc_%d" % i]
+
+    def get(self, stage, i, name):
+        return self.g["%s_%d_%s" % (stage, i, name)]
+
+    def output(self, stage, i, inputs):
+        g = lambda name: self.get(stage, i, name)  # noqa: E731
+        if stage.startswith("match"):
+            q, t, d = g("q"), g("t"), g("d")
+            matches = [[cv2.DMatch(int(a), int(b), 0, float(c))] for a, b, c in zip(q, t, d)]
+            kp1, kp2 = np.asarray(inputs["kp1"]), np.asarray(inputs["kp2"])
+            d1, d2 = np.asarray(inputs["desc1"]), np.asarray(inputs["desc2"])
+            return matches, kp1[q], d1[q], kp2[t], d2[t]
+        if stage == "essential":
+            return g("E"), g("inliers"), float(g("score"))
+        if stage == "relpose":
+            keep = g("keep")
+            return (g("R"), g("t"), float(g("vf")), g("tri"), [inputs["pts1"][k] for k in keep],
+                    [inputs["pts2"][k] for k in keep], [inputs["fts1"][k] for k in keep],
+                    [inputs["fts2"][k] for k in keep])
+        if stage == "guess":
+            return self.get("pnp", i, "rvec_guess"), self.get("pnp", i, "tvec_guess")
+        if stage == "pnp":
+            inl = g("inliers")
+            return bool(g("retval")), g("rvec"), g("tvec"), (inl if len(inl) else None)
+        if stage == "pose_plumbing":
+            return g("W_T_curr")
+        if stage == "listdiff":
+            return g("idx").tolist()
+        if stage == "triangulate":
+            return g("X"), g("good")
+        if stage.startswith("ba_"):
+            return {k: g(k) for k in ("frame_ids", "poses", "point_ids", "points")}
+        raise KeyError(stage)
+
+
+class DropIns:
+    """The backend of c1_loop.run made of visual_slam_b200's drop-ins (host containers from c1_containers)."""
+    Map, Point = cc.Map, cc.Point
+    deepcopy = staticmethod(copy.deepcopy)
+    feature_extractor = None
+
+    def __init__(self, features):
+        from visual_slam_b200 import FeatureMatcher, ba, keyframe, pnp, poses, triangulate, twoview
+        self._features = features
+        self.feature_matcher = FeatureMatcher()
+        self.estimateEssential = twoview.estimateEssential
+        self.estimateRelativePose = twoview.estimateRelativePose
+        self.solvePnPRansac = pnp.solvePnPRansac
+        self.BundleAdjustment = ba.BundleAdjustment
+        self.GetListDiff = keyframe.GetListDiff
+        self.triangulate = triangulate.triangulate
+        self.pose_guess = poses.pose_guess
+        self.camera_to_world = poses.camera_to_world
+
+    def make_frame(self, i, id):
+        return cc.Frame(self._features, i, id)
+
+    @staticmethod
+    def ba_stats(BA):
+        return BA.stats
+
+
+def _stage_list(g):
+    return [tuple(s.split()) for s in g["stages"]]
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU
+# ---------------------------------------------------------------------------------------------------------
+def test_record_shape():
+    g = np.load(GOLD)
+    assert int(g["init_index"]) == 18 and g["keyframe_indices"].tolist() == [1, 18, 39, 60, 81]
+    st = _stage_list(g)
+    assert sum(1 for s, _ in st if s == "pnp") == 67 and sum(1 for s, _ in st if s == "ba_full") == 3
+    assert str(g["cv2_version"]) == cv2.__version__, "the record was made with another OpenCV; regenerate it"
+
+
+def test_oracles_reproduce_every_recorded_stage(gold, monkeypatch):
+    """Playback of the whole loop on the CPU.  Matching, pose plumbing, list difference, triangulation and PnP
+    Stage B go through the oracles; bundle adjustment goes through the PRODUCT's drop-in wrapper with its device
+    solver swapped for the CPU restatement, so the wrapper's graph construction and write-back are compared with
+    the reference's LocalBA.py (same arithmetic underneath)."""
+    from oracle import ba as oba
+    from oracle import keyframe as okf
+    from oracle import matching as om
+    from oracle import pnp as opnp
+    from oracle import poses as opo
+    from oracle import triangulate as otri
+    from visual_slam_b200 import ba as vba
+    pb = Playback(gold)
+    seen = {}
+
+    def cpu_solver(prob, max_iterations=10, device=None, pcg_tol=None):
+        h = oba.optimize(prob, max_iterations)
+        return {"initial_cost": h["cost"][0], "final_cost": h["final_cost"], "iterations": h["iterations"],
+                "trials": h["trials"]}
+    monkeypatch.setattr(vba, "solve_problem", cpu_solver)
+
+    class Be(DropIns):
+        def __init__(self, features):
+            self._features = features
+            self.feature_matcher = None
+            self.BundleAdjustment = vba.BundleAdjustment
+
+    def hook(stage, i, fn, inputs):
+        rec = pb.output(stage, i, inputs)
+        seen[stage] = seen.get(stage, 0) + 1
+        if stage.startswith("match"):
+            idx, dist = om.knn2_numpy(inputs["desc1"], inputs["desc2"])
+            kq, kt = om.filter_numpy(idx, dist, 0.8, None)
+            assert np.array_equal(kq, pb.get(stage, i, "q")) and np.array_equal(kt, pb.get(stage, i, "t"))
+            assert np.array_equal(dist[kq, 0], pb.get(stage, i, "d").astype(np.int32))
+            if stage != "match_init":
+                assert np.array_equal(inputs["kp1"], pb.get(stage, i, "kp1"))     # playback stays on the recorded path
+                assert np.array_equal(inputs["desc1"], pb.get(stage, i, "desc1"))
+        elif stage == "guess":
+            assert np.array_equal(inputs["W_T_prev"], pb.get(stage, i, "W_T_prev"))
+            r, t = opo.pose_guess(inputs["W_T_prev"])
+            assert np.array_equal(r, rec[0]) and np.array_equal(t, rec[1])
+        elif stage == "pose_plumbing":
+            assert np.abs(opo.camera_to_world(inputs["rvec"], inputs["tvec"]) - rec).max() < 1e-15
+        elif stage == "listdiff":
+            assert okf.get_list_diff(inputs["kp1"], inputs["kp2"]) == rec
+        elif stage == "triangulate":
+            Xh = otri.triangulate(inputs["Proj1"], inputs["Proj2"], inputs["x1"], inputs["x2"])
+            X3, _, good = otri.dehomogenise_and_filter(Xh, inputs["p1"], inputs["p2"])
+            assert np.array_equal(X3, rec[0]) and np.array_equal(np.nonzero(good)[0], rec[1])
+        elif stage == "pnp":
+            # Stage B of cv2.solvePnPRansac = cv2.solvePnP(ITERATIVE) on the recorded inliers from the guess
+            X, uv = inputs["objectPoints"].reshape(-1, 3), inputs["imagePoints"].reshape(-1, 2)
+            ok, rv, tv = opnp.refine_cv2(X, uv, K4, rec[3].ravel(), inputs["rvec"], inputs["tvec"])
+            assert ok and np.array_equal(rv.ravel(), rec[1].ravel()) and np.array_equal(tv.ravel(), rec[2].ravel())
+        elif stage.startswith("ba_"):
+            ours = fn()                       # the drop-in wrapper over the CPU restatement
+            st = ours["stats"]
+            assert st["iterations"] == int(pb.get(stage, i, "stat_iterations"))
+            assert st["trials"] == int(pb.get(stage, i, "stat_trials"))
+            assert abs(st["final_cost"] - float(pb.get(stage, i, "stat_final_cost"))) <= 1e-9 * st["final_cost"]
+            assert np.array_equal(ours["frame_ids"], rec["frame_ids"]) and np.array_equal(ours["point_ids"], rec["point_ids"])
+            assert np.abs(ours["poses"] - rec["poses"]).max() < 1e-9
+            assert np.abs(ours["points"] - rec["points"]).max() < 1e-9
+        return rec
+
+    s = c1_loop.run(Be(pb.features), int(gold["first_index"]), int(gold["last_index"]), hook)
+    assert s["keyframe_indices"] == gold["keyframe_indices"].tolist()
+    assert seen == {"match_init": 18, "essential": 18, "relpose": 18, "ba_init": 1, "match_track": 67, "guess": 67,
+                    "pnp": 67, "pose_plumbing": 67, "ba_motion": 67, "listdiff": 3, "match_kf": 3, "triangulate": 3,
+                    "ba_full": 3}, seen
+
+
+# ---------------------------------------------------------------------------------------------------------
+# GPU
+# ---------------------------------------------------------------------------------------------------------
+def _inlier_set(inl):
+    return set() if inl is None else set(np.asarray(inl).ravel().tolist())
+
+
+@pytest.mark.gpu
+def test_gpu_teacher_forced_replay(gold):
+    """Every hot-path call of the loop through the drop-ins, each fed the recorded inputs.  Bit-exact where the
+    reference is deterministic integer / index work (matches, list difference), 1e-6 for poses, BA against the
+    restatement at north_star's tolerances; the two RANSAC stages draw their own samples (cv2's cannot be seeded)
+    and are compared through what is sample-independent: Stage B on the recorded inlier set, and the support."""
+    import torch
+    from oracle import pnp as opnp
+    from visual_slam_b200 import pnp as vpnp
+    pb = Playback(gold)
+    be = DropIns(pb.features)
+    worst = {"pnp_pose_given_inliers": 0.0, "pnp_jaccard_min": 1.0, "pnp_pose_vs_cv2": 0.0, "ba_cost_rel": 0.0,
+             "ba_pose": 0.0, "ba_point": 0.0}
+    traj = {"same": 0, "differ": 0}
+
+    def hook(stage, i, fn, inputs):
+        rec = pb.output(stage, i, inputs)
+        ours = fn()
+        if stage.startswith("match"):
+            assert [m[0].queryIdx for m in ours[0]] == pb.get(stage, i, "q").tolist()
+            assert [m[0].trainIdx for m in ours[0]] == pb.get(stage, i, "t").tolist()
+            assert [m[0].distance for m in ours[0]] == pb.get(stage, i, "d").tolist()
+            for a, b in zip(ours[1:], rec[1:]):
+                assert np.array_equal(a, b)
+        elif stage == "essential":
+            E, inl, _ = ours
+            assert E is not None and abs(np.linalg.norm(E) - 1.0) < 1e-9
+            n_ref = int(rec[1].sum())
+            assert int(inl.sum()) >= 0.9 * n_ref, (i, int(inl.sum()), n_ref)
+        elif stage == "relpose":                                    # deterministic given E (the recorded one)
+            assert np.abs(np.asarray(ours[0]) - rec[0]).max() < 1e-6 and np.abs(np.asarray(ours[1]) - rec[1]).max() < 1e-6
+            assert abs(ours[2] - rec[2]) < 1e-12 and len(ours[4]) == len(rec[4])
+            assert np.abs(ours[3] - rec[3]).max() <= 1e-6 * np.abs(rec[3]).max()
+            assert all(np.array_equal(a, b) for a, b in zip(ours[4], rec[4]))
+        elif stage == "guess":
+            assert np.abs(ours[0] - rec[0]).max() < 1e-12 and np.array_equal(ours[1], rec[1])
+        elif stage == "pose_plumbing":
+            assert np.abs(ours - rec).max() < 1e-12
+        elif stage == "listdiff":
+            assert ours == rec
+        elif stage == "triangulate":
+            assert np.abs(ours[0] - rec[0]).max() <= 1e-9 * max(1.0, np.abs(rec[0]).max())
+            assert np.array_equal(ours[1], rec[1])
+        elif stage == "pnp":
+            assert ours[0] and rec[0]
+            X, uv = inputs["objectPoints"].reshape(-1, 3), inputs["imagePoints"].reshape(-1, 2)
+            n = len(X)
+            # (a) same hypothesis set => identical counts, winner and inlier set (scorer / selection of cv2 restated)
+            words = np.random.default_rng(1000 + i).integers(0, 2 ** 32, size=(1, 100, 4), dtype=np.uint64).astype(np.uint32)
+            g6 = np.concatenate([inputs["rvec"].ravel(), inputs["tvec"].ravel()])
+            o = vpnp.pnp_ransac_batch(torch.from_numpy(X)[None].cuda(), torch.from_numpy(uv)[None].cuda(),
+                                      torch.tensor([n], dtype=torch.int32, device="cuda"),
+                                      torch.from_numpy(words.view(np.int32)).cuda(), K4,
+                                      torch.from_numpy(g6)[None].cuda())
+            hyps = o["hyps"][0].cpu().numpy().reshape(-1, 3, 4); valid = o["valid"][0].cpu().numpy().astype(bool)
+            masks, counts = opnp.score(hyps, valid, X, uv, K4)
+            assert np.array_equal(counts, o["counts"][0].cpu().numpy())
+            best, _ = opnp.select(counts, valid, n)
+            assert best == int(o["best"][0]) and best >= 0
+            inl = np.nonzero(masks[best])[0]
+            assert np.array_equal(vpnp.unpack_inliers(o["inlier_bits"][0].cpu().numpy(), n), inl)
+            ok, rv, tv = opnp.refine_cv2(X, uv, K4, inl, inputs["rvec"], inputs["tvec"])
+            pose = o["pose"][0].cpu().numpy()
+            assert ok and np.abs(pose[:3] - rv.ravel()).max() < 1e-6 and np.abs(pose[3:] - tv.ravel()).max() < 1e-6
+            # (b) Stage B on the RECORDED inlier set reproduces the recorded pose
+            ri = rec[3].ravel()
+            ok2, rv2, tv2, _ = vpnp.solvePnPRansac(X[ri], uv[ri], np.asarray(c1_loop.ICL_K), None, inputs["rvec"].copy(),
+                                                   np.asarray(inputs["tvec"]).copy(), True, reprojectionError=1e6)
+            d = max(np.abs(rv2 - rec[1]).max(), np.abs(tv2 - rec[2]).max())
+            worst["pnp_pose_given_inliers"] = max(worst["pnp_pose_given_inliers"], d)
+            assert ok2 and d < 1e-6, (i, d)
+            # (c) the drop-in as the loop calls it: support and pose close to cv2's (different samples)
+            a, b = _inlier_set(ours[3]), _inlier_set(rec[3])
+            worst["pnp_jaccard_min"] = min(worst["pnp_jaccard_min"], len(a & b) / len(a | b))
+            worst["pnp_pose_vs_cv2"] = max(worst["pnp_pose_vs_cv2"], np.abs(ours[1] - rec[1]).max(),
+                                           np.abs(ours[2] - rec[2]).max())
+        elif stage.startswith("ba_"):
+            st = ours["stats"]
+            fc = float(pb.get(stage, i, "stat_final_cost"))
+            rel = abs(st["final_cost"] - fc) / fc
+            worst["ba_cost_rel"] = max(worst["ba_cost_rel"], rel)
+            assert rel <= 1e-4, (stage, i, st["final_cost"], fc)
+            assert abs(st["initial_cost"] - float(pb.get(stage, i, "stat_initial_cost"))) <= 1e-9 * st["initial_cost"]
+            same = (int(st["iterations"]) == int(pb.get(stage, i, "stat_iterations")) and
+                    int(st["trials"]) == int(pb.get(stage, i, "stat_trials")))
+            traj["same" if same else "differ"] += 1
+            assert np.array_equal(ours["frame_ids"], rec["frame_ids"]) and np.array_equal(ours["point_ids"], rec["point_ids"])
+            dp, dx = np.abs(ours["poses"] - rec["poses"]).max(), np.abs(ours["points"] - rec["points"]).max() if len(rec["points"]) else 0.0
+            worst["ba_pose"], worst["ba_point"] = max(worst["ba_pose"], dp), max(worst["ba_point"], dx)
+            assert dp < 1e-6 and dx < 1e-6, (stage, i, dp, dx)
+        return rec
+
+    s = c1_loop.run(be, int(gold["first_index"]), int(gold["last_index"]), hook)
+    assert s["keyframe_indices"] == gold["keyframe_indices"].tolist()
+    print("C1 teacher-forced worst cases:", worst, "LM trajectories (iterations, trials) same/differ:", traj)
+    assert worst["pnp_jaccard_min"] > 0.8 and worst["pnp_pose_vs_cv2"] < 2e-2
+    assert traj["same"] >= 0.9 * (traj["same"] + traj["differ"])
+
+
+@pytest.mark.gpu
+def test_gpu_free_running_replay_stays_on_the_reference_trajectory(gold):
+    """The loop on our own results only (nothing is taken from the record except the frames' features): the same
+    key frames are chosen, the match counts follow the record and the camera trajectory stays close to the
+    reference's.  The two RANSAC stages sample differently from cv2, so agreement is bounded, not exact."""
+    pb = Playback(gold)
+    be = DropIns(pb.features)
+    rec_pose, our_pose, n_match = {}, {}, {}
+
+    def hook(stage, i, fn, inputs):
+        ours = fn()
+        if stage == "match_track":
+            n_match[i] = (len(ours[0]), len(pb.get(stage, i, "q")))
+        if stage == "ba_motion":
+            our_pose[i] = ours["poses"][-1]
+            rec_pose[i] = pb.get(stage, i, "poses")[-1]
+        return ours
+
+    s = c1_loop.run(be, int(gold["first_index"]), int(gold["last_index"]), hook)
+    assert s["init_index"] == int(gold["init_index"])
+    assert s["keyframe_indices"] == gold["keyframe_indices"].tolist()
+    dt = max(np.linalg.norm(our_pose[i][:3, 3] - rec_pose[i][:3, 3]) for i in our_pose)
+    dr = max(np.abs(our_pose[i][:3, :3] - rec_pose[i][:3, :3]).max() for i in our_pose)
+    dm = max(abs(a - b) for a, b in n_match.values())
+    print("C1 free-running: max |dt| %.3e (map scale: unit median depth), max |dR| %.3e, max match-count gap %d" % (dt, dr, dm))
+    assert dt < 5e-2 and dr < 2e-2 and dm <= 15

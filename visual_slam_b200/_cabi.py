@@ -34,6 +34,10 @@ def _declare(lib):
     lib.vslam_pnp_select_refine.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, i32, pd, f64, f64, vp, i32,
                                             vp, vp, vp, vp, vp, vp]
     lib.vslam_gather_correspondences.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp, vp]
+    lib.vslam_rodrigues.argtypes = [vp, vp, i32, vp]
+    lib.vslam_rodrigues_inverse.argtypes = [vp, vp, i32, vp]
+    lib.vslam_pose_camera_to_world.argtypes = [vp, vp, vp, vp, i32, vp]
+    lib.vslam_pose_guess.argtypes = [vp, vp, i32, vp]
     lib.vslam_undistort_points.argtypes = [vp, C.c_int64, pd, vp, vp]
     lib.vslam_essential_hypotheses.argtypes = [vp, vp, vp, i32, i32, vp, i32, vp, vp, vp]
     lib.vslam_essential_score.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, f64, vp, vp]

@@ -12,21 +12,29 @@ def R_to_quat(R):
     slightly non-orthonormal R (cv2.recoverPose output, products of 4x4 poses) still gives a rotation."""
     R = np.asarray(R, dtype=np.float64)
     tr = R[0, 0] + R[1, 1] + R[2, 2]
-    if tr > 0:
-        s = np.sqrt(tr + 1.0) * 2
-        q = [(R[2, 1] - R[1, 2]) / s, (R[0, 2] - R[2, 0]) / s, (R[1, 0] - R[0, 1]) / s, 0.25 * s]
+    q = [0.0, 0.0, 0.0, 0.0]
+    if tr > 0:                                   # operation order of Eigen::Quaternion(Matrix3)
+        s = np.sqrt(tr + 1.0)
+        q[3] = 0.5 * s
+        s = 0.5 / s
+        q[0], q[1], q[2] = (R[2, 1] - R[1, 2]) * s, (R[0, 2] - R[2, 0]) * s, (R[1, 0] - R[0, 1]) * s
     else:
-        i = int(np.argmax([R[0, 0], R[1, 1], R[2, 2]]))
+        i = 0
+        if R[1, 1] > R[0, 0]:
+            i = 1
+        if R[2, 2] > R[i, i]:
+            i = 2
         j, k = (i + 1) % 3, (i + 2) % 3
-        s = np.sqrt(R[i, i] - R[j, j] - R[k, k] + 1.0) * 2
-        q = [0.0, 0.0, 0.0, 0.0]
-        q[i] = 0.25 * s
-        q[j] = (R[j, i] + R[i, j]) / s
-        q[k] = (R[k, i] + R[i, k]) / s
-        q[3] = (R[k, j] - R[j, k]) / s
+        s = np.sqrt(R[i, i] - R[j, j] - R[k, k] + 1.0)
+        q[i] = 0.5 * s
+        s = 0.5 / s
+        q[3] = (R[k, j] - R[j, k]) * s
+        q[j] = (R[j, i] + R[i, j]) * s
+        q[k] = (R[k, i] + R[i, k]) * s
     q = np.asarray(q, dtype=np.float64)
-    q = q / np.linalg.norm(q)
-    return -q if q[3] < 0 else q
+    if q[3] < 0:
+        q = -q
+    return q / np.linalg.norm(q)
 
 
 def quat_to_R(q):
