@@ -42,3 +42,37 @@ def test_tracking_step_matches_chained_oracles():
         ok, rvec, tvec = op.refine_cv2(X[b][kq], kp[b][kt], K, inl, guess[b, :3], guess[b, 3:])
         assert ok and np.abs(g["pose"][b, :3] - rvec).max() < 1e-6 and np.abs(g["pose"][b, 3:] - tvec).max() < 1e-6
         assert np.abs(g["pose"][b, :3] - data[b][4]).max() < 3e-3 and np.abs(g["pose"][b, 3:] - data[b][5]).max() < 1e-2
+
+
+def test_c5_generator_is_device_independent_and_tracks():
+    """C5 data (per-pair seed hash(seq, i), random-walk poses, previous pose as the guess): identical bytes
+    on the CPU and on the device, any pair addressable on its own; the fused step recovers the true pose and its
+    camera->world outputs equal the reference's plumbing (main.py:199-203) applied to its own PnP result."""
+    from oracle import poses as opo
+    cpu = synth.c5_pairs(5, 40, 46, 512, device="cpu")
+    dev = synth.c5_pairs(5, 40, 46, 512, device="cuda")
+    for k in cpu:
+        assert torch.equal(cpu[k], dev[k].cpu()), k
+    one = synth.c5_pairs(5, 43, 44, 512, device="cuda")
+    assert all(torch.equal(one[k][0], dev[k][3]) for k in one)
+    step = np.linalg.norm((cpu["pose_true"] - cpu["guess"]).numpy()[:, :3], axis=1)
+    assert (np.rad2deg(step) <= 2.0 + 1e-9).all() and (np.rad2deg(step) > 0.1).all()
+    B, H = 6, 100
+    words = torch.from_numpy(np.random.default_rng(8).integers(0, 2 ** 32, size=(B, H, 4), dtype=np.uint64)
+                             .astype(np.uint32).view(np.int32)).cuda()
+    out = track_batch(dev["desc_kf"], dev["desc_cur"], dev["map_xyz"], dev["kp_cur"], words, K, dev["guess"],
+                      want_c2w=True)
+    pose = out["pose"].cpu().numpy()
+    err = np.abs(pose - cpu["pose_true"].numpy())
+    assert err[:, :3].max() < 2e-3 and err[:, 3:].max() < 1e-2
+    assert (out["n_inliers"].cpu().numpy() > 0.8 * out["n_keep"].cpu().numpy()).all()
+    for b in range(B):
+        W = opo.camera_to_world(pose[b, :3], pose[b, 3:])
+        assert np.abs(out["c2w"][b].cpu().numpy() - W).max() < 1e-14
+        assert np.abs(out["cam7"][b].cpu().numpy() - opo.sbacam(W)).max() < 1e-14
+    # the reference's way of seeding Stage B: the previous camera->world pose, turned into (rvec, tvec) on the device
+    prev = torch.from_numpy(np.stack([opo.camera_to_world(g[:3], g[3:]) for g in cpu["guess"].numpy()])).cuda()
+    out2 = track_batch(dev["desc_kf"], dev["desc_cur"], dev["map_xyz"], dev["kp_cur"], words, K, prev_c2w=prev)
+    for b in range(B):
+        r, t = opo.pose_guess(prev[b].cpu().numpy())
+        assert np.abs(out2["guess"][b].cpu().numpy() - np.concatenate([r.ravel(), t])).max() < 1e-9

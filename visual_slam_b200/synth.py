@@ -126,3 +126,108 @@ def frames(n, H=480, W=640, seed=0, block=8):
         img = img + rng.integers(-3, 4, (H, W, 3), dtype=np.int16)
         out[i] = np.clip(img, 0, 255).astype(np.uint8)
     return out
+
+
+# ---- C5: 8 sequences x 1000 frame pairs, every pair seeded by hash(seq, i) ------------------------
+# Counter-based generation (splitmix64 on int64 tensors, wrapping arithmetic) so that any pair of any sequence can
+# be produced on its own, on the CPU or on the device, with identical bytes: ranks generate their shard in place.
+_M64 = (1 << 64)
+_C1, _C2, _GOLD = 0xBF58476D1CE4E5B9 - _M64, 0x94D049BB133111EB - _M64, 0x9E3779B97F4A7C15 - _M64
+
+
+def _wrap(x):
+    """Python int -> the same value modulo 2^64 as a signed 64-bit number."""
+    x &= _M64 - 1
+    return x - _M64 if x >= (1 << 63) else x
+
+
+def _lsr(x, s):
+    return (x >> s) & ((1 << (64 - s)) - 1)
+
+
+def _mix64(x):
+    x = (x ^ _lsr(x, 30)) * _C1
+    x = (x ^ _lsr(x, 27)) * _C2
+    return x ^ _lsr(x, 31)
+
+
+def c5_pair_key(seq, i):
+    """hash(seq, i) as a Python int in [-2^63, 2^63)."""
+    import torch
+    return int(_mix64(torch.tensor([_wrap(((seq * 1000003 + i) * 2 + 1) * _GOLD)], dtype=torch.int64))[0])
+
+
+def _bits(keys, stream, count):
+    """int64 [B, count] of hashed counters: keys [B] (pair keys), stream = which array of the pair."""
+    import torch
+    ctr = torch.arange(count, dtype=torch.int64, device=keys.device)[None, :]
+    return _mix64(_mix64(keys[:, None] + _wrap(stream * _GOLD)) + ctr * _GOLD)
+
+
+def _uniform(keys, stream, count):
+    return _lsr(_bits(keys, stream, count), 11).double() * (1.0 / (1 << 53))
+
+
+def c5_poses(seq, n_pairs=1000):
+    """World->camera poses of frames 0..n_pairs of sequence `seq` (host, float64): a smooth random walk, per frame a
+    rotation <= 2 deg and a translation <= 5 cm whose directions drift slowly.  Returns rvec [n+1,3], tvec [n+1,3];
+    pair i tracks frame i+1 with frame i's pose as the guess."""
+    rng = np.random.default_rng(abs(c5_pair_key(seq, -1)) % (1 << 63))
+    R, t = np.eye(3), np.zeros(3)
+    w, v = rng.normal(size=3), rng.normal(size=3)
+    rv, tv = [np.zeros(3)], [np.zeros(3)]
+    for _ in range(n_pairs):
+        w = 0.95 * w + 0.3 * rng.normal(size=3)
+        v = 0.95 * v + 0.3 * rng.normal(size=3)
+        dr = w / np.linalg.norm(w) * np.deg2rad(rng.uniform(0.2, 2.0))
+        dt = v / np.linalg.norm(v) * rng.uniform(0.005, 0.05)
+        dR = _rodrigues(dr)
+        R, t = dR @ R, dR @ t + dt
+        c = np.clip((np.trace(R) - 1) / 2, -1, 1)
+        th = np.arccos(c)
+        ax = np.array([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]])
+        rv.append(ax * (0.5 if th < 1e-9 else th / (2 * np.sin(th))))
+        tv.append(t.copy())
+    return np.array(rv), np.array(tv)
+
+
+def c5_pairs(seq, lo, hi, n=2048, device="cpu", planted=0.7, flip=0.10, wrong_pix=0.10, pix_sigma=0.5, K=ICL_K,
+             width=640, height=480, poses=None):
+    """Frame pairs lo..hi-1 of sequence `seq` as tensors on `device`: desc_kf u8 [B,n,32], desc_cur u8 [B,n,32],
+    map_xyz f32 [B,n,3], kp_cur f32 [B,n,2], pose_true f64 [B,6] (rvec, tvec of the current frame, world->camera),
+    guess f64 [B,6] (the previous frame's pose).  n world points uniform in the current camera's frustum (depth
+    1-8 m); `planted` of the key-frame points reappear in the current frame with each descriptor bit flipped w.p.
+    `flip` and pixel noise sigma; `wrong_pix` of those carry a uniform-random pixel (wrong matches)."""
+    import torch
+    rv, tv = poses if poses is not None else c5_poses(seq, hi)
+    B = hi - lo
+    keys = torch.tensor([c5_pair_key(seq, i) for i in range(lo, hi)], dtype=torch.int64, device=device)
+    fx, fy, cx, cy = K
+    pose_true = torch.from_numpy(np.concatenate([rv[lo + 1:hi + 1], tv[lo + 1:hi + 1]], axis=1)).to(device)
+    guess = torch.from_numpy(np.concatenate([rv[lo:hi], tv[lo:hi]], axis=1)).to(device)
+    Rm = torch.from_numpy(np.stack([_rodrigues(r) for r in rv[lo + 1:hi + 1]])).to(device)          # [B,3,3]
+    tm = pose_true[:, 3:]
+    u = _uniform(keys, 1, n) * width
+    v = _uniform(keys, 2, n) * height
+    z = 1.0 + 7.0 * _uniform(keys, 3, n)
+    Xc = torch.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], dim=2)                              # [B,n,3]
+    Xw = torch.einsum("bji,bnj->bni", Rm, Xc - tm[:, None, :])                                      # R^T (Xc - t)
+    desc_kf = (_bits(keys, 4, n * 4).view(torch.uint8).view(B, n, 32)).clone()
+    desc_cur = (_bits(keys, 5, n * 4).view(torch.uint8).view(B, n, 32)).clone()
+    kp_cur = torch.stack([_uniform(keys, 6, n) * width, _uniform(keys, 7, n) * height], dim=2)
+    n_pl = int(round(planted * n))
+    src = torch.argsort(_bits(keys, 8, n), dim=1)[:, :n_pl]                                          # key-frame rows that reappear
+    dst = torch.argsort(_bits(keys, 9, n), dim=1)[:, :n_pl]                                          # their rows in the current frame
+    flips = (_uniform(keys, 10, n_pl * 256) < flip).view(B, n_pl, 32, 8)
+    weights = torch.tensor([128, 64, 32, 16, 8, 4, 2, 1], dtype=torch.int64, device=device)
+    noise = (flips.long() * weights).sum(dim=3).to(torch.uint8)                                     # packbits, MSB first
+    bi = torch.arange(B, device=device)[:, None]
+    desc_cur[bi, dst] = desc_kf[bi, src] ^ noise
+    r1, r2 = _uniform(keys, 11, n_pl * 2).view(B, n_pl, 2).clamp_min(1e-300), _uniform(keys, 12, n_pl * 2).view(B, n_pl, 2)
+    gauss = torch.sqrt(-2.0 * torch.log(r1)) * torch.cos(2.0 * np.pi * r2)                           # Box-Muller
+    pix = torch.stack([u, v], dim=2)[bi, src] + pix_sigma * gauss
+    bad = _uniform(keys, 13, n_pl) < wrong_pix
+    rnd = torch.stack([_uniform(keys, 14, n_pl) * width, _uniform(keys, 15, n_pl) * height], dim=2)
+    kp_cur[bi, dst] = torch.where(bad[:, :, None], rnd, pix)
+    return {"desc_kf": desc_kf, "desc_cur": desc_cur, "map_xyz": Xw.float(), "kp_cur": kp_cur.float(),
+            "pose_true": pose_true, "guess": guess}

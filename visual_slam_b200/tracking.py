@@ -5,6 +5,7 @@ import torch
 from . import _cabi
 from .matching import match_batch
 from .pnp import pnp_ransac_batch
+from .poses import camera_to_world_batch, guess_batch
 
 
 def gather_correspondences(keep_q, keep_t, n_keep, map_xyz, kp_cur):
@@ -18,13 +19,23 @@ def gather_correspondences(keep_q, keep_t, n_keep, map_xyz, kp_cur):
     return X, uv
 
 
-def track_batch(desc_kf, desc_cur, map_xyz, kp_cur, words, K, guess, ratio=0.8, cross_check=False,
-                thr=8.0, confidence=0.99):
+def track_batch(desc_kf, desc_cur, map_xyz, kp_cur, words, K, guess=None, ratio=0.8, cross_check=False,
+                thr=8.0, confidence=0.99, prev_c2w=None, want_c2w=False):
     """desc_kf u8 [B,nq,32] (descriptors of the key frame's mapped points), desc_cur u8 [B,nt,32],
-    map_xyz f32 [B,nq,3], kp_cur f32 [B,nt,2], words i32 [B,H,4], guess f64 [B,6] (rvec,tvec).
-    Returns the match lists and the PnP result dict (pose f64 [B,6] world->camera)."""
+    map_xyz f32 [B,nq,3], kp_cur f32 [B,nt,2], words i32 [B,H,4].  The Stage-B guess is either `guess` f64 [B,6]
+    (rvec, tvec) or, as the reference builds it (main.py:191-194), derived on the device from `prev_c2w` f64
+    [B,4,4], the previous frame's camera->world pose.  Returns the match lists and the PnP result dict (pose f64
+    [B,6] world->camera); with want_c2w also `c2w` [B,4,4] and `cam7` [B,7], the camera->world pose of main.py:201-203
+    as a matrix and in the (q, t) form the BA arrays hold -- nothing leaves the device."""
+    if (guess is None) == (prev_c2w is None):
+        raise ValueError("give exactly one of guess and prev_c2w")
+    if guess is None:
+        guess = guess_batch(prev_c2w)
     m = match_batch(desc_kf, desc_cur, ratio, cross_check)
     X, uv = gather_correspondences(m["keep_q"], m["keep_t"], m["n_keep"], map_xyz, kp_cur)
     out = pnp_ransac_batch(X, uv, m["n_keep"], words, K, guess, thr, confidence)
-    out.update(keep_q=m["keep_q"], keep_t=m["keep_t"], n_keep=m["n_keep"], X=X, uv=uv)
+    out.update(keep_q=m["keep_q"], keep_t=m["keep_t"], n_keep=m["n_keep"], X=X, uv=uv, guess=guess)
+    if want_c2w:
+        p = camera_to_world_batch(out["pose"])
+        out.update(c2w=p["c2w"], cam7=p["cam7"])
     return out
