@@ -133,3 +133,30 @@ def test_ragged_batch_matches_oracle_per_pair():
             assert n == len(kq), (b, cross)
             assert np.array_equal(out["keep_q"][b, :n].cpu().numpy(), kq), (b, cross)
             assert np.array_equal(out["keep_t"][b, :n].cpu().numpy(), kt), (b, cross)
+
+
+@pytest.mark.parametrize("batch,chunks", [(7, 3), (5, 8), (4, 1), (9, 4)])
+def test_host_matcher_equals_device_call_and_oracle(batch, chunks):
+    """HostMatcher (the object behind bench.py's e2e figure: pinned host buffers -> H2D -> kNN-2 + ratio + cross-check
+    -> D2H, chunks on two streams) on batches that do not divide into the chunk count, against match_batch on the
+    same data and against the oracle pair by pair; a second run() reuses the buffers."""
+    from visual_slam_b200.matching import HostMatcher
+    nq, nt = 300, 257
+    qs, ts = synth.descriptors_batch(batch, nq, nt, seed=31 + batch)
+    hm = HostMatcher(batch, nq, nt, 0.8, True, chunks=chunks)
+    assert hm.chunks == min(chunks, batch)
+    for rep in range(2):
+        hm.load(qs, ts)
+        kq, kt, nk = hm.run()
+        torch.cuda.synchronize()
+        g = run_gpu(qs, ts, 0.8, True)
+        assert np.array_equal(nk.numpy(), g["n_keep"]) and np.array_equal(kq.numpy(), g["keep_q"])
+        assert np.array_equal(kt.numpy(), g["keep_t"])
+        for b in range(batch):
+            idx, dist = om.knn2_numpy(qs[b], ts[b])
+            rev_idx, _ = om.rev_nearest_numpy(qs[b], ts[b])
+            oq, ot = om.filter_numpy(idx, dist, 0.8, rev_idx)
+            n = int(nk[b])
+            assert n == len(oq) and np.array_equal(kq[b, :n].numpy(), oq) and np.array_equal(kt[b, :n].numpy(), ot)
+        qs, ts = synth.descriptors_batch(batch, nq, nt, seed=77 + batch)              # other data, same buffers
+    assert hm.h2d_bytes == batch * (nq + nt) * 32 and hm.d2h_bytes == 4 * batch * (2 * nq + 1)
