@@ -624,6 +624,8 @@ def run_gpu(args):
     # roofline of the dominant kernel (popc-bound per SURVEY 8d: 8 popc.b32 per pair distance)
     probe = ctypes.c_double()
     _cabi.check(lib.vslam_microbench_popc(4096, ctypes.byref(probe), None))
+    lop3 = ctypes.c_double()
+    _cabi.check(lib.vslam_microbench_lop3(4096, ctypes.byref(lop3), None))
     peaks, peak_kind = measured_peaks()
     popc_per_launch = 8.0 * B * NQ * NT
     achieved = popc_per_launch / (knn_ms * 1e-3) / 1e9
@@ -635,7 +637,12 @@ def run_gpu(args):
                                "integer-pipe entry)",
                 "note": "frac > 1 is expected: the kernel needs 4 POPC + 16 LOP3 per pair distance "
                         "(carry-save adder tree) instead of the 8 POPC the yardstick assumes",
-                "kernel_ms": knn_ms, "pair_distances_per_s": B * NQ * NT / (knn_ms * 1e-3)}
+                "kernel_ms": knn_ms, "pair_distances_per_s": B * NQ * NT / (knn_ms * 1e-3),
+                # the pipe that binds the kernel (ncu: ALU 83 % busy, XU/POPC 63 %): 16 LOP3 + 4 min/max per pair distance
+                "binding_pipe": {"pipe": "alu (LOP3 / VIMNMX)", "ops_per_pair_distance": 20,
+                                 "achieved": 20.0 * B * NQ * NT / (knn_ms * 1e-3) / 1e9, "peak": lop3.value / 1e9,
+                                 "unit": "Gop/s", "frac": 20.0 * B * NQ * NT / (knn_ms * 1e-3) / lop3.value,
+                                 "peak_source": "vslam_microbench_lop3 measured in this run (dependent-free lop3.b32)"}}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": n_warm, "preheat_steps": PREHEAT_STEPS, "remeasured": remeasured,
             "ms_per_step": ms / args.steps, "ms_per_step_stats": _stats(step_ms),

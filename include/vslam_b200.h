@@ -104,6 +104,12 @@ int vslam_match_filter(const int32_t* idx, const int32_t* dist,
  * the achieved popc/s in *popc_per_s (host pointer).
  */
 int vslam_microbench_popc(int iters, double* popc_per_s, void* stream);
+/*
+ * The same for the pipe that actually binds the kNN kernel (ncu: ALU 83 % busy): dependent-free three-input logic
+ * operations (lop3.b32) per second in *lop3_per_s.  The kernel issues 16 LOP3 + 4 min/max per 256-bit pair
+ * distance (carry-save popcount tree), all on that pipe.
+ */
+int vslam_microbench_lop3(int iters, double* lop3_per_s, void* stream);
 
 
 /* ------------------------------------------------------------------------- */
@@ -286,12 +292,8 @@ int vslam_list_diff(const double* kp1, int n1, const double* kp2, int n2, int mo
  *   kp         dev f32 [batch][max_corners][2], n_kp dev i32 [batch]        key points ORB keeps (31-px border)
  *   desc       dev u8  [batch][max_corners][32]                             their descriptors
  *   status     dev i32 [batch] or NULL   1 if an internal list overflowed (cannot happen for valid input)
- *
- * vslam_features_set_variant: which response kernel runs -- 0 automatic (by batch size), 1 warp-specialised
- * (latency), 2 one thread per column (throughput).  Both are bit-identical; tests and tuning only.
  */
 long long vslam_features_workspace_bytes(int batch, int H, int W, double min_distance);
-int vslam_features_set_variant(int variant);
 int vslam_extract_features(const uint8_t* img, int batch, int H, int W, int max_corners, double quality,
                            double min_distance, float cos_a, float sin_a, const int8_t* pattern,
                            void* workspace, long long workspace_bytes, float* eig, uint8_t* blur,
@@ -365,8 +367,8 @@ int vslam_ba_read(vslam_ba* ba, int what, double* dst, int64_t capacity, void* s
 int vslam_pcg_solve(const double* S, const double* b, double* x, int n, double tol, int max_iter,
                     int32_t* status_iters, void* stream);
 
-/* Tuning knob for bench sweeps: selects a tile/thread variant of the kNN kernel (0 = default). */
-int vslam_hamming_set_variant(int variant);
+/* The library holds no mutable state besides the device-attribute cache and the last-error string; the kernel
+ * variant selectors used by tools/ and tests/ are declared in visual_slam_b200/csrc/tuning.h, not here. */
 
 #ifdef __cplusplus
 }

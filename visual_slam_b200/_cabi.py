@@ -27,6 +27,7 @@ def _declare(lib):
     lib.vslam_hamming_knn2_ragged.argtypes = [vp, i32, vp, vp, i32, vp, vp, vp, vp, i32, vp]
     lib.vslam_match_filter.argtypes = [vp, vp, vp, i32, i32, f64, i32, vp, vp, vp, i32, vp]
     lib.vslam_microbench_popc.argtypes = [i32, C.POINTER(f64), vp]
+    lib.vslam_microbench_lop3.argtypes = [i32, C.POINTER(f64), vp]
     lib.vslam_hamming_set_variant.argtypes = [i32]
     pd = C.POINTER(f64)
     lib.vslam_pnp_hypotheses.argtypes = [vp, vp, vp, i32, i32, vp, i32, pd, vp, vp, vp]

@@ -11,6 +11,7 @@
 #include <cooperative_groups.h>
 
 #include "common.cuh"
+#include "tuning.h"
 
 namespace cg = cooperative_groups;
 

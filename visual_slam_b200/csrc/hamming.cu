@@ -19,6 +19,7 @@
 // The popcount of the 8 XOR words uses a carry-save adder tree (Harley-Seal), which
 // needs 4 POPC instead of 8: POPC is a quarter-rate pipe on sm_100, LOP3 is not.
 #include "common.cuh"
+#include "tuning.h"
 
 namespace vslam {
 
@@ -261,6 +262,26 @@ __global__ void __launch_bounds__(256) popc_probe_kernel(int iters, uint32_t see
   if (s == 0xdeadbeefu) out[0] = s;
 }
 
+// ALU-pipe probe: 8 chains per thread, each step = ONE lop3.b32 (majority of three chain values: no constant
+// operand to fold, every input depends on the previous step).
+__global__ void __launch_bounds__(256) lop3_probe_kernel(int iters, uint32_t seed, uint32_t* out) {
+  uint32_t acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = seed * 747796405u + threadIdx.x * 2654435761u + i * 40503u;
+  for (int it = 0; it < iters; ++it) {
+    uint32_t nxt[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      asm volatile("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(nxt[i]) : "r"(acc[i]), "r"(acc[(i + 1) & 7]), "r"(acc[(i + 3) & 7]));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = nxt[i];
+  }
+  uint32_t s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += acc[i];
+  if (s == 0xdeadbeefu) out[0] = s;
+}
+
 template <int THREADS, int QPT, int TT, bool CSA>
 static int launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
                        int32_t* dist, uint32_t* rev_key, int batch, cudaStream_t st,
@@ -343,8 +364,21 @@ extern "C" int vslam_match_filter(const int32_t* idx, const int32_t* dist, const
   return check_launch("match_filter_kernel");
 }
 
+template <typename Kernel>
+static int run_probe(Kernel kernel, const char* name, int iters, double* per_s, void* stream);
+
+extern "C" int vslam_microbench_lop3(int iters, double* lop3_per_s, void* stream) {
+  if (!lop3_per_s || iters <= 0) return VSLAM_ERR_BAD_ARG;
+  return run_probe(lop3_probe_kernel, "lop3_probe_kernel", iters, lop3_per_s, stream);
+}
+
 extern "C" int vslam_microbench_popc(int iters, double* popc_per_s, void* stream) {
   if (!popc_per_s || iters <= 0) return VSLAM_ERR_BAD_ARG;
+  return run_probe(popc_probe_kernel, "popc_probe_kernel", iters, popc_per_s, stream);
+}
+
+template <typename Kernel>
+static int run_probe(Kernel kernel, const char* name, int iters, double* popc_per_s, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int sms = sm_count();
   if (sms <= 0) return VSLAM_ERR_NO_DEVICE;
@@ -354,11 +388,11 @@ extern "C" int vslam_microbench_popc(int iters, double* popc_per_s, void* stream
   VSLAM_CUDA_TRY(cudaEventCreate(&e0));
   VSLAM_CUDA_TRY(cudaEventCreate(&e1));
   const int blocks = sms * 8;
-  popc_probe_kernel<<<blocks, 256, 0, st>>>(iters, 1u, out);  // warm-up
+  kernel<<<blocks, 256, 0, st>>>(iters, 1u, out);  // warm-up
   float best = 1e30f;
   for (int rep = 0; rep < 5; ++rep) {
     cudaEventRecord(e0, st);
-    popc_probe_kernel<<<blocks, 256, 0, st>>>(iters, 2u + rep, out);
+    kernel<<<blocks, 256, 0, st>>>(iters, 2u + rep, out);
     cudaEventRecord(e1, st);
     VSLAM_CUDA_TRY(cudaEventSynchronize(e1));
     float ms = 0.f;
@@ -369,5 +403,5 @@ extern "C" int vslam_microbench_popc(int iters, double* popc_per_s, void* stream
   cudaEventDestroy(e1);
   cudaFree(out);
   *popc_per_s = (double)blocks * 256.0 * (double)iters * 8.0 / ((double)best * 1e-3);
-  return check_launch("popc_probe_kernel");
+  return check_launch(name);
 }
