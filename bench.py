@@ -484,6 +484,156 @@ def tracking_figures(torch, dist, world, rank, dev, steps=3):
             "median_inliers": float(allr[:, 6].median().item()), "gpu_launches_per_pass": 6 * ((pairs + chunk - 1) // chunk)}
 
 
+def _best_ms(fn, reps=7):
+    fn()
+    best = 1e30
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        fn()
+        best = min(best, (time.perf_counter() - t0) * 1e3)
+    return best
+
+
+def latency_figures(torch):
+    """One call of every drop-in at the reference's real sizes (C1: ~940 ORB features per frame, ~220 PnP
+    correspondences, ~300 two-view matches, a 13-frame / 2.8k-observation local window, one VGA frame), host arrays in,
+    host arrays out -- wall clock (perf_counter) around the call a user makes, copies and synchronisation included --
+    next to the reference's own CPU call on the same inputs.  Best of 7 after one warm-up call."""
+    import cv2
+    from oracle import ba as oba
+    from oracle import matching as om
+    from visual_slam_b200 import FeatureMatcher, synth
+    from visual_slam_b200.ba import BundleAdjustment
+    from visual_slam_b200.ba_problem import synthetic_ba
+    from visual_slam_b200.features import FeatureExtractor
+    from visual_slam_b200.pnp import solvePnPRansac
+    from visual_slam_b200.twoview import estimateEssential, estimateRelativePose
+    fx, fy, cx, cy = synth.ICL_K
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1.0]])
+    out = {}
+    # matching, 940 x 940 (ORB-1000 on ICL-NUIM, SURVEY 6)
+    q, t, _ = synth.descriptors_pair(940, 940, seed=5)
+    kp = np.zeros((940, 2), np.float32)
+    fm = FeatureMatcher()
+    out["match_features_940x940"] = {"gpu_ms": _best_ms(lambda: fm.match_features(kp, q, kp, t)),
+                                     "cpu_ms": _best_ms(lambda: om.match_features_cv2(kp, q, kp, t)),
+                                     "cpu": "cv2.BFMatcher(NORM_HAMMING).knnMatch + ratio loop (frame.py:20-49)"}
+    # PnP, 220 correspondences as main.py:196 calls it
+    X, uv, rvec, tvec, _ = synth.tracking_pair(11, 220)
+    g_r, g_t = (rvec * 0.9).reshape(3, 1), tvec * 0.9
+    out["solvePnPRansac_220"] = {
+        "gpu_ms": _best_ms(lambda: solvePnPRansac(X.reshape(-1, 1, 3), uv.reshape(-1, 1, 2), K, np.array([]),
+                                                  g_r.copy(), g_t.copy(), True)),
+        "cpu_ms": _best_ms(lambda: cv2.solvePnPRansac(objectPoints=X.reshape(-1, 1, 3), imagePoints=uv.reshape(-1, 1, 2),
+                                                      cameraMatrix=K, distCoeffs=np.array([]), rvec=g_r.copy(),
+                                                      tvec=g_t.copy(), useExtrinsicGuess=True)),
+        "cpu": "cv2.solvePnPRansac (main.py:196-197)"}
+    # two-view initialisation, 300 matches: estimateEssential + estimateRelativePose (main.py:103,111)
+    p1, p2, _, _, _ = synth.two_view_pair(3, 300)
+    ft = np.zeros((300, 32), np.uint8)
+
+    def gpu_twoview():
+        E, inl, _ = estimateEssential(p1, p2, K, 3.0 / fx)
+        sel = inl.ravel() == 1
+        return estimateRelativePose(E, p1[sel], p2[sel], ft[sel], ft[sel], K, "Essential")
+
+    def cpu_twoview():      # helper_functions.py:47-70 (without its unused epiline score) and :164-195
+        a = cv2.undistortPoints(np.expand_dims(p1, axis=1), cameraMatrix=K, distCoeffs=None)
+        b = cv2.undistortPoints(np.expand_dims(p2, axis=1), cameraMatrix=K, distCoeffs=None)
+        E, inl = cv2.findEssentialMat(np.squeeze(a), np.squeeze(b), method=cv2.RANSAC, prob=0.999, threshold=3.0 / fx)
+        sel = inl.ravel() == 1
+        _, R, tt, mask, tri = cv2.recoverPose(E, p1[sel], p2[sel], cameraMatrix=K, distanceThresh=50)
+        return [row for row, m in zip(p1[sel], mask.ravel()) if m == 255]
+    out["estimateEssential+estimateRelativePose_300"] = {
+        "gpu_ms": _best_ms(gpu_twoview), "cpu_ms": _best_ms(cpu_twoview),
+        "cpu": "cv2.undistortPoints + findEssentialMat(RANSAC) + recoverPose + the mask loop"}
+    # motion-only BA of a 13-frame local window with ~2.8k observations (SURVEY 3.4), through the Map interface
+    pb = synthetic_ba(n_cams=13, n_pts=237, obs_per_pt=13.0, seed=4, motion_only=True)
+
+    def gpu_ba():
+        m = synth.map_from_problem(pb)
+        m.frames[0].kf = True
+        BundleAdjustment(synth.IclCamera()).motionOnlyBundleAdjustement(m)
+        return m
+
+    def cpu_ba():
+        return oba.optimize(pb.copy(), 10)
+    build_ms = _best_ms(lambda: synth.map_from_problem(pb), 3)
+    out["motionOnlyBundleAdjustement_13x%d" % pb.n_obs] = {
+        "gpu_ms": _best_ms(gpu_ba) - build_ms, "cpu_ms": _best_ms(cpu_ba, 3),
+        "cpu": "oracle/ba.py restatement (NOT g2o, which cannot run here), arrays prepared outside the clock; the "
+               "drop-in's figure includes its graph construction from the Map"}
+    # features of one VGA frame (frame.py:10-14, ORB variant)
+    img = synth.frames(1, 480, 640, seed=9)[0]
+    fe = FeatureExtractor()
+    orb = cv2.ORB_create()
+
+    def cpu_feat():
+        pts = cv2.goodFeaturesToTrack(np.mean(img, axis=2).astype(np.uint8), 3000, qualityLevel=0.01, minDistance=7)
+        kps = [cv2.KeyPoint(x=f[0][0], y=f[0][1], size=20) for f in pts]
+        k2, des = orb.compute(img, kps)
+        return cv2.KeyPoint_convert(k2), des
+    out["compute_features_vga"] = {"gpu_ms": _best_ms(lambda: fe.compute_features(img)), "cpu_ms": _best_ms(cpu_feat, 3),
+                                   "cpu": "cv2.goodFeaturesToTrack + ORB.compute (frame.py:10-14)"}
+    for v in out.values():
+        v["gpu_over_cpu"] = v["gpu_ms"] / v["cpu_ms"]
+    out["note"] = ("wall clock of ONE call with host arrays (the reference's per-frame usage); cv2 threads = %d"
+                   % cv2.getNumThreads())
+    return out
+
+
+def twoview_figures(torch, pairs=1024, n=512, hyp=256, steps=5):
+    """Map-initialisation geometry, batched and device-resident: `pairs` frame pairs x n correspondences,
+    essential-matrix RANSAC (five-point hypotheses, Sampson scoring, cv2's budget rule) + recoverPose; the
+    reference's cv2 calls on the same pairs, one after the other, beside it."""
+    import cv2
+    from visual_slam_b200 import synth, twoview
+    dev = torch.device("cuda")
+    data = [synth.two_view_pair(s, n) for s in range(32)]
+    p1 = torch.from_numpy(np.stack([d[0] for d in data])).to(dev).repeat(pairs // 32, 1, 1).contiguous()
+    p2 = torch.from_numpy(np.stack([d[1] for d in data])).to(dev).repeat(pairs // 32, 1, 1).contiguous()
+    n_pts = torch.full((pairs,), n, dtype=torch.int32, device=dev)
+    words = torch.from_numpy(np.random.default_rng(3).integers(0, 2 ** 32, size=(pairs, hyp, 5), dtype=np.uint64)
+                             .astype(np.uint32).view(np.int32)).to(dev)
+    K = synth.ICL_K
+
+    def one():
+        x1, x2 = twoview.undistort_points(p1, K), twoview.undistort_points(p2, K)
+        o = twoview.essential_ransac_batch(x1, x2, n_pts, words, 3.0 / K[0])
+        r = twoview.recover_pose_batch(o["E"], p1, p2, n_pts, K, 50.0)
+        return o, r
+    o, r = one()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        o, r = one()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    fx, fy, cx, cy = K
+    Km = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1.0]])
+    t0, k = time.perf_counter(), 0
+    while time.perf_counter() - t0 < 3.0:
+        a, b = data[k % 32][0], data[k % 32][1]
+        ua = np.squeeze(cv2.undistortPoints(np.expand_dims(a, 1), cameraMatrix=Km, distCoeffs=None))
+        ub = np.squeeze(cv2.undistortPoints(np.expand_dims(b, 1), cameraMatrix=Km, distCoeffs=None))
+        E, inl = cv2.findEssentialMat(ua, ub, method=cv2.RANSAC, prob=0.999, threshold=3.0 / fx)
+        sel = inl.ravel() == 1
+        cv2.recoverPose(E, a[sel], b[sel], cameraMatrix=Km, distanceThresh=50)
+        k += 1
+    cpu_dt = time.perf_counter() - t0
+    Rt = np.stack([d[2] for d in data])
+    err = (r["R"][:32].cpu().numpy() - Rt)
+    return {"pairs_per_s": pairs / (ms * 1e-3), "ms_per_batch": ms, "pairs": pairs, "correspondences": n,
+            "hypotheses": hyp, "median_inliers": float(o["n_inliers"].float().median().item()),
+            "max_R_err_vs_truth": float(np.abs(err).max()), "gpu_launches_per_step": 6,
+            "cpu_reference": {"pairs_per_s": k / cpu_dt, "pairs": k, "seconds": cpu_dt,
+                              "kind": "reference: cv2.undistortPoints + findEssentialMat(RANSAC, 0.999) + recoverPose "
+                                      "per pair (helper_functions.py:47-70, :164-195), serial inside cv2"},
+            "what": "undistort + 5-point RANSAC (hypotheses, Sampson scoring, selection) + recoverPose, device-resident"}
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -665,6 +815,9 @@ def run_gpu(args):
             features = features_figures(torch)
         if tracking:
             tracking["cpu_pnp"] = cpu_pnp(3.0)
+            line["twoview"] = twoview_figures(torch)
+        if not args.skip_latency:
+            line["latency"] = latency_figures(torch)
         if not args.skip_ba:
             ba = ba_figures(torch)
             ba["cpu_restatement_c3"] = cpu_ba_restatement()
@@ -697,6 +850,7 @@ def main():
     ap.add_argument("--skip-ba", action="store_true")
     ap.add_argument("--skip-tracking", action="store_true")
     ap.add_argument("--skip-features", action="store_true")
+    ap.add_argument("--skip-latency", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

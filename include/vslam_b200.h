@@ -322,6 +322,13 @@ int vslam_ba_create(vslam_ba** out, int n_cams, int n_pts, int n_obs, int n_scal
                     const int32_t* obs_cam, const int32_t* obs_pt,
                     const uint8_t* cam_fixed, const uint8_t* pt_fixed,
                     const int32_t* scale_a, const int32_t* scale_b);
+/* Re-uses a problem object for another structure (same arguments as vslam_ba_create): device buffers are kept
+ * while the new sizes fit (capacity doubles otherwise), so the per-call cudaMalloc / cudaFree of building a fresh
+ * optimiser for every BA call -- what the reference does (src/v2/main.py:146,213,322) -- disappears.  Synchronises
+ * the device; vslam_ba_set_state must follow. */
+int vslam_ba_set_structure(vslam_ba* ba, int n_cams, int n_pts, int n_obs, int n_scale,
+                           const int32_t* obs_cam, const int32_t* obs_pt, const uint8_t* cam_fixed,
+                           const uint8_t* pt_fixed, const int32_t* scale_a, const int32_t* scale_b);
 int vslam_ba_destroy(vslam_ba* ba);
 int vslam_ba_set_state(vslam_ba* ba, const double* cams, const double* pts, const double* obs_uv,
                        const double* scale_meas, const double* K, void* stream);

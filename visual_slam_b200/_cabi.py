@@ -55,6 +55,7 @@ def _declare(lib):
     pp = C.POINTER(vp)
     lib.vslam_ba_create.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.vslam_ba_destroy.argtypes = [vp]
+    lib.vslam_ba_set_structure.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.vslam_ba_set_state.argtypes = [vp, vp, vp, vp, vp, C.POINTER(f64), vp]
     lib.vslam_ba_get_state.argtypes = [vp, vp, vp, vp]
     lib.vslam_ba_set_solver.argtypes = [vp, f64, i32]

@@ -20,18 +20,25 @@ class BAEngine:
         if not torch.cuda.is_available():
             raise _cabi.VslamError("visual_slam_b200 needs a CUDA device (no CPU fallback)")
         self.device = torch.device(device)
-        self.prob = prob
         self._h = C.c_void_p()
+        self.set_structure(prob)
+
+    def set_structure(self, prob):
+        """(Re)builds the problem structure for `prob` and uploads its state.  An engine that already exists keeps
+        its device buffers while the new sizes fit (vslam_ba_set_structure): no cudaMalloc / cudaFree per BA call."""
+        self.prob = prob
         oc, op = _i32(prob.obs_cam), _i32(prob.obs_pt)
         cf = np.ascontiguousarray(prob.cam_fixed, dtype=np.uint8)
         pf = np.ascontiguousarray(prob.pt_fixed, dtype=np.uint8)
         sa, sb = _i32(prob.scale_a), _i32(prob.scale_b)
         self._keep = (oc, op, cf, pf, sa, sb)
         p = lambda a: a.ctypes.data_as(C.c_void_p) if a.size else None  # noqa: E731
+        args = (prob.n_cams, prob.n_pts, prob.n_obs, prob.n_scale, p(oc), p(op), p(cf), p(pf), p(sa), p(sb))
         with torch.cuda.device(self.device):
-            _cabi.check(_cabi.lib().vslam_ba_create(
-                C.byref(self._h), prob.n_cams, prob.n_pts, prob.n_obs, prob.n_scale,
-                p(oc), p(op), p(cf), p(pf), p(sa), p(sb)))
+            if self._h:
+                _cabi.check(_cabi.lib().vslam_ba_set_structure(self._h, *args))
+            else:
+                _cabi.check(_cabi.lib().vslam_ba_create(C.byref(self._h), *args))
         self.set_state(prob.cams, prob.pts, prob.obs_uv, prob.scale_meas, prob.K)
 
     def close(self):
@@ -148,16 +155,32 @@ def pcg_solve(S, b, tol=1e-10, max_iter=2000):
     return x, int(out[0]), int(out[1])
 
 
+_POOL = {}    # device -> BAEngine kept between calls: the reference builds a fresh optimiser for EVERY BA call
+              # (main.py:146,213,322); here only the structure arrays change, the device buffers stay
+
+
 def solve_problem(prob, max_iterations=10, device="cuda:0", pcg_tol=1e-10):
-    """Host-buffer entry: optimise a BAProblem in place (H2D, LM on the GPU, D2H)."""
-    eng = BAEngine(prob, device)
+    """Host-buffer entry: optimise a BAProblem in place (H2D, LM on the GPU, D2H).  The engine object of a device
+    is re-used from call to call (capacity-based buffers, see BAEngine.set_structure)."""
+    key = str(torch.device(device))
+    eng = _POOL.get(key)
+    if eng is None:
+        eng = _POOL[key] = BAEngine(prob, device)
+    else:
+        eng.set_structure(prob)
     eng.set_solver(pcg_tol)
     stats = eng.optimize(max_iterations)
     cams, pts = eng.get_state()
     prob.cams = cams.cpu().numpy()
     prob.pts = pts.cpu().numpy()
-    eng.close()
     return stats
+
+
+def release_pool():
+    """Frees the pooled engines (their device memory)."""
+    for eng in _POOL.values():
+        eng.close()
+    _POOL.clear()
 
 
 class _Pose:

@@ -90,6 +90,14 @@ class FeatureMatcher:
     def __init__(self, cross_check=False, device="cuda:0"):
         self.cross_check = bool(cross_check)
         self.device = torch.device(device)
+        self._pin_in = self._pin_out = None      # pinned staging, grown on demand and kept between calls
+
+    def _staging(self, n_in, n_out):
+        if self._pin_in is None or self._pin_in.numel() < n_in:
+            self._pin_in = torch.empty(max(n_in, 1 << 16), dtype=torch.uint8).pin_memory()
+        if self._pin_out is None or self._pin_out.numel() < n_out:
+            self._pin_out = torch.empty(max(n_out, 1 << 12), dtype=torch.int32).pin_memory()
+        return self._pin_in, self._pin_out
 
     def match_features(self, kp1, desc1, kp2, desc2, ratio=0.8):
         import cv2  # only to build cv2.DMatch return objects, as callers expect (main.py:187,216)
@@ -103,16 +111,28 @@ class FeatureMatcher:
             # the reference unpacks `for m, n in rawMatches` (frame.py:30) and raises here too
             raise ValueError("not enough values to unpack (expected 2, got %d)" % desc2.shape[0])
         _require_cuda()
-        q = torch.from_numpy(desc1).to(self.device, non_blocking=True)[None]
-        t = torch.from_numpy(desc2).to(self.device, non_blocking=True)[None]
-        out = match_batch(q, t, ratio, self.cross_check)
-        n = int(out["n_keep"][0].item())
-        kq = out["keep_q"][0, :n].cpu().numpy()
-        kt = out["keep_t"][0, :n].cpu().numpy()
-        d0 = out["dist"][0, :, 0].cpu().numpy()
-        matches = [[cv2.DMatch(int(a), int(b), 0, float(d0[a]))] for a, b in zip(kq, kt)]
+        nq, nt = desc1.shape[0], desc2.shape[0]
         kp1 = np.asarray(kp1)
         kp2 = np.asarray(kp2)
+        if nq == 0:
+            e = np.asarray([])
+            return [], e, e.copy(), e.copy(), e.copy()
+        # ONE host->device copy (both descriptor sets through a pinned buffer), the kernels, ONE device->host copy of
+        # the packed result (count, kept query / train rows, best distances), one stream synchronisation
+        pin_in, pin_out = self._staging((nq + nt) * 32, 1 + 3 * nq)
+        pin_in[:nq * 32].view(nq, 32).numpy()[:] = desc1
+        pin_in[nq * 32:(nq + nt) * 32].view(nt, 32).numpy()[:] = desc2
+        with torch.cuda.device(self.device):
+            both = pin_in[:(nq + nt) * 32].to(self.device, non_blocking=True)
+            out = match_batch(both[:nq * 32].view(1, nq, 32), both[nq * 32:].view(1, nt, 32), ratio, self.cross_check)
+            packed = torch.cat([out["n_keep"], out["keep_q"][0], out["keep_t"][0], out["dist"][0, :, 0]])
+            res = pin_out[:1 + 3 * nq]
+            res.copy_(packed, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+        r = res.numpy()
+        n = int(r[0])
+        kq, kt, d0 = r[1:1 + n].copy(), r[1 + nq:1 + nq + n].copy(), r[1 + 2 * nq:]
+        matches = [[cv2.DMatch(a, b, 0, d)] for a, b, d in zip(kq.tolist(), kt.tolist(), d0[kq].astype(np.float64).tolist())]
         if n == 0:
             e = np.asarray([])
             return matches, e, e.copy(), e.copy(), e.copy()

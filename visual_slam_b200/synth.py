@@ -231,3 +231,61 @@ def c5_pairs(seq, lo, hi, n=2048, device="cpu", planted=0.7, flip=0.10, wrong_pi
     kp_cur[bi, dst] = torch.where(bad[:, :, None], rnd, pix)
     return {"desc_kf": desc_kf, "desc_cur": desc_cur, "map_xyz": Xw.float(), "kp_cur": kp_cur.float(),
             "pose_true": pose_true, "guess": guess}
+
+
+# ---- reference-style containers around a synthetic BA problem (for the drop-in BundleAdjustment's Map interface) ----
+class SynthFrame:
+    """What LocalBA.py touches of the reference's Frame (src/v2/frame.py:51-125)."""
+
+    def __init__(self, fid, pose, kf=False):
+        self.ID, self.pose, self.kf, self.parents = fid, pose, kf, {}
+
+    def GetPose(self): return self.pose
+    def GetParentIDs(self): return self.parents.keys()
+    def GetTransitionWithParentID(self, pid): return self.parents[pid]
+    def IsKeyFrame(self): return self.kf
+    def GetID(self): return self.ID
+
+
+class SynthPoint:
+    """... of Point (src/v2/point.py)."""
+
+    def __init__(self, pid, xyz):
+        self.ID, self.location_3d, self.frames = pid, xyz, {}
+
+    def GetFrame(self, fid): return self.frames.get(fid)
+    def Get3dPoint(self): return self.location_3d
+    def GetID(self): return self.ID
+
+
+class SynthMap:
+    """... of Map (src/v2/map.py)."""
+
+    def __init__(self): self.frames, self.points_3d = {}, {}
+    def GetFrame(self, fid): return self.frames[fid]
+    def GetPoint(self, pid): return self.points_3d[pid]
+    def UpdatePose(self, new_pose, frame_id): self.frames[frame_id].pose = new_pose
+    def UpdatePoint3D(self, new_point, point_id): self.points_3d[point_id].location_3d = new_point
+
+
+class IclCamera:
+    fx, fy, cx, cy = ICL_K
+
+
+def map_from_problem(p):
+    """A reference-style Map holding the BAProblem `p`: frame ids = camera rows, point ids = point rows, scale edges
+    as parent links whose stored relative translation has the measured norm."""
+    from .ba_problem import quat_to_R
+    m = SynthMap()
+    for c in range(p.n_cams):
+        T = np.eye(4); T[:3, :3] = quat_to_R(p.cams[c, :4]); T[:3, 3] = p.cams[c, 4:]
+        m.frames[c] = SynthFrame(c, T)
+    for k in range(p.n_scale):
+        a, b = int(p.scale_a[k]), int(p.scale_b[k])
+        rel = np.eye(4); rel[:3, 3] = [p.scale_meas[k], 0, 0]
+        m.frames[b].parents[a] = rel
+    for j in range(p.n_pts):
+        m.points_3d[j] = SynthPoint(j, p.pts[j].copy())
+    for o in range(p.n_obs):
+        m.points_3d[int(p.obs_pt[o])].frames[int(p.obs_cam[o])] = (m.frames[int(p.obs_cam[o])], p.obs_uv[o], None)
+    return m
