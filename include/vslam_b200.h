@@ -234,6 +234,16 @@ int vslam_essential_select(const float* x1, const float* x2, const int32_t* n_pt
                            double thr, double confidence, int32_t* best, double* E, uint8_t* mask,
                            int32_t* n_inliers, double* score, void* stream);
 /*
+ * The iteration budget cv2's RANSAC loop (RANSACUpdateNumIters) has left after the first H hypotheses of a run
+ * that started with max_iters iterations.  A caller that generates hypotheses in rounds may stop at the first
+ * prefix with budget <= H: vslam_essential_select on that prefix returns the model of the full max_iters run.
+ *   n_models dev i32 [batch][H], counts dev i32 [batch][H][10], budget dev i32 [batch]
+ */
+int vslam_essential_budget(const int32_t* n_pts, int n_max, int batch, const int32_t* n_models,
+                           const int32_t* counts, int H, int max_iters, double confidence, int32_t* budget,
+                           void* stream);
+
+/*
  * cv2.recoverPose(E, p1, p2, cameraMatrix=K, distanceThresh) (reference helper_functions.py:176).
  *   E dev f64 [batch][9];  p1, p2 dev f32 [batch][n_max][2] PIXEL coordinates;  K host f64[4]
  *   R dev f64 [batch][9];  t dev f64 [batch][3] (unit);  mask dev u8 [batch][n_max] in {0,255}

@@ -18,7 +18,8 @@ def test_packing_matches_the_drop_in_graph_builder():
     m = _map_from_problem(p)
     ba = BundleAdjustment.__new__(BundleAdjustment)          # graph construction only: no device needed
     ba.fx, ba.fy, ba.cx, ba.cy = _Cam.fx, _Cam.fy, _Cam.cx, _Cam.cy
-    ba._poses, ba._points, ba._edges, ba._scale, ba._result = {}, {}, [], [], None
+    ba._poses, ba._points, ba._scale, ba._result = {}, {}, [], None
+    ba._e_pt, ba._e_pose, ba._e_uv = [], [], []
     frame_ids = list(m.frames.keys())
     for fid in frame_ids:
         fr = m.GetFrame(fid)

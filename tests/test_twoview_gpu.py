@@ -165,3 +165,27 @@ def test_drop_in_signatures_and_golden_g1():
     assert agree > 0.9
     with pytest.raises(NotImplementedError):
         twoview.estimateRelativePose(np.eye(3), p1, p2, f, f, np.eye(3), "Homography")
+
+
+def test_round_based_single_pair_ransac_equals_the_full_run():
+    """essential_ransac_single solves the hypotheses in rounds and stops once cv2's iteration budget
+    (RANSACUpdateNumIters, started at maxIters) is covered: same model, mask and support as solving all maxIters
+    hypotheses, for easy pairs (stop after the first round), hard ones (60 % wrong matches) and pure noise."""
+    import torch
+    from visual_slam_b200 import synth, twoview
+    for seed, n, outl in ((1, 300, 0.2), (2, 400, 0.6), (3, 120, 0.75), (4, 200, 1.0)):
+        p1, p2, _, _, _ = synth.two_view_pair(seed, n, outlier_frac=outl)
+        both = twoview.undistort_points(torch.from_numpy(np.stack([p1, p2])).cuda(), synth.ICL_K)
+        words = torch.from_numpy(np.random.default_rng(seed).integers(0, 2 ** 32, size=(1, 1000, 5), dtype=np.uint64)
+                                 .astype(np.uint32).view(np.int32)).cuda()
+        n_pts = torch.tensor([n], dtype=torch.int32, device="cuda")
+        thr = 3.0 / synth.ICL_K[0]
+        full = twoview.essential_ransac_batch(both[0:1], both[1:2], n_pts, words, thr)
+        part = twoview.essential_ransac_single(both[0:1], both[1:2], n, words, thr)
+        assert int(full["best"][0]) == int(part["best"][0])
+        assert torch.equal(full["E"], part["E"]) and torch.equal(full["mask"], part["mask"])
+        assert int(full["n_inliers"][0]) == int(part["n_inliers"][0])
+        if outl <= 0.2:
+            assert part["hypotheses_solved"] == 48          # cv2 would have stopped after ~20 iterations as well
+        if outl >= 0.75:
+            assert part["hypotheses_solved"] == 1000

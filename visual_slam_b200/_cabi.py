@@ -44,6 +44,7 @@ def _declare(lib):
     lib.vslam_essential_score.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, f64, vp, vp]
     lib.vslam_essential_select.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, i32, f64, f64, vp, vp, vp, vp,
                                            vp, vp]
+    lib.vslam_essential_budget.argtypes = [vp, i32, i32, vp, vp, i32, i32, f64, vp, vp]
     lib.vslam_recover_pose.argtypes = [vp, vp, vp, vp, i32, i32, pd, f64, vp, vp, vp, vp, vp, vp]
     lib.vslam_triangulate.argtypes = [vp, vp, vp, vp, vp, i32, i32, f64, vp, vp, vp, vp, vp]
     lib.vslam_list_diff.argtypes = [vp, i32, vp, i32, i32, vp, vp, vp, vp]

@@ -211,7 +211,8 @@ class BundleAdjustment:
         self.principal_point = (camera.cx, camera.cy)
         self.baseline = 0
         self.device = device
-        self._poses, self._points, self._edges, self._scale = {}, {}, [], []
+        self._poses, self._points, self._scale = {}, {}, []
+        self._e_pt, self._e_pose, self._e_uv = [], [], []     # edges as three parallel lists (bulk-converted once)
         self._result = None
         self.stats = None
 
@@ -224,12 +225,14 @@ class BundleAdjustment:
         if point_id in self._points:
             print("WARNING: tried to add already existing point!")  # LocalBA.py:77
             return
-        self._points[point_id] = (np.asarray(point, dtype=np.float64).reshape(3), bool(fixed))
+        self._points[point_id] = (point, bool(fixed))
 
     def add_edge(self, point_id, pose_id, measurement, edge_id=None, information=None, robust_kernel=None):
         if information is not None and not np.array_equal(np.asarray(information), np.identity(2)):
             raise ValueError("only the reference's information matrix I2 is supported")
-        self._edges.append((point_id, pose_id, np.asarray(measurement, dtype=np.float64).reshape(2)))
+        self._e_pt.append(point_id)
+        self._e_pose.append(pose_id)
+        self._e_uv.append(measurement)
 
     def AddScalingEdge(self, parent_id, child_id, measurement, information=None, robust_kernel=None):
         m = np.asarray(measurement, dtype=np.float64)
@@ -239,12 +242,13 @@ class BundleAdjustment:
         pid = {k: i for i, k in enumerate(self._poses)}
         qid = {k: i for i, k in enumerate(self._points)}
         cams = np.array([v[0] for v in self._poses.values()]).reshape(-1, 7)
-        pts = np.array([v[0] for v in self._points.values()]).reshape(-1, 3)
+        pts = np.asarray([v[0] for v in self._points.values()], dtype=np.float64).reshape(-1, 3)
         cf = np.array([v[1] for v in self._poses.values()], dtype=bool)
         pf = np.array([v[1] for v in self._points.values()], dtype=bool)
-        oc = np.array([pid[e[1]] for e in self._edges], dtype=np.int32)
-        op = np.array([qid[e[0]] for e in self._edges], dtype=np.int32)
-        uv = np.array([e[2] for e in self._edges]).reshape(-1, 2)
+        oc = np.fromiter(map(pid.__getitem__, self._e_pose), dtype=np.int32, count=len(self._e_pose))
+        op = np.fromiter(map(qid.__getitem__, self._e_pt), dtype=np.int32, count=len(self._e_pt))
+        uv = (np.concatenate([np.ravel(u) for u in self._e_uv]) if self._e_uv and not isinstance(self._e_uv[0], np.ndarray)
+              else np.concatenate(self._e_uv) if self._e_uv else np.zeros(0)).astype(np.float64).reshape(-1, 2)
         sa = np.array([pid[s[0]] for s in self._scale], dtype=np.int32)
         sb = np.array([pid[s[1]] for s in self._scale], dtype=np.int32)
         sm = np.array([s[2] for s in self._scale], dtype=np.float64)
@@ -312,16 +316,22 @@ class BundleAdjustment:
 
     def _add_points_and_edges(self, map, frame_ids, point_ids, fixed):
         fset = set(frame_ids)
+        e_pt, e_pose, e_uv = self._e_pt, self._e_pose, self._e_uv
         for point_id in point_ids:
             point_obj = map.GetPoint(point_id)
             self.add_point(point_id=point_id, point=point_obj.Get3dPoint(), fixed=fixed)
             # the reference probes every frame per point (LocalBA.py:168-172); Point.frames is the
-            # dict it probes (point.py:14-46), so walking it directly yields the same edge set
-            for frame_id in frame_ids if not hasattr(point_obj, "frames") else point_obj.frames:
-                if frame_id not in fset:
-                    continue
-                corr = point_obj.GetFrame(frame_id)
-                if corr is not None:
-                    _, uv, _ = corr
-                    self.add_edge(point_id=point_id, pose_id=frame_id, measurement=uv,
-                                  edge_id=point_id * frame_id + 10000000)
+            # dict it probes (point.py:14-46), so walking it directly yields the same edge set (edge ids,
+            # point_id * frame_id + 10000000 there, are not used by the solver)
+            frames = getattr(point_obj, "frames", None)
+            if frames is None:
+                for frame_id in frame_ids:
+                    corr = point_obj.GetFrame(frame_id)
+                    if corr is not None:
+                        self.add_edge(point_id=point_id, pose_id=frame_id, measurement=corr[1])
+                continue
+            for frame_id, corr in frames.items():
+                if frame_id in fset and corr is not None:
+                    e_pt.append(point_id)
+                    e_pose.append(frame_id)
+                    e_uv.append(corr[1])

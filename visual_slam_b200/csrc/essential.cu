@@ -220,6 +220,29 @@ essential_select_kernel(const float* __restrict__ x1, const float* __restrict__ 
   }
 }
 
+// The iteration budget cv2's RANSAC loop is left with after the first H hypotheses of a run that started with
+// max_iters: lets a caller generate hypotheses in rounds and stop as soon as budget <= H, with the result of
+// the full run (essential_select_kernel on that prefix picks the same model).  One thread per pair.
+__global__ void essential_budget_kernel(const int32_t* __restrict__ n_pts, int n_max, int batch, int H, int max_iters,
+                                        const int32_t* __restrict__ n_models, const int32_t* __restrict__ counts,
+                                        double confidence, int32_t* __restrict__ budget) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  const int n = min(max(n_pts[b], 0), n_max);
+  int niters = max_iters, best_count = 0;
+  for (int it = 0; it < niters && it < H; ++it) {
+    const int nm = n_models[(size_t)b * H + it];
+    for (int m = 0; m < nm && m < kEssMaxModels; ++m) {
+      const int c = counts[((size_t)b * H + it) * kEssMaxModels + m];
+      if (c > max(best_count, kEssSample - 1)) {
+        best_count = c;
+        niters = ess_update_num_iters(confidence, (double)(n - c) / (double)n, kEssSample, niters);
+      }
+    }
+  }
+  budget[b] = niters;
+}
+
 // cv2.recoverPose: one CTA per pair.  Pass 1 counts, for each of the four (R, t) candidates, the
 // points that triangulate in front of both cameras and closer than `dist`; the candidate with the
 // most survivors wins (cv2's order of preference on ties); pass 2 writes its mask (0 / 255) and the
@@ -355,6 +378,17 @@ extern "C" int vslam_essential_select(const float* x1, const float* x2, const in
       x1, x2, n_pts, n_max, H, models, n_models, counts, (float)(thr * thr), confidence, best, E, mask,
       n_inliers, score);
   return check_launch("essential_select_kernel");
+}
+
+extern "C" int vslam_essential_budget(const int32_t* n_pts, int n_max, int batch, const int32_t* n_models,
+                                      const int32_t* counts, int H, int max_iters, double confidence,
+                                      int32_t* budget, void* stream) {
+  if (batch < 0 || H < 0 || n_max < 0 || max_iters < 0) return VSLAM_ERR_BAD_ARG;
+  if (batch == 0) return VSLAM_OK;
+  if (!n_pts || !budget || (H > 0 && (!n_models || !counts))) return VSLAM_ERR_BAD_ARG;
+  essential_budget_kernel<<<(batch + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
+      n_pts, n_max, batch, H, max_iters, n_models, counts, confidence, budget);
+  return check_launch("essential_budget_kernel");
 }
 
 extern "C" int vslam_recover_pose(const double* E, const float* p1, const float* p2, const int32_t* n_pts,

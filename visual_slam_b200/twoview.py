@@ -97,6 +97,40 @@ def essential_ransac_batch(x1, x2, n_pts, words, thr, confidence=DEFAULT_CONF):
     return out
 
 
+def essential_budget(n_pts, n_max, n_models, counts, max_iters, confidence=DEFAULT_CONF):
+    """Iteration budget left after the first H = n_models.shape[1] hypotheses of a max_iters run: i32 [B] (device)."""
+    B, H = n_models.shape[0], n_models.shape[1]
+    out = torch.empty((B,), dtype=torch.int32, device=n_models.device)
+    with torch.cuda.device(n_models.device):
+        _cabi.check(_cabi.lib().vslam_essential_budget(
+            _cabi.ptr(n_pts), int(n_max), B, _cabi.ptr(n_models.contiguous()), _cabi.ptr(counts.contiguous()), H,
+            int(max_iters), float(confidence), _cabi.ptr(out), _cabi.stream_ptr()))
+    return out
+
+
+def essential_ransac_single(x1, x2, n, words, thr, confidence=DEFAULT_CONF, rounds=(48, 192)):
+    """One pair (x1, x2 f32 [1,n,2]; words [1,H,5]), hypotheses generated in rounds: cv2's loop shrinks its budget as
+    soon as a well-supported model appears (typically after a few dozen of the 1000 iterations), so the later
+    samples are never drawn there; here they are never solved either.  Same result as essential_ransac_batch."""
+    dev, H = x1.device, words.shape[1]
+    n_pts = torch.tensor([n], dtype=torch.int32, device=dev)
+    models = torch.empty((1, H, MAX_MODELS, 9), dtype=torch.float64, device=dev)
+    n_models = torch.empty((1, H), dtype=torch.int32, device=dev)
+    counts = torch.empty((1, H, MAX_MODELS), dtype=torch.int32, device=dev)
+    lo = 0
+    for hi in [r for r in rounds if r < H] + [H]:
+        m, nm = essential_hypotheses(x1, x2, n_pts, words[:, lo:hi].contiguous())
+        models[:, lo:hi], n_models[:, lo:hi] = m, nm
+        counts[:, lo:hi] = essential_score(x1, x2, n_pts, m, nm, thr)
+        lo = hi
+        if hi < H and int(essential_budget(n_pts, x1.shape[1], n_models[:, :hi], counts[:, :hi], H, confidence)[0]) <= hi:
+            break
+    out = essential_select(x1, x2, n_pts, models[:, :lo].contiguous(), n_models[:, :lo].contiguous(),
+                           counts[:, :lo].contiguous(), thr, confidence)
+    out.update(models=models[:, :lo], n_models=n_models[:, :lo], counts=counts[:, :lo], hypotheses_solved=lo)
+    return out
+
+
 def recover_pose_batch(E, p1, p2, n_pts, K, distance_thresh=50.0):
     """E f64 [B,3,3], p1/p2 f32 [B,n_max,2] pixels, n_pts i32 [B] -- CUDA tensors.
     Returns dict: R [B,3,3], t [B,3], mask u8 [B,n_max] (0/255), tri f64 [B,4,n_max], good i32 [B,5]."""
@@ -136,9 +170,8 @@ def estimateEssential(pts1, pts2, K, essTh, *, maxIters=DEFAULT_ITERS, prob=DEFA
     k4 = _k4(K)
     both = undistort_points(torch.from_numpy(np.stack([p1, p2])).to(dev), k4)
     words = np.random.default_rng(seed).integers(0, 2 ** 32, size=(1, int(maxIters), 5), dtype=np.uint64)
-    out = essential_ransac_batch(both[0:1], both[1:2], torch.tensor([n], dtype=torch.int32, device=dev),
-                                 torch.from_numpy(words.astype(np.uint32).view(np.int32)).to(dev),
-                                 float(essTh), float(prob))
+    out = essential_ransac_single(both[0:1], both[1:2], n, torch.from_numpy(words.astype(np.uint32).view(np.int32)).to(dev),
+                                  float(essTh), float(prob))
     if int(out["best"][0].item()) < 0:
         return None, None, 0.0
     E = out["E"][0].cpu().numpy()
