@@ -192,6 +192,8 @@ int vslam_pose_camera_to_world(const double* pose6, double* w2c, double* c2w, do
  *   c2w dev f64 [batch][16];  pose6 dev f64 [batch][6]
  */
 int vslam_pose_guess(const double* c2w, double* pose6, int batch, void* stream);
+/* The same from the (qx,qy,qz,qw,tx,ty,tz) form of the pose (the rows of the BA / tracking-window camera arrays). */
+int vslam_pose_guess_cam7(const double* cam7, double* pose6, int batch, void* stream);
 
 /* ------------------------------------------------------------------------- */
 /* 2b. Two-view geometry (map initialisation)                                 */
@@ -383,6 +385,42 @@ int vslam_ba_read(vslam_ba* ba, int what, double* dst, int64_t capacity, void* s
  * g2o reports as "Cholesky failure" (reference debug.txt). */
 int vslam_pcg_solve(const double* S, const double* b, double* x, int n, double tol, int max_iter,
                     int32_t* status_iters, void* stream);
+
+/* ------------------------------------------------------------------------- */
+/* 5. Device-resident tracking window                          */
+/* ------------------------------------------------------------------------- */
+/*
+ * The local map of the reference's tracking loop (src/v2/main.py:153-214) as device arrays that frames are
+ * appended to, and the motion-only bundle adjustment that runs after every tracked frame
+ * (src/v2/LocalBA.py:195-229: key frame fixed, all points fixed, every tracked frame free, observation edges with
+ * Huber sqrt(5.991), 10 Levenberg iterations) as ONE cooperative kernel launch.  Replaces, per frame, the
+ * reference's graph rebuild (LocalBA.py:198-214: O(points x frames) dict probes, one pybind call per vertex and
+ * edge) and a fresh optimiser.  A frame's observations arrive together, so appending a frame keeps camera-major
+ * order: nothing is sorted, nothing is re-uploaded.
+ *
+ *   create   max_frames <= number of SMs (one co-resident CTA per frame, key frame included);
+ *            slot = observations a frame can hold (the nq of the matching call); max_points = rows of the point list
+ *   reset    a new key frame: pts dev f64 [n_pts][3] the map points it sees (main.py:183 / map.py:28-44),
+ *            kf_uv dev f32 [n_pts][2] their pixels in the key frame, kf_cam7 dev f64 [7] its camera->world pose as
+ *            (qx,qy,qz,qw,tx,ty,tz), K host f64[4]
+ *   append   main.py:208-210: one tracked frame -- cam7 dev f64 [7] (vslam_pose_camera_to_world's output) and one
+ *            observation per ratio match: point row keep_q[i], pixel kp_cur[keep_t[i]], i < *n_keep (all device
+ *            pointers, exactly vslam_match_filter's outputs; n_keep is read on the device: no host round trip)
+ *   motion_ba  LocalBA.py:195-229 on the window; stats8 (host, may be NULL = no synchronisation) as vslam_ba_optimize
+ *   info     out4 = {frames, points, max_frames, slot}; device pointers of the camera array [max_frames][7]
+ *            (updated in place by motion_ba) and of the stats
+ */
+typedef struct vslam_window vslam_window;
+int vslam_window_create(vslam_window** out, int max_frames, int slot, int max_points);
+int vslam_window_destroy(vslam_window* w);
+int vslam_window_reset(vslam_window* w, const double* pts, const float* kf_uv, int n_pts, const double* kf_cam7,
+                       const double* K, void* stream);
+int vslam_window_append(vslam_window* w, const double* cam7, const int32_t* keep_q, const int32_t* keep_t,
+                        const int32_t* n_keep, const float* kp_cur, void* stream);
+int vslam_window_motion_ba(vslam_window* w, int max_iterations, double* stats8, void* stream);
+int vslam_window_info(vslam_window* w, int32_t* out4, double** cams_dev, double** stats_dev);
+/* Copies `count` camera rows starting at frame `first` into dst (dev f64 [count][7]), stream-ordered. */
+int vslam_window_read_cams(vslam_window* w, double* dst, int first, int count, void* stream);
 
 /* The library holds no mutable state besides the device-attribute cache and the last-error string; the kernel
  * variant selectors used by tools/ and tests/ are declared in visual_slam_b200/csrc/tuning.h, not here. */

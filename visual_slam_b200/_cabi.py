@@ -39,6 +39,7 @@ def _declare(lib):
     lib.vslam_rodrigues_inverse.argtypes = [vp, vp, i32, vp]
     lib.vslam_pose_camera_to_world.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.vslam_pose_guess.argtypes = [vp, vp, i32, vp]
+    lib.vslam_pose_guess_cam7.argtypes = [vp, vp, i32, vp]
     lib.vslam_undistort_points.argtypes = [vp, C.c_int64, pd, vp, vp]
     lib.vslam_essential_hypotheses.argtypes = [vp, vp, vp, i32, i32, vp, i32, vp, vp, vp]
     lib.vslam_essential_score.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, f64, vp, vp]
@@ -68,6 +69,13 @@ def _declare(lib):
     lib.vslam_ba_accept.argtypes = [vp]
     lib.vslam_ba_dims.argtypes = [vp, C.POINTER(C.c_int32)]
     lib.vslam_ba_read.argtypes = [vp, i32, vp, C.c_int64, vp]
+    lib.vslam_window_create.argtypes = [pp, i32, i32, i32]
+    lib.vslam_window_destroy.argtypes = [vp]
+    lib.vslam_window_reset.argtypes = [vp, vp, vp, i32, vp, C.POINTER(f64), vp]
+    lib.vslam_window_append.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    lib.vslam_window_motion_ba.argtypes = [vp, i32, C.POINTER(f64), vp]
+    lib.vslam_window_read_cams.argtypes = [vp, vp, i32, i32, vp]
+    lib.vslam_window_info.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(vp), C.POINTER(vp)]
     lib.vslam_pcg_solve.argtypes = [vp, vp, vp, i32, f64, i32, C.POINTER(C.c_int32), vp]
 
 

@@ -11,6 +11,7 @@
 
 #include "ba_kernels.cuh"
 #include "ba_pcg.cuh"
+#include "ba_window.cuh"
 
 namespace vslam {
 
@@ -922,5 +923,100 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
   BA_TRY(cudaStreamSynchronize(st));
   status_iters_host[0] = host[1];
   status_iters_host[1] = host[2];
+  return VSLAM_OK;
+}
+
+// ---- device-resident tracking window (ba_window.cuh) ---------------------------------------------------------
+struct vslam_window { Window impl; };
+
+extern "C" int vslam_window_create(vslam_window** out, int max_frames, int slot, int max_points) {
+  if (!out || max_frames < 2 || slot < 1 || max_points < 1) return VSLAM_ERR_BAD_ARG;
+  int sms = sm_count();
+  if (sms <= 0) return VSLAM_ERR_NO_DEVICE;
+  if (max_frames > sms) return VSLAM_ERR_BAD_ARG;        // one co-resident CTA per frame
+  vslam_window* h = new vslam_window();
+  Window& W = h->impl;
+  W.max_frames = max_frames; W.slot = slot; W.max_pts = max_points;
+  const size_t F = max_frames, S = slot;
+  cudaError_t e = cudaSuccess;
+  auto take = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
+  take((void**)&W.pts4, (size_t)max_points * 4 * sizeof(double));
+  take((void**)&W.cams, F * 7 * sizeof(double));
+  take((void**)&W.fixed, F);
+  take((void**)&W.obs_pt, F * S * sizeof(int));
+  take((void**)&W.obs_uv, F * S * sizeof(double2));
+  take((void**)&W.n_obs, F * sizeof(int));
+  take((void**)&W.part, 3 * F * kWinPart * sizeof(double));
+  take((void**)&W.bar, sizeof(unsigned));
+  take((void**)&W.stats, 8 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMallocHost(&W.stats_host, 8 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMemset(W.n_obs, 0, F * sizeof(int));
+  if (e != cudaSuccess) { set_cuda_error(e, "vslam_window_create"); delete h; return VSLAM_ERR_CUDA; }
+  *out = h;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_window_destroy(vslam_window* h) {
+  delete h;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_window_reset(vslam_window* h, const double* pts, const float* kf_uv, int n_pts,
+                                  const double* kf_cam7, const double* K, void* stream) {
+  if (!h || !pts || !kf_uv || !kf_cam7 || !K || n_pts < 1) return VSLAM_ERR_BAD_ARG;
+  Window& W = h->impl;
+  if (n_pts > W.max_pts) return VSLAM_ERR_BAD_ARG;
+  W.K = make_double4(K[0], K[1], K[2], K[3]);
+  W.n_pts = n_pts; W.n_frames = 1;
+  window_reset_kernel<<<(std::max(n_pts, 7) + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      pts, kf_uv, kf_cam7, n_pts, W.slot, W.pts4, W.cams, W.fixed, W.obs_pt, W.obs_uv, W.n_obs);
+  return check_launch("window_reset_kernel");
+}
+
+extern "C" int vslam_window_append(vslam_window* h, const double* cam7, const int32_t* keep_q, const int32_t* keep_t,
+                                   const int32_t* n_keep, const float* kp_cur, void* stream) {
+  if (!h || !cam7 || !keep_q || !keep_t || !n_keep || !kp_cur) return VSLAM_ERR_BAD_ARG;
+  Window& W = h->impl;
+  if (W.n_frames < 1 || W.n_frames >= W.max_frames) return VSLAM_ERR_BAD_ARG;   // reset first; window full
+  const int f = W.n_frames++;
+  window_append_kernel<<<(std::max(W.slot, 7) + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      f, W.slot, cam7, keep_q, keep_t, n_keep, kp_cur, W.n_pts, W.cams, W.fixed, W.obs_pt, W.obs_uv, W.n_obs);
+  return check_launch("window_append_kernel");
+}
+
+extern "C" int vslam_window_motion_ba(vslam_window* h, int max_iterations, double* stats8, void* stream) {
+  if (!h || max_iterations < 0) return VSLAM_ERR_BAD_ARG;
+  Window& W = h->impl;
+  if (W.n_frames < 1) return VSLAM_ERR_BAD_ARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  WinView V;
+  V.n_frames = W.n_frames; V.slot = W.slot; V.max_iterations = max_iterations; V.K = W.K;
+  V.pts4 = W.pts4; V.cams = W.cams; V.fixed = W.fixed; V.obs_pt = W.obs_pt; V.obs_uv = W.obs_uv; V.n_obs = W.n_obs;
+  V.part = W.part; V.bar = W.bar; V.stats = W.stats;
+  BA_TRY(cudaMemsetAsync(W.bar, 0, sizeof(unsigned), st));
+  void* args[] = {&V};
+  BA_TRY(cudaLaunchCooperativeKernel((void*)window_motion_ba_kernel, dim3(W.n_frames), dim3(kWinThreads), args, 0, st));
+  if (stats8) {
+    BA_TRY(cudaMemcpyAsync(W.stats_host, W.stats, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    BA_TRY(cudaStreamSynchronize(st));
+    for (int i = 0; i < 8; ++i) stats8[i] = W.stats_host[i];
+  }
+  return check_launch("window_motion_ba_kernel");
+}
+
+extern "C" int vslam_window_read_cams(vslam_window* h, double* dst, int first, int count, void* stream) {
+  if (!h || !dst || first < 0 || count < 0 || first + count > h->impl.n_frames) return VSLAM_ERR_BAD_ARG;
+  if (count)
+    BA_TRY(cudaMemcpyAsync(dst, h->impl.cams + 7 * (size_t)first, (size_t)count * 7 * sizeof(double),
+                           cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_window_info(vslam_window* h, int32_t* out4, double** cams_dev, double** stats_dev) {
+  if (!h) return VSLAM_ERR_BAD_ARG;
+  Window& W = h->impl;
+  if (out4) { out4[0] = W.n_frames; out4[1] = W.n_pts; out4[2] = W.max_frames; out4[3] = W.slot; }
+  if (cams_dev) *cams_dev = W.cams;
+  if (stats_dev) *stats_dev = W.stats;
   return VSLAM_OK;
 }

@@ -169,9 +169,31 @@ __global__ void pose_guess_kernel(const double* __restrict__ c2w, double* __rest
   o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = T[3]; o[4] = T[7]; o[5] = T[11];
 }
 
+__global__ void pose_guess_cam7_kernel(const double* __restrict__ cam7, double* __restrict__ pose6, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double* c = cam7 + 7 * (size_t)i;
+  const double x = c[0], y = c[1], z = c[2], w = c[3];
+  const double R[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+                       2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                       2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)};
+  double r[3];
+  cv_rodrigues_inv(R, r);
+  double* o = pose6 + 6 * (size_t)i;
+  o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = c[4]; o[4] = c[5]; o[5] = c[6];
+}
+
 }  // namespace vslam
 
 using namespace vslam;
+
+extern "C" int vslam_pose_guess_cam7(const double* cam7, double* pose6, int batch, void* stream) {
+  if (batch < 0) return VSLAM_ERR_BAD_ARG;
+  if (batch == 0) return VSLAM_OK;
+  if (!cam7 || !pose6) return VSLAM_ERR_BAD_ARG;
+  pose_guess_cam7_kernel<<<(batch + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(cam7, pose6, batch);
+  return check_launch("vslam_pose_guess_cam7");
+}
 
 extern "C" int vslam_rodrigues(const double* rvec, double* R, int batch, void* stream) {
   if (batch < 0) return VSLAM_ERR_BAD_ARG;

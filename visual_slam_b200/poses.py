@@ -57,6 +57,16 @@ def guess_batch(c2w):
     return out
 
 
+def guess_from_cam7_batch(cam7):
+    """cam7 f64 [B,7] (qx,qy,qz,qw,tx,ty,tz of the previous frame's camera -> world pose) -> pose6 f64 [B,6]."""
+    cam7 = _f64(cam7, (7,), "cam7")
+    out = torch.empty((cam7.shape[0], 6), dtype=torch.float64, device=cam7.device)
+    with torch.cuda.device(cam7.device):
+        _cabi.check(_cabi.lib().vslam_pose_guess_cam7(_cabi.ptr(cam7), _cabi.ptr(out), cam7.shape[0],
+                                                      _cabi.stream_ptr()))
+    return out
+
+
 # ---- drop-ins with the reference's names and return objects ------------------------------------------
 def _dev(a, shape, device):
     if not torch.cuda.is_available():
