@@ -484,6 +484,67 @@ def tracking_figures(torch, dist, world, rank, dev, steps=3):
             "median_inliers": float(allr[:, 6].median().item()), "gpu_launches_per_pass": 6 * ((pairs + chunk - 1) // chunk)}
 
 
+def window_figures(torch):
+    """N1: the per-frame cost of the tracking loop's BA step.  A key-frame window is filled frame by frame; after each
+    frame the motion-only BA of the whole window runs (main.py:208-214).  Device-resident window (append kernel +
+    one cooperative BA launch) against the drop-in that rebuilds its problem from a Map on every call, at the
+    reference's real size (C1: 237 points, ~215 observations per frame) and at the C5 size (2048 points)."""
+    from visual_slam_b200 import synth
+    from visual_slam_b200.ba import BundleAdjustment
+    from visual_slam_b200.ba_problem import quat_to_R, synthetic_ba
+    from visual_slam_b200.window import TrackingWindow
+    out = {}
+    for name, n_pts, frames in (("c1_237pts_20frames", 237, 21), ("c5_2048pts_20frames", 2048, 21)):
+        pb = synthetic_ba(n_cams=frames, n_pts=n_pts, obs_per_pt=float(frames) * 0.9, seed=6, motion_only=True)
+        cams4 = np.stack([np.block([[quat_to_R(c[:4]), c[4:, None]], [np.zeros((1, 3)), np.ones((1, 1))]])
+                          for c in pb.cams])
+        per = [np.nonzero(pb.obs_cam == f)[0] for f in range(frames)]
+        kf_rows = pb.obs_pt[per[0]]
+        kf_uv = np.zeros((pb.n_pts, 2), np.float32); kf_uv[kf_rows] = pb.obs_uv[per[0]]
+        win = TrackingWindow(max_frames=frames + 1, slot=n_pts, max_points=pb.n_pts)
+        dev = win.device
+        rows = [torch.from_numpy(pb.obs_pt[p].astype(np.int32)).to(dev) for p in per]
+        uvs = [torch.from_numpy(pb.obs_uv[p].astype(np.float32)).to(dev) for p in per]
+        ar = [torch.arange(len(p), dtype=torch.int32, device=dev) for p in per]
+        nk = [torch.tensor([len(p)], dtype=torch.int32, device=dev) for p in per]
+        c7 = [torch.from_numpy(c).to(dev) for c in pb.cams]
+        best, wall = None, None
+        for rep in range(3):
+            win.reset(pb.pts, kf_uv, cams4[0], pb.K)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            e0.record()
+            for f in range(1, frames):
+                win.append(c7[f], rows[f], ar[f], nk[f], uvs[f])
+                win.motion_only_ba(10, want_stats=False)
+            e1.record()
+            torch.cuda.synchronize()
+            w = (time.perf_counter() - t0) * 1e3 / (frames - 1)
+            ms = e0.elapsed_time(e1) / (frames - 1)
+            best, wall = (ms if best is None else min(best, ms)), (w if wall is None else min(wall, w))
+        st = win.motion_only_ba(0)
+        win.close()
+        # the drop-in on the same growing window: a reference-style Map, rebuilt into a problem on every call
+        m = synth.map_from_problem(pb)
+        m.frames[0].kf = True
+        full_frames, full_pts = dict(m.frames), {k: dict(p.frames) for k, p in m.points_3d.items()}
+        t_drop = []
+        for f in (2, frames // 2, frames - 1):                     # window of f tracked frames
+            m.frames = {k: v for k, v in full_frames.items() if k <= f}
+            for k, p in m.points_3d.items():
+                p.frames = {a: b for a, b in full_pts[k].items() if a <= f}
+            t_drop.append(_best_ms(lambda: BundleAdjustment(synth.IclCamera()).motionOnlyBundleAdjustement(m), 3))
+        out[name] = {"window_ms_per_frame_device": best, "window_ms_per_frame_wall": wall,
+                     "dropin_rebuild_ms_per_call": {"2_frames": t_drop[0], "%d_frames" % (frames // 2): t_drop[1],
+                                                    "%d_frames" % (frames - 1): t_drop[2]},
+                     "frames": frames - 1, "points": pb.n_pts, "observations_full_window": pb.n_obs,
+                     "final_window_cost": st["final_cost"], "gpu_launches_per_frame": 3,
+                     "what": "append + motion-only BA (10 LM iterations) per tracked frame; device = CUDA events over "
+                             "the whole window / frames, wall = perf_counter incl. launch overhead, no per-frame sync"}
+    return out
+
+
 def _best_ms(fn, reps=7):
     fn()
     best = 1e30
@@ -821,6 +882,7 @@ def run_gpu(args):
         if not args.skip_ba:
             ba = ba_figures(torch)
             ba["cpu_restatement_c3"] = cpu_ba_restatement()
+            ba["tracking_window"] = window_figures(torch)
             line["ba"] = ba
             hbm = peaks.get("hbm_gbs", 6650.0)
             line["roofline_ba"] = {"bound": "hbm", "kernel": "ba_linearize_kernel<false> (fused linearisation, C4)",
