@@ -116,20 +116,33 @@ def test_ba_through_mapsoa_equals_the_drop_in():
         assert np.allclose(sink.frames[c].pose, m.frames[c].pose, atol=1e-12)
         assert np.allclose(soa.GetPose(c), m.frames[c].pose, atol=1e-12)
     assert np.allclose(soa.GetAll3DPoints(), np.array([m.points_3d[j].location_3d for j in range(p.n_pts)]), atol=1e-12)
+    # ... and both equal the CPU restatement run on the arrays MapSoA.problem() hands out (not on the drop-in's)
+    from oracle import ba as oba
+    ref = MapSoA.from_map(_map_from_problem(p)).problem((_Cam.fx, _Cam.fy, _Cam.cx, _Cam.cy))
+    h = oba.optimize(ref, 10)
+    assert abs(st["final_cost"] - h["final_cost"]) <= 1e-9 * h["final_cost"]
+    assert (int(st["iterations"]), int(st["trials"])) == (h["iterations"], h["trials"])
+    assert np.abs(soa.problem((_Cam.fx, _Cam.fy, _Cam.cx, _Cam.cy)).cams - ref.cams).max() < 1e-8
+    assert np.abs(soa.GetAll3DPoints() - ref.pts).max() < 1e-7
     # unchanged structure: the solver object is reused (state upload only) and converges further
     eng = soa._engine[1]
     st2 = soa.localBundleAdjustement(_Cam())
     assert soa._engine[1] is eng and st2["initial_cost"] <= st["final_cost"] * (1 + 1e-9)
-    # a structural change rebuilds it
+    # a structural change keeps the engine object (device buffers re-used) and gives it the new structure
     soa.AddPoint3D(10 ** 6, [0.0, 0.0, 3.0])
     soa.AddObservation(10 ** 6, 1, (300.0, 200.0)); soa.AddObservation(10 ** 6, 2, (310.0, 205.0))
-    soa.localBundleAdjustement(_Cam())
-    assert soa._engine[1] is not eng
+    st3 = soa.localBundleAdjustement(_Cam())
+    assert soa._engine[1] is eng and eng.prob.n_pts == p.n_pts + 1
+    ref3 = soa.problem((_Cam.fx, _Cam.fy, _Cam.cx, _Cam.cy))
+    assert abs(oba.cost(ref3) - st3["final_cost"]) <= 1e-9 * st3["final_cost"]
     # motion only
     p2 = synthetic_ba(5, 300, 4.0, seed=14, motion_only=True)
     m2 = _map_from_problem(p2); m2.frames[0].kf = True
     soa2 = MapSoA.from_map(m2)
     ba2 = BundleAdjustment(_Cam()); ba2.motionOnlyBundleAdjustement(m2)
-    st3 = soa2.motionOnlyBundleAdjustement(_Cam())
-    assert st3["final_cost"] == ba2.stats["final_cost"]
+    ref2 = soa2.problem((_Cam.fx, _Cam.fy, _Cam.cx, _Cam.cy), motion_only=True)
+    h2 = oba.optimize(ref2, 10)
+    st4 = soa2.motionOnlyBundleAdjustement(_Cam())
+    assert st4["final_cost"] == ba2.stats["final_cost"]
+    assert abs(st4["final_cost"] - h2["final_cost"]) <= 1e-9 * h2["final_cost"]
     soa.close(); soa2.close()

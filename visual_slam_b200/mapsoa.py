@@ -4,9 +4,11 @@ The reference rebuilds a g2o graph from its object map on EVERY BA call: one dic
 frame) pair and one pybind11 call per vertex and edge (src/v2/LocalBA.py:153-172, :198-214; containers
 src/v2/map.py:28-44,60-69,120-131 and src/v2/point.py:14-46).  MapSoA keeps the same information as
 growing arrays that are appended to as frames, points and observations arrive (amortised O(1)), hands
-them to the device solver without any per-element Python work, and keeps the solver object (sorted work
-lists, device buffers, captured CUDA graph) alive while the structure is unchanged, so that a repeated
-optimisation of the same window only uploads the state.
+them to the device solver without any per-element Python work, and keeps the solver object alive: while the
+structure is unchanged a repeated optimisation only uploads the state, and after an append the same object is
+given the new structure (its device buffers stay while they fit).  This class serves the GLOBAL map and the full
+BA that runs per key frame; the per-frame path of the tracking loop (append a frame, motion-only BA) lives on the
+device in visual_slam_b200.window.TrackingWindow.
 
 Conventions are the reference's: poses are camera->world 4x4 (Frame.pose, main.py:116-118), frame 0 is
 fixed in local BA (LocalBA.py:155-156), key frames are fixed and all points are fixed in motion-only BA
@@ -203,6 +205,10 @@ class MapSoA:
         if self._engine is not None and self._engine[0] == key:
             eng = self._engine[1]                       # same structure: only the state is uploaded
             eng.set_state(prob.cams, prob.pts, prob.obs_uv, prob.scale_meas, prob.K)
+        elif self._engine is not None and self._engine[0][2] == device:
+            eng = self._engine[1]                       # new structure, same engine object: its device buffers are
+            eng.set_structure(prob)                     # re-used while they fit (vslam_ba_set_structure)
+            self._engine = (key, eng)
         else:
             if self._engine is not None:
                 self._engine[1].close()
