@@ -347,6 +347,11 @@ int vslam_ba_set_state(vslam_ba* ba, const double* cams, const double* pts, cons
 int vslam_ba_get_state(vslam_ba* ba, double* cams, double* pts, void* stream);
 /* PCG relative residual tolerance (default 1e-10) and iteration cap (<=0 keeps the default). */
 int vslam_ba_set_solver(vslam_ba* ba, double pcg_tol, int pcg_max_iter);
+/* Linear solver of the reduced camera system: 0 = automatic (the default: in-CTA Cholesky with the system's assembly
+ * fused in front for n = 6 * free cameras <= 96, what g2o's CHOLMOD path does for such a window; block-Jacobi PCG
+ * above that, as north_star prescribes), 1 = PCG always, 2 = Cholesky (rejected when n > 96).  A non-positive pivot
+ * / curvature is reported the same way by both (rejected LM step). */
+int vslam_ba_set_linear_solver(vslam_ba* ba, int kind);
 
 /*
  * SparseOptimizer::optimize(max_iterations) with OptimizationAlgorithmLevenberg
@@ -379,6 +384,10 @@ int vslam_ba_dims(vslam_ba* ba, int32_t* out8);
 /* Copies an internal buffer to dst (device): 0 Hpp[Cf][36] 1 bp 2 Hll[Pf][6] 3 bl 4 S[n][n]
  * 5 bhat 6 dp 7 dl 8 trial cams 9 trial pts. */
 int vslam_ba_read(vslam_ba* ba, int what, double* dst, int64_t capacity, void* stream);
+
+/* The small-system solver on its own: in-CTA Cholesky of a dense symmetric system, n a multiple of 6, n <= 96
+ * (device pointers); *status (host) = 0 solved, 1 = a pivot was not positive (x = 0): g2o's "Cholesky failure". */
+int vslam_direct_solve(const double* S, const double* b, double* x, int n, int32_t* status, void* stream);
 
 /* Block-Jacobi PCG on a caller-supplied dense symmetric system (n multiple of 6, device pointers);
  * status_iters (host int32[2]) = {status, iterations}.  Status 1 = not positive definite, the case

@@ -105,6 +105,38 @@ def test_pcg_reports_indefinite_fixture_f1(golden_dir):
     assert status == 1 and float(x.abs().max()) == 0.0
 
 
+def test_direct_solver_solves_spd_systems_and_reports_the_indefinite_fixture(golden_dir):
+    """The small-system path (in-CTA Cholesky, csrc/ba_direct.cuh): exact on SPD systems of every block count up to
+    16 cameras, and fixture F1 (reference debug.txt, one negative eigenvalue) comes back as a failed solve."""
+    from visual_slam_b200.ba import direct_solve
+    rng = np.random.default_rng(1)
+    for n in (6, 12, 54, 90, 96):
+        A = rng.normal(size=(n, n)); S = A @ A.T + n * np.eye(n); b = rng.normal(size=n)
+        x, status = direct_solve(torch.from_numpy(S).cuda(), torch.from_numpy(b).cuda())
+        assert status == 0
+        assert np.abs(x.cpu().numpy() - np.linalg.solve(S, b)).max() <= 1e-12 * np.abs(b).max()
+    S = np.load(os.path.join(golden_dir, "ba_debug_reduced_system.npz"))["S"]
+    x, status = direct_solve(torch.from_numpy(S).cuda(), torch.ones(90, dtype=torch.float64).cuda())
+    assert status == 1 and float(x.abs().max()) == 0.0
+
+
+def test_both_linear_solvers_take_the_same_lm_path():
+    """C3-sized window: the Cholesky path (default for n <= 96) and PCG to 1e-10 agree on iterations, trials and cost."""
+    p = synthetic_ba(10, 2000, 6.0, seed=3)
+    res = {}
+    for kind in ("direct", "pcg"):
+        eng = BAEngine(p)
+        eng.set_linear_solver(kind)
+        res[kind] = eng.optimize(10)
+        eng.close()
+    a, b = res["direct"], res["pcg"]
+    assert (a["iterations"], a["trials"]) == (b["iterations"], b["trials"])
+    assert abs(a["final_cost"] - b["final_cost"]) <= 1e-9 * b["final_cost"]
+    assert a["pcg_iterations"] == 0 and b["pcg_iterations"] > 0
+    h = oba.optimize(p.copy(), 10)
+    assert abs(a["final_cost"] - h["final_cost"]) <= 1e-9 * h["final_cost"]
+
+
 def test_pcg_solves_spd_systems():
     rng = np.random.default_rng(0)
     for n in (6, 54, 96, 300):

@@ -61,6 +61,7 @@ def _declare(lib):
     lib.vslam_ba_set_state.argtypes = [vp, vp, vp, vp, vp, C.POINTER(f64), vp]
     lib.vslam_ba_get_state.argtypes = [vp, vp, vp, vp]
     lib.vslam_ba_set_solver.argtypes = [vp, f64, i32]
+    lib.vslam_ba_set_linear_solver.argtypes = [vp, i32]
     lib.vslam_ba_optimize.argtypes = [vp, i32, C.POINTER(f64), vp]
     lib.vslam_ba_linearize.argtypes = [vp, C.POINTER(f64), vp]
     lib.vslam_ba_trial.argtypes = [vp, f64, C.POINTER(f64), vp]
@@ -76,6 +77,7 @@ def _declare(lib):
     lib.vslam_window_motion_ba.argtypes = [vp, i32, C.POINTER(f64), vp]
     lib.vslam_window_read_cams.argtypes = [vp, vp, i32, i32, vp]
     lib.vslam_window_info.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(vp), C.POINTER(vp)]
+    lib.vslam_direct_solve.argtypes = [vp, vp, vp, i32, C.POINTER(C.c_int32), vp]
     lib.vslam_pcg_solve.argtypes = [vp, vp, vp, i32, f64, i32, C.POINTER(C.c_int32), vp]
 
 

@@ -77,6 +77,10 @@ class BAEngine:
     def set_solver(self, pcg_tol=1e-10, pcg_max_iter=0):
         _cabi.check(_cabi.lib().vslam_ba_set_solver(self._h, float(pcg_tol), int(pcg_max_iter)))
 
+    def set_linear_solver(self, kind="auto"):
+        """"auto": Cholesky in one CTA for n <= 96, PCG above; "pcg"; "direct"."""
+        _cabi.check(_cabi.lib().vslam_ba_set_linear_solver(self._h, {"auto": 0, "pcg": 1, "direct": 2}[kind]))
+
     def dims(self):
         out = (C.c_int32 * 8)()
         _cabi.check(_cabi.lib().vslam_ba_dims(self._h, out))
@@ -157,6 +161,17 @@ def pcg_solve(S, b, tol=1e-10, max_iter=2000):
 
 _POOL = {}    # device -> BAEngine kept between calls: the reference builds a fresh optimiser for EVERY BA call
               # (main.py:146,213,322); here only the structure arrays change, the device buffers stay
+
+
+def direct_solve(S, b):
+    """In-CTA Cholesky on a dense symmetric system (device tensors, n <= 96).  Returns (x, status)."""
+    S = S.contiguous(); b = b.contiguous()
+    x = torch.zeros_like(b)
+    out = C.c_int32(0)
+    with torch.cuda.device(S.device):
+        _cabi.check(_cabi.lib().vslam_direct_solve(_cabi.ptr(S), _cabi.ptr(b), _cabi.ptr(x), S.shape[0],
+                                                   C.byref(out), _cabi.stream_ptr()))
+    return x, int(out.value)
 
 
 def solve_problem(prob, max_iterations=10, device="cuda:0", pcg_tol=1e-10):

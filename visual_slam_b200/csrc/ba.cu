@@ -12,6 +12,7 @@
 #include "ba_kernels.cuh"
 #include "ba_pcg.cuh"
 #include "ba_window.cuh"
+#include "ba_direct.cuh"
 
 namespace vslam {
 
@@ -126,6 +127,8 @@ struct BA {
   size_t pcg_smem = 0;
   double pcg_tol = 1e-10;
   int pcg_max_iter = 0;
+  int linear_solver = 0;   // 0 auto (direct Cholesky for n <= kDirectMax, PCG above), 1 PCG, 2 direct
+  bool use_direct() const { return n > 0 && n <= kDirectMax && linear_solver != 1; }
 
   BAView view() const {
     BAView V;
@@ -477,6 +480,8 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     B.pcg_smem = smem_for(B.pcg_rows, B.pcg_slab);
     if (B.pcg_smem > budget) return VSLAM_ERR_BAD_ARG;
     BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)B.pcg_smem));
+    BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)direct_smem(kDirectMax)));
   }
   BA_TRY(B.part.alloc((size_t)4 * B.pcg_G)); BA_TRY(B.bar.alloc(1)); BA_TRY(B.pcg_flags.alloc(4));
   BA_TRY(cudaMemset(B.bar.p, 0, sizeof(unsigned))); BA_TRY(cudaMemset(B.pcg_flags.p, 0, 4 * sizeof(int)));
@@ -537,9 +542,18 @@ static int enqueue_schur(BA& B, cudaStream_t st) {
   }
   if (B.n) {
     BhatArgs Bh{B.Pf ? B.camp.p : nullptr, B.bp.p, B.bp_extra.p, B.bhat.p, B.bar.p, B.pcg_flags.p};
-    launch_step_kernel(ba_schur_finalize, (B.n_seg * 36 + B.C * 6 + 127) / 128, 128, 0, st,
-                       V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
-                       B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
+    if (B.use_direct()) {   // small system: assembled in shared memory and solved by the same launch
+      DirectArgs D{};
+      D.n_seg = B.n_seg; D.n = B.n; D.ld = B.n + 2;
+      D.seg_a = B.seg_a.p; D.seg_b = B.seg_b.p; D.seg_unit_start = B.seg_unit_start.p; D.partial = B.unit_partial.p;
+      D.Hpp = B.Hpp.p; D.extra = B.extra.p; D.seg_extra_idx = B.seg_extra_idx.p; D.S = B.S.p; D.Bh = Bh;
+      D.x = B.dp.p; D.status = B.pcg_flags.p + 1; D.iters = B.pcg_flags.p + 2;
+      launch_step_kernel(ba_solve_direct_kernel, 1, kDirectThreads, direct_smem(B.n), st, V, D);
+    } else {
+      launch_step_kernel(ba_schur_finalize, (B.n_seg * 36 + B.C * 6 + 127) / 128, 128, 0, st,
+                         V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
+                         B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
+    }
   }
   return check_launch("ba_schur");
 }
@@ -553,7 +567,7 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
     const int rc = enqueue_schur(B, st);
     if (rc) return rc;
   }
-  if (B.n) {
+  if (B.n && !B.use_direct()) {
     PcgArgs A{};   // (barrier counter and flags were reset by ba_schur_finalize)
     A.done = &B.lm.p->done;
     A.S = B.S.p; A.b = B.bhat.p; A.x = B.dp.p; A.n = B.n; A.rows = B.pcg_rows; A.G = B.pcg_G;
@@ -719,6 +733,18 @@ extern "C" int vslam_ba_set_solver(vslam_ba* h, double pcg_tol, int pcg_max_iter
   }
   B.pcg_tol = pcg_tol;
   B.pcg_max_iter = mi;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_set_linear_solver(vslam_ba* h, int kind) {
+  if (!h || kind < 0 || kind > 2) return VSLAM_ERR_BAD_ARG;
+  BA& B = h->impl;
+  if (kind == 2 && B.n > kDirectMax) return VSLAM_ERR_BAD_ARG;
+  if (kind != B.linear_solver) {   // the choice is baked into the captured step
+    if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }
+    B.graph_tried = false;
+  }
+  B.linear_solver = kind;
   return VSLAM_OK;
 }
 
@@ -891,6 +917,29 @@ extern "C" int vslam_ba_read(vslam_ba* h, int what, double* dst, int64_t capacit
   }
   if ((int64_t)n > capacity) return VSLAM_ERR_BAD_ARG;
   if (n) BA_TRY(cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+  return VSLAM_OK;
+}
+
+// Stand-alone in-CTA Cholesky solve of a caller-supplied dense symmetric system (tests: fixture F1).
+extern "C" int vslam_direct_solve(const double* S, const double* b, double* x, int n, int32_t* status_host,
+                                  void* stream) {
+  if (!S || !b || !x || n <= 0 || n % 6 || n > kDirectMax || !status_host) return VSLAM_ERR_BAD_ARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DevBuf<int> flags;
+  BA_TRY(flags.alloc(4));
+  BA_TRY(cudaMemsetAsync(flags.p, 0, 4 * sizeof(int), st));
+  BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)direct_smem(kDirectMax)));
+  DirectArgs D{};
+  D.n = n; D.ld = n + 2; D.x = x; D.status = flags.p + 1; D.iters = flags.p + 2; D.dense_S = S; D.dense_b = b;
+  BAView V{};
+  ba_solve_direct_kernel<<<1, kDirectThreads, direct_smem(n), st>>>(V, D);
+  int rc = check_launch("ba_solve_direct_kernel");
+  if (rc) return rc;
+  int host[4];
+  BA_TRY(cudaMemcpyAsync(host, flags.p, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  BA_TRY(cudaStreamSynchronize(st));
+  *status_host = host[1];
   return VSLAM_OK;
 }
 
