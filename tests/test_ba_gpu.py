@@ -121,7 +121,8 @@ def test_direct_solver_solves_spd_systems_and_reports_the_indefinite_fixture(gol
 
 
 def test_both_linear_solvers_take_the_same_lm_path():
-    """C3-sized window: the Cholesky path (default for n <= 96) and PCG to 1e-10 agree on iterations, trials and cost."""
+    """C3-sized window: the in-CTA factorisation (optional, n <= 96) and PCG to 1e-10 (the default) agree on
+    iterations, trials and cost."""
     p = synthetic_ba(10, 2000, 6.0, seed=3)
     res = {}
     for kind in ("direct", "pcg"):

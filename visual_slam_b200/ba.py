@@ -78,7 +78,7 @@ class BAEngine:
         _cabi.check(_cabi.lib().vslam_ba_set_solver(self._h, float(pcg_tol), int(pcg_max_iter)))
 
     def set_linear_solver(self, kind="auto"):
-        """"auto": Cholesky in one CTA for n <= 96, PCG above; "pcg"; "direct"."""
+        """"auto" = "pcg" (block-Jacobi PCG, the default and the faster one); "direct": LDL^T in one CTA, n <= 96."""
         _cabi.check(_cabi.lib().vslam_ba_set_linear_solver(self._h, {"auto": 0, "pcg": 1, "direct": 2}[kind]))
 
     def dims(self):

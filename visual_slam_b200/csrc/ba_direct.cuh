@@ -20,9 +20,15 @@
 namespace vslam {
 
 constexpr int kDirectMax = 96;
-constexpr int kDirectThreads = 256;
+constexpr int kDirectThreads = 512;
 
-static inline size_t direct_smem(int n) { return sizeof(double) * (size_t)(n + 1) * (size_t)(n + 2); }
+// (n + 1) rows x ld (odd: column walks are conflict-free) of the system + right-hand side row, and the (row, column)
+// table of the trailing triangle's entries
+static inline int direct_ld(int n) { return (n + 2) | 1; }
+static inline size_t direct_smem(int n) {
+  const size_t m = (size_t)n + 1;
+  return sizeof(double) * m * (size_t)direct_ld(n) + sizeof(uint16_t) * (m * (m + 1) / 2 + 2);
+}
 
 struct DirectArgs {
   int n_seg, n, ld;
@@ -34,162 +40,117 @@ struct DirectArgs {
   const double* dense_S; const double* dense_b;   // stand-alone use (vslam_direct_solve): the system as given
 };
 
+// Right-looking LDL^T, one pivot per step: the work per pivot is a rank-1 update of the trailing triangle -- one
+// FMA per entry, all entries independent -- so the sequential depth is the 54 pivots themselves and not the
+// arithmetic inside a block factorisation (a blocked variant with redundant 6x6 inverses measured 27 us at n = 54:
+// ~170 dependent FP64 instructions per block step in every warp).  The lower triangle holds the unscaled columns,
+// the UPPER triangle receives L^T (l_ik = a_ik / d_k at [k][i]), so a step needs no second barrier; the reciprocal of
+// the NEXT pivot is formed by every thread from three entries while the update of the current step is in flight.
+// The right-hand side is row n: its scaled entries v = D^-1 L^-1 b land at [k][n], and the backward pass
+// x_k = v_k - sum_{i > k} l_ik x_i runs column by column in warp 0 (no divisions, no reductions).
 __global__ void __launch_bounds__(kDirectThreads) ba_solve_direct_kernel(BAView V, DirectArgs A) {
-  extern __shared__ __align__(16) double Ls[];      // (n + 1) rows x ld: lower triangle + right-hand side row
-  __shared__ int s_fail;
+  extern __shared__ __align__(16) double Ls[];
   const int n = A.n, ld = A.ld, tid = threadIdx.x;
+  uint16_t* tri = reinterpret_cast<uint16_t*>(Ls + (size_t)(n + 1) * ld);   // entry e of the triangle -> (row << 8 | col)
   pdl_wait();
   pdl_trigger();
   if (tid == 0) {
-    s_fail = 0;
     if (A.Bh.pcg_bar) *A.Bh.pcg_bar = 0u;
     if (A.Bh.pcg_flags) { A.Bh.pcg_flags[0] = 0; A.Bh.pcg_flags[1] = 0; A.Bh.pcg_flags[2] = 0; A.Bh.pcg_flags[3] = 0; }
   }
   const bool standalone = A.dense_S != nullptr;
   if (!standalone && V.st->done) return;
   const double lambda = standalone ? 0.0 : V.st->lambda;
+  const double* __restrict__ partial = A.partial;
+  const double* __restrict__ Hpp = A.Hpp;
+  const double* __restrict__ extra = A.extra;
+  // ---- assembly (ba_schur_finalize's arithmetic); every entry of the lower triangle that belongs to a present
+  // block is written exactly once, absent blocks are zeroed first
   for (int i = tid; i < (n + 1) * ld; i += kDirectThreads) Ls[i] = 0.0;
-  __syncthreads();
-  if (standalone) {
-    for (int i = tid; i < n * n; i += kDirectThreads) Ls[(i / n) * ld + (i % n)] = A.dense_S[i];
-    for (int i = tid; i < n; i += kDirectThreads) Ls[n * ld + i] = A.dense_b[i];
-  }
-  // ---- assembly (ba_schur_finalize's arithmetic)
-  for (int t = tid; t < (standalone ? 0 : A.n_seg * 36); t += kDirectThreads) {
-    const int seg = t / 36, e = t - 36 * seg;
-    const int a = A.seg_a[seg], b = A.seg_b[seg], r = e / 6, c = e - 6 * r;
-    const int ex = A.seg_extra_idx[seg];
-    double v = ex >= 0 ? A.extra[(size_t)ex * 36 + e] : 0.0;
-    if (a == b) v += A.Hpp[36 * a + e] + (r == c ? lambda : 0.0);
-    double s = 0.0;
-    for (int u = A.seg_unit_start[seg]; u < A.seg_unit_start[seg + 1]; ++u) s += A.partial[(size_t)u * 36 + e];
-    v -= s;
-    Ls[(6 * a + r) * ld + 6 * b + c] = v;
-    if (a != b) Ls[(6 * b + c) * ld + 6 * a + r] = v;
-    A.S[(size_t)(6 * a + r) * n + 6 * b + c] = v;
-    if (a != b) A.S[(size_t)(6 * b + c) * n + 6 * a + r] = v;
-  }
-  for (int t = tid; t < (standalone ? 0 : V.C * 6); t += kDirectThreads) {
-    const int c = t / 6, i = t - 6 * c;
-    const int col = V.cam_col[c];
-    if (col < 0) continue;
-    double s = 0.0;
-    if (A.Bh.camp != nullptr) {
-      const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
-      const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
-      for (int k = 0; k < n_chunks; ++k) s += A.Bh.camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
-    }
-    const double v = (A.Bh.bp[6 * col + i] + A.Bh.bp_extra[6 * col + i]) - s;
-    Ls[n * ld + 6 * col + i] = v;
-    A.Bh.bhat[6 * col + i] = v;
-  }
-  __syncthreads();
-  // ---- blocked Cholesky; row n (the right-hand side) is carried as one more row of the lower triangle
-  const int nb = n / 6;
-  for (int k = 0; k < nb; ++k) {
-    const int kb = 6 * k;
-    // diagonal block, factored by every thread in registers: D = C C^T, ri = 1 / diag(C)
-    double Cf[6][6], ri[6];
-    bool ok = true;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-#pragma unroll
-      for (int j = 0; j <= i; ++j) Cf[i][j] = Ls[(kb + i) * ld + kb + j];
-    }
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      double d = Cf[j][j];
-#pragma unroll
-      for (int q = 0; q < j; ++q) d = fma(-Cf[j][q], Cf[j][q], d);
-      ok = ok && (d > 1e-290) && (d < 1e290);
-      ri[j] = fast_rsqrt(ok ? d : 1.0);
-      Cf[j][j] = d * ri[j];
-#pragma unroll
-      for (int i = j + 1; i < 6; ++i) {
-        double t = Cf[i][j];
-#pragma unroll
-        for (int q = 0; q < j; ++q) t = fma(-Cf[i][q], Cf[j][q], t);
-        Cf[i][j] = t * ri[j];
-      }
-    }
-    if (!ok) { if (tid == 0) s_fail = 1; }
-    __syncthreads();                                  // everybody has read the diagonal block
-    if (s_fail) break;
-    // rows kb .. n: the block's own rows take the factor, the rows below solve l C^T = a
-    if (tid < 6) {                                    // (static indices only: the factor stays in registers)
-      double* row = Ls + (kb + tid) * ld + kb;
-#pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        double v = 0.0;
-#pragma unroll
-        for (int i = j; i < 6; ++i) v = (i == tid) ? Cf[i][j] : v;
-        row[j] = v;
-      }
-    }
-    for (int r = kb + 6 + tid; r <= n; r += kDirectThreads) {
-      double* row = Ls + r * ld + kb;
-      double l[6];
-#pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        double t = row[j];
-#pragma unroll
-        for (int q = 0; q < j; ++q) t = fma(-l[q], Cf[j][q], t);
-        l[j] = t * ri[j];
-      }
-#pragma unroll
-      for (int j = 0; j < 6; ++j) row[j] = l[j];
-    }
-    __syncthreads();
-    // trailing update of the lower triangle (rows i > kb + 5, columns kb + 6 .. min(i, n - 1))
-    const int m0 = kb + 6, m = n + 1 - m0;            // rows m0 .. n
-    const int total = m * (m + 1) / 2 - 1;            // triangle without its last entry (row n, column n)
+  {
+    const int m = n + 1, total = m * (m + 1) / 2;
     for (int e = tid; e < total; e += kDirectThreads) {
       int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
       while ((i + 1) * (i + 2) / 2 <= e) ++i;
       while (i * (i + 1) / 2 > e) --i;
-      const int j = e - i * (i + 1) / 2;
-      const double* ri_ = Ls + (m0 + i) * ld + kb;
-      const double* rj_ = Ls + (m0 + j) * ld + kb;
-      double s = Ls[(m0 + i) * ld + m0 + j];
-#pragma unroll
-      for (int q = 0; q < 6; ++q) s = fma(-ri_[q], rj_[q], s);
-      Ls[(m0 + i) * ld + m0 + j] = s;
+      tri[e] = (uint16_t)((i << 8) | (e - i * (i + 1) / 2));
     }
+  }
+  __syncthreads();
+  if (standalone) {
+    for (int i = tid; i < n * n; i += kDirectThreads) Ls[(i / n) * ld + (i % n)] = A.dense_S[i];
+    for (int i = tid; i < n; i += kDirectThreads) Ls[n * ld + i] = A.dense_b[i];
+  } else {
+    for (int t = tid; t < A.n_seg * 36; t += kDirectThreads) {
+      const int seg = t / 36, e = t - 36 * seg;
+      const int a = A.seg_a[seg], b = A.seg_b[seg], r = e / 6, c = e - 6 * r;
+      const int ex = A.seg_extra_idx[seg];
+      const int u0 = A.seg_unit_start[seg], u1 = A.seg_unit_start[seg + 1];
+      double v = ex >= 0 ? extra[(size_t)ex * 36 + e] : 0.0;
+      if (a == b) v += Hpp[36 * a + e] + (r == c ? lambda : 0.0);
+      double s = 0.0;
+      for (int u = u0; u < u1; ++u) s += partial[(size_t)u * 36 + e];
+      v -= s;
+      Ls[(6 * a + r) * ld + 6 * b + c] = v;
+      if (a != b) Ls[(6 * b + c) * ld + 6 * a + r] = v;
+    }
+    for (int t = tid; t < V.C * 6; t += kDirectThreads) {
+      const int c = t / 6, i = t - 6 * c;
+      const int col = V.cam_col[c];
+      if (col < 0) continue;
+      double s = 0.0;
+      if (A.Bh.camp != nullptr) {
+        const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
+        const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
+        for (int k = 0; k < n_chunks; ++k) s += A.Bh.camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
+      }
+      Ls[n * ld + 6 * col + i] = (A.Bh.bp[6 * col + i] + A.Bh.bp_extra[6 * col + i]) - s;
+    }
+  }
+  __syncthreads();
+  if (!standalone) {      // HBM copies for the stage API (vslam_ba_read) -- off the critical path
+    for (int i = tid; i < n * n; i += kDirectThreads) A.S[i] = Ls[(i / n) * ld + (i % n)];
+    for (int i = tid; i < n; i += kDirectThreads) A.Bh.bhat[i] = Ls[n * ld + i];
+    __syncthreads();      // (the upper triangle is overwritten below)
+  }
+  bool ok = true;
+  double inv;
+  {
+    const double d0 = Ls[0];
+    ok = (d0 > 1e-290) && (d0 < 1e290);
+    inv = fast_rcp(ok ? d0 : 1.0);
+  }
+  for (int k = 0; k < n; ++k) {
+    const double* colk = Ls + k;                      // a_ik = colk[i * ld]
+    double inv_next = 1.0;
+    if (k + 1 < n) {                                  // pivot k + 1 after this step's update, by every thread
+      const double a10 = colk[(k + 1) * ld];
+      const double dn = fma(-(a10 * inv), a10, Ls[(k + 1) * ld + k + 1]);
+      ok = ok && (dn > 1e-290) && (dn < 1e290);
+      inv_next = fast_rcp(ok ? dn : 1.0);
+    }
+    const int m0 = k + 1, m = n - k;                  // rows m0 .. n
+    for (int r = tid; r < m; r += kDirectThreads) Ls[k * ld + m0 + r] = colk[(m0 + r) * ld] * inv;   // L^T row k
+    const int total = m * (m + 1) / 2 - 1;            // trailing triangle without the entry (n, n)
+    // (entry 0 = the next pivot: every thread has just formed its updated value in registers, and nobody reads
+    // the stored one again, so it is left alone -- no thread writes what another one is reading in this step)
+    for (int e = 1 + tid; e < total; e += kDirectThreads) {
+      const int ij = tri[e], i = m0 + (ij >> 8), j = m0 + (ij & 255);
+      Ls[i * ld + j] = fma(-(colk[i * ld] * inv), colk[j * ld], Ls[i * ld + j]);
+    }
+    inv = inv_next;
     __syncthreads();
   }
-  const bool fail = s_fail != 0;
-  // ---- backward substitution L^T x = y (y = row n), one block at a time, warp 0
+  const bool fail = !ok;
   if (tid < 32 && !fail) {
-    double* y = Ls + n * ld;
-    for (int k = nb - 1; k >= 0; --k) {
-      const int kb = 6 * k;
-      double acc[6] = {0, 0, 0, 0, 0, 0};
-      for (int i = kb + 6 + tid; i < n; i += 32) {
-        const double xi = y[i];
-#pragma unroll
-        for (int c = 0; c < 6; ++c) acc[c] = fma(Ls[i * ld + kb + c], xi, acc[c]);
-      }
-#pragma unroll
-      for (int c = 0; c < 6; ++c) acc[c] = warp_sum(acc[c]);
-      // x_k = C^-T (y_k - acc), C = the block's factor (lower): solve from the last row up; every lane does it
-      double xk[6];
-#pragma unroll
-      for (int c = 5; c >= 0; --c) {
-        double t = y[kb + c] - acc[c];
-#pragma unroll
-        for (int q = c + 1; q < 6; ++q) t = fma(-Ls[(kb + q) * ld + kb + c], xk[q], t);
-        xk[c] = t / Ls[(kb + c) * ld + kb + c];
-      }
-      __syncwarp();
-      if (tid == 0) {
-#pragma unroll
-        for (int c = 0; c < 6; ++c) y[kb + c] = xk[c];
-      }
+    for (int i = n - 1; i >= 1; --i) {                // x_i is final: fold it into the rows above
+      const double xi = Ls[i * ld + n];
+      for (int k = tid; k < i; k += 32) Ls[k * ld + n] = fma(-Ls[k * ld + i], xi, Ls[k * ld + n]);
       __syncwarp();
     }
   }
   __syncthreads();
-  for (int i = tid; i < n; i += kDirectThreads) A.x[i] = fail ? 0.0 : Ls[n * ld + i];
+  for (int i = tid; i < n; i += kDirectThreads) A.x[i] = fail ? 0.0 : Ls[i * ld + n];
   if (tid == 0) { *A.status = fail ? 1 : 0; *A.iters = 0; }
 }
 
