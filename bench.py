@@ -484,6 +484,44 @@ def tracking_figures(torch, dist, world, rank, dev, steps=3):
             "median_inliers": float(allr[:, 6].median().item()), "gpu_launches_per_pass": 6 * ((pairs + chunk - 1) // chunk)}
 
 
+def ba_batch_figures(torch, windows=148):
+    """C3-sized local windows optimised side by side (vslam_ba_optimize_batch; SURVEY 8e: independent BA problems shard
+    like frame pairs): aggregate LM iterations/s over `windows` different problems (seeds 100...), against the same
+    windows one after the other."""
+    from visual_slam_b200.ba import BAEngine, optimize_batch
+    from visual_slam_b200.ba_problem import synthetic_ba
+    probs = [synthetic_ba(n_cams=10, n_pts=5000, obs_per_pt=6.0, seed=100 + i) for i in range(windows)]
+    engs = [BAEngine(p) for p in probs]
+
+    def reset():
+        for e, p in zip(engs, probs):
+            e.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
+        torch.cuda.synchronize()
+    best, its = None, 0
+    for rep in range(4):
+        reset()
+        t0 = time.perf_counter()
+        out = optimize_batch(engs, 10)
+        dt = time.perf_counter() - t0
+        its = sum(int(o["iterations"]) for o in out)
+        if rep > 0:
+            best = dt if best is None else min(best, dt)
+    reset()
+    t0 = time.perf_counter()
+    for e in engs[:16]:
+        e.optimize(10)
+    serial = (time.perf_counter() - t0) / 16
+    obs = sum(p.n_obs for p in probs)
+    for e in engs:
+        e.close()
+    return {"windows": windows, "lm_iters_per_s": its / best, "ms_per_batch": best * 1e3, "iterations": its,
+            "one_by_one_ms_per_window": serial * 1e3, "one_by_one_lm_iters_per_s": 10.0 / serial,
+            "observations_total": obs,
+            "linearize_bytes_per_iteration": sum(p.linearize_bytes() for p in probs),
+            "what": "%d independent C3 windows (10 key frames x 5k points x ~30k observations each), 10 LM iterations each, "
+                    "wall clock of the batched call incl. its synchronisation" % windows}
+
+
 def window_figures(torch):
     """N1: the per-frame cost of the tracking loop's BA step.  A key-frame window is filled frame by frame; after each
     frame the motion-only BA of the whole window runs (main.py:208-214).  Device-resident window (append kernel +
@@ -883,6 +921,7 @@ def run_gpu(args):
             ba = ba_figures(torch)
             ba["cpu_restatement_c3"] = cpu_ba_restatement()
             ba["tracking_window"] = window_figures(torch)
+            ba["c3_batch"] = ba_batch_figures(torch)
             line["ba"] = ba
             hbm = peaks.get("hbm_gbs", 6650.0)
             line["roofline_ba"] = {"bound": "hbm", "kernel": "ba_linearize_kernel<false> (fused linearisation, C4)",

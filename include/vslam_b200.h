@@ -363,6 +363,12 @@ int vslam_ba_set_linear_solver(vslam_ba* ba, int kind);
 int vslam_ba_optimize(vslam_ba* ba, int max_iterations, double* stats8, void* stream);
 
 /* The stages of one LM iteration, exposed for parity tests and profiling. */
+/* vslam_ba_optimize for `count` INDEPENDENT problems at once (one local window per sequence, SURVEY 8e: "multiple
+ * independent BA problems shard like pairs"): their LM slots are enqueued side by side on internal streams and
+ * overlap on the device; results are identical to optimising them one after the other.  stats8: host f64 [count][8].
+ * Synchronises the device. */
+int vslam_ba_optimize_batch(vslam_ba** bas, int count, int max_iterations, double* stats8);
+
 /* buildSystem(): out2 (host) = {robust cost, max |diag H|}.  Synchronises the stream. */
 int vslam_ba_linearize(vslam_ba* ba, double* out2, void* stream);
 /* Profiling: times one stage with CUDA events recorded on `stream` around the stage's own kernels:

@@ -264,3 +264,25 @@ def test_c4_trajectory_matches_the_restatement_golden(golden_dir):
     assert abs(np.sqrt(np.mean(np.sum(e * e, axis=1))) - float(g["rms_px"])) < 1e-3   # north_star: RMS within 1e-3 px
     print("C4 vs restatement: max rel cost diff %.3e over %d iterations" % (rel.max(), len(costs) - 1))
     eng.close()
+
+
+def test_batch_of_independent_windows_equals_one_by_one():
+    """vslam_ba_optimize_batch: independent local windows side by side on the device -- same bits as one after
+    the other, different problems and sizes in one batch, including one whose steps get rejected."""
+    from visual_slam_b200.ba import optimize_batch
+    probs = [synthetic_ba(6, 400, 4.0, seed=20 + i) for i in range(5)] + [synthetic_ba(10, 1500, 6.0, seed=3),
+                                                                          synthetic_ba(4, 80, 3.0, seed=11, pose_noise=(8.0, 0.4))]
+    single = []
+    for p in probs:
+        e = BAEngine(p); single.append((e.optimize(10), [x.cpu().numpy() for x in e.get_state()])); e.close()
+    engs = [BAEngine(p) for p in probs]
+    for rep in range(2):                                  # second round: the steps run from captured graphs
+        for e, p in zip(engs, probs):
+            e.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
+        out = optimize_batch(engs, 10)
+        for e, st, (ref, state) in zip(engs, out, single):
+            assert st == ref
+            got = [x.cpu().numpy() for x in e.get_state()]
+            assert np.array_equal(got[0], state[0]) and np.array_equal(got[1], state[1])
+    for e in engs:
+        e.close()

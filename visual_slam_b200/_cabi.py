@@ -63,6 +63,7 @@ def _declare(lib):
     lib.vslam_ba_set_solver.argtypes = [vp, f64, i32]
     lib.vslam_ba_set_linear_solver.argtypes = [vp, i32]
     lib.vslam_ba_optimize.argtypes = [vp, i32, C.POINTER(f64), vp]
+    lib.vslam_ba_optimize_batch.argtypes = [C.POINTER(vp), i32, i32, C.POINTER(f64)]
     lib.vslam_ba_linearize.argtypes = [vp, C.POINTER(f64), vp]
     lib.vslam_ba_trial.argtypes = [vp, f64, C.POINTER(f64), vp]
     lib.vslam_ba_trace_linearize.argtypes = [vp, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_int32), vp]

@@ -148,6 +148,19 @@ class BAEngine:
         return dict(zip(keys, list(stats)))
 
 
+def optimize_batch(engines, max_iterations=10):
+    """Optimises independent problems concurrently (vslam_ba_optimize_batch).  Returns one stats dict per engine."""
+    n = len(engines)
+    hs = (C.c_void_p * n)(*[e._h for e in engines])
+    stats = (C.c_double * (8 * n))()
+    if n:
+        with torch.cuda.device(engines[0].device):
+            _cabi.check(_cabi.lib().vslam_ba_optimize_batch(hs, n, int(max_iterations), stats))
+    keys = ("initial_cost", "final_cost", "iterations", "trials", "lambda", "pcg_iterations", "rejected",
+            "pcg_breakdowns")
+    return [dict(zip(keys, list(stats[8 * i:8 * i + 8]))) for i in range(n)]
+
+
 def pcg_solve(S, b, tol=1e-10, max_iter=2000):
     """Block-Jacobi PCG on a dense symmetric system (device tensors).  Returns (x, status, iters)."""
     S = S.contiguous(); b = b.contiguous()

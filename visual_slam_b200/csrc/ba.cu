@@ -678,6 +678,54 @@ static int ba_optimize(BA& B, int max_iterations, double* stats, cudaStream_t st
   return VSLAM_OK;
 }
 
+// Independent BA problems (one local window per sequence) optimised concurrently: every problem's LM
+// slots are enqueued on one of a small pool of streams without waiting, the controller states are read once all
+// are in flight, and only problems that are not done yet (a rejected trial) get further slots.  Small windows are
+// latency-bound on their own (C3: ~70 us per LM iteration at a few per cent of the machine); side by side they
+// fill it.
+static int ba_optimize_batch(BA** Bs, int count, int max_iterations, double* stats) {
+  static cudaStream_t pool[32];
+  static int pool_n = 0;
+  const int want = std::min(count, 32);
+  while (pool_n < want) {
+    BA_TRY(cudaStreamCreateWithFlags(&pool[pool_n], cudaStreamNonBlocking));
+    ++pool_n;
+  }
+  std::vector<int> budget(count, max_iterations * 10 + 1), batch(count, max_iterations);
+  std::vector<char> done(count, 0);
+  BA_TRY(cudaDeviceSynchronize());          // the callers' set_state calls ran on other streams
+  for (int i = 0; i < count; ++i) {
+    if (Bs[i]->C == 0 || max_iterations <= 0) return VSLAM_ERR_BAD_ARG;
+    ba_lm_reset<<<1, 1, 0, pool[i % pool_n]>>>(Bs[i]->lm.p, max_iterations, 0);
+  }
+  int open = count;
+  while (open > 0) {
+    for (int i = 0; i < count; ++i) {
+      if (done[i]) continue;
+      const int rc = launch_steps(*Bs[i], batch[i], pool[i % pool_n]);
+      if (rc) return rc;
+    }
+    for (int i = 0; i < count; ++i)
+      if (!done[i]) BA_TRY(cudaMemcpyAsync(Bs[i]->lm_host, Bs[i]->lm.p, sizeof(LMState), cudaMemcpyDeviceToHost, pool[i % pool_n]));
+    for (int s = 0; s < pool_n; ++s) BA_TRY(cudaStreamSynchronize(pool[s]));
+    for (int i = 0; i < count; ++i) {
+      if (done[i]) continue;
+      budget[i] -= batch[i];
+      if (Bs[i]->lm_host->done || budget[i] <= 0) { done[i] = 1; --open; Bs[i]->optimizes_since_build++; }
+      else batch[i] = std::max(1, std::min(budget[i], max_iterations - Bs[i]->lm_host->iters));
+    }
+  }
+  if (stats) {
+    for (int i = 0; i < count; ++i) {
+      const LMState& L = *Bs[i]->lm_host;
+      double* s = stats + 8 * (size_t)i;
+      s[0] = L.initial_cost; s[1] = L.cur_cost; s[2] = L.iters; s[3] = L.trials;
+      s[4] = L.lambda; s[5] = L.pcg_total; s[6] = L.rejected; s[7] = L.breakdowns;
+    }
+  }
+  return VSLAM_OK;
+}
+
 extern "C" int vslam_ba_create(vslam_ba** out, int n_cams, int n_pts, int n_obs, int n_scale,
                                const int32_t* obs_cam, const int32_t* obs_pt, const uint8_t* cam_fixed,
                                const uint8_t* pt_fixed, const int32_t* scale_a, const int32_t* scale_b) {
@@ -875,6 +923,16 @@ extern "C" int vslam_ba_accept(vslam_ba* h) {
 extern "C" int vslam_ba_optimize(vslam_ba* h, int max_iterations, double* stats8, void* stream) {
   if (!h || max_iterations < 0) return VSLAM_ERR_BAD_ARG;
   return ba_optimize(h->impl, max_iterations, stats8, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int vslam_ba_optimize_batch(vslam_ba** hs, int count, int max_iterations, double* stats8) {
+  if (!hs || count < 0 || max_iterations <= 0) return VSLAM_ERR_BAD_ARG;
+  std::vector<BA*> Bs(count);
+  for (int i = 0; i < count; ++i) {
+    if (!hs[i]) return VSLAM_ERR_BAD_ARG;
+    Bs[i] = &hs[i]->impl;
+  }
+  return count ? ba_optimize_batch(Bs.data(), count, max_iterations, stats8) : VSLAM_OK;
 }
 
 extern "C" int vslam_ba_dims(vslam_ba* h, int32_t* out8) {
