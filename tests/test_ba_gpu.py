@@ -34,9 +34,11 @@ def close(a, b, rtol=1e-9):
                                   dict(n_cams=6, n_pts=500, obs_per_pt=4.0, seed=3, motion_only=True),
                                   # points seen by more than 32 cameras take the strided point-role path
                                   dict(n_cams=48, n_pts=120, obs_per_pt=40.0, seed=4)])
-def test_linearize_and_one_trial_match_restatement(args):
+@pytest.mark.parametrize("schur", ["chunks", "units"])
+def test_linearize_and_one_trial_match_restatement(args, schur):
     p = synthetic_ba(**args)
     eng = BAEngine(p)
+    eng.set_schur_variant(schur)          # both Schur kernels: resident chunks (default) and sorted units over G
     lin = eng.linearize()
     L = oba.linearize(p)
     assert abs(lin["cost"] - L.cost) <= 1e-11 * L.cost
@@ -286,3 +288,37 @@ def test_batch_of_independent_windows_equals_one_by_one():
             assert np.array_equal(got[0], state[0]) and np.array_equal(got[1], state[1])
     for e in engs:
         e.close()
+
+
+def test_schur_variants_agree_with_fixed_points_duplicates_and_fixed_cameras():
+    """The chunked Schur kernel against the sorted-unit one on structures that exercise its item rules: fixed points
+    (no contribution), a fixed camera in the middle, a point observed twice by the same camera, a camera with more
+    than one chunk of observations, a camera with none."""
+    p = synthetic_ba(9, 1500, 5.0, seed=21)
+    rng = np.random.default_rng(2)
+    pt_fixed = rng.random(p.n_pts) < 0.2
+    cam_fixed = p.cam_fixed.copy(); cam_fixed[4] = True
+    dup = np.arange(0, p.n_obs, 37)                            # duplicate observations: same (camera, point), other pixel
+    oc = np.concatenate([p.obs_cam, p.obs_cam[dup]]); op = np.concatenate([p.obs_pt, p.obs_pt[dup]])
+    uv = np.concatenate([p.obs_uv, p.obs_uv[dup] + 1.5])
+    keep = oc != 7                                             # camera 7 loses all its observations
+    q = BAProblem(p.cams, p.pts, oc[keep], op[keep], uv[keep], p.K, cam_fixed, pt_fixed, p.scale_a, p.scale_b, p.scale_meas)
+    assert np.bincount(q.obs_cam, minlength=9).max() > 512
+    out = {}
+    for v in ("chunks", "units"):
+        eng = BAEngine(q)
+        eng.set_schur_variant(v)
+        lin = eng.linearize()
+        eng.trial(1e-5 * lin["max_diag"])
+        out[v] = (eng.read("S").cpu().numpy(), eng.read("bhat").cpu().numpy(), eng.read("dp").cpu().numpy())
+        eng.set_state(q.cams, q.pts, q.obs_uv, q.scale_meas, q.K)
+        out[v] += (eng.optimize(10),)
+        eng.close()
+    (Sa, ba_, da, sa_), (Sb, bb, db, sb_) = out["chunks"], out["units"]
+    assert np.abs(Sa - Sb).max() <= 1e-12 * np.abs(Sb).max() and np.abs(ba_ - bb).max() <= 1e-12 * np.abs(bb).max()
+    assert np.abs(da - db).max() <= 1e-9 * np.abs(db).max()
+    assert (sa_["iterations"], sa_["trials"]) == (sb_["iterations"], sb_["trials"])
+    assert abs(sa_["final_cost"] - sb_["final_cost"]) <= 1e-10 * sb_["final_cost"]
+    L = oba.linearize(q)
+    S, bh, _, _ = oba.schur_system(L, 1e-5 * oba.lambda_init(L, 1.0))
+    assert close(Sa, S, 1e-9) and close(ba_, bh, 1e-9)

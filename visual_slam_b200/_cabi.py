@@ -62,6 +62,7 @@ def _declare(lib):
     lib.vslam_ba_get_state.argtypes = [vp, vp, vp, vp]
     lib.vslam_ba_set_solver.argtypes = [vp, f64, i32]
     lib.vslam_ba_set_linear_solver.argtypes = [vp, i32]
+    lib.vslam_ba_set_schur_variant.argtypes = [vp, i32]
     lib.vslam_ba_optimize.argtypes = [vp, i32, C.POINTER(f64), vp]
     lib.vslam_ba_optimize_batch.argtypes = [C.POINTER(vp), i32, i32, C.POINTER(f64)]
     lib.vslam_ba_linearize.argtypes = [vp, C.POINTER(f64), vp]

@@ -11,6 +11,7 @@
 
 #include "ba_kernels.cuh"
 #include "ba_pcg.cuh"
+#include "tuning.h"
 #include "ba_window.cuh"
 #include "ba_direct.cuh"
 
@@ -96,6 +97,11 @@ struct BA {
   DevBuf<int> cam_col, pt_col, cm_start, cm_pt, cm_pm, cm_src, pt_start, pm_cam, pm_src;
   DevBuf<int> item_a, item_b, unit_start, unit_len, seg_a, seg_b, seg_unit_start, seg_extra_idx;
   DevBuf<int> sa, sb, diag_extra, inc_start, inc_edge, extra_a, extra_b;
+  // chunked Schur work lists (ba_schur_chunks): per (free camera, chunk of its observations) the partner blocks
+  DevBuf<int> ck_cam, ck_start, ck_end, ck_ustart, cu_unit, cu_istart, it_partner, cam_ck_start, seg_cunit_start;
+  DevBuf<unsigned short> it_local;
+  DevBuf<double> ck_bh, ck_partial;
+  int n_chunks = 0, n_cunits = 0, schur_variant = 0;   // 0 = chunked (resident Y), 1 = sorted units over G
   // fused linearisation work lists
   DevBuf<LinWork> lin_work, cam_work;
   DevBuf<unsigned> cam_ticket, lin_ticket;
@@ -116,6 +122,8 @@ struct BA {
   cudaGraphExec_t step_graph = nullptr;   // one LM trial slot (rebuild-if-dirty + trial + controller)
   bool graph_tried = false;
   int optimizes_since_build = 0;          // the step is captured into a graph from the SECOND optimize() of a structure
+  cudaGraphExec_t multi_graph = nullptr;  // `multi_slots` LM trial slots in ONE graph (batched optimisation: one launch per problem)
+  int multi_slots = 0;
   cudaStream_t graph_stream = nullptr;
   // system
   DevBuf<double> Hpl, Gbuf, Hpp, bp, bhat, Hll, bl, Hinv, Wfac, camp, cam_cost, S, dp, dl, tmp3;
@@ -166,6 +174,7 @@ struct BA {
     return V;
   }
   ~BA() {
+    if (multi_graph) cudaGraphExecDestroy(multi_graph);
     if (step_graph) cudaGraphExecDestroy(step_graph);
     if (lm_host) cudaFreeHost(lm_host);
   }
@@ -213,6 +222,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
                     const uint8_t* cam_fixed, const uint8_t* pt_fixed, const int32_t* sa,
                     const int32_t* sb) {
   if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }
+    if (B.multi_graph) { cudaGraphExecDestroy(B.multi_graph); B.multi_graph = nullptr; B.multi_slots = 0; }
   B.graph_tried = false; B.optimizes_since_build = 0;
   B.K = make_double4(0, 0, 0, 0);
   B.C = C; B.P = P; B.N = N; B.E = E;
@@ -297,6 +307,80 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     }
   seg_unit_start.push_back((int)unit_start.size());
   B.n_items = (int)n_items; B.n_units = (int)unit_start.size(); B.n_seg = (int)seg_a.size();
+  // ---- chunked Schur lists: CTA = (free camera a, kSchurChunk of its camera-major observations).  The chunk's
+  // Y_o = Hpl_o (Hll + lambda I)^-1 stay in shared memory; an item pairs a resident observation with a partner
+  // observation o' of the same point whose camera column is >= a's (its own included); items are sorted by the
+  // partner's column, one unit per (chunk, column) -> partial 6x6 block; units are numbered in (a, b, chunk) order
+  // so that the blocks' partials are consecutive (seg_cunit_start).
+  std::vector<int> ck_cam, ck_start, ck_end, ck_ustart, cu_unit, cu_istart, it_partner, cam_ck_start(C + 1, 0), seg_cunit_start;
+  std::vector<unsigned short> it_local;
+  {
+    std::vector<int> chunk_first(C, 0);
+    for (int c = 0; c < C; ++c) {
+      cam_ck_start[c] = (int)ck_cam.size();
+      if (cam_col[c] < 0) continue;
+      for (int s = cm_start[c]; s < cm_start[c + 1]; s += kSchurChunk) {
+        ck_cam.push_back(c); ck_start.push_back(s); ck_end.push_back(std::min(cm_start[c + 1], s + kSchurChunk));
+      }
+    }
+    cam_ck_start[C] = (int)ck_cam.size();
+    const int n_ck = (int)ck_cam.size();
+    // pass 1: which (chunk, partner column) pairs have items -> unit numbering in (a, b, chunk) order
+    std::vector<std::vector<int>> ck_cols(n_ck);            // sorted partner columns with >= 1 item
+    std::vector<int> mark(Cf, -1);
+    auto for_chunk_items = [&](int ck, auto&& fn) {
+      const int ca = cam_col[ck_cam[ck]];
+      for (int o = ck_start[ck]; o < ck_end[ck]; ++o) {
+        const int p = cm_pt[o];
+        if (pt_col[p] < 0) continue;
+        for (int q = pt_start[p]; q < pt_start[p + 1]; ++q) {
+          const int cb = cam_col[pm_cam[q]];
+          if (cb < ca) continue;                            // (fixed cameras have column -1)
+          fn(o - ck_start[ck], cm_pos[pm_src[q]], cb);
+        }
+      }
+    };
+    for (int ck = 0; ck < n_ck; ++ck) {
+      for_chunk_items(ck, [&](int, int, int cb) { if (mark[cb] != ck) { mark[cb] = ck; ck_cols[ck].push_back(cb); } });
+      std::sort(ck_cols[ck].begin(), ck_cols[ck].end());
+    }
+    // units of block (a, b): the chunks of camera a that have items with column b, in chunk order
+    std::vector<int> seg_cunits(B.n_seg, 0);
+    for (int ck = 0; ck < n_ck; ++ck) {
+      const int ca = cam_col[ck_cam[ck]];
+      for (int cb : ck_cols[ck]) seg_cunits[seg_of_key[(size_t)ca * Cf + cb]]++;
+    }
+    seg_cunit_start.assign(B.n_seg + 1, 0);
+    for (int s = 0; s < B.n_seg; ++s) seg_cunit_start[s + 1] = seg_cunit_start[s] + seg_cunits[s];
+    std::vector<int> seg_fill(seg_cunit_start.begin(), seg_cunit_start.end() - 1);
+    // pass 2: items per chunk sorted by partner column (counting sort over the chunk's columns)
+    std::vector<int> col_slot(Cf, -1), cnt_c, fill_c;
+    ck_ustart.assign(n_ck + 1, 0);
+    for (int ck = 0; ck < n_ck; ++ck) {
+      const int ca = cam_col[ck_cam[ck]];
+      const int nc = (int)ck_cols[ck].size();
+      for (int i = 0; i < nc; ++i) col_slot[ck_cols[ck][i]] = i;
+      cnt_c.assign(nc + 1, 0);
+      for_chunk_items(ck, [&](int, int, int cb) { cnt_c[col_slot[cb] + 1]++; });
+      for (int i = 0; i < nc; ++i) cnt_c[i + 1] += cnt_c[i];
+      const size_t base = it_partner.size();
+      it_partner.resize(base + cnt_c[nc]); it_local.resize(base + cnt_c[nc]);
+      fill_c.assign(cnt_c.begin(), cnt_c.end() - 1);
+      for_chunk_items(ck, [&](int loc, int partner, int cb) {
+        const size_t at = base + fill_c[col_slot[cb]]++;
+        it_local[at] = (unsigned short)loc; it_partner[at] = partner;
+      });
+      for (int i = 0; i < nc; ++i) {
+        const int seg = seg_of_key[(size_t)ca * Cf + ck_cols[ck][i]];
+        cu_unit.push_back(seg_fill[seg]++);
+        cu_istart.push_back((int)(base + cnt_c[i]));
+      }
+      ck_ustart[ck + 1] = (int)cu_unit.size();
+    }
+    cu_istart.push_back((int)it_partner.size());
+    if (it_partner.size() > (size_t)((1ll << 31) - 1)) return VSLAM_ERR_BAD_ARG;
+    B.n_chunks = n_ck; B.n_cunits = (int)cu_unit.size();
+  }
   // extra (scale-edge) blocks: one per touched segment; incident-edge CSR per free camera
   std::vector<int> seg_extra_idx(B.n_seg, -1), diag_extra(Cf, -1), extra_a, extra_b;
   int n_extra = 0;
@@ -397,6 +481,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   B.lin_smem = std::max((size_t)kLinCamSmem,
                         B.cams_in_smem ? (size_t)C * kCamTabStride * sizeof(double) : 0);
   BA_TRY(cudaFuncSetAttribute(ba_schur_units, cudaFuncAttributeMaxDynamicSharedMemorySize, kSchurSmem));
+  BA_TRY(cudaFuncSetAttribute(ba_schur_chunks, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmem));
   BA_TRY(cudaFuncSetAttribute(ba_linearize_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)(kCamSmemMax * kCamTabStride * sizeof(double))));
   {
@@ -417,6 +502,11 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.cm_src.upload(cm_src)); BA_TRY(B.pt_start.upload(pt_start)); BA_TRY(B.pm_cam.upload(pm_cam));
   BA_TRY(B.pm_src.upload(pm_src)); BA_TRY(B.item_a.upload(item_a)); BA_TRY(B.item_b.upload(item_b));
   BA_TRY(B.unit_start.upload(unit_start)); BA_TRY(B.unit_len.upload(unit_len));
+  BA_TRY(B.ck_cam.upload(ck_cam)); BA_TRY(B.ck_start.upload(ck_start)); BA_TRY(B.ck_end.upload(ck_end));
+  BA_TRY(B.ck_ustart.upload(ck_ustart)); BA_TRY(B.cu_unit.upload(cu_unit)); BA_TRY(B.cu_istart.upload(cu_istart));
+  BA_TRY(B.it_partner.upload(it_partner)); BA_TRY(B.it_local.upload(it_local)); BA_TRY(B.cam_ck_start.upload(cam_ck_start));
+  BA_TRY(B.seg_cunit_start.upload(seg_cunit_start));
+  BA_TRY(B.ck_bh.alloc((size_t)std::max(B.n_chunks, 1) * 6)); BA_TRY(B.ck_partial.alloc((size_t)std::max(B.n_cunits, 1) * 36));
   BA_TRY(B.seg_a.upload(seg_a)); BA_TRY(B.seg_b.upload(seg_b));
   BA_TRY(B.seg_unit_start.upload(seg_unit_start)); BA_TRY(B.seg_extra_idx.upload(seg_extra_idx));
   BA_TRY(B.sa.upload(std::vector<int>(sa, sa + E))); BA_TRY(B.sb.upload(std::vector<int>(sb, sb + E)));
@@ -493,7 +583,8 @@ static int ba_set_state(BA& B, const double* cams, const double* pts, const doub
                         const double* scale_meas, const double* K, cudaStream_t st) {
   const double4 Knew = make_double4(K[0], K[1], K[2], K[3]);
   if (Knew.x != B.K.x || Knew.y != B.K.y || Knew.z != B.K.z || Knew.w != B.K.w) {
-    if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }  // K is baked into the nodes
+    if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }
+    if (B.multi_graph) { cudaGraphExecDestroy(B.multi_graph); B.multi_graph = nullptr; B.multi_slots = 0; }  // K is baked into the nodes
     B.graph_tried = false;
   }
   B.K = Knew;
@@ -532,7 +623,14 @@ static int enqueue_schur(BA& B, cudaStream_t st) {
   const BAView V = B.view();
   const LMState* lm = B.lm.p;
   dim3 grid(B.max_chunks, B.C);
-  if (B.Pf) {
+  const bool chunked = B.schur_variant == 0;
+  if (B.Pf && chunked) {
+    if (B.n_chunks) {
+      ChunkArgs A{B.ck_cam.p, B.ck_start.p, B.ck_end.p, B.ck_ustart.p, B.cu_unit.p, B.cu_istart.p, B.it_local.p,
+                  B.it_partner.p, B.Hpl.p, B.Hll.p, B.bl.p, B.ck_bh.p, B.ck_partial.p};
+      launch_step_kernel(ba_schur_chunks, B.n_chunks, kChunkThreads, kChunkSmem, st, V, A);
+    }
+  } else if (B.Pf) {
     launch_step_kernel(ba_point_invert, (B.Pf + 127) / 128, 128, 0, st, lm, B.Pf, B.Hll.p, B.Hinv.p, B.Wfac.p);
     launch_step_kernel(ba_compute_G, grid, kCamThreads, 0, st, V, B.Hpl.p, B.Wfac.p, B.bl.p, B.Gbuf.p, B.camp.p);
     if (B.n_units)
@@ -541,17 +639,20 @@ static int enqueue_schur(BA& B, cudaStream_t st) {
                          B.unit_partial.p);
   }
   if (B.n) {
-    BhatArgs Bh{B.Pf ? B.camp.p : nullptr, B.bp.p, B.bp_extra.p, B.bhat.p, B.bar.p, B.pcg_flags.p};
+    BhatArgs Bh{(B.Pf && !chunked) ? B.camp.p : nullptr, B.bp.p, B.bp_extra.p, B.bhat.p, B.bar.p, B.pcg_flags.p,
+                (B.Pf && chunked) ? B.ck_bh.p : nullptr, B.cam_ck_start.p};
+    const int* seg_us = chunked ? B.seg_cunit_start.p : B.seg_unit_start.p;
+    const double* partials = chunked ? B.ck_partial.p : B.unit_partial.p;
     if (B.use_direct()) {   // small system: assembled in shared memory and solved by the same launch
       DirectArgs D{};
       D.n_seg = B.n_seg; D.n = B.n; D.ld = direct_ld(B.n);
-      D.seg_a = B.seg_a.p; D.seg_b = B.seg_b.p; D.seg_unit_start = B.seg_unit_start.p; D.partial = B.unit_partial.p;
+      D.seg_a = B.seg_a.p; D.seg_b = B.seg_b.p; D.seg_unit_start = seg_us; D.partial = partials;
       D.Hpp = B.Hpp.p; D.extra = B.extra.p; D.seg_extra_idx = B.seg_extra_idx.p; D.S = B.S.p; D.Bh = Bh;
       D.x = B.dp.p; D.status = B.pcg_flags.p + 1; D.iters = B.pcg_flags.p + 2;
       launch_step_kernel(ba_solve_direct_kernel, 1, kDirectThreads, direct_smem(B.n), st, V, D);
     } else {
       launch_step_kernel(ba_schur_finalize, (B.n_seg * 36 + B.C * 6 + 127) / 128, 128, 0, st,
-                         V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, B.seg_unit_start.p, B.unit_partial.p, B.Hpp.p,
+                         V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, seg_us, partials, B.Hpp.p,
                          B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
     }
   }
@@ -587,7 +688,7 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
   if (B.Pf) launch_step_kernel(ba_backsub_cam, grid, kCamThreads, 0, st, V, B.Hpl.p, B.dp.p, B.tmp3.p);
   {
     const int n_pt_blocks = B.P ? B.n_sp : 0;
-    launch_step_kernel(ba_backsub_pt, n_pt_blocks + (B.C + 255) / 256, 256, 0, st, V, B.tmp3.p, B.Hinv.p, B.bl.p,
+    launch_step_kernel(ba_backsub_pt, n_pt_blocks + (B.C + 255) / 256, 256, 0, st, V, B.tmp3.p, B.Hll.p, B.bl.p,
                        B.dl.p, B.scale_partial.p, B.dp.p, n_pt_blocks);
   }
   // trial cost; its last CTA is the LM controller (accept / reject / terminate)
@@ -622,6 +723,30 @@ static void try_capture_step(BA& B) {
   if (graph) cudaGraphDestroy(graph);
   if (!ok) { B.step_graph = nullptr; cudaGetLastError(); }
   cudaStreamDestroy(cs);
+}
+
+// `count` trial slots as ONE graph launch (captured once per structure and count); false if capture is not possible.
+static bool launch_steps_as_one_graph(BA& B, int count, cudaStream_t st) {
+  if (B.optimizes_since_build < 1 || count < 2) return false;
+  if (B.multi_graph && B.multi_slots != count) { cudaGraphExecDestroy(B.multi_graph); B.multi_graph = nullptr; }
+  if (!B.multi_graph) {
+    cudaStream_t cs = nullptr;
+    if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return false; }
+    cudaGraph_t graph = nullptr;
+    bool ok = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+    if (ok) {
+      int rc = VSLAM_OK;
+      for (int i = 0; i < count && rc == VSLAM_OK; ++i) rc = enqueue_step(B, cs);
+      const cudaError_t e = cudaStreamEndCapture(cs, &graph);
+      ok = (rc == VSLAM_OK) && (e == cudaSuccess) && graph != nullptr;
+    }
+    if (ok) ok = cudaGraphInstantiate(&B.multi_graph, graph, 0) == cudaSuccess;
+    if (graph) cudaGraphDestroy(graph);
+    cudaStreamDestroy(cs);
+    if (!ok) { B.multi_graph = nullptr; cudaGetLastError(); return false; }
+    B.multi_slots = count;
+  }
+  return cudaGraphLaunch(B.multi_graph, st) == cudaSuccess;
 }
 
 static int launch_steps(BA& B, int count, cudaStream_t st) {
@@ -702,6 +827,7 @@ static int ba_optimize_batch(BA** Bs, int count, int max_iterations, double* sta
   while (open > 0) {
     for (int i = 0; i < count; ++i) {
       if (done[i]) continue;
+      if (launch_steps_as_one_graph(*Bs[i], batch[i], pool[i % pool_n])) continue;
       const int rc = launch_steps(*Bs[i], batch[i], pool[i % pool_n]);
       if (rc) return rc;
     }
@@ -777,10 +903,22 @@ extern "C" int vslam_ba_set_solver(vslam_ba* h, double pcg_tol, int pcg_max_iter
   const int mi = pcg_max_iter > 0 ? pcg_max_iter : B.pcg_max_iter;
   if (pcg_tol != B.pcg_tol || mi != B.pcg_max_iter) {   // both are baked into the captured step
     if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }
+    if (B.multi_graph) { cudaGraphExecDestroy(B.multi_graph); B.multi_graph = nullptr; B.multi_slots = 0; }
     B.graph_tried = false;
   }
   B.pcg_tol = pcg_tol;
   B.pcg_max_iter = mi;
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_ba_set_schur_variant(vslam_ba* h, int variant) {
+  if (!h || variant < 0 || variant > 1) return VSLAM_ERR_BAD_ARG;
+  BA& B = h->impl;
+  if (variant != B.schur_variant) {
+    if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }
+    B.graph_tried = false;
+  }
+  B.schur_variant = variant;
   return VSLAM_OK;
 }
 
@@ -790,6 +928,7 @@ extern "C" int vslam_ba_set_linear_solver(vslam_ba* h, int kind) {
   if (kind == 2 && B.n > kDirectMax) return VSLAM_ERR_BAD_ARG;
   if (kind != B.linear_solver) {   // the choice is baked into the captured step
     if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }
+    if (B.multi_graph) { cudaGraphExecDestroy(B.multi_graph); B.multi_graph = nullptr; B.multi_slots = 0; }
     B.graph_tried = false;
   }
   B.linear_solver = kind;

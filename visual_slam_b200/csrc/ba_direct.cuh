@@ -98,12 +98,7 @@ __global__ void __launch_bounds__(kDirectThreads) ba_solve_direct_kernel(BAView 
       const int c = t / 6, i = t - 6 * c;
       const int col = V.cam_col[c];
       if (col < 0) continue;
-      double s = 0.0;
-      if (A.Bh.camp != nullptr) {
-        const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
-        const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
-        for (int k = 0; k < n_chunks; ++k) s += A.Bh.camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
-      }
+      const double s = bhat_partial_sum(V, A.Bh, c, i);
       Ls[n * ld + 6 * col + i] = (A.Bh.bp[6 * col + i] + A.Bh.bp_extra[6 * col + i]) - s;
     }
   }

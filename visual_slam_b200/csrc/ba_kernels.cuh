@@ -923,11 +923,145 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
   }
 }
 
+// Schur complement by RESIDENT CHUNKS (the default; the sorted-unit kernel above is kept as a variant).  A CTA
+// owns kSchurChunk camera-major observations of ONE free camera a.  Load phase: for each of them
+// Y_o = Hpl_o (Hll_j + lambda I)^-1 (6x3; the 3x3 inverse is formed on the fly, so neither the point inverses nor
+// G = Hpl W are ever written to HBM) goes to shared memory, and the chunk's share of sum Hpl Hinv bl (bhat) is
+// reduced.  Item phase: an item pairs a resident observation with one partner observation o' of the same point
+// (camera column b >= a's, its own included); its contribution to block (a, b) is Y_o Hpl_o'^T.  Items are sorted by
+// b; a warp takes one (chunk, b) unit at a time, one item per lane and round; only the PARTNER blocks are gathered
+// (cooperative cp.async, consecutive lanes copy consecutive 16-byte pieces): half the L2 traffic of gathering both
+// factors, and no G pass.  36 warp sums per unit by the transposed butterfly -> ck_partial[unit], units numbered
+// in (a, b, chunk) order so that ba_schur_finalize sums a block's partials in a fixed order.
+constexpr int kSchurChunk = 512;
+constexpr int kChunkThreads = 256;
+constexpr int kChunkWarps = kChunkThreads / 32;
+constexpr int kChunkStageDoubles = 32 * 18;
+constexpr int kChunkSmem = (kSchurChunk * 18 + kChunkWarps * kChunkStageDoubles) * 8;
+
+struct ChunkArgs {
+  const int* ck_cam; const int* ck_start; const int* ck_end; const int* ck_ustart; const int* cu_unit;
+  const int* cu_istart; const unsigned short* it_local; const int* it_partner;
+  const double* Hpl; const double* Hll; const double* bl;
+  double* ck_bh; double* partial;
+};
+
+__global__ void __launch_bounds__(kChunkThreads, 2) ba_schur_chunks(BAView V, ChunkArgs A) {
+  extern __shared__ __align__(128) double ch_smem[];
+  __shared__ double red[kChunkWarps * 6];
+  double* Ys = ch_smem;                                            // [kSchurChunk][18]
+  const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31, ck = blockIdx.x;
+  double* stage = ch_smem + kSchurChunk * 18 + wid * kChunkStageDoubles;   // this warp's 32 gathered partner blocks
+  const int o0 = __ldg(A.ck_start + ck), o1 = __ldg(A.ck_end + ck);
+  const int u0 = __ldg(A.ck_ustart + ck), u1 = __ldg(A.ck_ustart + ck + 1);
+  pdl_wait();
+  pdl_trigger();
+  if (V.st->done) return;
+  const double lambda = V.st->lambda;
+  // ---- load phase
+  double bh[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+  for (int rep = 0; rep < kSchurChunk / kChunkThreads; ++rep) {
+    const int loc = rep * kChunkThreads + tid, o = o0 + loc;
+    double y[18];
+#pragma unroll
+    for (int i = 0; i < 18; ++i) y[i] = 0.0;
+    if (o < o1) {
+      const int pcol = V.pt_col[V.cm_pt[o]];
+      if (pcol >= 0) {
+        double h[6], hi[6], b[3], H[18];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) h[j] = A.Hll[6 * (size_t)pcol + j];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) b[j] = A.bl[3 * (size_t)pcol + j];
+        load18(A.Hpl + (size_t)o * 18, H);
+        h[0] += lambda; h[3] += lambda; h[5] += lambda;
+        sym3_inverse(h, hi);
+        double z[3];
+        sym3_mul(hi, b, z);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          const double h0 = H[3 * r], h1 = H[3 * r + 1], h2 = H[3 * r + 2];
+          y[3 * r] = h0 * hi[0] + h1 * hi[1] + h2 * hi[2];
+          y[3 * r + 1] = h0 * hi[1] + h1 * hi[3] + h2 * hi[4];
+          y[3 * r + 2] = h0 * hi[2] + h1 * hi[4] + h2 * hi[5];
+          bh[r] += h0 * z[0] + h1 * z[1] + h2 * z[2];
+        }
+      }
+    }
+    store18(Ys + (size_t)loc * 18, y);
+  }
+  block_reduce<6, kChunkThreads>(bh, red);                         // (ends with a block barrier: Ys is visible)
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) A.ck_bh[6 * (size_t)ck + i] = bh[i];
+  }
+  // ---- item phase
+  for (int ul = u0 + wid; ul < u1; ul += kChunkWarps) {
+    const int unit = __ldg(A.cu_unit + ul);
+    const int i0 = __ldg(A.cu_istart + ul), i1 = __ldg(A.cu_istart + ul + 1);
+    double acc[36];
+#pragma unroll
+    for (int i = 0; i < 36; ++i) acc[i] = 0.0;
+    int loc_n = -1, part_n = -1;
+    if (i0 + lane < i1) { loc_n = A.it_local[i0 + lane]; part_n = A.it_partner[i0 + lane]; }
+#pragma unroll 1
+    for (int base = i0; base < i1; base += 32) {
+      const int loc = loc_n, part = part_n;
+      loc_n = -1; part_n = -1;
+      if (base + 32 + lane < i1) { loc_n = A.it_local[base + 32 + lane]; part_n = A.it_partner[base + 32 + lane]; }
+      __syncwarp();                                                // the stage has been read by every lane
+#pragma unroll
+      for (int j = 0; j < 9; ++j) {
+        const int q = j * 32 + lane;                               // 16-byte piece of the stage
+        const int bk = (q * 7282) >> 16;                           // q / 9: block 0..31
+        const int r = q - 9 * bk;
+        const int idx = __shfl_sync(0xffffffffu, part, bk);
+        if (idx >= 0) cp_async16(stage + 2 * q, A.Hpl + (size_t)idx * 18 + 2 * r);
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      __syncwarp();
+      if (part >= 0) {
+        double gb[18];
+        load18(stage + lane * 18, gb);
+        const double* yr = Ys + (size_t)loc * 18;
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          const double y0 = yr[3 * r], y1 = yr[3 * r + 1], y2 = yr[3 * r + 2];
+#pragma unroll
+          for (int c = 0; c < 6; ++c)
+            acc[6 * r + c] = fma(y0, gb[3 * c], fma(y1, gb[3 * c + 1], fma(y2, gb[3 * c + 2], acc[6 * r + c])));
+        }
+      }
+    }
+    double tail[4] = {acc[32], acc[33], acc[34], acc[35]};
+    double (&head)[32] = reinterpret_cast<double (&)[32]>(acc);
+    warp_transpose_sum32(head, lane);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) tail[i] = warp_sum(tail[i]);
+    A.partial[(size_t)unit * 36 + lane] = head[0];
+    if (lane < 4) A.partial[(size_t)unit * 36 + 32 + lane] = lane == 0 ? tail[0] : lane == 1 ? tail[1] : lane == 2 ? tail[2] : tail[3];
+  }
+}
+
 // S block (a,b) = [a==b](Hpp_a + lambda I) + scale-edge block - sum of its units; mirrored.
 struct BhatArgs {   // bhat = (bp + bp_extra) - sum_j Hpl_j Hinv_j bl_j  (ordered chunk sum of ba_compute_G's partials)
   const double* camp; const double* bp; const double* bp_extra; double* bhat;
   unsigned* pcg_bar; int* pcg_flags;   // reset here for the solve that follows (no memset nodes in the step)
+  const double* ck_bh; const int* cam_ck_start;   // chunked Schur variant: per-chunk partials [chunk][6], chunks of a camera
 };
+__device__ __forceinline__ double bhat_partial_sum(const BAView& V, const BhatArgs& Bh, int c, int i) {
+  double s = 0.0;
+  if (Bh.ck_bh != nullptr) {
+    for (int k = Bh.cam_ck_start[c]; k < Bh.cam_ck_start[c + 1]; ++k) s += Bh.ck_bh[6 * (size_t)k + i];
+  } else if (Bh.camp != nullptr) {
+    const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
+    const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
+    for (int k = 0; k < n_chunks; ++k) s += Bh.camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
+  }
+  return s;
+}
 __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restrict__ seg_a,
                                   const int* __restrict__ seg_b,
                                   const int* __restrict__ seg_unit_start,
@@ -952,12 +1086,7 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
     if (Bh.bhat == nullptr || c >= V.C) return;
     const int col = V.cam_col[c];
     if (col < 0) return;
-    double s = 0.0;
-    if (Bh.camp != nullptr) {
-      const int n_obs = V.cm_start[c + 1] - V.cm_start[c];
-      const int n_chunks = (n_obs + kCamChunk - 1) / kCamChunk;
-      for (int k = 0; k < n_chunks; ++k) s += Bh.camp[((size_t)c * V.max_chunks + k) * kCamVals + i];
-    }
+    const double s = bhat_partial_sum(V, Bh, c, i);
     Bh.bhat[6 * col + i] = (Bh.bp[6 * col + i] + Bh.bp_extra[6 * col + i]) - s;
     return;
   }
@@ -1033,7 +1162,7 @@ __device__ __forceinline__ void update_cams_body(const BAView& V, const double* 
 // Back-substitution, point half: dl = Hinv (bl - sum_o v_o); trial point = point + dl.
 // Also the per-CTA partial of sum dl (lambda dl + bl)  (computeScale, landmark part).
 __global__ void __launch_bounds__(256)
-ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restrict__ Hinv,
+ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restrict__ Hll,
               const double* __restrict__ bl, double* __restrict__ dl_out,
               double* __restrict__ scale_partial, const double* __restrict__ dp, int n_pt_blocks) {
   __shared__ double red[8];
@@ -1059,9 +1188,11 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
         if (V.cam_col[V.pm_cam[o]] < 0) continue;
         r[0] -= tmp3[3 * (size_t)o]; r[1] -= tmp3[3 * (size_t)o + 1]; r[2] -= tmp3[3 * (size_t)o + 2];
       }
-      double hi[6], d[3];
+      double h[6], hi[6], d[3];   // (Hll + lambda I)^-1 on the fly: the inverses are not kept in HBM
 #pragma unroll
-      for (int j = 0; j < 6; ++j) hi[j] = Hinv[6 * (size_t)col + j];
+      for (int j = 0; j < 6; ++j) h[j] = Hll[6 * (size_t)col + j];
+      h[0] += lambda; h[3] += lambda; h[5] += lambda;
+      sym3_inverse(h, hi);
       sym3_mul(hi, r, d);
       sc[0] = d[0] * (lambda * d[0] + b0) + d[1] * (lambda * d[1] + b1) + d[2] * (lambda * d[2] + b2);
       X[0] += d[0]; X[1] += d[1]; X[2] += d[2];

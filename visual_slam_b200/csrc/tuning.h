@@ -8,6 +8,9 @@ extern "C" {
 int vslam_hamming_set_variant(int variant);
 /* Feature response kernel: 0 automatic (by batch size), 1 warp-specialised (latency), 2 one thread per column. */
 int vslam_features_set_variant(int variant);
+/* Schur complement kernel of a BA problem: 0 resident chunks (default), 1 sorted units over a precomputed G. */
+struct vslam_ba;
+int vslam_ba_set_schur_variant(struct vslam_ba* ba, int variant);
 #ifdef __cplusplus
 }
 #endif
