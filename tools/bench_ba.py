@@ -9,9 +9,9 @@ sys.path.insert(0, ".")
 from visual_slam_b200.ba import BAEngine  # noqa: E402
 from visual_slam_b200.ba_problem import synthetic_ba  # noqa: E402
 
-variant = "chunks"
-if "--units" in sys.argv:
-    sys.argv.remove("--units"); variant = "units"
+variant = "units"
+if "--chunks" in sys.argv:
+    sys.argv.remove("--chunks"); variant = "chunks"
 which = sys.argv[1:] or ["c3", "c4"]
 cfg = {"c3": dict(n_cams=10, n_pts=5000, obs_per_pt=6.0, seed=0),
        "c4": dict(n_cams=200, n_pts=100000, obs_per_pt=10.0, seed=1)}

@@ -81,8 +81,8 @@ class BAEngine:
         """"auto" = "pcg" (block-Jacobi PCG, the default and the faster one); "direct": LDL^T in one CTA, n <= 96."""
         _cabi.check(_cabi.lib().vslam_ba_set_linear_solver(self._h, {"auto": 0, "pcg": 1, "direct": 2}[kind]))
 
-    def set_schur_variant(self, variant="chunks"):
-        """Tuning / tests: "chunks" (resident Y per camera chunk, the default) or "units" (sorted units over G)."""
+    def set_schur_variant(self, variant="units"):
+        """Tuning / tests: "units" (sorted units over G, the default) or "chunks" (resident Y per camera chunk; slower)."""
         _cabi.check(_cabi.lib().vslam_ba_set_schur_variant(self._h, {"chunks": 0, "units": 1}[variant]))
 
     def dims(self):

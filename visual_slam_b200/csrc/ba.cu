@@ -101,7 +101,10 @@ struct BA {
   DevBuf<int> ck_cam, ck_start, ck_end, ck_ustart, cu_unit, cu_istart, it_partner, cam_ck_start, seg_cunit_start;
   DevBuf<unsigned short> it_local;
   DevBuf<double> ck_bh, ck_partial;
-  int n_chunks = 0, n_cunits = 0, schur_variant = 0;   // 0 = chunked (resident Y), 1 = sorted units over G
+  int n_chunks = 0, n_cunits = 0;
+  // 1 = sorted units over G (default: 323 us at C4), 0 = resident chunks (measured slower: 455 us; with 8-lane unit
+  // groups 712 us, with a double-buffered gather at one CTA per SM 1064 us -- latency-bound on its index loads)
+  int schur_variant = 1;
   // fused linearisation work lists
   DevBuf<LinWork> lin_work, cam_work;
   DevBuf<unsigned> cam_ticket, lin_ticket;
