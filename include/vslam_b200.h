@@ -29,7 +29,8 @@ typedef enum {
   VSLAM_ERR_ALIGNMENT = 2,  /* descriptor buffers must be 16-byte aligned */
   VSLAM_ERR_CUDA = 3,       /* a CUDA runtime call failed; see vslam_last_cuda_error() */
   VSLAM_ERR_NUMERIC = 4,    /* solver breakdown reported in-band (PCG indefinite, ...) */
-  VSLAM_ERR_NO_DEVICE = 5
+  VSLAM_ERR_NO_DEVICE = 5,
+  VSLAM_ERR_TOO_LARGE = 6   /* a no-allocation entry point was given a size beyond its static scratch; see vslam_last_cuda_error() */
 } vslam_status;
 
 const char* vslam_status_string(int status);
@@ -401,6 +402,23 @@ int vslam_direct_solve(const double* S, const double* b, double* x, int n, int32
  * g2o reports as "Cholesky failure" (reference debug.txt). */
 int vslam_pcg_solve(const double* S, const double* b, double* x, int n, double tol, int max_iter,
                     int32_t* status_iters, void* stream);
+
+/*
+ * vslam_pcg_solve WITHOUT any allocation.  This entry point has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernels and results as vslam_pcg_solve; its scratch (grid-barrier
+ * counter, flags, partial sums, two vectors of n doubles) lives in a file-scope device array of 24.25 KiB that every
+ * GPU loading the library holds until exit.  It calls no cudaMalloc / cudaFree and does not synchronise.
+ *   n                 multiple of 6, at most vslam_pcg_solve_static_max_n() = 1536 unknowns (256 free cameras);
+ *                     beyond that it returns VSLAM_ERR_TOO_LARGE (message in vslam_last_cuda_error()) and launches nothing
+ *   status_iters_dev  DEVICE int32[2] = {status, iterations}, written by the kernel (stream-ordered)
+ * All calls share the one scratch array, which keeps the last call's contents (what must start at zero is cleared
+ * on `stream` before every launch): calls that overlap on the GPU -- two streams, two host threads -- race on it
+ * and must be serialised by the caller.
+ */
+int vslam_pcg_solve_static(const double* S, const double* b, double* x, int n, double tol, int max_iter,
+                           int32_t* status_iters_dev, void* stream);
+int vslam_pcg_solve_static_max_n(void);
 
 /* ------------------------------------------------------------------------- */
 /* 5. Device-resident tracking window                          */

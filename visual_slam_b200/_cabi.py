@@ -80,6 +80,8 @@ def _declare(lib):
     lib.vslam_window_read_cams.argtypes = [vp, vp, i32, i32, vp]
     lib.vslam_window_info.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(vp), C.POINTER(vp)]
     lib.vslam_direct_solve.argtypes = [vp, vp, vp, i32, C.POINTER(C.c_int32), vp]
+    lib.vslam_pcg_solve_static.argtypes = [vp, vp, vp, i32, f64, i32, vp, vp]
+    lib.vslam_pcg_solve_static_max_n.argtypes = []
     lib.vslam_pcg_solve.argtypes = [vp, vp, vp, i32, f64, i32, C.POINTER(C.c_int32), vp]
 
 

@@ -8,6 +8,7 @@ static thread_local char g_err[512] = "";
 void set_cuda_error(cudaError_t e, const char* where) {
   snprintf(g_err, sizeof(g_err), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
 }
+void snprintf_last_error(const char* fmt, int a, int b) { snprintf(g_err, sizeof(g_err), fmt, a, b); }
 int sm_count() {
   static int cached = 0;
   if (cached > 0) return cached;
@@ -27,6 +28,7 @@ extern "C" const char* vslam_status_string(int s) {
     case VSLAM_ERR_CUDA: return "CUDA error";
     case VSLAM_ERR_NUMERIC: return "numerical breakdown";
     case VSLAM_ERR_NO_DEVICE: return "no CUDA device";
+    case VSLAM_ERR_TOO_LARGE: return "size exceeds the static scratch capacity of this entry point";
     default: return "unknown status";
   }
 }

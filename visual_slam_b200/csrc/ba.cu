@@ -1269,3 +1269,70 @@ extern "C" int vslam_window_info(vslam_window* h, int32_t* out4, double** cams_d
   if (stats_dev) *stats_dev = W.stats;
   return VSLAM_OK;
 }
+
+// ---- vslam_pcg_solve without any allocation -------------------------------------------------------------------
+// Added (no counterpart in the reference): callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it) get the stand-alone PCG solve with
+// its scratch (grid-barrier counter, flags, partial sums, the published search direction and the local S u rows) in
+// a file-scope device array.  Every GPU that loads the library holds kPcgStaticBytes (24.25 KiB) until exit.  All calls
+// share the array and it keeps the last call's contents: the header (barrier counter, flags, partials) is cleared
+// on the caller's stream before every launch; the vectors are fully written by the kernel before it reads them.
+// Calls that overlap on the GPU (two streams, two host threads) race on it -- serialise them.
+constexpr int kPcgStaticMaxN = 1536;                                   // unknowns (a multiple of 6): 256 free cameras
+constexpr size_t kPcgStaticHeader = 256;                               // bar (u32) @0, flags (4 x i32) @16, part (4 x f64) @64
+constexpr size_t kPcgStaticBytes = kPcgStaticHeader + 2 * (size_t)kPcgStaticMaxN * sizeof(double);
+static __device__ __align__(256) unsigned char g_pcg_static_scratch[kPcgStaticBytes];
+
+// In host code the array's name is only a stand-in for the symbol; its device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int pcg_static_scratch(unsigned char** out) {
+  constexpr int kMaxDevices = 64;
+  static unsigned char* addr[kMaxDevices] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { set_cuda_error(e, "cudaGetDevice"); return VSLAM_ERR_CUDA; }
+  if (dev < 0 || dev >= kMaxDevices) return VSLAM_ERR_BAD_ARG;
+  if (!addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_pcg_static_scratch);
+    if (e != cudaSuccess || !p) { set_cuda_error(e, "cudaGetSymbolAddress(g_pcg_static_scratch)"); return VSLAM_ERR_CUDA; }
+    addr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = addr[dev];
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_pcg_solve_static_max_n(void) { return kPcgStaticMaxN; }
+
+extern "C" int vslam_pcg_solve_static(const double* S, const double* b, double* x, int n, double tol, int max_iter,
+                                      int32_t* status_iters_dev, void* stream) {
+  if (!S || !b || !x || n <= 0 || n % 6 || !status_iters_dev || !(tol > 0) || max_iter < 0) return VSLAM_ERR_BAD_ARG;
+  if (n > kPcgStaticMaxN) {
+    snprintf_last_error("vslam_pcg_solve_static: n = %d exceeds the static scratch capacity of %d unknowns", n, kPcgStaticMaxN);
+    return VSLAM_ERR_TOO_LARGE;
+  }
+  unsigned char* base = nullptr;
+  int rc = pcg_static_scratch(&base);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  BA_TRY(cudaMemsetAsync(base, 0, kPcgStaticHeader, st));             // what must start at zero: barrier counter, flags, partials
+  PcgArgs A{};
+  A.S = S; A.b = b; A.x = x; A.n = n; A.rows = n; A.G = 1; A.max_iter = max_iter; A.tol = tol;
+  A.bar = reinterpret_cast<unsigned*>(base);
+  A.fail_flag = reinterpret_cast<int*>(base + 16);
+  A.part = reinterpret_cast<double*>(base + 64);
+  A.p_glob = reinterpret_cast<double*>(base + kPcgStaticHeader);
+  A.w_loc = A.p_glob + kPcgStaticMaxN;
+  A.status = status_iters_dev; A.iters = status_iters_dev + 1;         // outputs go straight to the caller's device buffer
+  if (n <= kPcgSmallMax) {
+    ba_pcg_small_kernel<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
+    return check_launch("ba_pcg_small_kernel");
+  }
+  const size_t smem_slab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8 + (size_t)n * n);
+  const size_t smem_noslab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8);
+  A.slab_in_smem = smem_slab <= 200 * 1024;
+  const size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
+  BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
+  return check_launch("ba_pcg_kernel");
+}

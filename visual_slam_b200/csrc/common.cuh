@@ -29,6 +29,8 @@ inline int check_launch(const char* where) {
   } while (0)
 
 int sm_count();  // cached cudaDevAttrMultiProcessorCount of the current device
+// Formats a message into the string vslam_last_cuda_error() returns (argument errors that deserve an explanation).
+void snprintf_last_error(const char* fmt, int a, int b);
 
 // ---- mbarrier + TMA bulk copy (cp.async.bulk, 1-D) -------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
