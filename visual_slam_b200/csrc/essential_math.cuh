@@ -204,35 +204,51 @@ VSLAM_HD inline int aberth_roots(const double* c, int deg, cplx* z) {
     sincos(2.0 * 3.14159265358979323846 * i / deg + 0.4, &s, &co);
     z[i] = {r0 * co, r0 * s};
   }
+  // A root is FINISHED (and frozen) once its correction is at rounding level relative to the root, or once p(z) is at
+  // the rounding level of its own evaluation (backward-stable root: |p(z)| <= 32 eps sum |c_k| |z|^k) -- the second
+  // test is what ends the iteration for roots whose corrections keep dithering in the last bits (a test on the
+  // largest relative step alone let about a fifth of all five-point polynomials run into the iteration cap, and
+  // in a warp one such lane holds the other 31).  The real roots are polished afterwards (polish_xyz).
+  unsigned finished = 0;
+  const unsigned all = (1u << deg) - 1u;
   int it = 0;
-  for (; it < 200; ++it) {
-    double worst = 0.0;
+  for (; it < 200 && finished != all; ++it) {
     for (int i = 0; i < deg; ++i) {
-      // Horner for p and p'
+      if ((finished >> i) & 1u) continue;
+      // Horner for p and p', and for the evaluation bound sum |c_k| |z|^k
+      const cplx zi = z[i];
+      const double az = sqrt(zi.re * zi.re + zi.im * zi.im);
       cplx p = {c[deg], 0.0}, dp = {0.0, 0.0};
+      double bound = fabs(c[deg]);
       for (int k = deg - 1; k >= 0; --k) {
-        dp = cmul(dp, z[i]); dp.re += p.re; dp.im += p.im;
-        p = cmul(p, z[i]); p.re += c[k];
+        dp = cmul(dp, zi); dp.re += p.re; dp.im += p.im;
+        p = cmul(p, zi); p.re += c[k];
+        bound = bound * az + fabs(c[k]);
       }
-      if (p.re == 0.0 && p.im == 0.0) continue;
+      if (fabs(p.re) + fabs(p.im) <= 7.2e-15 * bound) { finished |= 1u << i; continue; }
       cplx w = cdiv(p, dp);
-      if (!(isfinite(w.re) && isfinite(w.im))) { z[i].re += 1e-3 * r0; z[i].im += 1e-3 * r0; worst = 1.0; continue; }
+      if (!(isfinite(w.re) && isfinite(w.im))) { z[i].re += 1e-3 * r0; z[i].im += 1e-3 * r0; continue; }
       cplx s = {0.0, 0.0};
       for (int j = 0; j < deg; ++j) {
         if (j == i) continue;
-        const cplx d = {z[i].re - z[j].re, z[i].im - z[j].im};
-        const cplx inv = cdiv({1.0, 0.0}, d);
-        if (isfinite(inv.re) && isfinite(inv.im)) { s.re += inv.re; s.im += inv.im; }
+        // 1 / (z_i - z_j) = conj(d) / |d|^2: one division (coincident or absurdly distant roots give a non-finite
+        // term, which is left out exactly like before)
+        const double dr = zi.re - z[j].re, di = zi.im - z[j].im;
+        const double q = 1.0 / (dr * dr + di * di);
+        const double ir = dr * q, ii = -di * q;
+        if (isfinite(ir) && isfinite(ii)) { s.re += ir; s.im += ii; }
       }
       const cplx ws = cmul(w, s);
       const cplx step = cdiv(w, {1.0 - ws.re, -ws.im});
       if (!(isfinite(step.re) && isfinite(step.im))) continue;
       z[i].re -= step.re; z[i].im -= step.im;
       const double m = fmax(fabs(step.re), fabs(step.im)) / fmax(1e-300, fmax(fabs(z[i].re), fabs(z[i].im)));
-      worst = fmax(worst, m);
+      if (m < 1e-15) finished |= 1u << i;
     }
-    if (worst < 1e-15) break;
   }
+#ifdef VSLAM_ABERTH_HOOK
+  VSLAM_ABERTH_HOOK(it);
+#endif
   return it;
 }
 
