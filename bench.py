@@ -157,7 +157,7 @@ def cpu_matching_variants():
     return out
 
 
-REF_PAIRS_PER_STEP = 24
+REF_PAIRS_PER_STEP = 64          # ~0.2 s of CPU per step on 16 cores: long enough that the cv2 thread pool is warm throughout
 
 
 def run_reference(args):
@@ -171,10 +171,9 @@ def run_reference(args):
     pairs = _cpu_pairs()
     kp = np.zeros((NQ, 2), np.float32)
     per_step = REF_PAIRS_PER_STEP
-    for w in range(max(args.warmup, 1)):
-        for i in range(2):
-            q_, t_ = pairs[(2 * w + i) % 8]
-            om.match_features_cv2(kp, q_, kp, t_, RATIO)
+    for i in range(max(24, 8 * args.warmup)):            # untimed: thread pool, allocator and caches settle
+        q_, t_ = pairs[i % 8]
+        om.match_features_cv2(kp, q_, kp, t_, RATIO)
     step_ms = []
     t0 = time.perf_counter()
     for s in range(args.steps):

@@ -247,7 +247,7 @@ __global__ void essential_budget_kernel(const int32_t* __restrict__ n_pts, int n
 // points that triangulate in front of both cameras and closer than `dist`; the candidate with the
 // most survivors wins (cv2's order of preference on ties); pass 2 writes its mask (0 / 255) and the
 // homogeneous triangulated points (4 x N like cv2, unit columns, sign free).
-constexpr int kPoseThreads = 128;
+constexpr int kPoseThreads = 512;
 
 __global__ void __launch_bounds__(kPoseThreads)
 recover_pose_kernel(const double* __restrict__ E_in, const float* __restrict__ p1, const float* __restrict__ p2,
@@ -270,17 +270,19 @@ recover_pose_kernel(const double* __restrict__ E_in, const float* __restrict__ p
     const double sgn = (k >= 2) ? -1.0 : 1.0;
     t[0] = sgn * s_t[0]; t[1] = sgn * s_t[1]; t[2] = sgn * s_t[2];
   };
+  // pass 1: one work item per (point, candidate) -- the 4x4 DLT decomposition is a long dependent chain, so the
+  // items are spread over the threads instead of giving a thread all four candidates of its points
   int cnt[4] = {0, 0, 0, 0};
-  for (int i = tid; i < n; i += kPoseThreads) {
+  for (int w = tid; w < 4 * n; w += kPoseThreads) {
+    const int i = w >> 2, k = w & 3;
     const float2 a = g1[i], c = g2[i];
     const double x1 = ((double)a.x - cx) / fx, y1 = ((double)a.y - cy) / fy;
     const double x2 = ((double)c.x - cx) / fx, y2 = ((double)c.y - cy) / fy;
-    for (int k = 0; k < 4; ++k) {
-      const double* R; double t[3], Q[4];
-      candidate(k, R, t);
-      triangulate_dlt(R, t, x1, y1, x2, y2, Q);
-      cnt[k] += cheirality_ok(R, t, Q, dist) ? 1 : 0;
-    }
+    const double* R; double t[3], Q[4];
+    candidate(k, R, t);
+    triangulate_dlt(R, t, x1, y1, x2, y2, Q);
+    const int ok = cheirality_ok(R, t, Q, dist) ? 1 : 0;
+    cnt[0] += (k == 0) ? ok : 0; cnt[1] += (k == 1) ? ok : 0; cnt[2] += (k == 2) ? ok : 0; cnt[3] += (k == 3) ? ok : 0;
   }
   for (int k = 0; k < 4; ++k) cnt[k] = __reduce_add_sync(0xffffffffu, cnt[k]);
   if ((tid & 31) == 0)
