@@ -28,8 +28,8 @@ NQ = NT = 2048
 RATIO = 0.8
 PREHEAT_STEPS = 24            # fixed, untimed, before the W warm-up steps (identical on every rank)
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures
-HAMMING_DRAM_BYTES_PER_PAIR = (83026176 + 4331264) / 592.0
-HAMMING_TRAFFIC_SOURCE = "profiles/r1_hamming_knn2_ncu_full.txt (592 pairs per launch, scaled to this launch)"
+HAMMING_DRAM_BYTES_PER_PAIR = (165076480 + 26065408) / 1184.0
+HAMMING_TRAFFIC_SOURCE = "profiles/r2_hamming_knn2_ncu_full.txt (1184 pairs per launch, the bench's own launch)"
 BA_LIN_DRAM_BYTES_C4 = 45245440 + 92398336
 BA_LIN_TRAFFIC_SOURCE = "profiles/r1_ba_linearize_ncu_full.txt (C4, one launch; part of Hpl is still dirty in L2)"
 METRIC = "hamming_matches_per_s"
