@@ -348,11 +348,11 @@ int vslam_ba_set_state(vslam_ba* ba, const double* cams, const double* pts, cons
 int vslam_ba_get_state(vslam_ba* ba, double* cams, double* pts, void* stream);
 /* PCG relative residual tolerance (default 1e-10) and iteration cap (<=0 keeps the default). */
 int vslam_ba_set_solver(vslam_ba* ba, double pcg_tol, int pcg_max_iter);
-/* Linear solver of the reduced camera system: 0 = automatic = 1 = block-Jacobi PCG (north_star; also the faster one
- * where both apply), 2 = in-CTA LDL^T factorisation with the system's assembly fused in front, for n = 6 * free
- * cameras <= 96 (what g2o's CHOLMOD path does for a local window; rejected when n > 96).  A non-positive pivot /
- * curvature is reported the same way by both (rejected LM step).  Measured on B200 at n = 54 (C3): PCG 22.6 us +
- * 7 us assembly launch against 31 us + assembly for the factorisation (54 sequential pivots, ~0.5 us each). */
+/* Linear solver of the reduced camera system: 0 = automatic = 1 = block-Jacobi PCG (north_star), 2 = in-CTA direct
+ * solve for n = 6 * free cameras <= 96 (what g2o's CHOLMOD path does for a local window; rejected when n > 96):
+ * register-resident Gauss-Jordan elimination for n <= 63, shared-memory LDL^T above; 3 = the LDL^T kernel at every
+ * n <= 96.  A non-positive pivot / curvature is reported the same way by all (rejected LM step).  Measured on B200
+ * at n = 54 (C3): PCG 22 us, Gauss-Jordan 17 us, LDL^T 33 us per solve; the LM iteration as a whole 71 / 69 / 81 us. */
 int vslam_ba_set_linear_solver(vslam_ba* ba, int kind);
 
 /*
@@ -393,8 +393,9 @@ int vslam_ba_dims(vslam_ba* ba, int32_t* out8);
  * 5 bhat 6 dp 7 dl 8 trial cams 9 trial pts. */
 int vslam_ba_read(vslam_ba* ba, int what, double* dst, int64_t capacity, void* stream);
 
-/* The small-system solver on its own: in-CTA Cholesky of a dense symmetric system, n a multiple of 6, n <= 96
- * (device pointers); *status (host) = 0 solved, 1 = a pivot was not positive (x = 0): g2o's "Cholesky failure". */
+/* The small-system solver on its own on a dense symmetric system, n a multiple of 6, n <= 96 (device pointers):
+ * Gauss-Jordan for n <= 63, LDL^T above; pass -n to force the LDL^T kernel.  *status (host) = 0 solved, 1 = a pivot
+ * was not positive (x = 0): g2o's "Cholesky failure". */
 int vslam_direct_solve(const double* S, const double* b, double* x, int n, int32_t* status, void* stream);
 
 /* Block-Jacobi PCG on a caller-supplied dense symmetric system (n multiple of 6, device pointers);

@@ -108,36 +108,73 @@ def test_pcg_reports_indefinite_fixture_f1(golden_dir):
 
 
 def test_direct_solver_solves_spd_systems_and_reports_the_indefinite_fixture(golden_dir):
-    """The small-system path (in-CTA Cholesky, csrc/ba_direct.cuh): exact on SPD systems of every block count up to
-    16 cameras, and fixture F1 (reference debug.txt, one negative eigenvalue) comes back as a failed solve."""
+    """The small-system path (csrc/ba_direct.cuh: Gauss-Jordan in registers for n <= 63, LDL^T in shared memory
+    above, "ldlt" forces the latter): exact on SPD systems of every block count up to 16 cameras, and fixture F1
+    (reference debug.txt, one negative eigenvalue) comes back as a failed solve."""
     from visual_slam_b200.ba import direct_solve
     rng = np.random.default_rng(1)
-    for n in (6, 12, 54, 90, 96):
+    for n in (6, 12, 18, 30, 42, 48, 54, 60, 66, 90, 96):
         A = rng.normal(size=(n, n)); S = A @ A.T + n * np.eye(n); b = rng.normal(size=n)
-        x, status = direct_solve(torch.from_numpy(S).cuda(), torch.from_numpy(b).cuda())
-        assert status == 0
-        assert np.abs(x.cpu().numpy() - np.linalg.solve(S, b)).max() <= 1e-12 * np.abs(b).max()
+        for kernel in ("auto", "ldlt"):
+            x, status = direct_solve(torch.from_numpy(S).cuda(), torch.from_numpy(b).cuda(), kernel)
+            assert status == 0
+            assert np.abs(x.cpu().numpy() - np.linalg.solve(S, b)).max() <= 1e-12 * np.abs(b).max(), (n, kernel)
     S = np.load(os.path.join(golden_dir, "ba_debug_reduced_system.npz"))["S"]
     x, status = direct_solve(torch.from_numpy(S).cuda(), torch.ones(90, dtype=torch.float64).cuda())
     assert status == 1 and float(x.abs().max()) == 0.0
+    # an indefinite system small enough for the Gauss-Jordan kernel: both kernels refuse it
+    A = rng.normal(size=(54, 54)); S = A @ A.T + 54 * np.eye(54); S[20, 20] = -1.0
+    for kernel in ("auto", "ldlt"):
+        x, status = direct_solve(torch.from_numpy(S).cuda(), torch.ones(54, dtype=torch.float64).cuda(), kernel)
+        assert status == 1 and float(x.abs().max()) == 0.0
 
 
-def test_both_linear_solvers_take_the_same_lm_path():
-    """C3-sized window: the in-CTA factorisation (optional, n <= 96) and PCG to 1e-10 (the default) agree on
-    iterations, trials and cost."""
+def test_all_linear_solvers_take_the_same_lm_path():
+    """C3-sized window: Gauss-Jordan ("direct"), LDL^T ("ldlt") and PCG to 1e-10 (the default) agree on iterations,
+    trials and cost."""
     p = synthetic_ba(10, 2000, 6.0, seed=3)
     res = {}
-    for kind in ("direct", "pcg"):
+    for kind in ("direct", "ldlt", "pcg"):
         eng = BAEngine(p)
         eng.set_linear_solver(kind)
         res[kind] = eng.optimize(10)
         eng.close()
-    a, b = res["direct"], res["pcg"]
-    assert (a["iterations"], a["trials"]) == (b["iterations"], b["trials"])
-    assert abs(a["final_cost"] - b["final_cost"]) <= 1e-9 * b["final_cost"]
-    assert a["pcg_iterations"] == 0 and b["pcg_iterations"] > 0
+    b = res["pcg"]
+    for kind in ("direct", "ldlt"):
+        a = res[kind]
+        assert (a["iterations"], a["trials"]) == (b["iterations"], b["trials"])
+        assert abs(a["final_cost"] - b["final_cost"]) <= 1e-9 * b["final_cost"]
+        assert a["pcg_iterations"] == 0
+    assert b["pcg_iterations"] > 0
     h = oba.optimize(p.copy(), 10)
-    assert abs(a["final_cost"] - h["final_cost"]) <= 1e-9 * h["final_cost"]
+    assert abs(res["direct"]["final_cost"] - h["final_cost"]) <= 1e-9 * h["final_cost"]
+
+
+def test_blocks_of_s_without_schur_units_and_multi_chunk_cameras():
+    """Cameras 1 and 2 share no point but are joined by a scale edge: block (1, 2) of S has a scale-edge part and
+    no Schur unit; each camera has several 256-observation chunks (bhat is an ordered sum of chunk partials).
+    Trajectory and cost against the restatement, with PCG and with the direct solver."""
+    p0 = synthetic_ba(4, 1500, 3.0, seed=21)
+    # points with an even index keep their observations from cameras {0, 1, 3}, the others from {0, 2, 3}
+    keep = np.where(p0.obs_pt % 2 == 0, p0.obs_cam != 2, p0.obs_cam != 1)
+    cnt = np.bincount(p0.obs_pt[keep], minlength=p0.n_pts)
+    keep &= cnt[p0.obs_pt] >= 2
+    used = np.nonzero(np.bincount(p0.obs_pt[keep], minlength=p0.n_pts) > 0)[0]
+    remap = np.full(p0.n_pts, -1); remap[used] = np.arange(len(used))
+    p = BAProblem(p0.cams, p0.pts[used], p0.obs_cam[keep], remap[p0.obs_pt[keep]], p0.obs_uv[keep], p0.K,
+                  p0.cam_fixed, None, p0.scale_a, p0.scale_b, p0.scale_meas)
+    both = set(p.obs_pt[p.obs_cam == 1]) & set(p.obs_pt[p.obs_cam == 2])
+    assert not both and np.bincount(p.obs_cam).min() > 256
+    ref = p.copy()
+    h = oba.optimize(ref, 10)
+    for kind in ("pcg", "direct"):
+        q = p.copy()
+        eng = BAEngine(q)
+        eng.set_linear_solver(kind)
+        st = eng.optimize(10)
+        eng.close()
+        assert (st["iterations"], st["trials"]) == (h["iterations"], h["trials"])
+        assert abs(st["final_cost"] - h["final_cost"]) <= 1e-9 * h["final_cost"]
 
 
 def test_pcg_solves_spd_systems():

@@ -79,7 +79,7 @@ class BAEngine:
 
     def set_linear_solver(self, kind="auto"):
         """"auto" = "pcg" (block-Jacobi PCG, the default and the faster one); "direct": LDL^T in one CTA, n <= 96."""
-        _cabi.check(_cabi.lib().vslam_ba_set_linear_solver(self._h, {"auto": 0, "pcg": 1, "direct": 2}[kind]))
+        _cabi.check(_cabi.lib().vslam_ba_set_linear_solver(self._h, {"auto": 0, "pcg": 1, "direct": 2, "ldlt": 3}[kind]))
 
     def set_schur_variant(self, variant="units"):
         """Tuning / tests: "units" (sorted units over G, the default) or "chunks" (resident Y per camera chunk; slower)."""
@@ -180,13 +180,15 @@ _POOL = {}    # device -> BAEngine kept between calls: the reference builds a fr
               # (main.py:146,213,322); here only the structure arrays change, the device buffers stay
 
 
-def direct_solve(S, b):
-    """In-CTA Cholesky on a dense symmetric system (device tensors, n <= 96).  Returns (x, status)."""
+def direct_solve(S, b, kernel="auto"):
+    """In-CTA direct solve of a dense symmetric system (device tensors, n <= 96): register-resident Gauss-Jordan
+    for n <= 63, shared-memory LDL^T above (kernel="ldlt" forces the latter).  Returns (x, status)."""
     S = S.contiguous(); b = b.contiguous()
     x = torch.zeros_like(b)
     out = C.c_int32(0)
     with torch.cuda.device(S.device):
-        _cabi.check(_cabi.lib().vslam_direct_solve(_cabi.ptr(S), _cabi.ptr(b), _cabi.ptr(x), S.shape[0],
+        _cabi.check(_cabi.lib().vslam_direct_solve(_cabi.ptr(S), _cabi.ptr(b), _cabi.ptr(x),
+                                                   -S.shape[0] if kernel == "ldlt" else S.shape[0],
                                                    C.byref(out), _cabi.stream_ptr()))
     return x, int(out.value)
 

@@ -139,7 +139,8 @@ struct BA {
   double pcg_tol = 1e-10;
   int pcg_max_iter = 0;
   int linear_solver = 0;   // 0 auto = PCG (measured faster: 22.6 + 7 us against 31 us at n = 54), 1 PCG, 2 in-CTA LDL^T
-  bool use_direct() const { return n > 0 && n <= kDirectMax && linear_solver == 2; }
+  bool use_direct() const { return n > 0 && n <= kDirectMax && (linear_solver == 2 || linear_solver == 3); }
+  bool use_gj() const { return use_direct() && linear_solver == 2 && n <= kGJMax; }   // 3 forces the LDL^T kernel
 
   BAView view() const {
     BAView V;
@@ -621,7 +622,11 @@ static int enqueue_linearize(BA& B, cudaStream_t st) {
 }
 
 // Schur complement of the damped system: Hinv = W W^T, G = Hpl W, bhat, S = Hpp - sum G G^T
-// (sorted-segment reduction).
+// (sorted-segment reduction).  A small system is then solved by the in-CTA direct kernel from S, bhat in HBM when
+// that solver is selected.  (Measured and dropped: letting the last unit of a block finish S and the last chunk of
+// a camera finish bhat, with W formed on the fly -- two launches instead of four.  The launches overlap under
+// programmatic dependent launch anyway: C3 gained 1 us per trial, C4 lost 23 us to the ticket / fence tails of its
+// 31k units.)
 static int enqueue_schur(BA& B, cudaStream_t st) {
   const BAView V = B.view();
   const LMState* lm = B.lm.p;
@@ -646,17 +651,15 @@ static int enqueue_schur(BA& B, cudaStream_t st) {
                 (B.Pf && chunked) ? B.ck_bh.p : nullptr, B.cam_ck_start.p};
     const int* seg_us = chunked ? B.seg_cunit_start.p : B.seg_unit_start.p;
     const double* partials = chunked ? B.ck_partial.p : B.unit_partial.p;
-    if (B.use_direct()) {   // small system: assembled in shared memory and solved by the same launch
+    launch_step_kernel(ba_schur_finalize, (B.n_seg * 36 + B.C * 6 + 127) / 128, 128, 0, st,
+                       V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, seg_us, partials, B.Hpp.p,
+                       B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
+    if (B.use_direct()) {
       DirectArgs D{};
-      D.n_seg = B.n_seg; D.n = B.n; D.ld = direct_ld(B.n);
-      D.seg_a = B.seg_a.p; D.seg_b = B.seg_b.p; D.seg_unit_start = seg_us; D.partial = partials;
-      D.Hpp = B.Hpp.p; D.extra = B.extra.p; D.seg_extra_idx = B.seg_extra_idx.p; D.S = B.S.p; D.Bh = Bh;
+      D.n = B.n; D.ld = direct_ld(B.n); D.done = &B.lm.p->done; D.S = B.S.p; D.b = B.bhat.p;
       D.x = B.dp.p; D.status = B.pcg_flags.p + 1; D.iters = B.pcg_flags.p + 2;
-      launch_step_kernel(ba_solve_direct_kernel, 1, kDirectThreads, direct_smem(B.n), st, V, D);
-    } else {
-      launch_step_kernel(ba_schur_finalize, (B.n_seg * 36 + B.C * 6 + 127) / 128, 128, 0, st,
-                         V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, seg_us, partials, B.Hpp.p,
-                         B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
+      if (B.use_gj()) launch_step_kernel(ba_solve_gj_kernel, 1, kGJThreads, 0, st, D);
+      else launch_step_kernel(ba_solve_direct_kernel, 1, kDirectThreads, direct_smem(B.n), st, D);
     }
   }
   return check_launch("ba_schur");
@@ -926,9 +929,9 @@ extern "C" int vslam_ba_set_schur_variant(vslam_ba* h, int variant) {
 }
 
 extern "C" int vslam_ba_set_linear_solver(vslam_ba* h, int kind) {
-  if (!h || kind < 0 || kind > 2) return VSLAM_ERR_BAD_ARG;
+  if (!h || kind < 0 || kind > 3) return VSLAM_ERR_BAD_ARG;
   BA& B = h->impl;
-  if (kind == 2 && B.n > kDirectMax) return VSLAM_ERR_BAD_ARG;
+  if ((kind == 2 || kind == 3) && B.n > kDirectMax) return VSLAM_ERR_BAD_ARG;
   if (kind != B.linear_solver) {   // the choice is baked into the captured step
     if (B.step_graph) { cudaGraphExecDestroy(B.step_graph); B.step_graph = nullptr; }
     if (B.multi_graph) { cudaGraphExecDestroy(B.multi_graph); B.multi_graph = nullptr; B.multi_slots = 0; }
@@ -1120,21 +1123,29 @@ extern "C" int vslam_ba_read(vslam_ba* h, int what, double* dst, int64_t capacit
   return VSLAM_OK;
 }
 
-// Stand-alone in-CTA Cholesky solve of a caller-supplied dense symmetric system (tests: fixture F1).
-extern "C" int vslam_direct_solve(const double* S, const double* b, double* x, int n, int32_t* status_host,
+// Stand-alone small-system solve of a caller-supplied dense symmetric system (tests: fixture F1): the register-
+// resident Gauss-Jordan kernel for n <= 63, the shared-memory LDL^T kernel above that (negative n forces LDL^T).
+extern "C" int vslam_direct_solve(const double* S, const double* b, double* x, int n_signed, int32_t* status_host,
                                   void* stream) {
+  const int n = n_signed < 0 ? -n_signed : n_signed;
+  const bool force_ldl = n_signed < 0;
   if (!S || !b || !x || n <= 0 || n % 6 || n > kDirectMax || !status_host) return VSLAM_ERR_BAD_ARG;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   DevBuf<int> flags;
   BA_TRY(flags.alloc(4));
   BA_TRY(cudaMemsetAsync(flags.p, 0, 4 * sizeof(int), st));
-  BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)direct_smem(kDirectMax)));
   DirectArgs D{};
-  D.n = n; D.ld = direct_ld(n); D.x = x; D.status = flags.p + 1; D.iters = flags.p + 2; D.dense_S = S; D.dense_b = b;
-  BAView V{};
-  ba_solve_direct_kernel<<<1, kDirectThreads, direct_smem(n), st>>>(V, D);
-  int rc = check_launch("ba_solve_direct_kernel");
+  D.n = n; D.ld = direct_ld(n); D.x = x; D.status = flags.p + 1; D.iters = flags.p + 2; D.S = S; D.b = b;
+  int rc;
+  if (n <= kGJMax && !force_ldl) {
+    ba_solve_gj_kernel<<<1, kGJThreads, 0, st>>>(D);
+    rc = check_launch("ba_solve_gj_kernel");
+  } else {
+    BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)direct_smem(kDirectMax)));
+    ba_solve_direct_kernel<<<1, kDirectThreads, direct_smem(n), st>>>(D);
+    rc = check_launch("ba_solve_direct_kernel");
+  }
   if (rc) return rc;
   int host[4];
   BA_TRY(cudaMemcpyAsync(host, flags.p, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
