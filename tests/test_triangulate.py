@@ -100,3 +100,34 @@ def test_shape_errors_raise_before_any_device_work():
     with pytest.raises(ValueError):
         from visual_slam_b200.triangulate import _one
         _one(np.eye(4, 4)[:2], np.eye(3, 4), np.zeros((4, 2)), np.zeros((4, 2)), None, 1.0, "cpu")
+
+
+# The reference's only known-answer script for triangulation (src/v1/testing.py:46-97): hard-coded projection
+# matrices and pixels, recorded stdout "[-0.035 -0.006 2.022]" for cv2.triangulatePoints on the first pair and the
+# two-point set x1h2 / x2h2.  The numbers below are the script's literals.
+_V1_P1 = np.array([[5.010e+03, 0.000e+00, 3.600e+02, 0.000e+00],
+                   [0.000e+00, 5.010e+03, 6.400e+02, 0.000e+00],
+                   [0.000e+00, 0.000e+00, 1.000e+00, 0.000e+00]])
+_V1_P2 = np.array([[5.037e+03, -9.611e+01, -1.756e+03, 4.284e+03],
+                   [2.148e+02, 5.354e+03, 1.918e+02, 8.945e+02],
+                   [3.925e-01, 7.092e-02, 9.169e-01, 4.930e-01]])
+_V1_X1 = np.array([[274.128, 624.409], [274.129, 624.409], [322.527, 624.869]])
+_V1_X2 = np.array([[239.571, 533.568], [239.572, 533.568], [284.507, 534.572]])
+
+
+def test_oracle_reproduces_the_v1_known_answer():
+    import cv2
+    X = _dehom(otri.triangulate(_V1_P1, _V1_P2, _V1_X1, _V1_X2))
+    assert np.allclose(np.round(X[0], 3), [-0.035, -0.006, 2.022])          # the recorded stdout
+    ref = cv2.triangulatePoints(_V1_P1, _V1_P2, _V1_X1.T, _V1_X2.T)          # what the script calls
+    ref = (ref[:3] / ref[3]).T
+    # the reference's DLT (helper_functions.py:281-291) and cv2's differ in row scaling only: same point to 1e-4 m
+    assert np.abs(X - ref).max() < 1e-4
+
+
+@pytest.mark.gpu
+def test_kernel_reproduces_the_v1_known_answer():
+    from visual_slam_b200.triangulate import triangulate
+    X = _dehom(triangulate(_V1_P1, _V1_P2, _V1_X1, _V1_X2))
+    assert np.allclose(np.round(X[0], 3), [-0.035, -0.006, 2.022])
+    assert np.abs(X - _dehom(otri.triangulate(_V1_P1, _V1_P2, _V1_X1, _V1_X2))).max() < 1e-9
