@@ -297,6 +297,13 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     for_items([&](size_t key, int a, int b) { long long o = fill[key]++; item_a[o] = a; item_b[o] = b; });
   }
   std::vector<int> seg_a, seg_b, seg_unit_start, unit_start, unit_len, seg_of_key((size_t)Cf * Cf, -1);
+  // items per warp work unit: kUnitItems, or more when the problem still offers every resident warp several units
+  // (a unit pays ~600 instructions of prologue + 36-value reduction; C4's blocks hold ~300 items, so 256-item units
+  // split most of them into a full unit and a one-round remainder)
+  static const int unit_env = [] { const char* e = getenv("VSLAM_BA_UNIT_ITEMS"); return e ? atoi(e) : 0; }();
+  const long long warp_slots = (long long)std::max(1, sm_count()) * 12;
+  long long unit_items = (n_items / (2 * warp_slots) >= kUnitItemsLarge) ? kUnitItemsLarge : kUnitItems;
+  if (unit_env >= 32) unit_items = unit_env / 32 * 32;
   for (int a = 0; a < Cf; ++a)
     for (int b = a; b < Cf; ++b) {
       const size_t key = (size_t)a * Cf + b;
@@ -304,9 +311,9 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
       seg_of_key[key] = (int)seg_a.size();
       seg_a.push_back(a); seg_b.push_back(b);
       seg_unit_start.push_back((int)unit_start.size());
-      for (long long s = cnt[key]; s < cnt[key + 1]; s += kUnitItems) {
+      for (long long s = cnt[key]; s < cnt[key + 1]; s += unit_items) {
         unit_start.push_back((int)s);
-        unit_len.push_back((int)std::min<long long>(kUnitItems, cnt[key + 1] - s));
+        unit_len.push_back((int)std::min<long long>(unit_items, cnt[key + 1] - s));
       }
     }
   seg_unit_start.push_back((int)unit_start.size());
@@ -792,8 +799,10 @@ static int ba_optimize(BA& B, int max_iterations, double* stats, cudaStream_t st
   }
   int budget = max_iterations * 10 + 1;   // at most 10 trials per outer iteration
   int batch = max_iterations;
+  static const bool one_graph = [] { const char* e = getenv("VSLAM_BA_ONE_GRAPH"); return e && atoi(e) != 0; }();
   while (true) {
-    int rc = launch_steps(B, batch, st);
+    int rc = VSLAM_OK;
+    if (!(one_graph && launch_steps_as_one_graph(B, batch, st))) rc = launch_steps(B, batch, st);
     if (rc) return rc;
     rc = ba_sync_state(B, st);
     if (rc) return rc;

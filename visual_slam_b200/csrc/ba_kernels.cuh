@@ -16,6 +16,7 @@ constexpr int kCamChunk = 256;    // observations of one camera handled by one C
 constexpr int kCamThreads = 256;
 constexpr int kCamVals = 28;      // 21 Hpp upper + 6 bp + 1 cost
 constexpr int kUnitItems = 256;   // Schur items per warp work unit
+constexpr int kUnitItemsLarge = 352;   // ... when the problem is large enough to keep every warp busy with those
 constexpr int kPointLanes = 4;    // lanes cooperating on one point in the point role
 
 // Levenberg-Marquardt controller state, resident in HBM: every kernel of an LM step reads it, the
