@@ -849,8 +849,9 @@ def run_gpu(args):
     h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2e_steps = max(1, min(args.steps, 5))
     h0.record()
-    for _ in range(e2e_steps):
-        kq_pin, kt_pin, nk_pin = hm.run()
+    for _ in range(e2e_steps):                 # every step copies ITS inputs in and ITS results out; consecutive steps
+        kq_pin, kt_pin, nk_pin = hm.run(join=False)   # pipeline on the matcher's two streams (see HostMatcher.run)
+    hm.join()
     h1.record()
     sync()
     e2e_ms = torch.tensor([h0.elapsed_time(h1)], dtype=torch.float64, device=dev)
@@ -899,7 +900,9 @@ def run_gpu(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": workload_config(world), "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": hm.h2d_bytes,
-                    "d2h_bytes_per_step": hm.d2h_bytes, "steps": e2e_steps},
+                    "d2h_bytes_per_step": hm.d2h_bytes, "steps": e2e_steps,
+                    "path": "HostMatcher.run(join=False) x steps + join(): per step pinned host -> H2D -> kNN-2 + filter -> "
+                            "D2H in 8 chunks on two streams; consecutive steps pipeline on those streams"},
             "gpu_launches": 3 * args.steps, "roofline": roofline,
             "pair_distances_per_s": world * B * NQ * NT * args.steps / (ms * 1e-3)}
     if tracking:

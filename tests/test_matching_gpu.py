@@ -160,3 +160,23 @@ def test_host_matcher_equals_device_call_and_oracle(batch, chunks):
             assert n == len(oq) and np.array_equal(kq[b, :n].numpy(), oq) and np.array_equal(kt[b, :n].numpy(), ot)
         qs, ts = synth.descriptors_batch(batch, nq, nt, seed=77 + batch)              # other data, same buffers
     assert hm.h2d_bytes == batch * (nq + nt) * 32 and hm.d2h_bytes == 4 * batch * (2 * nq + 1)
+
+
+def test_host_matcher_pipelined_calls_give_the_same_lists():
+    """run(join=False) three times in a row (the bench's end-to-end loop: consecutive batches pipeline on the two
+    internal streams), then join(): the pinned results are those of a plain run()."""
+    from visual_slam_b200.matching import HostMatcher
+    batch, nq, nt = 11, 300, 257
+    qs, ts = synth.descriptors_batch(batch, nq, nt, seed=5)
+    hm = HostMatcher(batch, nq, nt, 0.8, True, chunks=4)
+    hm.load(qs, ts)
+    kq, kt, nk = hm.run()
+    torch.cuda.synchronize()
+    ref = (kq.numpy().copy(), kt.numpy().copy(), nk.numpy().copy())
+    kq.zero_(); kt.zero_(); nk.zero_()
+    for _ in range(3):
+        kq, kt, nk = hm.run(join=False)
+    hm.join()
+    torch.cuda.synchronize()
+    assert np.array_equal(nk.numpy(), ref[2]) and np.array_equal(kq.numpy(), ref[0]) and np.array_equal(kt.numpy(), ref[1])
+

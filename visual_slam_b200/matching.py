@@ -168,8 +168,13 @@ class HostMatcher:
         self.q_pin.copy_(torch.from_numpy(np.ascontiguousarray(q)))
         self.t_pin.copy_(torch.from_numpy(np.ascontiguousarray(t)))
 
-    def run(self):
-        """H2D -> match -> D2H for the staged batch; returns pinned (keep_q, keep_t, n_keep)."""
+    def run(self, join=True):
+        """H2D -> match -> D2H for the staged batch; returns pinned (keep_q, keep_t, n_keep), valid once the
+        current stream has been synchronised (join=True) or after `join()` + a synchronisation (join=False).
+        With join=False consecutive calls pipeline: the chunks of the next batch queue behind the same chunks of
+        this one on the two internal streams, so its first host->device copies run under this batch's last
+        kernels instead of waiting for its last device->host copy (a serving loop that stages batch i + 1 while
+        batch i is matched; the pinned result buffers are overwritten by the next call)."""
         B = self.batch
         step = (B + self.chunks - 1) // self.chunks
         cur = torch.cuda.current_stream(self.device)
@@ -188,6 +193,12 @@ class HostMatcher:
                 self.keep_q_pin[lo:hi].copy_(out["keep_q"], non_blocking=True)
                 self.keep_t_pin[lo:hi].copy_(out["keep_t"], non_blocking=True)
                 self.n_keep_pin[lo:hi].copy_(out["n_keep"], non_blocking=True)
+        if join:
+            self.join()
+        return self.keep_q_pin, self.keep_t_pin, self.n_keep_pin
+
+    def join(self):
+        """Makes the current stream wait for everything `run(join=False)` has enqueued."""
+        cur = torch.cuda.current_stream(self.device)
         for st in self.streams:
             cur.wait_stream(st)
-        return self.keep_q_pin, self.keep_t_pin, self.n_keep_pin
