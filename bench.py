@@ -295,7 +295,25 @@ def ba_figures(torch):
                      "linearize_ms": lin, "linearize_single_cold_launch_ms": lin_single,
                      "schur_ms": schur_ms, "trial_ms": trial_ms,
                      "linearize_bytes": p.linearize_bytes(),
-                     "linearize_gbs": p.linearize_bytes() / (lin * 1e-3) / 1e9}
+                     "linearize_gbs": p.linearize_bytes() / (lin * 1e-3) / 1e9,
+                     "linear_solver": "block-Jacobi PCG to 1e-10 (north_star; the default)"}
+        if name == "c3":   # the same window with the in-CTA direct solver (what g2o's CHOLMOD path does for n = 54)
+            eng.set_linear_solver("direct")
+            b2 = None
+            for rep in range(4):
+                eng.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                e0.record()
+                st2 = eng.optimize(10)
+                e1.record()
+                torch.cuda.synchronize()
+                if rep > 0:
+                    b2 = e0.elapsed_time(e1) if b2 is None else min(b2, e0.elapsed_time(e1))
+            out[name]["direct_solver"] = {"lm_iters_per_s": st2["iterations"] / (b2 * 1e-3), "ms_per_optimize10": b2,
+                                          "trials": st2["trials"], "final_cost": st2["final_cost"],
+                                          "what": "register-resident Gauss-Jordan on the 54 x 54 reduced system "
+                                                  "(vslam_ba_set_linear_solver(2)), same LM path"}
         eng.close()
         del flush
     return out
@@ -356,8 +374,9 @@ def features_figures(torch, batch=64, steps=5, dist=None, world=1, rank=0):
         hx.run()
     torch.cuda.synchronize()
     e0.record()
-    for _ in range(steps):
-        kp_pin, de_pin, nk_pin = hx.run()
+    for _ in range(steps):                     # consecutive batches pipeline on the extractor's two streams
+        kp_pin, de_pin, nk_pin = hx.run(join=False)
+    hx.join()
     e1.record()
     torch.cuda.synchronize()
     e2e_ms = e0.elapsed_time(e1) / steps
@@ -395,7 +414,7 @@ def features_figures(torch, batch=64, steps=5, dist=None, world=1, rank=0):
             "scaling": "weak (frames sharded by rank, NCCL all_gather of the key-point counts)", "height": H, "width": W,
             "keypoints_per_frame": float(n_kp.mean()),
             "e2e_frames_per_s": world * batch / (e2e_ms * 1e-3), "h2d_bytes_per_step": int(hx.h2d_bytes),
-            "d2h_bytes_per_step": int(hx.d2h_bytes), "e2e_path": "HostFeatureExtractor (pinned host -> H2D -> "
+            "d2h_bytes_per_step": int(hx.d2h_bytes), "e2e_path": "HostFeatureExtractor.run(join=False) x steps + join() (pinned host -> H2D -> "
             "pipeline -> D2H, 3 chunks on two streams; PCIe-bound)",
             "algorithmic_bytes_per_frame": alg, "algorithmic_gbs_per_gpu": batch * alg / (ms * 1e-3) / 1e9,
             "gpu_launches_per_step": 7, "data": "synthetic block-texture frames (synth.frames), 3000-corner cap binds",

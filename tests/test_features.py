@@ -243,6 +243,16 @@ def test_gpu_host_extractor_equals_direct_call():
             n = int(n_kp[b])
             assert np.array_equal(kp[b, :n].numpy(), want["kp"][b, :n])
             assert np.array_equal(desc[b, :n].numpy(), want["desc"][b, :n])
+    kp.zero_(); desc.zero_(); n_kp.zero_()
+    for _ in range(3):                      # pipelined calls (the bench's end-to-end loop), joined once
+        kp, desc, n_kp = hx.run(join=False)
+    hx.join()
+    torch.cuda.synchronize()
+    assert np.array_equal(n_kp.numpy(), want["n_kp"])
+    for b in range(7):
+        n = int(n_kp[b])
+        assert np.array_equal(kp[b, :n].numpy(), want["kp"][b, :n])
+        assert np.array_equal(desc[b, :n].numpy(), want["desc"][b, :n])
 
 
 @pytest.mark.gpu

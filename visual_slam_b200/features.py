@@ -118,8 +118,10 @@ class HostFeatureExtractor:
         """Copies caller frames (numpy uint8 [batch, H, W, 3], BGR) into the pinned staging buffer."""
         self.img_pin.copy_(torch.from_numpy(np.ascontiguousarray(frames)))
 
-    def run(self):
-        """H2D -> extract -> D2H for the staged batch; returns pinned (kp, desc, n_kp)."""
+    def run(self, join=True):
+        """H2D -> extract -> D2H for the staged batch; returns pinned (kp, desc, n_kp).  join=False leaves the two
+        internal streams un-joined so that consecutive calls pipeline (the next batch's frame copies run under this
+        batch's kernels); call join() before reading the pinned results."""
         cur = torch.cuda.current_stream(self.device)
         start = torch.cuda.Event()
         start.record(cur)
@@ -136,9 +138,15 @@ class HostFeatureExtractor:
                 self.kp_pin[lo:hi].copy_(o["kp"], non_blocking=True)
                 self.desc_pin[lo:hi].copy_(o["desc"], non_blocking=True)
                 self.n_kp_pin[lo:hi].copy_(o["n_kp"], non_blocking=True)
+        if join:
+            self.join()
+        return self.kp_pin, self.desc_pin, self.n_kp_pin
+
+    def join(self):
+        """Makes the current stream wait for everything run(join=False) has enqueued."""
+        cur = torch.cuda.current_stream(self.device)
         for st in self.streams:
             cur.wait_stream(st)
-        return self.kp_pin, self.desc_pin, self.n_kp_pin
 
 
 class FeatureExtractor:
