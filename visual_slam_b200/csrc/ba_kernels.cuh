@@ -790,16 +790,21 @@ __global__ void __launch_bounds__(kCamThreads)
 ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict__ Wf,
              const double* __restrict__ bl, double* __restrict__ Gout, double* __restrict__ camp) {
   __shared__ double red[(kCamThreads / 32) * 6];
+  static_assert(kCamChunk == kCamThreads, "one observation per thread and chunk");
+  // static structure before the wait (see ba_schur_finalize): chunk bounds and this thread's point column
+  const int c = blockIdx.y, chunk = blockIdx.x;
+  const int start = __ldg(V.cm_start + c) + chunk * kCamChunk;
+  const int end = min(__ldg(V.cm_start + c + 1), start + kCamChunk);
+  const int ccol = __ldg(V.cam_col + c);
+  const int o_mine = start + threadIdx.x;
+  const int pcol_mine = o_mine < end ? __ldg(V.pt_col + __ldg(V.cm_pt + o_mine)) : -1;
   pdl_wait();
   pdl_trigger();
   if (V.st->done) return;
-  const int c = blockIdx.y, chunk = blockIdx.x;
-  const int start = V.cm_start[c] + chunk * kCamChunk;
-  const int end = min(V.cm_start[c + 1], start + kCamChunk);
-  if (start >= end || V.cam_col[c] < 0) return;
+  if (start >= end || ccol < 0) return;
   double acc[6] = {0, 0, 0, 0, 0, 0};
-  for (int o = start + threadIdx.x; o < end; o += kCamThreads) {
-    const int pcol = V.pt_col[V.cm_pt[o]];
+  for (int o = o_mine; o < end; o += kCamThreads) {
+    const int pcol = pcol_mine;
     if (pcol < 0) continue;
     double h[18], w[6], b[3], g[18];
     load18(Hpl + (size_t)o * 18, h);
@@ -849,11 +854,12 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
   extern __shared__ __align__(128) double sch_smem[];
   const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int u = blockIdx.x * kSchurWarps + wid;
+  // (static work lists: the unit's bounds are fetched before the wait, see ba_schur_finalize)
+  const int s0 = u < n_units ? __ldg(unit_start + u) : 0, len = u < n_units ? __ldg(unit_len + u) : 0;
   pdl_wait();
   pdl_trigger();
   if (st->done || u >= n_units) return;
   double* ring = sch_smem + (size_t)wid * kSchurStages * kSchurStageDoubles;
-  const int s0 = unit_start[u], len = unit_len[u];
   const int n_it = (len + 31) >> 5;
   auto load_idx = [&](int it, int& ia, int& ib) {
     const int i = it * 32 + lane;
@@ -1070,6 +1076,15 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
                                   const double* __restrict__ Hpp,
                                   const double* __restrict__ extra,
                                   const int* __restrict__ seg_extra_idx, double* __restrict__ S, BhatArgs Bh) {
+  // the work lists are static structure: fetched BEFORE the wait, i.e. while the producing kernels still run
+  // (programmatic dependent launch), so the dependent part starts with its indices in registers
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int seg = t / 36, e = t % 36;
+  int a = 0, b = 0, ex = -1, u0 = 0, u1 = 0;
+  if (seg < n_seg) {
+    a = __ldg(seg_a + seg); b = __ldg(seg_b + seg); ex = __ldg(seg_extra_idx + seg);
+    u0 = __ldg(seg_unit_start + seg); u1 = __ldg(seg_unit_start + seg + 1);
+  }
   pdl_wait();
   pdl_trigger();
   if (blockIdx.x == 0 && threadIdx.x == 0) {   // PCG bookkeeping of this trial: grid-barrier counter, fail / status / iterations
@@ -1078,8 +1093,6 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
   }
   if (V.st->done) return;
   const double lambda = V.st->lambda;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int seg = t / 36, e = t % 36;
   if (seg >= n_seg) {
     // the threads behind the S blocks build bhat (one per camera and row)
     const int tb = t - n_seg * 36;
@@ -1091,12 +1104,11 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
     Bh.bhat[6 * col + i] = (Bh.bp[6 * col + i] + Bh.bp_extra[6 * col + i]) - s;
     return;
   }
-  const int a = seg_a[seg], b = seg_b[seg], r = e / 6, c = e % 6;
-  const int ex = seg_extra_idx[seg];
+  const int r = e / 6, c = e % 6;
   double v = ex >= 0 ? extra[(size_t)ex * 36 + e] : 0.0;
   if (a == b) v += Hpp[36 * a + e] + (r == c ? lambda : 0.0);
   double s = 0.0;
-  for (int u = seg_unit_start[seg]; u < seg_unit_start[seg + 1]; ++u) s += partial[(size_t)u * 36 + e];
+  for (int u = u0; u < u1; ++u) s += partial[(size_t)u * 36 + e];
   v -= s;
   S[(size_t)(6 * a + r) * n + 6 * b + c] = v;
   if (a != b) S[(size_t)(6 * b + c) * n + 6 * a + r] = v;
@@ -1106,18 +1118,21 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
 __global__ void __launch_bounds__(kCamThreads)
 ba_backsub_cam(BAView V, const double* __restrict__ Hpl, const double* __restrict__ dp,
                double* __restrict__ tmp3) {
+  const int c = blockIdx.y, chunk = blockIdx.x;   // (static structure before the wait, see ba_schur_finalize)
+  const int start = __ldg(V.cm_start + c) + chunk * kCamChunk;
+  const int end = min(__ldg(V.cm_start + c + 1), start + kCamChunk);
+  const int col = __ldg(V.cam_col + c);
+  const int o_mine = start + threadIdx.x;
+  const int pcol_mine = o_mine < end ? __ldg(V.pt_col + __ldg(V.cm_pt + o_mine)) : -1;
+  const int pm_mine = o_mine < end ? __ldg(V.cm_pm + o_mine) : 0;
   pdl_wait();
   pdl_trigger();
-  const int c = blockIdx.y, chunk = blockIdx.x;
-  const int start = V.cm_start[c] + chunk * kCamChunk;
-  const int end = min(V.cm_start[c + 1], start + kCamChunk);
-  const int col = V.cam_col[c];
   if (V.st->done || start >= end || col < 0) return;
   double d[6];
 #pragma unroll
   for (int i = 0; i < 6; ++i) d[i] = dp[6 * col + i];
-  for (int o = start + threadIdx.x; o < end; o += kCamThreads) {
-    if (V.pt_col[V.cm_pt[o]] < 0) continue;
+  for (int o = o_mine; o < end; o += kCamThreads) {
+    if (pcol_mine < 0) continue;
     double h[18];
     load18(Hpl + (size_t)o * 18, h);
     double v[3] = {0, 0, 0};
@@ -1126,7 +1141,7 @@ ba_backsub_cam(BAView V, const double* __restrict__ Hpl, const double* __restric
 #pragma unroll
       for (int j = 0; j < 3; ++j) v[j] += h[3 * r + j] * d[r];
     }
-    double* dst = tmp3 + (size_t)V.cm_pm[o] * 3;
+    double* dst = tmp3 + (size_t)pm_mine * 3;
     dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2];
   }
 }
@@ -1167,6 +1182,11 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
               const double* __restrict__ bl, double* __restrict__ dl_out,
               double* __restrict__ scale_partial, const double* __restrict__ dp, int n_pt_blocks) {
   __shared__ double red[8];
+  // static structure before the wait (see ba_schur_finalize)
+  const int p_mine = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool pt_role = (int)blockIdx.x < n_pt_blocks && p_mine < V.P;
+  const int col_mine = pt_role ? __ldg(V.pt_col + p_mine) : -1;
+  const int ps0 = pt_role ? __ldg(V.pt_start + p_mine) : 0, ps1 = pt_role ? __ldg(V.pt_start + p_mine + 1) : 0;
   pdl_wait();
   pdl_trigger();
   if (V.st->done) return;
@@ -1177,15 +1197,15 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
   const double lambda = V.st->lambda;
   const double* __restrict__ pts = V.pts[V.st->cur];
   double* __restrict__ pts_trial = V.pts[V.st->cur ^ 1];
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int p = p_mine;
   double sc[1] = {0.0};
   if (p < V.P) {
-    const int col = V.pt_col[p];
+    const int col = col_mine;
     double X[3] = {pts[4 * (size_t)p], pts[4 * (size_t)p + 1], pts[4 * (size_t)p + 2]};
     if (col >= 0) {
       double r[3] = {bl[3 * (size_t)col], bl[3 * (size_t)col + 1], bl[3 * (size_t)col + 2]};
       const double b0 = r[0], b1 = r[1], b2 = r[2];
-      for (int o = V.pt_start[p]; o < V.pt_start[p + 1]; ++o) {
+      for (int o = ps0; o < ps1; ++o) {
         if (V.cam_col[V.pm_cam[o]] < 0) continue;
         r[0] -= tmp3[3 * (size_t)o]; r[1] -= tmp3[3 * (size_t)o + 1]; r[2] -= tmp3[3 * (size_t)o + 2];
       }
