@@ -16,6 +16,7 @@ constexpr int kCamChunk = 256;    // observations of one camera handled by one C
 constexpr int kCamThreads = 256;
 constexpr int kCamVals = 28;      // 21 Hpp upper + 6 bp + 1 cost
 constexpr int kUnitItems = 256;   // Schur items per warp work unit
+constexpr int kUnitItemsSmall = 64;    // ... when it is a local window
 constexpr int kUnitItemsLarge = 352;   // ... when the problem is large enough to keep every warp busy with those
 constexpr int kPointLanes = 4;    // lanes cooperating on one point in the point role
 
@@ -1205,8 +1206,9 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
     if (col >= 0) {
       double r[3] = {bl[3 * (size_t)col], bl[3 * (size_t)col + 1], bl[3 * (size_t)col + 2]};
       const double b0 = r[0], b1 = r[1], b2 = r[2];
+      // (rows of observations by fixed cameras are never written by ba_backsub_cam and were zeroed at build time:
+      // subtracting them is exact, and the loop has no dependent index loads in front of its data loads)
       for (int o = ps0; o < ps1; ++o) {
-        if (V.cam_col[V.pm_cam[o]] < 0) continue;
         r[0] -= tmp3[3 * (size_t)o]; r[1] -= tmp3[3 * (size_t)o + 1]; r[2] -= tmp3[3 * (size_t)o + 2];
       }
       double h[6], hi[6], d[3];   // (Hll + lambda I)^-1 on the fly: the inverses are not kept in HBM
