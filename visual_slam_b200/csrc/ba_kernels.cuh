@@ -392,19 +392,21 @@ __device__ __forceinline__ void trial_controller(const BAView& V, const LinArgs&
                                                  double* red /*[2 * kLinWarps]*/) {
   LMState* st = A.st_rw;
   const TrialArgs& T = A.trial;
-  if (A.has_scale) {   // cost of the scale edges at the trial state (EdgeSBAScale + DCS)
-    scale_edges_body<kLinThreads>(SV, true, red);
-    __syncthreads();
-  }
+  // every load that does not depend on the scale edges is issued first, so that its L2 round trip runs under theirs
   const double lambda = st->lambda;
   double v[2] = {0.0, 0.0};
   for (int i = threadIdx.x; i < V.C; i += kLinThreads) v[0] += __ldcg(A.cam_cost + i);
   for (int i = threadIdx.x; i < T.n; i += kLinThreads) v[1] += T.dp[i] * (lambda * T.dp[i] + (T.bp[i] + T.bp_extra[i]));
   for (int i = threadIdx.x; i < T.n_sp; i += kLinThreads) v[1] += T.scale_partial[i];
+  int status = 0, its = 0;
+  if (threadIdx.x == 0 && T.n) { status = __ldcg(T.pcg_status); its = __ldcg(T.pcg_iters); }
+  if (A.has_scale) {   // cost of the scale edges at the trial state (EdgeSBAScale + DCS)
+    scale_edges_body<kLinThreads>(SV, true, red);
+    __syncthreads();
+  }
   block_reduce<2, kLinThreads>(v, red);
   if (threadIdx.x != 0) return;
   double tmp = v[0] + (A.has_scale ? *A.scale_cost : 0.0);
-  const int status = T.n ? *T.pcg_status : 0, its = T.n ? *T.pcg_iters : 0;
   st->last_cost = tmp; st->last_scale = v[1]; st->last_pcg_status = status; st->last_pcg_iters = its;
   if (st->manual) return;
   const bool ok = status != 1;
@@ -612,10 +614,20 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
     __syncthreads();
     if (s_flag) {
       fence_acq_rel_gpu();
-      if (tid < kCamVals) {
+      // the camera's chunk partials are summed by all four warps (warp g takes chunks g, g + 4, ...; the four sums
+      // are added in warp order): a camera of a local window has ~24 chunks, and one thread per column walking them
+      // one after the other was six dependent L2 round trips on the critical path of every linearisation / trial cost
+      {
         double s = 0.0;
-        const double* base = A.camp + (size_t)first_row * kCamVals + tid;
-        for (int k = 0; k < n_chunks; ++k) s += __ldcg(base + (size_t)k * kCamVals);
+        if (lane < kCamVals) {
+          const double* base = A.camp + (size_t)first_row * kCamVals + lane;
+          for (int k = wid; k < n_chunks; k += kLinWarps) s += __ldcg(base + (size_t)k * kCamVals);
+        }
+        red[wid * 32 + lane] = s;
+      }
+      __syncthreads();
+      if (tid < kCamVals) {
+        const double s = (red[tid] + red[32 + tid]) + (red[64 + tid] + red[96 + tid]);
         if (tid == 27) A.cam_cost[c] = s;
         if (!COST_ONLY && col >= 0 && tid < 27) {
           if (tid >= 21) {
@@ -1109,7 +1121,14 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
   double v = ex >= 0 ? extra[(size_t)ex * 36 + e] : 0.0;
   if (a == b) v += Hpp[36 * a + e] + (r == c ? lambda : 0.0);
   double s = 0.0;
-  for (int u = u0; u < u1; ++u) s += partial[(size_t)u * 36 + e];
+  for (int u = u0; u < u1; u += 8) {   // eight loads in flight, added in unit order
+    double w[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) w[q] = (u + q < u1) ? __ldcg(partial + (size_t)(u + q) * 36 + e) : 0.0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      if (u + q < u1) s += w[q];
+  }
   v -= s;
   S[(size_t)(6 * a + r) * n + 6 * b + c] = v;
   if (a != b) S[(size_t)(6 * b + c) * n + 6 * a + r] = v;
