@@ -544,8 +544,8 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.Hll.alloc((size_t)Pf * 6)); BA_TRY(B.bl.alloc((size_t)Pf * 3)); BA_TRY(B.Hinv.alloc((size_t)Pf * 6)); BA_TRY(B.Wfac.alloc((size_t)Pf * 6));
   BA_TRY(B.camp.alloc(std::max((size_t)C * B.max_chunks, (size_t)B.lin_nA) * kCamVals)); BA_TRY(B.cam_cost.alloc(C));
   BA_TRY(B.S.alloc((size_t)B.n * B.n)); BA_TRY(B.dp.alloc(B.n)); BA_TRY(B.dl.alloc((size_t)Pf * 3));
-  BA_TRY(B.tmp3.alloc((size_t)N * 3));
-  BA_TRY(cudaMemset(B.tmp3.p, 0, std::max<size_t>((size_t)N * 3, 1) * sizeof(double)));   // rows of fixed cameras / points stay 0
+  BA_TRY(B.tmp3.alloc((size_t)N * 4));   // [N][4]: one 32-byte sector per observation
+  BA_TRY(cudaMemset(B.tmp3.p, 0, std::max<size_t>((size_t)N * 4, 1) * sizeof(double)));   // rows of fixed cameras / points stay 0
   BA_TRY(B.unit_partial.alloc((size_t)B.n_units * 36));
   BA_TRY(B.extra.alloc((size_t)std::max(n_extra, 1) * 36)); BA_TRY(B.bp_extra.alloc(std::max(B.n, 1))); BA_TRY(B.extra_diag.alloc(std::max(3 * Cf, 1)));
   BA_TRY(B.scale_cost.alloc(1)); BA_TRY(B.scale_partial.alloc(B.n_sp)); BA_TRY(B.res.alloc(8));

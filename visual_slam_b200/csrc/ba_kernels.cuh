@@ -803,6 +803,7 @@ __global__ void __launch_bounds__(kCamThreads)
 ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict__ Wf,
              const double* __restrict__ bl, double* __restrict__ Gout, double* __restrict__ camp) {
   __shared__ double red[(kCamThreads / 32) * 6];
+  __shared__ __align__(128) double stage_all[(kCamThreads / 32) * 32 * 18];   // a warp's 32 blocks (4608 B)
   static_assert(kCamChunk == kCamThreads, "one observation per thread and chunk");
   // static structure before the wait (see ba_schur_finalize): chunk bounds and this thread's point column
   const int c = blockIdx.y, chunk = blockIdx.x;
@@ -815,16 +816,31 @@ ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict_
   pdl_trigger();
   if (V.st->done) return;
   if (start >= end || ccol < 0) return;
+  // The warp's 32 blocks are contiguous in HBM (camera-major).  A lane reading ITS block straight from global
+  // memory makes every 128-bit load of the warp touch 32 different lines (144-byte stride); instead the warp copies
+  // the 4608 bytes with consecutive lanes on consecutive 16-byte pieces (cp.async) into its slice of shared memory,
+  // every lane works on its block there (144-byte stride: conflict-free 128-bit accesses), G goes back into the
+  // same slice and leaves by ONE bulk async store.
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  double* stage = stage_all + wid * (32 * 18);
+  const int base = start + wid * 32;                     // first observation of this warp
+  const int n_blk = max(0, min(32, end - base));
+  for (int i = lane; i < n_blk * 9; i += 32) cp_async16(stage + 2 * i, Hpl + (size_t)base * 18 + 2 * i);
+  cp_async_commit();
   double acc[6] = {0, 0, 0, 0, 0, 0};
-  for (int o = o_mine; o < end; o += kCamThreads) {
-    const int pcol = pcol_mine;
-    if (pcol < 0) continue;
-    double h[18], w[6], b[3], g[18];
-    load18(Hpl + (size_t)o * 18, h);
+  double w[6], b[3];
+  const int pcol = pcol_mine;
+  if (pcol >= 0) {                                       // (the gathers run under the copy)
 #pragma unroll
     for (int j = 0; j < 6; ++j) w[j] = Wf[6 * (size_t)pcol + j];
 #pragma unroll
     for (int j = 0; j < 3; ++j) b[j] = bl[3 * (size_t)pcol + j];
+  }
+  cp_async_wait<0>();
+  __syncwarp();
+  if (pcol >= 0) {
+    double h[18], g[18];
+    load18(stage + lane * 18, h);
     // y = W^T bl  (W upper: 00 01 02 11 12 22)
     const double y0 = w[0] * b[0];
     const double y1 = w[1] * b[0] + w[3] * b[1];
@@ -837,14 +853,18 @@ ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict_
       g[3 * r + 2] = h0 * w[2] + h1 * w[4] + h2 * w[5];
       acc[r] += g[3 * r] * y0 + g[3 * r + 1] * y1 + g[3 * r + 2] * y2;
     }
-    store18(Gout + (size_t)o * 18, g);
+    store18(stage + lane * 18, g);                       // (rows of fixed points keep the copied block: never read)
   }
+  fence_async_smem();
+  __syncwarp();
+  if (lane == 0 && n_blk > 0) bulk_s2g(Gout + (size_t)base * 18, stage, (uint32_t)n_blk * 144u);
   block_reduce<6, kCamThreads>(acc, red);
   if (threadIdx.x == 0) {
     double* dst = camp + ((size_t)c * V.max_chunks + chunk) * kCamVals;
 #pragma unroll
     for (int i = 0; i < 6; ++i) dst[i] = acc[i];
   }
+  if (lane == 0) bulk_wait_read0();                      // the store has left the slice before the CTA retires
 }
 
 // Schur work units: one warp reduces <= kUnitItems products G_a * G_b^T of one (cam a, cam b) key,
@@ -1145,24 +1165,35 @@ ba_backsub_cam(BAView V, const double* __restrict__ Hpl, const double* __restric
   const int o_mine = start + threadIdx.x;
   const int pcol_mine = o_mine < end ? __ldg(V.pt_col + __ldg(V.cm_pt + o_mine)) : -1;
   const int pm_mine = o_mine < end ? __ldg(V.cm_pm + o_mine) : 0;
+  __shared__ __align__(128) double stage_all[(kCamThreads / 32) * 32 * 18];   // see ba_compute_G
   pdl_wait();
   pdl_trigger();
   if (V.st->done || start >= end || col < 0) return;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  double* stage = stage_all + wid * (32 * 18);
+  {
+    const int base = start + wid * 32;
+    const int n_blk = max(0, min(32, end - base));
+    for (int i = lane; i < n_blk * 9; i += 32) cp_async16(stage + 2 * i, Hpl + (size_t)base * 18 + 2 * i);
+    cp_async_commit();
+  }
   double d[6];
 #pragma unroll
   for (int i = 0; i < 6; ++i) d[i] = dp[6 * col + i];
+  cp_async_wait<0>();
+  __syncwarp();
   for (int o = o_mine; o < end; o += kCamThreads) {
     if (pcol_mine < 0) continue;
     double h[18];
-    load18(Hpl + (size_t)o * 18, h);
+    load18(stage + lane * 18, h);
     double v[3] = {0, 0, 0};
 #pragma unroll
     for (int r = 0; r < 6; ++r) {
 #pragma unroll
       for (int j = 0; j < 3; ++j) v[j] += h[3 * r + j] * d[r];
     }
-    double* dst = tmp3 + (size_t)pm_mine * 3;
-    dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2];
+    // rows padded to one 32-byte sector: the scattered store covers the whole sector (no partial-sector fill)
+    *reinterpret_cast<double4*>(tmp3 + (size_t)pm_mine * 4) = make_double4(v[0], v[1], v[2], 0.0);
   }
 }
 
@@ -1228,7 +1259,8 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
       // (rows of observations by fixed cameras are never written by ba_backsub_cam and were zeroed at build time:
       // subtracting them is exact, and the loop has no dependent index loads in front of its data loads)
       for (int o = ps0; o < ps1; ++o) {
-        r[0] -= tmp3[3 * (size_t)o]; r[1] -= tmp3[3 * (size_t)o + 1]; r[2] -= tmp3[3 * (size_t)o + 2];
+        const double4 t = *reinterpret_cast<const double4*>(tmp3 + 4 * (size_t)o);
+        r[0] -= t.x; r[1] -= t.y; r[2] -= t.z;
       }
       double h[6], hi[6], d[3];   // (Hll + lambda I)^-1 on the fly: the inverses are not kept in HBM
 #pragma unroll
