@@ -297,6 +297,32 @@ def ba_figures(torch):
                      "linearize_bytes": p.linearize_bytes(),
                      "linearize_gbs": p.linearize_bytes() / (lin * 1e-3) / 1e9,
                      "linear_solver": "block-Jacobi PCG to 1e-10 (north_star; the default)"}
+        if name == "c4":
+            # the same kernel INSIDE the LM loop (its inputs were just written by the previous kernels of the step):
+            # CUPTI activity records of one optimize(10), collected through torch.profiler; reported beside the
+            # stand-alone figure, which stays the one the roofline fraction is quoted on
+            try:
+                from torch.profiler import ProfilerActivity, profile
+                eng.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
+                torch.cuda.synchronize()
+                with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                    eng.optimize(10)
+                    torch.cuda.synchronize()
+                per = {}
+                for e in prof.events():
+                    if e.device_type == torch.autograd.DeviceType.CUDA:
+                        per.setdefault(e.name.split("(")[0].replace("void ", "").replace("vslam::", ""), []).append(
+                            (e.time_range.end - e.time_range.start) * 1e-3)
+                lin_in = per.get("ba_linearize_kernel<false>", [])
+                out[name]["in_situ"] = {
+                    "linearize_ms": float(np.mean(lin_in)) if lin_in else None,
+                    "linearize_gbs": p.linearize_bytes() / (float(np.mean(lin_in)) * 1e-3) / 1e9 if lin_in else None,
+                    "kernel_ms_per_lm_slot": {k: float(np.sum(v)) / 10.0 for k, v in sorted(per.items())
+                                              if k.startswith("ba_") and np.sum(v) > 0.01},
+                    "source": "torch.profiler (CUPTI kernel records) over one optimize(10); a number taken under a "
+                              "profiler: informative only"}
+            except Exception as exc:   # profiler unavailable: the stand-alone figures above stand
+                out[name]["in_situ"] = {"error": repr(exc)}
         if name == "c3":   # the same window with the in-CTA direct solver (what g2o's CHOLMOD path does for n = 54)
             eng.set_linear_solver("direct")
             b2 = None
@@ -955,7 +981,8 @@ def run_gpu(args):
                                              "events on the launching stream (working set 194 MB > L2); one "
                                              "launch bracketed alone after an L2 flush: %.4f ms"
                                              % ba["c4"]["linearize_single_cold_launch_ms"],
-                                   "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)"}
+                                   "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
+                                   "in_situ": ba["c4"].get("in_situ")}
     if features:
         line["features"] = features
     print(json.dumps(line))
