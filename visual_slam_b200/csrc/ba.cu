@@ -549,7 +549,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(B.unit_partial.alloc((size_t)B.n_units * 36));
   BA_TRY(B.extra.alloc((size_t)std::max(n_extra, 1) * 36)); BA_TRY(B.bp_extra.alloc(std::max(B.n, 1))); BA_TRY(B.extra_diag.alloc(std::max(3 * Cf, 1)));
   BA_TRY(B.scale_cost.alloc(1)); BA_TRY(B.scale_partial.alloc(B.n_sp)); BA_TRY(B.res.alloc(8));
-  BA_TRY(B.p_glob.alloc(std::max(B.n, 1))); BA_TRY(B.w_loc.alloc(std::max(B.n, 1)));
+  BA_TRY(B.p_glob.alloc(2 * (size_t)std::max(B.n, 1))); BA_TRY(B.w_loc.alloc(std::max(B.n, 1)));   // (two exchange buffers)
   BA_TRY(cudaMemset(B.Hll.p, 0, std::max<size_t>((size_t)Pf * 6, 1) * sizeof(double)));   // free points without
   BA_TRY(cudaMemset(B.bl.p, 0, std::max<size_t>((size_t)Pf * 3, 1) * sizeof(double)));    // observations stay 0
   BA_TRY(cudaMemset(B.S.p, 0, std::max<size_t>((size_t)B.n * B.n, 1) * sizeof(double)));
@@ -571,7 +571,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     const size_t budget = (size_t)std::max(max_smem - 2048, 16384);
     auto smem_for = [&](int rows, bool slab) {
-      return sizeof(double) * ((size_t)B.n + 6 * (size_t)rows + 6 * (size_t)rows + 8 +
+      return sizeof(double) * ((size_t)B.n + 10 * (size_t)rows + 6 * (size_t)rows + 8 +
                                (slab ? (size_t)rows * B.n : 0));
     };
     int bpc = std::max(1, (nb + sms - 1) / sms);  // blocks per CTA with one CTA per SM
@@ -589,7 +589,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)direct_smem(kDirectMax)));
   }
-  BA_TRY(B.part.alloc((size_t)4 * B.pcg_G)); BA_TRY(B.bar.alloc(1)); BA_TRY(B.pcg_flags.alloc(4));
+  BA_TRY(B.part.alloc((size_t)6 * B.pcg_G)); BA_TRY(B.bar.alloc(1)); BA_TRY(B.pcg_flags.alloc(4));
   BA_TRY(cudaMemset(B.bar.p, 0, sizeof(unsigned))); BA_TRY(cudaMemset(B.pcg_flags.p, 0, 4 * sizeof(int)));
   B.pcg_max_iter = std::max(200, 20 * B.n);
   return VSLAM_OK;
@@ -693,6 +693,8 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
     A.slab_in_smem = B.pcg_slab; A.max_iter = B.pcg_max_iter; A.tol = B.pcg_tol;
     A.p_glob = B.p_glob.p; A.w_loc = B.w_loc.p; A.part = B.part.p; A.bar = B.bar.p; A.fail_flag = B.pcg_flags.p;
     A.status = B.pcg_flags.p + 1; A.iters = B.pcg_flags.p + 2;
+    static const bool pipelined = [] { const char* e = getenv("VSLAM_BA_PCG_PIPELINED"); return !(e && atoi(e) == 0); }();
+    A.pipelined = (pipelined && B.pcg_G > 1) ? 1 : 0;
     void* args[] = {&A};
     if (B.pcg_G > 1) {
       BA_TRY(cudaLaunchCooperativeKernel((void*)ba_pcg_kernel, dim3(B.pcg_G), dim3(kPcgThreads), args,

@@ -16,6 +16,7 @@ struct PcgArgs {
   const int* done;    // optional (&LMState::done): the solve is skipped when the LM loop has terminated
   const double* S; const double* b; double* x;
   int n, rows, G, slab_in_smem, max_iter;
+  int pipelined;      // G > 1: one grid barrier per iteration (pipelined PCG); p_glob holds 2 n, part 6 G doubles
   double tol;
   double* p_glob;     // [n]  published u = M^-1 r
   double* w_loc;      // [n]  rows of S u, each CTA touches only its own rows
@@ -169,6 +170,12 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
   double* minv = wl + A.rows;          // [rows/6][36]
   double* red = minv + 6 * A.rows;     // [8]
   double* slab = red + 8;              // [rows][n] when slab_in_smem
+  // pipelined variant only (G > 1; the launch adds 4 * rows doubles behind the slab): m = M^-1 w, z = S q and
+  // q = M^-1 s (recurrences), n = S m
+  double* ml = slab + (A.slab_in_smem ? (size_t)A.rows * n : 0);
+  double* zl = ml + A.rows;
+  double* ql = zl + A.rows;
+  double* nl = ql + A.rows;
   __shared__ int s_fail;
   __shared__ double s_sum[3];
   __shared__ double red3[3 * (kPcgThreads / 32)];
@@ -176,7 +183,18 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
 
   if (tid == 0) s_fail = 0;
   if (A.slab_in_smem) {
-    for (int i = tid; i < R * n; i += kPcgThreads) slab[i] = A.S[(size_t)row0 * n + i];
+    // the slab arrives by 16-byte asynchronous copies, all of a thread's pieces in flight at once (a load -> store
+    // loop keeps only a few requests per thread outstanding: ~15 us for the 172 KB of a C4 slab, per solve)
+    const double* src = A.S + (size_t)row0 * n;
+    const int cnt = R * n;
+    if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(slab)) & 15) == 0 && (cnt & 1) == 0) {
+      for (int i = tid; i < cnt / 2; i += kPcgThreads)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(slab + 2 * i)), "l"(src + 2 * i) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    } else {
+      for (int i = tid; i < cnt; i += kPcgThreads) slab[i] = src[i];
+    }
   }
   __syncthreads();
   const double* Srows = A.slab_in_smem ? slab : A.S + (size_t)row0 * n;
@@ -198,6 +216,167 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
   const int lane = tid & 31, wid = tid >> 5;
   int status = 2, it = 0;
   double gamma_old = 0.0, alpha_old = 0.0, thresh = 0.0;
+  // local block-Jacobi application y = M^-1 v and the local rows of S * (vector in u_full)
+  auto apply_minv = [&](const double* v, double* y) {
+    for (int i = tid; i < R; i += kPcgThreads) {
+      const int bi = i / 6, ii = i % 6;
+      double z = 0.0;
+      for (int j = 0; j < 6; ++j) z += minv[36 * bi + 6 * ii + j] * v[6 * bi + j];
+      y[i] = z;
+    }
+  };
+  // Local rows of S * (vector in u_full).  A warp takes up to four rows (wid, wid + 8, ...) TOGETHER, so that an
+  // element of the vector is read from shared memory once for all of them: the product moves 16 bytes of shared
+  // memory per FMA otherwise, and at 18 rows x 1194 columns per CTA that alone is 2700 cycles of the one
+  // shared-memory pipe (measured 2.8 us per product, a third of a PCG iteration at C4).
+  auto local_matvec = [&](double* y) {
+    for (int r0 = wid; r0 < R; r0 += 4 * (kPcgThreads / 32)) {
+      const double* row0p = Srows + (size_t)r0 * n;
+      const size_t rs = (size_t)(kPcgThreads / 32) * n;           // stride between the warp's rows
+      constexpr int W = kPcgThreads / 32;
+      const bool h1 = r0 + W < R, h2 = r0 + 2 * W < R, h3 = r0 + 3 * W < R;
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+      // n is a multiple of 6 and the slab starts on a 16-byte boundary: every row does, so a lane reads two
+      // neighbouring columns with one 128-bit load
+      const bool vec = ((reinterpret_cast<uintptr_t>(row0p) | reinterpret_cast<uintptr_t>(u_full)) & 15) == 0 && (n & 1) == 0;
+      if (vec) {
+        for (int j = 2 * lane; j < n; j += 64) {
+          const double2 u = *reinterpret_cast<const double2*>(u_full + j);
+          const double2 s0 = *reinterpret_cast<const double2*>(row0p + j);
+          a0 = fma(s0.x, u.x, a0); b0 = fma(s0.y, u.y, b0);
+          if (h1) { const double2 t = *reinterpret_cast<const double2*>(row0p + rs + j); a1 = fma(t.x, u.x, a1); b1 = fma(t.y, u.y, b1); }
+          if (h2) { const double2 t = *reinterpret_cast<const double2*>(row0p + 2 * rs + j); a2 = fma(t.x, u.x, a2); b2 = fma(t.y, u.y, b2); }
+          if (h3) { const double2 t = *reinterpret_cast<const double2*>(row0p + 3 * rs + j); a3 = fma(t.x, u.x, a3); b3 = fma(t.y, u.y, b3); }
+        }
+      } else {
+        int j = lane;
+        for (; j + 32 < n; j += 64) {
+          const double u0 = u_full[j], u1 = u_full[j + 32];
+          a0 = fma(row0p[j], u0, a0); b0 = fma(row0p[j + 32], u1, b0);
+          if (h1) { a1 = fma(row0p[rs + j], u0, a1); b1 = fma(row0p[rs + j + 32], u1, b1); }
+          if (h2) { a2 = fma(row0p[2 * rs + j], u0, a2); b2 = fma(row0p[2 * rs + j + 32], u1, b2); }
+          if (h3) { a3 = fma(row0p[3 * rs + j], u0, a3); b3 = fma(row0p[3 * rs + j + 32], u1, b3); }
+        }
+        for (; j < n; j += 32) {
+          const double u0 = u_full[j];
+          a0 = fma(row0p[j], u0, a0);
+          if (h1) a1 = fma(row0p[rs + j], u0, a1);
+          if (h2) a2 = fma(row0p[2 * rs + j], u0, a2);
+          if (h3) a3 = fma(row0p[3 * rs + j], u0, a3);
+        }
+      }
+      a0 = warp_sum(a0 + b0); a1 = warp_sum(a1 + b1); a2 = warp_sum(a2 + b2); a3 = warp_sum(a3 + b3);
+      if (lane == 0) {
+        y[r0] = a0;
+        if (h1) y[r0 + W] = a1;
+        if (h2) y[r0 + 2 * W] = a2;
+        if (h3) y[r0 + 3 * W] = a3;
+      }
+    }
+  };
+  if (G > 1 && A.pipelined) {
+    // ---- Pipelined PCG (Ghysels & Vanroose): the matrix-vector product of an iteration (n = S m, m = M^-1 w) does
+    // not depend on that iteration's dot products, so the slab of m and the partial sums travel through ONE grid
+    // barrier per iteration instead of two.  Same iterates as the two-barrier form in exact arithmetic (both are
+    // preconditioned CG), three more recurrences (z = S q, q = M^-1 s, w = S u).  Measured at C4 (67 CTAs, 18 rows
+    // of S each; %globaltimer stamps): an iteration is 0.9 us of local work before the barrier, 1.2 us barrier,
+    // 1.4 us gather + scalars, 1.6 us product = 5.3 us, against 7.8 us with two barriers, a single-row product
+    // (2.8 us: 16 bytes of shared memory per FMA) and three dependent partial-sum loads.
+    apply_minv(rl, ul);
+    // (the initial exchange uses buffer 1: iteration 0 publishes into buffer 0 while a slower CTA may still read this one)
+    for (int i = tid; i < R; i += kPcgThreads) { A.p_glob[n + row0 + i] = ul[i]; zl[i] = 0.0; ql[i] = 0.0; }
+    grid_barrier(A.bar, target, G);
+    if (__ldcg(A.fail_flag)) {
+      status = 1;
+    } else {
+      for (int i = tid; i < n; i += kPcgThreads) u_full[i] = __ldcg(A.p_glob + n + i);
+      __syncthreads();
+      local_matvec(wl);                                  // w = S u
+      __syncthreads();
+      for (it = 0; it <= A.max_iter; ++it) {
+        apply_minv(wl, ml);                              // m = M^-1 w
+        double gam_p = 0.0, del_p = 0.0, rr_p = 0.0;
+        for (int i = tid; i < R; i += kPcgThreads) {
+          gam_p += rl[i] * ul[i];
+          del_p += wl[i] * ul[i];
+          rr_p += rl[i] * rl[i];
+        }
+        block_sum3(gam_p, del_p, rr_p, red3);            // (also orders ml before its publication below)
+        // the exchange buffers alternate with the iteration's parity: a CTA that has left the barrier may publish
+        // the NEXT iteration's values while a slower one still reads this iteration's
+        double* xch = A.p_glob + (size_t)(it & 1) * n;
+        double* pch = A.part + (size_t)(it & 1) * 3 * G;
+        for (int i = tid; i < R; i += kPcgThreads) xch[row0 + i] = ml[i];
+        if (tid == 0) { pch[g] = gam_p; pch[G + g] = del_p; pch[2 * G + g] = rr_p; }
+        grid_barrier(A.bar, target, G);
+        for (int i = tid; i < n; i += kPcgThreads) u_full[i] = __ldcg(xch + i);
+        double sums[3];
+        if (tid < 32) {                                    // all nine loads of a lane in flight, then the three sums
+          double v[3][3];
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              const int gg = tid + 32 * q;
+              v[k][q] = gg < G ? __ldcg(pch + k * G + gg) : 0.0;
+            }
+          }
+          if (G <= 96) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+              double sk = 0.0;
+#pragma unroll
+              for (int q = 0; q < 3; ++q)
+                if (tid + 32 * q < G) sk += v[k][q];
+              sk = warp_sum(sk);
+              if (tid == 0) s_sum[k] = sk;
+            }
+          } else {                                         // (more CTAs than three per lane: the general form)
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+              double sk = 0.0;
+              for (int gg = tid; gg < G; gg += 32) sk += __ldcg(pch + k * G + gg);
+              sk = warp_sum(sk);
+              if (tid == 0) s_sum[k] = sk;
+            }
+          }
+        }
+        __syncthreads();                                   // (u_full is complete after it, too)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) sums[k] = s_sum[k];
+        __syncthreads();
+        const double gamma = sums[0], delta = sums[1], rr = sums[2];
+        if (it == 0) {
+          if (!(rr > 0.0)) { status = 0; break; }        // b == 0: x = 0
+          thresh = A.tol * A.tol * rr;
+        }
+        if (rr <= thresh && it > 0) { status = 0; break; }
+        if (it == A.max_iter) break;
+        double beta = 0.0, pap = delta;
+        if (it > 0) {
+          beta = gamma / gamma_old;
+          pap = delta - beta * gamma / alpha_old;
+        }
+        if (!(pap > 0.0) || !isfinite(pap) || !(gamma > 0.0)) { status = 1; break; }
+        const double alpha = gamma / pap;
+        local_matvec(nl);                                // n = S m (u_full holds m)
+        __syncthreads();
+        for (int i = tid; i < R; i += kPcgThreads) {
+          const double z = nl[i] + beta * zl[i];
+          const double q = ml[i] + beta * ql[i];
+          const double sv = wl[i] + beta * sl[i];
+          const double pv = ul[i] + beta * pl[i];
+          zl[i] = z; ql[i] = q; sl[i] = sv; pl[i] = pv;
+          xl[i] += alpha * pv;
+          rl[i] -= alpha * sv;
+          ul[i] -= alpha * q;
+          wl[i] -= alpha * z;
+        }
+        __syncthreads();
+        gamma_old = gamma; alpha_old = alpha;
+      }
+    }
+  } else
   for (it = 0; it <= A.max_iter; ++it) {
     // u = M^-1 r (block local), published for the other CTAs
     for (int i = tid; i < R; i += kPcgThreads) {
@@ -217,9 +396,14 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
     double gam_p = 0.0, del_p = 0.0, rr_p = 0.0;
     for (int r = wid; r < R; r += kPcgThreads / 32) {
       const double* row = Srows + (size_t)r * n;
-      double s = 0.0;
-      for (int j = lane; j < n; j += 32) s += row[j] * u_full[j];
-      s = warp_sum(s);
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;   // (see local_matvec)
+      int j = lane;
+      for (; j + 96 < n; j += 128) {
+        a0 = fma(row[j], u_full[j], a0); a1 = fma(row[j + 32], u_full[j + 32], a1);
+        a2 = fma(row[j + 64], u_full[j + 64], a2); a3 = fma(row[j + 96], u_full[j + 96], a3);
+      }
+      for (; j < n; j += 32) a0 = fma(row[j], u_full[j], a0);
+      const double s = warp_sum((a0 + a1) + (a2 + a3));
       if (lane == 0) wl[r] = s;
     }
     __syncthreads();
