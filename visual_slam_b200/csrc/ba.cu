@@ -315,8 +315,13 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
       seg_a.push_back(a); seg_b.push_back(b);
       seg_unit_start.push_back((int)unit_start.size());
       for (long long s = cnt[key]; s < cnt[key + 1]; s += unit_items) {
+        const int len = (int)std::min<long long>(unit_items, cnt[key + 1] - s);
+        // bit 30: every item of the unit pairs an observation with itself (a diagonal block without duplicate
+        // observations): the kernel then fetches each block once
+        bool self = a == b;
+        for (long long i = s; self && i < s + len; ++i) self = item_a[i] == item_b[i];
         unit_start.push_back((int)s);
-        unit_len.push_back((int)std::min<long long>(unit_items, cnt[key + 1] - s));
+        unit_len.push_back(len | (self ? (1 << 30) : 0));
       }
     }
   seg_unit_start.push_back((int)unit_start.size());

@@ -888,7 +888,9 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
   const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int u = blockIdx.x * kSchurWarps + wid;
   // (static work lists: the unit's bounds are fetched before the wait, see ba_schur_finalize)
-  const int s0 = u < n_units ? __ldg(unit_start + u) : 0, len = u < n_units ? __ldg(unit_len + u) : 0;
+  const int s0 = u < n_units ? __ldg(unit_start + u) : 0, len_raw = u < n_units ? __ldg(unit_len + u) : 0;
+  const int len = len_raw & 0x3fffffff;
+  const bool diag = (len_raw >> 30) & 1;   // self-paired items (set by the host): each block is fetched once
   pdl_wait();
   pdl_trigger();
   if (st->done || u >= n_units) return;
@@ -904,6 +906,7 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
       double* stg = ring + (it % kSchurStages) * kSchurStageDoubles;
 #pragma unroll
       for (int j = 0; j < 18; ++j) {
+        if (j >= 9 && diag) break;
         const int q = j * 32 + lane;                 // 16-byte piece of the stage
         const int b = (q * 7282) >> 16;              // q / 9: block 0..63 (A blocks, then B blocks)
         const int r = q - 9 * b;
@@ -935,7 +938,7 @@ ba_schur_units(const LMState* __restrict__ st, const double* __restrict__ G,
     if (i < len) {
       double ga[18], gb[18];
       load18(stg + lane * 18, ga);
-      load18(stg + 32 * 18 + lane * 18, gb);
+      load18(stg + (diag ? 0 : 32 * 18) + lane * 18, gb);
 #pragma unroll
       for (int r = 0; r < 6; ++r) {
 #pragma unroll
