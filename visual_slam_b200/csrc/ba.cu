@@ -163,7 +163,8 @@ struct BA {
     A.Hll = Hll.p; A.bl = bl.p; A.pt_maxd = pt_maxd.p;
     A.extra_diag = extra_diag.p; A.scale_cost = scale_cost.p;
     A.st_rw = lm.p; A.trace = trace.p; A.force = 0;
-    A.trial.n_sp = P ? n_sp : 0; A.trial.n = n; A.trial.scale_partial = scale_partial.p; A.trial.dp = dp.p;
+    A.trial.n_sp = (P ? n_sp : 0) + (C + 255) / 256;   // point blocks + camera blocks of ba_backsub_pt
+    A.trial.n = n; A.trial.scale_partial = scale_partial.p; A.trial.dp = dp.p;
     A.trial.bp = bp.p; A.trial.bp_extra = bp_extra.p; A.trial.pcg_status = pcg_flags.p + 1;
     A.trial.pcg_iters = pcg_flags.p + 2;
     return A;
@@ -553,7 +554,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
   BA_TRY(cudaMemset(B.tmp3.p, 0, std::max<size_t>((size_t)N * 4, 1) * sizeof(double)));   // rows of fixed cameras / points stay 0
   BA_TRY(B.unit_partial.alloc((size_t)B.n_units * 36));
   BA_TRY(B.extra.alloc((size_t)std::max(n_extra, 1) * 36)); BA_TRY(B.bp_extra.alloc(std::max(B.n, 1))); BA_TRY(B.extra_diag.alloc(std::max(3 * Cf, 1)));
-  BA_TRY(B.scale_cost.alloc(1)); BA_TRY(B.scale_partial.alloc(B.n_sp)); BA_TRY(B.res.alloc(8));
+  BA_TRY(B.scale_cost.alloc(1)); BA_TRY(B.scale_partial.alloc((size_t)B.n_sp + (C + 255) / 256)); BA_TRY(B.res.alloc(8));
   BA_TRY(B.p_glob.alloc(2 * (size_t)std::max(B.n, 1))); BA_TRY(B.w_loc.alloc(std::max(B.n, 1)));   // (two exchange buffers)
   BA_TRY(cudaMemset(B.Hll.p, 0, std::max<size_t>((size_t)Pf * 6, 1) * sizeof(double)));   // free points without
   BA_TRY(cudaMemset(B.bl.p, 0, std::max<size_t>((size_t)Pf * 3, 1) * sizeof(double)));    // observations stay 0
@@ -714,7 +715,7 @@ static int enqueue_trial(BA& B, cudaStream_t st) {
   {
     const int n_pt_blocks = B.P ? B.n_sp : 0;
     launch_step_kernel(ba_backsub_pt, n_pt_blocks + (B.C + 255) / 256, 256, 0, st, V, B.tmp3.p, B.Hll.p, B.bl.p,
-                       B.dl.p, B.scale_partial.p, B.dp.p, n_pt_blocks);
+                       B.dl.p, B.scale_partial.p, B.dp.p, n_pt_blocks, B.bp.p, B.bp_extra.p);
   }
   // trial cost; its last CTA is the LM controller (accept / reject / terminate)
   launch_step_kernel(ba_linearize_kernel<true>, B.lin_nA, kLinThreads, kLinCostSmem, st, V, B.lin_args(), B.scale_view());

@@ -396,8 +396,7 @@ __device__ __forceinline__ void trial_controller(const BAView& V, const LinArgs&
   const double lambda = st->lambda;
   double v[2] = {0.0, 0.0};
   for (int i = threadIdx.x; i < V.C; i += kLinThreads) v[0] += __ldcg(A.cam_cost + i);
-  for (int i = threadIdx.x; i < T.n; i += kLinThreads) v[1] += T.dp[i] * (lambda * T.dp[i] + (T.bp[i] + T.bp_extra[i]));
-  for (int i = threadIdx.x; i < T.n_sp; i += kLinThreads) v[1] += T.scale_partial[i];
+  for (int i = threadIdx.x; i < T.n_sp; i += kLinThreads) v[1] += __ldcg(T.scale_partial + i);   // points, then cameras
   int status = 0, its = 0;
   if (threadIdx.x == 0 && T.n) { status = __ldcg(T.pcg_status); its = __ldcg(T.pcg_iters); }
   if (A.has_scale) {   // cost of the scale edges at the trial state (EdgeSBAScale + DCS)
@@ -1234,7 +1233,8 @@ __device__ __forceinline__ void update_cams_body(const BAView& V, const double* 
 __global__ void __launch_bounds__(256)
 ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restrict__ Hll,
               const double* __restrict__ bl, double* __restrict__ dl_out,
-              double* __restrict__ scale_partial, const double* __restrict__ dp, int n_pt_blocks) {
+              double* __restrict__ scale_partial, const double* __restrict__ dp, int n_pt_blocks,
+              const double* __restrict__ bp, const double* __restrict__ bp_extra) {
   __shared__ double red[8];
   // static structure before the wait (see ba_schur_finalize)
   const int p_mine = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1245,7 +1245,22 @@ ba_backsub_pt(BAView V, const double* __restrict__ tmp3, const double* __restric
   pdl_trigger();
   if (V.st->done) return;
   if ((int)blockIdx.x >= n_pt_blocks) {   // the blocks behind the points update the cameras (SBACam::update)
-    update_cams_body(V, dp, ((int)blockIdx.x - n_pt_blocks) * 256 + (int)threadIdx.x);
+    const int c = ((int)blockIdx.x - n_pt_blocks) * 256 + (int)threadIdx.x;
+    update_cams_body(V, dp, c);
+    // ... and leave the camera part of computeScale, sum dp (lambda dp + bp + bp_extra), as this block's partial: the
+    // controller reads partials only (the speculative linearisation that ends a trial overwrites bp before it runs)
+    double sc[1] = {0.0};
+    const int col = c < V.C ? V.cam_col[c] : -1;
+    if (col >= 0) {
+      const double lambda = V.st->lambda;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+        const double d = dp[6 * col + i];
+        sc[0] += d * (lambda * d + (bp[6 * col + i] + bp_extra[6 * col + i]));
+      }
+    }
+    block_reduce<1, 256>(sc, red);
+    if (threadIdx.x == 0) scale_partial[blockIdx.x] = sc[0];
     return;
   }
   const double lambda = V.st->lambda;
