@@ -98,8 +98,9 @@ struct ScaleView {
 };
 
 template <int THREADS>
-__device__ __forceinline__ void scale_edges_body(const ScaleView& V, bool cost_only, double* red /*[THREADS/32]*/) {
-  const double* __restrict__ cams = V.cams2[cost_only ? (V.st->cur ^ 1) : V.st->cur];
+__device__ __forceinline__ void scale_edges_body(const ScaleView& V, bool cost_only, double* red /*[THREADS/32]*/,
+                                                 bool trial_state = false) {
+  const double* __restrict__ cams = V.cams2[(cost_only || trial_state) ? (V.st->cur ^ 1) : V.st->cur];
   double c[1] = {0.0};
   for (int k = threadIdx.x; k < V.E; k += THREADS) {
     const double* ta = cams + 7 * V.sa[k] + 4;
@@ -223,6 +224,7 @@ struct LinArgs {
   LMState* st_rw;
   long long* trace;                 // optional [n_ctas][2] globaltimer stamps (profiling), else null
   int force;                        // profiling: rebuild even when the system is not dirty
+  int spec;                         // speculative: build the system of the TRIAL state and let the LM controller decide
 };
 
 __device__ __forceinline__ long long globaltimer_ns();
@@ -385,33 +387,18 @@ __device__ __forceinline__ void lin_controller(const BAView& V, const LinArgs& A
   }
 }
 
-// Controller after a trial (last CTA of the cost-only launch): cost of the trial state, computeScale,
-// then the Levenberg-Marquardt accept / reject logic of g2o (OptimizationAlgorithmLevenberg::solve)
-// entirely on the device.
-__device__ __forceinline__ void trial_controller(const BAView& V, const LinArgs& A, const ScaleView& SV,
-                                                 double* red /*[2 * kLinWarps]*/) {
-  LMState* st = A.st_rw;
-  const TrialArgs& T = A.trial;
-  // every load that does not depend on the scale edges is issued first, so that its L2 round trip runs under theirs
+// The Levenberg-Marquardt accept / reject logic of g2o (OptimizationAlgorithmLevenberg::solve), one thread.  tmp = cost
+// of the trial state, scale_sum = sum dx (lambda dx + b).  system_of_trial: the system in memory was built at the trial
+// state (speculative linearisation), max_diag is its largest diagonal entry.
+__device__ __forceinline__ void lm_decide(LMState* st, double tmp, double scale_sum, int status, int its,
+                                          bool system_of_trial, double max_diag) {
   const double lambda = st->lambda;
-  double v[2] = {0.0, 0.0};
-  for (int i = threadIdx.x; i < V.C; i += kLinThreads) v[0] += __ldcg(A.cam_cost + i);
-  for (int i = threadIdx.x; i < T.n_sp; i += kLinThreads) v[1] += __ldcg(T.scale_partial + i);   // points, then cameras
-  int status = 0, its = 0;
-  if (threadIdx.x == 0 && T.n) { status = __ldcg(T.pcg_status); its = __ldcg(T.pcg_iters); }
-  if (A.has_scale) {   // cost of the scale edges at the trial state (EdgeSBAScale + DCS)
-    scale_edges_body<kLinThreads>(SV, true, red);
-    __syncthreads();
-  }
-  block_reduce<2, kLinThreads>(v, red);
-  if (threadIdx.x != 0) return;
-  double tmp = v[0] + (A.has_scale ? *A.scale_cost : 0.0);
-  st->last_cost = tmp; st->last_scale = v[1]; st->last_pcg_status = status; st->last_pcg_iters = its;
+  st->last_cost = tmp; st->last_scale = scale_sum; st->last_pcg_status = status; st->last_pcg_iters = its;
   if (st->manual) return;
   const bool ok = status != 1;
   st->pcg_total += (double)its;
   if (!ok) { tmp = 1.7976931348623157e308; st->breakdowns += 1.0; }
-  const double scale = v[1] + 1e-3;
+  const double scale = scale_sum + 1e-3;
   const double rho = (st->cur_cost - tmp) / scale;
   st->last_rho = rho;
   st->trials += 1;
@@ -423,11 +410,13 @@ __device__ __forceinline__ void trial_controller(const BAView& V, const LinArgs&
     st->ni = 2.0;
     st->cur_cost = tmp;
     st->cur ^= 1;          // discardTop(): the trial state becomes current
-    st->dirty = 1;
+    st->dirty = system_of_trial ? 0 : 1;
+    if (system_of_trial) st->max_diag = max_diag;
   } else {
-    st->lambda = lambda * st->ni;   // pop(): current state untouched, the system stays valid
-    st->ni *= 2.0;
+    st->lambda = lambda * st->ni;   // pop(): current state untouched; the system stays valid unless it was rebuilt
+    st->ni *= 2.0;                  // at the trial state
     st->rejected += 1.0;
+    if (system_of_trial) st->dirty = 1;
   }
   const bool lam_bad = !accepted && !isfinite(st->lambda);
   int q = st->q;
@@ -438,6 +427,63 @@ __device__ __forceinline__ void trial_controller(const BAView& V, const LinArgs&
   st->q = 0;
   if (!accepted) st->dirty = 1;   // g2o rebuilds the system at the start of every outer iteration
   if (stop || st->iters >= st->max_iterations) st->done = 1;
+}
+
+// Controller after a trial (last CTA of the cost-only launch): cost of the trial state, computeScale,
+// then the Levenberg-Marquardt accept / reject logic of g2o (OptimizationAlgorithmLevenberg::solve)
+// entirely on the device.
+__device__ __forceinline__ void trial_controller(const BAView& V, const LinArgs& A, const ScaleView& SV,
+                                                 double* red /*[2 * kLinWarps]*/) {
+  LMState* st = A.st_rw;
+  const TrialArgs& T = A.trial;
+  // every load that does not depend on the scale edges is issued first, so that its L2 round trip runs under theirs
+  double v[2] = {0.0, 0.0};
+  for (int i = threadIdx.x; i < V.C; i += kLinThreads) v[0] += __ldcg(A.cam_cost + i);
+  for (int i = threadIdx.x; i < T.n_sp; i += kLinThreads) v[1] += __ldcg(T.scale_partial + i);   // points, then cameras
+  int status = 0, its = 0;
+  if (threadIdx.x == 0 && T.n) { status = __ldcg(T.pcg_status); its = __ldcg(T.pcg_iters); }
+  if (A.has_scale) {   // cost of the scale edges at the trial state (EdgeSBAScale + DCS)
+    scale_edges_body<kLinThreads>(SV, true, red);
+    __syncthreads();
+  }
+  block_reduce<2, kLinThreads>(v, red);
+  if (threadIdx.x != 0) return;
+  const double tmp = v[0] + (A.has_scale ? *A.scale_cost : 0.0);
+  lm_decide(st, tmp, v[1], status, its, false, 0.0);
+}
+
+// Controller of a SPECULATIVE linearisation (last CTA): the launch has built the system of the trial state (cost
+// included), so the accept / reject decision needs no separate cost pass, and an accepted trial -- the usual case --
+// leaves the next LM iteration's system ready (its linearisation launch returns at once).  A rejected trial has
+// overwritten the system of the current state: it is marked dirty and rebuilt, bit for bit the same, by the next
+// launch.  The state sequence is that of the cost-pass form; only what is evaluated when differs.
+__device__ __forceinline__ void spec_controller(const BAView& V, const LinArgs& A, double* red /*[3 * kLinWarps]*/) {
+  LMState* st = A.st_rw;
+  const TrialArgs& T = A.trial;
+  double cost = 0.0, md = 0.0, sct = 0.0;
+  const int n6 = 6 * V.Cf;
+  const int n_max = max(max(max(V.C, n6), A.n_pt_ctas), T.n_sp);
+  for (int i = threadIdx.x; i < n_max; i += kLinThreads) {
+    const int col = i / 6, r = i - 6 * col;
+    const double a = i < n6 ? __ldcg(A.Hpp + 36 * (size_t)col + 7 * r) : 0.0;
+    const double x = (i < n6 && A.has_scale && r < 3) ? __ldcg(A.extra_diag + 3 * col + r) : 0.0;
+    const double pm = i < A.n_pt_ctas ? __ldcg(A.pt_maxd + i) : 0.0;
+    if (i < V.C) cost += __ldcg(A.cam_cost + i);
+    if (i < T.n_sp) sct += __ldcg(T.scale_partial + i);
+    md = fmax(md, fmax(fabs(a + x), pm));
+  }
+  int status = 0, its = 0;
+  if (threadIdx.x == 0 && T.n) { status = __ldcg(T.pcg_status); its = __ldcg(T.pcg_iters); }
+  const double sc = A.has_scale ? __ldcg(A.scale_cost) : 0.0;
+  cost = warp_sum(cost); sct = warp_sum(sct);
+  for (int o = 16; o > 0; o >>= 1) md = fmax(md, __shfl_xor_sync(0xffffffffu, md, o));
+  const int wid = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) { red[wid] = cost; red[kLinWarps + wid] = sct; red[2 * kLinWarps + wid] = md; }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  double c2 = 0.0, s2 = 0.0, m2 = 0.0;
+  for (int w = 0; w < kLinWarps; ++w) { c2 += red[w]; s2 += red[kLinWarps + w]; m2 = fmax(m2, red[2 * kLinWarps + w]); }
+  lm_decide(st, c2 + sc, s2, status, its, true, m2);
 }
 
 __device__ __forceinline__ constexpr int hpp_u(int i, int j) { return i * 6 - (i * (i - 1)) / 2 + (j - i); }
@@ -453,8 +499,9 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
   const int4 w0 = __ldg(wsrc), w1 = __ldg(wsrc + 1);   // (static work list: may be read before the wait)
   pdl_wait();
   pdl_trigger();
-  if (V.st->done || (!COST_ONLY && !V.st->dirty && !A.force)) return;
-  const int sb = COST_ONLY ? (V.st->cur ^ 1) : V.st->cur;   // the cost-only pass evaluates the trial state
+  const bool spec = !COST_ONLY && A.spec != 0;
+  if (V.st->done || (!COST_ONLY && !spec && !V.st->dirty && !A.force)) return;
+  const int sb = (COST_ONLY || spec) ? (V.st->cur ^ 1) : V.st->cur;   // cost pass / speculative launch: the trial state
   const CamRT* __restrict__ camrt = V.camrt[sb];
   const double* __restrict__ pts = V.pts[sb];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -737,7 +784,7 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
     take_ticket = true;
   } else {
     // ------------------------------------------------ scale edges
-    scale_edges_body<kLinThreads>(SV, false, red);
+    scale_edges_body<kLinThreads>(SV, false, red, spec);
     take_ticket = true;
   }
 
@@ -757,6 +804,7 @@ ba_linearize_kernel(BAView V, LinArgs A, ScaleView SV) {
     if (!COST_ONLY && A.trace && tid == 0) A.trace[2 * gridDim.x + 3] = globaltimer_ns();
     fence_acq_rel_gpu();
     if (COST_ONLY) trial_controller(V, A, SV, red);
+    else if (spec) spec_controller(V, A, red);
     else lin_controller(V, A, red);
     if (!COST_ONLY && A.trace && tid == 0) A.trace[2 * gridDim.x] = globaltimer_ns();
   }
