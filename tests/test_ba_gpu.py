@@ -94,6 +94,25 @@ def test_ten_lm_iterations_match_restatement(args):
     assert np.abs(got.cams - ref.cams).max() < 1e-6 and np.abs(got.pts - ref.pts).max() < 1e-5
 
 
+@pytest.mark.parametrize("seed,pose_noise,pt_noise", [(0, (60.0, 3.0), 1.5), (3, (40.0, 2.0), 1.0), (5, (60.0, 3.0), 1.5)])
+def test_lm_loop_with_rejected_trials_matches_restatement(seed, pose_noise, pt_noise):
+    """Starts so far off that Levenberg-Marquardt rejects steps (the restatement needs 11-13 trials for its 10
+    iterations).  Inside the LM loop a trial ends with a speculative linearisation of the trial state; a rejected
+    trial therefore destroys the system of the current state, which must be rebuilt exactly: same iterations, trials
+    and rejected count as the restatement, cost within 1e-9, on a fresh engine and again from its captured graph."""
+    p = synthetic_ba(4, 80, 3.0, seed=seed, pose_noise=pose_noise, pt_noise=pt_noise)
+    h = oba.optimize(p.copy(), 10)
+    assert h["trials"] > h["iterations"]
+    eng = BAEngine(p)
+    for rep in range(3):
+        eng.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
+        st = eng.optimize(10)
+        assert (st["iterations"], st["trials"]) == (h["iterations"], h["trials"])
+        assert st["rejected"] == h["trials"] - h["iterations"]
+        assert abs(st["final_cost"] - h["final_cost"]) <= 1e-9 * h["final_cost"]
+    eng.close()
+
+
 def test_runs_are_bit_reproducible():
     p = synthetic_ba(6, 1000, 5.0, seed=9)
     a, b = p.copy(), p.copy()
