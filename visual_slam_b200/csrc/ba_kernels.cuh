@@ -848,7 +848,8 @@ __global__ void ba_point_invert(const LMState* __restrict__ st, int Pf, const do
 // partial of sum Hpl Hinv bl = sum G (W^T bl).
 __global__ void __launch_bounds__(kCamThreads)
 ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict__ Wf,
-             const double* __restrict__ bl, double* __restrict__ Gout, double* __restrict__ camp) {
+             const double* __restrict__ bl, double* __restrict__ Gout, double* __restrict__ camp,
+             const double* __restrict__ Hll /* non-null: W is formed here from Hll + lambda I (no ba_point_invert launch) */) {
   __shared__ double red[(kCamThreads / 32) * 6];
   __shared__ __align__(128) double stage_all[(kCamThreads / 32) * 32 * 18];   // a warp's 32 blocks (4608 B)
   static_assert(kCamChunk == kCamThreads, "one observation per thread and chunk");
@@ -878,8 +879,30 @@ ba_compute_G(BAView V, const double* __restrict__ Hpl, const double* __restrict_
   double w[6], b[3];
   const int pcol = pcol_mine;
   if (pcol >= 0) {                                       // (the gathers run under the copy)
+    if (Hll != nullptr) {
+      // small problems: the upper factor W (W W^T = (Hll + lambda I)^-1) per observation, by the statements of
+      // ba_point_invert -- one launch fewer in a chain where a launch costs as much as the arithmetic
+      double h[6];
 #pragma unroll
-    for (int j = 0; j < 6; ++j) w[j] = Wf[6 * (size_t)pcol + j];
+      for (int j = 0; j < 6; ++j) h[j] = Hll[6 * (size_t)pcol + j];
+      const double lambda = V.st->lambda;
+      h[0] += lambda; h[3] += lambda; h[5] += lambda;
+      const double c00 = sqrt(h[0]);
+      const double i00 = 1.0 / c00;
+      const double c10 = h[1] * i00, c20 = h[2] * i00;
+      const double c11 = sqrt(h[3] - c10 * c10);
+      const double i11 = 1.0 / c11;
+      const double c21 = (h[4] - c20 * c10) * i11;
+      const double c22 = sqrt(h[5] - c20 * c20 - c21 * c21);
+      const double i22 = 1.0 / c22;
+      const double m10 = -c10 * i00 * i11;
+      const double m21 = -c21 * i11 * i22;
+      const double m20 = -(c20 * i00 + c21 * m10) * i22;
+      w[0] = i00; w[1] = m10; w[2] = m20; w[3] = i11; w[4] = m21; w[5] = i22;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) w[j] = Wf[6 * (size_t)pcol + j];
+    }
 #pragma unroll
     for (int j = 0; j < 3; ++j) b[j] = bl[3 * (size_t)pcol + j];
   }
