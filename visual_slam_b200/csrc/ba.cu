@@ -674,9 +674,16 @@ static int enqueue_schur(BA& B, cudaStream_t st) {
                 (B.Pf && chunked) ? B.ck_bh.p : nullptr, B.cam_ck_start.p};
     const int* seg_us = chunked ? B.seg_cunit_start.p : B.seg_unit_start.p;
     const double* partials = chunked ? B.ck_partial.p : B.unit_partial.p;
-    launch_step_kernel(ba_schur_finalize, (B.n_seg * 36 + B.C * 6 + 127) / 128, 128, 0, st,
-                       V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, seg_us, partials, B.Hpp.p,
-                       B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
+    // four threads per entry when a block has many unit partials to add (a local window with 64-item units)
+    const long long n_part = chunked ? B.n_cunits : B.n_units;
+    if (n_part > 8ll * B.n_seg)
+      launch_step_kernel(ba_schur_finalize<4>, ((B.n_seg * 36 + B.C * 6) * 4 + 127) / 128, 128, 0, st,
+                         V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, seg_us, partials, B.Hpp.p,
+                         B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
+    else
+      launch_step_kernel(ba_schur_finalize<1>, (B.n_seg * 36 + B.C * 6 + 127) / 128, 128, 0, st,
+                         V, B.n_seg, B.n, B.seg_a.p, B.seg_b.p, seg_us, partials, B.Hpp.p,
+                         B.extra.p, B.seg_extra_idx.p, B.S.p, Bh);
     if (B.use_direct()) {
       DirectArgs D{};
       D.n = B.n; D.ld = direct_ld(B.n); D.done = &B.lm.p->done; D.S = B.S.p; D.b = B.bhat.p;

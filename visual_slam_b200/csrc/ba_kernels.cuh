@@ -1175,6 +1175,7 @@ __device__ __forceinline__ double bhat_partial_sum(const BAView& V, const BhatAr
   }
   return s;
 }
+template <int PARTS>   // threads per entry: 4 when a block has many unit partials (small work units), else 1
 __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restrict__ seg_a,
                                   const int* __restrict__ seg_b,
                                   const int* __restrict__ seg_unit_start,
@@ -1184,7 +1185,7 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
                                   const int* __restrict__ seg_extra_idx, double* __restrict__ S, BhatArgs Bh) {
   // the work lists are static structure: fetched BEFORE the wait, i.e. while the producing kernels still run
   // (programmatic dependent launch), so the dependent part starts with its indices in registers
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = (blockIdx.x * blockDim.x + threadIdx.x) / PARTS, part = threadIdx.x % PARTS;
   const int seg = t / 36, e = t % 36;
   int a = 0, b = 0, ex = -1, u0 = 0, u1 = 0;
   if (seg < n_seg) {
@@ -1199,11 +1200,12 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
   }
   if (V.st->done) return;
   const double lambda = V.st->lambda;
+  const unsigned quad_mask = __ballot_sync(0xffffffffu, seg < n_seg);   // (the lanes that take part in the sums below)
   if (seg >= n_seg) {
     // the threads behind the S blocks build bhat (one per camera and row)
     const int tb = t - n_seg * 36;
     const int c = tb / 6, i = tb - 6 * c;
-    if (Bh.bhat == nullptr || c >= V.C) return;
+    if (Bh.bhat == nullptr || c >= V.C || part != 0) return;
     const int col = V.cam_col[c];
     if (col < 0) return;
     const double s = bhat_partial_sum(V, Bh, c, i);
@@ -1214,13 +1216,18 @@ __global__ void ba_schur_finalize(BAView V, int n_seg, int n, const int* __restr
   double v = ex >= 0 ? extra[(size_t)ex * 36 + e] : 0.0;
   if (a == b) v += Hpp[36 * a + e] + (r == c ? lambda : 0.0);
   double s = 0.0;
-  for (int u = u0; u < u1; u += 8) {   // eight loads in flight, added in unit order
+  for (int u = u0 + part; u < u1; u += 8 * PARTS) {   // eight loads in flight per thread, added in unit order
     double w[8];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) w[q] = (u + q < u1) ? __ldcg(partial + (size_t)(u + q) * 36 + e) : 0.0;
+    for (int q = 0; q < 8; ++q) w[q] = (u + q * PARTS < u1) ? __ldcg(partial + (size_t)(u + q * PARTS) * 36 + e) : 0.0;
 #pragma unroll
     for (int q = 0; q < 8; ++q)
-      if (u + q < u1) s += w[q];
+      if (u + q * PARTS < u1) s += w[q];
+  }
+  if (PARTS == 4) {                     // (p0 + p1) + (p2 + p3): a fixed tree
+    s += __shfl_xor_sync(quad_mask, s, 1);
+    s += __shfl_xor_sync(quad_mask, s, 2);
+    if (part != 0) return;
   }
   v -= s;
   S[(size_t)(6 * a + r) * n + 6 * b + c] = v;
