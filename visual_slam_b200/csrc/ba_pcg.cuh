@@ -293,21 +293,42 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
       __syncthreads();
       local_matvec(wl);                                  // w = S u
       __syncthreads();
+      double inv_gamma_old = 0.0, pap_old = 0.0;
+      // With at most 32 local rows (the usual split: 18 at C4) the short serial part of an iteration -- recurrences,
+      // m = M^-1 w, the three dot products, publication -- runs in warp 0 alone under __syncwarp, and the other warps
+      // go straight to the grid barrier: four block-wide barriers and a shared-memory reduction fewer per iteration.
+      const bool warp_tail = R <= 32;
       for (it = 0; it <= A.max_iter; ++it) {
-        apply_minv(wl, ml);                              // m = M^-1 w
-        double gam_p = 0.0, del_p = 0.0, rr_p = 0.0;
-        for (int i = tid; i < R; i += kPcgThreads) {
-          gam_p += rl[i] * ul[i];
-          del_p += wl[i] * ul[i];
-          rr_p += rl[i] * rl[i];
-        }
-        block_sum3(gam_p, del_p, rr_p, red3);            // (also orders ml before its publication below)
         // the exchange buffers alternate with the iteration's parity: a CTA that has left the barrier may publish
         // the NEXT iteration's values while a slower one still reads this iteration's
         double* xch = A.p_glob + (size_t)(it & 1) * n;
         double* pch = A.part + (size_t)(it & 1) * 3 * G;
-        for (int i = tid; i < R; i += kPcgThreads) xch[row0 + i] = ml[i];
-        if (tid == 0) { pch[g] = gam_p; pch[G + g] = del_p; pch[2 * G + g] = rr_p; }
+        if (warp_tail) {
+          if (wid == 0) {
+            if (lane < R) {
+              const int bi = lane / 6, ii = lane % 6;
+              double z = 0.0;
+#pragma unroll
+              for (int j = 0; j < 6; ++j) z += minv[36 * bi + 6 * ii + j] * wl[6 * bi + j];
+              ml[lane] = z;
+              xch[row0 + lane] = z;
+            }
+            const double rv = lane < R ? rl[lane] : 0.0, uv = lane < R ? ul[lane] : 0.0, wv = lane < R ? wl[lane] : 0.0;
+            const double gam_p = warp_sum(rv * uv), del_p = warp_sum(wv * uv), rr_p = warp_sum(rv * rv);
+            if (lane == 0) { pch[g] = gam_p; pch[G + g] = del_p; pch[2 * G + g] = rr_p; }
+          }
+        } else {
+          apply_minv(wl, ml);                            // m = M^-1 w
+          double gam_p = 0.0, del_p = 0.0, rr_p = 0.0;
+          for (int i = tid; i < R; i += kPcgThreads) {
+            gam_p += rl[i] * ul[i];
+            del_p += wl[i] * ul[i];
+            rr_p += rl[i] * rl[i];
+          }
+          block_sum3(gam_p, del_p, rr_p, red3);          // (also orders ml before its publication below)
+          for (int i = tid; i < R; i += kPcgThreads) xch[row0 + i] = ml[i];
+          if (tid == 0) { pch[g] = gam_p; pch[G + g] = del_p; pch[2 * G + g] = rr_p; }
+        }
         grid_barrier(A.bar, target, G);
         for (int i = tid; i < n; i += kPcgThreads) u_full[i] = __ldcg(xch + i);
         double sums[3];
@@ -343,8 +364,7 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
         }
         __syncthreads();                                   // (u_full is complete after it, too)
 #pragma unroll
-        for (int k = 0; k < 3; ++k) sums[k] = s_sum[k];
-        __syncthreads();
+        for (int k = 0; k < 3; ++k) sums[k] = s_sum[k];    // (rewritten only after the next grid barrier)
         const double gamma = sums[0], delta = sums[1], rr = sums[2];
         if (it == 0) {
           if (!(rr > 0.0)) { status = 0; break; }        // b == 0: x = 0
@@ -352,28 +372,32 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
         }
         if (rr <= thresh && it > 0) { status = 0; break; }
         if (it == A.max_iter) break;
+        // reciprocals instead of divisions on the scalar path that every thread walks between the barrier and the
+        // product (p^T S p = delta - beta^2 * previous p^T S p, as in the single-CTA kernel)
         double beta = 0.0, pap = delta;
         if (it > 0) {
-          beta = gamma / gamma_old;
-          pap = delta - beta * gamma / alpha_old;
+          beta = gamma * inv_gamma_old;
+          pap = delta - beta * beta * pap_old;
         }
-        if (!(pap > 0.0) || !isfinite(pap) || !(gamma > 0.0)) { status = 1; break; }
-        const double alpha = gamma / pap;
+        if (!(pap > 1e-290) || !(pap < 1e290) || !(gamma > 1e-290) || !(gamma < 1e290)) { status = 1; break; }
+        const double alpha = gamma * fast_rcp(pap);
+        inv_gamma_old = fast_rcp(gamma); pap_old = pap;
         local_matvec(nl);                                // n = S m (u_full holds m)
         __syncthreads();
-        for (int i = tid; i < R; i += kPcgThreads) {
-          const double z = nl[i] + beta * zl[i];
-          const double q = ml[i] + beta * ql[i];
-          const double sv = wl[i] + beta * sl[i];
-          const double pv = ul[i] + beta * pl[i];
-          zl[i] = z; ql[i] = q; sl[i] = sv; pl[i] = pv;
-          xl[i] += alpha * pv;
-          rl[i] -= alpha * sv;
-          ul[i] -= alpha * q;
-          wl[i] -= alpha * z;
+        if (!warp_tail || wid == 0) {
+          for (int i = tid; i < R; i += kPcgThreads) {
+            const double z = nl[i] + beta * zl[i];
+            const double q = ml[i] + beta * ql[i];
+            const double sv = wl[i] + beta * sl[i];
+            const double pv = ul[i] + beta * pl[i];
+            zl[i] = z; ql[i] = q; sl[i] = sv; pl[i] = pv;
+            xl[i] += alpha * pv;
+            rl[i] -= alpha * sv;
+            ul[i] -= alpha * q;
+            wl[i] -= alpha * z;
+          }
         }
-        __syncthreads();
-        gamma_old = gamma; alpha_old = alpha;
+        if (warp_tail) __syncwarp(); else __syncthreads();
       }
     }
   } else
