@@ -346,6 +346,28 @@ def test_batch_of_independent_windows_equals_one_by_one():
         e.close()
 
 
+def test_solvers_of_different_sizes_side_by_side():
+    """The PCG kernel's shared-memory limit is an attribute of the process: a mid-size window (its PCG runs as many CTAs
+    as it has free cameras, each with its slab of S in shared memory) keeps working after smaller users of the same
+    kernel -- another engine, the stand-alone vslam_pcg_solve -- have been set up, and repeats its result bit for bit."""
+    p = synthetic_ba(30, 4000, 6.0, seed=8)
+    big = BAEngine(p)
+    assert big.dims()["pcg_ctas"] > 1
+    ref = big.optimize(5)
+    state = [x.cpu().numpy() for x in big.get_state()]
+    small = BAEngine(synthetic_ba(12, 500, 4.0, seed=9))
+    small.optimize(3)
+    rng = np.random.default_rng(0)
+    A = rng.normal(size=(72, 72)); S = A @ A.T + 72 * np.eye(72); b = rng.normal(size=72)
+    x, status, _ = pcg_solve(torch.from_numpy(S).cuda(), torch.from_numpy(b).cuda())
+    assert status == 0 and np.allclose(x.cpu().numpy(), np.linalg.solve(S, b), rtol=1e-8, atol=1e-10)
+    big.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
+    assert big.optimize(5) == ref
+    got = [x.cpu().numpy() for x in big.get_state()]
+    assert np.array_equal(got[0], state[0]) and np.array_equal(got[1], state[1])
+    big.close(); small.close()
+
+
 def test_schur_variants_agree_with_fixed_points_duplicates_and_fixed_cameras():
     """The chunked Schur kernel against the sorted-unit one on structures that exercise its item rules: fixed points
     (no contribution), a fixed camera in the middle, a point observed twice by the same camera, a camera with more

@@ -207,6 +207,21 @@ static void launch_step_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, 
   cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);   // errors surface in check_launch
 }
 
+// The dynamic shared memory limit of a kernel is a per-function attribute of the process, not of a launch: every user of
+// ba_pcg_kernel (solvers of different sizes, the stand-alone entry points) raises it to the device maximum, so that
+// none lowers it under another's feet.
+static cudaError_t pcg_kernel_allow_max_smem() {
+  int max_smem = 0, dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  e = cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (e != cudaSuccess) return e;
+  cudaFuncAttributes fa{};
+  e = cudaFuncGetAttributes(&fa, ba_pcg_kernel);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              max_smem - (int)fa.sharedSizeBytes);   // (static + dynamic share the opt-in limit)
+}
 static size_t pcg_small_smem(int n) { return sizeof(double) * ((size_t)n * n + 6 * (size_t)n + 16 * 64); }   // S, M^-1, r/u copies, partials
 
 static void counting_sort(const std::vector<int>& in, const int* key, int n_keys, std::vector<int>& out) {
@@ -581,17 +596,22 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
                                (slab ? (size_t)rows * B.n : 0));
     };
     int bpc = std::max(1, (nb + sms - 1) / sms);  // blocks per CTA with one CTA per SM
-    // prefer fewer CTAs (cheaper barriers) while the slab still fits
-    int best = bpc;
-    for (int t = nb; t >= bpc; --t) {
-      if (smem_for(6 * t, true) <= budget) { best = t; break; }
+    // As many CTAs as there are camera blocks, up to 128: with one grid barrier per iteration the local product is what
+    // is left to shrink, and the barrier costs about the same for 30 as for 120 arrivals.  (Measured, optimize(10):
+    // 29 free cameras 4.3k -> 6.0k LM it/s against two CTAs of 150 rows, 59 cameras 3.7k -> 4.7k, 119 cameras
+    // 2.9k -> 3.3k, C4 (199 cameras, 100 CTAs instead of 67) 1.90k -> 1.93k.)
+    int best = std::max(bpc, (nb + 127) / 128);
+    while (best > bpc && smem_for(6 * best, true) > budget) --best;
+    if (const char* e = std::getenv("VSLAM_BA_PCG_BLOCKS")) {   // (experiments: camera blocks per PCG CTA)
+      const int t = std::atoi(e);
+      if (t >= bpc && t <= nb && smem_for(6 * t, true) <= budget) best = t;
     }
     B.pcg_slab = smem_for(6 * best, true) <= budget ? 1 : 0;
     B.pcg_rows = 6 * std::max(best, 1);
     B.pcg_G = std::max(1, (nb + best - 1) / std::max(best, 1));
     B.pcg_smem = smem_for(B.pcg_rows, B.pcg_slab);
     if (B.pcg_smem > budget) return VSLAM_ERR_BAD_ARG;
-    BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)B.pcg_smem));
+    BA_TRY(pcg_kernel_allow_max_smem());
     BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)direct_smem(kDirectMax)));
   }
@@ -1221,7 +1241,7 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
   size_t smem_noslab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8);
   A.slab_in_smem = smem_slab <= 200 * 1024;
   size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
-  BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  BA_TRY(pcg_kernel_allow_max_smem());
   if (n <= kPcgSmallMax) ba_pcg_small_kernel<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
   else ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
   int rc = check_launch("ba_pcg_kernel");
@@ -1391,7 +1411,7 @@ extern "C" int vslam_pcg_solve_static(const double* S, const double* b, double* 
   const size_t smem_noslab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8);
   A.slab_in_smem = smem_slab <= 200 * 1024;
   const size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
-  BA_TRY(cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  BA_TRY(pcg_kernel_allow_max_smem());
   ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
   return check_launch("ba_pcg_kernel");
 }

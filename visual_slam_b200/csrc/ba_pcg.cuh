@@ -333,21 +333,21 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
         for (int i = tid; i < n; i += kPcgThreads) u_full[i] = __ldcg(xch + i);
         double sums[3];
         if (tid < 32) {                                    // all nine loads of a lane in flight, then the three sums
-          double v[3][3];
+          double v[3][5];
 #pragma unroll
           for (int k = 0; k < 3; ++k) {
 #pragma unroll
-            for (int q = 0; q < 3; ++q) {
+            for (int q = 0; q < 5; ++q) {
               const int gg = tid + 32 * q;
               v[k][q] = gg < G ? __ldcg(pch + k * G + gg) : 0.0;
             }
           }
-          if (G <= 96) {
+          if (G <= 160) {                                  // (one CTA per SM at most: always, on 148 SMs)
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
               double sk = 0.0;
 #pragma unroll
-              for (int q = 0; q < 3; ++q)
+              for (int q = 0; q < 5; ++q)
                 if (tid + 32 * q < G) sk += v[k][q];
               sk = warp_sum(sk);
               if (tid == 0) s_sum[k] = sk;
