@@ -74,7 +74,11 @@ def test_linearize_and_one_trial_match_restatement(args, schur):
 
 @pytest.mark.parametrize("args", [dict(n_cams=10, n_pts=5000, obs_per_pt=6.0, seed=0),
                                   dict(n_cams=5, n_pts=200, obs_per_pt=3.5, seed=7),
-                                  dict(n_cams=8, n_pts=800, obs_per_pt=5.0, seed=5, motion_only=True)])
+                                  dict(n_cams=8, n_pts=800, obs_per_pt=5.0, seed=5, motion_only=True),
+                                  # 11 / 21 free cameras: the four-rows-per-lane single-CTA PCG; 26: the multi-CTA one
+                                  dict(n_cams=12, n_pts=900, obs_per_pt=5.0, seed=31),
+                                  dict(n_cams=22, n_pts=1200, obs_per_pt=6.0, seed=32),
+                                  dict(n_cams=27, n_pts=1200, obs_per_pt=6.0, seed=33)])
 def test_ten_lm_iterations_match_restatement(args):
     """north_star tolerance: final cost within 1e-4 relative, RMS reprojection within 1e-3 px."""
     p = synthetic_ba(**args)
@@ -198,11 +202,21 @@ def test_blocks_of_s_without_schur_units_and_multi_chunk_cameras():
 
 def test_pcg_solves_spd_systems():
     rng = np.random.default_rng(0)
-    for n in (6, 54, 96, 300):
+    # 6 .. 60: single CTA, two rows per lane; 66 .. 126: single CTA, four rows per lane (S in registers in both);
+    # beyond: the general kernel
+    for n in (6, 54, 60, 66, 72, 96, 102, 126, 132, 300):
         A = rng.normal(size=(n, n)); S = A @ A.T + n * np.eye(n); b = rng.normal(size=n)
         x, status, iters = pcg_solve(torch.from_numpy(S).cuda(), torch.from_numpy(b).cuda(), 1e-12, 5000)
         assert status == 0 and iters <= 5000
         assert np.abs(S @ x.cpu().numpy() - b).max() <= 1e-9 * np.abs(b).max()
+    # an indefinite system and a zero right-hand side at the four-rows-per-lane size
+    n = 96
+    A = rng.normal(size=(n, n)); S = A @ A.T + n * np.eye(n); S[7, 7] = -5.0
+    _, status, _ = pcg_solve(torch.from_numpy(S).cuda(), torch.from_numpy(rng.normal(size=n)).cuda(), 1e-12, 500)
+    assert status == 1
+    S[7, 7] = 500.0
+    x, status, iters = pcg_solve(torch.from_numpy(S).cuda(), torch.zeros(n, dtype=torch.float64).cuda(), 1e-12, 500)
+    assert status == 0 and iters == 0 and float(x.abs().max()) == 0.0
 
 
 def test_rejected_step_leaves_state_untouched_and_lambda_grows():

@@ -602,6 +602,7 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     // 2.9k -> 3.3k, C4 (199 cameras, 100 CTAs instead of 67) 1.90k -> 1.93k.)
     int best = std::max(bpc, (nb + 127) / 128);
     while (best > bpc && smem_for(6 * best, true) > budget) --best;
+    if (B.n <= kPcgMidMax) best = std::max(nb, 1);   // one CTA: ba_pcg_small_kernel / ba_pcg_mid_kernel keep S in registers
     if (const char* e = std::getenv("VSLAM_BA_PCG_BLOCKS")) {   // (experiments: camera blocks per PCG CTA)
       const int t = std::atoi(e);
       if (t >= bpc && t <= nb && smem_for(6 * t, true) <= budget) best = t;
@@ -739,6 +740,8 @@ static int enqueue_trial(BA& B, cudaStream_t st, bool speculative = false) {
                                          B.pcg_smem, st));
     } else if (B.n <= kPcgSmallMax) {
       launch_step_kernel(ba_pcg_small_kernel, 1, kPcgSmallThreads, pcg_small_smem(B.n), st, A);
+    } else if (B.n <= kPcgMidMax) {
+      launch_step_kernel(ba_pcg_mid_kernel, 1, kPcgMidThreads, kPcgMidSmemDoubles * sizeof(double), st, A);
     } else {
       launch_step_kernel(ba_pcg_kernel, 1, kPcgThreads, B.pcg_smem, st, A);
     }
@@ -1243,6 +1246,7 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
   size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
   BA_TRY(pcg_kernel_allow_max_smem());
   if (n <= kPcgSmallMax) ba_pcg_small_kernel<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
+  else if (n <= kPcgMidMax && n % 6 == 0) ba_pcg_mid_kernel<<<1, kPcgMidThreads, kPcgMidSmemDoubles * sizeof(double), st>>>(A);
   else ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
   int rc = check_launch("ba_pcg_kernel");
   if (rc) return rc;
@@ -1406,6 +1410,10 @@ extern "C" int vslam_pcg_solve_static(const double* S, const double* b, double* 
   if (n <= kPcgSmallMax) {
     ba_pcg_small_kernel<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
     return check_launch("ba_pcg_small_kernel");
+  }
+  if (n <= kPcgMidMax && n % 6 == 0) {
+    ba_pcg_mid_kernel<<<1, kPcgMidThreads, kPcgMidSmemDoubles * sizeof(double), st>>>(A);
+    return check_launch("ba_pcg_mid_kernel");
   }
   const size_t smem_slab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8 + (size_t)n * n);
   const size_t smem_noslab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8);

@@ -596,4 +596,146 @@ __global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_kernel(PcgArgs 
   }
 }
 
+// Systems of 11 .. 21 free cameras (64 < n <= kPcgMidMax): the single-CTA kernel above with four rows per lane and
+// eight warps, i.e. S (<= 128 x 128) still lives in registers for the whole solve -- 64 doubles per thread -- and an
+// iteration still costs one block barrier.  The cooperative multi-CTA kernel pays a grid barrier and a gather through
+// L2 per iteration (~3.2 us) whatever the size: at n = 66 that was 70 of the 120 us of an LM iteration.  The
+// preconditioner rows are read from shared memory here (no registers left for them); the diagonal blocks are inverted
+// BEFORE the loads of S are issued, because the inversion's live set and the 128 registers of S do not fit together.
+constexpr int kPcgMidMax = 128;
+constexpr int kPcgMidThreads = 256;
+constexpr int kPcgMidWarps = kPcgMidThreads / 32;
+constexpr int kPcgMidRows = 4;                         // rows per lane: lane, lane + 32, ...
+constexpr int kPcgMidCols = 16;                        // columns per warp, at most
+constexpr size_t kPcgMidSmemDoubles = 6 * kPcgMidMax + 4 * kPcgMidWarps * kPcgMidMax;   // M^-1, r / u copies, two sets of partials
+
+__global__ void __launch_bounds__(kPcgMidThreads, 1) ba_pcg_mid_kernel(PcgArgs A) {
+  extern __shared__ __align__(16) double sm[];
+  pdl_wait();
+  pdl_trigger();
+  if (A.done != nullptr && *A.done) return;
+  constexpr int NR = kPcgMidRows, W = kPcgMidWarps, NM = kPcgMidMax;
+  const int n = A.n, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  double* minv = sm;                                // [n/6][36]
+  double* rs = sm + 6 * NM + wid * NM;              // [W][NM] each warp's own copy of r
+  double* us = sm + 6 * NM + (W + wid) * NM;        // [W][NM] ... of u
+  double* part = sm + 6 * NM + 2 * W * NM;          // [2][W][NM]
+  int fail = 0;
+  if (threadIdx.x < n / 6) {                        // n <= 128: at most 21 blocks, all in warp 0
+    const int bi = threadIdx.x;
+    double blk[36];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) blk[6 * i + j] = __ldcg(A.S + (size_t)(6 * bi + i) * n + 6 * bi + j);
+    }
+    if (!spd6_inverse(blk)) fail = 1;
+#pragma unroll
+    for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
+  }
+  // this lane's entries of S for the warp's column range: four rows x <= 16 columns (S is symmetric, so a warp reads
+  // consecutive addresses of row j for its "column" j)
+  int ri[NR], rb6[NR], rm[NR];
+  bool h[NR];
+#pragma unroll
+  for (int k = 0; k < NR; ++k) {
+    ri[k] = lane + 32 * k;
+    h[k] = ri[k] < n;
+    const int b = h[k] ? ri[k] / 6 : 0;
+    rb6[k] = 6 * b;                                 // first row of the diagonal block
+    rm[k] = h[k] ? 36 * b + 6 * (ri[k] - 6 * b) : 0;   // this row of M^-1
+  }
+  const int cols = ((n + 2 * W - 1) / (2 * W)) * 2;   // column range of this warp, <= 16 (multiples of 2)
+  const int j0 = min(n, wid * cols), j1 = min(n, j0 + cols);
+  double sr[NR][kPcgMidCols];
+#pragma unroll
+  for (int q = 0; q < kPcgMidCols; ++q) {
+    const int j = j0 + q;
+#pragma unroll
+    for (int k = 0; k < NR; ++k) sr[k][q] = (j < j1 && h[k]) ? __ldcg(A.S + (size_t)j * n + ri[k]) : 0.0;
+  }
+#pragma unroll
+  for (int k = 0; k < NR; ++k) { rs[ri[k]] = 0.0; us[ri[k]] = 0.0; }
+  fail = __syncthreads_or(fail);
+  double x[NR], p[NR], sv[NR], r[NR];
+#pragma unroll
+  for (int k = 0; k < NR; ++k) { x[k] = 0.0; p[k] = 0.0; sv[k] = 0.0; r[k] = h[k] ? A.b[ri[k]] : 0.0; }
+  int status = fail ? 1 : 2, it = 0, buf = 0;
+  double inv_gamma_old = 0.0, pap_old = 0.0, thresh = 0.0;
+  if (!fail) {
+    for (it = 0;; ++it) {
+      // u = M^-1 r through the warp's own shared-memory copy of r
+#pragma unroll
+      for (int k = 0; k < NR; ++k) rs[ri[k]] = r[k];
+      __syncwarp();
+      double u[NR];
+#pragma unroll
+      for (int k = 0; k < NR; ++k) {
+        const double* ra = rs + rb6[k];
+        const double* m = minv + rm[k];
+        const double t = (m[0] * ra[0] + m[1] * ra[1]) + (m[2] * ra[2] + m[3] * ra[3]) + (m[4] * ra[4] + m[5] * ra[5]);
+        u[k] = h[k] ? t : 0.0;
+        us[ri[k]] = u[k];
+      }
+      __syncwarp();
+      {   // partial w = S[:, j0:j1] u[j0:j1] for this lane's rows
+        double wa[NR], wb[NR];
+#pragma unroll
+        for (int k = 0; k < NR; ++k) { wa[k] = 0.0; wb[k] = 0.0; }
+#pragma unroll
+        for (int q = 0; q < kPcgMidCols / 2; ++q) {   // (entries beyond the column range are zero, u beyond n is zero)
+          const int j = min(j0 + 2 * q, NM - 2);
+          const double ua = us[j], ub = us[j + 1];
+#pragma unroll
+          for (int k = 0; k < NR; ++k) { wa[k] = fma(sr[k][2 * q], ua, wa[k]); wb[k] = fma(sr[k][2 * q + 1], ub, wb[k]); }
+        }
+        double* pw = part + (buf * W + wid) * NM;
+#pragma unroll
+        for (int k = 0; k < NR; ++k) pw[ri[k]] = h[k] ? wa[k] + wb[k] : 0.0;
+      }
+      __syncthreads();
+      const double* pr = part + buf * W * NM;
+      buf ^= 1;
+      double w[NR];
+      double g_p = 0.0, d_p = 0.0, r_p = 0.0;
+#pragma unroll
+      for (int k = 0; k < NR; ++k) {
+        const double* q = pr + ri[k];
+        w[k] = ((q[0] + q[NM]) + (q[2 * NM] + q[3 * NM])) + ((q[4 * NM] + q[5 * NM]) + (q[6 * NM] + q[7 * NM]));
+        g_p = fma(r[k], u[k], g_p); d_p = fma(w[k], u[k], d_p); r_p = fma(r[k], r[k], r_p);
+      }
+      const double gamma = warp_sum(g_p);
+      const double delta = warp_sum(d_p);
+      const double rr = warp_sum(r_p);
+      if (it == 0) {
+        if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
+        thresh = A.tol * A.tol * rr;
+      }
+      if (rr <= thresh && it > 0) { status = 0; break; }
+      if (it == A.max_iter) break;
+      double beta = 0.0, pap = delta;
+      if (it > 0) {
+        beta = gamma * inv_gamma_old;
+        pap = delta - beta * beta * pap_old;           // = p^T S p in exact arithmetic
+      }
+      if (!(pap > 1e-290) || !(pap < 1e290) || !(gamma > 1e-290) || !(gamma < 1e290)) { status = 1; break; }
+      const double alpha = gamma * fast_rcp(pap);
+      inv_gamma_old = fast_rcp(gamma); pap_old = pap;
+#pragma unroll
+      for (int k = 0; k < NR; ++k) {
+        p[k] = u[k] + beta * p[k];
+        sv[k] = w[k] + beta * sv[k];
+        x[k] += alpha * p[k];
+        r[k] -= alpha * sv[k];
+      }
+    }
+  }
+  if (wid == 0) {
+#pragma unroll
+    for (int k = 0; k < NR; ++k)
+      if (h[k]) A.x[ri[k]] = (status == 1) ? 0.0 : x[k];
+    if (lane == 0) { *A.status = status; *A.iters = it; }
+  }
+}
+
 }  // namespace vslam
