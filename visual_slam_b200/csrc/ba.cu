@@ -134,7 +134,7 @@ struct BA {
   DevBuf<unsigned> bar;
   DevBuf<int> pcg_flags;  // [0] fail flag, [1] status, [2] iters
   // PCG launch configuration
-  int pcg_G = 1, pcg_rows = 6, pcg_slab = 1;
+  int pcg_G = 1, pcg_rows = 6, pcg_slab = 1, pcg_cluster = 0;
   size_t pcg_smem = 0;
   double pcg_tol = 1e-10;
   int pcg_max_iter = 0;
@@ -221,6 +221,18 @@ static cudaError_t pcg_kernel_allow_max_smem() {
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               max_smem - (int)fa.sharedSizeBytes);   // (static + dynamic share the opt-in limit)
+}
+static cudaError_t pcg_cluster_kernel_allow_max_smem() {
+  int max_smem = 0, dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  e = cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (e != cudaSuccess) return e;
+  cudaFuncAttributes fa{};
+  e = cudaFuncGetAttributes(&fa, ba_pcg_cluster_kernel);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(ba_pcg_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              max_smem - (int)fa.sharedSizeBytes);
 }
 static size_t pcg_small_smem(int n) { return sizeof(double) * ((size_t)n * n + 6 * (size_t)n + 16 * 64); }   // S, M^-1, r/u copies, partials
 
@@ -607,10 +619,18 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
       const int t = std::atoi(e);
       if (t >= bpc && t <= nb && smem_for(6 * t, true) <= budget) best = t;
     }
+    // 22 .. 64 free cameras: one thread-block cluster (ba_pcg_cluster_kernel), exchange through DSMEM
+    static const bool cluster_ok = [] { const char* e = getenv("VSLAM_BA_PCG_CLUSTER"); return !(e && atoi(e) == 0); }();
+    B.pcg_cluster = 0;
+    if (cluster_ok && B.n > kPcgMidMax && B.n <= kPcgClusterMaxN) {
+      const int t = (nb + kPcgClusterMaxCtas - 1) / kPcgClusterMaxCtas;
+      if (6 * t <= kPcgClusterMaxRows && pcg_cluster_smem_doubles(B.n, 6 * t) * sizeof(double) <= budget) { best = t; B.pcg_cluster = 1; }
+    }
     B.pcg_slab = smem_for(6 * best, true) <= budget ? 1 : 0;
     B.pcg_rows = 6 * std::max(best, 1);
     B.pcg_G = std::max(1, (nb + best - 1) / std::max(best, 1));
-    B.pcg_smem = smem_for(B.pcg_rows, B.pcg_slab);
+    B.pcg_smem = B.pcg_cluster ? pcg_cluster_smem_doubles(B.n, B.pcg_rows) * sizeof(double) : smem_for(B.pcg_rows, B.pcg_slab);
+    if (B.pcg_cluster) BA_TRY(pcg_cluster_kernel_allow_max_smem());
     if (B.pcg_smem > budget) return VSLAM_ERR_BAD_ARG;
     BA_TRY(pcg_kernel_allow_max_smem());
     BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -735,7 +755,19 @@ static int enqueue_trial(BA& B, cudaStream_t st, bool speculative = false) {
     static const bool pipelined = [] { const char* e = getenv("VSLAM_BA_PCG_PIPELINED"); return !(e && atoi(e) == 0); }();
     A.pipelined = (pipelined && B.pcg_G > 1) ? 1 : 0;
     void* args[] = {&A};
-    if (B.pcg_G > 1) {
+    if (B.pcg_cluster) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(B.pcg_G); cfg.blockDim = dim3(kPcgThreads); cfg.dynamicSmemBytes = B.pcg_smem; cfg.stream = st;
+      cudaLaunchAttribute attr[2];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = (unsigned)B.pcg_G; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[1].val.programmaticStreamSerializationAllowed = 1;
+      cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+      cudaStreamIsCapturing(st, &cap);
+      cfg.attrs = attr; cfg.numAttrs = (use_pdl() && cap == cudaStreamCaptureStatusNone) ? 2 : 1;
+      BA_TRY(cudaLaunchKernelEx(&cfg, ba_pcg_cluster_kernel, A));
+    } else if (B.pcg_G > 1) {
       BA_TRY(cudaLaunchCooperativeKernel((void*)ba_pcg_kernel, dim3(B.pcg_G), dim3(kPcgThreads), args,
                                          B.pcg_smem, st));
     } else if (B.n <= kPcgSmallMax) {

@@ -8,6 +8,8 @@
 // A non-positive curvature p^T S p (or a non-SPD diagonal block) reports status 1: the LM loop
 // treats that exactly like g2o treats a failed Cholesky (rejected step; cf. reference debug.txt).
 #pragma once
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace vslam {
@@ -151,6 +153,57 @@ __device__ __forceinline__ void gather_sums(const double* part, int G, double* s
   __syncthreads();
 }
 
+// Local rows of S * (vector in u_full).  A warp takes up to four rows (wid, wid + 8, ...) TOGETHER, so that an
+// element of the vector is read from shared memory once for all of them: the product moves 16 bytes of shared
+// memory per FMA otherwise, and at 18 rows x 1194 columns per CTA that alone is 2700 cycles of the one
+// shared-memory pipe (measured 2.8 us per product, a third of a PCG iteration at C4).
+__device__ __forceinline__ void pcg_local_matvec(const double* __restrict__ Srows, int n, int R, const double* u_full,
+                                               double* y, int wid, int lane) {
+  for (int r0 = wid; r0 < R; r0 += 4 * (kPcgThreads / 32)) {
+    const double* row0p = Srows + (size_t)r0 * n;
+    const size_t rs = (size_t)(kPcgThreads / 32) * n;           // stride between the warp's rows
+    constexpr int W = kPcgThreads / 32;
+    const bool h1 = r0 + W < R, h2 = r0 + 2 * W < R, h3 = r0 + 3 * W < R;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+    // n is a multiple of 6 and the slab starts on a 16-byte boundary: every row does, so a lane reads two
+    // neighbouring columns with one 128-bit load
+    const bool vec = ((reinterpret_cast<uintptr_t>(row0p) | reinterpret_cast<uintptr_t>(u_full)) & 15) == 0 && (n & 1) == 0;
+    if (vec) {
+      for (int j = 2 * lane; j < n; j += 64) {
+        const double2 u = *reinterpret_cast<const double2*>(u_full + j);
+        const double2 s0 = *reinterpret_cast<const double2*>(row0p + j);
+        a0 = fma(s0.x, u.x, a0); b0 = fma(s0.y, u.y, b0);
+        if (h1) { const double2 t = *reinterpret_cast<const double2*>(row0p + rs + j); a1 = fma(t.x, u.x, a1); b1 = fma(t.y, u.y, b1); }
+        if (h2) { const double2 t = *reinterpret_cast<const double2*>(row0p + 2 * rs + j); a2 = fma(t.x, u.x, a2); b2 = fma(t.y, u.y, b2); }
+        if (h3) { const double2 t = *reinterpret_cast<const double2*>(row0p + 3 * rs + j); a3 = fma(t.x, u.x, a3); b3 = fma(t.y, u.y, b3); }
+      }
+    } else {
+      int j = lane;
+      for (; j + 32 < n; j += 64) {
+        const double u0 = u_full[j], u1 = u_full[j + 32];
+        a0 = fma(row0p[j], u0, a0); b0 = fma(row0p[j + 32], u1, b0);
+        if (h1) { a1 = fma(row0p[rs + j], u0, a1); b1 = fma(row0p[rs + j + 32], u1, b1); }
+        if (h2) { a2 = fma(row0p[2 * rs + j], u0, a2); b2 = fma(row0p[2 * rs + j + 32], u1, b2); }
+        if (h3) { a3 = fma(row0p[3 * rs + j], u0, a3); b3 = fma(row0p[3 * rs + j + 32], u1, b3); }
+      }
+      for (; j < n; j += 32) {
+        const double u0 = u_full[j];
+        a0 = fma(row0p[j], u0, a0);
+        if (h1) a1 = fma(row0p[rs + j], u0, a1);
+        if (h2) a2 = fma(row0p[2 * rs + j], u0, a2);
+        if (h3) a3 = fma(row0p[3 * rs + j], u0, a3);
+      }
+    }
+    a0 = warp_sum(a0 + b0); a1 = warp_sum(a1 + b1); a2 = warp_sum(a2 + b2); a3 = warp_sum(a3 + b3);
+    if (lane == 0) {
+      y[r0] = a0;
+      if (h1) y[r0 + W] = a1;
+      if (h2) y[r0 + 2 * W] = a2;
+      if (h3) y[r0 + 3 * W] = a3;
+    }
+  }
+}
+
 // Chronopoulos-Gear preconditioned CG: one matrix-vector product and ONE fused reduction per
 // iteration, i.e. two grid barriers (publish u = M^-1 r; reduce (r,u), (Au,u), (r,r)).
 __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
@@ -225,55 +278,7 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
       y[i] = z;
     }
   };
-  // Local rows of S * (vector in u_full).  A warp takes up to four rows (wid, wid + 8, ...) TOGETHER, so that an
-  // element of the vector is read from shared memory once for all of them: the product moves 16 bytes of shared
-  // memory per FMA otherwise, and at 18 rows x 1194 columns per CTA that alone is 2700 cycles of the one
-  // shared-memory pipe (measured 2.8 us per product, a third of a PCG iteration at C4).
-  auto local_matvec = [&](double* y) {
-    for (int r0 = wid; r0 < R; r0 += 4 * (kPcgThreads / 32)) {
-      const double* row0p = Srows + (size_t)r0 * n;
-      const size_t rs = (size_t)(kPcgThreads / 32) * n;           // stride between the warp's rows
-      constexpr int W = kPcgThreads / 32;
-      const bool h1 = r0 + W < R, h2 = r0 + 2 * W < R, h3 = r0 + 3 * W < R;
-      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
-      // n is a multiple of 6 and the slab starts on a 16-byte boundary: every row does, so a lane reads two
-      // neighbouring columns with one 128-bit load
-      const bool vec = ((reinterpret_cast<uintptr_t>(row0p) | reinterpret_cast<uintptr_t>(u_full)) & 15) == 0 && (n & 1) == 0;
-      if (vec) {
-        for (int j = 2 * lane; j < n; j += 64) {
-          const double2 u = *reinterpret_cast<const double2*>(u_full + j);
-          const double2 s0 = *reinterpret_cast<const double2*>(row0p + j);
-          a0 = fma(s0.x, u.x, a0); b0 = fma(s0.y, u.y, b0);
-          if (h1) { const double2 t = *reinterpret_cast<const double2*>(row0p + rs + j); a1 = fma(t.x, u.x, a1); b1 = fma(t.y, u.y, b1); }
-          if (h2) { const double2 t = *reinterpret_cast<const double2*>(row0p + 2 * rs + j); a2 = fma(t.x, u.x, a2); b2 = fma(t.y, u.y, b2); }
-          if (h3) { const double2 t = *reinterpret_cast<const double2*>(row0p + 3 * rs + j); a3 = fma(t.x, u.x, a3); b3 = fma(t.y, u.y, b3); }
-        }
-      } else {
-        int j = lane;
-        for (; j + 32 < n; j += 64) {
-          const double u0 = u_full[j], u1 = u_full[j + 32];
-          a0 = fma(row0p[j], u0, a0); b0 = fma(row0p[j + 32], u1, b0);
-          if (h1) { a1 = fma(row0p[rs + j], u0, a1); b1 = fma(row0p[rs + j + 32], u1, b1); }
-          if (h2) { a2 = fma(row0p[2 * rs + j], u0, a2); b2 = fma(row0p[2 * rs + j + 32], u1, b2); }
-          if (h3) { a3 = fma(row0p[3 * rs + j], u0, a3); b3 = fma(row0p[3 * rs + j + 32], u1, b3); }
-        }
-        for (; j < n; j += 32) {
-          const double u0 = u_full[j];
-          a0 = fma(row0p[j], u0, a0);
-          if (h1) a1 = fma(row0p[rs + j], u0, a1);
-          if (h2) a2 = fma(row0p[2 * rs + j], u0, a2);
-          if (h3) a3 = fma(row0p[3 * rs + j], u0, a3);
-        }
-      }
-      a0 = warp_sum(a0 + b0); a1 = warp_sum(a1 + b1); a2 = warp_sum(a2 + b2); a3 = warp_sum(a3 + b3);
-      if (lane == 0) {
-        y[r0] = a0;
-        if (h1) y[r0 + W] = a1;
-        if (h2) y[r0 + 2 * W] = a2;
-        if (h3) y[r0 + 3 * W] = a3;
-      }
-    }
-  };
+  auto local_matvec = [&](double* y) { pcg_local_matvec(Srows, n, R, u_full, y, wid, lane); };
   if (G > 1 && A.pipelined) {
     // ---- Pipelined PCG (Ghysels & Vanroose): the matrix-vector product of an iteration (n = S m, m = M^-1 w) does
     // not depend on that iteration's dot products, so the slab of m and the partial sums travel through ONE grid
@@ -736,6 +741,216 @@ __global__ void __launch_bounds__(kPcgMidThreads, 1) ba_pcg_mid_kernel(PcgArgs A
       if (h[k]) A.x[ri[k]] = (status == 1) ? 0.0 : x[k];
     if (lane == 0) { *A.status = status; *A.iters = it; }
   }
+}
+
+// Systems of 22 .. 64 free cameras (kPcgMidMax < n <= kPcgClusterMaxN): the pipelined iteration of ba_pcg_kernel on ONE
+// thread-block cluster of up to eight CTAs, with S in registers as in the single-CTA kernels.  A CTA owns a slab of
+// <= 48 rows (two per lane); its eight warps split the COLUMNS (S is symmetric: a warp loads consecutive addresses), so
+// a thread keeps 2 x <= 48 entries for the whole solve.  What the cooperative kernel exchanges through L2 behind a grid
+// barrier -- the CTA's rows of m = M^-1 w and its three partial dot products -- is stored straight into every CTA's
+// shared memory (DSMEM) ahead of one cluster barrier: an iteration has no global-memory round trip, nothing to gather,
+// and every CTA adds the same partials in the same order (identical decisions, deterministic).  Warp 0 owns the
+// vector recurrences of the slab; exchange buffers alternate with the iteration's parity (a CTA that has left the
+// barrier may publish the next iteration's values while a slower one still reads this iteration's).
+constexpr int kPcgClusterMaxCtas = 8;
+constexpr int kPcgClusterMaxRows = 48;                 // rows of S per CTA
+constexpr int kPcgClusterMaxCols = 48;                 // columns of S per warp
+constexpr int kPcgClusterMaxN = kPcgClusterMaxCtas * kPcgClusterMaxRows;
+constexpr int kPcgClusterWarps = kPcgThreads / 32;
+__host__ __device__ inline size_t pcg_cluster_smem_doubles(int n, int rows) {
+  return 2 * (size_t)n + 48 + 8 + 6 * kPcgClusterMaxRows + 10 * 64 + kPcgClusterWarps * 64 + (size_t)n * rows;   // + staging of the slab
+}
+
+__global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs A) {
+  extern __shared__ __align__(16) double sm[];
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  pdl_wait();
+  pdl_trigger();
+  if (A.done != nullptr && *A.done) return;          // (uniform over the cluster)
+  constexpr int W = kPcgClusterWarps, CM = kPcgClusterMaxCols;
+  const int n = A.n, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int g = (int)cluster.block_rank(), G = (int)cluster.num_blocks();
+  const int row0 = g * A.rows, R = max(0, min(A.rows, n - row0));
+  // identical layout in every CTA of the cluster (remote stores address it by offset)
+  double* u_buf = sm;                                 // [2][n]   exchange: m of every CTA
+  double* pch = sm + 2 * (size_t)n;                   // [2][3][8] exchange: partial dot products
+  double* failv = pch + 48;                           // [8]
+  double* minv = failv + 8;                           // [<= 8][36]
+  double* vec = minv + 6 * kPcgClusterMaxRows;        // [10][64]  the slab's vectors (warp 0)
+  double* part = vec + 10 * 64;                       // [W][64]   partial products of the warps
+  double *xl = vec, *rl = vec + 64, *pl = vec + 128, *sl = vec + 192, *ul = vec + 256, *wl = vec + 320, *ml = vec + 384,
+         *zl = vec + 448, *ql = vec + 512;
+  double* stage = part + W * 64;                      // [n][rows]  columns row0 .. of S, until they are in registers
+  const int ia = lane, ib = lane + 32;                // this lane's rows of the slab
+  const bool ha = ia < R, hb = ib < R;
+  // The slab arrives by 16-byte asynchronous copies -- S is symmetric, so the CTA's rows are read as a column slab:
+  // R consecutive doubles of every row j -- while warp 0 inverts the diagonal blocks.  (Loading the registers straight
+  // from global memory, 96 eight-byte loads per thread, cost 2-4 us per solve.)
+  {
+    const int per_row = R / 2;                        // (row0, R and n are even: every piece is 16-byte aligned)
+    const int cnt = n * per_row;
+    for (int i = tid; i < cnt; i += kPcgThreads) {
+      const int j = i / per_row, k = i - j * per_row;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stage + (size_t)j * A.rows + 2 * k)),
+                   "l"(A.S + (size_t)j * n + row0 + 2 * k) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  // block-Jacobi preconditioner: the local diagonal 6x6 blocks, straight from global memory
+  int fail = 0;
+  if (tid < R / 6) {
+    const int bi = tid;
+    double blk[36];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) blk[6 * i + j] = __ldcg(A.S + (size_t)(row0 + 6 * bi + i) * n + row0 + 6 * bi + j);
+    }
+    if (!spd6_inverse(blk)) fail = 1;
+#pragma unroll
+    for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  // this lane's entries of S for the warp's column range (after the inversion: its live set and these do not fit in
+  // the register file together)
+  const int cols = ((n + 2 * W - 1) / (2 * W)) * 2;  // <= 48, even
+  const int j0 = min(n, wid * cols), j1 = min(n, j0 + cols);
+  double sa[CM], sb[CM];
+#pragma unroll
+  for (int q = 0; q < CM; ++q) {
+    const int j = j0 + q;
+    sa[q] = (j < j1 && ha) ? stage[(size_t)j * A.rows + ia] : 0.0;
+    sb[q] = (j < j1 && hb) ? stage[(size_t)j * A.rows + ib] : 0.0;
+  }
+  if (wid == 0) {
+    xl[ia] = 0.0; xl[ib] = 0.0; pl[ia] = 0.0; pl[ib] = 0.0; sl[ia] = 0.0; sl[ib] = 0.0; zl[ia] = 0.0; zl[ib] = 0.0;
+    ql[ia] = 0.0; ql[ib] = 0.0; wl[ia] = 0.0; wl[ib] = 0.0; ul[ia] = 0.0; ul[ib] = 0.0; ml[ia] = 0.0; ml[ib] = 0.0;
+    rl[ia] = ha ? A.b[row0 + ia] : 0.0; rl[ib] = hb ? A.b[row0 + ib] : 0.0;
+  }
+  fail = __syncthreads_or(fail);
+  auto minv_row = [&](int i, const double* v) {       // (M^-1 v)_i for a local row i
+    const int bi = i / 6, ii = i - 6 * bi;
+    const double* m = minv + 36 * bi + 6 * ii;
+    const double* q = v + 6 * bi;
+    return (m[0] * q[0] + m[1] * q[1]) + (m[2] * q[2] + m[3] * q[3]) + (m[4] * q[4] + m[5] * q[5]);
+  };
+  auto push = [&](int buf, int i, double v) {         // value of local row i into every CTA's exchange buffer
+    double* dst = u_buf + (size_t)buf * n + row0 + i;
+#pragma unroll
+    for (int k = 0; k < kPcgClusterMaxCtas; ++k)
+      if (k < G) *cluster.map_shared_rank(dst, k) = v;
+  };
+  // this warp's part of (S v)[slab rows], v = exchange buffer `buf`, into part[wid]
+  auto partial_product = [&](int buf) {
+    const double* v = u_buf + (size_t)buf * n;
+    double wa0 = 0.0, wa1 = 0.0, wb0 = 0.0, wb1 = 0.0;
+    // eight columns per (uniform) step, their four 128-bit loads issued together: with a branch around every pair of
+    // columns each load's latency was exposed (80 cycles per pair, two warps per scheduler).  Entries of S beyond the
+    // column range are zero and the index is clamped, so a partly used step multiplies finite values by zero.
+#pragma unroll
+    for (int c = 0; c < CM / 8; ++c) {
+      if (8 * c < cols) {
+        double2 uu[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) uu[k] = *reinterpret_cast<const double2*>(v + min(j0 + 8 * c + 2 * k, n - 2));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int q = 8 * c + 2 * k;
+          wa0 = fma(sa[q], uu[k].x, wa0); wa1 = fma(sa[q + 1], uu[k].y, wa1);
+          wb0 = fma(sb[q], uu[k].x, wb0); wb1 = fma(sb[q + 1], uu[k].y, wb1);
+        }
+      }
+    }
+    part[wid * 64 + ia] = wa0 + wa1;
+    part[wid * 64 + ib] = wb0 + wb1;
+  };
+  auto summed_product = [&](int i) {                  // (after a block barrier) the eight partials of row i, in warp order
+    const double* q = part + i;
+    return ((q[0] + q[64]) + (q[128] + q[192])) + ((q[256] + q[320]) + (q[384] + q[448]));
+  };
+  if (wid == 0) {
+    if (ha) { const double u = minv_row(ia, rl); ul[ia] = u; push(1, ia, u); }   // (the initial exchange uses buffer 1)
+    if (hb) { const double u = minv_row(ib, rl); ul[ib] = u; push(1, ib, u); }
+    if (lane < G) *cluster.map_shared_rank(failv + g, lane) = fail ? 1.0 : 0.0;
+  }
+  cluster.sync();
+  bool any_fail = false;
+  for (int k = 0; k < G; ++k) any_fail = any_fail || failv[k] != 0.0;
+  int status = 2, it = 0;
+  double thresh = 0.0;
+  if (any_fail) {
+    status = 1;
+  } else {
+    partial_product(1);                                // w = S u
+    __syncthreads();
+    if (wid == 0) { wl[ia] = ha ? summed_product(ia) : 0.0; wl[ib] = hb ? summed_product(ib) : 0.0; }
+    __syncthreads();                                   // (part is rewritten after the next cluster barrier only; wl: warp 0)
+    double inv_gamma_old = 0.0, pap_old = 0.0;
+    for (it = 0; it <= A.max_iter; ++it) {
+      const int buf = it & 1;
+      if (wid == 0) {
+        __syncwarp();
+        double ma = 0.0, mb = 0.0;
+        if (ha) { ma = minv_row(ia, wl); push(buf, ia, ma); }                    // m = M^-1 w
+        if (hb) { mb = minv_row(ib, wl); push(buf, ib, mb); }
+        ml[ia] = ma; ml[ib] = mb;
+        const double ra = rl[ia], rb = rl[ib], ua = ul[ia], ub = ul[ib], wa = wl[ia], wb = wl[ib];
+        const double gam_p = warp_sum(fma(ra, ua, rb * ub)), del_p = warp_sum(fma(wa, ua, wb * ub)),
+                     rr_p = warp_sum(fma(ra, ra, rb * rb));
+        if (lane < 3 * G) {
+          const int k = lane / 3, which = lane - 3 * k;
+          const double v = which == 0 ? gam_p : (which == 1 ? del_p : rr_p);
+          *cluster.map_shared_rank(pch + buf * 24 + which * 8 + g, k) = v;
+        }
+      }
+      cluster.sync();
+      double gamma = 0.0, delta = 0.0, rr = 0.0;
+#pragma unroll
+      for (int k = 0; k < kPcgClusterMaxCtas; ++k)
+        if (k < G) { gamma += pch[buf * 24 + k]; delta += pch[buf * 24 + 8 + k]; rr += pch[buf * 24 + 16 + k]; }
+      if (it == 0) {
+        if (!(rr > 0.0)) { status = 0; break; }        // b == 0: x = 0
+        thresh = A.tol * A.tol * rr;
+      }
+      if (rr <= thresh && it > 0) { status = 0; break; }
+      if (it == A.max_iter) break;
+      partial_product(buf);                            // n = S m
+      double beta = 0.0, pap = delta;
+      if (it > 0) {
+        beta = gamma * inv_gamma_old;
+        pap = delta - beta * beta * pap_old;
+      }
+      if (!(pap > 1e-290) || !(pap < 1e290) || !(gamma > 1e-290) || !(gamma < 1e290)) status = 1;
+      const double alpha = gamma * fast_rcp(pap);
+      inv_gamma_old = fast_rcp(gamma); pap_old = pap;
+      __syncthreads();
+      if (status == 1) break;                          // (uniform: every thread of every CTA has the same scalars)
+      if (wid == 0) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int i = lane + 32 * k;
+          const double nv = (i < R) ? summed_product(i) : 0.0;
+          const double z = nv + beta * zl[i];
+          const double q = ml[i] + beta * ql[i];
+          const double sv = wl[i] + beta * sl[i];
+          const double pv = ul[i] + beta * pl[i];
+          zl[i] = z; ql[i] = q; sl[i] = sv; pl[i] = pv;
+          xl[i] += alpha * pv;
+          rl[i] -= alpha * sv;
+          ul[i] -= alpha * q;
+          wl[i] -= alpha * z;
+        }
+      }
+    }
+  }
+  if (wid == 0) {
+    if (ha) A.x[row0 + ia] = (status == 1) ? 0.0 : xl[ia];
+    if (hb) A.x[row0 + ib] = (status == 1) ? 0.0 : xl[ib];
+    if (g == 0 && lane == 0) { *A.status = status; *A.iters = it; }
+  }
+  cluster.sync();                                      // nobody leaves while its shared memory may still be written
 }
 
 }  // namespace vslam
