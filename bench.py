@@ -344,6 +344,29 @@ def ba_figures(torch):
                                                   "(vslam_ba_set_linear_solver(2)), same LM path"}
         eng.close()
         del flush
+    # windows between C3 and C4 (the sizes a growing map passes through): each takes a different PCG kernel
+    mids = {}
+    for cams, what in ((17, "single CTA, S in registers, four rows per lane (ba_pcg_mid_kernel)"),
+                       (45, "one thread-block cluster, exchange through DSMEM (ba_pcg_cluster_kernel)"),
+                       (100, "cooperative multi-CTA, one grid barrier per iteration (ba_pcg_kernel)")):
+        p = synthetic_ba(n_cams=cams, n_pts=4000 if cams < 100 else 20000, obs_per_pt=8.0, seed=3)
+        eng = BAEngine(p)
+        best, st = None, None
+        for rep in range(5):
+            eng.set_state(p.cams, p.pts, p.obs_uv, p.scale_meas, p.K)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            st = eng.optimize(10)
+            e1.record()
+            torch.cuda.synchronize()
+            if rep > 1:
+                best = e0.elapsed_time(e1) if best is None else min(best, e0.elapsed_time(e1))
+        mids["%d_cameras" % cams] = {"lm_iters_per_s": st["iterations"] / (best * 1e-3), "ms_per_optimize10": best,
+                                      "n_pts": p.n_pts, "n_obs": p.n_obs, "pcg_iterations": st["pcg_iterations"],
+                                      "reduced_system": eng.dims()["n"], "pcg": what}
+        eng.close()
+    out["windows"] = mids
     return out
 
 

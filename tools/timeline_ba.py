@@ -1,5 +1,5 @@
 """GPU timeline of BA LM iterations (kernel start / duration / gap to the previous kernel) through torch.profiler
-(CUPTI activity records cover the library's own launches too).  Usage: python tools/timeline_ba.py [c3|c4] [solver]"""
+(CUPTI activity records cover the library's own launches too).  Usage: python tools/timeline_ba.py [c3|c4|w17|w45] [solver]"""
 import sys
 
 import torch
@@ -11,7 +11,10 @@ from visual_slam_b200.ba_problem import synthetic_ba  # noqa: E402
 
 name = sys.argv[1] if len(sys.argv) > 1 else "c3"
 cfg = {"c3": dict(n_cams=10, n_pts=5000, obs_per_pt=6.0, seed=0),
-       "c4": dict(n_cams=200, n_pts=100000, obs_per_pt=10.0, seed=1)}[name]
+       "c4": dict(n_cams=200, n_pts=100000, obs_per_pt=10.0, seed=1),
+       # mid-size windows: the single-CTA four-rows-per-lane PCG, the cluster PCG
+       "w17": dict(n_cams=17, n_pts=4000, obs_per_pt=8.0, seed=3),
+       "w45": dict(n_cams=45, n_pts=4000, obs_per_pt=8.0, seed=3)}[name]
 p = synthetic_ba(**cfg)
 eng = BAEngine(p)
 if len(sys.argv) > 2:

@@ -121,7 +121,7 @@ __device__ __forceinline__ double block_sum1(double v, double* red) {
 
 // Three block sums with one barrier pair; every thread ends with the same, order-fixed sums.
 __device__ __forceinline__ void block_sum3(double& a, double& b, double& c, double* red3) {
-  a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+  warp_sum3(a, b, c);
   if ((threadIdx.x & 31) == 0) {
     const int w = threadIdx.x >> 5;
     red3[3 * w] = a; red3[3 * w + 1] = b; red3[3 * w + 2] = c;
@@ -194,7 +194,8 @@ __device__ __forceinline__ void pcg_local_matvec(const double* __restrict__ Srow
         if (h3) a3 = fma(row0p[3 * rs + j], u0, a3);
       }
     }
-    a0 = warp_sum(a0 + b0); a1 = warp_sum(a1 + b1); a2 = warp_sum(a2 + b2); a3 = warp_sum(a3 + b3);
+    a0 += b0; a1 += b1; a2 += b2; a3 += b3;
+    warp_sum4(a0, a1, a2, a3);
     if (lane == 0) {
       y[r0] = a0;
       if (h1) y[r0 + W] = a1;
@@ -319,7 +320,8 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
               xch[row0 + lane] = z;
             }
             const double rv = lane < R ? rl[lane] : 0.0, uv = lane < R ? ul[lane] : 0.0, wv = lane < R ? wl[lane] : 0.0;
-            const double gam_p = warp_sum(rv * uv), del_p = warp_sum(wv * uv), rr_p = warp_sum(rv * rv);
+            double gam_p = rv * uv, del_p = wv * uv, rr_p = rv * rv;
+            warp_sum3(gam_p, del_p, rr_p);
             if (lane == 0) { pch[g] = gam_p; pch[G + g] = del_p; pch[2 * G + g] = rr_p; }
           }
         } else {
@@ -571,9 +573,8 @@ __global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_kernel(PcgArgs 
       buf ^= 1;
       const double w0 = (pr[i0] + pr[64 + i0]) + (pr[128 + i0] + pr[192 + i0]);
       const double w1 = (pr[i1] + pr[64 + i1]) + (pr[128 + i1] + pr[192 + i1]);
-      const double gamma = warp_sum(r0 * u0 + r1 * u1);
-      const double delta = warp_sum(w0 * u0 + w1 * u1);
-      const double rr = warp_sum(r0 * r0 + r1 * r1);
+      double gamma = r0 * u0 + r1 * u1, delta = w0 * u0 + w1 * u1, rr = r0 * r0 + r1 * r1;
+      warp_sum3(gamma, delta, rr);
       if (it == 0) {
         if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
         thresh = A.tol * A.tol * rr;
@@ -709,9 +710,8 @@ __global__ void __launch_bounds__(kPcgMidThreads, 1) ba_pcg_mid_kernel(PcgArgs A
         w[k] = ((q[0] + q[NM]) + (q[2 * NM] + q[3 * NM])) + ((q[4 * NM] + q[5 * NM]) + (q[6 * NM] + q[7 * NM]));
         g_p = fma(r[k], u[k], g_p); d_p = fma(w[k], u[k], d_p); r_p = fma(r[k], r[k], r_p);
       }
-      const double gamma = warp_sum(g_p);
-      const double delta = warp_sum(d_p);
-      const double rr = warp_sum(r_p);
+      double gamma = g_p, delta = d_p, rr = r_p;
+      warp_sum3(gamma, delta, rr);
       if (it == 0) {
         if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
         thresh = A.tol * A.tol * rr;
@@ -758,7 +758,41 @@ constexpr int kPcgClusterMaxCols = 48;                 // columns of S per warp
 constexpr int kPcgClusterMaxN = kPcgClusterMaxCtas * kPcgClusterMaxRows;
 constexpr int kPcgClusterWarps = kPcgThreads / 32;
 __host__ __device__ inline size_t pcg_cluster_smem_doubles(int n, int rows) {
-  return 2 * (size_t)n + 48 + 8 + 6 * kPcgClusterMaxRows + 10 * 64 + kPcgClusterWarps * 64 + (size_t)n * rows;   // + staging of the slab
+  return 2 * (size_t)n + 48 + 8 + 2 + 6 * kPcgClusterMaxRows + 10 * 64 + kPcgClusterWarps * 64 + (size_t)n * rows;   // + staging of the slab
+}
+
+// DSMEM exchange of the cluster kernel: a value goes into a peer's shared memory by an asynchronous store that also
+// counts its bytes on the peer's mbarrier (st.async ... mbarrier::complete_tx::bytes); the peer waits on its OWN barrier
+// for the bytes of a phase.  No cluster-wide barrier per iteration: a cluster barrier cost ~600 cycles plus ~900 more
+// before the first shared-memory read behind its acquire returned (measured with clock64 stamps).
+__device__ __forceinline__ uint32_t cluster_map_u32(const void* local_smem, int rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(local_smem)), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_async_f64(uint32_t remote_addr, double v, uint32_t remote_bar) {
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(remote_addr),
+               "l"(__double_as_longlong(v)), "r"(remote_bar)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// (bounded: a protocol error must end as a reported breakdown, not as a hung device)
+__device__ __forceinline__ bool mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+  for (int k = 0; k < (1 << 24); ++k)
+    if (mbar_try_wait(bar, parity)) return true;
+  return false;
 }
 
 __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs A) {
@@ -776,7 +810,8 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
   double* u_buf = sm;                                 // [2][n]   exchange: m of every CTA
   double* pch = sm + 2 * (size_t)n;                   // [2][3][8] exchange: partial dot products
   double* failv = pch + 48;                           // [8]
-  double* minv = failv + 8;                           // [<= 8][36]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(failv + 8);   // [2] one mbarrier per exchange buffer
+  double* minv = failv + 10;                          // [<= 8][36]
   double* vec = minv + 6 * kPcgClusterMaxRows;        // [10][64]  the slab's vectors (warp 0)
   double* part = vec + 10 * 64;                       // [W][64]   partial products of the warps
   double *xl = vec, *rl = vec + 64, *pl = vec + 128, *sl = vec + 192, *ul = vec + 256, *wl = vec + 320, *ml = vec + 384,
@@ -829,6 +864,7 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
     ql[ia] = 0.0; ql[ib] = 0.0; wl[ia] = 0.0; wl[ib] = 0.0; ul[ia] = 0.0; ul[ib] = 0.0; ml[ia] = 0.0; ml[ib] = 0.0;
     rl[ia] = ha ? A.b[row0 + ia] : 0.0; rl[ib] = hb ? A.b[row0 + ib] : 0.0;
   }
+  if (tid == 0) { mbar_init(bars, 1); mbar_init(bars + 1, 1); mbar_fence_init(); }
   fail = __syncthreads_or(fail);
   auto minv_row = [&](int i, const double* v) {       // (M^-1 v)_i for a local row i
     const int bi = i / 6, ii = i - 6 * bi;
@@ -836,12 +872,19 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
     const double* q = v + 6 * bi;
     return (m[0] * q[0] + m[1] * q[1]) + (m[2] * q[2] + m[3] * q[3]) + (m[4] * q[4] + m[5] * q[5]);
   };
-  auto push = [&](int buf, int i, double v) {         // value of local row i into every CTA's exchange buffer
-    double* dst = u_buf + (size_t)buf * n + row0 + i;
+  // every CTA's window onto this shared memory layout (the mapping only adds a per-CTA base: one mapa per peer, once,
+  // instead of two in front of every store)
+  uint32_t rbase[kPcgClusterMaxCtas];
+#pragma unroll
+  for (int k = 0; k < kPcgClusterMaxCtas; ++k) rbase[k] = cluster_map_u32(sm, min(k, G - 1)) - smem_u32(sm);
+  auto push_to = [&](int buf, const double* dst, double v) {   // a value into every CTA's copy of *dst, counted on its barrier
+    const uint32_t a = smem_u32(dst), b = smem_u32(bars + buf);
 #pragma unroll
     for (int k = 0; k < kPcgClusterMaxCtas; ++k)
-      if (k < G) *cluster.map_shared_rank(dst, k) = v;
+      if (k < G) st_async_f64(a + rbase[k], v, b + rbase[k]);
   };
+  auto push = [&](int buf, int i, double v) { push_to(buf, u_buf + (size_t)buf * n + row0 + i, v); };
+  bool lost = false;                                  // a wait ran out: reported as a breakdown
   // this warp's part of (S v)[slab rows], v = exchange buffer `buf`, into part[wid]
   auto partial_product = [&](int buf) {
     const double* v = u_buf + (size_t)buf * n;
@@ -870,13 +913,15 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
     const double* q = part + i;
     return ((q[0] + q[64]) + (q[128] + q[192])) + ((q[256] + q[320]) + (q[384] + q[448]));
   };
+  cluster.sync();                                     // every CTA's barriers are initialised
   if (wid == 0) {
-    if (ha) { const double u = minv_row(ia, rl); ul[ia] = u; push(1, ia, u); }   // (the initial exchange uses buffer 1)
+    if (lane == 0) mbar_expect_tx(bars + 1, (uint32_t)(8 * (n + G)));            // (the initial exchange uses buffer 1)
+    if (ha) { const double u = minv_row(ia, rl); ul[ia] = u; push(1, ia, u); }
     if (hb) { const double u = minv_row(ib, rl); ul[ib] = u; push(1, ib, u); }
-    if (lane < G) *cluster.map_shared_rank(failv + g, lane) = fail ? 1.0 : 0.0;
+    if (lane == 0) push_to(1, failv + g, fail ? 1.0 : 0.0);
   }
-  cluster.sync();
-  bool any_fail = false;
+  lost = !mbar_wait_bounded(bars + 1, 0);
+  bool any_fail = lost;
   for (int k = 0; k < G; ++k) any_fail = any_fail || failv[k] != 0.0;
   int status = 2, it = 0;
   double thresh = 0.0;
@@ -892,24 +937,34 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
       const int buf = it & 1;
       if (wid == 0) {
         __syncwarp();
-        double ma = 0.0, mb = 0.0;
-        if (ha) { ma = minv_row(ia, wl); push(buf, ia, ma); }                    // m = M^-1 w
-        if (hb) { mb = minv_row(ib, wl); push(buf, ib, mb); }
+        if (lane == 0) mbar_expect_tx(bars + buf, (uint32_t)(8 * (n + 3 * G)));
+        const double ma = ha ? minv_row(ia, wl) : 0.0, mb = hb ? minv_row(ib, wl) : 0.0;   // m = M^-1 w
         ml[ia] = ma; ml[ib] = mb;
+        if (ha) push(buf, ia, ma);
+        if (hb) push(buf, ib, mb);
         const double ra = rl[ia], rb = rl[ib], ua = ul[ia], ub = ul[ib], wa = wl[ia], wb = wl[ib];
-        const double gam_p = warp_sum(fma(ra, ua, rb * ub)), del_p = warp_sum(fma(wa, ua, wb * ub)),
-                     rr_p = warp_sum(fma(ra, ra, rb * rb));
+        double gam_p = fma(ra, ua, rb * ub), del_p = fma(wa, ua, wb * ub), rr_p = fma(ra, ra, rb * rb);
+        warp_sum3(gam_p, del_p, rr_p);
         if (lane < 3 * G) {
           const int k = lane / 3, which = lane - 3 * k;
           const double v = which == 0 ? gam_p : (which == 1 ? del_p : rr_p);
-          *cluster.map_shared_rank(pch + buf * 24 + which * 8 + g, k) = v;
+          const uint32_t rb = cluster_map_u32(sm, k) - smem_u32(sm);
+          st_async_f64(smem_u32(pch + buf * 24 + which * 8 + g) + rb, v, smem_u32(bars + buf) + rb);
         }
       }
-      cluster.sync();
+      // phase of this buffer's barrier: buffer 1 was used once by the initial exchange
+      if (!mbar_wait_bounded(bars + buf, (uint32_t)(((it + buf) >> 1) & 1))) { lost = true; status = 1; break; }
+      // (all 24 loads first, whatever G: with a branch per CTA the loop was eight load -> add round trips)
       double gamma = 0.0, delta = 0.0, rr = 0.0;
+      {
+        double pv[24];
 #pragma unroll
-      for (int k = 0; k < kPcgClusterMaxCtas; ++k)
-        if (k < G) { gamma += pch[buf * 24 + k]; delta += pch[buf * 24 + 8 + k]; rr += pch[buf * 24 + 16 + k]; }
+        for (int k = 0; k < 24; ++k) pv[k] = pch[buf * 24 + k];
+#pragma unroll
+        for (int k = 0; k < kPcgClusterMaxCtas; ++k) {
+          gamma += k < G ? pv[k] : 0.0; delta += k < G ? pv[8 + k] : 0.0; rr += k < G ? pv[16 + k] : 0.0;
+        }
+      }
       if (it == 0) {
         if (!(rr > 0.0)) { status = 0; break; }        // b == 0: x = 0
         thresh = A.tol * A.tol * rr;
@@ -929,18 +984,28 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
       if (status == 1) break;                          // (uniform: every thread of every CTA has the same scalars)
       if (wid == 0) {
 #pragma unroll
+        // (every load of both rows ahead of the first store: the arrays may alias as far as the compiler knows, and
+        //  load -> FMA -> store -> load ... chains made this 640 cycles)
+        double nv[2], zo[2], mo[2], qo[2], wo[2], so[2], uo[2], po[2], xo[2], ro[2];
+#pragma unroll
         for (int k = 0; k < 2; ++k) {
           const int i = lane + 32 * k;
-          const double nv = (i < R) ? summed_product(i) : 0.0;
-          const double z = nv + beta * zl[i];
-          const double q = ml[i] + beta * ql[i];
-          const double sv = wl[i] + beta * sl[i];
-          const double pv = ul[i] + beta * pl[i];
+          nv[k] = (i < R) ? summed_product(i) : 0.0;
+          zo[k] = zl[i]; mo[k] = ml[i]; qo[k] = ql[i]; wo[k] = wl[i]; so[k] = sl[i]; uo[k] = ul[i]; po[k] = pl[i];
+          xo[k] = xl[i]; ro[k] = rl[i];
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int i = lane + 32 * k;
+          const double z = nv[k] + beta * zo[k];
+          const double q = mo[k] + beta * qo[k];
+          const double sv = wo[k] + beta * so[k];
+          const double pv = uo[k] + beta * po[k];
           zl[i] = z; ql[i] = q; sl[i] = sv; pl[i] = pv;
-          xl[i] += alpha * pv;
-          rl[i] -= alpha * sv;
-          ul[i] -= alpha * q;
-          wl[i] -= alpha * z;
+          xl[i] = xo[k] + alpha * pv;
+          rl[i] = ro[k] - alpha * sv;
+          ul[i] = uo[k] - alpha * q;
+          wl[i] = wo[k] - alpha * z;
         }
       }
     }

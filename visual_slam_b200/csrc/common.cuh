@@ -76,6 +76,25 @@ __device__ __forceinline__ double warp_sum(double v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// Several sums at once, stage by stage: shuffles keep their program order, so back-to-back warp_sum() calls run one
+// after the other (measured: 217 cycles each); interleaved, the shuffles of a stage are in flight together.  Each
+// value sees the same additions in the same order as in warp_sum().
+__device__ __forceinline__ void warp_sum3(double& a, double& b, double& c) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ta = __shfl_xor_sync(0xffffffffu, a, o), tb = __shfl_xor_sync(0xffffffffu, b, o),
+                 tc = __shfl_xor_sync(0xffffffffu, c, o);
+    a += ta; b += tb; c += tc;
+  }
+}
+__device__ __forceinline__ void warp_sum4(double& a, double& b, double& c, double& d) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ta = __shfl_xor_sync(0xffffffffu, a, o), tb = __shfl_xor_sync(0xffffffffu, b, o),
+                 tc = __shfl_xor_sync(0xffffffffu, c, o), td = __shfl_xor_sync(0xffffffffu, d, o);
+    a += ta; b += tb; c += tc; d += td;
+  }
+}
 __device__ __forceinline__ int warp_sum_i(int v) { return __reduce_add_sync(0xffffffffu, v); }
 
 }  // namespace vslam
