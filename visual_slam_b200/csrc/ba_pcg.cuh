@@ -350,15 +350,16 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
             }
           }
           if (G <= 160) {                                  // (one CTA per SM at most: always, on 148 SMs)
+            double sk[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
-              double sk = 0.0;
+              sk[k] = 0.0;
 #pragma unroll
               for (int q = 0; q < 5; ++q)
-                if (tid + 32 * q < G) sk += v[k][q];
-              sk = warp_sum(sk);
-              if (tid == 0) s_sum[k] = sk;
+                if (tid + 32 * q < G) sk[k] += v[k][q];
             }
+            warp_sum3(sk[0], sk[1], sk[2]);                // (the three butterflies stage by stage, not one after the other)
+            if (tid == 0) { s_sum[0] = sk[0]; s_sum[1] = sk[1]; s_sum[2] = sk[2]; }
           } else {                                         // (more CTAs than three per lane: the general form)
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
@@ -393,15 +394,18 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
         __syncthreads();
         if (!warp_tail || wid == 0) {
           for (int i = tid; i < R; i += kPcgThreads) {
-            const double z = nl[i] + beta * zl[i];
-            const double q = ml[i] + beta * ql[i];
-            const double sv = wl[i] + beta * sl[i];
-            const double pv = ul[i] + beta * pl[i];
+            // (loads ahead of the stores: the arrays may alias as far as the compiler knows)
+            const double nv = nl[i], zo = zl[i], mo = ml[i], qo = ql[i], wo = wl[i], so = sl[i], uo = ul[i], po = pl[i],
+                         xo = xl[i], ro = rl[i];
+            const double z = nv + beta * zo;
+            const double q = mo + beta * qo;
+            const double sv = wo + beta * so;
+            const double pv = uo + beta * po;
             zl[i] = z; ql[i] = q; sl[i] = sv; pl[i] = pv;
-            xl[i] += alpha * pv;
-            rl[i] -= alpha * sv;
-            ul[i] -= alpha * q;
-            wl[i] -= alpha * z;
+            xl[i] = xo + alpha * pv;
+            rl[i] = ro - alpha * sv;
+            ul[i] = uo - alpha * q;
+            wl[i] = wo - alpha * z;
           }
         }
         if (warp_tail) __syncwarp(); else __syncthreads();
