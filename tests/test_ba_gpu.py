@@ -343,7 +343,10 @@ def test_batch_of_independent_windows_equals_one_by_one():
     the other, different problems and sizes in one batch, including one whose steps get rejected."""
     from visual_slam_b200.ba import optimize_batch
     probs = [synthetic_ba(6, 400, 4.0, seed=20 + i) for i in range(5)] + [synthetic_ba(10, 1500, 6.0, seed=3),
-                                                                          synthetic_ba(4, 80, 3.0, seed=11, pose_noise=(8.0, 0.4))]
+                                                                          synthetic_ba(4, 80, 3.0, seed=11, pose_noise=(8.0, 0.4)),
+                                                                          # the four-rows-per-lane and the cluster PCG
+                                                                          synthetic_ba(14, 600, 5.0, seed=41),
+                                                                          synthetic_ba(24, 800, 6.0, seed=42)]
     single = []
     for p in probs:
         e = BAEngine(p); single.append((e.optimize(10), [x.cpu().numpy() for x in e.get_state()])); e.close()

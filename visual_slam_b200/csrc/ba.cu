@@ -624,13 +624,29 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
     B.pcg_cluster = 0;
     if (cluster_ok && B.n > kPcgMidMax && B.n <= kPcgClusterMaxN) {
       const int t = (nb + kPcgClusterMaxCtas - 1) / kPcgClusterMaxCtas;
-      if (6 * t <= kPcgClusterMaxRows && pcg_cluster_smem_doubles(B.n, 6 * t) * sizeof(double) <= budget) { best = t; B.pcg_cluster = 1; }
+      const size_t need = pcg_cluster_smem_doubles(B.n, 6 * t) * sizeof(double);
+      if (6 * t <= kPcgClusterMaxRows && need <= budget && pcg_cluster_kernel_allow_max_smem() == cudaSuccess) {
+        // the device must be able to place such a cluster (partitioned or partly busy devices may not): else the
+        // cooperative kernel takes the system
+        cudaLaunchConfig_t cfg = {};
+        const int Gc = (nb + t - 1) / t;
+        cfg.gridDim = dim3(Gc); cfg.blockDim = dim3(kPcgThreads); cfg.dynamicSmemBytes = need;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)Gc; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        int n_clusters = 0;
+        if (cudaOccupancyMaxActiveClusters(&n_clusters, ba_pcg_cluster_kernel, &cfg) == cudaSuccess && n_clusters >= 1) {
+          best = t; B.pcg_cluster = 1;
+        } else {
+          cudaGetLastError();
+        }
+      }
     }
     B.pcg_slab = smem_for(6 * best, true) <= budget ? 1 : 0;
     B.pcg_rows = 6 * std::max(best, 1);
     B.pcg_G = std::max(1, (nb + best - 1) / std::max(best, 1));
     B.pcg_smem = B.pcg_cluster ? pcg_cluster_smem_doubles(B.n, B.pcg_rows) * sizeof(double) : smem_for(B.pcg_rows, B.pcg_slab);
-    if (B.pcg_cluster) BA_TRY(pcg_cluster_kernel_allow_max_smem());
     if (B.pcg_smem > budget) return VSLAM_ERR_BAD_ARG;
     BA_TRY(pcg_kernel_allow_max_smem());
     BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
