@@ -939,21 +939,34 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
     double inv_gamma_old = 0.0, pap_old = 0.0;
     for (it = 0; it <= A.max_iter; ++it) {
       const int buf = it & 1;
-      if (wid == 0) {
-        __syncwarp();
-        if (lane == 0) mbar_expect_tx(bars + buf, (uint32_t)(8 * (n + 3 * G)));
-        const double ma = ha ? minv_row(ia, wl) : 0.0, mb = hb ? minv_row(ib, wl) : 0.0;   // m = M^-1 w
-        ml[ia] = ma; ml[ib] = mb;
-        if (ha) push(buf, ia, ma);
-        if (hb) push(buf, ib, mb);
-        const double ra = rl[ia], rb = rl[ib], ua = ul[ia], ub = ul[ib], wa = wl[ia], wb = wl[ib];
-        double gam_p = fma(ra, ua, rb * ub), del_p = fma(wa, ua, wb * ub), rr_p = fma(ra, ra, rb * rb);
-        warp_sum3(gam_p, del_p, rr_p);
-        if (lane < 3 * G) {
-          const int k = lane / 3, which = lane - 3 * k;
-          const double v = which == 0 ? gam_p : (which == 1 ? del_p : rr_p);
-          const uint32_t rb = cluster_map_u32(sm, k) - smem_u32(sm);
-          st_async_f64(smem_u32(pch + buf * 24 + which * 8 + g) + rb, v, smem_u32(bars + buf) + rb);
+      // The serial part of an iteration on FIVE warps (every dependent latency of it is exposed, so it is spread, not
+      // shortened): warp 1 forms the three dot products; warps 0 / 3 form m for the lane rows 0..31 and publish it to
+      // the peers 0..3 / 4..7, warps 2 / 4 do the same for the rows 32..47.  All of them read what the recurrences of
+      // the previous iteration (warps 0 and 2, below) left in shared memory: a 160-thread named barrier orders that.
+      if (wid <= 4) {
+        asm volatile("bar.sync 1, 160;" ::: "memory");
+        if (wid == 1) {
+          const double ra = rl[ia], rb = rl[ib], ua = ul[ia], ub = ul[ib], wa = wl[ia], wb = wl[ib];
+          double gam_p = fma(ra, ua, rb * ub), del_p = fma(wa, ua, wb * ub), rr_p = fma(ra, ra, rb * rb);
+          warp_sum3(gam_p, del_p, rr_p);
+          if (lane < 3 * G) {
+            const int k = lane / 3, which = lane - 3 * k;
+            const double v = which == 0 ? gam_p : (which == 1 ? del_p : rr_p);
+            const uint32_t rk = cluster_map_u32(sm, k) - smem_u32(sm);
+            st_async_f64(smem_u32(pch + buf * 24 + which * 8 + g) + rk, v, smem_u32(bars + buf) + rk);
+          }
+        } else {
+          if (wid == 0 && lane == 0) mbar_expect_tx(bars + buf, (uint32_t)(8 * (n + 3 * G)));
+          const int i = (wid == 2 || wid == 4) ? ib : ia;
+          const int k0 = wid >= 3 ? 4 : 0;                 // first peer of this warp's half
+          if (i < R && k0 < G) {
+            const double m = minv_row(i, wl);              // m = M^-1 w
+            if (wid <= 2) ml[i] = m;
+            const uint32_t a = smem_u32(u_buf + (size_t)buf * n + row0 + i), bb = smem_u32(bars + buf);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              if (k0 + k < G) st_async_f64(a + rbase[k0 + k], m, bb + rbase[k0 + k]);
+          }
         }
       }
       // phase of this buffer's barrier: buffer 1 was used once by the initial exchange
@@ -986,30 +999,23 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
       inv_gamma_old = fast_rcp(gamma); pap_old = pap;
       __syncthreads();
       if (status == 1) break;                          // (uniform: every thread of every CTA has the same scalars)
-      if (wid == 0) {
-#pragma unroll
-        // (every load of both rows ahead of the first store: the arrays may alias as far as the compiler knows, and
+      if (wid == 0 || wid == 2) {                      // the recurrences: warp 0 rows 0..31, warp 2 rows 32..47
+        // (every load ahead of the first store: the arrays may alias as far as the compiler knows, and
         //  load -> FMA -> store -> load ... chains made this 640 cycles)
-        double nv[2], zo[2], mo[2], qo[2], wo[2], so[2], uo[2], po[2], xo[2], ro[2];
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-          const int i = lane + 32 * k;
-          nv[k] = (i < R) ? summed_product(i) : 0.0;
-          zo[k] = zl[i]; mo[k] = ml[i]; qo[k] = ql[i]; wo[k] = wl[i]; so[k] = sl[i]; uo[k] = ul[i]; po[k] = pl[i];
-          xo[k] = xl[i]; ro[k] = rl[i];
-        }
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-          const int i = lane + 32 * k;
-          const double z = nv[k] + beta * zo[k];
-          const double q = mo[k] + beta * qo[k];
-          const double sv = wo[k] + beta * so[k];
-          const double pv = uo[k] + beta * po[k];
+        const int i = wid == 0 ? ia : ib;
+        if (i < R) {
+          const double nv = summed_product(i);
+          const double zo = zl[i], mo = ml[i], qo = ql[i], wo = wl[i], so = sl[i], uo = ul[i], po = pl[i], xo = xl[i],
+                       ro = rl[i];
+          const double z = nv + beta * zo;
+          const double q = mo + beta * qo;
+          const double sv = wo + beta * so;
+          const double pv = uo + beta * po;
           zl[i] = z; ql[i] = q; sl[i] = sv; pl[i] = pv;
-          xl[i] = xo[k] + alpha * pv;
-          rl[i] = ro[k] - alpha * sv;
-          ul[i] = uo[k] - alpha * q;
-          wl[i] = wo[k] - alpha * z;
+          xl[i] = xo + alpha * pv;
+          rl[i] = ro - alpha * sv;
+          ul[i] = uo - alpha * q;
+          wl[i] = wo - alpha * z;
         }
       }
     }
