@@ -310,7 +310,9 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
         double* xch = A.p_glob + (size_t)(it & 1) * n;
         double* pch = A.part + (size_t)(it & 1) * 3 * G;
         if (warp_tail) {
+          // (two warps, as in the cluster kernel: the dot products do not wait for M^-1 w and its publication)
           if (wid == 0) {
+            asm volatile("bar.sync 1, 64;" ::: "memory");
             if (lane < R) {
               const int bi = lane / 6, ii = lane % 6;
               double z = 0.0;
@@ -319,6 +321,8 @@ __global__ void __launch_bounds__(kPcgThreads) ba_pcg_kernel(PcgArgs A) {
               ml[lane] = z;
               xch[row0 + lane] = z;
             }
+          } else if (wid == 1) {
+            asm volatile("bar.sync 1, 64;" ::: "memory");
             const double rv = lane < R ? rl[lane] : 0.0, uv = lane < R ? ul[lane] : 0.0, wv = lane < R ? wl[lane] : 0.0;
             double gam_p = rv * uv, del_p = wv * uv, rr_p = rv * rv;
             warp_sum3(gam_p, del_p, rr_p);
