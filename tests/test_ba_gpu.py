@@ -78,7 +78,10 @@ def test_linearize_and_one_trial_match_restatement(args, schur):
                                   # 11 / 21 free cameras: the four-rows-per-lane single-CTA PCG; 26: the multi-CTA one
                                   dict(n_cams=12, n_pts=900, obs_per_pt=5.0, seed=31),
                                   dict(n_cams=22, n_pts=1200, obs_per_pt=6.0, seed=32),
-                                  dict(n_cams=27, n_pts=1200, obs_per_pt=6.0, seed=33)])
+                                  dict(n_cams=27, n_pts=1200, obs_per_pt=6.0, seed=33),
+                                  # 69 free cameras: the sixteen-CTA cluster PCG (or the cooperative one where the
+                                  # device does not place such a cluster)
+                                  dict(n_cams=70, n_pts=1500, obs_per_pt=6.0, seed=34)])
 def test_ten_lm_iterations_match_restatement(args):
     """north_star tolerance: final cost within 1e-4 relative, RMS reprojection within 1e-3 px."""
     p = synthetic_ba(**args)

@@ -222,16 +222,27 @@ static cudaError_t pcg_kernel_allow_max_smem() {
   return cudaFuncSetAttribute(ba_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               max_smem - (int)fa.sharedSizeBytes);   // (static + dynamic share the opt-in limit)
 }
-static cudaError_t pcg_cluster_kernel_allow_max_smem() {
+// The two instances of the cluster PCG kernel: 1 = <2, 48, 8> (n <= 384), 2 = <1, 64, 16> (n <= 480, non-portable cluster size)
+using PcgClusterFn = void (*)(PcgArgs);
+static PcgClusterFn pcg_cluster_fn(int kind) {
+  return kind == 2 ? ba_pcg_cluster_kernel<1, kPcgCluster16MaxCols, kPcgCluster16MaxCtas>
+                   : ba_pcg_cluster_kernel<2, kPcgClusterMaxCols, kPcgClusterMaxCtas>;
+}
+static int pcg_cluster_max_ctas(int kind) { return kind == 2 ? kPcgCluster16MaxCtas : kPcgClusterMaxCtas; }
+static cudaError_t pcg_cluster_kernel_allow_max_smem(int kind) {
   int max_smem = 0, dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   e = cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   if (e != cudaSuccess) return e;
   cudaFuncAttributes fa{};
-  e = cudaFuncGetAttributes(&fa, ba_pcg_cluster_kernel);
+  e = cudaFuncGetAttributes(&fa, pcg_cluster_fn(kind));
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(ba_pcg_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  if (kind == 2) {
+    e = cudaFuncSetAttribute(pcg_cluster_fn(kind), cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaFuncSetAttribute(pcg_cluster_fn(kind), cudaFuncAttributeMaxDynamicSharedMemorySize,
                               max_smem - (int)fa.sharedSizeBytes);
 }
 static size_t pcg_small_smem(int n) { return sizeof(double) * ((size_t)n * n + 6 * (size_t)n + 16 * 64); }   // S, M^-1, r/u copies, partials
@@ -619,34 +630,43 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
       const int t = std::atoi(e);
       if (t >= bpc && t <= nb && smem_for(6 * t, true) <= budget) best = t;
     }
-    // 22 .. 64 free cameras: one thread-block cluster (ba_pcg_cluster_kernel), exchange through DSMEM
-    static const bool cluster_ok = [] { const char* e = getenv("VSLAM_BA_PCG_CLUSTER"); return !(e && atoi(e) == 0); }();
+    // 22 .. 64 free cameras: one thread-block cluster of <= 8 CTAs (ba_pcg_cluster_kernel), exchange through DSMEM;
+    // 65 .. 80: sixteen CTAs where the device places such a cluster
+    static const int cluster_env = [] { const char* e = getenv("VSLAM_BA_PCG_CLUSTER"); return e ? atoi(e) : -1; }();
     B.pcg_cluster = 0;
-    if (cluster_ok && B.n > kPcgMidMax && B.n <= kPcgClusterMaxN) {
-      const int t = (nb + kPcgClusterMaxCtas - 1) / kPcgClusterMaxCtas;
-      const size_t need = pcg_cluster_smem_doubles(B.n, 6 * t) * sizeof(double);
-      if (6 * t <= kPcgClusterMaxRows && need <= budget && pcg_cluster_kernel_allow_max_smem() == cudaSuccess) {
-        // the device must be able to place such a cluster (partitioned or partly busy devices may not): else the
-        // cooperative kernel takes the system
-        cudaLaunchConfig_t cfg = {};
-        const int Gc = (nb + t - 1) / t;
-        cfg.gridDim = dim3(Gc); cfg.blockDim = dim3(kPcgThreads); cfg.dynamicSmemBytes = need;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = (unsigned)Gc; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr; cfg.numAttrs = 1;
-        int n_clusters = 0;
-        if (cudaOccupancyMaxActiveClusters(&n_clusters, ba_pcg_cluster_kernel, &cfg) == cudaSuccess && n_clusters >= 1) {
-          best = t; B.pcg_cluster = 1;
-        } else {
-          cudaGetLastError();
-        }
+    // (measured: up to 40 free cameras, where eight CTAs need one row per lane, the two are level or <2, 48, 8> ahead;
+    //  beyond, sixteen CTAs of one row per lane win: 44 cameras 10.5k -> 11.3k LM it/s, 59 cameras 9.9k -> 10.4k)
+    const int first_kind = nb > 40 ? 2 : 1;
+    for (int pass = 0; pass < 2 && !B.pcg_cluster; ++pass) {
+      const int kind = pass == 0 ? first_kind : 3 - first_kind;
+      if (cluster_env == 0 || (cluster_env > 0 && cluster_env != kind)) continue;
+      const int max_ctas = pcg_cluster_max_ctas(kind);
+      const int max_rows = kind == 2 ? kPcgCluster16MaxRows : kPcgClusterMaxRows;
+      const int max_n = kind == 2 ? kPcgCluster16MaxN : kPcgClusterMaxN;
+      if (B.n <= kPcgMidMax || B.n > max_n) continue;
+      const int t = (nb + max_ctas - 1) / max_ctas;
+      const size_t need = pcg_cluster_smem_doubles(B.n, 6 * t, max_ctas) * sizeof(double);
+      if (6 * t > max_rows || need > budget || pcg_cluster_kernel_allow_max_smem(kind) != cudaSuccess) { cudaGetLastError(); continue; }
+      // the device must be able to place such a cluster (partitioned or partly busy devices may not): else the
+      // cooperative kernel takes the system
+      cudaLaunchConfig_t cfg = {};
+      const int Gc = (nb + t - 1) / t;
+      cfg.gridDim = dim3(Gc); cfg.blockDim = dim3(kPcgThreads); cfg.dynamicSmemBytes = need;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = (unsigned)Gc; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      int n_clusters = 0;
+      if (cudaOccupancyMaxActiveClusters(&n_clusters, pcg_cluster_fn(kind), &cfg) == cudaSuccess && n_clusters >= 1) {
+        best = t; B.pcg_cluster = kind;
+      } else {
+        cudaGetLastError();
       }
     }
     B.pcg_slab = smem_for(6 * best, true) <= budget ? 1 : 0;
     B.pcg_rows = 6 * std::max(best, 1);
     B.pcg_G = std::max(1, (nb + best - 1) / std::max(best, 1));
-    B.pcg_smem = B.pcg_cluster ? pcg_cluster_smem_doubles(B.n, B.pcg_rows) * sizeof(double) : smem_for(B.pcg_rows, B.pcg_slab);
+    B.pcg_smem = B.pcg_cluster ? pcg_cluster_smem_doubles(B.n, B.pcg_rows, pcg_cluster_max_ctas(B.pcg_cluster)) * sizeof(double) : smem_for(B.pcg_rows, B.pcg_slab);
     if (B.pcg_smem > budget) return VSLAM_ERR_BAD_ARG;
     BA_TRY(pcg_kernel_allow_max_smem());
     BA_TRY(cudaFuncSetAttribute(ba_solve_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -782,7 +802,7 @@ static int enqueue_trial(BA& B, cudaStream_t st, bool speculative = false) {
       cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
       cudaStreamIsCapturing(st, &cap);
       cfg.attrs = attr; cfg.numAttrs = (use_pdl() && cap == cudaStreamCaptureStatusNone) ? 2 : 1;
-      BA_TRY(cudaLaunchKernelEx(&cfg, ba_pcg_cluster_kernel, A));
+      BA_TRY(cudaLaunchKernelEx(&cfg, pcg_cluster_fn(B.pcg_cluster), A));
     } else if (B.pcg_G > 1) {
       BA_TRY(cudaLaunchCooperativeKernel((void*)ba_pcg_kernel, dim3(B.pcg_G), dim3(kPcgThreads), args,
                                          B.pcg_smem, st));

@@ -760,13 +760,18 @@ __global__ void __launch_bounds__(kPcgMidThreads, 1) ba_pcg_mid_kernel(PcgArgs A
 // and every CTA adds the same partials in the same order (identical decisions, deterministic).  Warp 0 owns the
 // vector recurrences of the slab; exchange buffers alternate with the iteration's parity (a CTA that has left the
 // barrier may publish the next iteration's values while a slower one still reads this iteration's).
-constexpr int kPcgClusterMaxCtas = 8;
+constexpr int kPcgClusterMaxCtas = 8;                  // <2, 48, 8>: two rows per lane, portable cluster size
 constexpr int kPcgClusterMaxRows = 48;                 // rows of S per CTA
 constexpr int kPcgClusterMaxCols = 48;                 // columns of S per warp
 constexpr int kPcgClusterMaxN = kPcgClusterMaxCtas * kPcgClusterMaxRows;
+constexpr int kPcgCluster16MaxCtas = 16;               // <1, 64, 16>: one row per lane, sixteen CTAs
+constexpr int kPcgCluster16MaxRows = 30;
+constexpr int kPcgCluster16MaxCols = 64;
+constexpr int kPcgCluster16MaxN = kPcgCluster16MaxCtas * kPcgCluster16MaxRows;
 constexpr int kPcgClusterWarps = kPcgThreads / 32;
-__host__ __device__ inline size_t pcg_cluster_smem_doubles(int n, int rows) {
-  return 2 * (size_t)n + 48 + 8 + 2 + 6 * kPcgClusterMaxRows + 10 * 64 + kPcgClusterWarps * 64 + (size_t)n * rows;   // + staging of the slab
+__host__ __device__ inline size_t pcg_cluster_smem_doubles(int n, int rows, int max_ctas) {
+  return 2 * (size_t)n + 7 * (size_t)max_ctas + 2 + 6 * kPcgClusterMaxRows + 10 * 64 + kPcgClusterWarps * 64 +
+         (size_t)n * rows;   // (the last term: staging of the slab)
 }
 
 // DSMEM exchange of the cluster kernel: a value goes into a peer's shared memory by an asynchronous store that also
@@ -803,6 +808,9 @@ __device__ __forceinline__ bool mbar_wait_bounded(uint64_t* bar, uint32_t parity
   return false;
 }
 
+// NRL rows per lane, CM columns per warp at most, MAXG CTAs per cluster at most: <2, 48, 8> for n <= 384 (portable cluster
+// size), <1, 64, 16> for n <= 480 (sixteen CTAs of <= 30 rows: a non-portable cluster size, used where the device places it).
+template <int NRL, int CM, int MAXG>
 __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs A) {
   extern __shared__ __align__(16) double sm[];
   namespace cg = cooperative_groups;
@@ -810,23 +818,23 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
   pdl_wait();
   pdl_trigger();
   if (A.done != nullptr && *A.done) return;          // (uniform over the cluster)
-  constexpr int W = kPcgClusterWarps, CM = kPcgClusterMaxCols;
+  constexpr int W = kPcgClusterWarps;
   const int n = A.n, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int g = (int)cluster.block_rank(), G = (int)cluster.num_blocks();
   const int row0 = g * A.rows, R = max(0, min(A.rows, n - row0));
   // identical layout in every CTA of the cluster (remote stores address it by offset)
   double* u_buf = sm;                                 // [2][n]   exchange: m of every CTA
-  double* pch = sm + 2 * (size_t)n;                   // [2][3][8] exchange: partial dot products
-  double* failv = pch + 48;                           // [8]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(failv + 8);   // [2] one mbarrier per exchange buffer
-  double* minv = failv + 10;                          // [<= 8][36]
+  double* pch = sm + 2 * (size_t)n;                   // [2][3][MAXG] exchange: partial dot products
+  double* failv = pch + 6 * MAXG;                     // [MAXG]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(failv + MAXG);   // [2] one mbarrier per exchange buffer
+  double* minv = failv + MAXG + 2;                    // [<= 8][36]
   double* vec = minv + 6 * kPcgClusterMaxRows;        // [10][64]  the slab's vectors (warp 0)
   double* part = vec + 10 * 64;                       // [W][64]   partial products of the warps
   double *xl = vec, *rl = vec + 64, *pl = vec + 128, *sl = vec + 192, *ul = vec + 256, *wl = vec + 320, *ml = vec + 384,
          *zl = vec + 448, *ql = vec + 512;
   double* stage = part + W * 64;                      // [n][rows]  columns row0 .. of S, until they are in registers
   const int ia = lane, ib = lane + 32;                // this lane's rows of the slab
-  const bool ha = ia < R, hb = ib < R;
+  const bool ha = ia < R, hb = NRL == 2 && ib < R;
   // The slab arrives by 16-byte asynchronous copies -- S is symmetric, so the CTA's rows are read as a column slab:
   // R consecutive doubles of every row j -- while warp 0 inverts the diagonal blocks.  (Loading the registers straight
   // from global memory, 96 eight-byte loads per thread, cost 2-4 us per solve.)
@@ -860,12 +868,12 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
   // the register file together)
   const int cols = ((n + 2 * W - 1) / (2 * W)) * 2;  // <= 48, even
   const int j0 = min(n, wid * cols), j1 = min(n, j0 + cols);
-  double sa[CM], sb[CM];
+  double sa[CM], sb[NRL == 2 ? CM : 2];
 #pragma unroll
   for (int q = 0; q < CM; ++q) {
     const int j = j0 + q;
     sa[q] = (j < j1 && ha) ? stage[(size_t)j * A.rows + ia] : 0.0;
-    sb[q] = (j < j1 && hb) ? stage[(size_t)j * A.rows + ib] : 0.0;
+    if constexpr (NRL == 2) sb[q] = (j < j1 && hb) ? stage[(size_t)j * A.rows + ib] : 0.0;
   }
   if (wid == 0) {
     xl[ia] = 0.0; xl[ib] = 0.0; pl[ia] = 0.0; pl[ib] = 0.0; sl[ia] = 0.0; sl[ib] = 0.0; zl[ia] = 0.0; zl[ib] = 0.0;
@@ -882,13 +890,13 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
   };
   // every CTA's window onto this shared memory layout (the mapping only adds a per-CTA base: one mapa per peer, once,
   // instead of two in front of every store)
-  uint32_t rbase[kPcgClusterMaxCtas];
+  uint32_t rbase[MAXG];
 #pragma unroll
-  for (int k = 0; k < kPcgClusterMaxCtas; ++k) rbase[k] = cluster_map_u32(sm, min(k, G - 1)) - smem_u32(sm);
+  for (int k = 0; k < MAXG; ++k) rbase[k] = cluster_map_u32(sm, min(k, G - 1)) - smem_u32(sm);
   auto push_to = [&](int buf, const double* dst, double v) {   // a value into every CTA's copy of *dst, counted on its barrier
     const uint32_t a = smem_u32(dst), b = smem_u32(bars + buf);
 #pragma unroll
-    for (int k = 0; k < kPcgClusterMaxCtas; ++k)
+    for (int k = 0; k < MAXG; ++k)
       if (k < G) st_async_f64(a + rbase[k], v, b + rbase[k]);
   };
   auto push = [&](int buf, int i, double v) { push_to(buf, u_buf + (size_t)buf * n + row0 + i, v); };
@@ -910,12 +918,12 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
         for (int k = 0; k < 4; ++k) {
           const int q = 8 * c + 2 * k;
           wa0 = fma(sa[q], uu[k].x, wa0); wa1 = fma(sa[q + 1], uu[k].y, wa1);
-          wb0 = fma(sb[q], uu[k].x, wb0); wb1 = fma(sb[q + 1], uu[k].y, wb1);
+          if constexpr (NRL == 2) { wb0 = fma(sb[q], uu[k].x, wb0); wb1 = fma(sb[q + 1], uu[k].y, wb1); }
         }
       }
     }
     part[wid * 64 + ia] = wa0 + wa1;
-    part[wid * 64 + ib] = wb0 + wb1;
+    if constexpr (NRL == 2) part[wid * 64 + ib] = wb0 + wb1;
   };
   auto summed_product = [&](int i) {                  // (after a block barrier) the eight partials of row i, in warp order
     const double* q = part + i;
@@ -953,23 +961,31 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
           const double ra = rl[ia], rb = rl[ib], ua = ul[ia], ub = ul[ib], wa = wl[ia], wb = wl[ib];
           double gam_p = fma(ra, ua, rb * ub), del_p = fma(wa, ua, wb * ub), rr_p = fma(ra, ra, rb * rb);
           warp_sum3(gam_p, del_p, rr_p);
-          if (lane < 3 * G) {
-            const int k = lane / 3, which = lane - 3 * k;
-            const double v = which == 0 ? gam_p : (which == 1 ? del_p : rr_p);
-            const uint32_t rk = cluster_map_u32(sm, k) - smem_u32(sm);
-            st_async_f64(smem_u32(pch + buf * 24 + which * 8 + g) + rk, v, smem_u32(bars + buf) + rk);
+#pragma unroll
+          for (int e0 = 0; e0 < 3 * MAXG; e0 += 32) {
+            const int e = e0 + lane;
+            if (e < 3 * G) {
+              const int k = e / 3, which = e - 3 * k;
+              const double v = which == 0 ? gam_p : (which == 1 ? del_p : rr_p);
+              const uint32_t rk = cluster_map_u32(sm, k) - smem_u32(sm);
+              st_async_f64(smem_u32(pch + buf * 3 * MAXG + which * MAXG + g) + rk, v, smem_u32(bars + buf) + rk);
+            }
           }
         } else {
           if (wid == 0 && lane == 0) mbar_expect_tx(bars + buf, (uint32_t)(8 * (n + 3 * G)));
-          const int i = (wid == 2 || wid == 4) ? ib : ia;
-          const int k0 = wid >= 3 ? 4 : 0;                 // first peer of this warp's half
+          // publisher p = 0..3 (warps 0, 2, 3, 4).  Two rows per lane: rows lane (p even) / lane + 32 (p odd), peers in
+          // two halves; one row per lane: the peers in four quarters
+          const int pidx = wid == 0 ? 0 : wid - 1;
+          constexpr int PN = NRL == 2 ? MAXG / 2 : MAXG / 4;   // peers per publisher
+          const int i = (NRL == 2 && (pidx & 1)) ? ib : ia;
+          const int k0 = (NRL == 2 ? (pidx >> 1) : pidx) * PN;
           if (i < R && k0 < G) {
             const double m = minv_row(i, wl);              // m = M^-1 w
-            if (wid <= 2) ml[i] = m;
+            if (NRL == 2 ? pidx < 2 : pidx == 0) ml[i] = m;
             const uint32_t a = smem_u32(u_buf + (size_t)buf * n + row0 + i), bb = smem_u32(bars + buf);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              if (k0 + k < G) st_async_f64(a + rbase[k0 + k], m, bb + rbase[k0 + k]);
+            for (int k = 0; k < MAXG; ++k)
+              if (k >= k0 && k < k0 + PN && k < G) st_async_f64(a + rbase[k], m, bb + rbase[k]);
           }
         }
       }
@@ -978,12 +994,12 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
       // (all 24 loads first, whatever G: with a branch per CTA the loop was eight load -> add round trips)
       double gamma = 0.0, delta = 0.0, rr = 0.0;
       {
-        double pv[24];
+        double pv[3 * MAXG];
 #pragma unroll
-        for (int k = 0; k < 24; ++k) pv[k] = pch[buf * 24 + k];
+        for (int k = 0; k < 3 * MAXG; ++k) pv[k] = pch[buf * 3 * MAXG + k];
 #pragma unroll
-        for (int k = 0; k < kPcgClusterMaxCtas; ++k) {
-          gamma += k < G ? pv[k] : 0.0; delta += k < G ? pv[8 + k] : 0.0; rr += k < G ? pv[16 + k] : 0.0;
+        for (int k = 0; k < MAXG; ++k) {
+          gamma += k < G ? pv[k] : 0.0; delta += k < G ? pv[MAXG + k] : 0.0; rr += k < G ? pv[2 * MAXG + k] : 0.0;
         }
       }
       if (it == 0) {
@@ -1003,7 +1019,7 @@ __global__ void __launch_bounds__(kPcgThreads, 1) ba_pcg_cluster_kernel(PcgArgs 
       inv_gamma_old = fast_rcp(gamma); pap_old = pap;
       __syncthreads();
       if (status == 1) break;                          // (uniform: every thread of every CTA has the same scalars)
-      if (wid == 0 || wid == 2) {                      // the recurrences: warp 0 rows 0..31, warp 2 rows 32..47
+      if (wid == 0 || (NRL == 2 && wid == 2)) {        // the recurrences: warp 0 rows 0..31, warp 2 rows 32..47
         // (every load ahead of the first store: the arrays may alias as far as the compiler knows, and
         //  load -> FMA -> store -> load ... chains made this 640 cycles)
         const int i = wid == 0 ? ia : ib;
