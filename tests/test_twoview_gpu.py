@@ -143,6 +143,27 @@ def test_batched_pairs_with_ragged_sizes_equal_single_calls():
         assert not out["mask"][b, ns[b]:].any()
 
 
+def test_recover_pose_of_a_batch_equals_pair_by_pair():
+    """A batch of pairs with ragged sizes against the same pairs one by one: same bits."""
+    B, n_max = 40, 96
+    rng = np.random.default_rng(5)
+    ns = rng.integers(8, n_max + 1, size=B)
+    p1 = np.zeros((B, n_max, 2), np.float32); p2 = np.zeros((B, n_max, 2), np.float32)
+    E = np.zeros((B, 3, 3))
+    for b in range(B):
+        a, c, R, t, _ = synth.two_view_pair(100 + b, n_max)
+        p1[b], p2[b] = a, c
+        tx = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]])
+        E[b] = (tx @ R) / np.linalg.norm(tx @ R)
+    n_pts = torch.from_numpy(ns.astype(np.int32)).cuda()
+    Ed = torch.from_numpy(E).cuda()
+    got = twoview.recover_pose_batch(Ed, _dev(p1), _dev(p2), n_pts, K, 50.0)
+    for b in range(0, B, 7):
+        one = twoview.recover_pose_batch(Ed[b:b + 1], _dev(p1[b:b + 1]), _dev(p2[b:b + 1]), n_pts[b:b + 1], K, 50.0)
+        for key in ("R", "t", "mask", "good", "tri"):
+            assert torch.equal(one[key][0], got[key][b]), (key, b)
+
+
 def test_drop_in_signatures_and_golden_g1():
     g = np.load(G1)
     # estimateRelativePose on the notebook's E and inliers (normalised coordinates, identity camera)
