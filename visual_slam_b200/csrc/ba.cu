@@ -245,6 +245,11 @@ static cudaError_t pcg_cluster_kernel_allow_max_smem(int kind) {
   return cudaFuncSetAttribute(pcg_cluster_fn(kind), cudaFuncAttributeMaxDynamicSharedMemorySize,
                               max_smem - (int)fa.sharedSizeBytes);
 }
+// n <= 64: the pipelined single-CTA kernel unless VSLAM_BA_PCG_SMALL_PIPELINED=0
+static PcgClusterFn pcg_small_fn() {
+  static const bool pipelined = [] { const char* e = getenv("VSLAM_BA_PCG_SMALL_PIPELINED"); return !(e && atoi(e) == 0); }();
+  return pipelined ? ba_pcg_small_pipelined_kernel : ba_pcg_small_kernel;
+}
 static size_t pcg_small_smem(int n) { return sizeof(double) * ((size_t)n * n + 6 * (size_t)n + 16 * 64); }   // S, M^-1, r/u copies, partials
 
 static void counting_sort(const std::vector<int>& in, const int* key, int n_keys, std::vector<int>& out) {
@@ -807,7 +812,7 @@ static int enqueue_trial(BA& B, cudaStream_t st, bool speculative = false) {
       BA_TRY(cudaLaunchCooperativeKernel((void*)ba_pcg_kernel, dim3(B.pcg_G), dim3(kPcgThreads), args,
                                          B.pcg_smem, st));
     } else if (B.n <= kPcgSmallMax) {
-      launch_step_kernel(ba_pcg_small_kernel, 1, kPcgSmallThreads, pcg_small_smem(B.n), st, A);
+      launch_step_kernel(pcg_small_fn(), 1, kPcgSmallThreads, pcg_small_smem(B.n), st, A);
     } else if (B.n <= kPcgMidMax) {
       launch_step_kernel(ba_pcg_mid_kernel, 1, kPcgMidThreads, kPcgMidSmemDoubles * sizeof(double), st, A);
     } else {
@@ -1313,7 +1318,7 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
   A.slab_in_smem = smem_slab <= 200 * 1024;
   size_t smem = A.slab_in_smem ? smem_slab : smem_noslab;
   BA_TRY(pcg_kernel_allow_max_smem());
-  if (n <= kPcgSmallMax) ba_pcg_small_kernel<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
+  if (n <= kPcgSmallMax) pcg_small_fn()<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
   else if (n <= kPcgMidMax && n % 6 == 0) ba_pcg_mid_kernel<<<1, kPcgMidThreads, kPcgMidSmemDoubles * sizeof(double), st>>>(A);
   else ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
   int rc = check_launch("ba_pcg_kernel");
@@ -1476,7 +1481,7 @@ extern "C" int vslam_pcg_solve_static(const double* S, const double* b, double* 
   A.w_loc = A.p_glob + kPcgStaticMaxN;
   A.status = status_iters_dev; A.iters = status_iters_dev + 1;         // outputs go straight to the caller's device buffer
   if (n <= kPcgSmallMax) {
-    ba_pcg_small_kernel<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
+    pcg_small_fn()<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
     return check_launch("ba_pcg_small_kernel");
   }
   if (n <= kPcgMidMax && n % 6 == 0) {

@@ -610,6 +610,162 @@ __global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_kernel(PcgArgs 
   }
 }
 
+// The same single-CTA layout running the PIPELINED recurrences (Ghysels-Vanroose, as in ba_pcg_kernel): the three dot
+// products of an iteration do not depend on its matrix-vector product n = S (M^-1 w), so the five butterfly stages of
+// their warp reduction -- a shuffle round trip each, ~350 cycles of an iteration's ~760 -- are written BETWEEN the
+// phases of the product (shuffles issued, a phase of the product, then the additions): shuffles and barriers keep
+// their program order, so the overlap has to be in the source.
+__global__ void __launch_bounds__(kPcgSmallThreads) ba_pcg_small_pipelined_kernel(PcgArgs A) {
+  extern __shared__ __align__(16) double sm[];
+  pdl_wait();
+  pdl_trigger();
+  if (A.done != nullptr && *A.done) return;
+  const int n = A.n, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  double* minv = sm + n * n;                        // (same shared-memory layout as ba_pcg_small_kernel)
+  double* rs = minv + 6 * n + wid * 64;             // [warps][64] each warp's own copy of w
+  double* us = minv + 6 * n + (kPcgSmallWarps + wid) * 64;   // [warps][64] ... of m
+  double* part = minv + 6 * n + 2 * kPcgSmallWarps * 64;     // [2][warps][64]
+  const int i0 = lane, i1 = lane + 32;
+  const bool h0 = i0 < n, h1 = i1 < n;
+  const int cols = ((n + 7) / 8) * 2;
+  const int j0 = min(n, wid * cols), j1 = min(n, j0 + cols);
+  double sr0[16], sr1[16];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) {
+    const int j = j0 + q;
+    sr0[q] = (j < j1 && h0) ? __ldcg(A.S + (size_t)j * n + i0) : 0.0;
+    sr1[q] = (j < j1 && h1) ? __ldcg(A.S + (size_t)j * n + i1) : 0.0;
+  }
+  int fail = 0;
+  if (threadIdx.x < n / 6) {
+    const int bi = threadIdx.x;
+    double blk[36];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) blk[6 * i + j] = __ldcg(A.S + (size_t)(6 * bi + i) * n + 6 * bi + j);
+    }
+    if (!spd6_inverse(blk)) fail = 1;
+#pragma unroll
+    for (int i = 0; i < 36; ++i) minv[36 * bi + i] = blk[i];
+  }
+  rs[lane] = 0.0; rs[lane + 32] = 0.0; us[lane] = 0.0; us[lane + 32] = 0.0;
+  fail = __syncthreads_or(fail);
+  double m0[6], m1[6];
+  const int b0 = h0 ? i0 / 6 : 0, b1 = h1 ? i1 / 6 : 0;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    m0[k] = h0 ? minv[36 * b0 + 6 * (i0 - 6 * b0) + k] : 0.0;
+    m1[k] = h1 ? minv[36 * b1 + 6 * (i1 - 6 * b1) + k] : 0.0;
+  }
+  const double* ra = rs + 6 * b0;
+  const double* rb = rs + 6 * b1;
+  int buf = 0;
+  // y = M^-1 v (rows of this lane) through the warp's own copy of v; then this warp's part of S y into part[buf]
+  auto apply_minv = [&](double v0, double v1, double& y0, double& y1) {
+    rs[i0] = v0; rs[i1] = v1;
+    __syncwarp();
+    y0 = (m0[0] * ra[0] + m0[1] * ra[1]) + (m0[2] * ra[2] + m0[3] * ra[3]) + (m0[4] * ra[4] + m0[5] * ra[5]);
+    y1 = (m1[0] * rb[0] + m1[1] * rb[1]) + (m1[2] * rb[2] + m1[3] * rb[3]) + (m1[4] * rb[4] + m1[5] * rb[5]);
+  };
+  auto publish = [&](double y0, double y1) {
+    us[i0] = y0; us[i1] = y1;
+    __syncwarp();
+  };
+  auto product_half = [&](int qa, int qb, double& wa, double& wb, double& wc, double& wd) {
+#pragma unroll
+    for (int q = qa; q < qb; ++q) {                 // (entries beyond the column range are zero, the vector beyond n is zero)
+      const int j = min(j0 + 2 * q, 62);
+      const double ua = us[j], ub = us[j + 1];
+      wa = fma(sr0[2 * q], ua, wa); wb = fma(sr0[2 * q + 1], ub, wb);
+      wc = fma(sr1[2 * q], ua, wc); wd = fma(sr1[2 * q + 1], ub, wd);
+    }
+  };
+  auto store_partial = [&](double wa, double wb, double wc, double wd) {
+    double* pw = part + (buf * kPcgSmallWarps + wid) * 64;
+    pw[i0] = h0 ? wa + wb : 0.0;
+    pw[i1] = h1 ? wc + wd : 0.0;
+  };
+  auto summed = [&](double& y0, double& y1) {        // (after the block barrier) the four partials, in warp order
+    const double* pr = part + buf * kPcgSmallWarps * 64;
+    buf ^= 1;
+    y0 = (pr[i0] + pr[64 + i0]) + (pr[128 + i0] + pr[192 + i0]);
+    y1 = (pr[i1] + pr[64 + i1]) + (pr[128 + i1] + pr[192 + i1]);
+  };
+  double x0 = 0.0, x1 = 0.0, p0 = 0.0, p1 = 0.0, s0 = 0.0, s1 = 0.0, q0 = 0.0, q1 = 0.0, z0 = 0.0, z1 = 0.0;
+  double r0 = h0 ? A.b[i0] : 0.0, r1 = h1 ? A.b[i1] : 0.0;
+  double u0 = 0.0, u1 = 0.0, w0 = 0.0, w1 = 0.0;
+  int status = fail ? 1 : 2, it = 0;
+  double inv_gamma_old = 0.0, pap_old = 0.0, thresh = 0.0;
+  if (!fail) {
+    apply_minv(r0, r1, u0, u1);                      // u = M^-1 r
+    __syncwarp();
+    publish(u0, u1);
+    {
+      double wa = 0.0, wb = 0.0, wc = 0.0, wd = 0.0;
+      product_half(0, 8, wa, wb, wc, wd);
+      store_partial(wa, wb, wc, wd);
+    }
+    __syncthreads();
+    summed(w0, w1);                                  // w = S u
+    for (it = 0;; ++it) {
+      double gamma = r0 * u0 + r1 * u1, delta = w0 * u0 + w1 * u1, rr = r0 * r0 + r1 * r1;
+      double ta, tb, tc, mm0, mm1, wa = 0.0, wb = 0.0, wc = 0.0, wd = 0.0;
+#define VSLAM_BFLY_ISSUE(o) ta = __shfl_xor_sync(0xffffffffu, gamma, o); tb = __shfl_xor_sync(0xffffffffu, delta, o); \
+                            tc = __shfl_xor_sync(0xffffffffu, rr, o);
+#define VSLAM_BFLY_ADD() gamma += ta; delta += tb; rr += tc;
+      __syncwarp();                                  // (the previous iteration's reads of rs / us are done)
+      VSLAM_BFLY_ISSUE(16)
+      apply_minv(w0, w1, mm0, mm1);                  // m = M^-1 w
+      VSLAM_BFLY_ADD()
+      VSLAM_BFLY_ISSUE(8)
+      publish(mm0, mm1);
+      VSLAM_BFLY_ADD()
+      VSLAM_BFLY_ISSUE(4)
+      product_half(0, 4, wa, wb, wc, wd);
+      VSLAM_BFLY_ADD()
+      VSLAM_BFLY_ISSUE(2)
+      product_half(4, 8, wa, wb, wc, wd);
+      VSLAM_BFLY_ADD()
+      VSLAM_BFLY_ISSUE(1)
+      store_partial(wa, wb, wc, wd);
+      VSLAM_BFLY_ADD()
+#undef VSLAM_BFLY_ISSUE
+#undef VSLAM_BFLY_ADD
+      __syncthreads();
+      double n0, n1;
+      summed(n0, n1);                                // n = S m
+      if (it == 0) {
+        if (!(rr > 0.0)) { status = 0; break; }      // b == 0: x = 0
+        thresh = A.tol * A.tol * rr;
+      }
+      if (rr <= thresh && it > 0) { status = 0; break; }
+      if (it == A.max_iter) break;
+      double beta = 0.0, pap = delta;
+      if (it > 0) {
+        beta = gamma * inv_gamma_old;
+        pap = delta - beta * beta * pap_old;           // = p^T S p in exact arithmetic
+      }
+      if (!(pap > 1e-290) || !(pap < 1e290) || !(gamma > 1e-290) || !(gamma < 1e290)) { status = 1; break; }
+      const double alpha = gamma * fast_rcp(pap);
+      inv_gamma_old = fast_rcp(gamma); pap_old = pap;
+      z0 = n0 + beta * z0; z1 = n1 + beta * z1;
+      q0 = mm0 + beta * q0; q1 = mm1 + beta * q1;
+      s0 = w0 + beta * s0; s1 = w1 + beta * s1;
+      p0 = u0 + beta * p0; p1 = u1 + beta * p1;
+      x0 += alpha * p0; x1 += alpha * p1;
+      r0 -= alpha * s0; r1 -= alpha * s1;
+      u0 -= alpha * q0; u1 -= alpha * q1;
+      w0 -= alpha * z0; w1 -= alpha * z1;
+    }
+  }
+  if (wid == 0) {
+    if (h0) A.x[i0] = (status == 1) ? 0.0 : x0;
+    if (h1) A.x[i1] = (status == 1) ? 0.0 : x1;
+    if (lane == 0) { *A.status = status; *A.iters = it; }
+  }
+}
+
 // Systems of 11 .. 21 free cameras (64 < n <= kPcgMidMax): the single-CTA kernel above with four rows per lane and
 // eight warps, i.e. S (<= 128 x 128) still lives in registers for the whole solve -- 64 doubles per thread -- and an
 // iteration still costs one block barrier.  The cooperative multi-CTA kernel pays a grid barrier and a gather through
