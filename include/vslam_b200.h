@@ -353,7 +353,9 @@ int vslam_ba_set_solver(vslam_ba* ba, double pcg_tol, int pcg_max_iter);
  * register-resident Gauss-Jordan elimination for n <= 63, shared-memory LDL^T above; 3 = the LDL^T kernel at every
  * n <= 96.  A non-positive pivot / curvature is reported the same way by all (rejected LM step).  Measured on B200
  * at n = 54 (C3): PCG 8-12 us per solve (its matrix entries live in registers), Gauss-Jordan 17 us, LDL^T 33 us;
- * C3 as a whole 20.3k / 18.7k / 12k LM iterations per second. */
+ * C3 as a whole 20.6k / 18.7k / 12k LM iterations per second.  The PCG runs one of four kernels by n: one CTA with the
+ * matrix in registers (n <= 64, n <= 128), one thread-block cluster exchanging through distributed shared memory
+ * (n <= 480 where the device places the cluster), a cooperative multi-CTA kernel beyond. */
 int vslam_ba_set_linear_solver(vslam_ba* ba, int kind);
 
 /*
