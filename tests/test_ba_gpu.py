@@ -207,19 +207,20 @@ def test_pcg_solves_spd_systems():
     rng = np.random.default_rng(0)
     # 6 .. 60: single CTA, two rows per lane; 66 .. 126: single CTA, four rows per lane (S in registers in both);
     # beyond: the general kernel
-    for n in (6, 54, 60, 66, 72, 96, 102, 126, 132, 300):
+    # 132 .. 384 / .. 480: one thread-block cluster of <= 8 / 16 CTAs (both instances, ragged last CTAs included)
+    for n in (6, 54, 60, 66, 72, 96, 102, 126, 132, 150, 240, 246, 300, 384, 390, 444, 480, 486, 600):
         A = rng.normal(size=(n, n)); S = A @ A.T + n * np.eye(n); b = rng.normal(size=n)
         x, status, iters = pcg_solve(torch.from_numpy(S).cuda(), torch.from_numpy(b).cuda(), 1e-12, 5000)
         assert status == 0 and iters <= 5000
         assert np.abs(S @ x.cpu().numpy() - b).max() <= 1e-9 * np.abs(b).max()
-    # an indefinite system and a zero right-hand side at the four-rows-per-lane size
-    n = 96
-    A = rng.normal(size=(n, n)); S = A @ A.T + n * np.eye(n); S[7, 7] = -5.0
-    _, status, _ = pcg_solve(torch.from_numpy(S).cuda(), torch.from_numpy(rng.normal(size=n)).cuda(), 1e-12, 500)
-    assert status == 1
-    S[7, 7] = 500.0
-    x, status, iters = pcg_solve(torch.from_numpy(S).cuda(), torch.zeros(n, dtype=torch.float64).cuda(), 1e-12, 500)
-    assert status == 0 and iters == 0 and float(x.abs().max()) == 0.0
+    # an indefinite system and a zero right-hand side at the four-rows-per-lane size and at the two cluster sizes
+    for n in (96, 210, 420):
+        A = rng.normal(size=(n, n)); S = A @ A.T + n * np.eye(n); S[7, 7] = -5.0
+        _, status, _ = pcg_solve(torch.from_numpy(S).cuda(), torch.from_numpy(rng.normal(size=n)).cuda(), 1e-12, 500)
+        assert status == 1
+        S[7, 7] = 500.0
+        x, status, iters = pcg_solve(torch.from_numpy(S).cuda(), torch.zeros(n, dtype=torch.float64).cuda(), 1e-12, 500)
+        assert status == 0 and iters == 0 and float(x.abs().max()) == 0.0
 
 
 def test_rejected_step_leaves_state_untouched_and_lambda_grows():

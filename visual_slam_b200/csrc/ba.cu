@@ -7,6 +7,8 @@
 #include <cstring>
 #include <utility>
 #include <limits>
+#include <mutex>
+#include <unordered_map>
 #include <vector>
 
 #include "ba_kernels.cuh"
@@ -244,6 +246,81 @@ static cudaError_t pcg_cluster_kernel_allow_max_smem(int kind) {
   }
   return cudaFuncSetAttribute(pcg_cluster_fn(kind), cudaFuncAttributeMaxDynamicSharedMemorySize,
                               max_smem - (int)fa.sharedSizeBytes);
+}
+// Plan of the cluster PCG for a system of nb camera blocks (n = 6 nb): which instance, camera blocks per CTA, CTAs, shared
+// memory -- or kind 0 when n is out of its range, the switch is off or the device does not place such a cluster.
+struct PcgClusterPlan { int kind = 0, blocks = 0, ctas = 0; size_t smem = 0; };
+static PcgClusterPlan pcg_cluster_plan_uncached(int nb, size_t budget);
+static PcgClusterPlan pcg_cluster_plan(int nb, size_t budget) {
+  // (per device and size: the occupancy query and the attribute calls are host work a serving loop should pay once)
+  static std::mutex mu;
+  static std::unordered_map<long long, PcgClusterPlan> cache;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const long long key = ((long long)dev << 32) | (unsigned)nb;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+  }
+  const PcgClusterPlan P = pcg_cluster_plan_uncached(nb, budget);
+  std::lock_guard<std::mutex> lock(mu);
+  cache[key] = P;
+  return P;
+}
+static PcgClusterPlan pcg_cluster_plan_uncached(int nb, size_t budget) {
+  PcgClusterPlan P;
+  const int n = 6 * nb;
+  static const int cluster_env = [] { const char* e = getenv("VSLAM_BA_PCG_CLUSTER"); return e ? atoi(e) : -1; }();
+  // (measured: up to 40 free cameras, where eight CTAs need one row per lane, the two are level or <2, 48, 8> ahead;
+  //  beyond, sixteen CTAs of one row per lane win: 44 cameras 10.5k -> 11.3k LM it/s, 59 cameras 9.9k -> 10.4k)
+  const int first_kind = nb > 40 ? 2 : 1;
+  for (int pass = 0; pass < 2 && !P.kind; ++pass) {
+    const int kind = pass == 0 ? first_kind : 3 - first_kind;
+    if (cluster_env == 0 || (cluster_env > 0 && cluster_env != kind)) continue;
+    const int max_ctas = pcg_cluster_max_ctas(kind);
+    const int max_rows = kind == 2 ? kPcgCluster16MaxRows : kPcgClusterMaxRows;
+    const int max_n = kind == 2 ? kPcgCluster16MaxN : kPcgClusterMaxN;
+    if (n <= kPcgMidMax || n > max_n) continue;
+    const int t = (nb + max_ctas - 1) / max_ctas;
+    const size_t need = pcg_cluster_smem_doubles(n, 6 * t, max_ctas) * sizeof(double);
+    if (6 * t > max_rows || need > budget || pcg_cluster_kernel_allow_max_smem(kind) != cudaSuccess) { cudaGetLastError(); continue; }
+    // the device must be able to place such a cluster (partitioned or partly busy devices may not): else the
+    // cooperative kernel takes the system
+    cudaLaunchConfig_t cfg = {};
+    const int Gc = (nb + t - 1) / t;
+    cfg.gridDim = dim3(Gc); cfg.blockDim = dim3(kPcgThreads); cfg.dynamicSmemBytes = need;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)Gc; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    int n_clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&n_clusters, pcg_cluster_fn(kind), &cfg) == cudaSuccess && n_clusters >= 1) {
+      P.kind = kind; P.blocks = t; P.ctas = Gc; P.smem = need;
+    } else {
+      cudaGetLastError();
+    }
+  }
+  return P;
+}
+static cudaError_t launch_pcg_cluster(int kind, int ctas, size_t smem, const PcgArgs& A, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(kPcgThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)ctas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cap);
+  cfg.attrs = attr; cfg.numAttrs = (use_pdl() && cap == cudaStreamCaptureStatusNone) ? 2 : 1;
+  return cudaLaunchKernelEx(&cfg, pcg_cluster_fn(kind), A);
+}
+static size_t pcg_smem_budget() {
+  int max_smem = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  return (size_t)std::max(max_smem - 2048, 16384);
 }
 // n <= 64: the pipelined single-CTA kernel unless VSLAM_BA_PCG_SMALL_PIPELINED=0
 static PcgClusterFn pcg_small_fn() {
@@ -635,38 +712,11 @@ static int ba_build(BA& B, int C, int P, int N, int E, const int32_t* obs_cam, c
       const int t = std::atoi(e);
       if (t >= bpc && t <= nb && smem_for(6 * t, true) <= budget) best = t;
     }
-    // 22 .. 64 free cameras: one thread-block cluster of <= 8 CTAs (ba_pcg_cluster_kernel), exchange through DSMEM;
-    // 65 .. 80: sixteen CTAs where the device places such a cluster
-    static const int cluster_env = [] { const char* e = getenv("VSLAM_BA_PCG_CLUSTER"); return e ? atoi(e) : -1; }();
-    B.pcg_cluster = 0;
-    // (measured: up to 40 free cameras, where eight CTAs need one row per lane, the two are level or <2, 48, 8> ahead;
-    //  beyond, sixteen CTAs of one row per lane win: 44 cameras 10.5k -> 11.3k LM it/s, 59 cameras 9.9k -> 10.4k)
-    const int first_kind = nb > 40 ? 2 : 1;
-    for (int pass = 0; pass < 2 && !B.pcg_cluster; ++pass) {
-      const int kind = pass == 0 ? first_kind : 3 - first_kind;
-      if (cluster_env == 0 || (cluster_env > 0 && cluster_env != kind)) continue;
-      const int max_ctas = pcg_cluster_max_ctas(kind);
-      const int max_rows = kind == 2 ? kPcgCluster16MaxRows : kPcgClusterMaxRows;
-      const int max_n = kind == 2 ? kPcgCluster16MaxN : kPcgClusterMaxN;
-      if (B.n <= kPcgMidMax || B.n > max_n) continue;
-      const int t = (nb + max_ctas - 1) / max_ctas;
-      const size_t need = pcg_cluster_smem_doubles(B.n, 6 * t, max_ctas) * sizeof(double);
-      if (6 * t > max_rows || need > budget || pcg_cluster_kernel_allow_max_smem(kind) != cudaSuccess) { cudaGetLastError(); continue; }
-      // the device must be able to place such a cluster (partitioned or partly busy devices may not): else the
-      // cooperative kernel takes the system
-      cudaLaunchConfig_t cfg = {};
-      const int Gc = (nb + t - 1) / t;
-      cfg.gridDim = dim3(Gc); cfg.blockDim = dim3(kPcgThreads); cfg.dynamicSmemBytes = need;
-      cudaLaunchAttribute attr[1];
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = (unsigned)Gc; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr; cfg.numAttrs = 1;
-      int n_clusters = 0;
-      if (cudaOccupancyMaxActiveClusters(&n_clusters, pcg_cluster_fn(kind), &cfg) == cudaSuccess && n_clusters >= 1) {
-        best = t; B.pcg_cluster = kind;
-      } else {
-        cudaGetLastError();
-      }
+    // 22 .. 80 free cameras: one thread-block cluster (ba_pcg_cluster_kernel), exchange through DSMEM
+    {
+      const PcgClusterPlan P = pcg_cluster_plan(nb, budget);
+      B.pcg_cluster = P.kind;
+      if (P.kind) best = P.blocks;
     }
     B.pcg_slab = smem_for(6 * best, true) <= budget ? 1 : 0;
     B.pcg_rows = 6 * std::max(best, 1);
@@ -797,17 +847,7 @@ static int enqueue_trial(BA& B, cudaStream_t st, bool speculative = false) {
     A.pipelined = (pipelined && B.pcg_G > 1) ? 1 : 0;
     void* args[] = {&A};
     if (B.pcg_cluster) {
-      cudaLaunchConfig_t cfg = {};
-      cfg.gridDim = dim3(B.pcg_G); cfg.blockDim = dim3(kPcgThreads); cfg.dynamicSmemBytes = B.pcg_smem; cfg.stream = st;
-      cudaLaunchAttribute attr[2];
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = (unsigned)B.pcg_G; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-      attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-      attr[1].val.programmaticStreamSerializationAllowed = 1;
-      cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-      cudaStreamIsCapturing(st, &cap);
-      cfg.attrs = attr; cfg.numAttrs = (use_pdl() && cap == cudaStreamCaptureStatusNone) ? 2 : 1;
-      BA_TRY(cudaLaunchKernelEx(&cfg, pcg_cluster_fn(B.pcg_cluster), A));
+      BA_TRY(launch_pcg_cluster(B.pcg_cluster, B.pcg_G, B.pcg_smem, A, st));
     } else if (B.pcg_G > 1) {
       BA_TRY(cudaLaunchCooperativeKernel((void*)ba_pcg_kernel, dim3(B.pcg_G), dim3(kPcgThreads), args,
                                          B.pcg_smem, st));
@@ -1320,7 +1360,16 @@ extern "C" int vslam_pcg_solve(const double* S, const double* b, double* x, int 
   BA_TRY(pcg_kernel_allow_max_smem());
   if (n <= kPcgSmallMax) pcg_small_fn()<<<1, kPcgSmallThreads, pcg_small_smem(n), st>>>(A);
   else if (n <= kPcgMidMax && n % 6 == 0) ba_pcg_mid_kernel<<<1, kPcgMidThreads, kPcgMidSmemDoubles * sizeof(double), st>>>(A);
-  else ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
+  else {
+    // (n is a multiple of 6, checked above) the thread-block cluster kernel where it applies, as inside the BA engine
+    const PcgClusterPlan P = pcg_cluster_plan(n / 6, pcg_smem_budget());
+    if (P.kind) {
+      A.rows = 6 * P.blocks; A.G = P.ctas;
+      BA_TRY(launch_pcg_cluster(P.kind, P.ctas, P.smem, A, st));
+    } else {
+      ba_pcg_kernel<<<1, kPcgThreads, smem, st>>>(A);
+    }
+  }
   int rc = check_launch("ba_pcg_kernel");
   if (rc) return rc;
   int host[4];
@@ -1487,6 +1536,14 @@ extern "C" int vslam_pcg_solve_static(const double* S, const double* b, double* 
   if (n <= kPcgMidMax && n % 6 == 0) {
     ba_pcg_mid_kernel<<<1, kPcgMidThreads, kPcgMidSmemDoubles * sizeof(double), st>>>(A);
     return check_launch("ba_pcg_mid_kernel");
+  }
+  {
+    const PcgClusterPlan P = pcg_cluster_plan(n / 6, pcg_smem_budget());
+    if (P.kind) {
+      A.rows = 6 * P.blocks; A.G = P.ctas;
+      BA_TRY(launch_pcg_cluster(P.kind, P.ctas, P.smem, A, st));
+      return check_launch("ba_pcg_cluster_kernel");
+    }
   }
   const size_t smem_slab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8 + (size_t)n * n);
   const size_t smem_noslab = sizeof(double) * ((size_t)n + 12 * (size_t)n + 8);
